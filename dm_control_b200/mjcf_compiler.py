@@ -1,0 +1,1046 @@
+"""Host-side MJCF-subset compiler: XML string -> `FlatModel`.
+
+Stand-in for the reference's `mj_loadXML` call
+(/root/reference/dm_control/mujoco/wrapper/core.py:312-328), which lives in the
+closed MuJoCo 2.00 binary that is absent here.  Covers the MJCF
+subset the configured suite models use: <include>, nested
+<default class>/childclass, fromto, euler/zaxis/xyaxes/axisangle/quat, degrees,
+inertia from geoms, mass/density, settotalmass, <freejoint>, joint ref/springref,
+<motor>/<general>/<position>/<velocity>, sensors, keyframes, <option>/<flag>.
+
+Host only, runs once per model (cold path).  Compile rules are MuJoCo 2.0's
+documented ones [MJ-doc]; they are validated by tests/test_compiler.py and the
+known-answer tests of SURVEY §8c.
+"""
+
+import math
+import xml.etree.ElementTree as ET
+
+import numpy as np
+
+from dm_control_b200 import model as M
+
+# ----------------------------------------------------------------- math utils
+
+
+def _normalize(v):
+  v = np.asarray(v, dtype=np.float64)
+  n = np.linalg.norm(v)
+  if n < M.MINVAL:
+    raise ValueError("cannot normalize zero vector")
+  return v / n
+
+
+def quat_mul(a, b):
+  return np.array([
+      a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3],
+      a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2],
+      a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1],
+      a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0]])
+
+
+def quat_conj(q):
+  return np.array([q[0], -q[1], -q[2], -q[3]])
+
+
+def quat_to_mat(q):
+  w, x, y, z = q
+  return np.array([
+      [w * w + x * x - y * y - z * z, 2 * (x * y - w * z), 2 * (x * z + w * y)],
+      [2 * (x * y + w * z), w * w - x * x + y * y - z * z, 2 * (y * z - w * x)],
+      [2 * (x * z - w * y), 2 * (y * z + w * x), w * w - x * x - y * y + z * z]])
+
+
+def mat_to_quat(R):
+  """Rotation matrix -> unit quaternion (w >= 0 branch-stable)."""
+  t = np.trace(R)
+  if t > 0:
+    s = math.sqrt(t + 1.0) * 2
+    q = [0.25 * s, (R[2, 1] - R[1, 2]) / s, (R[0, 2] - R[2, 0]) / s,
+         (R[1, 0] - R[0, 1]) / s]
+  elif R[0, 0] > R[1, 1] and R[0, 0] > R[2, 2]:
+    s = math.sqrt(1.0 + R[0, 0] - R[1, 1] - R[2, 2]) * 2
+    q = [(R[2, 1] - R[1, 2]) / s, 0.25 * s, (R[0, 1] + R[1, 0]) / s,
+         (R[0, 2] + R[2, 0]) / s]
+  elif R[1, 1] > R[2, 2]:
+    s = math.sqrt(1.0 + R[1, 1] - R[0, 0] - R[2, 2]) * 2
+    q = [(R[0, 2] - R[2, 0]) / s, (R[0, 1] + R[1, 0]) / s, 0.25 * s,
+         (R[1, 2] + R[2, 1]) / s]
+  else:
+    s = math.sqrt(1.0 + R[2, 2] - R[0, 0] - R[1, 1]) * 2
+    q = [(R[1, 0] - R[0, 1]) / s, (R[0, 2] + R[2, 0]) / s,
+         (R[1, 2] + R[2, 1]) / s, 0.25 * s]
+  q = np.array(q)
+  return q / np.linalg.norm(q)
+
+
+def axisangle_to_quat(axis, angle):
+  axis = _normalize(axis)
+  return np.concatenate([[math.cos(angle / 2)], axis * math.sin(angle / 2)])
+
+
+def z_to_quat(vec):
+  """Quaternion rotating +z onto `vec` [MJ-doc: zaxis / fromto semantics]."""
+  vec = _normalize(vec)
+  axis = np.cross([0.0, 0.0, 1.0], vec)
+  s = np.linalg.norm(axis)
+  if s < 1e-10:
+    axis = np.array([1.0, 0.0, 0.0])
+  else:
+    axis = axis / s
+  ang = math.atan2(s, vec[2])
+  return np.concatenate([[math.cos(ang / 2)], axis * math.sin(ang / 2)])
+
+
+def rot_vec(q, v):
+  return quat_to_mat(q) @ np.asarray(v, dtype=np.float64)
+
+
+# ---------------------------------------------------------------- XML loading
+
+
+def _expand_includes(elem, assets):
+  """Replaces <include file=...> by the children of the included root
+  (cartpole.xml:2-4).  `assets` maps file name -> bytes/str, as the VFS of
+  core.py:209-259 does."""
+  out = []
+  for child in list(elem):
+    if child.tag == "include":
+      fname = child.get("file")
+      src = None
+      for key in (fname, fname.lstrip("./"), "./" + fname.lstrip("./")):
+        if key in assets:
+          src = assets[key]
+          break
+      if src is None:
+        raise ValueError("include file %r not found in assets" % fname)
+      if isinstance(src, bytes):
+        src = src.decode()
+      sub = ET.fromstring(src.rstrip("\0"))
+      _expand_includes(sub, assets)
+      out.extend(list(sub))
+    else:
+      _expand_includes(child, assets)
+      out.append(child)
+  for c in list(elem):
+    elem.remove(c)
+  for c in out:
+    elem.append(c)
+
+
+def _floats(s, n=None):
+  v = [float(x) for x in s.split()]
+  if n is not None and len(v) != n:
+    raise ValueError("expected %d numbers, got %r" % (n, s))
+  return v
+
+
+class _Defaults:
+  """One <default class=...> node: per-tag attribute dicts with inheritance."""
+
+  def __init__(self, name, parent=None):
+    self.name = name
+    self.attrs = {}
+    if parent is not None:
+      self.attrs = {t: dict(a) for t, a in parent.attrs.items()}
+
+  def update(self, tag, attrib):
+    self.attrs.setdefault(tag, {}).update(attrib)
+
+  def get(self, tag):
+    return self.attrs.get(tag, {})
+
+
+_ACT_TAGS = ("motor", "position", "velocity", "general", "cylinder", "muscle")
+
+
+def _parse_defaults(root):
+  classes = {"main": _Defaults("main")}
+
+  def rec(node, cur):
+    for ch in node:
+      if ch.tag == "default":
+        name = ch.get("class")
+        if name is None:
+          raise ValueError("nested <default> needs a class")
+        d = _Defaults(name, cur)
+        classes[name] = d
+        rec(ch, d)
+      else:
+        cur.update(ch.tag, ch.attrib)
+
+  for top in root.findall("default"):
+    cls = top.get("class", "main")
+    if cls != "main" and cls not in classes:
+      classes[cls] = _Defaults(cls, classes["main"])
+    rec(top, classes[cls if cls in classes else "main"])
+  return classes
+
+
+def _merged(elem, classes, childclass, tag=None):
+  """Element attributes with class defaults applied underneath."""
+  tag = tag or elem.tag
+  cls = elem.get("class") or childclass or "main"
+  if cls not in classes:
+    raise ValueError("unknown default class %r" % cls)
+  a = dict(classes[cls].get(tag))
+  a.update(elem.attrib)
+  return a
+
+
+# ------------------------------------------------------------- element compile
+
+
+class _Ctx:
+  def __init__(self):
+    self.degree = True
+    self.eulerseq = "xyz"
+    self.inertiafromgeom = "auto"
+    self.settotalmass = -1.0
+    self.boundmass = 0.0
+    self.boundinertia = 0.0
+    self.balanceinertia = False
+
+
+def _orientation(a, ctx):
+  """quat / axisangle / euler / xyaxes / zaxis -> unit quaternion."""
+  if "quat" in a:
+    return _normalize(_floats(a["quat"], 4))
+  if "axisangle" in a:
+    v = _floats(a["axisangle"], 4)
+    ang = math.radians(v[3]) if ctx.degree else v[3]
+    return axisangle_to_quat(v[:3], ang)
+  if "euler" in a:
+    e = _floats(a["euler"], 3)
+    if ctx.degree:
+      e = [math.radians(x) for x in e]
+    q = np.array([1.0, 0, 0, 0])
+    for ch, ang in zip(ctx.eulerseq, e):
+      ax = {"x": [1, 0, 0], "y": [0, 1, 0], "z": [0, 0, 1]}[ch.lower()]
+      r = axisangle_to_quat(ax, ang)
+      # lower case: intrinsic (rotating frame) -> post-multiply
+      q = quat_mul(q, r) if ch.islower() else quat_mul(r, q)
+    return _normalize(q)
+  if "xyaxes" in a:
+    v = _floats(a["xyaxes"], 6)
+    x = _normalize(v[:3])
+    y = np.array(v[3:])
+    y = _normalize(y - x * np.dot(x, y))
+    z = np.cross(x, y)
+    return mat_to_quat(np.stack([x, y, z], axis=1))
+  if "zaxis" in a:
+    return z_to_quat(_floats(a["zaxis"], 3))
+  return np.array([1.0, 0, 0, 0])
+
+
+def _geom_volume_inertia(gtype, size):
+  """Volume and unit-density diagonal inertia of a primitive in its own frame."""
+  if gtype == M.GEOM_SPHERE:
+    r = size[0]
+    v = 4.0 / 3.0 * math.pi * r ** 3
+    i = 2.0 / 5.0 * v * r * r
+    return v, np.array([i, i, i])
+  if gtype == M.GEOM_CAPSULE:
+    r, h = size[0], size[1]
+    vc = math.pi * r * r * 2 * h
+    vs = 4.0 / 3.0 * math.pi * r ** 3
+    ixx = vc * (3 * r * r + 4 * h * h) / 12.0 + vs * (
+        2.0 / 5.0 * r * r + h * h + 3.0 / 4.0 * h * r)
+    izz = vc * r * r / 2.0 + vs * 2.0 / 5.0 * r * r
+    return vc + vs, np.array([ixx, ixx, izz])
+  if gtype == M.GEOM_CYLINDER:
+    r, h = size[0], size[1]
+    v = math.pi * r * r * 2 * h
+    ixx = v * (3 * r * r + 4 * h * h) / 12.0
+    return v, np.array([ixx, ixx, v * r * r / 2.0])
+  if gtype == M.GEOM_BOX:
+    a, b, c = size
+    v = 8 * a * b * c
+    return v, v / 3.0 * np.array([b * b + c * c, a * a + c * c, a * a + b * b])
+  if gtype == M.GEOM_ELLIPSOID:
+    a, b, c = size
+    v = 4.0 / 3.0 * math.pi * a * b * c
+    return v, v / 5.0 * np.array([b * b + c * c, a * a + c * c, a * a + b * b])
+  return 0.0, np.zeros(3)
+
+
+def _rbound(gtype, size):
+  if gtype == M.GEOM_SPHERE:
+    return size[0]
+  if gtype == M.GEOM_CAPSULE:
+    return size[0] + size[1]
+  if gtype == M.GEOM_CYLINDER:
+    return math.hypot(size[0], size[1])
+  if gtype == M.GEOM_BOX:
+    return float(np.linalg.norm(size))
+  if gtype == M.GEOM_ELLIPSOID:
+    return float(max(size))
+  return 0.0
+
+
+def _compile_geom(a, ctx):
+  g = {}
+  g["name"] = a.get("name", "")
+  gtype = M.GEOM_TYPES[a.get("type", "sphere")]
+  g["type"] = gtype
+  size = _floats(a["size"]) if "size" in a else []
+  size = (size + [0.0, 0.0, 0.0])[:3]
+  pos = np.array(_floats(a.get("pos", "0 0 0"), 3))
+  quat = _orientation(a, ctx)
+  if "fromto" in a:
+    ft = np.array(_floats(a["fromto"], 6))
+    vec = ft[:3] - ft[3:]                     # [MJ-doc] z axis points to->from
+    size[1] = 0.5 * float(np.linalg.norm(vec))
+    pos = 0.5 * (ft[:3] + ft[3:])
+    quat = z_to_quat(vec)
+  g["size"] = np.array(size, dtype=np.float64)
+  g["pos"], g["quat"] = pos, quat
+  g["contype"] = int(a.get("contype", 1))
+  g["conaffinity"] = int(a.get("conaffinity", 1))
+  g["condim"] = int(a.get("condim", 3))
+  fr = _floats(a.get("friction", "1 0.005 0.0001"))
+  g["friction"] = np.array((fr + [0.005, 0.0001][len(fr) - 1:])[:3]
+                           if len(fr) < 3 else fr[:3])
+  g["solmix"] = float(a.get("solmix", 1))
+  g["solref"] = np.array(_floats(a.get("solref", "0.02 1"), 2))
+  si = _floats(a.get("solimp", "0.9 0.95 0.001 0.5 2"))
+  g["solimp"] = np.array((si + [0.9, 0.95, 0.001, 0.5, 2][len(si):])[:5])
+  g["margin"] = float(a.get("margin", 0))
+  g["gap"] = float(a.get("gap", 0))
+  g["group"] = int(a.get("group", 0))
+  g["rbound"] = _rbound(gtype, g["size"])
+  g["hfield"] = a.get("hfield")
+  # mass properties
+  vol, inertia = _geom_volume_inertia(gtype, g["size"])
+  if "mass" in a:
+    mass = float(a["mass"])
+    dens = mass / vol if vol > 0 else 0.0
+  else:
+    dens = float(a.get("density", 1000))
+    mass = dens * vol
+  g["mass"] = mass
+  g["inertia"] = inertia * dens
+  return g
+
+
+def _compile_site(a, ctx):
+  s = {"name": a.get("name", "")}
+  s["type"] = M.GEOM_TYPES[a.get("type", "sphere")]
+  size = _floats(a.get("size", "0.005"))
+  size = (size + [0.005, 0.005, 0.005][len(size):])[:3]
+  pos = np.array(_floats(a.get("pos", "0 0 0"), 3))
+  quat = _orientation(a, ctx)
+  if "fromto" in a:
+    ft = np.array(_floats(a["fromto"], 6))
+    vec = ft[:3] - ft[3:]
+    size[1] = 0.5 * float(np.linalg.norm(vec))
+    pos = 0.5 * (ft[:3] + ft[3:])
+    quat = z_to_quat(vec)
+  s["size"] = np.array(size)
+  s["pos"], s["quat"] = pos, quat
+  return s
+
+
+def _compile_joint(a, ctx, free=False):
+  j = {"name": a.get("name", "")}
+  jt = M.JNT_FREE if free else M.JNT_TYPES[a.get("type", "hinge")]
+  j["type"] = jt
+  j["pos"] = np.array(_floats(a.get("pos", "0 0 0"), 3))
+  j["axis"] = _normalize(_floats(a.get("axis", "0 0 1"), 3))
+  ang = ctx.degree and jt in (M.JNT_HINGE, M.JNT_BALL)
+  cv = math.radians if ang else (lambda x: x)
+  rng = _floats(a.get("range", "0 0"), 2)
+  j["range"] = np.array([cv(rng[0]), cv(rng[1])])
+  lim = a.get("limited", "false")
+  j["limited"] = 1 if lim == "true" else 0
+  j["ref"] = cv(float(a.get("ref", 0)))
+  j["springref"] = cv(float(a.get("springref", 0)))
+  j["stiffness"] = float(a.get("stiffness", 0))
+  j["damping"] = float(a.get("damping", 0))
+  j["armature"] = float(a.get("armature", 0))
+  j["frictionloss"] = float(a.get("frictionloss", 0))
+  j["margin"] = float(a.get("margin", 0))
+  j["solref_limit"] = np.array(_floats(a.get("solreflimit", "0.02 1"), 2))
+  si = _floats(a.get("solimplimit", "0.9 0.95 0.001 0.5 2"))
+  j["solimp_limit"] = np.array((si + [0.9, 0.95, 0.001, 0.5, 2][len(si):])[:5])
+  j["solref_fric"] = np.array(_floats(a.get("solreffriction", "0.02 1"), 2))
+  si = _floats(a.get("solimpfriction", "0.9 0.95 0.001 0.5 2"))
+  j["solimp_fric"] = np.array((si + [0.9, 0.95, 0.001, 0.5, 2][len(si):])[:5])
+  if free:
+    j["limited"] = 0
+    j["stiffness"] = j["damping"] = j["armature"] = j["frictionloss"] = 0.0
+    j["pos"] = np.zeros(3)
+    j["axis"] = np.array([0.0, 0, 1])
+  return j
+
+
+def _eig3_frame(I):
+  """Principal axes of a symmetric 3x3 inertia: returns (diag, quat) with
+  eigenvalues in decreasing order and a right-handed eigenvector frame."""
+  w, v = np.linalg.eigh(I)
+  order = np.argsort(-w, kind="stable")
+  w, v = w[order], v[:, order]
+  if np.linalg.det(v) < 0:
+    v[:, 2] = -v[:, 2]
+  return w, mat_to_quat(v)
+
+
+def _body_inertial(body, ctx):
+  """Sets body mass / ipos / iquat / inertia (explicit <inertial> or from
+  geoms [MJ-doc inertiafromgeom=auto])."""
+  inr = body.get("inertial")
+  if inr is not None and ctx.inertiafromgeom != "true":
+    body["mass"] = float(inr["mass"])
+    body["ipos"] = np.array(_floats(inr.get("pos", "0 0 0"), 3))
+    if "fullinertia" in inr:
+      f = _floats(inr["fullinertia"], 6)
+      I = np.array([[f[0], f[3], f[4]], [f[3], f[1], f[5]], [f[4], f[5], f[2]]])
+      w, q = _eig3_frame(I)
+      body["inertia"], body["iquat"] = w, q
+    else:
+      body["inertia"] = np.array(_floats(inr["diaginertia"], 3))
+      body["iquat"] = _orientation(inr, ctx)
+    return
+  geoms = [g for g in body["geoms"] if g["mass"] > 0]
+  if not geoms or ctx.inertiafromgeom == "false":
+    body["mass"] = 0.0
+    body["ipos"] = np.zeros(3)
+    body["iquat"] = np.array([1.0, 0, 0, 0])
+    body["inertia"] = np.zeros(3)
+    return
+  mass = sum(g["mass"] for g in geoms)
+  com = sum(g["mass"] * g["pos"] for g in geoms) / mass
+  I = np.zeros((3, 3))
+  for g in geoms:
+    R = quat_to_mat(g["quat"])
+    Ig = R @ np.diag(g["inertia"]) @ R.T
+    d = g["pos"] - com
+    I += Ig + g["mass"] * (np.dot(d, d) * np.eye(3) - np.outer(d, d))
+  if len(geoms) == 1:
+    # single geom: keep the geom's own principal frame (no eigen-solve)
+    body["inertia"] = geoms[0]["inertia"].copy()
+    body["iquat"] = geoms[0]["quat"].copy()
+    # decreasing-order convention is only applied when diagonalising
+  else:
+    w, q = _eig3_frame(I)
+    body["inertia"], body["iquat"] = w, q
+  body["mass"] = mass
+  body["ipos"] = com
+
+
+def _parse_body(elem, classes, childclass, ctx, parent_id, bodies):
+  """Depth-first (pre-order) traversal; appends to `bodies` [MJ-doc: body ids
+  follow document order, children after all of the parent's own elements]."""
+  childclass = elem.get("childclass") or childclass
+  b = {"name": elem.get("name", ""), "parent": parent_id, "joints": [],
+       "geoms": [], "sites": [], "cameras": [], "lights": []}
+  b["pos"] = np.array(_floats(elem.get("pos", "0 0 0"), 3))
+  b["quat"] = _orientation(elem.attrib, ctx)
+  b["mocap"] = elem.get("mocap") == "true"
+  bid = len(bodies)
+  bodies.append(b)
+  for ch in elem:
+    if ch.tag == "joint":
+      b["joints"].append(_compile_joint(_merged(ch, classes, childclass), ctx))
+    elif ch.tag == "freejoint":
+      b["joints"].append(_compile_joint(dict(ch.attrib), ctx, free=True))
+    elif ch.tag == "geom":
+      b["geoms"].append(_compile_geom(_merged(ch, classes, childclass), ctx))
+    elif ch.tag == "site":
+      b["sites"].append(_compile_site(_merged(ch, classes, childclass), ctx))
+    elif ch.tag == "inertial":
+      b["inertial"] = dict(ch.attrib)
+    elif ch.tag == "camera":
+      b["cameras"].append(ch.get("name", ""))
+    elif ch.tag == "light":
+      b["lights"].append(ch.get("name", ""))
+  if bid == 0:
+    b["mass"], b["ipos"] = 0.0, np.zeros(3)
+    b["iquat"], b["inertia"] = np.array([1.0, 0, 0, 0]), np.zeros(3)
+  else:
+    _body_inertial(b, ctx)
+  for ch in elem:
+    if ch.tag == "body":
+      _parse_body(ch, classes, childclass, ctx, bid, bodies)
+
+
+# ------------------------------------------------------------------- assembly
+
+_SENSOR_SPEC = {
+    # tag: (objtype attr, objtype enum name, dim, needstage)
+    "touch": ("site", "site", 1, M.STAGE_ACC),
+    "accelerometer": ("site", "site", 3, M.STAGE_ACC),
+    "velocimeter": ("site", "site", 3, M.STAGE_VEL),
+    "gyro": ("site", "site", 3, M.STAGE_VEL),
+    "force": ("site", "site", 3, M.STAGE_ACC),
+    "torque": ("site", "site", 3, M.STAGE_ACC),
+    "rangefinder": ("site", "site", 1, M.STAGE_POS),
+    "jointpos": ("joint", "joint", 1, M.STAGE_POS),
+    "jointvel": ("joint", "joint", 1, M.STAGE_VEL),
+    "actuatorfrc": ("actuator", "actuator", 1, M.STAGE_ACC),
+    "subtreecom": ("body", "body", 3, M.STAGE_POS),
+    "subtreelinvel": ("body", "body", 3, M.STAGE_VEL),
+    "subtreeangmom": ("body", "body", 3, M.STAGE_VEL),
+    "framepos": (None, None, 3, M.STAGE_POS),
+    "framequat": (None, None, 4, M.STAGE_POS),
+    "framexaxis": (None, None, 3, M.STAGE_POS),
+    "frameyaxis": (None, None, 3, M.STAGE_POS),
+    "framezaxis": (None, None, 3, M.STAGE_POS),
+    "framelinvel": (None, None, 3, M.STAGE_VEL),
+    "frameangvel": (None, None, 3, M.STAGE_VEL),
+}
+
+
+def compile_xml(xml_string, assets=None):
+  """MJCF string (+ include assets) -> FlatModel."""
+  if isinstance(xml_string, bytes):
+    xml_string = xml_string.decode()
+  root = ET.fromstring(xml_string.rstrip("\0"))
+  if root.tag != "mujoco":
+    raise ValueError("root element must be <mujoco>")
+  _expand_includes(root, {} if assets is None else assets)
+  ctx = _Ctx()
+  for comp in root.findall("compiler"):
+    if "angle" in comp.attrib:
+      ctx.degree = comp.get("angle") == "degree"
+    ctx.eulerseq = comp.get("eulerseq", ctx.eulerseq)
+    ctx.inertiafromgeom = comp.get("inertiafromgeom", ctx.inertiafromgeom)
+    ctx.settotalmass = float(comp.get("settotalmass", ctx.settotalmass))
+    ctx.boundmass = float(comp.get("boundmass", ctx.boundmass))
+    ctx.boundinertia = float(comp.get("boundinertia", ctx.boundinertia))
+  classes = _parse_defaults(root)
+
+  bodies = []
+  world = ET.Element("body", {"name": "world"})
+  for wb in root.findall("worldbody"):
+    for ch in wb:
+      world.append(ch)
+  _parse_body(world, classes, None, ctx, 0, bodies)
+  bodies[0]["parent"] = 0
+
+  m = M.FlatModel()
+  m.model_name = root.get("model", "MuJoCo Model")
+  _emit_tree(m, bodies, ctx)
+  _emit_options(m, root)
+  _emit_actuators(m, root, classes)
+  _emit_sensors(m, root, classes)
+  _emit_pairs(m)
+  _emit_keyframes(m, root)
+  _set_const(m)
+  _emit_statistic(m, root)
+  return m
+
+
+def _emit_tree(m, bodies, ctx):
+  nbody = len(bodies)
+  if ctx.boundmass > 0 or ctx.boundinertia > 0:
+    for b in bodies[1:]:
+      b["mass"] = max(b["mass"], ctx.boundmass)
+      b["inertia"] = np.maximum(b["inertia"], ctx.boundinertia)
+  if ctx.settotalmass > 0:
+    tot = sum(b["mass"] for b in bodies)
+    sc = ctx.settotalmass / tot
+    for b in bodies:
+      b["mass"] *= sc
+      b["inertia"] = b["inertia"] * sc
+  names = m.names
+  body_f = {k: [] for k in ("parentid", "jntnum", "jntadr", "dofnum", "dofadr",
+                            "geomnum", "geomadr", "pos", "quat", "ipos",
+                            "iquat", "mass", "inertia", "weldid", "rootid")}
+  J = {k: [] for k in ("type", "qposadr", "dofadr", "bodyid", "limited", "pos",
+                       "axis", "stiffness", "range", "margin", "solref",
+                       "solimp")}
+  D = {k: [] for k in ("bodyid", "jntid", "parentid", "armature", "damping",
+                       "frictionloss", "solref", "solimp")}
+  G = {k: [] for k in ("type", "contype", "conaffinity", "condim", "bodyid",
+                       "dataid", "group", "solmix", "solref", "solimp", "size",
+                       "rbound", "pos", "quat", "friction", "margin", "gap")}
+  S = {k: [] for k in ("type", "bodyid", "size", "pos", "quat")}
+  qpos0, qpos_spring = [], []
+  nq = nv = 0
+  last_dof_of_body = {}
+  for bid, b in enumerate(bodies):
+    names["body"].append(b["name"])
+    p = b["parent"]
+    body_f["parentid"].append(p)
+    body_f["pos"].append(b["pos"]); body_f["quat"].append(b["quat"])
+    body_f["ipos"].append(b["ipos"]); body_f["iquat"].append(b["iquat"])
+    body_f["mass"].append(b["mass"]); body_f["inertia"].append(b["inertia"])
+    body_f["jntnum"].append(len(b["joints"]))
+    body_f["jntadr"].append(len(J["type"]) if b["joints"] else -1)
+    body_f["geomnum"].append(len(b["geoms"]))
+    body_f["geomadr"].append(len(G["type"]) if b["geoms"] else -1)
+    if bid == 0:
+      body_f["weldid"].append(0); body_f["rootid"].append(0)
+    else:
+      body_f["weldid"].append(bid if b["joints"] else body_f["weldid"][p])
+      body_f["rootid"].append(bid if p == 0 else body_f["rootid"][p])
+    # parent dof for the first dof of this body: last dof of nearest ancestor
+    anc, pd = p, -1
+    while bid != 0:
+      if anc in last_dof_of_body:
+        pd = last_dof_of_body[anc]
+        break
+      if anc == 0:
+        break
+      anc = bodies[anc]["parent"]
+    dof0 = nv
+    for j in b["joints"]:
+      jid = len(J["type"])
+      names["joint"].append(j["name"])
+      jt = j["type"]
+      J["type"].append(jt); J["qposadr"].append(nq); J["dofadr"].append(nv)
+      J["bodyid"].append(bid); J["limited"].append(j["limited"])
+      J["pos"].append(j["pos"]); J["axis"].append(j["axis"])
+      J["stiffness"].append(j["stiffness"]); J["range"].append(j["range"])
+      J["margin"].append(j["margin"]); J["solref"].append(j["solref_limit"])
+      J["solimp"].append(j["solimp_limit"])
+      if jt == M.JNT_FREE:
+        q0 = np.concatenate([b["pos"], b["quat"]]); nd = 6
+        qs = q0
+      elif jt == M.JNT_BALL:
+        q0 = np.array([1.0, 0, 0, 0]); nd = 3; qs = q0
+      else:
+        q0 = np.array([j["ref"]]); nd = 1; qs = np.array([j["springref"]])
+      qpos0.extend(q0); qpos_spring.extend(qs)
+      nq += len(q0)
+      for k in range(nd):
+        D["bodyid"].append(bid); D["jntid"].append(jid)
+        D["parentid"].append(pd); pd = nv
+        D["armature"].append(j["armature"]); D["damping"].append(j["damping"])
+        D["frictionloss"].append(j["frictionloss"])
+        D["solref"].append(j["solref_fric"]); D["solimp"].append(j["solimp_fric"])
+        nv += 1
+    body_f["dofnum"].append(nv - dof0)
+    body_f["dofadr"].append(dof0 if nv > dof0 else -1)
+    if nv > dof0:
+      last_dof_of_body[bid] = nv - 1
+    for g in b["geoms"]:
+      names["geom"].append(g["name"])
+      for k in ("type", "contype", "conaffinity", "condim", "group", "solmix",
+                "solref", "solimp", "size", "rbound", "pos", "quat", "friction",
+                "margin", "gap"):
+        G[k].append(g[k])
+      G["bodyid"].append(bid); G["dataid"].append(-1)
+    for s in b["sites"]:
+      names["site"].append(s["name"])
+      for k in ("type", "size", "pos", "quat"):
+        S[k].append(s[k])
+      S["bodyid"].append(bid)
+    names["camera"].extend(b["cameras"]); names["light"].extend(b["lights"])
+
+  def arr(lst, shape, dt=np.float64):
+    a = np.array(lst, dtype=dt)
+    return a.reshape(shape)
+
+  nj, ng, ns = len(J["type"]), len(G["type"]), len(S["type"])
+  m.set("nq", nq); m.set("nv", nv); m.set("nbody", nbody); m.set("njnt", nj)
+  m.set("ngeom", ng); m.set("nsite", ns)
+  m.set("ncam", len(names["camera"])); m.set("nlight", len(names["light"]))
+  for k in ("parentid", "jntnum", "jntadr", "dofnum", "dofadr", "geomnum",
+            "geomadr", "weldid", "rootid"):
+    m.set("body_" + k, arr(body_f[k], (nbody,), np.int32))
+  for k, w in (("pos", 3), ("quat", 4), ("ipos", 3), ("iquat", 4),
+               ("inertia", 3)):
+    m.set("body_" + k, arr(body_f[k], (nbody, w)))
+  m.set("body_mass", arr(body_f["mass"], (nbody,)))
+  for k in ("type", "qposadr", "dofadr", "bodyid", "limited"):
+    m.set("jnt_" + k, arr(J[k], (nj,), np.int32))
+  for k, w in (("pos", 3), ("axis", 3), ("range", 2), ("solref", 2),
+               ("solimp", 5)):
+    m.set("jnt_" + k, arr(J[k], (nj, w)))
+  m.set("jnt_stiffness", arr(J["stiffness"], (nj,)))
+  m.set("jnt_margin", arr(J["margin"], (nj,)))
+  for k in ("bodyid", "jntid", "parentid"):
+    m.set("dof_" + k, arr(D[k], (nv,), np.int32))
+  for k in ("armature", "damping", "frictionloss"):
+    m.set("dof_" + k, arr(D[k], (nv,)))
+  m.set("dof_solref", arr(D["solref"], (nv, 2)))
+  m.set("dof_solimp", arr(D["solimp"], (nv, 5)))
+  # sparse inertia addressing: row i = dof i and its ancestors
+  madr, n = [], 0
+  for i in range(nv):
+    madr.append(n)
+    k = i
+    while k >= 0:
+      n += 1
+      k = D["parentid"][k]
+  m.set("dof_Madr", arr(madr, (nv,), np.int32)); m.set("nM", n)
+  for k in ("type", "contype", "conaffinity", "condim", "bodyid", "dataid",
+            "group"):
+    m.set("geom_" + k, arr(G[k], (ng,), np.int32))
+  for k, w in (("solref", 2), ("solimp", 5), ("size", 3), ("pos", 3),
+               ("quat", 4), ("friction", 3)):
+    m.set("geom_" + k, arr(G[k], (ng, w)))
+  for k in ("solmix", "rbound", "margin", "gap"):
+    m.set("geom_" + k, arr(G[k], (ng,)))
+  m.set("site_type", arr(S["type"], (ns,), np.int32))
+  m.set("site_bodyid", arr(S["bodyid"], (ns,), np.int32))
+  for k, w in (("size", 3), ("pos", 3), ("quat", 4)):
+    m.set("site_" + k, arr(S[k], (ns, w)))
+  m.set("qpos0", arr(qpos0, (nq,))); m.set("qpos_spring", arr(qpos_spring, (nq,)))
+  # subtree mass
+  sub = np.array(body_f["mass"], dtype=np.float64)
+  for b in range(nbody - 1, 0, -1):
+    sub[body_f["parentid"][b]] += sub[b]
+  m.set("body_subtreemass", sub)
+  # unsupported-in-v1 sizes, present so the schema is stable
+  for k in ("ntendon", "nwrap", "neq", "nhfield", "nmocap"):
+    m.set(k, 0)
+
+
+def _emit_options(m, root):
+  o = {"timestep": 0.002, "impratio": 1.0, "tolerance": 1e-8,
+       "noslip_tolerance": 1e-6, "mpr_tolerance": 1e-6, "density": 0.0,
+       "viscosity": 0.0, "o_margin": 0.0}
+  grav = [0.0, 0.0, -9.81]
+  wind = [0.0, 0.0, 0.0]
+  integ, cone, solver, jac = M.INT_EULER, M.CONE_PYRAMIDAL, M.SOL_NEWTON, 2
+  iters, noslip, mpr = 100, 0, 50
+  dis = en = 0
+  njmax = nconmax = -1
+  for sz in root.findall("size"):
+    njmax = int(sz.get("njmax", njmax)); nconmax = int(sz.get("nconmax", nconmax))
+  for op in root.findall("option"):
+    for k in list(o):
+      if k in op.attrib:
+        o[k] = float(op.get(k))
+    if "gravity" in op.attrib:
+      grav = _floats(op.get("gravity"), 3)
+    if "wind" in op.attrib:
+      wind = _floats(op.get("wind"), 3)
+    integ = {"Euler": 0, "RK4": 1}[op.get("integrator", "Euler" if integ == 0
+                                          else "RK4")]
+    cone = {"pyramidal": 0, "elliptic": 1}[op.get(
+        "cone", "pyramidal" if cone == 0 else "elliptic")]
+    solver = {"PGS": 0, "CG": 1, "Newton": 2}[op.get(
+        "solver", ["PGS", "CG", "Newton"][solver])]
+    iters = int(op.get("iterations", iters))
+    noslip = int(op.get("noslip_iterations", noslip))
+    mpr = int(op.get("mpr_iterations", mpr))
+    for fl in op.findall("flag"):
+      for k, v in fl.attrib.items():
+        if k in M.DSBL:
+          dis = (dis | M.DSBL[k]) if v == "disable" else (dis & ~M.DSBL[k])
+        elif k in M.ENBL:
+          en = (en | M.ENBL[k]) if v == "enable" else (en & ~M.ENBL[k])
+        else:
+          raise ValueError("unknown flag %r" % k)
+  for k, v in o.items():
+    m.set("opt_" + k, v)
+  m.set("opt_gravity", grav); m.set("opt_wind", wind)
+  m.set("opt_integrator", integ); m.set("opt_cone", cone)
+  m.set("opt_solver", solver); m.set("opt_jacobian", jac)
+  m.set("opt_iterations", iters); m.set("opt_noslip_iterations", noslip)
+  m.set("opt_mpr_iterations", mpr)
+  m.set("opt_ls_iterations", 50); m.set("opt_ls_tolerance", 0.01)
+  m.set("opt_disableflags", dis); m.set("opt_enableflags", en)
+  m.set("njmax_xml", njmax); m.set("nconmax_xml", nconmax)
+
+
+def _emit_actuators(m, root, classes):
+  A = {k: [] for k in ("trntype", "dyntype", "gaintype", "biastype", "trnid",
+                       "ctrllimited", "forcelimited", "dynprm", "gainprm",
+                       "biasprm", "ctrlrange", "forcerange", "gear")}
+  for sec in root.findall("actuator"):
+    for el in sec:
+      if el.tag not in _ACT_TAGS:
+        continue
+      a = dict(classes[el.get("class") or "main"].get("general"))
+      a.update(classes[el.get("class") or "main"].get(el.tag))
+      a.update(el.attrib)
+      m.names["actuator"].append(a.get("name", ""))
+      dyn, gain, bias = M.DYN_NONE, M.GAIN_FIXED, M.BIAS_NONE
+      dynprm = [1.0] + [0.0] * 2
+      gainprm = [1.0] + [0.0] * 2
+      biasprm = [0.0] * 3
+      if el.tag == "general":
+        dyn = {"none": 0, "integrator": 1, "filter": 2}[a.get("dyntype", "none")]
+        gain = {"fixed": 0}[a.get("gaintype", "fixed")]
+        bias = {"none": 0, "affine": 1}[a.get("biastype", "none")]
+        for nm, dst in (("dynprm", dynprm), ("gainprm", gainprm),
+                        ("biasprm", biasprm)):
+          if nm in a:
+            v = _floats(a[nm])
+            dst[:len(v)] = v[:3]
+      elif el.tag == "position":
+        kp = float(a.get("kp", 1))
+        gainprm[0] = kp; bias = M.BIAS_AFFINE; biasprm[1] = -kp
+      elif el.tag == "velocity":
+        kv = float(a.get("kv", 1))
+        gainprm[0] = kv; bias = M.BIAS_AFFINE; biasprm[2] = -kv
+      elif el.tag != "motor":
+        raise ValueError("actuator <%s> unsupported" % el.tag)
+      if "joint" in a:
+        trn, tid = M.TRN_JOINT, m.name2id(a["joint"], "joint")
+      elif "tendon" in a:
+        trn, tid = M.TRN_TENDON, m.name2id(a["tendon"], "tendon")
+      else:
+        raise ValueError("actuator transmission unsupported")
+      gear = _floats(a.get("gear", "1"))
+      gear = (gear + [0.0] * 6)[:6]
+      A["trntype"].append(trn); A["trnid"].append([tid, -1])
+      A["dyntype"].append(dyn); A["gaintype"].append(gain)
+      A["biastype"].append(bias)
+      A["ctrllimited"].append(1 if a.get("ctrllimited") == "true" else 0)
+      A["forcelimited"].append(1 if a.get("forcelimited") == "true" else 0)
+      A["dynprm"].append(dynprm); A["gainprm"].append(gainprm)
+      A["biasprm"].append(biasprm)
+      A["ctrlrange"].append(_floats(a.get("ctrlrange", "0 0"), 2))
+      A["forcerange"].append(_floats(a.get("forcerange", "0 0"), 2))
+      A["gear"].append(gear)
+  nu = len(A["trntype"])
+  na = sum(1 for d in A["dyntype"] if d != M.DYN_NONE)
+  m.set("nu", nu); m.set("na", na)
+  for k in ("trntype", "dyntype", "gaintype", "biastype", "ctrllimited",
+            "forcelimited"):
+    m.set("actuator_" + k, np.array(A[k], dtype=np.int32).reshape(nu))
+  m.set("actuator_trnid", np.array(A["trnid"], dtype=np.int32).reshape(nu, 2))
+  for k, w in (("dynprm", 3), ("gainprm", 3), ("biasprm", 3), ("ctrlrange", 2),
+               ("forcerange", 2), ("gear", 6)):
+    m.set("actuator_" + k, np.array(A[k], dtype=np.float64).reshape(nu, w))
+
+
+def _emit_sensors(m, root, classes):
+  S = {k: [] for k in ("type", "needstage", "objtype", "objid", "dim", "adr",
+                       "cutoff")}
+  adr = 0
+  for sec in root.findall("sensor"):
+    for el in sec:
+      if el.tag not in _SENSOR_SPEC:
+        raise ValueError("sensor <%s> unsupported" % el.tag)
+      attr, objname, dim, stage = _SENSOR_SPEC[el.tag]
+      if attr is None:                       # frame sensors: objtype + objname
+        objname = el.get("objtype")
+        oid = m.name2id(el.get("objname"), {"xbody": "body"}.get(objname,
+                                                                  objname))
+      else:
+        oid = m.name2id(el.get(attr), objname)
+      m.names["sensor"].append(el.get("name", ""))
+      S["type"].append(M.SENS[el.tag]); S["needstage"].append(stage)
+      S["objtype"].append(M.OBJ[objname]); S["objid"].append(oid)
+      S["dim"].append(dim); S["adr"].append(adr)
+      S["cutoff"].append(float(el.get("cutoff", 0)))
+      adr += dim
+  ns = len(S["type"])
+  m.set("nsensor", ns); m.set("nsensordata", adr)
+  for k in ("type", "needstage", "objtype", "objid", "dim", "adr"):
+    m.set("sensor_" + k, np.array(S[k], dtype=np.int32).reshape(ns))
+  m.set("sensor_cutoff", np.array(S["cutoff"], dtype=np.float64).reshape(ns))
+
+
+def _emit_pairs(m):
+  """Static candidate geom pairs, in the engine's contact order [MJ-doc A.7]:
+  ascending (body1, body2), then geom order inside each body; filtered by
+  contype/conaffinity, same-weld and (optionally, at run time) parent-child."""
+  ng = m.ngeom
+  gb = m.geom_bodyid
+  weld, par = m.body_weldid, m.body_parentid
+  pairs = []
+  order = sorted(range(ng), key=lambda g: (gb[g], g))
+  for i1 in range(ng):
+    for i2 in range(i1 + 1, ng):
+      g1, g2 = order[i1], order[i2]
+      b1, b2 = gb[g1], gb[g2]
+      if b1 == b2:
+        continue
+      if weld[b1] == weld[b2]:
+        continue
+      if not ((m.geom_contype[g1] & m.geom_conaffinity[g2]) or
+              (m.geom_contype[g2] & m.geom_conaffinity[g1])):
+        continue
+      # parent-child filter flag (applied unless DSBL filterparent is set)
+      w1, w2 = weld[b1], weld[b2]
+      pc = int((w1 != 0 and w2 != 0) and
+               (w1 == weld[par[w2]] or w2 == weld[par[w1]]))
+      # order by geom type so that type1 <= type2 (function-table convention)
+      a, b = (g1, g2) if m.geom_type[g1] <= m.geom_type[g2] else (g2, g1)
+      pairs.append((a, b, pc))
+  npair = len(pairs)
+  arr = np.array(pairs, dtype=np.int32).reshape(npair, 3)
+  m.set("npair", npair)
+  m.set("pair_geom1", arr[:, 0].copy()); m.set("pair_geom2", arr[:, 1].copy())
+  m.set("pair_parentchild", arr[:, 2].copy())
+  # contact / constraint buffer sizes.  MuJoCo's "auto" heuristics are not
+  # documented; we bound by what the pair list can produce (plane-box 4,
+  # plane-capsule 2, else 1) so CONTACTFULL can only fire for explicit sizes.
+  maxcon = 0
+  maxrow = 0
+  for a, b, _ in pairs:
+    ta, tb = m.geom_type[a], m.geom_type[b]
+    if ta == M.GEOM_PLANE:
+      n = {M.GEOM_BOX: 4, M.GEOM_CAPSULE: 2, M.GEOM_CYLINDER: 4}.get(tb, 1)
+    elif tb == M.GEOM_BOX:
+      n = 8 if ta == M.GEOM_BOX else 1
+    else:
+      n = 1
+    dim = max(m.geom_condim[a], m.geom_condim[b])
+    maxcon += n
+    maxrow += n * (1 if dim == 1 else 2 * (dim - 1))
+  lim = int(np.sum(m.jnt_limited != 0)) if m.njnt else 0
+  fl = int(np.sum(m.dof_frictionloss > 0)) if m.nv else 0
+  nconmax = m.nconmax_xml if m.nconmax_xml > 0 else max(maxcon, 1)
+  njmax = m.njmax_xml if m.njmax_xml > 0 else max(maxrow + lim + fl, 1)
+  m.set("nconmax", nconmax); m.set("njmax", njmax)
+
+
+def _emit_keyframes(m, root):
+  K = {"time": [], "qpos": [], "qvel": [], "act": []}
+  for sec in root.findall("keyframe"):
+    for k in sec.findall("key"):
+      m.names["key"].append(k.get("name", ""))
+      K["time"].append(float(k.get("time", 0)))
+      K["qpos"].append(_floats(k["qpos"]) if False else (
+          _floats(k.get("qpos")) if k.get("qpos") else list(m.qpos0)))
+      K["qvel"].append(_floats(k.get("qvel")) if k.get("qvel")
+                       else [0.0] * m.nv)
+      K["act"].append(_floats(k.get("act")) if k.get("act") else [0.0] * m.na)
+  nk = len(K["time"])
+  m.set("nkey", nk)
+  m.set("key_time", np.array(K["time"], dtype=np.float64).reshape(nk))
+  m.set("key_qpos", np.array(K["qpos"], dtype=np.float64).reshape(nk, m.nq))
+  m.set("key_qvel", np.array(K["qvel"], dtype=np.float64).reshape(nk, m.nv))
+  m.set("key_act", np.array(K["act"], dtype=np.float64).reshape(nk, m.na))
+
+
+# --------------------------------------------------- mj_setConst restatement
+
+
+def host_kinematics(m, qpos):
+  """Dense numpy forward kinematics (host, cold path): body/inertial frames and
+  per-dof world motion axes.  Used by `_set_const` and compile-time checks."""
+  nb = m.nbody
+  xpos = np.zeros((nb, 3)); xquat = np.zeros((nb, 4)); xquat[0, 0] = 1
+  dof_axis = np.zeros((m.nv, 3)); dof_anchor = np.zeros((m.nv, 3))
+  dof_kind = np.zeros(m.nv, dtype=int)       # 0 translational, 1 rotational
+  for b in range(1, nb):
+    p = m.body_parentid[b]
+    Rp = quat_to_mat(xquat[p])
+    pos = xpos[p] + Rp @ m.body_pos[b]
+    quat = quat_mul(xquat[p], m.body_quat[b])
+    for k in range(m.body_jntnum[b]):
+      j = m.body_jntadr[b] + k
+      qa, da, jt = m.jnt_qposadr[j], m.jnt_dofadr[j], m.jnt_type[j]
+      if jt == M.JNT_FREE:
+        pos = qpos[qa:qa + 3].copy()
+        quat = _normalize(qpos[qa + 3:qa + 7])
+        R = quat_to_mat(quat)
+        for c in range(3):
+          dof_axis[da + c] = np.eye(3)[c]; dof_kind[da + c] = 0
+          dof_axis[da + 3 + c] = R[:, c]; dof_kind[da + 3 + c] = 1
+          dof_anchor[da + 3 + c] = pos
+        continue
+      R = quat_to_mat(quat)
+      anchor = pos + R @ m.jnt_pos[j]
+      axis = R @ m.jnt_axis[j]
+      if jt == M.JNT_SLIDE:
+        pos = pos + axis * (qpos[qa] - m.qpos0[qa])
+        dof_axis[da] = axis; dof_kind[da] = 0
+      elif jt == M.JNT_HINGE:
+        qr = axisangle_to_quat(m.jnt_axis[j], qpos[qa] - m.qpos0[qa])
+        quat = quat_mul(quat, qr)
+        pos = anchor - quat_to_mat(quat) @ m.jnt_pos[j]
+        dof_axis[da] = axis; dof_kind[da] = 1; dof_anchor[da] = anchor
+      elif jt == M.JNT_BALL:
+        quat = quat_mul(quat, _normalize(qpos[qa:qa + 4]))
+        pos = anchor - quat_to_mat(quat) @ m.jnt_pos[j]
+        Rn = quat_to_mat(quat)
+        for c in range(3):
+          dof_axis[da + c] = Rn[:, c]; dof_kind[da + c] = 1
+          dof_anchor[da + c] = anchor
+    xpos[b], xquat[b] = pos, _normalize(quat)
+  xipos = np.zeros((nb, 3)); ximat = np.zeros((nb, 3, 3))
+  for b in range(nb):
+    R = quat_to_mat(xquat[b])
+    xipos[b] = xpos[b] + R @ m.body_ipos[b]
+    ximat[b] = R @ quat_to_mat(m.body_iquat[b])
+  return dict(xpos=xpos, xquat=xquat, xipos=xipos, ximat=ximat,
+              dof_axis=dof_axis, dof_anchor=dof_anchor, dof_kind=dof_kind)
+
+
+def host_jac(m, kin, body, point):
+  """3 x nv translational and rotational Jacobians of `point` on `body`."""
+  jp = np.zeros((3, m.nv)); jr = np.zeros((3, m.nv))
+  b = body
+  while b > 0 and m.body_dofnum[b] == 0:
+    b = m.body_parentid[b]
+  if b == 0:
+    return jp, jr
+  i = m.body_dofadr[b] + m.body_dofnum[b] - 1
+  while i >= 0:
+    ax = kin["dof_axis"][i]
+    if kin["dof_kind"][i] == 0:
+      jp[:, i] = ax
+    else:
+      jr[:, i] = ax
+      jp[:, i] = np.cross(ax, point - kin["dof_anchor"][i])
+    i = m.dof_parentid[i]
+  return jp, jr
+
+
+def host_mass_matrix(m, kin):
+  """Dense joint-space inertia by summing per-body J^T I J (host, cold path)."""
+  Mm = np.zeros((m.nv, m.nv))
+  for b in range(1, m.nbody):
+    if m.body_mass[b] == 0 and not np.any(m.body_inertia[b]):
+      continue
+    jp, jr = host_jac(m, kin, b, kin["xipos"][b])
+    R = kin["ximat"][b]
+    Iw = R @ np.diag(m.body_inertia[b]) @ R.T
+    Mm += m.body_mass[b] * jp.T @ jp + jr.T @ Iw @ jr
+  Mm[np.diag_indices(m.nv)] += m.dof_armature
+  return Mm
+
+
+def _set_const(m):
+  """dof_M0, dof_invweight0, body_invweight0, stat_meaninertia at qpos0
+  [MJ-doc A.8: needed by the constraint regulariser diagApprox]."""
+  nv, nb = m.nv, m.nbody
+  binv = np.zeros((nb, 2)); dinv = np.zeros(nv); m0 = np.zeros(nv)
+  mean_inertia = 1.0
+  if nv > 0:
+    kin = host_kinematics(m, np.array(m.qpos0))
+    Mm = host_mass_matrix(m, kin)
+    Minv = np.linalg.inv(Mm)
+    m0 = np.diag(Mm).copy()
+    mean_inertia = float(np.mean(m0))
+    for b in range(1, nb):
+      jp, jr = host_jac(m, kin, b, kin["xipos"][b])
+      binv[b, 0] = np.trace(jp @ Minv @ jp.T) / 3.0
+      binv[b, 1] = np.trace(jr @ Minv @ jr.T) / 3.0
+    for j in range(m.njnt):
+      da, jt = m.jnt_dofadr[j], m.jnt_type[j]
+      d = np.diag(Minv)
+      if jt == M.JNT_FREE:
+        dinv[da:da + 3] = np.mean(d[da:da + 3])
+        dinv[da + 3:da + 6] = np.mean(d[da + 3:da + 6])
+      elif jt == M.JNT_BALL:
+        dinv[da:da + 3] = np.mean(d[da:da + 3])
+      else:
+        dinv[da] = d[da]
+  m.set("dof_M0", m0); m.set("dof_invweight0", dinv)
+  m.set("body_invweight0", binv)
+  m.set("stat_meaninertia", mean_inertia)
+
+
+def _emit_statistic(m, root):
+  for st in root.findall("statistic"):
+    if "meaninertia" in st.attrib:
+      m.set("stat_meaninertia", float(st.get("meaninertia")))
+
+
+def compile_file(path):
+  import os
+  d = os.path.dirname(os.path.abspath(path))
+  with open(path) as f:
+    xml = f.read()
+
+  class _Dir(dict):
+    def __contains__(self, k):
+      return os.path.exists(os.path.join(d, k))
+
+    def __getitem__(self, k):
+      with open(os.path.join(d, k)) as f:
+        return f.read()
+
+  return compile_xml(xml, _Dir())

@@ -1,0 +1,918 @@
+/* CPU ORACLE — TEST INFRASTRUCTURE ONLY (see oracle.h).  fp64, one env per OData.
+ *
+ * Stage list follows the reference's call sequence Physics.step() ->
+ * mj_step2 + mj_step1 (/root/reference/dm_control/mujoco/engine.py:149-166) and
+ * SURVEY.md §3.1 / Appendix A ([MJ-doc] = restated from MuJoCo's documentation,
+ * not from the reference tree, which holds no engine source).
+ */
+#include "oracle.h"
+
+#include <math.h>
+#include <pthread.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define MINVAL 1e-15
+#define MAXVAL 1e10
+#define PI 3.14159265358979323846
+
+enum { GEOM_PLANE, GEOM_HFIELD, GEOM_SPHERE, GEOM_CAPSULE, GEOM_ELLIPSOID,
+       GEOM_CYLINDER, GEOM_BOX, GEOM_MESH };
+enum { JNT_FREE, JNT_BALL, JNT_SLIDE, JNT_HINGE };
+enum { DSBL_CONSTRAINT = 1, DSBL_EQUALITY = 2, DSBL_FRICTIONLOSS = 4,
+       DSBL_LIMIT = 8, DSBL_CONTACT = 16, DSBL_PASSIVE = 32, DSBL_GRAVITY = 64,
+       DSBL_CLAMPCTRL = 128, DSBL_WARMSTART = 256, DSBL_FILTERPARENT = 512,
+       DSBL_ACTUATION = 1024, DSBL_REFSAFE = 2048 };
+enum { ENBL_OVERRIDE = 1, ENBL_ENERGY = 2 };
+enum { CN_EQUALITY, CN_FRICTION_DOF, CN_FRICTION_TENDON, CN_LIMIT_JOINT,
+       CN_LIMIT_TENDON, CN_CONTACT_FRICTIONLESS, CN_CONTACT_PYRAMIDAL,
+       CN_CONTACT_ELLIPTIC };
+enum { ST_SATISFIED, ST_QUADRATIC, ST_LINEARNEG, ST_LINEARPOS, ST_CONE };
+enum { W_INERTIA, W_CONTACTFULL, W_CNSTRFULL, W_VGEOMFULL, W_BADQPOS,
+       W_BADQVEL, W_BADQACC, W_BADCTRL };
+enum { SENS_TOUCH = 0, SENS_ACCELEROMETER = 1, SENS_VELOCIMETER = 2,
+       SENS_GYRO = 3, SENS_FORCE = 4, SENS_TORQUE = 5, SENS_JOINTPOS = 8,
+       SENS_JOINTVEL = 9, SENS_ACTUATORFRC = 14, SENS_FRAMEPOS = 23,
+       SENS_SUBTREECOM = 32, SENS_SUBTREELINVEL = 33 };
+enum { OBJ_BODY = 1, OBJ_XBODY = 2, OBJ_GEOM = 5, OBJ_SITE = 6 };
+enum { STAGE_POS = 1, STAGE_VEL = 2, STAGE_ACC = 3 };
+
+/* ------------------------------------------------------------------ model */
+
+typedef struct {
+  char name[40];
+  int32_t dtype, ndim, dims[4];
+  int64_t offset, count;
+} BlobEntry;
+
+#define MODEL_INT_SCALARS(X) \
+  X(nq) X(nv) X(nu) X(na) X(nbody) X(njnt) X(ngeom) X(nsite) X(nM) X(npair) \
+  X(nconmax) X(njmax) X(nsensor) X(nsensordata) X(nkey) \
+  X(opt_integrator) X(opt_cone) X(opt_solver) X(opt_iterations) \
+  X(opt_ls_iterations) X(opt_disableflags) X(opt_enableflags)
+#define MODEL_F64_SCALARS(X) \
+  X(opt_timestep) X(opt_impratio) X(opt_tolerance) X(opt_ls_tolerance) \
+  X(stat_meaninertia)
+#define MODEL_INT_ARRAYS(X) \
+  X(body_parentid) X(body_rootid) X(body_weldid) X(body_jntnum) X(body_jntadr) \
+  X(body_dofnum) X(body_dofadr) X(jnt_type) X(jnt_qposadr) X(jnt_dofadr) \
+  X(jnt_bodyid) X(jnt_limited) X(dof_bodyid) X(dof_jntid) X(dof_parentid) \
+  X(dof_Madr) X(geom_type) X(geom_condim) X(geom_bodyid) X(site_bodyid) \
+  X(site_type) X(pair_geom1) X(pair_geom2) X(pair_parentchild) \
+  X(actuator_trntype) X(actuator_dyntype) X(actuator_gaintype) \
+  X(actuator_biastype) X(actuator_trnid) X(actuator_ctrllimited) \
+  X(actuator_forcelimited) X(sensor_type) X(sensor_objtype) X(sensor_objid) \
+  X(sensor_dim) X(sensor_adr) X(sensor_needstage)
+#define MODEL_F64_ARRAYS(X) \
+  X(opt_gravity) X(body_pos) X(body_quat) X(body_ipos) X(body_iquat) \
+  X(body_mass) X(body_subtreemass) X(body_inertia) X(body_invweight0) \
+  X(jnt_pos) X(jnt_axis) X(jnt_stiffness) X(jnt_range) X(jnt_margin) \
+  X(jnt_solref) X(jnt_solimp) X(dof_armature) X(dof_damping) \
+  X(dof_frictionloss) X(dof_solref) X(dof_solimp) X(dof_invweight0) \
+  X(geom_size) X(geom_rbound) X(geom_pos) X(geom_quat) X(geom_friction) \
+  X(geom_margin) X(geom_gap) X(geom_solmix) X(geom_solref) X(geom_solimp) \
+  X(site_pos) X(site_quat) X(site_size) X(qpos0) X(qpos_spring) \
+  X(actuator_dynprm) X(actuator_gainprm) X(actuator_biasprm) \
+  X(actuator_ctrlrange) X(actuator_forcerange) X(actuator_gear) \
+  X(sensor_cutoff) X(key_qpos) X(key_qvel) X(key_act) X(key_time)
+
+struct OModel {
+  char* blob;
+  int64_t nbytes;
+  int nfields;
+  BlobEntry* entries;
+#define X(n) int n;
+  MODEL_INT_SCALARS(X)
+#undef X
+#define X(n) double n;
+  MODEL_F64_SCALARS(X)
+#undef X
+#define X(n) int32_t* n;
+  MODEL_INT_ARRAYS(X)
+#undef X
+#define X(n) double* n;
+  MODEL_F64_ARRAYS(X)
+#undef X
+};
+
+static BlobEntry* find_entry(const OModel* m, const char* name) {
+  for (int i = 0; i < m->nfields; i++)
+    if (strncmp(m->entries[i].name, name, 40) == 0) return &m->entries[i];
+  return NULL;
+}
+
+void* om_field(OModel* m, const char* name, int64_t* count, int* dtype) {
+  BlobEntry* e = find_entry(m, name);
+  if (!e) return NULL;
+  if (count) *count = e->count;
+  if (dtype) *dtype = e->dtype;
+  return m->blob + e->offset;
+}
+
+OModel* om_create(const void* blob, int64_t nbytes, char* err, int errsz) {
+  if (nbytes < 16 || memcmp(blob, "BPMODEL1", 8) != 0) {
+    if (err) snprintf(err, errsz, "bad model blob magic");
+    return NULL;
+  }
+  OModel* m = (OModel*)calloc(1, sizeof(OModel));
+  m->blob = (char*)malloc(nbytes);
+  memcpy(m->blob, blob, nbytes);
+  m->nbytes = nbytes;
+  m->nfields = *(int32_t*)(m->blob + 8);
+  m->entries = (BlobEntry*)(m->blob + 16);
+  const char* missing = NULL;
+#define X(n) { BlobEntry* e = find_entry(m, #n); if (!e) missing = #n; \
+               else m->n = *(int32_t*)(m->blob + e->offset); }
+  MODEL_INT_SCALARS(X)
+#undef X
+#define X(n) { BlobEntry* e = find_entry(m, #n); if (!e) missing = #n; \
+               else m->n = *(double*)(m->blob + e->offset); }
+  MODEL_F64_SCALARS(X)
+#undef X
+#define X(n) { BlobEntry* e = find_entry(m, #n); if (!e) missing = #n; \
+               else m->n = (int32_t*)(m->blob + e->offset); }
+  MODEL_INT_ARRAYS(X)
+#undef X
+#define X(n) { BlobEntry* e = find_entry(m, #n); if (!e) missing = #n; \
+               else m->n = (double*)(m->blob + e->offset); }
+  MODEL_F64_ARRAYS(X)
+#undef X
+  if (missing) {
+    if (err) snprintf(err, errsz, "model blob lacks field %s", missing);
+    om_free(m);
+    return NULL;
+  }
+  return m;
+}
+
+void om_free(OModel* m) {
+  if (!m) return;
+  free(m->blob);
+  free(m);
+}
+
+/* ------------------------------------------------------------------- data */
+
+typedef struct {
+  double dist, pos[3], frame[9], includemargin, friction[5], solref[2],
+      solimp[5], mu;
+  int dim, geom1, geom2, exclude, efc_address;
+} OContact;
+
+/* name, type, element count (expression over m) */
+#define DATA_FIELDS(X) \
+  X(qpos, double, m->nq) X(qvel, double, m->nv) X(act, double, m->na) \
+  X(ctrl, double, m->nu) X(qacc, double, m->nv) X(qacc_warmstart, double, m->nv) \
+  X(act_dot, double, m->na) X(qfrc_applied, double, m->nv) \
+  X(xfrc_applied, double, 6 * m->nbody) X(time, double, 1) \
+  X(energy, double, 2) X(xpos, double, 3 * m->nbody) \
+  X(xquat, double, 4 * m->nbody) X(xmat, double, 9 * m->nbody) \
+  X(xipos, double, 3 * m->nbody) X(ximat, double, 9 * m->nbody) \
+  X(xanchor, double, 3 * m->njnt) X(xaxis, double, 3 * m->njnt) \
+  X(geom_xpos, double, 3 * m->ngeom) X(geom_xmat, double, 9 * m->ngeom) \
+  X(site_xpos, double, 3 * m->nsite) X(site_xmat, double, 9 * m->nsite) \
+  X(subtree_com, double, 3 * m->nbody) X(cinert, double, 10 * m->nbody) \
+  X(cdof, double, 6 * m->nv) X(cdof_dot, double, 6 * m->nv) \
+  X(cvel, double, 6 * m->nbody) X(cacc, double, 6 * m->nbody) \
+  X(cfrc_int, double, 6 * m->nbody) X(cfrc_ext, double, 6 * m->nbody) \
+  X(crb, double, 10 * m->nbody) X(subtree_linvel, double, 3 * m->nbody) \
+  X(subtree_angmom, double, 3 * m->nbody) \
+  X(qM, double, m->nM) X(qLD, double, m->nM) X(qLDiagInv, double, m->nv) \
+  X(qfrc_bias, double, m->nv) X(qfrc_passive, double, m->nv) \
+  X(qfrc_actuator, double, m->nv) X(qfrc_smooth, double, m->nv) \
+  X(qacc_smooth, double, m->nv) X(qfrc_constraint, double, m->nv) \
+  X(actuator_length, double, m->nu) X(actuator_velocity, double, m->nu) \
+  X(actuator_moment, double, m->nu * m->nv) X(actuator_force, double, m->nu) \
+  X(sensordata, double, m->nsensordata) \
+  X(efc_J, double, m->njmax * m->nv) X(efc_pos, double, m->njmax) \
+  X(efc_margin, double, m->njmax) X(efc_frictionloss, double, m->njmax) \
+  X(efc_diagApprox, double, m->njmax) X(efc_KBIP, double, 4 * m->njmax) \
+  X(efc_D, double, m->njmax) X(efc_R, double, m->njmax) \
+  X(efc_vel, double, m->njmax) X(efc_aref, double, m->njmax) \
+  X(efc_force, double, m->njmax) X(efc_type, int32_t, m->njmax) \
+  X(efc_id, int32_t, m->njmax) X(efc_state, int32_t, m->njmax) \
+  X(contact_geom1, int32_t, m->nconmax) X(contact_geom2, int32_t, m->nconmax) \
+  X(contact_dim, int32_t, m->nconmax) X(contact_dist, double, m->nconmax) \
+  X(contact_pos, double, 3 * m->nconmax) X(contact_frame, double, 9 * m->nconmax) \
+  X(contact_efc_address, int32_t, m->nconmax) \
+  X(ncon, int32_t, 1) X(nefc, int32_t, 1) X(ne, int32_t, 1) X(nf, int32_t, 1) \
+  X(solver_iter, int32_t, 1) X(warning, int32_t, 8) \
+  X(solver_improvement, double, 1) X(solver_gradient, double, 1)
+
+struct OData {
+  const OModel* m;
+#define X(n, t, c) t* n; int64_t n##_count;
+  DATA_FIELDS(X)
+#undef X
+  OContact* contact;
+  /* solver scratch */
+  double *s_Ma, *s_jar, *s_grad, *s_Mgrad, *s_search, *s_Mv, *s_jv, *s_H,
+      *s_Mdense;
+};
+
+OData* od_create(const OModel* m) {
+  OData* d = (OData*)calloc(1, sizeof(OData));
+  d->m = m;
+#define X(n, t, c) d->n##_count = (c); \
+  d->n = (t*)calloc((size_t)((c) > 0 ? (c) : 1), sizeof(t));
+  DATA_FIELDS(X)
+#undef X
+  d->contact = (OContact*)calloc(m->nconmax > 0 ? m->nconmax : 1, sizeof(OContact));
+  int nv = m->nv > 0 ? m->nv : 1, nj = m->njmax > 0 ? m->njmax : 1;
+  d->s_Ma = calloc(nv, 8); d->s_jar = calloc(nj, 8); d->s_grad = calloc(nv, 8);
+  d->s_Mgrad = calloc(nv, 8); d->s_search = calloc(nv, 8); d->s_Mv = calloc(nv, 8);
+  d->s_jv = calloc(nj, 8); d->s_H = calloc((size_t)nv * nv, 8);
+  d->s_Mdense = calloc((size_t)nv * nv, 8);
+  o_reset(m, d);
+  return d;
+}
+
+void od_free(OData* d) {
+  if (!d) return;
+#define X(n, t, c) free(d->n);
+  DATA_FIELDS(X)
+#undef X
+  free(d->contact);
+  free(d->s_Ma); free(d->s_jar); free(d->s_grad); free(d->s_Mgrad);
+  free(d->s_search); free(d->s_Mv); free(d->s_jv); free(d->s_H);
+  free(d->s_Mdense);
+  free(d);
+}
+
+void* od_field(OData* d, const char* name, int64_t* count, int* dtype) {
+#define X(n, t, c) if (strcmp(name, #n) == 0) { \
+    if (count) *count = d->n##_count; \
+    if (dtype) { *dtype = (sizeof(t) == 8) ? 0 : 1; } \
+    return d->n; }
+  DATA_FIELDS(X)
+#undef X
+  return NULL;
+}
+
+void o_reset(const OModel* m, OData* d) {
+#define X(n, t, c) memset(d->n, 0, sizeof(t) * (size_t)((c) > 0 ? (c) : 1));
+  DATA_FIELDS(X)
+#undef X
+  memcpy(d->qpos, m->qpos0, sizeof(double) * m->nq);
+}
+
+/* ------------------------------------------------------------- small math */
+
+static inline double dot3(const double* a, const double* b) {
+  return a[0] * b[0] + a[1] * b[1] + a[2] * b[2];
+}
+static inline void cross3(double* r, const double* a, const double* b) {
+  double x = a[1] * b[2] - a[2] * b[1], y = a[2] * b[0] - a[0] * b[2],
+         z = a[0] * b[1] - a[1] * b[0];
+  r[0] = x; r[1] = y; r[2] = z;
+}
+static inline double norm3(const double* a) { return sqrt(dot3(a, a)); }
+static inline double normalize3(double* a) {
+  double n = norm3(a);
+  if (n < MINVAL) { a[0] = 1; a[1] = 0; a[2] = 0; }
+  else { a[0] /= n; a[1] /= n; a[2] /= n; }
+  return n;
+}
+static inline void normalize4(double* q) {
+  double n = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
+  if (n < MINVAL) { q[0] = 1; q[1] = q[2] = q[3] = 0; }
+  else { q[0] /= n; q[1] /= n; q[2] /= n; q[3] /= n; }
+}
+static inline void quat_mul(double* r, const double* a, const double* b) {
+  double w = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3];
+  double x = a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2];
+  double y = a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1];
+  double z = a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0];
+  r[0] = w; r[1] = x; r[2] = y; r[3] = z;
+}
+static inline void quat2mat(double* R, const double* q) {
+  double w = q[0], x = q[1], y = q[2], z = q[3];
+  R[0] = w * w + x * x - y * y - z * z; R[1] = 2 * (x * y - w * z);
+  R[2] = 2 * (x * z + w * y); R[3] = 2 * (x * y + w * z);
+  R[4] = w * w - x * x + y * y - z * z; R[5] = 2 * (y * z - w * x);
+  R[6] = 2 * (x * z - w * y); R[7] = 2 * (y * z + w * x);
+  R[8] = w * w - x * x - y * y + z * z;
+}
+static inline void mat_vec3(double* r, const double* R, const double* v) {
+  double x = R[0] * v[0] + R[1] * v[1] + R[2] * v[2];
+  double y = R[3] * v[0] + R[4] * v[1] + R[5] * v[2];
+  double z = R[6] * v[0] + R[7] * v[1] + R[8] * v[2];
+  r[0] = x; r[1] = y; r[2] = z;
+}
+static inline void matT_vec3(double* r, const double* R, const double* v) {
+  double x = R[0] * v[0] + R[3] * v[1] + R[6] * v[2];
+  double y = R[1] * v[0] + R[4] * v[1] + R[7] * v[2];
+  double z = R[2] * v[0] + R[5] * v[1] + R[8] * v[2];
+  r[0] = x; r[1] = y; r[2] = z;
+}
+static inline void axis_angle_quat(double* q, const double* axis, double ang) {
+  double s = sin(0.5 * ang);
+  q[0] = cos(0.5 * ang); q[1] = axis[0] * s; q[2] = axis[1] * s; q[3] = axis[2] * s;
+}
+/* integrate a quaternion by a body-frame angular velocity over dt */
+static void quat_integrate(double* q, const double* w, double dt) {
+  double ax[3] = {w[0], w[1], w[2]};
+  double n = norm3(ax);
+  if (n < MINVAL) return;
+  ax[0] /= n; ax[1] /= n; ax[2] /= n;
+  double dq[4], r[4];
+  axis_angle_quat(dq, ax, n * dt);
+  quat_mul(r, q, dq);
+  normalize4(r);
+  memcpy(q, r, 32);
+}
+
+/* spatial algebra: motion vectors [w; v], force vectors [torque; force], both
+ * referred to the kinematic tree's centre of mass */
+static void cross_motion(double* r, const double* v, const double* s) {
+  double a[3], b[3], c[3];
+  cross3(a, v, s);          /* w_v x w_s */
+  cross3(b, v, s + 3);      /* w_v x v_s */
+  cross3(c, v + 3, s);      /* v_v x w_s */
+  r[0] = a[0]; r[1] = a[1]; r[2] = a[2];
+  r[3] = b[0] + c[0]; r[4] = b[1] + c[1]; r[5] = b[2] + c[2];
+}
+static void cross_force(double* r, const double* v, const double* f) {
+  double a[3], b[3], c[3];
+  cross3(a, v, f);          /* w x torque */
+  cross3(b, v + 3, f + 3);  /* v x force  */
+  cross3(c, v, f + 3);      /* w x force  */
+  r[0] = a[0] + b[0]; r[1] = a[1] + b[1]; r[2] = a[2] + b[2];
+  r[3] = c[0]; r[4] = c[1]; r[5] = c[2];
+}
+/* 10-number spatial inertia about the reference point:
+ * [Ixx Iyy Izz Ixy Ixz Iyz  m*dx m*dy m*dz  m] */
+static void inert_mul(double* r, const double* I, const double* v) {
+  const double* h = I + 6;
+  double t[3], f[3];
+  t[0] = I[0] * v[0] + I[3] * v[1] + I[4] * v[2];
+  t[1] = I[3] * v[0] + I[1] * v[1] + I[5] * v[2];
+  t[2] = I[4] * v[0] + I[5] * v[1] + I[2] * v[2];
+  double hv[3], wh[3];
+  cross3(hv, h, v + 3);     /* (m d) x v  */
+  cross3(wh, v, h);         /* w x (m d)  */
+  f[0] = I[9] * v[3] + wh[0]; f[1] = I[9] * v[4] + wh[1]; f[2] = I[9] * v[5] + wh[2];
+  r[0] = t[0] + hv[0]; r[1] = t[1] + hv[1]; r[2] = t[2] + hv[2];
+  r[3] = f[0]; r[4] = f[1]; r[5] = f[2];
+}
+static inline double dot6(const double* a, const double* b) {
+  return a[0] * b[0] + a[1] * b[1] + a[2] * b[2] + a[3] * b[3] + a[4] * b[4] +
+         a[5] * b[5];
+}
+
+static void warn(OData* d, int w) { d->warning[w]++; }
+
+/* ------------------------------------------------ position stage [A.1-A.4] */
+
+static void o_kinematics(const OModel* m, OData* d) {
+  /* normalise quaternions stored in qpos */
+  for (int j = 0; j < m->njnt; j++) {
+    if (m->jnt_type[j] == JNT_FREE) normalize4(d->qpos + m->jnt_qposadr[j] + 3);
+    else if (m->jnt_type[j] == JNT_BALL) normalize4(d->qpos + m->jnt_qposadr[j]);
+  }
+  d->xquat[0] = 1;
+  d->xmat[0] = d->xmat[4] = d->xmat[8] = 1;
+  for (int b = 1; b < m->nbody; b++) {
+    int p = m->body_parentid[b];
+    double pos[3], quat[4], R[9], t[3];
+    mat_vec3(t, d->xmat + 9 * p, m->body_pos + 3 * b);
+    for (int k = 0; k < 3; k++) pos[k] = d->xpos[3 * p + k] + t[k];
+    quat_mul(quat, d->xquat + 4 * p, m->body_quat + 4 * b);
+    for (int k = 0; k < m->body_jntnum[b]; k++) {
+      int j = m->body_jntadr[b] + k, qa = m->jnt_qposadr[j];
+      int jt = m->jnt_type[j];
+      if (jt == JNT_FREE) {
+        memcpy(pos, d->qpos + qa, 24);
+        memcpy(quat, d->qpos + qa + 3, 32);
+        memcpy(d->xanchor + 3 * j, pos, 24);
+        d->xaxis[3 * j] = 0; d->xaxis[3 * j + 1] = 0; d->xaxis[3 * j + 2] = 1;
+        continue;
+      }
+      quat2mat(R, quat);
+      mat_vec3(t, R, m->jnt_pos + 3 * j);
+      double* anchor = d->xanchor + 3 * j;
+      for (int c = 0; c < 3; c++) anchor[c] = pos[c] + t[c];
+      mat_vec3(d->xaxis + 3 * j, R, m->jnt_axis + 3 * j);
+      if (jt == JNT_SLIDE) {
+        double dq = d->qpos[qa] - m->qpos0[qa];
+        for (int c = 0; c < 3; c++) pos[c] += d->xaxis[3 * j + c] * dq;
+      } else {
+        double qr[4], qn[4];
+        if (jt == JNT_HINGE)
+          axis_angle_quat(qr, m->jnt_axis + 3 * j, d->qpos[qa] - m->qpos0[qa]);
+        else
+          memcpy(qr, d->qpos + qa, 32);
+        quat_mul(qn, quat, qr);
+        memcpy(quat, qn, 32);
+        quat2mat(R, quat);
+        mat_vec3(t, R, m->jnt_pos + 3 * j);
+        for (int c = 0; c < 3; c++) pos[c] = anchor[c] - t[c];
+      }
+    }
+    normalize4(quat);
+    memcpy(d->xpos + 3 * b, pos, 24);
+    memcpy(d->xquat + 4 * b, quat, 32);
+    quat2mat(d->xmat + 9 * b, quat);
+  }
+  for (int b = 0; b < m->nbody; b++) {
+    double t[3], q[4];
+    mat_vec3(t, d->xmat + 9 * b, m->body_ipos + 3 * b);
+    for (int c = 0; c < 3; c++) d->xipos[3 * b + c] = d->xpos[3 * b + c] + t[c];
+    quat_mul(q, d->xquat + 4 * b, m->body_iquat + 4 * b);
+    quat2mat(d->ximat + 9 * b, q);
+  }
+  for (int g = 0; g < m->ngeom; g++) {
+    int b = m->geom_bodyid[g];
+    double t[3], q[4];
+    mat_vec3(t, d->xmat + 9 * b, m->geom_pos + 3 * g);
+    for (int c = 0; c < 3; c++) d->geom_xpos[3 * g + c] = d->xpos[3 * b + c] + t[c];
+    quat_mul(q, d->xquat + 4 * b, m->geom_quat + 4 * g);
+    quat2mat(d->geom_xmat + 9 * g, q);
+  }
+  for (int s = 0; s < m->nsite; s++) {
+    int b = m->site_bodyid[s];
+    double t[3], q[4];
+    mat_vec3(t, d->xmat + 9 * b, m->site_pos + 3 * s);
+    for (int c = 0; c < 3; c++) d->site_xpos[3 * s + c] = d->xpos[3 * b + c] + t[c];
+    quat_mul(q, d->xquat + 4 * b, m->site_quat + 4 * s);
+    quat2mat(d->site_xmat + 9 * s, q);
+  }
+}
+
+static void o_com_pos(const OModel* m, OData* d) {
+  int nb = m->nbody;
+  for (int b = 0; b < nb; b++)
+    for (int c = 0; c < 3; c++)
+      d->subtree_com[3 * b + c] = m->body_mass[b] * d->xipos[3 * b + c];
+  for (int b = nb - 1; b > 0; b--) {
+    int p = m->body_parentid[b];
+    for (int c = 0; c < 3; c++) d->subtree_com[3 * p + c] += d->subtree_com[3 * b + c];
+  }
+  for (int b = 0; b < nb; b++) {
+    if (m->body_subtreemass[b] < MINVAL)
+      memcpy(d->subtree_com + 3 * b, d->xipos + 3 * b, 24);
+    else
+      for (int c = 0; c < 3; c++) d->subtree_com[3 * b + c] /= m->body_subtreemass[b];
+  }
+  /* body inertias about the tree COM, world axes */
+  for (int b = 1; b < nb; b++) {
+    const double* R = d->ximat + 9 * b;
+    const double* I = m->body_inertia + 3 * b;
+    const double* com = d->subtree_com + 3 * m->body_rootid[b];
+    double mass = m->body_mass[b], dif[3];
+    for (int c = 0; c < 3; c++) dif[c] = d->xipos[3 * b + c] - com[c];
+    double T[9];
+    for (int r = 0; r < 3; r++)
+      for (int c = 0; c < 3; c++)
+        T[3 * r + c] = R[3 * r] * I[0] * R[3 * c] + R[3 * r + 1] * I[1] * R[3 * c + 1] +
+                       R[3 * r + 2] * I[2] * R[3 * c + 2];
+    double* ci = d->cinert + 10 * b;
+    ci[0] = T[0] + mass * (dif[1] * dif[1] + dif[2] * dif[2]);
+    ci[1] = T[4] + mass * (dif[0] * dif[0] + dif[2] * dif[2]);
+    ci[2] = T[8] + mass * (dif[0] * dif[0] + dif[1] * dif[1]);
+    ci[3] = T[1] - mass * dif[0] * dif[1];
+    ci[4] = T[2] - mass * dif[0] * dif[2];
+    ci[5] = T[5] - mass * dif[1] * dif[2];
+    ci[6] = mass * dif[0]; ci[7] = mass * dif[1]; ci[8] = mass * dif[2];
+    ci[9] = mass;
+  }
+  /* motion axes about the tree COM */
+  for (int j = 0; j < m->njnt; j++) {
+    int b = m->jnt_bodyid[j], da = m->jnt_dofadr[j];
+    const double* com = d->subtree_com + 3 * m->body_rootid[b];
+    double off[3];
+    for (int c = 0; c < 3; c++) off[c] = com[c] - d->xanchor[3 * j + c];
+    int jt = m->jnt_type[j];
+    if (jt == JNT_SLIDE) {
+      double* cd = d->cdof + 6 * da;
+      cd[0] = cd[1] = cd[2] = 0;
+      memcpy(cd + 3, d->xaxis + 3 * j, 24);
+    } else if (jt == JNT_HINGE) {
+      double* cd = d->cdof + 6 * da;
+      memcpy(cd, d->xaxis + 3 * j, 24);
+      cross3(cd + 3, cd, off);
+    } else {
+      if (jt == JNT_FREE) {
+        for (int k = 0; k < 3; k++) {
+          double* cd = d->cdof + 6 * (da + k);
+          memset(cd, 0, 48);
+          cd[3 + k] = 1;
+        }
+        da += 3;
+      }
+      const double* R = d->xmat + 9 * b;
+      for (int k = 0; k < 3; k++) {
+        double* cd = d->cdof + 6 * (da + k);
+        cd[0] = R[k]; cd[1] = R[3 + k]; cd[2] = R[6 + k];
+        cross3(cd + 3, cd, off);
+      }
+    }
+  }
+}
+
+static void o_crb(const OModel* m, OData* d) {
+  int nb = m->nbody, nv = m->nv;
+  memcpy(d->crb, d->cinert, sizeof(double) * 10 * nb);
+  for (int b = nb - 1; b > 0; b--) {
+    int p = m->body_parentid[b];
+    if (p > 0)
+      for (int c = 0; c < 10; c++) d->crb[10 * p + c] += d->crb[10 * b + c];
+  }
+  memset(d->qM, 0, sizeof(double) * m->nM);
+  for (int i = 0; i < nv; i++) {
+    double buf[6];
+    inert_mul(buf, d->crb + 10 * m->dof_bodyid[i], d->cdof + 6 * i);
+    int adr = m->dof_Madr[i];
+    d->qM[adr] = m->dof_armature[i];
+    for (int j = i; j >= 0; j = m->dof_parentid[j])
+      d->qM[adr++] += dot6(d->cdof + 6 * j, buf);
+  }
+}
+
+/* in-place sparse L^T D L of a qM-layout matrix [A.4] */
+static void factor_sparse(const OModel* m, double* LD, double* diaginv) {
+  int nv = m->nv;
+  for (int k = nv - 1; k >= 0; k--) {
+    int akk = m->dof_Madr[k];
+    int aki = akk + 1;
+    double dkk = LD[akk];
+    for (int i = m->dof_parentid[k]; i >= 0; i = m->dof_parentid[i], aki++) {
+      double t = LD[aki] / dkk;
+      int aij = m->dof_Madr[i], akj = aki;
+      for (int j = i; j >= 0; j = m->dof_parentid[j]) LD[aij++] -= t * LD[akj++];
+      LD[aki] = t;
+    }
+    diaginv[k] = 1.0 / dkk;
+  }
+}
+
+static void solve_sparse(const OModel* m, const double* LD, const double* diaginv,
+                         double* x) {
+  int nv = m->nv;
+  for (int i = nv - 1; i >= 0; i--) {          /* x <- L^-T x */
+    int a = m->dof_Madr[i] + 1;
+    for (int j = m->dof_parentid[i]; j >= 0; j = m->dof_parentid[j])
+      x[j] -= LD[a++] * x[i];
+  }
+  for (int i = 0; i < nv; i++) x[i] *= diaginv[i];
+  for (int i = 0; i < nv; i++) {               /* x <- L^-1 x */
+    int a = m->dof_Madr[i] + 1;
+    for (int j = m->dof_parentid[i]; j >= 0; j = m->dof_parentid[j])
+      x[i] -= LD[a++] * x[j];
+  }
+}
+
+static void o_factor_m(const OModel* m, OData* d) {
+  memcpy(d->qLD, d->qM, sizeof(double) * m->nM);
+  factor_sparse(m, d->qLD, d->qLDiagInv);
+}
+
+static void mul_m(const OModel* m, const double* qM, double* res, const double* v) {
+  for (int i = 0; i < m->nv; i++) res[i] = 0;
+  for (int i = 0; i < m->nv; i++) {
+    int a = m->dof_Madr[i];
+    res[i] += qM[a] * v[i];
+    a++;
+    for (int j = m->dof_parentid[i]; j >= 0; j = m->dof_parentid[j], a++) {
+      res[i] += qM[a] * v[j];
+      res[j] += qM[a] * v[i];
+    }
+  }
+}
+
+/* --------------------------------------------------- velocity stage [A.5] */
+
+static void o_com_vel(const OModel* m, OData* d) {
+  memset(d->cvel, 0, 48);
+  for (int b = 1; b < m->nbody; b++) {
+    double cv[6];
+    memcpy(cv, d->cvel + 6 * m->body_parentid[b], 48);
+    for (int k = 0; k < m->body_jntnum[b]; k++) {
+      int j = m->body_jntadr[b] + k, da = m->jnt_dofadr[j], jt = m->jnt_type[j];
+      if (jt == JNT_FREE) {
+        for (int i = 0; i < 3; i++) {
+          memset(d->cdof_dot + 6 * (da + i), 0, 48);
+          for (int c = 0; c < 6; c++) cv[c] += d->cdof[6 * (da + i) + c] * d->qvel[da + i];
+        }
+        da += 3;
+      }
+      int n = (jt == JNT_FREE || jt == JNT_BALL) ? 3 : 1;
+      for (int i = 0; i < n; i++)
+        cross_motion(d->cdof_dot + 6 * (da + i), cv, d->cdof + 6 * (da + i));
+      for (int i = 0; i < n; i++)
+        for (int c = 0; c < 6; c++) cv[c] += d->cdof[6 * (da + i) + c] * d->qvel[da + i];
+    }
+    memcpy(d->cvel + 6 * b, cv, 48);
+  }
+}
+
+static void o_passive(const OModel* m, OData* d) {
+  memset(d->qfrc_passive, 0, sizeof(double) * m->nv);
+  if (m->opt_disableflags & DSBL_PASSIVE) return;
+  for (int j = 0; j < m->njnt; j++) {
+    double k = m->jnt_stiffness[j];
+    if (k == 0) continue;
+    int jt = m->jnt_type[j], qa = m->jnt_qposadr[j], da = m->jnt_dofadr[j];
+    if (jt == JNT_SLIDE || jt == JNT_HINGE)
+      d->qfrc_passive[da] -= k * (d->qpos[qa] - m->qpos_spring[qa]);
+  }
+  for (int i = 0; i < m->nv; i++) d->qfrc_passive[i] -= m->dof_damping[i] * d->qvel[i];
+}
+
+/* recursive Newton-Euler; flg_acc adds cdof*qacc.  result = inverse-dynamics
+ * joint forces */
+static void o_rne(const OModel* m, OData* d, int flg_acc, double* result) {
+  int nb = m->nbody;
+  double* cacc = (double*)calloc(6 * nb, 8);
+  double* cfrc = (double*)calloc(6 * nb, 8);
+  if (!(m->opt_disableflags & DSBL_GRAVITY))
+    for (int c = 0; c < 3; c++) cacc[3 + c] = -m->opt_gravity[c];
+  for (int b = 1; b < nb; b++) {
+    double* a = cacc + 6 * b;
+    memcpy(a, cacc + 6 * m->body_parentid[b], 48);
+    int da = m->body_dofadr[b];
+    for (int k = 0; k < m->body_dofnum[b]; k++) {
+      for (int c = 0; c < 6; c++) {
+        a[c] += d->cdof_dot[6 * (da + k) + c] * d->qvel[da + k];
+        if (flg_acc) a[c] += d->cdof[6 * (da + k) + c] * d->qacc[da + k];
+      }
+    }
+    double Ia[6], Iv[6], vxIv[6];
+    inert_mul(Ia, d->cinert + 10 * b, a);
+    inert_mul(Iv, d->cinert + 10 * b, d->cvel + 6 * b);
+    cross_force(vxIv, d->cvel + 6 * b, Iv);
+    for (int c = 0; c < 6; c++) cfrc[6 * b + c] = Ia[c] + vxIv[c];
+  }
+  for (int b = nb - 1; b > 0; b--) {
+    int p = m->body_parentid[b];
+    for (int c = 0; c < 6; c++) cfrc[6 * p + c] += cfrc[6 * b + c];
+  }
+  for (int i = 0; i < m->nv; i++)
+    result[i] = dot6(d->cdof + 6 * i, cfrc + 6 * m->dof_bodyid[i]);
+  free(cacc); free(cfrc);
+}
+
+/* ------------------------------------------------------ actuation [A.6] */
+
+static void o_transmission(const OModel* m, OData* d) {
+  int nv = m->nv;
+  memset(d->actuator_moment, 0, sizeof(double) * m->nu * nv);
+  for (int i = 0; i < m->nu; i++) {
+    int j = m->actuator_trnid[2 * i];
+    double g = m->actuator_gear[6 * i];
+    /* joint transmission, scalar joints only in this subset */
+    d->actuator_length[i] = g * d->qpos[m->jnt_qposadr[j]];
+    d->actuator_moment[i * nv + m->jnt_dofadr[j]] = g;
+  }
+}
+
+static void o_fwd_actuation(const OModel* m, OData* d) {
+  int nv = m->nv, nu = m->nu;
+  memset(d->qfrc_actuator, 0, sizeof(double) * nv);
+  memset(d->actuator_force, 0, sizeof(double) * nu);
+  for (int i = 0; i < m->na; i++) d->act_dot[i] = 0;
+  if (nu == 0 || (m->opt_disableflags & DSBL_ACTUATION)) return;
+  for (int i = 0; i < nu; i++)
+    if (isnan(d->ctrl[i]) || fabs(d->ctrl[i]) > MAXVAL) {
+      warn(d, W_BADCTRL);
+      memset(d->ctrl, 0, sizeof(double) * nu);
+      break;
+    }
+  int ia = 0;
+  for (int i = 0; i < nu; i++) {
+    double c = d->ctrl[i];
+    if (m->actuator_ctrllimited[i] && !(m->opt_disableflags & DSBL_CLAMPCTRL)) {
+      double lo = m->actuator_ctrlrange[2 * i], hi = m->actuator_ctrlrange[2 * i + 1];
+      c = c < lo ? lo : (c > hi ? hi : c);
+    }
+    double in = c;
+    int dyn = m->actuator_dyntype[i];
+    if (dyn != 0) {
+      double a = d->act[ia];
+      if (dyn == 1) d->act_dot[ia] = c;                             /* integrator */
+      else d->act_dot[ia] = (c - a) / fmax(MINVAL, m->actuator_dynprm[3 * i]);
+      in = a;
+      ia++;
+    }
+    double f = m->actuator_gainprm[3 * i] * in;
+    if (m->actuator_biastype[i] == 1)
+      f += m->actuator_biasprm[3 * i] +
+           m->actuator_biasprm[3 * i + 1] * d->actuator_length[i] +
+           m->actuator_biasprm[3 * i + 2] * d->actuator_velocity[i];
+    if (m->actuator_forcelimited[i]) {
+      double lo = m->actuator_forcerange[2 * i], hi = m->actuator_forcerange[2 * i + 1];
+      f = f < lo ? lo : (f > hi ? hi : f);
+    }
+    d->actuator_force[i] = f;
+    for (int k = 0; k < nv; k++) d->qfrc_actuator[k] += d->actuator_moment[i * nv + k] * f;
+  }
+}
+
+static void o_fwd_acceleration(const OModel* m, OData* d) {
+  for (int i = 0; i < m->nv; i++) {
+    d->qfrc_smooth[i] = d->qfrc_passive[i] - d->qfrc_bias[i] + d->qfrc_actuator[i] +
+                        d->qfrc_applied[i];
+    d->qacc_smooth[i] = d->qfrc_smooth[i];
+  }
+  solve_sparse(m, d->qLD, d->qLDiagInv, d->qacc_smooth);
+}
+
+/* ------------------------------------------------------- collision [A.7] */
+
+typedef struct { double dist, pos[3], frame[9]; } RawCon;
+
+static int col_plane_sphere_raw(const double* ppos, const double* pn,
+                                const double* c, double r, double margin,
+                                RawCon* out) {
+  double dif[3] = {c[0] - ppos[0], c[1] - ppos[1], c[2] - ppos[2]};
+  double dist = dot3(dif, pn) - r;
+  if (dist > margin) return 0;
+  out->dist = dist;
+  for (int k = 0; k < 3; k++) {
+    out->pos[k] = c[k] - pn[k] * (r + 0.5 * dist);
+    out->frame[k] = pn[k];
+  }
+  memset(out->frame + 3, 0, 48);
+  return 1;
+}
+
+static int col_sphere_sphere_raw(const double* c1, double r1, const double* c2,
+                                 double r2, double margin, RawCon* out) {
+  double n[3] = {c2[0] - c1[0], c2[1] - c1[1], c2[2] - c1[2]};
+  double len = norm3(n);
+  double dist = len - r1 - r2;
+  if (dist > margin) return 0;
+  if (len < MINVAL) { n[0] = 1; n[1] = 0; n[2] = 0; }
+  else { n[0] /= len; n[1] /= len; n[2] /= len; }
+  out->dist = dist;
+  for (int k = 0; k < 3; k++) {
+    out->pos[k] = c1[k] + n[k] * (r1 + 0.5 * dist);
+    out->frame[k] = n[k];
+  }
+  memset(out->frame + 3, 0, 48);
+  return 1;
+}
+
+static void geom_axis(const double* xmat, int col, double* ax) {
+  ax[0] = xmat[col]; ax[1] = xmat[3 + col]; ax[2] = xmat[6 + col];
+}
+
+static int collide_pair(const OModel* m, const OData* d, int g1, int g2,
+                        double margin, RawCon* out) {
+  int t1 = m->geom_type[g1], t2 = m->geom_type[g2];
+  const double *p1 = d->geom_xpos + 3 * g1, *p2 = d->geom_xpos + 3 * g2;
+  const double *R1 = d->geom_xmat + 9 * g1, *R2 = d->geom_xmat + 9 * g2;
+  const double *s1 = m->geom_size + 3 * g1, *s2 = m->geom_size + 3 * g2;
+  if (t1 == GEOM_PLANE) {
+    double n[3];
+    geom_axis(R1, 2, n);
+    if (t2 == GEOM_SPHERE) return col_plane_sphere_raw(p1, n, p2, s2[0], margin, out);
+    if (t2 == GEOM_CAPSULE) {
+      double ax[3], e[3];
+      geom_axis(R2, 2, ax);
+      int cnt = 0;
+      for (int sgn = 1; sgn >= -1; sgn -= 2) {
+        for (int k = 0; k < 3; k++) e[k] = p2[k] + sgn * ax[k] * s2[1];
+        if (col_plane_sphere_raw(p1, n, e, s2[0], margin, out + cnt)) {
+          memcpy(out[cnt].frame + 3, ax, 24);   /* tangent hint: capsule axis */
+          cnt++;
+        }
+      }
+      return cnt;
+    }
+    if (t2 == GEOM_BOX) {
+      double dif[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
+      double dist = dot3(dif, n);
+      int cnt = 0;
+      for (int i = 0; i < 8 && cnt < 4; i++) {
+        double v[3] = {(i & 1) ? s2[0] : -s2[0], (i & 2) ? s2[1] : -s2[1],
+                       (i & 4) ? s2[2] : -s2[2]};
+        double c[3];
+        mat_vec3(c, R2, v);
+        double ld = dot3(n, c);
+        if (dist + ld > margin) continue;
+        out[cnt].dist = dist + ld;
+        for (int k = 0; k < 3; k++) {
+          out[cnt].pos[k] = p2[k] + c[k] - n[k] * 0.5 * (dist + ld);
+          out[cnt].frame[k] = n[k];
+        }
+        memset(out[cnt].frame + 3, 0, 48);
+        cnt++;
+      }
+      return cnt;
+    }
+    return 0;
+  }
+  if (t1 == GEOM_SPHERE && t2 == GEOM_SPHERE)
+    return col_sphere_sphere_raw(p1, s1[0], p2, s2[0], margin, out);
+  if (t1 == GEOM_SPHERE && t2 == GEOM_CAPSULE) {
+    double ax[3], dif[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
+    geom_axis(R2, 2, ax);
+    double x = dot3(ax, dif);
+    x = x < -s2[1] ? -s2[1] : (x > s2[1] ? s2[1] : x);
+    double c[3] = {p2[0] + ax[0] * x, p2[1] + ax[1] * x, p2[2] + ax[2] * x};
+    return col_sphere_sphere_raw(p1, s1[0], c, s2[0], margin, out);
+  }
+  if (t1 == GEOM_CAPSULE && t2 == GEOM_CAPSULE) {
+    /* closest points of two segments p1 + x1*a1, p2 + x2*a2, |xi| <= li */
+    double a1[3], a2[3], dif[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
+    geom_axis(R1, 2, a1); geom_axis(R2, 2, a2);
+    double l1 = s1[1], l2 = s2[1];
+    double b = dot3(a1, a2), u = -dot3(a1, dif), v = dot3(a2, dif);
+    double det = 1.0 - b * b;
+    double x1, x2;
+    if (fabs(det) >= 1e-12) {
+      x1 = (u + b * v) / det;
+      x2 = (v + b * u) / det;
+      if (x1 > l1) { x1 = l1; x2 = v + b * x1; }
+      else if (x1 < -l1) { x1 = -l1; x2 = v + b * x1; }
+      if (x2 > l2) {
+        x2 = l2; x1 = u + b * x2;
+        x1 = x1 < -l1 ? -l1 : (x1 > l1 ? l1 : x1);
+      } else if (x2 < -l2) {
+        x2 = -l2; x1 = u + b * x2;
+        x1 = x1 < -l1 ? -l1 : (x1 > l1 ? l1 : x1);
+      }
+    } else {
+      /* parallel axes: centre of the overlap interval */
+      x1 = u; x1 = x1 < -l1 ? -l1 : (x1 > l1 ? l1 : x1);
+      x2 = v + b * x1; x2 = x2 < -l2 ? -l2 : (x2 > l2 ? l2 : x2);
+      x1 = u + b * x2; x1 = x1 < -l1 ? -l1 : (x1 > l1 ? l1 : x1);
+    }
+    double c1[3], c2[3];
+    for (int k = 0; k < 3; k++) { c1[k] = p1[k] + a1[k] * x1; c2[k] = p2[k] + a2[k] * x2; }
+    return col_sphere_sphere_raw(c1, s1[0], c2, s2[0], margin, out);
+  }
+  return 0;
+}
+
+static void make_frame(double* f) {
+  normalize3(f);
+  if (norm3(f + 3) < 0.5) {
+    f[3] = f[4] = f[5] = 0;
+    if (f[1] < 0.5 && f[1] > -0.5) f[4] = 1; else f[5] = 1;
+  }
+  double t = dot3(f, f + 3);
+  for (int k = 0; k < 3; k++) f[3 + k] -= t * f[k];
+  normalize3(f + 3);
+  cross3(f + 6, f, f + 3);
+}
+
+static void o_collision(const OModel* m, OData* d) {
+  d->ncon[0] = 0;
+  if (m->opt_disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT)) return;
+  int filterparent = !(m->opt_disableflags & DSBL_FILTERPARENT);
+  for (int p = 0; p < m->npair; p++) {
+    int g1 = m->pair_geom1[p], g2 = m->pair_geom2[p];
+    if (filterparent && m->pair_parentchild[p]) continue;
+    double margin = fmax(m->geom_margin[g1], m->geom_margin[g2]);
+    double gap = fmax(m->geom_gap[g1], m->geom_gap[g2]);
+    /* bounding-sphere rejection */
+    const double *p1 = d->geom_xpos + 3 * g1, *p2 = d->geom_xpos + 3 * g2;
+    if (m->geom_type[g1] == GEOM_PLANE) {
+      double n[3], dif[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
+      geom_axis(d->geom_xmat + 9 * g1, 2, n);
+      if (dot3(dif, n) > m->geom_rbound[g2] + margin) continue;
+    } else {
+      double dif[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
+      double bound = m->geom_rbound[g1] + m->geom_rbound[g2] + margin;
+      if (dot3(dif, dif) > bound * bound) continue;
+    }
+    RawCon raw[8];
+    int n = collide_pair(m, d, g1, g2, margin, raw);
+    for (int i = 0; i < n; i++) {
+      if (d->ncon[0] >= m->nconmax) { warn(d, W_CONTACTFULL); return; }
+      OContact* c = d->contact + d->ncon[0];
+      int id = d->ncon[0]++;
+      c->dist = raw[i].dist;
+      memcpy(c->pos, raw[i].pos, 24);
+      memcpy(c->frame, raw[i].frame, 72);
+      make_frame(c->frame);
+      c->includemargin = margin - gap;
+      c->geom1 = g1; c->geom2 = g2;
+      int dim1 = m->geom_condim[g1], dim2 = m->geom_condim[g2];
+      c->dim = dim1 > dim2 ? dim1 : dim2;
+      const double *f1 = m->geom_friction + 3 * g1, *f2 = m->geom_friction + 3 * g2;
+      double fr[3];
+      for (int k = 0; k < 3; k++) fr[k] = fmax(f1[k], f2[k]);
+      c->friction[0] = c->friction[1] = fr[0];
+      c->friction[2] = fr[1];
+      c->friction[3] = c->friction[4] = fr[2];
+      double mix1 = m->geom_solmix[g1], mix2 = m->geom_solmix[g2], mix;
+      if (mix1 >= MINVAL && mix2 >= MINVAL) mix = mix1 / (mix1 + mix2);
+      else if (mix1 < MINVAL && mix2 < MINVAL) mix = 0.5;
+      else mix = mix1 < MINVAL ? 0.0 : 1.0;
+      for (int k = 0; k < 2; k++)
+        c->solref[k] = mix * m->geom_solref[2 * g1 + k] + (1 - mix) * m->geom_solref[2 * g2 + k];
+      for (int k = 0; k < 5; k++)
+        c->solimp[k] = mix * m->geom_solimp[5 * g1 + k] + (1 - mix) * m->geom_solimp[5 * g2 + k];
+      c->exclude = c->dist >= c->includemargin;
+      c->efc_address = -1;
+      d->contact_geom1[id] = g1; d->contact_geom2[id] = g2;
+      d->contact_dim[id] = c->dim; d->contact_dist[id] = c->dist;
+      memcpy(d->contact_pos + 3 * id, c->pos, 24);
+      memcpy(d->contact_frame + 9 * id, c->frame, 72);
+    }
+  }
+}
