@@ -916,3 +916,898 @@ static void o_collision(const OModel* m, OData* d) {
     }
   }
 }
+
+/* --------------------------------------------- constraint rows [A.8] */
+
+/* translational / rotational Jacobian (3 x nv each) of a world point on a body */
+static void o_jac(const OModel* m, const OData* d, double* jp, double* jr,
+                  const double* point, int body) {
+  int nv = m->nv;
+  if (jp) memset(jp, 0, sizeof(double) * 3 * nv);
+  if (jr) memset(jr, 0, sizeof(double) * 3 * nv);
+  while (body > 0 && m->body_dofnum[body] == 0) body = m->body_parentid[body];
+  if (body == 0) return;
+  const double* com = d->subtree_com + 3 * m->body_rootid[body];
+  double off[3] = {point[0] - com[0], point[1] - com[1], point[2] - com[2]};
+  for (int i = m->body_dofadr[body] + m->body_dofnum[body] - 1; i >= 0;
+       i = m->dof_parentid[i]) {
+    const double* cd = d->cdof + 6 * i;
+    if (jr) { jr[i] = cd[0]; jr[nv + i] = cd[1]; jr[2 * nv + i] = cd[2]; }
+    if (jp) {
+      double t[3];
+      cross3(t, cd, off);
+      jp[i] = cd[3] + t[0]; jp[nv + i] = cd[4] + t[1]; jp[2 * nv + i] = cd[5] + t[2];
+    }
+  }
+}
+
+static int add_row(const OModel* m, OData* d, int type, int id, double pos,
+                   double margin, double floss) {
+  if (d->nefc[0] >= m->njmax) { warn(d, W_CNSTRFULL); return -1; }
+  int r = d->nefc[0]++;
+  memset(d->efc_J + (size_t)r * m->nv, 0, sizeof(double) * m->nv);
+  d->efc_type[r] = type; d->efc_id[r] = id; d->efc_pos[r] = pos;
+  d->efc_margin[r] = margin; d->efc_frictionloss[r] = floss;
+  return r;
+}
+
+static void impedance(const double* si, double pos, double margin, double* imp,
+                      double* impP) {
+  if (si[0] == si[1] || si[2] <= MINVAL) { *imp = 0.5 * (si[0] + si[1]); *impP = 0; return; }
+  double x = (pos - margin) / si[2], sgn = 1;
+  if (x < 0) { x = -x; sgn = -1; }
+  if (x >= 1 || x <= 0) { *imp = x >= 1 ? si[1] : si[0]; *impP = 0; return; }
+  double y, yP, p = si[4], mid = si[3];
+  if (p == 1) { y = x; yP = 1; }
+  else if (x <= mid) {
+    double a = 1 / pow(mid, p - 1);
+    y = a * pow(x, p); yP = p * a * pow(x, p - 1);
+  } else {
+    double b = 1 / pow(1 - mid, p - 1);
+    y = 1 - b * pow(1 - x, p); yP = p * b * pow(1 - x, p - 1);
+  }
+  *imp = si[0] + y * (si[1] - si[0]);
+  *impP = yP * sgn * (si[1] - si[0]) / si[2];
+}
+
+static void o_make_constraint(const OModel* m, OData* d) {
+  int nv = m->nv;
+  d->nefc[0] = d->ne[0] = d->nf[0] = 0;
+  if (m->opt_disableflags & DSBL_CONSTRAINT) return;
+  /* friction loss */
+  if (!(m->opt_disableflags & DSBL_FRICTIONLOSS))
+    for (int i = 0; i < nv; i++)
+      if (m->dof_frictionloss[i] > 0) {
+        int r = add_row(m, d, CN_FRICTION_DOF, i, 0, 0, m->dof_frictionloss[i]);
+        if (r < 0) return;
+        d->efc_J[(size_t)r * nv + i] = 1;
+        d->nf[0]++;
+      }
+  /* joint limits (scalar joints) */
+  if (!(m->opt_disableflags & DSBL_LIMIT))
+    for (int j = 0; j < m->njnt; j++) {
+      if (!m->jnt_limited[j]) continue;
+      int jt = m->jnt_type[j];
+      if (jt != JNT_SLIDE && jt != JNT_HINGE) continue;
+      double q = d->qpos[m->jnt_qposadr[j]], margin = m->jnt_margin[j];
+      for (int side = -1; side <= 1; side += 2) {
+        double dist = side * (m->jnt_range[2 * j + (side + 1) / 2] - q);
+        if (dist < margin) {
+          int r = add_row(m, d, CN_LIMIT_JOINT, j, dist, margin, 0);
+          if (r < 0) return;
+          d->efc_J[(size_t)r * nv + m->jnt_dofadr[j]] = -side;
+        }
+      }
+    }
+  /* contacts */
+  double* jp1 = malloc(sizeof(double) * 12 * (nv + 1));
+  double *jr1 = jp1 + 3 * nv, *jp2 = jr1 + 3 * nv, *jr2 = jp2 + 3 * nv;
+  for (int ci = 0; ci < d->ncon[0]; ci++) {
+    OContact* c = d->contact + ci;
+    c->efc_address = -1;
+    d->contact_efc_address[ci] = -1;
+    if (c->exclude) continue;
+    int b1 = m->geom_bodyid[c->geom1], b2 = m->geom_bodyid[c->geom2];
+    o_jac(m, d, jp1, jr1, c->pos, b1);
+    o_jac(m, d, jp2, jr2, c->pos, b2);
+    /* contact-frame Jacobian rows: 0..2 translational, 3..5 rotational */
+    double Jc[6][64 * 2];
+    for (int k = 0; k < 3; k++)
+      for (int i = 0; i < nv; i++) {
+        double tp = 0, tr = 0;
+        for (int a = 0; a < 3; a++) {
+          tp += c->frame[3 * k + a] * (jp2[a * nv + i] - jp1[a * nv + i]);
+          tr += c->frame[3 * k + a] * (jr2[a * nv + i] - jr1[a * nv + i]);
+        }
+        Jc[k][i] = tp; Jc[3 + k][i] = tr;
+      }
+    int dim = c->dim;
+    if (dim == 1) {
+      int r = add_row(m, d, CN_CONTACT_FRICTIONLESS, ci, c->dist, c->includemargin, 0);
+      if (r < 0) break;
+      memcpy(d->efc_J + (size_t)r * nv, Jc[0], sizeof(double) * nv);
+      c->efc_address = r;
+    } else if (m->opt_cone == 0) {
+      for (int k = 1; k < dim; k++)
+        for (int sgn = 1; sgn >= -1; sgn -= 2) {
+          int r = add_row(m, d, CN_CONTACT_PYRAMIDAL, ci, c->dist, c->includemargin, 0);
+          if (r < 0) goto done;
+          if (c->efc_address < 0) c->efc_address = r;
+          double mu = c->friction[k - 1];
+          for (int i = 0; i < nv; i++)
+            d->efc_J[(size_t)r * nv + i] = Jc[0][i] + sgn * mu * Jc[k][i];
+        }
+    } else {
+      for (int k = 0; k < dim; k++) {
+        int r = add_row(m, d, CN_CONTACT_ELLIPTIC, ci, c->dist, c->includemargin, 0);
+        if (r < 0) goto done;
+        if (c->efc_address < 0) c->efc_address = r;
+        memcpy(d->efc_J + (size_t)r * nv, Jc[k], sizeof(double) * nv);
+      }
+    }
+    d->contact_efc_address[ci] = c->efc_address;
+  }
+done:
+  free(jp1);
+  /* per-row solver parameters: diagApprox, impedance, R, D, KBIP, aref */
+  int nefc = d->nefc[0];
+  double dt = m->opt_timestep;
+  for (int r = 0; r < nefc; r++) {
+    int type = d->efc_type[r], id = d->efc_id[r];
+    const double *solref, *solimp;
+    double dA;
+    if (type == CN_FRICTION_DOF) {
+      solref = m->dof_solref + 2 * id; solimp = m->dof_solimp + 5 * id;
+      dA = m->dof_invweight0[id];
+    } else if (type == CN_LIMIT_JOINT) {
+      solref = m->jnt_solref + 2 * id; solimp = m->jnt_solimp + 5 * id;
+      dA = m->dof_invweight0[m->jnt_dofadr[id]];
+    } else {
+      OContact* c = d->contact + id;
+      solref = c->solref; solimp = c->solimp;
+      int b1 = m->geom_bodyid[c->geom1], b2 = m->geom_bodyid[c->geom2];
+      double tran = m->body_invweight0[2 * b1] + m->body_invweight0[2 * b2];
+      double rot = m->body_invweight0[2 * b1 + 1] + m->body_invweight0[2 * b2 + 1];
+      int k = r - c->efc_address;
+      if (type == CN_CONTACT_FRICTIONLESS) dA = tran;
+      else if (type == CN_CONTACT_PYRAMIDAL) {
+        double fri = c->friction[k / 2];
+        dA = tran + fri * fri * (k < 4 ? tran : rot);
+      } else dA = k < 3 ? tran : rot;
+    }
+    d->efc_diagApprox[r] = dA;
+    double sr0 = solref[0], sr1 = solref[1];
+    if (!(m->opt_disableflags & DSBL_REFSAFE) && sr0 > 0 && sr0 < 2 * dt) sr0 = 2 * dt;
+    double imp, impP;
+    impedance(solimp, d->efc_pos[r], d->efc_margin[r], &imp, &impP);
+    if (imp < 0.0001) imp = 0.0001;
+    if (imp > 0.9999) imp = 0.9999;
+    double R = fmax(MINVAL, (1 - imp) * dA / imp);
+    double dmax = solimp[1] < 0.0001 ? 0.0001 : (solimp[1] > 0.9999 ? 0.9999 : solimp[1]);
+    double K, B;
+    if (type == CN_FRICTION_DOF) { K = 0; B = 0; }
+    else if (sr0 > 0) {
+      K = 1 / fmax(MINVAL, dmax * dmax * sr0 * sr0 * sr1 * sr1);
+      B = 2 / fmax(MINVAL, dmax * sr0);
+    } else { K = -sr0 / fmax(MINVAL, dmax * dmax); B = -sr1 / fmax(MINVAL, dmax); }
+    d->efc_R[r] = R;
+    d->efc_KBIP[4 * r] = K; d->efc_KBIP[4 * r + 1] = B;
+    d->efc_KBIP[4 * r + 2] = imp; d->efc_KBIP[4 * r + 3] = impP;
+  }
+  /* friction dimensions of frictional contacts */
+  for (int ci = 0; ci < d->ncon[0]; ci++) {
+    OContact* c = d->contact + ci;
+    int a = c->efc_address;
+    if (a < 0 || c->dim == 1) continue;
+    if (m->opt_cone == 0) {
+      c->mu = c->friction[0] / sqrt(m->opt_impratio);
+      double Rpy = 2 * c->mu * c->mu * d->efc_R[a];
+      for (int k = 0; k < 2 * (c->dim - 1); k++) d->efc_R[a + k] = Rpy;
+    } else {
+      d->efc_R[a + 1] = d->efc_R[a] / fmax(MINVAL, m->opt_impratio);
+      c->mu = c->friction[0] * sqrt(d->efc_R[a + 1] / d->efc_R[a]);
+      for (int k = 2; k < c->dim; k++)
+        d->efc_R[a + k] = d->efc_R[a + 1] * c->friction[0] * c->friction[0] /
+                          (c->friction[k - 1] * c->friction[k - 1]);
+    }
+  }
+  for (int r = 0; r < nefc; r++) {
+    d->efc_D[r] = 1 / d->efc_R[r];
+    double v = 0;
+    for (int i = 0; i < nv; i++) v += d->efc_J[(size_t)r * nv + i] * d->qvel[i];
+    d->efc_vel[r] = v;
+  }
+}
+
+/* reference acceleration: needs qvel, hence evaluated with the velocity stage */
+static void o_reference_constraint(const OModel* m, OData* d) {
+  int nv = m->nv;
+  for (int r = 0; r < d->nefc[0]; r++) {
+    double v = 0;
+    for (int i = 0; i < nv; i++) v += d->efc_J[(size_t)r * nv + i] * d->qvel[i];
+    d->efc_vel[r] = v;
+    d->efc_aref[r] = -d->efc_KBIP[4 * r + 1] * v -
+                     d->efc_KBIP[4 * r] * d->efc_KBIP[4 * r + 2] *
+                         (d->efc_pos[r] - d->efc_margin[r]);
+  }
+}
+
+/* ------------------------------------------------ Newton solver [A.9] */
+
+typedef struct { double cost, d0, d1; } LSPoint;
+
+/* constraint cost / force / state at acceleration-space residual jar */
+static double update_constraint(const OModel* m, OData* d, const double* jar) {
+  int nv = m->nv, nefc = d->nefc[0];
+  double cost = 0;
+  for (int r = 0; r < nefc; r++) {
+    double D = d->efc_D[r], x = jar[r];
+    int type = d->efc_type[r];
+    if (type == CN_EQUALITY) {
+      d->efc_force[r] = -D * x; d->efc_state[r] = ST_QUADRATIC; cost += 0.5 * D * x * x;
+    } else if (type == CN_FRICTION_DOF || type == CN_FRICTION_TENDON) {
+      double f = d->efc_frictionloss[r], R = d->efc_R[r];
+      if (x <= -R * f) { d->efc_force[r] = f; d->efc_state[r] = ST_LINEARNEG; cost += -f * (0.5 * R * f + x); }
+      else if (x >= R * f) { d->efc_force[r] = -f; d->efc_state[r] = ST_LINEARPOS; cost += -f * (0.5 * R * f - x); }
+      else { d->efc_force[r] = -D * x; d->efc_state[r] = ST_QUADRATIC; cost += 0.5 * D * x * x; }
+    } else {
+      if (x >= 0) { d->efc_force[r] = 0; d->efc_state[r] = ST_SATISFIED; }
+      else { d->efc_force[r] = -D * x; d->efc_state[r] = ST_QUADRATIC; cost += 0.5 * D * x * x; }
+    }
+  }
+  for (int i = 0; i < nv; i++) {
+    double s = 0;
+    for (int r = 0; r < nefc; r++) s += d->efc_J[(size_t)r * nv + i] * d->efc_force[r];
+    d->qfrc_constraint[i] = s;
+  }
+  return cost;
+}
+
+static LSPoint ls_eval(const OModel* m, const OData* d, double alpha,
+                       const double* quad_gauss) {
+  int nefc = d->nefc[0];
+  double c0 = quad_gauss[0], c1 = quad_gauss[1], c2 = quad_gauss[2];
+  for (int r = 0; r < nefc; r++) {
+    double D = d->efc_D[r], j0 = d->s_jar[r], jv = d->s_jv[r];
+    double x = j0 + alpha * jv;
+    int type = d->efc_type[r];
+    double q0 = 0.5 * D * j0 * j0, q1 = D * j0 * jv, q2 = 0.5 * D * jv * jv;
+    if (type == CN_EQUALITY) { c0 += q0; c1 += q1; c2 += q2; }
+    else if (type == CN_FRICTION_DOF || type == CN_FRICTION_TENDON) {
+      double f = d->efc_frictionloss[r], R = d->efc_R[r];
+      if (x <= -R * f) { c0 += -f * (0.5 * R * f + j0); c1 += -f * jv; }
+      else if (x >= R * f) { c0 += -f * (0.5 * R * f - j0); c1 += f * jv; }
+      else { c0 += q0; c1 += q1; c2 += q2; }
+    } else if (x < 0) { c0 += q0; c1 += q1; c2 += q2; }
+  }
+  LSPoint p;
+  p.cost = alpha * alpha * c2 + alpha * c1 + c0;
+  p.d0 = 2 * alpha * c2 + c1;
+  p.d1 = 2 * c2;
+  return p;
+}
+
+/* exact 1-D minimisation along `search`: safeguarded Newton on the (monotone,
+ * piecewise-linear) derivative; returns the step length */
+static double linesearch(const OModel* m, OData* d, double scale) {
+  int nv = m->nv;
+  double snorm = 0;
+  for (int i = 0; i < nv; i++) snorm += d->s_search[i] * d->s_search[i];
+  snorm = sqrt(snorm);
+  if (snorm < MINVAL) return 0;
+  double gtol = m->opt_tolerance * m->opt_ls_tolerance * snorm / scale;
+  double qg[3] = {0, 0, 0};
+  for (int i = 0; i < nv; i++) {
+    qg[0] += 0.5 * (d->s_Ma[i] - d->qfrc_smooth[i]) * (d->qacc[i] - d->qacc_smooth[i]);
+    qg[1] += d->s_search[i] * (d->s_Ma[i] - d->qfrc_smooth[i]);
+    qg[2] += 0.5 * d->s_search[i] * d->s_Mv[i];
+  }
+  LSPoint p = ls_eval(m, d, 0, qg);
+  if (p.d1 < MINVAL) return 0;
+  double lo = 0, hi = 0;
+  int have_hi = 0;
+  double a = -p.d0 / p.d1;
+  for (int it = 0; it < m->opt_ls_iterations; it++) {
+    p = ls_eval(m, d, a, qg);
+    if (fabs(p.d0) < gtol) break;
+    if (p.d0 < 0) lo = a; else { hi = a; have_hi = 1; }
+    double an = a - p.d0 / p.d1;
+    if (have_hi && !(an > lo && an < hi)) an = 0.5 * (lo + hi);
+    a = an;
+  }
+  return a;
+}
+
+/* dense Cholesky H = L L^T in place (lower), returns 0 on failure */
+static int chol_factor(double* H, int n) {
+  for (int j = 0; j < n; j++) {
+    double s = H[j * n + j];
+    for (int k = 0; k < j; k++) s -= H[j * n + k] * H[j * n + k];
+    if (s < MINVAL) return 0;
+    s = sqrt(s);
+    H[j * n + j] = s;
+    for (int i = j + 1; i < n; i++) {
+      double t = H[i * n + j];
+      for (int k = 0; k < j; k++) t -= H[i * n + k] * H[j * n + k];
+      H[i * n + j] = t / s;
+    }
+  }
+  return 1;
+}
+static void chol_solve(const double* L, int n, double* x) {
+  for (int i = 0; i < n; i++) {
+    double t = x[i];
+    for (int k = 0; k < i; k++) t -= L[i * n + k] * x[k];
+    x[i] = t / L[i * n + i];
+  }
+  for (int i = n - 1; i >= 0; i--) {
+    double t = x[i];
+    for (int k = i + 1; k < n; k++) t -= L[k * n + i] * x[k];
+    x[i] = t / L[i * n + i];
+  }
+}
+
+static void dense_m(const OModel* m, const double* qM, double* Md) {
+  int nv = m->nv;
+  memset(Md, 0, sizeof(double) * nv * nv);
+  for (int i = 0; i < nv; i++) {
+    int a = m->dof_Madr[i];
+    for (int j = i; j >= 0; j = m->dof_parentid[j], a++) {
+      Md[i * nv + j] = qM[a]; Md[j * nv + i] = qM[a];
+    }
+  }
+}
+
+static void newton_gradient(const OModel* m, OData* d) {
+  int nv = m->nv, nefc = d->nefc[0];
+  for (int i = 0; i < nv; i++)
+    d->s_grad[i] = d->s_Ma[i] - d->qfrc_smooth[i] - d->qfrc_constraint[i];
+  memcpy(d->s_H, d->s_Mdense, sizeof(double) * nv * nv);
+  for (int r = 0; r < nefc; r++) {
+    if (d->efc_state[r] != ST_QUADRATIC) continue;
+    const double* J = d->efc_J + (size_t)r * nv;
+    double D = d->efc_D[r];
+    for (int i = 0; i < nv; i++) {
+      if (J[i] == 0) continue;
+      for (int j = 0; j <= i; j++) d->s_H[i * nv + j] += D * J[i] * J[j];
+    }
+  }
+  if (!chol_factor(d->s_H, nv)) {
+    /* not expected (M is PD); fall back to the unconstrained metric */
+    memcpy(d->s_H, d->s_Mdense, sizeof(double) * nv * nv);
+    chol_factor(d->s_H, nv);
+  }
+  memcpy(d->s_Mgrad, d->s_grad, sizeof(double) * nv);
+  chol_solve(d->s_H, nv, d->s_Mgrad);
+}
+
+static double total_cost(const OModel* m, OData* d, double ccost) {
+  double g = 0;
+  for (int i = 0; i < m->nv; i++)
+    g += 0.5 * (d->s_Ma[i] - d->qfrc_smooth[i]) * (d->qacc[i] - d->qacc_smooth[i]);
+  return ccost + g;
+}
+
+static void jar_from_qacc(const OModel* m, OData* d) {
+  int nv = m->nv;
+  for (int r = 0; r < d->nefc[0]; r++) {
+    double s = 0;
+    for (int i = 0; i < nv; i++) s += d->efc_J[(size_t)r * nv + i] * d->qacc[i];
+    d->s_jar[r] = s - d->efc_aref[r];
+  }
+}
+
+static void o_fwd_constraint(const OModel* m, OData* d) {
+  int nv = m->nv, nefc = d->nefc[0];
+  d->solver_iter[0] = 0;
+  if (nefc == 0) {
+    memcpy(d->qacc, d->qacc_smooth, sizeof(double) * nv);
+    memcpy(d->qacc_warmstart, d->qacc_smooth, sizeof(double) * nv);
+    memset(d->qfrc_constraint, 0, sizeof(double) * nv);
+    return;
+  }
+  dense_m(m, d->qM, d->s_Mdense);
+  /* warm start: the cheaper of qacc_warmstart and qacc_smooth */
+  double cost;
+  if (!(m->opt_disableflags & DSBL_WARMSTART)) {
+    memcpy(d->qacc, d->qacc_warmstart, sizeof(double) * nv);
+    mul_m(m, d->qM, d->s_Ma, d->qacc);
+    jar_from_qacc(m, d);
+    double cw = total_cost(m, d, update_constraint(m, d, d->s_jar));
+    memcpy(d->qacc, d->qacc_smooth, sizeof(double) * nv);
+    memcpy(d->s_Ma, d->qfrc_smooth, sizeof(double) * nv);
+    jar_from_qacc(m, d);
+    double cs = update_constraint(m, d, d->s_jar);
+    if (cw < cs) memcpy(d->qacc, d->qacc_warmstart, sizeof(double) * nv);
+  } else {
+    memcpy(d->qacc, d->qacc_smooth, sizeof(double) * nv);
+  }
+  mul_m(m, d->qM, d->s_Ma, d->qacc);
+  jar_from_qacc(m, d);
+  cost = total_cost(m, d, update_constraint(m, d, d->s_jar));
+  newton_gradient(m, d);
+  for (int i = 0; i < nv; i++) d->s_search[i] = -d->s_Mgrad[i];
+  double scale = 1.0 / (m->stat_meaninertia * (nv > 1 ? nv : 1));
+  int iter = 0;
+  while (iter < m->opt_iterations) {
+    mul_m(m, d->qM, d->s_Mv, d->s_search);
+    for (int r = 0; r < nefc; r++) {
+      double s = 0;
+      for (int i = 0; i < nv; i++) s += d->efc_J[(size_t)r * nv + i] * d->s_search[i];
+      d->s_jv[r] = s;
+    }
+    double alpha = linesearch(m, d, scale);
+    if (alpha == 0) break;
+    for (int i = 0; i < nv; i++) {
+      d->qacc[i] += alpha * d->s_search[i];
+      d->s_Ma[i] += alpha * d->s_Mv[i];
+    }
+    for (int r = 0; r < nefc; r++) d->s_jar[r] += alpha * d->s_jv[r];
+    double old = cost;
+    cost = total_cost(m, d, update_constraint(m, d, d->s_jar));
+    newton_gradient(m, d);
+    double gn = 0;
+    for (int i = 0; i < nv; i++) gn += d->s_grad[i] * d->s_grad[i];
+    double improvement = scale * (old - cost), gradient = scale * sqrt(gn);
+    d->solver_improvement[0] = improvement; d->solver_gradient[0] = gradient;
+    iter++;
+    if (improvement < m->opt_tolerance || gradient < m->opt_tolerance) break;
+    for (int i = 0; i < nv; i++) d->s_search[i] = -d->s_Mgrad[i];
+  }
+  d->solver_iter[0] = iter;
+  memcpy(d->qacc_warmstart, d->qacc, sizeof(double) * nv);
+}
+
+/* ------------------------------------------------------- sensors [A.11] */
+
+static void o_subtree_vel(const OModel* m, OData* d) {
+  int nb = m->nbody;
+  for (int b = 0; b < nb; b++) {
+    const double* cv = d->cvel + 6 * b;
+    const double* com = d->subtree_com + 3 * m->body_rootid[b];
+    double dif[3], t[3];
+    for (int c = 0; c < 3; c++) dif[c] = d->xipos[3 * b + c] - com[c];
+    cross3(t, cv, dif);
+    for (int c = 0; c < 3; c++)
+      d->subtree_linvel[3 * b + c] = m->body_mass[b] * (cv[3 + c] + t[c]);
+  }
+  for (int b = nb - 1; b > 0; b--) {
+    int p = m->body_parentid[b];
+    for (int c = 0; c < 3; c++) d->subtree_linvel[3 * p + c] += d->subtree_linvel[3 * b + c];
+  }
+  for (int b = 0; b < nb; b++) {
+    double sm = m->body_subtreemass[b] > MINVAL ? m->body_subtreemass[b] : MINVAL;
+    for (int c = 0; c < 3; c++) d->subtree_linvel[3 * b + c] /= sm;
+  }
+}
+
+static void contact_force(const OModel* m, const OData* d, int ci, double* f6) {
+  const OContact* c = d->contact + ci;
+  memset(f6, 0, 48);
+  int a = c->efc_address;
+  if (a < 0) return;
+  if (c->dim == 1) { f6[0] = d->efc_force[a]; return; }
+  if (m->opt_cone == 0) {
+    for (int k = 0; k < 2 * (c->dim - 1); k++) f6[0] += d->efc_force[a + k];
+    for (int k = 1; k < c->dim; k++)
+      f6[k] = c->friction[k - 1] * (d->efc_force[a + 2 * k - 2] - d->efc_force[a + 2 * k - 1]);
+  } else {
+    for (int k = 0; k < c->dim; k++) f6[k] = d->efc_force[a + k];
+  }
+}
+
+static void o_rne_post_constraint(const OModel* m, OData* d) {
+  int nb = m->nbody;
+  memset(d->cfrc_ext, 0, sizeof(double) * 6 * nb);
+  for (int ci = 0; ci < d->ncon[0]; ci++) {
+    const OContact* c = d->contact + ci;
+    if (c->efc_address < 0) continue;
+    double f6[6], fw[3], tw[3];
+    contact_force(m, d, ci, f6);
+    matT_vec3(fw, c->frame, f6);
+    matT_vec3(tw, c->frame, f6 + 3);
+    for (int side = 0; side < 2; side++) {
+      int b = m->geom_bodyid[side ? c->geom2 : c->geom1];
+      if (b == 0) continue;
+      double sgn = side ? 1 : -1;
+      const double* com = d->subtree_com + 3 * m->body_rootid[b];
+      double dif[3] = {c->pos[0] - com[0], c->pos[1] - com[1], c->pos[2] - com[2]}, t[3];
+      cross3(t, dif, fw);
+      for (int k = 0; k < 3; k++) {
+        d->cfrc_ext[6 * b + k] += sgn * (tw[k] + t[k]);
+        d->cfrc_ext[6 * b + 3 + k] += sgn * fw[k];
+      }
+    }
+  }
+  memset(d->cacc, 0, 48);
+  if (!(m->opt_disableflags & DSBL_GRAVITY))
+    for (int c = 0; c < 3; c++) d->cacc[3 + c] = -m->opt_gravity[c];
+  memset(d->cfrc_int, 0, 48);
+  for (int b = 1; b < nb; b++) {
+    double* a = d->cacc + 6 * b;
+    memcpy(a, d->cacc + 6 * m->body_parentid[b], 48);
+    int da = m->body_dofadr[b];
+    for (int k = 0; k < m->body_dofnum[b]; k++)
+      for (int c = 0; c < 6; c++)
+        a[c] += d->cdof_dot[6 * (da + k) + c] * d->qvel[da + k] +
+                d->cdof[6 * (da + k) + c] * d->qacc[da + k];
+    double Ia[6], Iv[6], vxIv[6];
+    inert_mul(Ia, d->cinert + 10 * b, a);
+    inert_mul(Iv, d->cinert + 10 * b, d->cvel + 6 * b);
+    cross_force(vxIv, d->cvel + 6 * b, Iv);
+    for (int c = 0; c < 6; c++) d->cfrc_int[6 * b + c] = Ia[c] + vxIv[c] - d->cfrc_ext[6 * b + c];
+  }
+  for (int b = nb - 1; b > 0; b--) {
+    int p = m->body_parentid[b];
+    if (p > 0)
+      for (int c = 0; c < 6; c++) d->cfrc_int[6 * p + c] += d->cfrc_int[6 * b + c];
+  }
+}
+
+static int inside_site(const OModel* m, const OData* d, int s, const double* p) {
+  double dif[3] = {p[0] - d->site_xpos[3 * s], p[1] - d->site_xpos[3 * s + 1],
+                   p[2] - d->site_xpos[3 * s + 2]}, l[3];
+  matT_vec3(l, d->site_xmat + 9 * s, dif);
+  const double* sz = m->site_size + 3 * s;
+  switch (m->site_type[s]) {
+    case GEOM_SPHERE: return dot3(l, l) <= sz[0] * sz[0];
+    case GEOM_CAPSULE: {
+      double z = l[2] < -sz[1] ? -sz[1] : (l[2] > sz[1] ? sz[1] : l[2]);
+      double dz = l[2] - z;
+      return l[0] * l[0] + l[1] * l[1] + dz * dz <= sz[0] * sz[0];
+    }
+    case GEOM_ELLIPSOID:
+      return l[0] * l[0] / (sz[0] * sz[0]) + l[1] * l[1] / (sz[1] * sz[1]) +
+             l[2] * l[2] / (sz[2] * sz[2]) <= 1;
+    case GEOM_CYLINDER:
+      return fabs(l[2]) <= sz[1] && l[0] * l[0] + l[1] * l[1] <= sz[0] * sz[0];
+    case GEOM_BOX:
+      return fabs(l[0]) <= sz[0] && fabs(l[1]) <= sz[1] && fabs(l[2]) <= sz[2];
+  }
+  return 0;
+}
+
+static void obj_frame(const OModel* m, const OData* d, int objtype, int id,
+                      const double** pos, const double** mat, int* body) {
+  if (objtype == OBJ_SITE) { *pos = d->site_xpos + 3 * id; *mat = d->site_xmat + 9 * id; *body = m->site_bodyid[id]; }
+  else if (objtype == OBJ_GEOM) { *pos = d->geom_xpos + 3 * id; *mat = d->geom_xmat + 9 * id; *body = m->geom_bodyid[id]; }
+  else if (objtype == OBJ_XBODY) { *pos = d->xpos + 3 * id; *mat = d->xmat + 9 * id; *body = id; }
+  else { *pos = d->xipos + 3 * id; *mat = d->ximat + 9 * id; *body = id; }
+}
+
+static void o_sensors(const OModel* m, OData* d, int stage) {
+  int need_subtree = 0, need_rne = 0;
+  for (int s = 0; s < m->nsensor; s++) {
+    if (m->sensor_needstage[s] != stage) continue;
+    int t = m->sensor_type[s];
+    if (t == SENS_SUBTREELINVEL) need_subtree = 1;
+    if (t == SENS_ACCELEROMETER || t == SENS_FORCE || t == SENS_TORQUE) need_rne = 1;
+  }
+  if (need_subtree) o_subtree_vel(m, d);
+  if (need_rne) o_rne_post_constraint(m, d);
+  for (int s = 0; s < m->nsensor; s++) {
+    if (m->sensor_needstage[s] != stage) continue;
+    int t = m->sensor_type[s], id = m->sensor_objid[s];
+    double* out = d->sensordata + m->sensor_adr[s];
+    const double *pos, *mat;
+    int body;
+    switch (t) {
+      case SENS_JOINTPOS: out[0] = d->qpos[m->jnt_qposadr[id]]; break;
+      case SENS_JOINTVEL: out[0] = d->qvel[m->jnt_dofadr[id]]; break;
+      case SENS_ACTUATORFRC: out[0] = d->actuator_force[id]; break;
+      case SENS_SUBTREECOM: memcpy(out, d->subtree_com + 3 * id, 24); break;
+      case SENS_SUBTREELINVEL: memcpy(out, d->subtree_linvel + 3 * id, 24); break;
+      case SENS_FRAMEPOS:
+        obj_frame(m, d, m->sensor_objtype[s], id, &pos, &mat, &body);
+        memcpy(out, pos, 24);
+        break;
+      case SENS_VELOCIMETER: case SENS_GYRO: case SENS_ACCELEROMETER: {
+        obj_frame(m, d, OBJ_SITE, id, &pos, &mat, &body);
+        const double* com = d->subtree_com + 3 * m->body_rootid[body];
+        const double* cv = d->cvel + 6 * body;
+        double dif[3] = {pos[0] - com[0], pos[1] - com[1], pos[2] - com[2]};
+        double t3[3], vlin[3], wl[3], vl[3];
+        cross3(t3, cv, dif);
+        for (int c = 0; c < 3; c++) vlin[c] = cv[3 + c] + t3[c];
+        matT_vec3(wl, mat, cv);
+        matT_vec3(vl, mat, vlin);
+        if (t == SENS_GYRO) memcpy(out, wl, 24);
+        else if (t == SENS_VELOCIMETER) memcpy(out, vl, 24);
+        else {
+          const double* ca = d->cacc + 6 * body;
+          double alin[3], al[3], cor[3];
+          cross3(t3, ca, dif);
+          for (int c = 0; c < 3; c++) alin[c] = ca[3 + c] + t3[c];
+          matT_vec3(al, mat, alin);
+          cross3(cor, wl, vl);
+          for (int c = 0; c < 3; c++) out[c] = al[c] + cor[c];
+        }
+        break;
+      }
+      case SENS_FORCE: case SENS_TORQUE: {
+        obj_frame(m, d, OBJ_SITE, id, &pos, &mat, &body);
+        const double* com = d->subtree_com + 3 * m->body_rootid[body];
+        const double* cf = d->cfrc_int + 6 * body;
+        if (t == SENS_FORCE) matT_vec3(out, mat, cf + 3);
+        else {
+          double dif[3] = {pos[0] - com[0], pos[1] - com[1], pos[2] - com[2]}, t3[3], tq[3];
+          cross3(t3, dif, cf + 3);
+          for (int c = 0; c < 3; c++) tq[c] = cf[c] - t3[c];
+          matT_vec3(out, mat, tq);
+        }
+        break;
+      }
+      case SENS_TOUCH: {
+        int sb = m->site_bodyid[id];
+        out[0] = 0;
+        for (int ci = 0; ci < d->ncon[0]; ci++) {
+          const OContact* c = d->contact + ci;
+          if (c->efc_address < 0) continue;
+          if (m->geom_bodyid[c->geom1] != sb && m->geom_bodyid[c->geom2] != sb) continue;
+          double f6[6];
+          contact_force(m, d, ci, f6);
+          if (f6[0] <= 0) continue;
+          if (inside_site(m, d, id, c->pos)) out[0] += f6[0];
+        }
+        break;
+      }
+    }
+    double cut = m->sensor_cutoff[s];
+    if (cut > 0)
+      for (int c = 0; c < m->sensor_dim[s]; c++) {
+        if (t == SENS_TOUCH) { if (out[c] > cut) out[c] = cut; }
+        else { if (out[c] > cut) out[c] = cut; else if (out[c] < -cut) out[c] = -cut; }
+      }
+  }
+}
+
+static void o_energy_pos(const OModel* m, OData* d) {
+  if (!(m->opt_enableflags & ENBL_ENERGY)) { d->energy[0] = d->energy[1] = 0; return; }
+  double e = 0;
+  if (!(m->opt_disableflags & DSBL_GRAVITY))
+    for (int b = 1; b < m->nbody; b++)
+      e -= m->body_mass[b] * dot3(m->opt_gravity, d->xipos + 3 * b);
+  if (!(m->opt_disableflags & DSBL_PASSIVE))
+    for (int j = 0; j < m->njnt; j++) {
+      int jt = m->jnt_type[j], qa = m->jnt_qposadr[j];
+      if (jt == JNT_SLIDE || jt == JNT_HINGE) {
+        double dq = d->qpos[qa] - m->qpos_spring[qa];
+        e += 0.5 * m->jnt_stiffness[j] * dq * dq;
+      }
+    }
+  d->energy[0] = e;
+}
+
+static void o_energy_vel(const OModel* m, OData* d) {
+  if (!(m->opt_enableflags & ENBL_ENERGY)) return;
+  double* t = (double*)calloc(m->nv > 0 ? m->nv : 1, 8);
+  mul_m(m, d->qM, t, d->qvel);
+  double e = 0;
+  for (int i = 0; i < m->nv; i++) e += 0.5 * t[i] * d->qvel[i];
+  d->energy[1] = e;
+  free(t);
+}
+
+/* ---------------------------------------------------- pipeline (§3.1) */
+
+static int is_bad(double x) { return isnan(x) || x > MAXVAL || x < -MAXVAL; }
+
+static int check_array(const OModel* m, OData* d, const double* x, int n, int w) {
+  for (int i = 0; i < n; i++)
+    if (is_bad(x[i])) {
+      o_reset(m, d);
+      d->warning[w] = 1;
+      return 1;
+    }
+  return 0;
+}
+
+static void fwd_position(const OModel* m, OData* d) {
+  o_kinematics(m, d);
+  o_com_pos(m, d);
+  o_transmission(m, d);
+  o_crb(m, d);
+  o_factor_m(m, d);
+  o_collision(m, d);
+  o_make_constraint(m, d);
+}
+
+static void fwd_velocity(const OModel* m, OData* d) {
+  int nv = m->nv;
+  for (int i = 0; i < m->nu; i++) {
+    double v = 0;
+    for (int k = 0; k < nv; k++) v += d->actuator_moment[i * nv + k] * d->qvel[k];
+    d->actuator_velocity[i] = v;
+  }
+  o_com_vel(m, d);
+  o_passive(m, d);
+  o_reference_constraint(m, d);
+  o_rne(m, d, 0, d->qfrc_bias);
+}
+
+static void forward_skip(const OModel* m, OData* d, int skipsensor) {
+  fwd_position(m, d);
+  if (!skipsensor) o_sensors(m, d, STAGE_POS);
+  o_energy_pos(m, d);
+  fwd_velocity(m, d);
+  if (!skipsensor) o_sensors(m, d, STAGE_VEL);
+  o_energy_vel(m, d);
+  o_fwd_actuation(m, d);
+  o_fwd_acceleration(m, d);
+  o_fwd_constraint(m, d);
+  if (!skipsensor) o_sensors(m, d, STAGE_ACC);
+}
+
+void o_forward(const OModel* m, OData* d) { forward_skip(m, d, 0); }
+
+static void integrate_pos(const OModel* m, double* qpos, const double* qvel, double dt) {
+  for (int j = 0; j < m->njnt; j++) {
+    int qa = m->jnt_qposadr[j], da = m->jnt_dofadr[j];
+    switch (m->jnt_type[j]) {
+      case JNT_FREE:
+        for (int c = 0; c < 3; c++) qpos[qa + c] += dt * qvel[da + c];
+        quat_integrate(qpos + qa + 3, qvel + da + 3, dt);
+        break;
+      case JNT_BALL: quat_integrate(qpos + qa, qvel + da, dt); break;
+      default: qpos[qa] += dt * qvel[da];
+    }
+  }
+}
+
+/* qvel += dt*qacc ; qpos integrates with qvel_for_pos (NULL = updated qvel) */
+static void advance(const OModel* m, OData* d, const double* act_dot,
+                    const double* qacc, const double* qvel_for_pos) {
+  double dt = m->opt_timestep;
+  for (int i = 0; i < m->na; i++) d->act[i] += dt * act_dot[i];
+  for (int i = 0; i < m->nv; i++) d->qvel[i] += dt * qacc[i];
+  integrate_pos(m, d->qpos, qvel_for_pos ? qvel_for_pos : d->qvel, dt);
+  d->time[0] += dt;
+}
+
+static void o_euler(const OModel* m, OData* d) {
+  int nv = m->nv, damped = 0;
+  for (int i = 0; i < nv; i++) if (m->dof_damping[i] > 0) { damped = 1; break; }
+  double* qacc = (double*)malloc(sizeof(double) * (nv + 1));
+  if (!damped) memcpy(qacc, d->qacc, sizeof(double) * nv);
+  else {
+    /* implicit joint damping: (M + dt*diag(damping)) a = f_smooth + f_constraint */
+    double* MM = (double*)malloc(sizeof(double) * (m->nM + 1));
+    double* di = (double*)malloc(sizeof(double) * (nv + 1));
+    memcpy(MM, d->qM, sizeof(double) * m->nM);
+    for (int i = 0; i < nv; i++) MM[m->dof_Madr[i]] += m->opt_timestep * m->dof_damping[i];
+    factor_sparse(m, MM, di);
+    for (int i = 0; i < nv; i++) qacc[i] = d->qfrc_smooth[i] + d->qfrc_constraint[i];
+    solve_sparse(m, MM, di, qacc);
+    free(MM); free(di);
+  }
+  advance(m, d, d->act_dot, qacc, NULL);
+  free(qacc);
+}
+
+static void o_rk4(const OModel* m, OData* d) {
+  static const double A[3][3] = {{0.5, 0, 0}, {0, 0.5, 0}, {0, 0, 1}};
+  static const double B[4] = {1.0 / 6, 1.0 / 3, 1.0 / 3, 1.0 / 6};
+  static const double C[3] = {0.5, 0.5, 1.0};
+  int nq = m->nq, nv = m->nv, na = m->na;
+  double h = m->opt_timestep, t0 = d->time[0];
+  double* buf = (double*)calloc((size_t)(nq + nv + na + 4 * (2 * nv + na) + 2 * nv + na + 8), 8);
+  double *q0 = buf, *v0 = q0 + nq, *a0 = v0 + nv;
+  double* F[4];
+  F[0] = a0 + na;
+  for (int i = 1; i < 4; i++) F[i] = F[i - 1] + 2 * nv + na;
+  double* dX = F[3] + 2 * nv + na;
+  memcpy(q0, d->qpos, 8 * nq); memcpy(v0, d->qvel, 8 * nv); memcpy(a0, d->act, 8 * na);
+  memcpy(F[0], d->qvel, 8 * nv); memcpy(F[0] + nv, d->qacc, 8 * nv);
+  memcpy(F[0] + 2 * nv, d->act_dot, 8 * na);
+  for (int i = 1; i < 4; i++) {
+    for (int k = 0; k < 2 * nv + na; k++) {
+      dX[k] = 0;
+      for (int j = 0; j < i; j++) dX[k] += A[i - 1][j] * F[j][k];
+    }
+    memcpy(d->qpos, q0, 8 * nq);
+    integrate_pos(m, d->qpos, dX, h);
+    for (int k = 0; k < nv; k++) d->qvel[k] = v0[k] + h * dX[nv + k];
+    for (int k = 0; k < na; k++) d->act[k] = a0[k] + h * dX[2 * nv + k];
+    d->time[0] = t0 + h * C[i - 1];
+    forward_skip(m, d, 1);
+    memcpy(F[i], d->qvel, 8 * nv); memcpy(F[i] + nv, d->qacc, 8 * nv);
+    memcpy(F[i] + 2 * nv, d->act_dot, 8 * na);
+  }
+  for (int k = 0; k < 2 * nv + na; k++) {
+    dX[k] = 0;
+    for (int j = 0; j < 4; j++) dX[k] += B[j] * F[j][k];
+  }
+  memcpy(d->qpos, q0, 8 * nq); memcpy(d->qvel, v0, 8 * nv); memcpy(d->act, a0, 8 * na);
+  d->time[0] = t0;
+  advance(m, d, dX + 2 * nv, dX + nv, dX);
+  free(buf);
+}
+
+static void check_acc(const OModel* m, OData* d) {
+  if (check_array(m, d, d->qacc, m->nv, W_BADQACC)) o_forward(m, d);
+}
+
+void o_step(const OModel* m, OData* d) {
+  check_array(m, d, d->qpos, m->nq, W_BADQPOS);
+  check_array(m, d, d->qvel, m->nv, W_BADQVEL);
+  o_forward(m, d);
+  check_acc(m, d);
+  if (m->opt_integrator == 1) o_rk4(m, d); else o_euler(m, d);
+}
+
+void o_step1(const OModel* m, OData* d) {
+  check_array(m, d, d->qpos, m->nq, W_BADQPOS);
+  check_array(m, d, d->qvel, m->nv, W_BADQVEL);
+  fwd_position(m, d);
+  o_sensors(m, d, STAGE_POS);
+  o_energy_pos(m, d);
+  fwd_velocity(m, d);
+  o_sensors(m, d, STAGE_VEL);
+  o_energy_vel(m, d);
+}
+
+void o_step2(const OModel* m, OData* d) {
+  o_fwd_actuation(m, d);
+  o_fwd_acceleration(m, d);
+  o_fwd_constraint(m, d);
+  o_sensors(m, d, STAGE_ACC);
+  check_acc(m, d);
+  o_euler(m, d);
+}
+
+/* engine.py:149-166 */
+void o_physics_step(const OModel* m, OData* d) {
+  if (m->opt_integrator == 0) o_step2(m, d); else o_step(m, d);
+  o_step1(m, d);
+}
+
+/* -------------------------------------------------- CPU-baseline driver */
+
+typedef struct {
+  const OModel* m; int lo, hi, nsteps, nsub, ctrl_per_step, nenv;
+  double *qpos, *qvel, *act, *warm, *time; const double* ctrl;
+} BatchJob;
+
+static void* batch_worker(void* arg) {
+  BatchJob* j = (BatchJob*)arg;
+  const OModel* m = j->m;
+  OData* d = od_create(m);
+  for (int e = j->lo; e < j->hi; e++) {
+    o_reset(m, d);
+    memcpy(d->qpos, j->qpos + (size_t)e * m->nq, 8 * m->nq);
+    memcpy(d->qvel, j->qvel + (size_t)e * m->nv, 8 * m->nv);
+    if (m->na) memcpy(d->act, j->act + (size_t)e * m->na, 8 * m->na);
+    memcpy(d->qacc_warmstart, j->warm + (size_t)e * m->nv, 8 * m->nv);
+    d->time[0] = j->time[e];
+    o_step1(m, d);   /* derived quantities in sync with the loaded state */
+    for (int s = 0; s < j->nsteps; s++) {
+      const double* c = j->ctrl + ((size_t)(j->ctrl_per_step ? s : 0) * j->nenv + e) * m->nu;
+      memcpy(d->ctrl, c, 8 * m->nu);
+      for (int k = 0; k < j->nsub; k++) o_physics_step(m, d);
+    }
+    memcpy(j->qpos + (size_t)e * m->nq, d->qpos, 8 * m->nq);
+    memcpy(j->qvel + (size_t)e * m->nv, d->qvel, 8 * m->nv);
+    if (m->na) memcpy(j->act + (size_t)e * m->na, d->act, 8 * m->na);
+    memcpy(j->warm + (size_t)e * m->nv, d->qacc_warmstart, 8 * m->nv);
+    j->time[e] = d->time[0];
+  }
+  od_free(d);
+  return NULL;
+}
+
+void o_run_batch(const OModel* m, int nenv, int nsteps, int nsub, double* qpos,
+                 double* qvel, double* act, double* warm, double* time,
+                 const double* ctrl, int ctrl_per_step, int nthreads) {
+  if (nthreads < 1) nthreads = 1;
+  if (nthreads > nenv) nthreads = nenv;
+  pthread_t* th = (pthread_t*)malloc(sizeof(pthread_t) * nthreads);
+  BatchJob* jobs = (BatchJob*)malloc(sizeof(BatchJob) * nthreads);
+  for (int t = 0; t < nthreads; t++) {
+    BatchJob j = {m, (int)((long)nenv * t / nthreads), (int)((long)nenv * (t + 1) / nthreads),
+                  nsteps, nsub, ctrl_per_step, nenv, qpos, qvel, act, warm, time, ctrl};
+    jobs[t] = j;
+    pthread_create(&th[t], NULL, batch_worker, &jobs[t]);
+  }
+  for (int t = 0; t < nthreads; t++) pthread_join(th[t], NULL);
+  free(th); free(jobs);
+}

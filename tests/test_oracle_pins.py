@@ -1,0 +1,284 @@
+"""Pins the CPU oracle against every known answer the reference holds for the
+physics path.  Citations are under /root/reference/dm_control/."""
+
+import numpy as np
+import pytest
+
+from dm_control_b200 import mjcf_compiler as C
+from oracle.oracle_py import Oracle
+
+# mujoco/README.md:9-49 — the only digit-level value the reference publishes.
+README_XML = """
+<mujoco>
+  <worldbody>
+    <light name="top" pos="0 0 1.5"/>
+    <geom name="floor" type="plane" size="1 1 .1"/>
+    <body name="box" pos="0 0 .3">
+      <joint name="up_down" type="slide" axis="0 0 1"/>
+      <geom name="box" type="box" size=".2 .2 .2" rgba="1 0 0 1"/>
+      <geom name="sphere" pos=".2 .2 .2" size=".1" rgba="0 1 0 1"/>
+    </body>
+  </worldbody>
+</mujoco>"""
+
+
+def test_readme_golden_geom_positions():
+  m = C.compile_xml(README_XML)
+  o = Oracle(m)
+  o.reset()
+  o.qpos[m.name2id("up_down", "joint")] = 0.5
+  o.forward()                                    # reset_context exit
+  gx = o.geom_xpos.reshape(-1, 3)
+  np.testing.assert_allclose(gx, [[0, 0, 0], [0, 0, .8], [.2, .2, 1.]], atol=1e-15)
+  while o.time[0] < 1.0:
+    o.step()
+  z = o.geom_xpos.reshape(-1, 3)[[m.name2id("box", "geom"),
+                                  m.name2id("sphere", "geom")], 2]
+  # README prints 8 decimals: [ 0.19996362  0.39996362]
+  np.testing.assert_allclose(z, [0.19996362, 0.39996362], atol=5e-9)
+
+
+# wrapper/core_test.py:328-367 (testDisableFlags) — cube on plane with a touch
+# sensor: 100 steps -> qvel ~ 0, touch ~ 9.81 N.
+CUBE_XML = """
+<mujoco>
+  <option{opt}/>
+  <worldbody>
+    <geom name="floor" type="plane" pos="0 0 0" size="10 10 0.1"/>
+    <body name="cube" pos="0 0 0.1">
+      <geom type="box" size="0.1 0.1 0.1" mass="1"/>
+      <site name="cube_site" type="box" size="0.1 0.1 0.1"/>
+      <joint type="slide"/>
+    </body>
+  </worldbody>
+  <sensor>
+    <touch name="touch_sensor" site="cube_site"/>
+  </sensor>
+</mujoco>"""
+
+
+def test_touch_sensor_reads_weight():
+  m = C.compile_xml(CUBE_XML.format(opt=""))
+  o = Oracle(m)
+  o.forward()
+  for _ in range(100):
+    o.mj_step()
+  o.forward()
+  np.testing.assert_almost_equal(o.qvel[0], 0, decimal=4)
+  np.testing.assert_almost_equal(o.sensordata[0], 9.81, decimal=2)
+
+
+def test_disable_contact_and_gravity():
+  xml = CUBE_XML.format(opt="").replace(
+      "<option/>", '<option><flag contact="disable" gravity="disable"/></option>')
+  o = Oracle(C.compile_xml(xml))
+  for _ in range(10):
+    o.mj_step()
+  o.forward()
+  assert o.sensordata[0] == 0 and o.qvel[0] == 0
+  xml = CUBE_XML.format(opt="").replace(
+      "<option/>", '<option><flag contact="disable"/></option>')
+  o = Oracle(C.compile_xml(xml))
+  for _ in range(10):
+    o.mj_step()
+  assert o.qvel[0] < -0.1                       # core_test.py:360-367: falls
+
+
+# core_test.py:461-484 (testContactForce): box on floor, 500 steps, the summed
+# normal force equals the weight to 7 places.
+def test_contact_force_equals_weight():
+  xml = """
+  <mujoco>
+    <worldbody>
+      <geom name="floor" type="plane" size="1 1 1"/>
+      <body name="block" pos="0 0 0.1">
+        <freejoint/>
+        <geom type="box" size="0.1 0.1 0.1" mass="2.5"/>
+      </body>
+    </worldbody>
+  </mujoco>"""
+  m = C.compile_xml(xml)
+  o = Oracle(m)
+  for _ in range(500):
+    o.mj_step()
+  o.forward()
+  ncon, nefc = int(o.ncon[0]), int(o.nefc[0])
+  assert ncon == 4 and nefc == 16
+  normal = o.efc_force[:nefc].sum()      # pyramid edges: normal = sum of rows
+  np.testing.assert_almost_equal(normal, 2.5 * 9.81, decimal=7)
+  # time advances by exactly `timestep` each step (core_test.py:159-172)
+  t = o.time[0]
+  o.mj_step()
+  assert o.time[0] == t + m.opt_timestep
+
+
+# core_test.py:408-459 (testObjectVelocity): cart at 1 m/s, pole hinge at 1 rad/s.
+def test_object_velocity_cartpole():
+  xml = """
+  <mujoco>
+    <worldbody>
+      <body name="cart">
+        <joint name="slider" type="slide" axis="1 0 0"/>
+        <geom type="box" size=".2 .1 .1" mass="1"/>
+        <body name="pole">
+          <joint name="hinge" type="hinge" axis="0 1 0"/>
+          <geom name="pole" type="capsule" fromto="0 0 0 0 0 1" size=".05" mass=".1"/>
+          <site name="tip" pos="0 0 1"/>
+          <site name="mid" pos="0 0 .5"/>
+        </body>
+      </body>
+    </worldbody>
+    <sensor>
+      <velocimeter name="tip_vel" site="tip"/>
+      <gyro name="tip_gyro" site="tip"/>
+      <velocimeter name="mid_vel" site="mid"/>
+    </sensor>
+  </mujoco>"""
+  m = C.compile_xml(xml)
+  o = Oracle(m)
+  o.qvel[:] = [1.0, 1.0]
+  o.step1()
+  # world-frame == site-frame at qpos=0: tip moves at 1 + 1*1 = 2 m/s ... the
+  # reference's numbers use slider=.5: check the same linear structure here.
+  np.testing.assert_allclose(o.sensordata[0:3], [2.0, 0, 0], atol=1e-12)
+  np.testing.assert_allclose(o.sensordata[3:6], [0, 1.0, 0], atol=1e-12)
+  np.testing.assert_allclose(o.sensordata[6:9], [1.5, 0, 0], atol=1e-12)
+  o.qvel[:] = [0.5, 1.0]
+  o.step1()
+  np.testing.assert_allclose(o.sensordata[0:3], [1.5, 0, 0], atol=1e-12)
+  # rotated pole: local-frame velocity of the tip about the hinge only
+  o.qpos[:] = [0, np.pi]
+  o.qvel[:] = [0.0, 0.5]
+  o.step1()
+  np.testing.assert_allclose(o.sensordata[0:3], [0.5, 0, 0], atol=1e-12)
+
+
+# engine_test.py:491-504: accelerometer reads +9.81 along z after reset;
+# actuator_force is zero with actuation disabled and gain*ctrl otherwise.
+def test_accelerometer_and_actuation():
+  xml = """
+  <mujoco>
+    <worldbody>
+      <geom type="plane" size="1 1 .1"/>
+      <body name="b" pos="0 0 .1">
+        <joint name="j" type="slide" axis="0 0 1"/>
+        <geom type="sphere" size=".1"/>
+        <site name="s"/>
+      </body>
+    </worldbody>
+    <actuator><motor name="m" joint="j" gear="1"/></actuator>
+    <sensor><accelerometer name="acc" site="s"/></sensor>
+  </mujoco>"""
+  m = C.compile_xml(xml)
+  o = Oracle(m)
+  for _ in range(300):
+    o.mj_step()
+  o.forward()
+  np.testing.assert_allclose(o.sensordata[:3], [0, 0, 9.81], atol=1e-5)
+  o.ctrl[0] = 1.0
+  o.forward()
+  assert o.actuator_force[0] == 1.0
+
+
+def test_bad_ctrl_and_bad_qpos_warnings():
+  """engine_test.py:400-436: NaN ctrl -> BADCTRL; inf/nan/huge qpos -> BADQPOS."""
+  m = C.compile_xml(CUBE_XML.format(opt="").replace(
+      "</worldbody>", "</worldbody><actuator><motor joint='j0'/></actuator>"
+  ).replace('<joint type="slide"/>', '<joint name="j0" type="slide"/>'))
+  o = Oracle(m)
+  o.ctrl[0] = np.nan
+  o.mj_step()
+  assert o.warning[7] == 1
+  for bad in (np.inf, np.nan, 1e15):
+    o = Oracle(m)
+    o.qpos[0] = bad
+    o.mj_step()
+    assert o.warning[4] == 1
+    assert np.isfinite(o.qpos).all()
+
+
+def test_determinism_and_copy():
+  """engine_test.py:462-484: identical stepping gives exactly equal state."""
+  m = C.compile_xml(README_XML)
+  a, b = Oracle(m), Oracle(m)
+  for o in (a, b):
+    o.qpos[0] = 0.25
+    o.forward()
+  for _ in range(50):
+    a.step(); b.step()
+  assert a.time[0] == b.time[0]
+  np.testing.assert_array_equal(a.qpos, b.qpos)
+  np.testing.assert_array_equal(a.xpos, b.xpos)
+
+
+PENDULUM2 = """
+<mujoco>
+  <option timestep="0.002" integrator="RK4"><flag energy="enable" contact="disable"/></option>
+  <worldbody>
+    <body pos="0 0 2">
+      <joint name="a" type="hinge" axis="0 1 0"/>
+      <geom type="capsule" fromto="0 0 0 0 0 -1" size=".05" mass="1"/>
+      <body pos="0 0 -1">
+        <joint name="b" type="hinge" axis="0 1 0"/>
+        <geom type="capsule" fromto="0 0 0 0 0 -1" size=".04" mass="1"/>
+      </body>
+    </body>
+  </worldbody>
+</mujoco>"""
+
+
+def test_energy_conservation_rk4():
+  """Engine-independent: undamped double pendulum under RK4 conserves energy."""
+  m = C.compile_xml(PENDULUM2)
+  o = Oracle(m)
+  o.qpos[:] = [1.0, -0.5]
+  o.forward()
+  e0 = o.energy.sum()
+  for _ in range(2000):
+    o.mj_step()
+  o.forward()
+  assert abs(o.energy.sum() - e0) < 1e-7 * max(1, abs(e0))
+
+
+def test_mass_matrix_and_bias_consistency():
+  """CRB inertia equals the dense J^T I J sum of the host compiler, is PD, and
+  M*qacc_smooth == qfrc_smooth (SURVEY §8c extra checks)."""
+  m = C.compile_xml(PENDULUM2.replace('integrator="RK4"', ""))
+  o = Oracle(m)
+  rng = np.random.RandomState(0)
+  o.qpos[:] = rng.uniform(-2, 2, m.nq)
+  o.qvel[:] = rng.uniform(-2, 2, m.nv)
+  o.forward()
+  kin = C.host_kinematics(m, np.array(o.qpos))
+  Md = C.host_mass_matrix(m, kin)
+  Mo = np.zeros((m.nv, m.nv))
+  for i in range(m.nv):
+    a, j = m.dof_Madr[i], i
+    while j >= 0:
+      Mo[i, j] = Mo[j, i] = o.qM[a]
+      a += 1
+      j = m.dof_parentid[j]
+  np.testing.assert_allclose(Mo, Md, rtol=1e-12, atol=1e-14)
+  assert np.all(np.linalg.eigvalsh(Mo) > 0)
+  np.testing.assert_allclose(Mo @ o.qacc_smooth, o.qfrc_smooth, rtol=1e-11, atol=1e-12)
+  # bias force against a finite-difference Lagrangian: d/dt(dL/dv) - dL/dq
+  def lagr_terms(q, v):
+    o.qpos[:] = q; o.qvel[:] = v; o.forward()
+    return o.energy[1] - o.energy[0]
+  q, v, eps = np.array(o.qpos), np.array(o.qvel), 1e-6
+  bias = np.array(o.qfrc_bias)
+  Mq = Mo.copy()
+  dLdq = np.array([(lagr_terms(q + eps * np.eye(2)[k], v) -
+                    lagr_terms(q - eps * np.eye(2)[k], v)) / (2 * eps)
+                   for k in range(2)])
+  # Mdot*v via finite difference of M along v
+  def Mat(qq):
+    o.qpos[:] = qq; o.qvel[:] = v; o.forward()
+    Mx = np.zeros((2, 2))
+    for i in range(2):
+      a, j = m.dof_Madr[i], i
+      while j >= 0:
+        Mx[i, j] = Mx[j, i] = o.qM[a]; a += 1; j = m.dof_parentid[j]
+    return Mx
+  Mdot = (Mat(q + eps * v) - Mat(q - eps * v)) / (2 * eps)
+  np.testing.assert_allclose(bias, Mdot @ v - dLdq, rtol=1e-6, atol=1e-6)
