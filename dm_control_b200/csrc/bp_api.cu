@@ -1,0 +1,541 @@
+// C ABI of libbphys.so (include/bphys.h): model upload, batch allocation, launches.
+// Host side only; the kernels live in bp_step.cu / bp_task.cu.
+#include <cuda_runtime.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/bphys.h"
+#include "bp_types.h"
+
+extern "C" int bp_launch_step(const BpParams* P, cudaStream_t stream);
+extern "C" int bp_launch_reset(const BpParams* P, const double* key_qpos,
+                               const double* key_qvel, const double* key_act,
+                               double key_time, cudaStream_t stream);
+extern "C" int bp_launch_task(const BpParams* P, const BpTask* T, double* obs,
+                              double* reward, cudaStream_t stream);
+extern "C" int bp_task_nobs_impl(const BpModel* m, int task);
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+#define CUDA_OK(expr)                                                        \
+  do {                                                                       \
+    cudaError_t e_ = (expr);                                                 \
+    if (e_ != cudaSuccess)                                                   \
+      return fail(BP_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(e_)); \
+  } while (0)
+
+struct BlobEntry {
+  char name[40];
+  int32_t dtype, ndim, dims[4];
+  int64_t offset, count;
+};
+
+struct HostField {
+  int dtype;                     // 0 f64, 1 i32
+  std::vector<double> f;
+  std::vector<int32_t> i;
+  size_t dev_off = 0;            // byte offset inside the device buffer
+  size_t nbytes() const { return dtype == 0 ? f.size() * 8 : i.size() * 4; }
+  const void* data() const { return dtype == 0 ? (const void*)f.data() : (const void*)i.data(); }
+};
+
+struct bp_model {
+  int device = 0;
+  std::map<std::string, HostField> fields;   // blob fields + derived arrays
+  std::vector<unsigned long long> dofmask;
+  char* dev = nullptr;                        // one device buffer for every array
+  size_t dev_bytes = 0;
+  BpModel M;                                  // scalars + device pointers
+};
+
+static const std::vector<int32_t>& I(bp_model* m, const char* n) { return m->fields[n].i; }
+static const std::vector<double>& F(bp_model* m, const char* n) { return m->fields[n].f; }
+static void put_i(bp_model* m, const char* n, const std::vector<int32_t>& v) {
+  HostField h; h.dtype = 1; h.i = v; if (h.i.empty()) h.i.push_back(0); m->fields[n] = h;
+}
+
+// scalars are refreshed from the host fields (after bp_model_set_field too)
+static int refresh_scalars(bp_model* m) {
+  BpModel& M = m->M;
+#define X(n) { auto it = m->fields.find(#n); \
+    if (it == m->fields.end()) return fail(BP_EINVAL, "model blob lacks field " #n); \
+    M.n = it->second.dtype == 1 ? it->second.i[0] : (int)it->second.f[0]; }
+  BP_MODEL_INT_SCALARS(X)
+#undef X
+#define X(n) { auto it = m->fields.find(#n); \
+    if (it == m->fields.end()) return fail(BP_EINVAL, "model blob lacks field " #n); \
+    M.n = it->second.dtype == 0 ? it->second.f[0] : (double)it->second.i[0]; }
+  BP_MODEL_F64_SCALARS(X)
+#undef X
+  M.any_damping = 0;
+  for (double d : F(m, "dof_damping")) if (d > 0) M.any_damping = 1;
+  if (M.nv == 0) M.any_damping = 0;
+  return BP_OK;
+}
+
+static int derive(bp_model* m) {
+  BpModel& M = m->M;
+  const int nb = M.nbody, nv = M.nv;
+  if (nv > 64) return fail(BP_EINVAL, "models with nv > 64 are not supported");
+  auto& par = I(m, "body_parentid");
+  std::vector<int32_t> depth(nb, 0);
+  int maxd = 0;
+  for (int b = 1; b < nb; b++) { depth[b] = depth[par[b]] + 1; if (depth[b] > maxd) maxd = depth[b]; }
+  M.nlevel = maxd + 1;
+  std::vector<int32_t> ladr(M.nlevel + 1, 0), llist;
+  for (int l = 0; l < M.nlevel; l++) {
+    ladr[l] = (int)llist.size();
+    for (int b = 0; b < nb; b++) if (depth[b] == l) llist.push_back(b);
+  }
+  ladr[M.nlevel] = (int)llist.size();
+  put_i(m, "body_level_adr", ladr); put_i(m, "body_level_list", llist);
+  std::vector<int32_t> cadr(nb + 1, 0), clist;
+  for (int b = 0; b < nb; b++) {
+    cadr[b] = (int)clist.size();
+    for (int ch = nb - 1; ch > 0; ch--) if (par[ch] == b && ch != b) clist.push_back(ch);
+  }
+  cadr[nb] = (int)clist.size();
+  put_i(m, "body_child_adr", cadr); put_i(m, "body_child_list", clist);
+  auto& dpar = I(m, "dof_parentid");
+  auto& madr = I(m, "dof_Madr");
+  std::vector<int32_t> ddepth(nv > 0 ? nv : 1, 0), mcol(M.nM > 0 ? M.nM : 1, 0);
+  int maxdd = 0;
+  for (int i = 0; i < nv; i++) {
+    int a = madr[i], d = 0;
+    for (int j = i; j >= 0; j = dpar[j]) { mcol[a++] = j; d++; }
+    ddepth[i] = d - 1;
+    if (d - 1 > maxdd) maxdd = d - 1;
+  }
+  M.ndoflevel = nv > 0 ? maxdd + 1 : 0;
+  put_i(m, "dof_depth", ddepth); put_i(m, "M_col", mcol);
+  std::vector<int32_t> dladr(M.ndoflevel + 1, 0), dllist;
+  for (int l = 0; l < M.ndoflevel; l++) {
+    dladr[l] = (int)dllist.size();
+    for (int i = 0; i < nv; i++) if (ddepth[i] == l) dllist.push_back(i);
+  }
+  dladr[M.ndoflevel] = (int)dllist.size();
+  put_i(m, "dof_level_adr", dladr); put_i(m, "dof_level_list", dllist);
+  // dof ancestry masks per body
+  auto& bdofadr = I(m, "body_dofadr");
+  auto& bdofnum = I(m, "body_dofnum");
+  m->dofmask.assign(nb, 0ull);
+  for (int b = 1; b < nb; b++) {
+    unsigned long long mk = m->dofmask[par[b]];
+    for (int k = 0; k < bdofnum[b]; k++) mk |= 1ull << (bdofadr[b] + k);
+    m->dofmask[b] = mk;
+  }
+  std::vector<int32_t> fric, lim;
+  auto& fl = F(m, "dof_frictionloss");
+  for (int i = 0; i < nv; i++) if (fl[i] > 0) fric.push_back(i);
+  auto& jl = I(m, "jnt_limited");
+  auto& jt = I(m, "jnt_type");
+  for (int j = 0; j < M.njnt; j++)
+    if (jl[j] && (jt[j] == JNT_SLIDE || jt[j] == JNT_HINGE)) lim.push_back(j);
+  M.nfric = (int)fric.size(); M.nlim = (int)lim.size();
+  put_i(m, "fric_dof", fric); put_i(m, "lim_jnt", lim);
+  std::vector<int32_t> ti, tj;
+  for (int i = 0; i < nv; i++) for (int j = 0; j <= i; j++) { ti.push_back(i); tj.push_back(j); }
+  M.ntri = (int)ti.size();
+  put_i(m, "tri_i", ti); put_i(m, "tri_j", tj);
+  M.nvp = nv | 1;
+  // actuators attached to each dof (joint transmission on scalar joints)
+  auto& trnid = I(m, "actuator_trnid");
+  auto& trntype = I(m, "actuator_trntype");
+  auto& jdof = I(m, "jnt_dofadr");
+  std::vector<int32_t> aadr(nv + 1, 0), alist;
+  for (int u = 0; u < M.nu; u++)
+    if (trntype[u] != 0) return fail(BP_EINVAL, "only joint transmissions are supported");
+  for (int d = 0; d < nv; d++) {
+    aadr[d] = (int)alist.size();
+    for (int u = 0; u < M.nu; u++) if (jdof[trnid[2 * u]] == d) alist.push_back(u);
+  }
+  aadr[nv] = (int)alist.size();
+  put_i(m, "dof_actadr", aadr); put_i(m, "dof_actlist", alist);
+  M.need_subtreevel = 0; M.need_rnepost_stage = 0;
+  auto& st = I(m, "sensor_type");
+  auto& ss = I(m, "sensor_needstage");
+  for (int s = 0; s < M.nsensor; s++) {
+    if (st[s] == SENS_SUBTREELINVEL) M.need_subtreevel = 1;
+    if (st[s] == SENS_ACCELEROMETER || st[s] == SENS_FORCE || st[s] == SENS_TORQUE)
+      M.need_rnepost_stage = ss[s];
+  }
+  return BP_OK;
+}
+
+static int upload(bp_model* m) {
+  size_t off = 0;
+  for (auto& kv : m->fields) { kv.second.dev_off = off; off += (kv.second.nbytes() + 15) / 16 * 16; }
+  size_t mask_off = off;
+  off += (m->dofmask.size() * 8 + 15) / 16 * 16 + 16;
+  if (!m->dev || off > m->dev_bytes) {
+    if (m->dev) cudaFree(m->dev);
+    m->dev = nullptr;
+    CUDA_OK(cudaMalloc((void**)&m->dev, off));
+    m->dev_bytes = off;
+  }
+  std::vector<char> stage(off, 0);
+  for (auto& kv : m->fields) memcpy(stage.data() + kv.second.dev_off, kv.second.data(), kv.second.nbytes());
+  if (!m->dofmask.empty()) memcpy(stage.data() + mask_off, m->dofmask.data(), m->dofmask.size() * 8);
+  CUDA_OK(cudaMemcpy(m->dev, stage.data(), off, cudaMemcpyHostToDevice));
+  BpModel& M = m->M;
+#define X(n) M.n = (const int*)(m->dev + m->fields[#n].dev_off);
+  BP_MODEL_INT_ARRAYS(X)
+  BP_MODEL_DERIVED_INT_ARRAYS(X)
+#undef X
+#define X(n) M.n = (const double*)(m->dev + m->fields[#n].dev_off);
+  BP_MODEL_F64_ARRAYS(X)
+#undef X
+  M.body_dofmask = (const unsigned long long*)(m->dev + mask_off);
+  return BP_OK;
+}
+
+extern "C" int bp_version(void) { return 100; }
+extern "C" const char* bp_last_error(void) { return g_err.c_str(); }
+extern "C" int bp_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  return n;
+}
+
+extern "C" bp_model* bp_model_create(const void* blob, int64_t nbytes, int device,
+                                     char* err, int errsz) {
+  auto bail = [&](const std::string& msg) -> bp_model* {
+    g_err = msg;
+    if (err && errsz > 0) snprintf(err, errsz, "%s", msg.c_str());
+    return nullptr;
+  };
+  if (!blob || nbytes < 16 || memcmp(blob, "BPMODEL1", 8) != 0) return bail("bad model blob magic");
+  if (bp_device_count() <= 0) return bail("no CUDA device: libbphys has no CPU fallback");
+  if (cudaSetDevice(device) != cudaSuccess) return bail("cudaSetDevice failed");
+  const char* base = (const char*)blob;
+  int nfields = *(const int32_t*)(base + 8);
+  const BlobEntry* ent = (const BlobEntry*)(base + 16);
+  bp_model* m = new bp_model();
+  m->device = device;
+  for (int k = 0; k < nfields; k++) {
+    HostField h;
+    h.dtype = ent[k].dtype;
+    if (ent[k].offset < 0 || ent[k].offset + ent[k].count * (h.dtype == 0 ? 8 : 4) > nbytes) {
+      delete m; return bail("model blob truncated");
+    }
+    if (h.dtype == 0) h.f.assign((const double*)(base + ent[k].offset), (const double*)(base + ent[k].offset) + ent[k].count);
+    else h.i.assign((const int32_t*)(base + ent[k].offset), (const int32_t*)(base + ent[k].offset) + ent[k].count);
+    if (h.dtype == 0 && h.f.empty()) h.f.push_back(0);
+    if (h.dtype == 1 && h.i.empty()) h.i.push_back(0);
+    char nm[41]; memcpy(nm, ent[k].name, 40); nm[40] = 0;
+    m->fields[nm] = h;
+  }
+  const char* missing = nullptr;
+#define X(n) if (!m->fields.count(#n)) missing = #n;
+  BP_MODEL_INT_ARRAYS(X)
+  BP_MODEL_F64_ARRAYS(X)
+#undef X
+  if (missing) { std::string s = std::string("model blob lacks field ") + missing; delete m; return bail(s); }
+  if (refresh_scalars(m) != BP_OK || derive(m) != BP_OK || upload(m) != BP_OK) {
+    std::string s = g_err; if (m->dev) cudaFree(m->dev); delete m; return bail(s);
+  }
+  return m;
+}
+
+extern "C" void bp_model_free(bp_model* m) {
+  if (!m) return;
+  if (m->dev) cudaFree(m->dev);
+  delete m;
+}
+
+extern "C" int bp_model_set_field(bp_model* m, const char* name, const void* data,
+                                  int64_t nbytes) {
+  if (!m || !name || !data) return fail(BP_EINVAL, "null argument");
+  auto it = m->fields.find(name);
+  if (it == m->fields.end()) return fail(BP_ENOFIELD, std::string("no model field ") + name);
+  HostField& h = it->second;
+  if ((int64_t)h.nbytes() != nbytes) return fail(BP_EINVAL, std::string("size mismatch for ") + name);
+  memcpy(h.dtype == 0 ? (void*)h.f.data() : (void*)h.i.data(), data, nbytes);
+  cudaSetDevice(m->device);
+  CUDA_OK(cudaMemcpy(m->dev + h.dev_off, data, nbytes, cudaMemcpyHostToDevice));
+  return refresh_scalars(m);
+}
+
+extern "C" int bp_model_get_field(bp_model* m, const char* name, void* data, int64_t nbytes) {
+  if (!m || !name || !data) return fail(BP_EINVAL, "null argument");
+  auto it = m->fields.find(name);
+  if (it == m->fields.end()) return fail(BP_ENOFIELD, std::string("no model field ") + name);
+  if ((int64_t)it->second.nbytes() != nbytes) return fail(BP_EINVAL, "size mismatch");
+  memcpy(data, it->second.data(), nbytes);
+  return BP_OK;
+}
+
+// ------------------------------------------------------------------ batch
+struct FieldInfo { std::string name; int64_t offset_bytes, count; int dtype; };
+
+struct bp_batch {
+  bp_model* model;
+  int64_t nenv;
+  BpLayout L;
+  double* image = nullptr;
+  unsigned char* mask = nullptr;
+  bool use_mask = false;
+  cudaStream_t stream = nullptr;
+  std::vector<FieldInfo> fields;
+  double *ctrl_stage = nullptr, *obs_dev = nullptr, *rew_dev = nullptr;  // e2e staging
+  int obs_cap = 0;
+  BpTask task;
+};
+
+static void make_layout(const BpModel& m, int njmax, int nconmax, BpLayout* L,
+                        std::vector<FieldInfo>* fields) {
+  int off = 0;
+#define X(n, cnt) { L->n = off; int c_ = (cnt); \
+    if (fields) fields->push_back({#n, (int64_t)off * 8, c_, 0}); off += c_; }
+  BP_DATA_F64(X)
+#undef X
+  L->ints = off;
+  int ioff = 0;
+#define X(n, cnt) { L->n = ioff; int c_ = (cnt); \
+    if (fields) fields->push_back({#n, (int64_t)L->ints * 8 + (int64_t)ioff * 4, c_, 1}); ioff += c_; }
+  BP_DATA_I32(X)
+#undef X
+  off += (ioff + 1) / 2;
+  off = (off + 1) / 2 * 2;      // keep 16-byte alignment of each env image
+  L->persist = off;
+#define X(n, cnt) { L->n = off; off += (cnt); }
+  BP_DATA_SCRATCH(X)
+#undef X
+  L->total = off;
+  L->njmax = njmax; L->nconmax = nconmax;
+}
+
+extern "C" bp_batch* bp_batch_create(bp_model* m, int64_t nenv, int njmax, int nconmax,
+                                     char* err, int errsz) {
+  auto bail = [&](const std::string& msg) -> bp_batch* {
+    g_err = msg;
+    if (err && errsz > 0) snprintf(err, errsz, "%s", msg.c_str());
+    return nullptr;
+  };
+  if (!m || nenv <= 0) return bail("bad arguments to bp_batch_create");
+  if (njmax <= 0) njmax = m->M.njmax;
+  if (nconmax <= 0) nconmax = m->M.nconmax;
+  cudaSetDevice(m->device);
+  bp_batch* b = new bp_batch();
+  b->model = m; b->nenv = nenv;
+  memset(&b->task, 0, sizeof b->task);
+  make_layout(m->M, njmax, nconmax, &b->L, &b->fields);
+  int maxsm = 0;
+  cudaDeviceGetAttribute(&maxsm, cudaDevAttrMaxSharedMemoryPerBlockOptin, m->device);
+  if ((size_t)b->L.total * 8 > (size_t)maxsm) {
+    char msg[256];
+    snprintf(msg, sizeof msg, "one environment needs %zu B of shared memory (njmax=%d, "
+             "nconmax=%d) but an SM offers %d B: lower njmax/nconmax",
+             (size_t)b->L.total * 8, njmax, nconmax, maxsm);
+    delete b; return bail(msg);
+  }
+  size_t bytes = (size_t)nenv * b->L.persist * 8;
+  if (cudaMalloc((void**)&b->image, bytes) != cudaSuccess ||
+      cudaMalloc((void**)&b->mask, nenv) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking) != cudaSuccess) {
+    std::string s = std::string("device allocation failed: ") + cudaGetErrorString(cudaGetLastError());
+    if (b->image) cudaFree(b->image);
+    if (b->mask) cudaFree(b->mask);
+    delete b; return bail(s);
+  }
+  cudaMemsetAsync(b->image, 0, bytes, b->stream);
+  cudaMemsetAsync(b->mask, 1, nenv, b->stream);
+  bp_reset(b, -1);
+  cudaStreamSynchronize(b->stream);
+  return b;
+}
+
+extern "C" void bp_batch_free(bp_batch* b) {
+  if (!b) return;
+  cudaSetDevice(b->model->device);
+  if (b->stream) { cudaStreamSynchronize(b->stream); cudaStreamDestroy(b->stream); }
+  cudaFree(b->image); cudaFree(b->mask);
+  if (b->ctrl_stage) cudaFree(b->ctrl_stage);
+  if (b->obs_dev) cudaFree(b->obs_dev);
+  if (b->rew_dev) cudaFree(b->rew_dev);
+  delete b;
+}
+
+extern "C" void* bp_batch_image(bp_batch* b) { return b ? b->image : nullptr; }
+extern "C" int64_t bp_batch_stride(bp_batch* b) { return b ? b->L.persist : 0; }
+extern "C" int64_t bp_batch_nenv(bp_batch* b) { return b ? b->nenv : 0; }
+extern "C" int64_t bp_batch_smem_bytes(bp_batch* b) { return b ? (int64_t)b->L.total * 8 : 0; }
+extern "C" void* bp_batch_stream(bp_batch* b) { return b ? (void*)b->stream : nullptr; }
+extern "C" int bp_field_count(bp_batch* b) { return b ? (int)b->fields.size() : 0; }
+extern "C" const char* bp_field_name(bp_batch* b, int i) {
+  return (b && i >= 0 && i < (int)b->fields.size()) ? b->fields[i].name.c_str() : nullptr;
+}
+static const FieldInfo* find_field(bp_batch* b, const char* name) {
+  for (auto& f : b->fields) if (f.name == name) return &f;
+  return nullptr;
+}
+extern "C" int bp_field_info(bp_batch* b, const char* name, int64_t* off, int64_t* count,
+                             int* dtype) {
+  if (!b || !name) return fail(BP_EINVAL, "null argument");
+  const FieldInfo* f = find_field(b, name);
+  if (!f) return fail(BP_ENOFIELD, std::string("no data field ") + name);
+  if (off) *off = f->offset_bytes;
+  if (count) *count = f->count;
+  if (dtype) *dtype = f->dtype;
+  return BP_OK;
+}
+
+static int field_copy(bp_batch* b, const char* name, void* host, int64_t env0, int64_t n,
+                      bool to_device) {
+  if (!b || !name || !host) return fail(BP_EINVAL, "null argument");
+  const FieldInfo* f = find_field(b, name);
+  if (!f) return fail(BP_ENOFIELD, std::string("no data field ") + name);
+  if (env0 < 0 || n < 0 || env0 + n > b->nenv) return fail(BP_EINVAL, "env range out of bounds");
+  if (n == 0 || f->count == 0) return BP_OK;
+  cudaSetDevice(b->model->device);
+  size_t w = (size_t)f->count * (f->dtype == 0 ? 8 : 4), pitch = (size_t)b->L.persist * 8;
+  char* dev = (char*)b->image + (size_t)env0 * pitch + f->offset_bytes;
+  if (to_device)
+    CUDA_OK(cudaMemcpy2DAsync(dev, pitch, host, w, w, n, cudaMemcpyHostToDevice, b->stream));
+  else
+    CUDA_OK(cudaMemcpy2DAsync(host, w, dev, pitch, w, n, cudaMemcpyDeviceToHost, b->stream));
+  CUDA_OK(cudaStreamSynchronize(b->stream));
+  return BP_OK;
+}
+extern "C" int bp_field_write(bp_batch* b, const char* name, const void* host, int64_t env0,
+                              int64_t n) {
+  return field_copy(b, name, (void*)host, env0, n, true);
+}
+extern "C" int bp_field_read(bp_batch* b, const char* name, void* host, int64_t env0,
+                             int64_t n) {
+  return field_copy(b, name, host, env0, n, false);
+}
+
+extern "C" int bp_set_mask(bp_batch* b, const uint8_t* mask_host) {
+  if (!b) return fail(BP_EINVAL, "null batch");
+  cudaSetDevice(b->model->device);
+  b->use_mask = mask_host != nullptr;
+  if (mask_host) {
+    CUDA_OK(cudaMemcpyAsync(b->mask, mask_host, b->nenv, cudaMemcpyHostToDevice, b->stream));
+    CUDA_OK(cudaStreamSynchronize(b->stream));
+  }
+  return BP_OK;
+}
+
+static BpParams make_params(bp_batch* b, int mode, int nsub, int disable_actuation) {
+  BpParams P;
+  memset(&P, 0, sizeof P);
+  P.m = b->model->M; P.L = b->L; P.image = b->image;
+  P.mask = b->use_mask ? b->mask : nullptr;
+  P.nenv = b->nenv; P.mode = mode; P.nsub = nsub; P.disable_actuation = disable_actuation;
+  return P;
+}
+
+static int launch(bp_batch* b, int mode, int nsub, int disable_actuation) {
+  if (!b) return fail(BP_EINVAL, "null batch");
+  cudaSetDevice(b->model->device);
+  BpParams P = make_params(b, mode, nsub, disable_actuation);
+  int e = bp_launch_step(&P, b->stream);
+  if (e != 0) return fail(BP_ECUDA, std::string("step launch: ") + cudaGetErrorString((cudaError_t)e));
+  return BP_OK;
+}
+extern "C" int bp_step(bp_batch* b, int nsub) { return launch(b, BP_MODE_STEP, nsub, 0); }
+extern "C" int bp_mj_step(bp_batch* b, int nsub) { return launch(b, BP_MODE_MJSTEP, nsub, 0); }
+extern "C" int bp_forward(bp_batch* b, int da) { return launch(b, BP_MODE_FORWARD, 1, da); }
+extern "C" int bp_step1(bp_batch* b) { return launch(b, BP_MODE_STEP1, 1, 0); }
+extern "C" int bp_step2(bp_batch* b) { return launch(b, BP_MODE_STEP2, 1, 0); }
+
+extern "C" int bp_reset(bp_batch* b, int key) {
+  if (!b) return fail(BP_EINVAL, "null batch");
+  bp_model* m = b->model;
+  cudaSetDevice(m->device);
+  BpParams P = make_params(b, 0, 0, 0);
+  const double *kq = nullptr, *kv = nullptr, *ka = nullptr;
+  double kt = 0;
+  if (key >= 0) {
+    if (key >= m->M.nkey) return fail(BP_EINVAL, "keyframe index out of range");
+    auto dev = [&](const char* n, int stride) {
+      return (const double*)(m->dev + m->fields[n].dev_off) + (size_t)key * stride;
+    };
+    if (!m->fields.count("key_qpos")) return fail(BP_ENOFIELD, "model has no keyframes");
+    kq = dev("key_qpos", m->M.nq); kv = dev("key_qvel", m->M.nv); ka = dev("key_act", m->M.na);
+    kt = m->fields["key_time"].f[key];
+  }
+  int e = bp_launch_reset(&P, kq, kv, ka, kt, b->stream);
+  if (e != 0) return fail(BP_ECUDA, std::string("reset launch: ") + cudaGetErrorString((cudaError_t)e));
+  return BP_OK;
+}
+
+extern "C" int bp_set_task(bp_batch* b, int kind, const int32_t* ip, int nip,
+                           const double* fp, int nfp) {
+  if (!b || nip < 0 || nip > 16 || nfp < 0 || nfp > 8) return fail(BP_EINVAL, "bad task arguments");
+  BpTask t;
+  memset(&t, 0, sizeof t);
+  t.kind = kind;
+  for (int i = 0; i < nip; i++) t.ip[i] = ip[i];
+  for (int i = 0; i < nfp; i++) t.fp[i] = fp[i];
+  if (bp_task_nobs_impl(&b->model->M, kind) < 0) return fail(BP_EINVAL, "unknown task kind");
+  b->task = t;
+  return BP_OK;
+}
+
+extern "C" int bp_task_nobs(bp_batch* b) {
+  return b ? bp_task_nobs_impl(&b->model->M, b->task.kind) : -1;
+}
+
+extern "C" int bp_obs_reward(bp_batch* b, double* obs, double* reward) {
+  if (!b) return fail(BP_EINVAL, "null batch");
+  cudaSetDevice(b->model->device);
+  BpParams P = make_params(b, 0, 0, 0);
+  int e = bp_launch_task(&P, &b->task, obs, reward, b->stream);
+  if (e < 0) return fail(BP_EINVAL, "unknown task kind");
+  if (e != 0) return fail(BP_ECUDA, std::string("task launch: ") + cudaGetErrorString((cudaError_t)e));
+  return BP_OK;
+}
+
+extern "C" int bp_env_step_host(bp_batch* b, int nsub, const double* ctrl_host,
+                                double* obs_host, double* reward_host) {
+  if (!b || !ctrl_host) return fail(BP_EINVAL, "null argument");
+  bp_model* m = b->model;
+  cudaSetDevice(m->device);
+  int nobs = bp_task_nobs_impl(&m->M, b->task.kind);
+  if (nobs < 0) return fail(BP_EINVAL, "unknown task kind");
+  int nu = m->M.nu;
+  if (!b->ctrl_stage) {
+    CUDA_OK(cudaMalloc((void**)&b->ctrl_stage, (size_t)b->nenv * (nu > 0 ? nu : 1) * 8));
+    CUDA_OK(cudaMalloc((void**)&b->rew_dev, (size_t)b->nenv * 8));
+  }
+  if (nobs > b->obs_cap) {
+    if (b->obs_dev) cudaFree(b->obs_dev);
+    CUDA_OK(cudaMalloc((void**)&b->obs_dev, (size_t)b->nenv * nobs * 8));
+    b->obs_cap = nobs;
+  }
+  const FieldInfo* f = find_field(b, "ctrl");
+  size_t w = (size_t)nu * 8, pitch = (size_t)b->L.persist * 8;
+  if (nu > 0)
+    CUDA_OK(cudaMemcpy2DAsync((char*)b->image + f->offset_bytes, pitch, ctrl_host, w, w,
+                              b->nenv, cudaMemcpyHostToDevice, b->stream));
+  int e = launch(b, BP_MODE_STEP, nsub, 0);
+  if (e != BP_OK) return e;
+  e = bp_obs_reward(b, nobs > 0 ? b->obs_dev : nullptr, b->rew_dev);
+  if (e != BP_OK) return e;
+  if (obs_host && nobs > 0)
+    CUDA_OK(cudaMemcpyAsync(obs_host, b->obs_dev, (size_t)b->nenv * nobs * 8,
+                            cudaMemcpyDeviceToHost, b->stream));
+  if (reward_host)
+    CUDA_OK(cudaMemcpyAsync(reward_host, b->rew_dev, (size_t)b->nenv * 8,
+                            cudaMemcpyDeviceToHost, b->stream));
+  CUDA_OK(cudaStreamSynchronize(b->stream));
+  return BP_OK;
+}
+
+extern "C" int bp_warnings(bp_batch* b, int32_t* out_host) {
+  return bp_field_read(b, "warning", out_host, 0, b ? b->nenv : 0);
+}
+
+extern "C" int bp_sync(bp_batch* b) {
+  if (!b) return fail(BP_EINVAL, "null batch");
+  cudaSetDevice(b->model->device);
+  CUDA_OK(cudaStreamSynchronize(b->stream));
+  CUDA_OK(cudaGetLastError());
+  return BP_OK;
+}

@@ -1,0 +1,215 @@
+// mj_collision: static candidate pairs on lanes, primitive narrowphase, contacts
+// emitted in pair order through a warp prefix sum so that contact ids are
+// reproducible.
+#ifndef BP_COLLIDE_CUH_
+#define BP_COLLIDE_CUH_
+#include "bp_math.cuh"
+
+struct RawCon { double dist, pos[3], n[3], hint[3]; };
+
+__device__ __forceinline__ int col_plane_sphere(const double* ppos, const double* pn,
+                                                const double* ctr, double r,
+                                                double margin, RawCon& o) {
+  double dif[3] = {ctr[0] - ppos[0], ctr[1] - ppos[1], ctr[2] - ppos[2]};
+  double dist = dot3(dif, pn) - r;
+  if (dist > margin) return 0;
+  o.dist = dist;
+  for (int k = 0; k < 3; k++) {
+    o.pos[k] = ctr[k] - pn[k] * (r + 0.5 * dist);
+    o.n[k] = pn[k];
+    o.hint[k] = 0;
+  }
+  return 1;
+}
+
+__device__ __forceinline__ int col_sphere_sphere(const double* c1, double r1,
+                                                 const double* c2, double r2,
+                                                 double margin, RawCon& o) {
+  double n[3] = {c2[0] - c1[0], c2[1] - c1[1], c2[2] - c1[2]};
+  double len = norm3(n), dist = len - r1 - r2;
+  if (dist > margin) return 0;
+  if (len < BP_MINVAL) { n[0] = 1; n[1] = 0; n[2] = 0; }
+  else { n[0] /= len; n[1] /= len; n[2] /= len; }
+  o.dist = dist;
+  for (int k = 0; k < 3; k++) {
+    o.pos[k] = c1[k] + n[k] * (r1 + 0.5 * dist);
+    o.n[k] = n[k];
+    o.hint[k] = 0;
+  }
+  return 1;
+}
+
+// returns the number of raw contacts (<= 4) of ordered pair (type1 <= type2)
+__device__ int bp_collide_pair(const Ctx& c, int g1, int g2, double margin, RawCon* out) {
+  const BpModel& m = c.P.m;
+  int t1 = m.geom_type[g1], t2 = m.geom_type[g2];
+  const double *p1 = DF(geom_xpos) + 3 * g1, *p2 = DF(geom_xpos) + 3 * g2;
+  const double *R1 = DF(geom_xmat) + 9 * g1, *R2 = DF(geom_xmat) + 9 * g2;
+  const double *s1 = m.geom_size + 3 * g1, *s2 = m.geom_size + 3 * g2;
+  if (t1 == GEOM_PLANE) {
+    double n[3] = {R1[2], R1[5], R1[8]};
+    if (t2 == GEOM_SPHERE) return col_plane_sphere(p1, n, p2, s2[0], margin, out[0]);
+    if (t2 == GEOM_CAPSULE) {
+      double ax[3] = {R2[2], R2[5], R2[8]}, e[3], hl = s2[1];
+      int cnt = 0;
+      for (int sgn = 1; sgn >= -1; sgn -= 2) {
+        for (int k = 0; k < 3; k++) e[k] = p2[k] + sgn * ax[k] * hl;
+        if (col_plane_sphere(p1, n, e, s2[0], margin, out[cnt])) {
+          for (int k = 0; k < 3; k++) out[cnt].hint[k] = ax[k];
+          cnt++;
+        }
+      }
+      return cnt;
+    }
+    if (t2 == GEOM_BOX) {
+      double dif[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
+      double dist = dot3(dif, n);
+      int cnt = 0;
+      for (int i = 0; i < 8 && cnt < 4; i++) {
+        double v[3] = {(i & 1) ? s2[0] : -s2[0], (i & 2) ? s2[1] : -s2[1],
+                       (i & 4) ? s2[2] : -s2[2]}, cr[3];
+        mat_vec3(cr, R2, v);
+        double ld = dot3(n, cr);
+        if (dist + ld > margin) continue;
+        out[cnt].dist = dist + ld;
+        for (int k = 0; k < 3; k++) {
+          out[cnt].pos[k] = p2[k] + cr[k] - n[k] * 0.5 * (dist + ld);
+          out[cnt].n[k] = n[k];
+          out[cnt].hint[k] = 0;
+        }
+        cnt++;
+      }
+      return cnt;
+    }
+    return 0;
+  }
+  if (t1 == GEOM_SPHERE && t2 == GEOM_SPHERE)
+    return col_sphere_sphere(p1, s1[0], p2, s2[0], margin, out[0]);
+  if (t1 == GEOM_SPHERE && t2 == GEOM_CAPSULE) {
+    double ax[3] = {R2[2], R2[5], R2[8]};
+    double dif[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
+    double x = clampd(dot3(ax, dif), -s2[1], s2[1]);
+    double cc[3] = {p2[0] + ax[0] * x, p2[1] + ax[1] * x, p2[2] + ax[2] * x};
+    return col_sphere_sphere(p1, s1[0], cc, s2[0], margin, out[0]);
+  }
+  if (t1 == GEOM_CAPSULE && t2 == GEOM_CAPSULE) {
+    // closest points of segments p1 + x1*a1, p2 + x2*a2 with |xi| <= li
+    double a1[3] = {R1[2], R1[5], R1[8]}, a2[3] = {R2[2], R2[5], R2[8]};
+    double dif[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
+    double l1 = s1[1], l2 = s2[1];
+    double b = dot3(a1, a2), u = -dot3(a1, dif), v = dot3(a2, dif);
+    double det = 1.0 - b * b, x1, x2;
+    if (fabs(det) >= 1e-12) {
+      x1 = (u + b * v) / det;
+      x2 = (v + b * u) / det;
+      if (x1 > l1) { x1 = l1; x2 = v + b * x1; }
+      else if (x1 < -l1) { x1 = -l1; x2 = v + b * x1; }
+      if (x2 > l2) { x2 = l2; x1 = clampd(u + b * x2, -l1, l1); }
+      else if (x2 < -l2) { x2 = -l2; x1 = clampd(u + b * x2, -l1, l1); }
+    } else {
+      x1 = clampd(u, -l1, l1);
+      x2 = clampd(v + b * x1, -l2, l2);
+      x1 = clampd(u + b * x2, -l1, l1);
+    }
+    double c1[3], c2[3];
+    for (int k = 0; k < 3; k++) { c1[k] = p1[k] + a1[k] * x1; c2[k] = p2[k] + a2[k] * x2; }
+    return col_sphere_sphere(c1, s1[0], c2, s2[0], margin, out[0]);
+  }
+  return 0;
+}
+
+// frame rows: normal, tangent 1 (from the hint or a default axis), tangent 2
+__device__ __forceinline__ void make_frame(double* f) {
+  normalize3(f);
+  if (norm3(f + 3) < 0.5) {
+    f[3] = f[4] = f[5] = 0;
+    if (f[1] < 0.5 && f[1] > -0.5) f[4] = 1; else f[5] = 1;
+  }
+  double t = dot3(f, f + 3);
+  for (int k = 0; k < 3; k++) f[3 + k] -= t * f[k];
+  normalize3(f + 3);
+  cross3(f + 6, f, f + 3);
+}
+
+__device__ void bp_collision(const Ctx& c) {
+  const BpModel& m = c.P.m;
+  int* ncon_p = IF(ncon);
+  if (c.lane == 0) *ncon_p = 0;
+  SYNC();
+  if (m.opt_disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT)) return;
+  bool filterparent = !(m.opt_disableflags & DSBL_FILTERPARENT);
+  int nconmax = c.P.L.nconmax, base = 0;
+  bool full = false;
+  for (int p0 = 0; p0 < m.npair; p0 += 32) {
+    int p = p0 + c.lane, n = 0, g1 = 0, g2 = 0;
+    double margin = 0, gap = 0;
+    RawCon raw[4];
+    if (p < m.npair && !(filterparent && m.pair_parentchild[p])) {
+      g1 = m.pair_geom1[p]; g2 = m.pair_geom2[p];
+      margin = fmax(m.geom_margin[g1], m.geom_margin[g2]);
+      gap = fmax(m.geom_gap[g1], m.geom_gap[g2]);
+      const double *p1 = DF(geom_xpos) + 3 * g1, *p2 = DF(geom_xpos) + 3 * g2;
+      double dif[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
+      bool keep;
+      if (m.geom_type[g1] == GEOM_PLANE) {
+        const double* R1 = DF(geom_xmat) + 9 * g1;
+        double nrm[3] = {R1[2], R1[5], R1[8]};
+        keep = !(dot3(dif, nrm) > m.geom_rbound[g2] + margin);
+      } else {
+        double bound = m.geom_rbound[g1] + m.geom_rbound[g2] + margin;
+        keep = !(dot3(dif, dif) > bound * bound);
+      }
+      if (keep) n = bp_collide_pair(c, g1, g2, margin, raw);
+    }
+    // exclusive prefix sum of n over lanes -> slots in pair order
+    int incl = n;
+    for (int o = 1; o < 32; o <<= 1) {
+      int t = __shfl_up_sync(FULL, incl, o);
+      if (c.lane >= o) incl += t;
+    }
+    int start = base + incl - n;
+    base += __shfl_sync(FULL, incl, 31);
+    for (int i = 0; i < n; i++) {
+      int id = start + i;
+      if (id >= nconmax) { full = true; break; }
+      double f[9];
+      for (int k = 0; k < 3; k++) { f[k] = raw[i].n[k]; f[3 + k] = raw[i].hint[k]; f[6 + k] = 0; }
+      make_frame(f);
+      DF(contact_dist)[id] = raw[i].dist;
+      for (int k = 0; k < 3; k++) DF(contact_pos)[3 * id + k] = raw[i].pos[k];
+      for (int k = 0; k < 9; k++) DF(contact_frame)[9 * id + k] = f[k];
+      double inc = margin - gap;
+      DF(contact_includemargin)[id] = inc;
+      IF(contact_geom1)[id] = g1; IF(contact_geom2)[id] = g2;
+      int d1 = m.geom_condim[g1], d2 = m.geom_condim[g2];
+      IF(contact_dim)[id] = d1 > d2 ? d1 : d2;
+      const double *f1 = m.geom_friction + 3 * g1, *f2 = m.geom_friction + 3 * g2;
+      double fr[3];
+      for (int k = 0; k < 3; k++) fr[k] = fmax(f1[k], f2[k]);
+      double* cf = DF(contact_friction) + 5 * id;
+      cf[0] = cf[1] = fr[0]; cf[2] = fr[1]; cf[3] = cf[4] = fr[2];
+      double mix1 = m.geom_solmix[g1], mix2 = m.geom_solmix[g2], mix;
+      if (mix1 >= BP_MINVAL && mix2 >= BP_MINVAL) mix = mix1 / (mix1 + mix2);
+      else if (mix1 < BP_MINVAL && mix2 < BP_MINVAL) mix = 0.5;
+      else mix = mix1 < BP_MINVAL ? 0.0 : 1.0;
+      for (int k = 0; k < 2; k++)
+        DF(contact_solref)[2 * id + k] =
+            mix * m.geom_solref[2 * g1 + k] + (1 - mix) * m.geom_solref[2 * g2 + k];
+      for (int k = 0; k < 5; k++)
+        DF(contact_solimp)[5 * id + k] =
+            mix * m.geom_solimp[5 * g1 + k] + (1 - mix) * m.geom_solimp[5 * g2 + k];
+      IF(contact_exclude)[id] = raw[i].dist >= inc;
+      IF(contact_efc_address)[id] = -1;
+      DF(contact_mu)[id] = 0;
+    }
+    if (base > nconmax) break;    // uniform: every lane sees the same base
+  }
+  full = __any_sync(FULL, full);
+  if (c.lane == 0) {
+    *ncon_p = base < nconmax ? base : nconmax;
+    if (full) IF(warning)[W_CONTACTFULL]++;
+  }
+  SYNC();
+}
+
+#endif  // BP_COLLIDE_CUH_

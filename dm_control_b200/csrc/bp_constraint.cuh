@@ -1,0 +1,245 @@
+// mj_makeConstraint + reference acceleration: rows in the order friction loss,
+// joint limits, contacts.  Row slots come from
+// warp prefix sums so row ids are reproducible; Jacobian entries are produced one
+// (contact, dof) pair per lane using per-body dof-ancestry bit masks.
+#ifndef BP_CONSTRAINT_CUH_
+#define BP_CONSTRAINT_CUH_
+#include "bp_math.cuh"
+
+__device__ __forceinline__ int warp_excl_scan(int n, int lane, int* total) {
+  int incl = n;
+  for (int o = 1; o < 32; o <<= 1) {
+    int t = __shfl_up_sync(FULL, incl, o);
+    if (lane >= o) incl += t;
+  }
+  *total = __shfl_sync(FULL, incl, 31);
+  return incl - n;
+}
+
+__device__ __forceinline__ void bp_impedance(const double* si, double pos, double margin,
+                                             double* imp, double* impP) {
+  if (si[0] == si[1] || si[2] <= BP_MINVAL) { *imp = 0.5 * (si[0] + si[1]); *impP = 0; return; }
+  double x = (pos - margin) / si[2], sgn = 1;
+  if (x < 0) { x = -x; sgn = -1; }
+  if (x >= 1 || x <= 0) { *imp = x >= 1 ? si[1] : si[0]; *impP = 0; return; }
+  double y, yP, p = si[4], mid = si[3];
+  if (p == 1) { y = x; yP = 1; }
+  else if (x <= mid) {
+    double a = 1 / pow(mid, p - 1);
+    y = a * pow(x, p); yP = p * a * pow(x, p - 1);
+  } else {
+    double b = 1 / pow(1 - mid, p - 1);
+    y = 1 - b * pow(1 - x, p); yP = p * b * pow(1 - x, p - 1);
+  }
+  *imp = si[0] + y * (si[1] - si[0]);
+  *impP = yP * sgn * (si[1] - si[0]) / si[2];
+}
+
+__device__ __forceinline__ void bp_row_header(const Ctx& c, int r, int type, int id,
+                                              double pos, double margin, double floss) {
+  IF(efc_type)[r] = type; IF(efc_id)[r] = id;
+  DF(efc_pos)[r] = pos; DF(efc_margin)[r] = margin; DF(efc_frictionloss)[r] = floss;
+}
+
+__device__ void bp_make_constraint(const Ctx& c) {
+  const BpModel& m = c.P.m;
+  const int nv = m.nv, nvp = m.nvp, njmax = c.P.L.njmax;
+  double* J = DF(efc_J);
+  if (c.lane == 0) { *IF(nefc) = 0; *IF(ne) = 0; *IF(nf) = 0; }
+  SYNC();
+  if (m.opt_disableflags & DSBL_CONSTRAINT) return;
+  int base = 0, nf = 0;
+  // ---- pass 1: headers + slots -------------------------------------------------
+  if (!(m.opt_disableflags & DSBL_FRICTIONLOSS)) {
+    for (int k = c.lane; k < m.nfric; k += 32) {
+      int r = base + k, i = m.fric_dof[k];
+      if (r < njmax) bp_row_header(c, r, CN_FRICTION_DOF, i, 0, 0, m.dof_frictionloss[i]);
+    }
+    base += m.nfric;
+    nf = base < njmax ? base : njmax;
+  }
+  int lim_base = base;
+  if (!(m.opt_disableflags & DSBL_LIMIT)) {
+    for (int k0 = 0; k0 < m.nlim; k0 += 32) {
+      int k = k0 + c.lane, n = 0, j = 0;
+      double dist[2] = {0, 0}, margin = 0;
+      bool on[2] = {false, false};
+      if (k < m.nlim) {
+        j = m.lim_jnt[k];
+        double q = DF(qpos)[m.jnt_qposadr[j]];
+        margin = m.jnt_margin[j];
+        dist[0] = -(m.jnt_range[2 * j] - q);        // side = -1: lower bound
+        dist[1] = m.jnt_range[2 * j + 1] - q;       // side = +1: upper bound
+        on[0] = dist[0] < margin; on[1] = dist[1] < margin;
+        n = on[0] + on[1];
+      }
+      int tot, start = base + warp_excl_scan(n, c.lane, &tot);
+      for (int s = 0; s < 2; s++)
+        if (on[s]) {
+          if (start < njmax) bp_row_header(c, start, CN_LIMIT_JOINT, j, dist[s], margin, 0);
+          start++;
+        }
+      base += tot;
+    }
+  }
+  int con_base = base, ncon = *IF(ncon);
+  const bool pyramidal = m.opt_cone == 0;
+  for (int c0 = 0; c0 < ncon; c0 += 32) {
+    int ci = c0 + c.lane, n = 0, dim = 0;
+    if (ci < ncon && !IF(contact_exclude)[ci]) {
+      dim = IF(contact_dim)[ci];
+      n = dim == 1 ? 1 : (pyramidal ? 2 * (dim - 1) : dim);
+    }
+    int tot, start = base + warp_excl_scan(n, c.lane, &tot);
+    if (ci < ncon) {
+      int adr = (n > 0 && start < njmax) ? start : -1;
+      IF(contact_efc_address)[ci] = adr;
+      int type = dim == 1 ? CN_CONTACT_FRICTIONLESS
+                          : (pyramidal ? CN_CONTACT_PYRAMIDAL : CN_CONTACT_ELLIPTIC);
+      double dist = DF(contact_dist)[ci], inc = DF(contact_includemargin)[ci];
+      for (int k = 0; k < n; k++)
+        if (start + k < njmax) bp_row_header(c, start + k, type, ci, dist, inc, 0);
+    }
+    base += tot;
+  }
+  int nefc = base < njmax ? base : njmax;
+  if (c.lane == 0) {
+    *IF(nefc) = nefc; *IF(nf) = nf;
+    if (base > njmax) IF(warning)[W_CNSTRFULL]++;
+  }
+  SYNC();
+  // ---- pass 2: Jacobian ----------------------------------------------------------
+  for (int w = c.lane; w < nefc * nvp; w += 32) J[w] = 0;
+  SYNC();
+  for (int r = c.lane; r < lim_base && r < nefc; r += 32) J[r * nvp + IF(efc_id)[r]] = 1;
+  // limit rows: sign of the Jacobian entry is -side; recompute side from the slot
+  // order (lower bound first).  A joint with both sides active owns two adjacent rows.
+  for (int r = lim_base + c.lane; r < con_base && r < nefc; r += 32) {
+    int j = IF(efc_id)[r];
+    double q = DF(qpos)[m.jnt_qposadr[j]];
+    bool lower_on = -(m.jnt_range[2 * j] - q) < m.jnt_margin[j];
+    bool first = (r == lim_base) || IF(efc_id)[r - 1] != j;
+    int side = (lower_on && first) ? -1 : 1;
+    J[r * nvp + m.jnt_dofadr[j]] = -side;
+  }
+  const double *cdof = DF(cdof), *com = DF(subtree_com);
+  for (int w = c.lane; w < ncon * nv; w += 32) {
+    int ci = w / nv, i = w - ci * nv;
+    int a = IF(contact_efc_address)[ci];
+    if (a < 0) continue;
+    int b1 = m.geom_bodyid[IF(contact_geom1)[ci]], b2 = m.geom_bodyid[IF(contact_geom2)[ci]];
+    bool in1 = (m.body_dofmask[b1] >> i) & 1ull, in2 = (m.body_dofmask[b2] >> i) & 1ull;
+    if (!in1 && !in2) continue;          // column stays zero
+    const double* cd = cdof + 6 * i;
+    const double* pos = DF(contact_pos) + 3 * ci;
+    double dp[3] = {0, 0, 0}, dr[3] = {0, 0, 0};
+    if (in2) {
+      const double* cm = com + 3 * m.body_rootid[b2];
+      double off[3] = {pos[0] - cm[0], pos[1] - cm[1], pos[2] - cm[2]}, t[3];
+      cross3(t, cd, off);
+      for (int k = 0; k < 3; k++) { dp[k] = cd[3 + k] + t[k]; dr[k] = cd[k]; }
+    }
+    if (in1) {
+      const double* cm = com + 3 * m.body_rootid[b1];
+      double off[3] = {pos[0] - cm[0], pos[1] - cm[1], pos[2] - cm[2]}, t[3];
+      cross3(t, cd, off);
+      for (int k = 0; k < 3; k++) { dp[k] -= cd[3 + k] + t[k]; dr[k] -= cd[k]; }
+    }
+    const double* fr = DF(contact_frame) + 9 * ci;
+    double Jc[6];
+    for (int k = 0; k < 3; k++) { Jc[k] = dot3(fr + 3 * k, dp); Jc[3 + k] = dot3(fr + 3 * k, dr); }
+    int dim = IF(contact_dim)[ci];
+    if (dim == 1) J[a * nvp + i] = Jc[0];
+    else if (pyramidal) {
+      for (int k = 1; k < dim; k++) {
+        double mu = DF(contact_friction)[5 * ci + k - 1];
+        int r = a + 2 * (k - 1);
+        if (r < nefc) J[r * nvp + i] = Jc[0] + mu * Jc[k];
+        if (r + 1 < nefc) J[(r + 1) * nvp + i] = Jc[0] - mu * Jc[k];
+      }
+    } else {
+      for (int k = 0; k < dim; k++)
+        if (a + k < nefc) J[(a + k) * nvp + i] = Jc[k];
+    }
+  }
+  SYNC();
+  // ---- pass 3: per-row solver parameters -----------------------------------------
+  const double dt = m.opt_timestep;
+  for (int r = c.lane; r < nefc; r += 32) {
+    int type = IF(efc_type)[r], id = IF(efc_id)[r];
+    const double *solref, *solimp;
+    double dA;
+    if (type == CN_FRICTION_DOF) {
+      solref = m.dof_solref + 2 * id; solimp = m.dof_solimp + 5 * id;
+      dA = m.dof_invweight0[id];
+    } else if (type == CN_LIMIT_JOINT) {
+      solref = m.jnt_solref + 2 * id; solimp = m.jnt_solimp + 5 * id;
+      dA = m.dof_invweight0[m.jnt_dofadr[id]];
+    } else {
+      solref = DF(contact_solref) + 2 * id; solimp = DF(contact_solimp) + 5 * id;
+      int b1 = m.geom_bodyid[IF(contact_geom1)[id]], b2 = m.geom_bodyid[IF(contact_geom2)[id]];
+      double tran = m.body_invweight0[2 * b1] + m.body_invweight0[2 * b2];
+      double rot = m.body_invweight0[2 * b1 + 1] + m.body_invweight0[2 * b2 + 1];
+      int k = r - IF(contact_efc_address)[id];
+      if (type == CN_CONTACT_FRICTIONLESS) dA = tran;
+      else if (type == CN_CONTACT_PYRAMIDAL) {
+        double fri = DF(contact_friction)[5 * id + k / 2];
+        dA = tran + fri * fri * (k < 4 ? tran : rot);
+      } else dA = k < 3 ? tran : rot;
+    }
+    DF(efc_diagApprox)[r] = dA;
+    double sr0 = solref[0], sr1 = solref[1];
+    if (!(m.opt_disableflags & DSBL_REFSAFE) && sr0 > 0 && sr0 < 2 * dt) sr0 = 2 * dt;
+    double imp, impP;
+    bp_impedance(solimp, DF(efc_pos)[r], DF(efc_margin)[r], &imp, &impP);
+    imp = clampd(imp, 0.0001, 0.9999);
+    DF(efc_R)[r] = fmax(BP_MINVAL, (1 - imp) * dA / imp);
+    double dmax = clampd(solimp[1], 0.0001, 0.9999), K, B;
+    if (type == CN_FRICTION_DOF) { K = 0; B = 0; }
+    else if (sr0 > 0) {
+      K = 1 / fmax(BP_MINVAL, dmax * dmax * sr0 * sr0 * sr1 * sr1);
+      B = 2 / fmax(BP_MINVAL, dmax * sr0);
+    } else { K = -sr0 / fmax(BP_MINVAL, dmax * dmax); B = -sr1 / fmax(BP_MINVAL, dmax); }
+    double* kb = DF(efc_KBIP) + 4 * r;
+    kb[0] = K; kb[1] = B; kb[2] = imp; kb[3] = impP;
+  }
+  SYNC();
+  for (int ci = c.lane; ci < ncon; ci += 32) {
+    int a = IF(contact_efc_address)[ci], dim = IF(contact_dim)[ci];
+    if (a < 0 || dim == 1) continue;
+    double* R = DF(efc_R);
+    const double* f = DF(contact_friction) + 5 * ci;
+    if (pyramidal) {
+      double mu = f[0] / sqrt(m.opt_impratio);
+      DF(contact_mu)[ci] = mu;
+      double Rpy = 2 * mu * mu * R[a];
+      for (int k = 0; k < 2 * (dim - 1); k++) if (a + k < nefc) R[a + k] = Rpy;
+    } else {
+      if (a + 1 < nefc) R[a + 1] = R[a] / fmax(BP_MINVAL, m.opt_impratio);
+      double R1 = a + 1 < nefc ? R[a + 1] : R[a];
+      DF(contact_mu)[ci] = f[0] * sqrt(R1 / R[a]);
+      for (int k = 2; k < dim; k++)
+        if (a + k < nefc) R[a + k] = R1 * f[0] * f[0] / (f[k - 1] * f[k - 1]);
+    }
+  }
+  SYNC();
+  for (int r = c.lane; r < nefc; r += 32) DF(efc_D)[r] = 1 / DF(efc_R)[r];
+  SYNC();
+}
+
+// efc_vel = J qvel, efc_aref = -B vel - K imp (pos - margin)
+__device__ void bp_reference_constraint(const Ctx& c) {
+  const BpModel& m = c.P.m;
+  const int nv = m.nv, nvp = m.nvp, nefc = *IF(nefc);
+  const double *J = DF(efc_J), *qvel = DF(qvel);
+  for (int r = c.lane; r < nefc; r += 32) {
+    double v = 0;
+    for (int i = 0; i < nv; i++) v += J[r * nvp + i] * qvel[i];
+    DF(efc_vel)[r] = v;
+    const double* kb = DF(efc_KBIP) + 4 * r;
+    DF(efc_aref)[r] = -kb[1] * v - kb[0] * kb[2] * (DF(efc_pos)[r] - DF(efc_margin)[r]);
+  }
+  SYNC();
+}
+
+#endif  // BP_CONSTRAINT_CUH_

@@ -1,0 +1,167 @@
+"""Shared helpers of the GPU-vs-oracle parity tests (test infrastructure).
+
+States are seeded with numpy so that both sides see identical inputs; the oracle
+(oracle/mjstep_oracle.c) is the checker, the CUDA path behind include/bphys.h is
+the thing checked.
+"""
+
+import os
+
+import numpy as np
+
+from dm_control_b200.model import FlatModel, JNT_FREE, JNT_BALL
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+MODELS = os.path.join(ROOT, "dm_control_b200", "suite", "models")
+
+# fields that exist on both sides, by dtype
+F64_FIELDS = ["qpos", "qvel", "act", "qacc", "qacc_warmstart", "act_dot", "time",
+              "energy", "xpos", "xquat", "xmat", "xipos", "ximat", "xanchor",
+              "xaxis", "geom_xpos", "geom_xmat", "site_xpos", "site_xmat",
+              "subtree_com", "cinert", "cdof", "cdof_dot", "cvel", "crb", "qM", "qLD",
+              "qLDiagInv", "qfrc_bias", "qfrc_passive", "qfrc_actuator",
+              "qfrc_smooth", "qacc_smooth", "qfrc_constraint", "actuator_length",
+              "actuator_velocity", "actuator_force", "sensordata", "cacc",
+              "cfrc_int", "cfrc_ext", "subtree_linvel"]
+EFC_F64 = ["efc_pos", "efc_margin", "efc_frictionloss", "efc_diagApprox", "efc_D",
+           "efc_R", "efc_vel", "efc_aref", "efc_force"]
+EFC_I32 = ["efc_type", "efc_id", "efc_state"]
+CON_F64 = [("contact_dist", 1), ("contact_pos", 3), ("contact_frame", 9)]
+CON_I32 = ["contact_geom1", "contact_geom2", "contact_dim", "contact_efc_address"]
+INT_SCALARS = ["ncon", "nefc", "nf", "solver_iter", "warning"]
+
+
+def load_model(domain):
+  return FlatModel.load(os.path.join(MODELS, domain + ".npz"))
+
+
+def random_states(m, nenv, seed, vel_scale=1.0, spread=1.0):
+  """Seeded (qpos, qvel, ctrl) covering joint limits, contacts and free bodies."""
+  rng = np.random.RandomState(seed)
+  qpos = np.tile(m.qpos0, (nenv, 1))
+  for j in range(m.njnt):
+    jt, qa = m.jnt_type[j], m.jnt_qposadr[j]
+    if jt == JNT_FREE:
+      qpos[:, qa:qa + 2] += rng.uniform(-.5, .5, (nenv, 2))
+      qpos[:, qa + 2] = rng.uniform(0.1, 1.6, nenv)
+      q = rng.randn(nenv, 4)
+      qpos[:, qa + 3:qa + 7] = q / np.linalg.norm(q, axis=1, keepdims=True)
+    elif jt == JNT_BALL:
+      q = rng.randn(nenv, 4)
+      qpos[:, qa:qa + 4] = q / np.linalg.norm(q, axis=1, keepdims=True)
+    elif m.jnt_limited[j]:
+      lo, hi = m.jnt_range[j]
+      w = (hi - lo) * 0.05            # a little beyond the limits: active limit rows
+      qpos[:, qa] = rng.uniform(lo - w, hi + w, nenv)
+    else:
+      qpos[:, qa] += spread * rng.uniform(-1.0, 1.0, nenv)
+  qvel = vel_scale * rng.randn(nenv, m.nv)
+  ctrl = rng.uniform(-1, 1, (nenv, m.nu))
+  return qpos, qvel, ctrl
+
+
+def rel_err(a, b):
+  """max |a-b| scaled by the magnitude of the reference array b (>= 1e-12)."""
+  a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
+  if a.size == 0:
+    return 0.0
+  if not (np.all(np.isfinite(a)) and np.all(np.isfinite(b))):
+    return np.inf
+  return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-6))
+
+
+class Comparison:
+  """Accumulates per-field worst errors over envs and steps."""
+
+  def __init__(self):
+    self.f64 = {}
+    self.int_mismatch = {}
+
+  def add_f64(self, name, a, b):
+    self.f64[name] = max(self.f64.get(name, 0.0), rel_err(a, b))
+
+  def add_int(self, name, a, b):
+    bad = int(np.sum(np.asarray(a) != np.asarray(b)))
+    self.int_mismatch[name] = self.int_mismatch.get(name, 0) + bad
+
+  def worst(self):
+    return max(self.f64.values()) if self.f64 else 0.0
+
+  def report(self):
+    lines = ["  %-22s %.3e" % (k, v) for k, v in sorted(self.f64.items(),
+                                                        key=lambda kv: -kv[1])]
+    lines += ["  %-22s %d mismatches" % (k, v) for k, v in
+              sorted(self.int_mismatch.items())]
+    return "\n".join(lines)
+
+
+def compare_env(cmp, m, oracle, gpu, e, nvp, skip=()):
+  """Compares every shared field of env `e` (gpu: dict name -> [nenv, n])."""
+  nv = m.nv
+  for name in F64_FIELDS:
+    if name in skip:
+      continue
+    cmp.add_f64(name, gpu[name][e], getattr(oracle, name))
+  for name in INT_SCALARS:
+    cmp.add_int(name, gpu[name][e], getattr(oracle, name))
+  nefc, ncon = int(oracle.nefc[0]), int(oracle.ncon[0])
+  if int(gpu["nefc"][e, 0]) == nefc and int(gpu["ncon"][e, 0]) == ncon:
+    for name in EFC_F64:
+      cmp.add_f64(name, gpu[name][e, :nefc], getattr(oracle, name)[:nefc])
+    for name in EFC_I32:
+      cmp.add_int(name, gpu[name][e, :nefc], getattr(oracle, name)[:nefc])
+    gj = gpu["efc_J"][e].reshape(-1, nvp)[:nefc, :nv]
+    cmp.add_f64("efc_J", gj, oracle.efc_J[:nefc * nv].reshape(nefc, nv))
+    for name, w in CON_F64:
+      cmp.add_f64(name, gpu[name][e, :ncon * w], getattr(oracle, name)[:ncon * w])
+    for name in CON_I32:
+      cmp.add_int(name, gpu[name][e, :ncon], getattr(oracle, name)[:ncon])
+
+
+def run_parity(domain, nenv=32, nsteps=3, seed=0, njmax=0, nconmax=0, check_steps=None,
+               vel_scale=1.0, spread=1.0, mutate=None):
+  """forward() then `nsteps` Physics.step() on both sides; returns (Comparison per
+  phase, stats).  The GPU side goes through the C ABI (dm_control_b200.binding)."""
+  from dm_control_b200 import binding
+  from oracle.oracle_py import Oracle, OracleModel
+  m = load_model(domain)
+  if mutate:
+    mutate(m)
+  qpos, qvel, ctrl = random_states(m, nenv, seed, vel_scale, spread)
+  model = binding.Model(m)
+  batch = binding.Batch(model, nenv, njmax, nconmax)
+  nvp = m.nv | 1
+  batch.write("qpos", qpos); batch.write("qvel", qvel); batch.write("ctrl", ctrl)
+  om = OracleModel(m)
+  oracles = []
+  for e in range(nenv):
+    o = Oracle(om)
+    o.reset()
+    o.qpos[:] = qpos[e]; o.qvel[:] = qvel[e]; o.ctrl[:] = ctrl[e]
+    oracles.append(o)
+  names = (F64_FIELDS + EFC_F64 + EFC_I32 + ["efc_J"] + [n for n, _ in CON_F64] +
+           CON_I32 + INT_SCALARS)
+  out = {}
+  check_steps = set(range(nsteps + 1)) if check_steps is None else set(check_steps)
+  stats = {"ncon": [], "nefc": [], "iter": []}
+  for step in range(nsteps + 1):
+    if step == 0:
+      batch.forward()
+      for o in oracles:
+        o.forward()
+    else:
+      batch.step(1)
+      for o in oracles:
+        o.step()
+    if step in check_steps:
+      batch.sync()
+      gpu = {n: batch.read(n) for n in names}
+      cmp = Comparison()
+      for e, o in enumerate(oracles):
+        compare_env(cmp, m, o, gpu, e, nvp)
+      out[step] = cmp
+      stats["ncon"].append(float(np.mean(gpu["ncon"])))
+      stats["nefc"].append(float(np.mean(gpu["nefc"])))
+      stats["iter"].append(float(np.mean(gpu["solver_iter"])))
+  batch.free(); model.free()
+  return out, stats

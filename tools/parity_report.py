@@ -1,0 +1,38 @@
+"""Prints per-field GPU-vs-oracle errors for the suite models (run on a GPU box)."""
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+import parity_util as PU   # noqa: E402
+
+
+def main():
+  domains = sys.argv[1:] or ["pendulum", "cartpole", "acrobot", "cheetah", "walker",
+                             "hopper", "humanoid"]
+  os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+  with open(os.path.join(ROOT, "gpurun_out", "parity_report.txt"), "w") as f:
+    for d in domains:
+      t = time.time()
+      kw = dict(njmax=120, nconmax=40) if d == "humanoid" else {}
+      try:
+        res, stats = PU.run_parity(d, nenv=64, nsteps=20, seed=1,
+                                   check_steps=[0, 1, 2, 5, 10, 20], **kw)
+      except Exception as e:   # keep going: this is a report, not a test
+        msg = "%s: FAILED %r" % (d, e)
+        print(msg); f.write(msg + "\n")
+        continue
+      for step, cmp in sorted(res.items()):
+        bad_int = {k: v for k, v in cmp.int_mismatch.items() if v}
+        msg = "%s step %d worst %.3e int-mismatch %s" % (d, step, cmp.worst(), bad_int)
+        print(msg); f.write(msg + "\n")
+        f.write(cmp.report() + "\n")
+      msg = "%s stats %s (%.1fs)" % (d, stats, time.time() - t)
+      print(msg); f.write(msg + "\n")
+      f.flush()
+
+
+if __name__ == "__main__":
+  main()
