@@ -1,0 +1,368 @@
+"""Headline benchmark: env-steps/sec of suite tasks through the batched backend.
+
+  python bench.py --gpus N --steps K --warmup W            # this repo, N GPUs
+  python bench.py --impl reference --steps K --warmup W    # CPU arm (see below)
+
+One "step" = one `Environment.step` for every environment of the batch: copy of the
+step's actions into the images, `n_sub_steps` physics steps in ONE kernel launch
+(engine.py:149-166 inside rl/control.py:100-106) and the task's observation/reward
+kernel.  Workload at every N: cheetah-run at 16384 envs per GPU (BASELINE.json
+configs[2]; weak scaling, no per-step collective); humanoid-run at 8192 envs per GPU
+(configs[3]) is reported in "extra".
+
+The reference's own engine (MuJoCo 2.00) is a closed binary that is absent here
+(SURVEY.md §0.2), so the reference arm and `cpu_baseline` time the CPU oracle port
+(oracle/mjstep_oracle.c) on all host threads: kind "port".
+"""
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from dm_control_b200.model import FlatModel   # noqa: E402
+from dm_control_b200.suite import tasks as T   # noqa: E402
+
+MODELS = os.path.join(ROOT, "dm_control_b200", "suite", "models")
+# algorithmic bytes per env-step (state + obs I/O) and the contract
+# estimate v0 of fp64 flops per physics sub-step.
+ALGO = {"cheetah": dict(bytes=648, flops=2.0e4), "humanoid": dict(bytes=2048, flops=2.3e5),
+        "walker": dict(bytes=704, flops=1.8e4), "cartpole": dict(bytes=176, flops=1.0e4),
+        "acrobot": dict(bytes=184, flops=1.0e4), "pendulum": dict(bytes=112, flops=1.5e3)}
+WORKLOADS = {"cheetah-run": dict(nenv=16384, njmax=64, nconmax=16, settle=200),
+             "humanoid-run": dict(nenv=8192, njmax=120, nconmax=40, settle=100),
+             "walker-walk": dict(nenv=16384, njmax=48, nconmax=12, settle=50),
+             "cartpole-swingup": dict(nenv=4096, njmax=4, nconmax=1, settle=0),
+             "acrobot-swingup": dict(nenv=4096, njmax=1, nconmax=1, settle=0),
+             "pendulum-swingup": dict(nenv=4096, njmax=1, nconmax=1, settle=0)}
+
+
+def load_task(name):
+  domain, task = name.split("-", 1)
+  tdef = T.REGISTRY[(domain, task)]
+  m = FlatModel.load(os.path.join(MODELS, tdef.model + ".npz"))
+  return tdef, m
+
+
+def initial_qpos(m, nenv, seed):
+  """Uniform in joint ranges for limited joints (cheetah.py:63-71 style)."""
+  rng = np.random.RandomState(seed)
+  qpos = np.tile(m.qpos0, (nenv, 1))
+  for j in range(m.njnt):
+    if m.jnt_type[j] >= 2 and m.jnt_limited[j]:
+      lo, hi = m.jnt_range[j]
+      qpos[:, m.jnt_qposadr[j]] = rng.uniform(lo, hi, nenv)
+  return qpos
+
+
+class ClockSampler:
+  """nvidia-smi clocks + throttle reasons during the timed region."""
+  Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+       "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+       "clocks_event_reasons.sw_power_cap")
+
+  def __init__(self, index):
+    self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+    try:
+      self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                 "--format=csv,noheader,nounits", "-lms", "100"],
+                                stdout=self.f, stderr=subprocess.DEVNULL)
+    except OSError:
+      self.p = None
+
+  def stop(self):
+    if self.p is None:
+      return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+    time.sleep(0.15)
+    self.p.terminate(); self.p.wait()
+    self.f.flush(); self.f.seek(0)
+    sm, mx, reasons = [], [], set()
+    names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    for line in self.f:
+      parts = [x.strip() for x in line.split(",")]
+      if len(parts) < 6:
+        continue
+      try:
+        sm.append(float(parts[0])); mx.append(float(parts[1]))
+      except ValueError:
+        continue
+      for n, v in zip(names, parts[2:6]):
+        if v.lower().startswith("active"):
+          reasons.add(n)
+    self.f.close(); os.unlink(self.f.name)
+    return {"sm_mhz": float(np.median(sm)) if sm else None,
+            "sm_max_mhz": float(np.max(mx)) if mx else None, "reasons": sorted(reasons)}
+
+
+def make_batch(name, nenv, device, seed):
+  from dm_control_b200 import binding
+  w = WORKLOADS[name]
+  tdef, m = load_task(name)
+  model = binding.Model(m, device)
+  batch = binding.Batch(model, nenv, w["njmax"], w["nconmax"])
+  ip, fp = tdef.params(m)
+  batch.set_task(tdef.kind, ip, fp)
+  batch.write("qpos", initial_qpos(m, nenv, seed))
+  batch.forward(disable_actuation=True)
+  nsub = T.n_sub_steps(tdef, m)
+  return tdef, m, model, batch, nsub
+
+
+def run_gpu(name, nenv, steps, warmup, rank, world, device):
+  import torch
+  from dm_control_b200 import binding
+  tdef, m, model, batch, nsub = make_batch(name, nenv, device, seed=1000 + rank)
+  stream = torch.cuda.ExternalStream(batch.stream, device=device)
+  nu, nobs = m.nu, batch.nobs
+  gen = torch.Generator(device="cuda:%d" % device); gen.manual_seed(rank)
+  total = steps + warmup
+  ctrl = (torch.rand((total, nenv, nu), generator=gen, device="cuda:%d" % device,
+                     dtype=torch.float64) * 2 - 1)
+  obs = torch.empty((nenv, nobs), device="cuda:%d" % device, dtype=torch.float64)
+  rew = torch.empty((nenv,), device="cuda:%d" % device, dtype=torch.float64)
+  torch.cuda.synchronize(device)
+
+  def env_step(k):
+    batch.copy_from_device("ctrl", ctrl[k].data_ptr())
+    batch.step(nsub)
+    batch.obs_reward(obs.data_ptr(), rew.data_ptr())
+
+  # settle: the task's own warm-up of the physics (e.g. cheetah.py:73-75), untimed
+  settle = WORKLOADS[name]["settle"]
+  for k in range(settle):
+    batch.copy_from_device("ctrl", ctrl[k % total].data_ptr())
+    batch.step(1 if name.startswith("cheetah") else nsub)
+  for k in range(warmup):
+    env_step(k)
+  batch.sync()
+
+  def barrier():
+    if world > 1:
+      torch.distributed.barrier()
+    torch.cuda.synchronize(device)
+
+  # ---- device-resident timing (value) ---------------------------------------------
+  ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+  kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+         for _ in range(steps)]
+  sampler = ClockSampler(device) if rank == 0 else None
+  barrier()
+  ev[0].record(stream)
+  for k in range(steps):
+    batch.copy_from_device("ctrl", ctrl[warmup + k].data_ptr())
+    kev[k][0].record(stream)
+    batch.step(nsub)
+    kev[k][1].record(stream)
+    batch.obs_reward(obs.data_ptr(), rew.data_ptr())
+  ev[1].record(stream)
+  batch.sync()
+  barrier()
+  ms_total = ev[0].elapsed_time(ev[1])
+  ms_kernel = float(np.mean([a.elapsed_time(b) for a, b in kev]))
+  clocks = sampler.stop() if sampler else None
+
+  # ---- end to end through the C ABI with pinned host buffers (e2e) ----------------------
+  h_ctrl = torch.empty((nenv, nu), dtype=torch.float64).pin_memory()
+  h_obs = torch.empty((nenv, nobs), dtype=torch.float64).pin_memory()
+  h_rew = torch.empty((nenv,), dtype=torch.float64).pin_memory()
+  rng = np.random.RandomState(7 + rank)
+  acts = rng.uniform(-1, 1, (steps + 2, nenv, nu))
+  hc, ho, hr = h_ctrl.numpy(), h_obs.numpy(), h_rew.numpy()
+  for k in range(2):
+    hc[:] = acts[k]
+    batch.env_step_host(nsub, hc, ho, hr)
+  barrier()
+  t0 = time.perf_counter()
+  for k in range(steps):
+    hc[:] = acts[2 + k]
+    batch.env_step_host(nsub, hc, ho, hr)
+  torch.cuda.synchronize(device)
+  e2e_s = time.perf_counter() - t0
+  barrier()
+  warn = batch.warnings().sum(axis=0)
+  finite = bool(np.all(np.isfinite(ho)) and np.all(np.isfinite(hr)))
+  stats = dict(ncon=float(batch.read("ncon").mean()), nefc=float(batch.read("nefc").mean()),
+               solver_iter=float(batch.read("solver_iter").mean()),
+               reward_mean=float(hr.mean()))
+  out = dict(ms_total=ms_total, ms_kernel=ms_kernel, e2e_s=e2e_s, nsub=nsub, nu=nu,
+             nobs=nobs, clocks=clocks, warnings=[int(x) for x in warn], finite=finite,
+             stats=stats, smem=batch.smem_bytes, stride=batch.stride)
+  batch.free(); model.free()
+  return out
+
+
+def cpu_run(name, nenv, steps, threads, seed=0):
+  """Times the oracle port on host threads: `steps` env-steps of `nenv` envs."""
+  from oracle import oracle_py
+  tdef, m = load_task(name)
+  nsub = T.n_sub_steps(tdef, m)
+  om = oracle_py.OracleModel(m)
+  rng = np.random.RandomState(seed)
+  qpos = initial_qpos(m, nenv, seed)
+  qvel = np.zeros((nenv, m.nv)); act = np.zeros((nenv, max(m.na, 1)))
+  warm = np.zeros((nenv, m.nv)); tm = np.zeros(nenv)
+  ctrl = rng.uniform(-1, 1, (steps, nenv, m.nu))
+  t0 = time.perf_counter()
+  oracle_py.run_batch(om, qpos, qvel, act, warm, tm, ctrl, steps, nsub, threads)
+  dt = time.perf_counter() - t0
+  return nenv * steps / dt, dt, nsub
+
+
+def cpu_baseline(name, budget_s=12.0):
+  threads = os.cpu_count() or 1
+  v, dt, _ = cpu_run(name, 8 * threads, 50, threads)          # calibration
+  nenv = 16 * threads
+  steps = int(max(50, min(2000, budget_s * v / nenv)))
+  v, dt, nsub = cpu_run(name, nenv, steps, threads, seed=1)
+  return {"value": v, "unit": "env-steps/s", "cores": threads, "kind": "port",
+          "sample": "%s: %d envs x %d env-steps (x%d physics sub-steps), %d pthreads, "
+                    "%.1f s" % (name, nenv, steps, nsub, threads, dt)}
+
+
+def reference_arm(args):
+  rank = int(os.environ.get("RANK", "0"))
+  if rank != 0:
+    return
+  name = args.task
+  threads = os.cpu_count() or 1
+  nenv = 16 * threads
+  # size one "step" (= one env-step of the sample batch) so the run stays short
+  v, _, nsub = cpu_run(name, nenv, 20, threads)
+  per_step = nenv / v
+  for _ in range(args.warmup):
+    cpu_run(name, nenv, 1, threads)
+  reps = max(1, int(0.5 / max(per_step, 1e-6)))               # >= 0.5 s per timed step
+  t0 = time.perf_counter()
+  for k in range(args.steps):
+    cpu_run(name, nenv, reps, threads, seed=k)
+  dt = time.perf_counter() - t0
+  value = nenv * reps * args.steps / dt
+  sample = ("%s: %d envs x %d env-steps per step (x%d sub-steps), %d pthreads"
+            % (name, nenv, reps, nsub, threads))
+  line = {"impl": "reference", "metric": "env-steps/sec (%s)" % name, "value": value,
+          "unit": "env-steps/s", "n_gpus": args.gpus, "steps": args.steps,
+          "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
+          "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+          "data": "synthetic",
+          "config": {"workload": sample, "note": "reference engine (MuJoCo 2.00) is a "
+                     "closed binary absent from the reference tree; CPU oracle port timed"},
+          "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": threads,
+                           "kind": "port", "sample": sample},
+          "e2e": {"value": value, "unit": "env-steps/s", "h2d_bytes_per_step": 0,
+                  "d2h_bytes_per_step": 0}}
+  print(json.dumps(line))
+
+
+def main():
+  ap = argparse.ArgumentParser()
+  ap.add_argument("--gpus", type=int, default=1)
+  ap.add_argument("--steps", type=int, default=20)
+  ap.add_argument("--warmup", type=int, default=5)
+  ap.add_argument("--impl", default="b200")
+  ap.add_argument("--task", default="cheetah-run")
+  ap.add_argument("--nenv", type=int, default=0, help="envs per GPU (0 = workload default)")
+  ap.add_argument("--no-extra", action="store_true")
+  ap.add_argument("--no-cpu", action="store_true")
+  args = ap.parse_args()
+  args.warmup = max(args.warmup, 3)
+  if args.impl == "reference":
+    return reference_arm(args)
+
+  import torch
+  rank = int(os.environ.get("RANK", "0"))
+  world = int(os.environ.get("WORLD_SIZE", "1"))
+  local = int(os.environ.get("LOCAL_RANK", "0"))
+  torch.cuda.set_device(local)
+  if world > 1:
+    torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+  def reduce_max(x):
+    if world == 1:
+      return x
+    t = torch.tensor([x], dtype=torch.float64, device="cuda:%d" % local)
+    torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    return float(t.item())
+
+  name = args.task
+  nenv = args.nenv or WORKLOADS[name]["nenv"]
+  r = run_gpu(name, nenv, args.steps, args.warmup, rank, world, local)
+  ms_total = reduce_max(r["ms_total"]); e2e_s = reduce_max(r["e2e_s"])
+  ms_kernel = reduce_max(r["ms_kernel"])
+  extra = {}
+  if not args.no_extra and name == "cheetah-run":
+    n2 = "humanoid-run"
+    r2 = run_gpu(n2, WORKLOADS[n2]["nenv"], args.steps, args.warmup, rank, world, local)
+    ms2 = reduce_max(r2["ms_total"]); e2 = reduce_max(r2["e2e_s"])
+    extra[n2] = {"value": WORKLOADS[n2]["nenv"] * world * args.steps / (ms2 * 1e-3),
+                 "e2e": WORKLOADS[n2]["nenv"] * world * args.steps / e2,
+                 "unit": "env-steps/s", "envs_per_gpu": WORKLOADS[n2]["nenv"],
+                 "n_sub_steps": r2["nsub"], "ms_per_step": ms2 / args.steps,
+                 "step_kernel_ms": reduce_max(r2["ms_kernel"]), "warnings": r2["warnings"],
+                 "finite": r2["finite"], "stats": r2["stats"], "smem_bytes_per_env": r2["smem"]}
+  if rank != 0:
+    if world > 1:
+      torch.distributed.destroy_process_group()
+    return
+  from dm_control_b200 import binding
+  domain = name.split("-")[0]
+  total_envs = nenv * world
+  value = total_envs * args.steps / (ms_total * 1e-3)
+  e2e = total_envs * args.steps / e2e_s
+  peaks = {}
+  try:
+    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+  except (OSError, ValueError):
+    pass
+  hbm_peak = peaks.get("hbm_gbs", 6650.0)
+  algo_bytes = ALGO[domain]["bytes"] * nenv
+  achieved = algo_bytes / (ms_kernel * 1e-3) / 1e9
+  fp64_peak = binding.fp64_peak_tflops(local)
+  fl = ALGO[domain]["flops"] * r["nsub"] * nenv / (ms_kernel * 1e-3) / 1e12
+  line = {
+      "metric": "env-steps/sec (%s)" % name, "value": value, "unit": "env-steps/s",
+      "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+      "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+      "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+      "config": {"workload": "%s, %d envs per GPU, random actions U(-1,1), %d physics "
+                             "sub-step(s) per env-step" % (name, nenv, r["nsub"]),
+                 "envs_per_gpu": nenv, "n_sub_steps": r["nsub"],
+                 "l2": "per-GPU image %.0f MB > 126 MB L2 (inputs larger than L2)"
+                       % (nenv * r["stride"] * 8 / 1e6),
+                 "smem_bytes_per_env": r["smem"]},
+      "e2e": {"value": e2e, "unit": "env-steps/s",
+              "h2d_bytes_per_step": nenv * r["nu"] * 8,
+              "d2h_bytes_per_step": nenv * (r["nobs"] + 1) * 8},
+      "gpu_launches": 2 * args.steps,
+      "clocks": r["clocks"],
+      "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                   "frac": achieved / hbm_peak, "traffic": None,
+                   "peak_source": "measured" if peaks else "fallback",
+                   "kernel": "bp_step_kernel", "kernel_ms": ms_kernel,
+                   "algorithmic_bytes_per_launch": algo_bytes,
+                   "image_bytes_per_launch": 2 * nenv * r["stride"] * 8},
+      "roofline_fp64": {"bound": "fp64 vector pipe", "achieved": fl, "peak": fp64_peak,
+                        "unit": "TFLOP/s", "frac": fl / fp64_peak,
+                        "flops_per_substep": ALGO[domain]["flops"],
+                        "note": "flops = SURVEY 8d contract estimate v0; peak = DFMA "
+                                "microbenchmark in this run"},
+      "physics_steps_per_s": value * r["nsub"],
+      "warnings": r["warnings"], "finite": r["finite"], "stats": r["stats"],
+      "extra": extra,
+  }
+  if world == 1 and not args.no_cpu:
+    line["cpu_baseline"] = cpu_baseline(name)
+  print(json.dumps(line))
+  if world > 1:
+    torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+  main()

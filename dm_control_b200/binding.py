@@ -49,6 +49,8 @@ _SIGNATURES = {
                              ctypes.POINTER(_i64), ctypes.POINTER(_i32)]),
     "bp_field_write": (_i32, [_vp, ctypes.c_char_p, _vp, _i64, _i64]),
     "bp_field_read": (_i32, [_vp, ctypes.c_char_p, _vp, _i64, _i64]),
+    "bp_field_copy_device": (_i32, [_vp, ctypes.c_char_p, _vp, _i32]),
+    "bp_fp64_peak": (_i32, [_i32, ctypes.POINTER(ctypes.c_double)]),
     "bp_set_mask": (_i32, [_vp, _vp]),
     "bp_step": (_i32, [_vp, _i32]),
     "bp_mj_step": (_i32, [_vp, _i32]),
@@ -81,6 +83,12 @@ def load():
       fn.restype, fn.argtypes = res, args
     _lib = L
   return _lib
+
+
+def fp64_peak_tflops(device=0):
+  out = ctypes.c_double()
+  check(load().bp_fp64_peak(device, ctypes.byref(out)))
+  return out.value
 
 
 def last_error():
@@ -187,6 +195,12 @@ class Batch:
       holder = _CudaArray(self.image_ptr, (self.nenv, self.stride), self)
       self._image = torch.as_tensor(holder, device="cuda:%d" % self.model.device)
     return self._image
+
+  def copy_from_device(self, name, dev_ptr):
+    check(load().bp_field_copy_device(self.ptr, name.encode(), dev_ptr, 1))
+
+  def copy_to_device(self, name, dev_ptr):
+    check(load().bp_field_copy_device(self.ptr, name.encode(), dev_ptr, 0))
 
   # ---- pipeline -------------------------------------------------------------------
   def set_mask(self, mask):

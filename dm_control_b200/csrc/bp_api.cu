@@ -410,6 +410,39 @@ extern "C" int bp_field_read(bp_batch* b, const char* name, void* host, int64_t 
   return field_copy(b, name, host, env0, n, false);
 }
 
+extern "C" int bp_field_copy_device(bp_batch* b, const char* name, void* dev, int to_image) {
+  if (!b || !name || !dev) return fail(BP_EINVAL, "null argument");
+  const FieldInfo* f = find_field(b, name);
+  if (!f) return fail(BP_ENOFIELD, std::string("no data field ") + name);
+  if (f->count == 0) return BP_OK;
+  cudaSetDevice(b->model->device);
+  size_t w = (size_t)f->count * (f->dtype == 0 ? 8 : 4), pitch = (size_t)b->L.persist * 8;
+  char* img = (char*)b->image + f->offset_bytes;
+  if (to_image)
+    CUDA_OK(cudaMemcpy2DAsync(img, pitch, dev, w, w, b->nenv, cudaMemcpyDeviceToDevice, b->stream));
+  else
+    CUDA_OK(cudaMemcpy2DAsync(dev, w, img, pitch, w, b->nenv, cudaMemcpyDeviceToDevice, b->stream));
+  return BP_OK;
+}
+
+extern "C" int bp_dfma_bench(int blocks, int threads, int iters, double* scratch, float* ms,
+                             cudaStream_t stream);
+extern "C" int bp_fp64_peak(int device, double* tflops) {
+  if (!tflops) return fail(BP_EINVAL, "null argument");
+  CUDA_OK(cudaSetDevice(device));
+  int sms = 0;
+  CUDA_OK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+  double* scratch = nullptr;
+  CUDA_OK(cudaMalloc((void**)&scratch, 64));
+  const int blocks = sms * 8, threads = 256, iters = 1 << 16;
+  float ms = 0;
+  int e = bp_dfma_bench(blocks, threads, iters, scratch, &ms, 0);
+  cudaFree(scratch);
+  if (e != 0) return fail(BP_ECUDA, std::string("dfma bench: ") + cudaGetErrorString((cudaError_t)e));
+  *tflops = (double)blocks * threads * iters * 8.0 * 2.0 / (ms * 1e-3) / 1e12;
+  return BP_OK;
+}
+
 extern "C" int bp_set_mask(bp_batch* b, const uint8_t* mask_host) {
   if (!b) return fail(BP_EINVAL, "null batch");
   cudaSetDevice(b->model->device);

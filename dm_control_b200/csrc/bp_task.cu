@@ -207,3 +207,32 @@ extern "C" int bp_launch_reset(const BpParams* P, const double* kq, const double
   bp_reset_kernel<<<(unsigned)P->nenv, 64, 0, stream>>>(*P, kq, kv, ka, kt);
   return (int)cudaGetLastError();
 }
+
+// FP64 vector-pipe saturation microbenchmark: the roofline denominator SURVEY.md §8d
+// asks for (MEASURED_PEAKS.json has no FP64 figure).  8 independent DFMA chains per
+// thread; returns the elapsed milliseconds of the timed launch.
+__global__ void bp_dfma_kernel(double* out, int iters) {
+  double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4,
+         a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+  const double x = 1.0000001, y = 1e-9;
+  for (int i = 0; i < iters; i++) {
+    a0 = fma(a0, x, y); a1 = fma(a1, x, y); a2 = fma(a2, x, y); a3 = fma(a3, x, y);
+    a4 = fma(a4, x, y); a5 = fma(a5, x, y); a6 = fma(a6, x, y); a7 = fma(a7, x, y);
+  }
+  double s = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+  if (s == 12345.678) out[0] = s;   // keeps the chains alive
+}
+
+extern "C" int bp_dfma_bench(int blocks, int threads, int iters, double* scratch,
+                             float* ms, cudaStream_t stream) {
+  cudaEvent_t a, b;
+  cudaEventCreate(&a); cudaEventCreate(&b);
+  bp_dfma_kernel<<<blocks, threads, 0, stream>>>(scratch, iters / 8);   // warm-up
+  cudaEventRecord(a, stream);
+  bp_dfma_kernel<<<blocks, threads, 0, stream>>>(scratch, iters);
+  cudaEventRecord(b, stream);
+  cudaError_t e = cudaEventSynchronize(b);
+  if (e == cudaSuccess) cudaEventElapsedTime(ms, a, b);
+  cudaEventDestroy(a); cudaEventDestroy(b);
+  return (int)e;
+}

@@ -1,0 +1,121 @@
+"""Registry of the suite tasks served by the device backend.
+
+Each entry restates the constants of the reference's task module
+(/root/reference/dm_control/suite/<domain>.py; lines cited per entry) and resolves
+the object ids its observation/reward kernel (csrc/bp_task.cu) needs by name, the
+way the reference resolves `named.data.*` keys (mujoco/index.py:436-510).
+"""
+
+import collections
+
+import numpy as np
+
+# task kinds of csrc/bp_task.cu
+NONE, CARTPOLE, ACROBOT, PENDULUM, CHEETAH, WALKER, HUMANOID = range(7)
+
+TaskDef = collections.namedtuple(
+    "TaskDef", "domain task model kind time_limit control_timestep params obs")
+
+
+def _sens_adr(m, name):
+  return int(m.sensor_adr[m.name2id(name, "sensor")])
+
+
+def _cartpole(sparse):
+  def f(m):
+    return [int(m.jnt_qposadr[m.name2id("slider", "joint")]), int(sparse)], []
+  return f
+
+
+def _acrobot(sparse):
+  def f(m):
+    tgt = m.name2id("target", "site")
+    return ([m.name2id("upper_arm", "body"), m.name2id("lower_arm", "body"), tgt,
+             m.name2id("tip", "site")],
+            [float(m.site_size[tgt, 0]), 0.0 if sparse else 1.0])
+  return f
+
+
+def _pendulum(m):
+  # suite/pendulum.py:31-33 _ANGLE_BOUND = 8 degrees
+  return ([m.name2id("pole", "body"), int(m.jnt_dofadr[m.name2id("hinge", "joint")])],
+          [float(np.cos(np.deg2rad(8)))])
+
+
+def _cheetah(m):
+  return [_sens_adr(m, "torso_subtreelinvel")], [10.0]      # cheetah.py:31 _RUN_SPEED
+
+
+def _walker(speed):
+  def f(m):
+    return [m.name2id("torso", "body"), _sens_adr(m, "torso_subtreelinvel")], [speed]
+  return f
+
+
+def _humanoid(speed):
+  def f(m):
+    ids = [m.name2id(n, "body") for n in
+           ("torso", "head", "left_hand", "left_foot", "right_hand", "right_foot")]
+    return ids + [_sens_adr(m, "torso_subtreelinvel")], [speed]
+  return f
+
+
+def _obs_cartpole(m):
+  return [("position", 1 + 2 * (m.nbody - 2)), ("velocity", m.nv)]
+
+
+_TASKS = [
+    # cartpole.py:30 time limit 10 s, no control_timestep (62-99)
+    TaskDef("cartpole", "swingup", "cartpole", CARTPOLE, 10, None, _cartpole(False), _obs_cartpole),
+    TaskDef("cartpole", "swingup_sparse", "cartpole", CARTPOLE, 10, None, _cartpole(True), _obs_cartpole),
+    TaskDef("cartpole", "balance", "cartpole", CARTPOLE, 10, None, _cartpole(False), _obs_cartpole),
+    TaskDef("cartpole", "balance_sparse", "cartpole", CARTPOLE, 10, None, _cartpole(True), _obs_cartpole),
+    # acrobot.py:28 time limit 10 s
+    TaskDef("acrobot", "swingup", "acrobot", ACROBOT, 10, None, _acrobot(False),
+            lambda m: [("orientations", 4), ("velocity", m.nv)]),
+    TaskDef("acrobot", "swingup_sparse", "acrobot", ACROBOT, 10, None, _acrobot(True),
+            lambda m: [("orientations", 4), ("velocity", m.nv)]),
+    # pendulum.py:29 time limit 20 s
+    TaskDef("pendulum", "swingup", "pendulum", PENDULUM, 20, None, _pendulum,
+            lambda m: [("orientation", 2), ("velocity", 1)]),
+    # cheetah.py:28 time limit 10 s
+    TaskDef("cheetah", "run", "cheetah", CHEETAH, 10, None, _cheetah,
+            lambda m: [("position", m.nq - 1), ("velocity", m.nv)]),
+    # walker.py:29-36: 25 s, control timestep .025, speeds 0 / 1 / 8
+    TaskDef("walker", "stand", "walker", WALKER, 25, .025, _walker(0.0),
+            lambda m: [("orientations", 2 * (m.nbody - 1)), ("height", 1), ("velocity", m.nv)]),
+    TaskDef("walker", "walk", "walker", WALKER, 25, .025, _walker(1.0),
+            lambda m: [("orientations", 2 * (m.nbody - 1)), ("height", 1), ("velocity", m.nv)]),
+    TaskDef("walker", "run", "walker", WALKER, 25, .025, _walker(8.0),
+            lambda m: [("orientations", 2 * (m.nbody - 1)), ("height", 1), ("velocity", m.nv)]),
+    # humanoid.py:28-35: 25 s, control timestep .025, speeds 0 / 1 / 10
+    TaskDef("humanoid", "stand", "humanoid", HUMANOID, 25, .025, _humanoid(0.0), None),
+    TaskDef("humanoid", "walk", "humanoid", HUMANOID, 25, .025, _humanoid(1.0), None),
+    TaskDef("humanoid", "run", "humanoid", HUMANOID, 25, .025, _humanoid(10.0), None),
+]
+
+
+def _obs_humanoid(m):
+  return [("joint_angles", m.nq - 7), ("head_height", 1), ("extremities", 12),
+          ("torso_vertical", 3), ("com_velocity", 3), ("velocity", m.nv)]
+
+
+REGISTRY = {}
+for _t in _TASKS:
+  if _t.obs is None:
+    _t = _t._replace(obs=_obs_humanoid)
+  REGISTRY[(_t.domain, _t.task)] = _t
+
+# (domain, task) pairs in the order of the reference's suite.BENCHMARKING subset we serve
+ALL_TASKS = tuple(sorted(REGISTRY))
+
+
+def n_sub_steps(tdef, m):
+  """rl/control.py:164-190 compute_n_steps."""
+  if tdef.control_timestep is None:
+    return 1
+  ratio = tdef.control_timestep / m.opt_timestep
+  if tdef.control_timestep < m.opt_timestep or abs(ratio - round(ratio)) > 1e-8:
+    raise ValueError("Control timestep ({}) must be an integer multiple of physics "
+                     "timestep ({})".format(tdef.control_timestep, m.opt_timestep))
+  return int(round(ratio))

@@ -73,6 +73,10 @@ int bp_field_info(bp_batch* b, const char* name, int64_t* offset_bytes, int64_t*
 int bp_field_write(bp_batch* b, const char* name, const void* host, int64_t env0, int64_t n);
 int bp_field_read(bp_batch* b, const char* name, void* host, int64_t env0, int64_t n);
 
+/* Device <-> image copy of one field: `dev` is a dense [nenv][count] device array
+ * (e.g. a torch tensor); asynchronous on the batch's stream. */
+int bp_field_copy_device(bp_batch* b, const char* name, void* dev, int to_image);
+
 /* Optional per-env mask (device or host bytes, nenv long; NULL = all envs): envs
  * whose byte is 0 are left untouched by the calls below. */
 int bp_set_mask(bp_batch* b, const uint8_t* mask_host);
@@ -110,6 +114,9 @@ int bp_env_step_host(bp_batch* b, int nsub, const double* ctrl_host, double* obs
  * [nenv][8] int32 copied to the host (synchronises). */
 int bp_warnings(bp_batch* b, int32_t* out_host);
 int bp_sync(bp_batch* b);
+/* DFMA saturation microbenchmark: measured FP64 vector peak of `device` in TFLOP/s
+ * (the roofline denominator the reference's FP64 pipeline is judged against). */
+int bp_fp64_peak(int device, double* tflops);
 void* bp_batch_stream(bp_batch* b);             /* cudaStream_t of the batch */
 /* milliseconds spent by the device in the last `n` bp_step-family launches is not
  * tracked here; time with CUDA events on bp_batch_stream(). */
