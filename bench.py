@@ -102,12 +102,15 @@ class ClockSampler:
             "sm_max_mhz": float(np.max(mx)) if mx else None, "reasons": sorted(reasons)}
 
 
+LANES = {"value": 0}
+
+
 def make_batch(name, nenv, device, seed):
   from dm_control_b200 import binding
   w = WORKLOADS[name]
   tdef, m = load_task(name)
   model = binding.Model(m, device)
-  batch = binding.Batch(model, nenv, w["njmax"], w["nconmax"])
+  batch = binding.Batch(model, nenv, w["njmax"], w["nconmax"], LANES["value"])
   ip, fp = tdef.params(m)
   batch.set_task(tdef.kind, ip, fp)
   batch.write("qpos", initial_qpos(m, nenv, seed))
@@ -194,7 +197,7 @@ def run_gpu(name, nenv, steps, warmup, rank, world, device):
                reward_mean=float(hr.mean()))
   out = dict(ms_total=ms_total, ms_kernel=ms_kernel, e2e_s=e2e_s, nsub=nsub, nu=nu,
              nobs=nobs, clocks=clocks, warnings=[int(x) for x in warn], finite=finite,
-             stats=stats, smem=batch.smem_bytes, stride=batch.stride)
+             stats=stats, smem=batch.smem_bytes, stride=batch.stride, lanes=batch.lanes)
   batch.free(); model.free()
   return out
 
@@ -269,10 +272,12 @@ def main():
   ap.add_argument("--impl", default="b200")
   ap.add_argument("--task", default="cheetah-run")
   ap.add_argument("--nenv", type=int, default=0, help="envs per GPU (0 = workload default)")
+  ap.add_argument("--lanes", type=int, default=0, help="GPU lanes per environment")
   ap.add_argument("--no-extra", action="store_true")
   ap.add_argument("--no-cpu", action="store_true")
   args = ap.parse_args()
   args.warmup = max(args.warmup, 3)
+  LANES["value"] = args.lanes
   if args.impl == "reference":
     return reference_arm(args)
 
@@ -336,7 +341,7 @@ def main():
                  "envs_per_gpu": nenv, "n_sub_steps": r["nsub"],
                  "l2": "per-GPU image %.0f MB > 126 MB L2 (inputs larger than L2)"
                        % (nenv * r["stride"] * 8 / 1e6),
-                 "smem_bytes_per_env": r["smem"]},
+                 "smem_bytes_per_env": r["smem"], "lanes_per_env": r["lanes"]},
       "e2e": {"value": e2e, "unit": "env-steps/s",
               "h2d_bytes_per_step": nenv * r["nu"] * 8,
               "d2h_bytes_per_step": nenv * (r["nobs"] + 1) * 8},

@@ -37,7 +37,9 @@ _SIGNATURES = {
     "bp_model_free": (None, [_vp]),
     "bp_model_set_field": (_i32, [_vp, ctypes.c_char_p, _vp, _i64]),
     "bp_model_get_field": (_i32, [_vp, ctypes.c_char_p, _vp, _i64]),
-    "bp_batch_create": (_vp, [_vp, _i64, _i32, _i32, ctypes.c_char_p, _i32]),
+    "bp_batch_create": (_vp, [_vp, _i64, _i32, _i32, _i32, ctypes.c_char_p, _i32]),
+    "bp_batch_lanes": (_i32, [_vp]),
+    "bp_batch_interleave": (_i32, [_vp]),
     "bp_batch_free": (None, [_vp]),
     "bp_batch_image": (_vp, [_vp]),
     "bp_batch_stride": (_i64, [_vp]),
@@ -140,17 +142,19 @@ class Model:
 class Batch:
   """`nenv` mjData images on the device (cf. `MjData`, wrapper/core.py:630-780)."""
 
-  def __init__(self, model, nenv, njmax=0, nconmax=0):
+  def __init__(self, model, nenv, njmax=0, nconmax=0, lanes=0):
     L = load()
     self.model = model
     err = ctypes.create_string_buffer(1000)
-    self.ptr = L.bp_batch_create(model.ptr, nenv, njmax, nconmax, err, len(err))
+    self.ptr = L.bp_batch_create(model.ptr, nenv, njmax, nconmax, lanes, err, len(err))
     if not self.ptr:
       raise Error(err.value.decode())
     self.nenv = nenv
     self.stride = L.bp_batch_stride(self.ptr)
     self.image_ptr = L.bp_batch_image(self.ptr)
     self.smem_bytes = L.bp_batch_smem_bytes(self.ptr)
+    self.lanes = L.bp_batch_lanes(self.ptr)
+    self.interleave = L.bp_batch_interleave(self.ptr)
     self.fields = {}
     for i in range(L.bp_field_count(self.ptr)):
       name = L.bp_field_name(self.ptr, i)
@@ -180,8 +184,11 @@ class Batch:
 
   # ---- zero-copy device views ---------------------------------------------------
   def view(self, name):
-    """torch view [nenv, count] of a field inside the image (no copy)."""
+    """torch view [nenv, count] of a field inside the image (no copy).  Only for
+    contiguous images (interleave == 1); use read_device() otherwise."""
     import torch
+    if self.interleave != 1:
+      raise Error("zero-copy views need a contiguous image (lanes > 1)")
     off, cnt, dt = self.fields[name]
     img = self.image_tensor()
     if dt == np.float64:
@@ -195,6 +202,16 @@ class Batch:
       holder = _CudaArray(self.image_ptr, (self.nenv, self.stride), self)
       self._image = torch.as_tensor(holder, device="cuda:%d" % self.model.device)
     return self._image
+
+  def read_device(self, name):
+    """Dense torch copy [nenv, count] of a field (works for every layout)."""
+    import torch
+    _, cnt, dt = self.fields[name]
+    out = torch.empty((self.nenv, cnt), device="cuda:%d" % self.model.device,
+                      dtype=torch.float64 if dt == np.float64 else torch.int32)
+    if cnt:
+      self.copy_to_device(name, out.data_ptr())
+    return out
 
   def copy_from_device(self, name, dev_ptr):
     check(load().bp_field_copy_device(self.ptr, name.encode(), dev_ptr, 1))

@@ -11,7 +11,15 @@
 #include "../../include/bphys.h"
 #include "bp_types.h"
 
-extern "C" int bp_launch_step(const BpParams* P, cudaStream_t stream);
+extern "C" int bp_launch_step_g32(const BpParams* P, cudaStream_t stream);
+extern "C" int bp_launch_step_g16(const BpParams* P, cudaStream_t stream);
+extern "C" int bp_launch_step_g8(const BpParams* P, cudaStream_t stream);
+extern "C" int bp_launch_step_g4(const BpParams* P, cudaStream_t stream);
+extern "C" int bp_launch_step_g2(const BpParams* P, cudaStream_t stream);
+extern "C" int bp_launch_step_g1(const BpParams* P, cudaStream_t stream);
+extern "C" int bp_launch_field_copy(const BpParams* P, long long off, int count, int is_int,
+                                    void* dense, long long env0, long long n, int to_image,
+                                    cudaStream_t stream);
 extern "C" int bp_launch_reset(const BpParams* P, const double* key_qpos,
                                const double* key_qvel, const double* key_act,
                                double key_time, cudaStream_t stream);
@@ -283,6 +291,10 @@ struct bp_batch {
   std::vector<FieldInfo> fields;
   double *ctrl_stage = nullptr, *obs_dev = nullptr, *rew_dev = nullptr;  // e2e staging
   int obs_cap = 0;
+  int lanes = 32, interleave = 1;
+  int64_t stride = 0, nenv_alloc = 0;
+  void* stage = nullptr;           // dense staging buffer for host <-> image copies
+  size_t stage_bytes = 0;
   BpTask task;
 };
 
@@ -310,7 +322,7 @@ static void make_layout(const BpModel& m, int njmax, int nconmax, BpLayout* L,
 }
 
 extern "C" bp_batch* bp_batch_create(bp_model* m, int64_t nenv, int njmax, int nconmax,
-                                     char* err, int errsz) {
+                                     int lanes, char* err, int errsz) {
   auto bail = [&](const std::string& msg) -> bp_batch* {
     g_err = msg;
     if (err && errsz > 0) snprintf(err, errsz, "%s", msg.c_str());
@@ -324,16 +336,24 @@ extern "C" bp_batch* bp_batch_create(bp_model* m, int64_t nenv, int njmax, int n
   b->model = m; b->nenv = nenv;
   memset(&b->task, 0, sizeof b->task);
   make_layout(m->M, njmax, nconmax, &b->L, &b->fields);
+  if (lanes <= 0) lanes = 32;
+  if (lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8 && lanes != 16 && lanes != 32) {
+    delete b; return bail("lanes per environment must be 1, 2, 4, 8, 16 or 32");
+  }
+  b->lanes = lanes;
+  b->interleave = lanes == 1 ? 32 : 1;
+  b->stride = lanes == 32 ? b->L.persist : b->L.total;
+  b->nenv_alloc = (nenv + 31) / 32 * 32;
   int maxsm = 0;
   cudaDeviceGetAttribute(&maxsm, cudaDevAttrMaxSharedMemoryPerBlockOptin, m->device);
-  if ((size_t)b->L.total * 8 > (size_t)maxsm) {
+  if (lanes == 32 && (size_t)b->L.total * 8 > (size_t)maxsm) {
     char msg[256];
     snprintf(msg, sizeof msg, "one environment needs %zu B of shared memory (njmax=%d, "
              "nconmax=%d) but an SM offers %d B: lower njmax/nconmax",
              (size_t)b->L.total * 8, njmax, nconmax, maxsm);
     delete b; return bail(msg);
   }
-  size_t bytes = (size_t)nenv * b->L.persist * 8;
+  size_t bytes = (size_t)b->nenv_alloc * b->stride * 8;
   if (cudaMalloc((void**)&b->image, bytes) != cudaSuccess ||
       cudaMalloc((void**)&b->mask, nenv) != cudaSuccess ||
       cudaStreamCreateWithFlags(&b->stream, cudaStreamNonBlocking) != cudaSuccess) {
@@ -355,13 +375,16 @@ extern "C" void bp_batch_free(bp_batch* b) {
   if (b->stream) { cudaStreamSynchronize(b->stream); cudaStreamDestroy(b->stream); }
   cudaFree(b->image); cudaFree(b->mask);
   if (b->ctrl_stage) cudaFree(b->ctrl_stage);
+  if (b->stage) cudaFree(b->stage);
   if (b->obs_dev) cudaFree(b->obs_dev);
   if (b->rew_dev) cudaFree(b->rew_dev);
   delete b;
 }
 
 extern "C" void* bp_batch_image(bp_batch* b) { return b ? b->image : nullptr; }
-extern "C" int64_t bp_batch_stride(bp_batch* b) { return b ? b->L.persist : 0; }
+extern "C" int64_t bp_batch_stride(bp_batch* b) { return b ? b->stride : 0; }
+extern "C" int bp_batch_lanes(bp_batch* b) { return b ? b->lanes : 0; }
+extern "C" int bp_batch_interleave(bp_batch* b) { return b ? b->interleave : 0; }
 extern "C" int64_t bp_batch_nenv(bp_batch* b) { return b ? b->nenv : 0; }
 extern "C" int64_t bp_batch_smem_bytes(bp_batch* b) { return b ? (int64_t)b->L.total * 8 : 0; }
 extern "C" void* bp_batch_stream(bp_batch* b) { return b ? (void*)b->stream : nullptr; }
@@ -384,6 +407,19 @@ extern "C" int bp_field_info(bp_batch* b, const char* name, int64_t* off, int64_
   return BP_OK;
 }
 
+static BpParams make_params(bp_batch* b, int mode, int nsub, int disable_actuation);
+
+// dense [n][count] device buffer <-> the field inside the (possibly interleaved) image
+static int field_copy_dev(bp_batch* b, const FieldInfo* f, void* dense, int64_t env0, int64_t n,
+                          bool to_image) {
+  BpParams P = make_params(b, 0, 0, 0);
+  long long off = f->dtype == 0 ? f->offset_bytes / 8 : (f->offset_bytes - (int64_t)b->L.ints * 8) / 4;
+  int e = bp_launch_field_copy(&P, off, (int)f->count, f->dtype, dense, env0, n, to_image ? 1 : 0,
+                               b->stream);
+  if (e != 0) return fail(BP_ECUDA, std::string("field copy: ") + cudaGetErrorString((cudaError_t)e));
+  return BP_OK;
+}
+
 static int field_copy(bp_batch* b, const char* name, void* host, int64_t env0, int64_t n,
                       bool to_device) {
   if (!b || !name || !host) return fail(BP_EINVAL, "null argument");
@@ -392,12 +428,21 @@ static int field_copy(bp_batch* b, const char* name, void* host, int64_t env0, i
   if (env0 < 0 || n < 0 || env0 + n > b->nenv) return fail(BP_EINVAL, "env range out of bounds");
   if (n == 0 || f->count == 0) return BP_OK;
   cudaSetDevice(b->model->device);
-  size_t w = (size_t)f->count * (f->dtype == 0 ? 8 : 4), pitch = (size_t)b->L.persist * 8;
-  char* dev = (char*)b->image + (size_t)env0 * pitch + f->offset_bytes;
-  if (to_device)
-    CUDA_OK(cudaMemcpy2DAsync(dev, pitch, host, w, w, n, cudaMemcpyHostToDevice, b->stream));
-  else
-    CUDA_OK(cudaMemcpy2DAsync(host, w, dev, pitch, w, n, cudaMemcpyDeviceToHost, b->stream));
+  size_t bytes = (size_t)n * f->count * (f->dtype == 0 ? 8 : 4);
+  if (bytes > b->stage_bytes) {
+    if (b->stage) { cudaStreamSynchronize(b->stream); cudaFree(b->stage); b->stage = nullptr; }
+    CUDA_OK(cudaMalloc(&b->stage, bytes));
+    b->stage_bytes = bytes;
+  }
+  if (to_device) {
+    CUDA_OK(cudaMemcpyAsync(b->stage, host, bytes, cudaMemcpyHostToDevice, b->stream));
+    int e = field_copy_dev(b, f, b->stage, env0, n, true);
+    if (e != BP_OK) return e;
+  } else {
+    int e = field_copy_dev(b, f, b->stage, env0, n, false);
+    if (e != BP_OK) return e;
+    CUDA_OK(cudaMemcpyAsync(host, b->stage, bytes, cudaMemcpyDeviceToHost, b->stream));
+  }
   CUDA_OK(cudaStreamSynchronize(b->stream));
   return BP_OK;
 }
@@ -416,13 +461,7 @@ extern "C" int bp_field_copy_device(bp_batch* b, const char* name, void* dev, in
   if (!f) return fail(BP_ENOFIELD, std::string("no data field ") + name);
   if (f->count == 0) return BP_OK;
   cudaSetDevice(b->model->device);
-  size_t w = (size_t)f->count * (f->dtype == 0 ? 8 : 4), pitch = (size_t)b->L.persist * 8;
-  char* img = (char*)b->image + f->offset_bytes;
-  if (to_image)
-    CUDA_OK(cudaMemcpy2DAsync(img, pitch, dev, w, w, b->nenv, cudaMemcpyDeviceToDevice, b->stream));
-  else
-    CUDA_OK(cudaMemcpy2DAsync(dev, w, img, pitch, w, b->nenv, cudaMemcpyDeviceToDevice, b->stream));
-  return BP_OK;
+  return field_copy_dev(b, f, dev, 0, b->nenv, to_image != 0);
 }
 
 extern "C" int bp_dfma_bench(int blocks, int threads, int iters, double* scratch, float* ms,
@@ -460,6 +499,7 @@ static BpParams make_params(bp_batch* b, int mode, int nsub, int disable_actuati
   P.m = b->model->M; P.L = b->L; P.image = b->image;
   P.mask = b->use_mask ? b->mask : nullptr;
   P.nenv = b->nenv; P.mode = mode; P.nsub = nsub; P.disable_actuation = disable_actuation;
+  P.stride = b->stride; P.interleave = b->interleave; P.lanes = b->lanes;
   return P;
 }
 
@@ -467,7 +507,15 @@ static int launch(bp_batch* b, int mode, int nsub, int disable_actuation) {
   if (!b) return fail(BP_EINVAL, "null batch");
   cudaSetDevice(b->model->device);
   BpParams P = make_params(b, mode, nsub, disable_actuation);
-  int e = bp_launch_step(&P, b->stream);
+  int e;
+  switch (b->lanes) {
+    case 1: e = bp_launch_step_g1(&P, b->stream); break;
+    case 2: e = bp_launch_step_g2(&P, b->stream); break;
+    case 4: e = bp_launch_step_g4(&P, b->stream); break;
+    case 8: e = bp_launch_step_g8(&P, b->stream); break;
+    case 16: e = bp_launch_step_g16(&P, b->stream); break;
+    default: e = bp_launch_step_g32(&P, b->stream); break;
+  }
   if (e != 0) return fail(BP_ECUDA, std::string("step launch: ") + cudaGetErrorString((cudaError_t)e));
   return BP_OK;
 }
@@ -543,10 +591,12 @@ extern "C" int bp_env_step_host(bp_batch* b, int nsub, const double* ctrl_host,
     b->obs_cap = nobs;
   }
   const FieldInfo* f = find_field(b, "ctrl");
-  size_t w = (size_t)nu * 8, pitch = (size_t)b->L.persist * 8;
-  if (nu > 0)
-    CUDA_OK(cudaMemcpy2DAsync((char*)b->image + f->offset_bytes, pitch, ctrl_host, w, w,
-                              b->nenv, cudaMemcpyHostToDevice, b->stream));
+  if (nu > 0) {
+    CUDA_OK(cudaMemcpyAsync(b->ctrl_stage, ctrl_host, (size_t)b->nenv * nu * 8,
+                            cudaMemcpyHostToDevice, b->stream));
+    int ec = field_copy_dev(b, f, b->ctrl_stage, 0, b->nenv, true);
+    if (ec != BP_OK) return ec;
+  }
   int e = launch(b, BP_MODE_STEP, nsub, 0);
   if (e != BP_OK) return e;
   e = bp_obs_reward(b, nobs > 0 ? b->obs_dev : nullptr, b->rew_dev);

@@ -1,6 +1,6 @@
 // mj_collision: static candidate pairs on lanes, primitive narrowphase, contacts
-// emitted in pair order through a warp prefix sum so that contact ids are
-// reproducible.
+// emitted in pair order through a group prefix sum so that contact ids are
+// reproducible for every group size.
 #ifndef BP_COLLIDE_CUH_
 #define BP_COLLIDE_CUH_
 #include "bp_math.cuh"
@@ -39,23 +39,23 @@ __device__ __forceinline__ int col_sphere_sphere(const double* c1, double r1,
   return 1;
 }
 
-// returns the number of raw contacts (<= 4) of ordered pair (type1 <= type2)
-__device__ int bp_collide_pair(const Ctx& c, int g1, int g2, double margin, RawCon* out) {
-  const BpModel& m = c.P.m;
-  int t1 = m.geom_type[g1], t2 = m.geom_type[g2];
-  const double *p1 = DF(geom_xpos) + 3 * g1, *p2 = DF(geom_xpos) + 3 * g2;
-  const double *R1 = DF(geom_xmat) + 9 * g1, *R2 = DF(geom_xmat) + 9 * g2;
-  const double *s1 = m.geom_size + 3 * g1, *s2 = m.geom_size + 3 * g2;
+// Narrowphase of ordered pair (type1 <= type2) on geom poses already copied to
+// registers (p = centre, z = local z axis, R2 = full frame of geom 2 for boxes).
+// Returns the number of raw contacts written to out[0..3].
+static __device__ __noinline__ int bp_collide_prims(int t1, int t2, const double* p1,
+                                                    const double* z1, const double* s1,
+                                                    const double* p2, const double* z2,
+                                                    const double* R2, const double* s2,
+                                                    double margin, RawCon* out) {
   if (t1 == GEOM_PLANE) {
-    double n[3] = {R1[2], R1[5], R1[8]};
-    if (t2 == GEOM_SPHERE) return col_plane_sphere(p1, n, p2, s2[0], margin, out[0]);
+    if (t2 == GEOM_SPHERE) return col_plane_sphere(p1, z1, p2, s2[0], margin, out[0]);
     if (t2 == GEOM_CAPSULE) {
-      double ax[3] = {R2[2], R2[5], R2[8]}, e[3], hl = s2[1];
+      double e[3], hl = s2[1];
       int cnt = 0;
       for (int sgn = 1; sgn >= -1; sgn -= 2) {
-        for (int k = 0; k < 3; k++) e[k] = p2[k] + sgn * ax[k] * hl;
-        if (col_plane_sphere(p1, n, e, s2[0], margin, out[cnt])) {
-          for (int k = 0; k < 3; k++) out[cnt].hint[k] = ax[k];
+        for (int k = 0; k < 3; k++) e[k] = p2[k] + sgn * z2[k] * hl;
+        if (col_plane_sphere(p1, z1, e, s2[0], margin, out[cnt])) {
+          for (int k = 0; k < 3; k++) out[cnt].hint[k] = z2[k];
           cnt++;
         }
       }
@@ -63,18 +63,19 @@ __device__ int bp_collide_pair(const Ctx& c, int g1, int g2, double margin, RawC
     }
     if (t2 == GEOM_BOX) {
       double dif[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
-      double dist = dot3(dif, n);
+      double dist = dot3(dif, z1);
       int cnt = 0;
+#pragma unroll 1
       for (int i = 0; i < 8 && cnt < 4; i++) {
         double v[3] = {(i & 1) ? s2[0] : -s2[0], (i & 2) ? s2[1] : -s2[1],
                        (i & 4) ? s2[2] : -s2[2]}, cr[3];
         mat_vec3(cr, R2, v);
-        double ld = dot3(n, cr);
+        double ld = dot3(z1, cr);
         if (dist + ld > margin) continue;
         out[cnt].dist = dist + ld;
         for (int k = 0; k < 3; k++) {
-          out[cnt].pos[k] = p2[k] + cr[k] - n[k] * 0.5 * (dist + ld);
-          out[cnt].n[k] = n[k];
+          out[cnt].pos[k] = p2[k] + cr[k] - z1[k] * 0.5 * (dist + ld);
+          out[cnt].n[k] = z1[k];
           out[cnt].hint[k] = 0;
         }
         cnt++;
@@ -86,18 +87,16 @@ __device__ int bp_collide_pair(const Ctx& c, int g1, int g2, double margin, RawC
   if (t1 == GEOM_SPHERE && t2 == GEOM_SPHERE)
     return col_sphere_sphere(p1, s1[0], p2, s2[0], margin, out[0]);
   if (t1 == GEOM_SPHERE && t2 == GEOM_CAPSULE) {
-    double ax[3] = {R2[2], R2[5], R2[8]};
     double dif[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
-    double x = clampd(dot3(ax, dif), -s2[1], s2[1]);
-    double cc[3] = {p2[0] + ax[0] * x, p2[1] + ax[1] * x, p2[2] + ax[2] * x};
+    double x = clampd(dot3(z2, dif), -s2[1], s2[1]);
+    double cc[3] = {p2[0] + z2[0] * x, p2[1] + z2[1] * x, p2[2] + z2[2] * x};
     return col_sphere_sphere(p1, s1[0], cc, s2[0], margin, out[0]);
   }
   if (t1 == GEOM_CAPSULE && t2 == GEOM_CAPSULE) {
-    // closest points of segments p1 + x1*a1, p2 + x2*a2 with |xi| <= li
-    double a1[3] = {R1[2], R1[5], R1[8]}, a2[3] = {R2[2], R2[5], R2[8]};
+    // closest points of segments p1 + x1*z1, p2 + x2*z2 with |xi| <= li
     double dif[3] = {p1[0] - p2[0], p1[1] - p2[1], p1[2] - p2[2]};
     double l1 = s1[1], l2 = s2[1];
-    double b = dot3(a1, a2), u = -dot3(a1, dif), v = dot3(a2, dif);
+    double b = dot3(z1, z2), u = -dot3(z1, dif), v = dot3(z2, dif);
     double det = 1.0 - b * b, x1, x2;
     if (fabs(det) >= 1e-12) {
       x1 = (u + b * v) / det;
@@ -112,7 +111,7 @@ __device__ int bp_collide_pair(const Ctx& c, int g1, int g2, double margin, RawC
       x1 = clampd(u + b * x2, -l1, l1);
     }
     double c1[3], c2[3];
-    for (int k = 0; k < 3; k++) { c1[k] = p1[k] + a1[k] * x1; c2[k] = p2[k] + a2[k] * x2; }
+    for (int k = 0; k < 3; k++) { c1[k] = p1[k] + z1[k] * x1; c2[k] = p2[k] + z2[k] * x2; }
     return col_sphere_sphere(c1, s1[0], c2, s2[0], margin, out[0]);
   }
   return 0;
@@ -131,16 +130,17 @@ __device__ __forceinline__ void make_frame(double* f) {
   cross3(f + 6, f, f + 3);
 }
 
-__device__ void bp_collision(const Ctx& c) {
+BP_STAGE void bp_collision(const C& c) {
   const BpModel& m = c.P.m;
-  int* ncon_p = IF(ncon);
-  if (c.lane == 0) *ncon_p = 0;
+  if (c.lane == 0) IF(ncon)[0] = 0;
   SYNC();
   if (m.opt_disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT)) return;
   bool filterparent = !(m.opt_disableflags & DSBL_FILTERPARENT);
   int nconmax = c.P.L.nconmax, base = 0;
   bool full = false;
-  for (int p0 = 0; p0 < m.npair; p0 += 32) {
+  auto gpos = DF(geom_xpos), gmat = DF(geom_xmat);
+#pragma unroll 1
+  for (int p0 = 0; p0 < m.npair; p0 += C::G) {
     int p = p0 + c.lane, n = 0, g1 = 0, g2 = 0;
     double margin = 0, gap = 0;
     RawCon raw[4];
@@ -148,27 +148,33 @@ __device__ void bp_collision(const Ctx& c) {
       g1 = m.pair_geom1[p]; g2 = m.pair_geom2[p];
       margin = fmax(m.geom_margin[g1], m.geom_margin[g2]);
       gap = fmax(m.geom_gap[g1], m.geom_gap[g2]);
-      const double *p1 = DF(geom_xpos) + 3 * g1, *p2 = DF(geom_xpos) + 3 * g2;
-      double dif[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
+      double p1[3], p2[3], z1[3], dif[3];
+      for (int k = 0; k < 3; k++) {
+        p1[k] = gpos[3 * g1 + k]; p2[k] = gpos[3 * g2 + k];
+        z1[k] = gmat[9 * g1 + 3 * k + 2];
+        dif[k] = p2[k] - p1[k];
+      }
+      int t1 = m.geom_type[g1], t2 = m.geom_type[g2];
       bool keep;
-      if (m.geom_type[g1] == GEOM_PLANE) {
-        const double* R1 = DF(geom_xmat) + 9 * g1;
-        double nrm[3] = {R1[2], R1[5], R1[8]};
-        keep = !(dot3(dif, nrm) > m.geom_rbound[g2] + margin);
-      } else {
+      if (t1 == GEOM_PLANE) keep = !(dot3(dif, z1) > m.geom_rbound[g2] + margin);
+      else {
         double bound = m.geom_rbound[g1] + m.geom_rbound[g2] + margin;
         keep = !(dot3(dif, dif) > bound * bound);
       }
-      if (keep) n = bp_collide_pair(c, g1, g2, margin, raw);
+      if (keep) {
+        double R2[9], z2[3], s1[3], s2[3];
+        for (int k = 0; k < 9; k++) R2[k] = gmat[9 * g2 + k];
+        for (int k = 0; k < 3; k++) {
+          z2[k] = R2[3 * k + 2];
+          s1[k] = m.geom_size[3 * g1 + k]; s2[k] = m.geom_size[3 * g2 + k];
+        }
+        n = bp_collide_prims(t1, t2, p1, z1, s1, p2, z2, R2, s2, margin, raw);
+      }
     }
-    // exclusive prefix sum of n over lanes -> slots in pair order
-    int incl = n;
-    for (int o = 1; o < 32; o <<= 1) {
-      int t = __shfl_up_sync(FULL, incl, o);
-      if (c.lane >= o) incl += t;
-    }
-    int start = base + incl - n;
-    base += __shfl_sync(FULL, incl, 31);
+    // exclusive prefix sum of n over the group -> slots in pair order
+    int tot, start = base + group_excl_scan(c, n, &tot);
+    base += tot;
+#pragma unroll 1
     for (int i = 0; i < n; i++) {
       int id = start + i;
       if (id >= nconmax) { full = true; break; }
@@ -186,8 +192,8 @@ __device__ void bp_collision(const Ctx& c) {
       const double *f1 = m.geom_friction + 3 * g1, *f2 = m.geom_friction + 3 * g2;
       double fr[3];
       for (int k = 0; k < 3; k++) fr[k] = fmax(f1[k], f2[k]);
-      double* cf = DF(contact_friction) + 5 * id;
-      cf[0] = cf[1] = fr[0]; cf[2] = fr[1]; cf[3] = cf[4] = fr[2];
+      auto cf = DF(contact_friction) + 5 * id;
+      cf[0] = fr[0]; cf[1] = fr[0]; cf[2] = fr[1]; cf[3] = fr[2]; cf[4] = fr[2];
       double mix1 = m.geom_solmix[g1], mix2 = m.geom_solmix[g2], mix;
       if (mix1 >= BP_MINVAL && mix2 >= BP_MINVAL) mix = mix1 / (mix1 + mix2);
       else if (mix1 < BP_MINVAL && mix2 < BP_MINVAL) mix = 0.5;
@@ -202,11 +208,11 @@ __device__ void bp_collision(const Ctx& c) {
       IF(contact_efc_address)[id] = -1;
       DF(contact_mu)[id] = 0;
     }
-    if (base > nconmax) break;    // uniform: every lane sees the same base
+    if (base > nconmax) break;    // uniform inside the group
   }
-  full = __any_sync(FULL, full);
+  full = group_any(c, full);
   if (c.lane == 0) {
-    *ncon_p = base < nconmax ? base : nconmax;
+    IF(ncon)[0] = base < nconmax ? base : nconmax;
     if (full) IF(warning)[W_CONTACTFULL]++;
   }
   SYNC();

@@ -1,23 +1,16 @@
 // mj_makeConstraint + reference acceleration: rows in the order friction loss,
 // joint limits, contacts.  Row slots come from
-// warp prefix sums so row ids are reproducible; Jacobian entries are produced one
+// group prefix sums so row ids are reproducible; Jacobian entries are produced one
 // (contact, dof) pair per lane using per-body dof-ancestry bit masks.
 #ifndef BP_CONSTRAINT_CUH_
 #define BP_CONSTRAINT_CUH_
 #include "bp_math.cuh"
 
-__device__ __forceinline__ int warp_excl_scan(int n, int lane, int* total) {
-  int incl = n;
-  for (int o = 1; o < 32; o <<= 1) {
-    int t = __shfl_up_sync(FULL, incl, o);
-    if (lane >= o) incl += t;
-  }
-  *total = __shfl_sync(FULL, incl, 31);
-  return incl - n;
-}
+// one shared copy of pow(): the inlined expansion is ~200 instructions per call site
+static __device__ __noinline__ double bp_pow(double x, double p) { return pow(x, p); }
 
-__device__ __forceinline__ void bp_impedance(const double* si, double pos, double margin,
-                                             double* imp, double* impP) {
+static __device__ __noinline__ void bp_impedance(const double* si, double pos, double margin,
+                                                 double* imp, double* impP) {
   if (si[0] == si[1] || si[2] <= BP_MINVAL) { *imp = 0.5 * (si[0] + si[1]); *impP = 0; return; }
   double x = (pos - margin) / si[2], sgn = 1;
   if (x < 0) { x = -x; sgn = -1; }
@@ -25,33 +18,34 @@ __device__ __forceinline__ void bp_impedance(const double* si, double pos, doubl
   double y, yP, p = si[4], mid = si[3];
   if (p == 1) { y = x; yP = 1; }
   else if (x <= mid) {
-    double a = 1 / pow(mid, p - 1);
-    y = a * pow(x, p); yP = p * a * pow(x, p - 1);
+    double a = 1 / bp_pow(mid, p - 1);
+    y = a * bp_pow(x, p); yP = p * a * bp_pow(x, p - 1);
   } else {
-    double b = 1 / pow(1 - mid, p - 1);
-    y = 1 - b * pow(1 - x, p); yP = p * b * pow(1 - x, p - 1);
+    double b = 1 / bp_pow(1 - mid, p - 1);
+    y = 1 - b * bp_pow(1 - x, p); yP = p * b * bp_pow(1 - x, p - 1);
   }
   *imp = si[0] + y * (si[1] - si[0]);
   *impP = yP * sgn * (si[1] - si[0]) / si[2];
 }
 
-__device__ __forceinline__ void bp_row_header(const Ctx& c, int r, int type, int id,
+template <class C>
+__device__ __forceinline__ void bp_row_header(const C& c, int r, int type, int id,
                                               double pos, double margin, double floss) {
   IF(efc_type)[r] = type; IF(efc_id)[r] = id;
   DF(efc_pos)[r] = pos; DF(efc_margin)[r] = margin; DF(efc_frictionloss)[r] = floss;
 }
 
-__device__ void bp_make_constraint(const Ctx& c) {
+BP_STAGE void bp_make_constraint(const C& c) {
   const BpModel& m = c.P.m;
   const int nv = m.nv, nvp = m.nvp, njmax = c.P.L.njmax;
-  double* J = DF(efc_J);
-  if (c.lane == 0) { *IF(nefc) = 0; *IF(ne) = 0; *IF(nf) = 0; }
+  auto J = DF(efc_J);
+  if (c.lane == 0) { IF(nefc)[0] = 0; IF(ne)[0] = 0; IF(nf)[0] = 0; }
   SYNC();
   if (m.opt_disableflags & DSBL_CONSTRAINT) return;
   int base = 0, nf = 0;
   // ---- pass 1: headers + slots -------------------------------------------------
   if (!(m.opt_disableflags & DSBL_FRICTIONLOSS)) {
-    for (int k = c.lane; k < m.nfric; k += 32) {
+    for (int k = c.lane; k < m.nfric; k += C::G) {
       int r = base + k, i = m.fric_dof[k];
       if (r < njmax) bp_row_header(c, r, CN_FRICTION_DOF, i, 0, 0, m.dof_frictionloss[i]);
     }
@@ -60,37 +54,39 @@ __device__ void bp_make_constraint(const Ctx& c) {
   }
   int lim_base = base;
   if (!(m.opt_disableflags & DSBL_LIMIT)) {
-    for (int k0 = 0; k0 < m.nlim; k0 += 32) {
+#pragma unroll 1
+    for (int k0 = 0; k0 < m.nlim; k0 += C::G) {
       int k = k0 + c.lane, n = 0, j = 0;
-      double dist[2] = {0, 0}, margin = 0;
-      bool on[2] = {false, false};
+      double dist0 = 0, dist1 = 0, margin = 0;
+      bool on0 = false, on1 = false;
       if (k < m.nlim) {
         j = m.lim_jnt[k];
         double q = DF(qpos)[m.jnt_qposadr[j]];
         margin = m.jnt_margin[j];
-        dist[0] = -(m.jnt_range[2 * j] - q);        // side = -1: lower bound
-        dist[1] = m.jnt_range[2 * j + 1] - q;       // side = +1: upper bound
-        on[0] = dist[0] < margin; on[1] = dist[1] < margin;
-        n = on[0] + on[1];
+        dist0 = -(m.jnt_range[2 * j] - q);        // side = -1: lower bound
+        dist1 = m.jnt_range[2 * j + 1] - q;       // side = +1: upper bound
+        on0 = dist0 < margin; on1 = dist1 < margin;
+        n = on0 + on1;
       }
-      int tot, start = base + warp_excl_scan(n, c.lane, &tot);
-      for (int s = 0; s < 2; s++)
-        if (on[s]) {
-          if (start < njmax) bp_row_header(c, start, CN_LIMIT_JOINT, j, dist[s], margin, 0);
-          start++;
-        }
+      int tot, start = base + group_excl_scan(c, n, &tot);
+      if (on0) {
+        if (start < njmax) bp_row_header(c, start, CN_LIMIT_JOINT, j, dist0, margin, 0);
+        start++;
+      }
+      if (on1 && start < njmax) bp_row_header(c, start, CN_LIMIT_JOINT, j, dist1, margin, 0);
       base += tot;
     }
   }
-  int con_base = base, ncon = *IF(ncon);
+  int con_base = base, ncon = IF(ncon)[0];
   const bool pyramidal = m.opt_cone == 0;
-  for (int c0 = 0; c0 < ncon; c0 += 32) {
+#pragma unroll 1
+  for (int c0 = 0; c0 < ncon; c0 += C::G) {
     int ci = c0 + c.lane, n = 0, dim = 0;
     if (ci < ncon && !IF(contact_exclude)[ci]) {
       dim = IF(contact_dim)[ci];
       n = dim == 1 ? 1 : (pyramidal ? 2 * (dim - 1) : dim);
     }
-    int tot, start = base + warp_excl_scan(n, c.lane, &tot);
+    int tot, start = base + group_excl_scan(c, n, &tot);
     if (ci < ncon) {
       int adr = (n > 0 && start < njmax) ? start : -1;
       IF(contact_efc_address)[ci] = adr;
@@ -104,17 +100,17 @@ __device__ void bp_make_constraint(const Ctx& c) {
   }
   int nefc = base < njmax ? base : njmax;
   if (c.lane == 0) {
-    *IF(nefc) = nefc; *IF(nf) = nf;
+    IF(nefc)[0] = nefc; IF(nf)[0] = nf;
     if (base > njmax) IF(warning)[W_CNSTRFULL]++;
   }
   SYNC();
   // ---- pass 2: Jacobian ----------------------------------------------------------
-  for (int w = c.lane; w < nefc * nvp; w += 32) J[w] = 0;
+  for (int w = c.lane; w < nefc * nvp; w += C::G) J[w] = 0;
   SYNC();
-  for (int r = c.lane; r < lim_base && r < nefc; r += 32) J[r * nvp + IF(efc_id)[r]] = 1;
-  // limit rows: sign of the Jacobian entry is -side; recompute side from the slot
-  // order (lower bound first).  A joint with both sides active owns two adjacent rows.
-  for (int r = lim_base + c.lane; r < con_base && r < nefc; r += 32) {
+  for (int r = c.lane; r < lim_base && r < nefc; r += C::G) J[r * nvp + IF(efc_id)[r]] = 1;
+  // limit rows: the Jacobian entry is -side; a joint with both sides active owns two
+  // adjacent rows, lower bound first
+  for (int r = lim_base + c.lane; r < con_base && r < nefc; r += C::G) {
     int j = IF(efc_id)[r];
     double q = DF(qpos)[m.jnt_qposadr[j]];
     bool lower_on = -(m.jnt_range[2 * j] - q) < m.jnt_margin[j];
@@ -122,35 +118,38 @@ __device__ void bp_make_constraint(const Ctx& c) {
     int side = (lower_on && first) ? -1 : 1;
     J[r * nvp + m.jnt_dofadr[j]] = -side;
   }
-  const double *cdof = DF(cdof), *com = DF(subtree_com);
-  for (int w = c.lane; w < ncon * nv; w += 32) {
+  auto cdof = DF(cdof), com = DF(subtree_com);
+#pragma unroll 1
+  for (int w = c.lane; w < ncon * nv; w += C::G) {
     int ci = w / nv, i = w - ci * nv;
     int a = IF(contact_efc_address)[ci];
     if (a < 0) continue;
     int b1 = m.geom_bodyid[IF(contact_geom1)[ci]], b2 = m.geom_bodyid[IF(contact_geom2)[ci]];
     bool in1 = (m.body_dofmask[b1] >> i) & 1ull, in2 = (m.body_dofmask[b2] >> i) & 1ull;
     if (!in1 && !in2) continue;          // column stays zero
-    const double* cd = cdof + 6 * i;
-    const double* pos = DF(contact_pos) + 3 * ci;
+    double cd[6], pos[3];
+    for (int k = 0; k < 6; k++) cd[k] = cdof[6 * i + k];
+    for (int k = 0; k < 3; k++) pos[k] = DF(contact_pos)[3 * ci + k];
     double dp[3] = {0, 0, 0}, dr[3] = {0, 0, 0};
     if (in2) {
-      const double* cm = com + 3 * m.body_rootid[b2];
+      auto cm = com + 3 * m.body_rootid[b2];
       double off[3] = {pos[0] - cm[0], pos[1] - cm[1], pos[2] - cm[2]}, t[3];
       cross3(t, cd, off);
       for (int k = 0; k < 3; k++) { dp[k] = cd[3 + k] + t[k]; dr[k] = cd[k]; }
     }
     if (in1) {
-      const double* cm = com + 3 * m.body_rootid[b1];
+      auto cm = com + 3 * m.body_rootid[b1];
       double off[3] = {pos[0] - cm[0], pos[1] - cm[1], pos[2] - cm[2]}, t[3];
       cross3(t, cd, off);
       for (int k = 0; k < 3; k++) { dp[k] -= cd[3 + k] + t[k]; dr[k] -= cd[k]; }
     }
-    const double* fr = DF(contact_frame) + 9 * ci;
+    auto fr = DF(contact_frame) + 9 * ci;
     double Jc[6];
     for (int k = 0; k < 3; k++) { Jc[k] = dot3(fr + 3 * k, dp); Jc[3 + k] = dot3(fr + 3 * k, dr); }
     int dim = IF(contact_dim)[ci];
     if (dim == 1) J[a * nvp + i] = Jc[0];
     else if (pyramidal) {
+#pragma unroll 1
       for (int k = 1; k < dim; k++) {
         double mu = DF(contact_friction)[5 * ci + k - 1];
         int r = a + 2 * (k - 1);
@@ -158,6 +157,7 @@ __device__ void bp_make_constraint(const Ctx& c) {
         if (r + 1 < nefc) J[(r + 1) * nvp + i] = Jc[0] - mu * Jc[k];
       }
     } else {
+#pragma unroll 1
       for (int k = 0; k < dim; k++)
         if (a + k < nefc) J[(a + k) * nvp + i] = Jc[k];
     }
@@ -165,18 +165,21 @@ __device__ void bp_make_constraint(const Ctx& c) {
   SYNC();
   // ---- pass 3: per-row solver parameters -----------------------------------------
   const double dt = m.opt_timestep;
-  for (int r = c.lane; r < nefc; r += 32) {
+#pragma unroll 1
+  for (int r = c.lane; r < nefc; r += C::G) {
     int type = IF(efc_type)[r], id = IF(efc_id)[r];
-    const double *solref, *solimp;
-    double dA;
+    double solref[2], solimp[5], dA;
     if (type == CN_FRICTION_DOF) {
-      solref = m.dof_solref + 2 * id; solimp = m.dof_solimp + 5 * id;
+      for (int k = 0; k < 2; k++) solref[k] = m.dof_solref[2 * id + k];
+      for (int k = 0; k < 5; k++) solimp[k] = m.dof_solimp[5 * id + k];
       dA = m.dof_invweight0[id];
     } else if (type == CN_LIMIT_JOINT) {
-      solref = m.jnt_solref + 2 * id; solimp = m.jnt_solimp + 5 * id;
+      for (int k = 0; k < 2; k++) solref[k] = m.jnt_solref[2 * id + k];
+      for (int k = 0; k < 5; k++) solimp[k] = m.jnt_solimp[5 * id + k];
       dA = m.dof_invweight0[m.jnt_dofadr[id]];
     } else {
-      solref = DF(contact_solref) + 2 * id; solimp = DF(contact_solimp) + 5 * id;
+      for (int k = 0; k < 2; k++) solref[k] = DF(contact_solref)[2 * id + k];
+      for (int k = 0; k < 5; k++) solimp[k] = DF(contact_solimp)[5 * id + k];
       int b1 = m.geom_bodyid[IF(contact_geom1)[id]], b2 = m.geom_bodyid[IF(contact_geom2)[id]];
       double tran = m.body_invweight0[2 * b1] + m.body_invweight0[2 * b2];
       double rot = m.body_invweight0[2 * b1 + 1] + m.body_invweight0[2 * b2 + 1];
@@ -200,15 +203,16 @@ __device__ void bp_make_constraint(const Ctx& c) {
       K = 1 / fmax(BP_MINVAL, dmax * dmax * sr0 * sr0 * sr1 * sr1);
       B = 2 / fmax(BP_MINVAL, dmax * sr0);
     } else { K = -sr0 / fmax(BP_MINVAL, dmax * dmax); B = -sr1 / fmax(BP_MINVAL, dmax); }
-    double* kb = DF(efc_KBIP) + 4 * r;
+    auto kb = DF(efc_KBIP) + 4 * r;
     kb[0] = K; kb[1] = B; kb[2] = imp; kb[3] = impP;
   }
   SYNC();
-  for (int ci = c.lane; ci < ncon; ci += 32) {
+#pragma unroll 1
+  for (int ci = c.lane; ci < ncon; ci += C::G) {
     int a = IF(contact_efc_address)[ci], dim = IF(contact_dim)[ci];
     if (a < 0 || dim == 1) continue;
-    double* R = DF(efc_R);
-    const double* f = DF(contact_friction) + 5 * ci;
+    auto R = DF(efc_R);
+    auto f = DF(contact_friction) + 5 * ci;
     if (pyramidal) {
       double mu = f[0] / sqrt(m.opt_impratio);
       DF(contact_mu)[ci] = mu;
@@ -223,20 +227,21 @@ __device__ void bp_make_constraint(const Ctx& c) {
     }
   }
   SYNC();
-  for (int r = c.lane; r < nefc; r += 32) DF(efc_D)[r] = 1 / DF(efc_R)[r];
+  for (int r = c.lane; r < nefc; r += C::G) DF(efc_D)[r] = 1 / DF(efc_R)[r];
   SYNC();
 }
 
 // efc_vel = J qvel, efc_aref = -B vel - K imp (pos - margin)
-__device__ void bp_reference_constraint(const Ctx& c) {
+BP_STAGE void bp_reference_constraint(const C& c) {
   const BpModel& m = c.P.m;
-  const int nv = m.nv, nvp = m.nvp, nefc = *IF(nefc);
-  const double *J = DF(efc_J), *qvel = DF(qvel);
-  for (int r = c.lane; r < nefc; r += 32) {
+  const int nv = m.nv, nvp = m.nvp, nefc = IF(nefc)[0];
+  auto J = DF(efc_J), qvel = DF(qvel);
+#pragma unroll 1
+  for (int r = c.lane; r < nefc; r += C::G) {
     double v = 0;
     for (int i = 0; i < nv; i++) v += J[r * nvp + i] * qvel[i];
     DF(efc_vel)[r] = v;
-    const double* kb = DF(efc_KBIP) + 4 * r;
+    auto kb = DF(efc_KBIP) + 4 * r;
     DF(efc_aref)[r] = -kb[1] * v - kb[0] * kb[2] * (DF(efc_pos)[r] - DF(efc_margin)[r]);
   }
   SYNC();

@@ -4,25 +4,29 @@
 #define BP_DYN_CUH_
 #include "bp_smooth.cuh"
 
-__device__ void bp_com_vel(const Ctx& c) {
+BP_STAGE void bp_com_vel(const C& c) {
   const BpModel& m = c.P.m;
-  double *cvel = DF(cvel), *cdof = DF(cdof), *cdof_dot = DF(cdof_dot), *qvel = DF(qvel);
-  if (c.lane < 6) cvel[c.lane] = 0;
+  auto cvel = DF(cvel), cdof = DF(cdof), cdof_dot = DF(cdof_dot), qvel = DF(qvel);
+  for (int i = c.lane; i < 6; i += C::G) cvel[i] = 0;
   SYNC();
+#pragma unroll 1
   for (int lev = 1; lev < m.nlevel; lev++) {
+#pragma unroll 1
     for (int idx = m.body_level_adr[lev] + c.lane; idx < m.body_level_adr[lev + 1];
-         idx += 32) {
+         idx += C::G) {
       int b = m.body_level_list[idx];
       double cv[6];
       for (int i = 0; i < 6; i++) cv[i] = cvel[6 * m.body_parentid[b] + i];
       int jn = m.body_jntnum[b], j0 = m.body_jntadr[b];
+#pragma unroll 1
       for (int k = 0; k < jn; k++) {
         int j = j0 + k, da = m.jnt_dofadr[j], jt = m.jnt_type[j];
         if (jt == JNT_FREE) {
           for (int i = 0; i < 3; i++) {
+            double v = qvel[da + i];
             for (int q = 0; q < 6; q++) {
               cdof_dot[6 * (da + i) + q] = 0;
-              cv[q] += cdof[6 * (da + i) + q] * qvel[da + i];
+              cv[q] += cdof[6 * (da + i) + q] * v;
             }
           }
           da += 3;
@@ -33,8 +37,10 @@ __device__ void bp_com_vel(const Ctx& c) {
           cross_motion(t, cv, cdof + 6 * (da + i));
           for (int q = 0; q < 6; q++) cdof_dot[6 * (da + i) + q] = t[q];
         }
-        for (int i = 0; i < n; i++)
-          for (int q = 0; q < 6; q++) cv[q] += cdof[6 * (da + i) + q] * qvel[da + i];
+        for (int i = 0; i < n; i++) {
+          double v = qvel[da + i];
+          for (int q = 0; q < 6; q++) cv[q] += cdof[6 * (da + i) + q] * v;
+        }
       }
       for (int i = 0; i < 6; i++) cvel[6 * b + i] = cv[i];
     }
@@ -42,11 +48,11 @@ __device__ void bp_com_vel(const Ctx& c) {
   }
 }
 
-__device__ void bp_passive(const Ctx& c) {
+BP_STAGE void bp_passive(const C& c) {
   const BpModel& m = c.P.m;
-  double *qp = DF(qfrc_passive), *qpos = DF(qpos), *qvel = DF(qvel);
+  auto qp = DF(qfrc_passive), qpos = DF(qpos), qvel = DF(qvel);
   bool off = m.opt_disableflags & DSBL_PASSIVE;
-  for (int i = c.lane; i < m.nv; i += 32) {
+  for (int i = c.lane; i < m.nv; i += C::G) {
     double f = 0;
     if (!off) {
       int j = m.dof_jntid[i], jt = m.jnt_type[j];
@@ -65,24 +71,27 @@ __device__ void bp_passive(const Ctx& c) {
 // Recursive Newton-Euler.  with_acc adds cdof*qacc; cfrc_ext (may be null) is
 // subtracted from the body forces (post-constraint variant used by sensors).
 // Writes cacc / cfrc into the given buffers; result (may be null) = J^T cfrc.
-__device__ void bp_rne(const Ctx& c, bool with_acc, double* cacc, double* cfrc,
-                       const double* cfrc_ext, double* result, int stop_level) {
+BP_STAGE void bp_rne(const C& c, bool with_acc, typename C::DP cacc, typename C::DP cfrc,
+                     typename C::DP cfrc_ext, typename C::DP result, int stop_level) {
   const BpModel& m = c.P.m;
-  double *cdof = DF(cdof), *cdof_dot = DF(cdof_dot), *qvel = DF(qvel), *qacc = DF(qacc);
-  double *cinert = DF(cinert), *cvel = DF(cvel);
+  auto cdof = DF(cdof), cdof_dot = DF(cdof_dot), qvel = DF(qvel), qacc = DF(qacc);
+  auto cinert = DF(cinert), cvel = DF(cvel);
   bool grav = !(m.opt_disableflags & DSBL_GRAVITY);
-  if (c.lane < 6) {
-    cacc[c.lane] = (c.lane >= 3 && grav) ? -m.opt_gravity[c.lane - 3] : 0.0;
-    cfrc[c.lane] = 0;
+  for (int i = c.lane; i < 6; i += C::G) {
+    cacc[i] = (i >= 3 && grav) ? -m.opt_gravity[i - 3] : 0.0;
+    cfrc[i] = 0;
   }
   SYNC();
+#pragma unroll 1
   for (int lev = 1; lev < m.nlevel; lev++) {
+#pragma unroll 1
     for (int idx = m.body_level_adr[lev] + c.lane; idx < m.body_level_adr[lev + 1];
-         idx += 32) {
+         idx += C::G) {
       int b = m.body_level_list[idx];
       double a[6];
       for (int i = 0; i < 6; i++) a[i] = cacc[6 * m.body_parentid[b] + i];
       int da = m.body_dofadr[b], dn = m.body_dofnum[b];
+#pragma unroll 1
       for (int k = 0; k < dn; k++) {
         double v = qvel[da + k], qa = with_acc ? qacc[da + k] : 0.0;
         for (int i = 0; i < 6; i++) {
@@ -93,69 +102,69 @@ __device__ void bp_rne(const Ctx& c, bool with_acc, double* cacc, double* cfrc,
         }
       }
       for (int i = 0; i < 6; i++) cacc[6 * b + i] = a[i];
-      double Ia[6], Iv[6], vxIv[6];
+      double Ia[6], Iv[6], vxIv[6], cv[6];
+      for (int i = 0; i < 6; i++) cv[i] = cvel[6 * b + i];
       inert_mul(Ia, cinert + 10 * b, a);
-      inert_mul(Iv, cinert + 10 * b, cvel + 6 * b);
-      cross_force(vxIv, cvel + 6 * b, Iv);
+      inert_mul(Iv, cinert + 10 * b, cv);
+      cross_force(vxIv, cv, Iv);
       for (int i = 0; i < 6; i++)
-        cfrc[6 * b + i] = Ia[i] + vxIv[i] - (cfrc_ext ? cfrc_ext[6 * b + i] : 0.0);
+        cfrc[6 * b + i] = Ia[i] + vxIv[i] - (cfrc_ext.valid() ? cfrc_ext[6 * b + i] : 0.0);
     }
     SYNC();
   }
   bp_tree_gather(c, cfrc, 6, stop_level);
-  if (result) {
-    for (int i = c.lane; i < m.nv; i += 32)
+  if (result.valid()) {
+    for (int i = c.lane; i < m.nv; i += C::G)
       result[i] = dot6(cdof + 6 * i, cfrc + 6 * m.dof_bodyid[i]);
     SYNC();
   }
 }
 
 // joint transmission with scalar joints (the only kind the compiled subset emits)
-__device__ void bp_transmission(const Ctx& c) {
+BP_STAGE void bp_transmission(const C& c) {
   const BpModel& m = c.P.m;
-  double *len = DF(actuator_length), *qpos = DF(qpos);
-  for (int i = c.lane; i < m.nu; i += 32)
+  auto len = DF(actuator_length), qpos = DF(qpos);
+  for (int i = c.lane; i < m.nu; i += C::G)
     len[i] = m.actuator_gear[6 * i] * qpos[m.jnt_qposadr[m.actuator_trnid[2 * i]]];
   SYNC();
 }
 
-__device__ void bp_actuator_velocity(const Ctx& c) {
+BP_STAGE void bp_actuator_velocity(const C& c) {
   const BpModel& m = c.P.m;
-  double *vel = DF(actuator_velocity), *qvel = DF(qvel);
-  for (int i = c.lane; i < m.nu; i += 32)
+  auto vel = DF(actuator_velocity), qvel = DF(qvel);
+  for (int i = c.lane; i < m.nu; i += C::G)
     vel[i] = m.actuator_gear[6 * i] * qvel[m.jnt_dofadr[m.actuator_trnid[2 * i]]];
   SYNC();
 }
 
-__device__ void bp_fwd_actuation(const Ctx& c) {
+BP_STAGE void bp_fwd_actuation(const C& c) {
   const BpModel& m = c.P.m;
   int nu = m.nu, nv = m.nv;
-  double *ctrl = DF(ctrl), *force = DF(actuator_force), *qa = DF(qfrc_actuator);
-  double *act = DF(act), *act_dot = DF(act_dot);
+  auto ctrl = DF(ctrl), force = DF(actuator_force), qa = DF(qfrc_actuator);
+  auto act = DF(act), act_dot = DF(act_dot);
   bool off = nu == 0 || (m.opt_disableflags & DSBL_ACTUATION) || c.P.disable_actuation;
-  for (int i = c.lane; i < m.na; i += 32) act_dot[i] = 0;
+  for (int i = c.lane; i < m.na; i += C::G) act_dot[i] = 0;
   if (off) {
-    for (int i = c.lane; i < nu; i += 32) force[i] = 0;
-    for (int i = c.lane; i < nv; i += 32) qa[i] = 0;
+    for (int i = c.lane; i < nu; i += C::G) force[i] = 0;
+    for (int i = c.lane; i < nv; i += C::G) qa[i] = 0;
     SYNC();
     return;
   }
   bool bad = false;
-  for (int i = c.lane; i < nu; i += 32) {
+  for (int i = c.lane; i < nu; i += C::G) {
     double x = ctrl[i];
     bad |= isnan(x) || fabs(x) > BP_MAXVAL;
   }
-  if (__any_sync(FULL, bad)) {
+  if (group_any(c, bad)) {
     if (c.lane == 0) IF(warning)[W_BADCTRL]++;
-    for (int i = c.lane; i < nu; i += 32) ctrl[i] = 0;
+    for (int i = c.lane; i < nu; i += C::G) ctrl[i] = 0;
   }
   SYNC();
-  for (int i = c.lane; i < nu; i += 32) {
+#pragma unroll 1
+  for (int i = c.lane; i < nu; i += C::G) {
     double x = ctrl[i];
-    if (m.actuator_ctrllimited[i] && !(m.opt_disableflags & DSBL_CLAMPCTRL)) {
-      double lo = m.actuator_ctrlrange[2 * i], hi = m.actuator_ctrlrange[2 * i + 1];
-      x = x < lo ? lo : (x > hi ? hi : x);
-    }
+    if (m.actuator_ctrllimited[i] && !(m.opt_disableflags & DSBL_CLAMPCTRL))
+      x = clampd(x, m.actuator_ctrlrange[2 * i], m.actuator_ctrlrange[2 * i + 1]);
     double in = x;
     int dyn = m.actuator_dyntype[i];
     if (dyn != 0) {
@@ -169,15 +178,14 @@ __device__ void bp_fwd_actuation(const Ctx& c) {
     if (m.actuator_biastype[i] == 1)
       f += m.actuator_biasprm[3 * i] + m.actuator_biasprm[3 * i + 1] * DF(actuator_length)[i] +
            m.actuator_biasprm[3 * i + 2] * DF(actuator_velocity)[i];
-    if (m.actuator_forcelimited[i]) {
-      double lo = m.actuator_forcerange[2 * i], hi = m.actuator_forcerange[2 * i + 1];
-      f = f < lo ? lo : (f > hi ? hi : f);
-    }
+    if (m.actuator_forcelimited[i])
+      f = clampd(f, m.actuator_forcerange[2 * i], m.actuator_forcerange[2 * i + 1]);
     force[i] = f;
   }
   SYNC();
   // qfrc_actuator = moment^T force: each dof sums its own actuators in id order
-  for (int d = c.lane; d < nv; d += 32) {
+#pragma unroll 1
+  for (int d = c.lane; d < nv; d += C::G) {
     double s = 0;
     for (int k = m.dof_actadr[d]; k < m.dof_actadr[d + 1]; k++) {
       int u = m.dof_actlist[k];
@@ -188,10 +196,10 @@ __device__ void bp_fwd_actuation(const Ctx& c) {
   SYNC();
 }
 
-__device__ void bp_fwd_acceleration(const Ctx& c) {
+BP_STAGE void bp_fwd_acceleration(const C& c) {
   const BpModel& m = c.P.m;
-  double *fs = DF(qfrc_smooth), *as = DF(qacc_smooth);
-  for (int i = c.lane; i < m.nv; i += 32) {
+  auto fs = DF(qfrc_smooth), as = DF(qacc_smooth);
+  for (int i = c.lane; i < m.nv; i += C::G) {
     double f = DF(qfrc_passive)[i] - DF(qfrc_bias)[i] + DF(qfrc_actuator)[i] +
                DF(qfrc_applied)[i];
     fs[i] = f; as[i] = f;

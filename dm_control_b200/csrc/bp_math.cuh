@@ -1,73 +1,112 @@
-// Small fixed-size math used by every stage, plus the warp context.
+// Small fixed-size math used by every stage, plus the execution context.
+//
+// An environment is advanced by a GROUP of G lanes (G = 1, 2, 4, 8, 16 or 32; 32/G
+// environments share a warp).  Its data image is addressed through strided pointers:
+// element i of a field lives at base[i * S].  S = 1 is a contiguous image (shared
+// memory for G = 32, global memory for 1 < G < 32); S = 32 interleaves the images of
+// the 32 environments of a warp so that the G = 1 (thread per environment) variant
+// makes fully coalesced accesses.  All helpers are templates over "pointer-like"
+// arguments so that they accept strided pointers, model pointers and local arrays.
 #ifndef BP_MATH_CUH_
 #define BP_MATH_CUH_
 #include "bp_types.h"
 
-struct Ctx {
-  const BpParams& P;
-  double* sm;   // this env's image in shared memory
-  int* ip;      // int32 region of the image
-  int lane;
+template <class T, int S>
+struct SP {
+  T* p;
+  __device__ __forceinline__ T& operator[](int i) const { return p[(long long)i * S]; }
+  __device__ __forceinline__ SP operator+(int n) const { return SP{p + (long long)n * S}; }
+  __device__ __forceinline__ bool valid() const { return p != nullptr; }
 };
 
-#define DF(f) (c.sm + c.P.L.f)
-#define IF(f) (c.ip + c.P.L.f)
-#define SYNC() __syncwarp()
-#define FULL 0xffffffffu
+template <int G_, int S_>
+struct Ctx {
+  static constexpr int G = G_, S = S_;
+  using DP = SP<double, S_>;
+  using IP = SP<int, S_>;
+  const BpParams& P;
+  double* sm;      // element 0 of this env's image
+  int* ip;         // element 0 of the int32 region
+  int lane;        // lane inside the group, 0 .. G-1
+  unsigned mask;   // warp lanes of this group
+  __device__ __forceinline__ DP null() const { return DP{nullptr}; }
+};
 
-__device__ __forceinline__ double dot3(const double* a, const double* b) {
+#define DF(f) (typename C::DP{c.sm + (long long)c.P.L.f * C::S})
+#define IF(f) (typename C::IP{c.ip + (long long)c.P.L.f * C::S})
+#define SYNC() do { if (C::G > 1) __syncwarp(c.mask); } while (0)
+#define BP_STAGE template <class C> __device__ __noinline__
+
+template <class A, class B>
+__device__ __forceinline__ double dot3(A a, B b) {
   return a[0] * b[0] + a[1] * b[1] + a[2] * b[2];
 }
-__device__ __forceinline__ void cross3(double* r, const double* a, const double* b) {
+template <class R, class A, class B>
+__device__ __forceinline__ void cross3(R r, A a, B b) {
   double x = a[1] * b[2] - a[2] * b[1], y = a[2] * b[0] - a[0] * b[2],
          z = a[0] * b[1] - a[1] * b[0];
   r[0] = x; r[1] = y; r[2] = z;
 }
-__device__ __forceinline__ double norm3(const double* a) { return sqrt(dot3(a, a)); }
-__device__ __forceinline__ double normalize3(double* a) {
+template <class A>
+__device__ __forceinline__ double norm3(A a) { return sqrt(dot3(a, a)); }
+template <class A>
+__device__ __forceinline__ double normalize3(A a) {
   double n = norm3(a);
   if (n < BP_MINVAL) { a[0] = 1; a[1] = 0; a[2] = 0; }
   else { a[0] /= n; a[1] /= n; a[2] /= n; }
   return n;
 }
-__device__ __forceinline__ void normalize4(double* q) {
-  double n = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
-  if (n < BP_MINVAL) { q[0] = 1; q[1] = q[2] = q[3] = 0; }
-  else { q[0] /= n; q[1] /= n; q[2] /= n; q[3] /= n; }
+template <class A>
+__device__ __forceinline__ void normalize4(A q) {
+  double q0 = q[0], q1 = q[1], q2 = q[2], q3 = q[3];
+  double n = sqrt(q0 * q0 + q1 * q1 + q2 * q2 + q3 * q3);
+  if (n < BP_MINVAL) { q[0] = 1; q[1] = 0; q[2] = 0; q[3] = 0; }
+  else { q[0] = q0 / n; q[1] = q1 / n; q[2] = q2 / n; q[3] = q3 / n; }
 }
-__device__ __forceinline__ void quat_mul(double* r, const double* a, const double* b) {
-  r[0] = a[0] * b[0] - a[1] * b[1] - a[2] * b[2] - a[3] * b[3];
-  r[1] = a[0] * b[1] + a[1] * b[0] + a[2] * b[3] - a[3] * b[2];
-  r[2] = a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1];
-  r[3] = a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0];
+template <class R, class A, class B>
+__device__ __forceinline__ void quat_mul(R r, A a, B b) {
+  double a0 = a[0], a1 = a[1], a2 = a[2], a3 = a[3];
+  double b0 = b[0], b1 = b[1], b2 = b[2], b3 = b[3];
+  r[0] = a0 * b0 - a1 * b1 - a2 * b2 - a3 * b3;
+  r[1] = a0 * b1 + a1 * b0 + a2 * b3 - a3 * b2;
+  r[2] = a0 * b2 - a1 * b3 + a2 * b0 + a3 * b1;
+  r[3] = a0 * b3 + a1 * b2 - a2 * b1 + a3 * b0;
 }
-__device__ __forceinline__ void quat2mat(double* R, const double* q) {
-  double q00 = q[0] * q[0], q01 = q[0] * q[1], q02 = q[0] * q[2], q03 = q[0] * q[3];
-  double q11 = q[1] * q[1], q12 = q[1] * q[2], q13 = q[1] * q[3];
-  double q22 = q[2] * q[2], q23 = q[2] * q[3], q33 = q[3] * q[3];
-  R[0] = q00 + q11 - q22 - q33; R[4] = q00 - q11 + q22 - q33;
-  R[8] = q00 - q11 - q22 + q33;
-  R[1] = 2 * (q12 - q03); R[2] = 2 * (q13 + q02);
-  R[3] = 2 * (q12 + q03); R[5] = 2 * (q23 - q01);
-  R[6] = 2 * (q13 - q02); R[7] = 2 * (q23 + q01);
+template <class R, class A>
+__device__ __forceinline__ void quat2mat(R R_, A q) {
+  double w = q[0], x = q[1], y = q[2], z = q[3];
+  double q00 = w * w, q01 = w * x, q02 = w * y, q03 = w * z;
+  double q11 = x * x, q12 = x * y, q13 = x * z;
+  double q22 = y * y, q23 = y * z, q33 = z * z;
+  R_[0] = q00 + q11 - q22 - q33; R_[4] = q00 - q11 + q22 - q33;
+  R_[8] = q00 - q11 - q22 + q33;
+  R_[1] = 2 * (q12 - q03); R_[2] = 2 * (q13 + q02);
+  R_[3] = 2 * (q12 + q03); R_[5] = 2 * (q23 - q01);
+  R_[6] = 2 * (q13 - q02); R_[7] = 2 * (q23 + q01);
 }
-__device__ __forceinline__ void mat_vec3(double* r, const double* R, const double* v) {
-  r[0] = R[0] * v[0] + R[1] * v[1] + R[2] * v[2];
-  r[1] = R[3] * v[0] + R[4] * v[1] + R[5] * v[2];
-  r[2] = R[6] * v[0] + R[7] * v[1] + R[8] * v[2];
+template <class R, class M, class V>
+__device__ __forceinline__ void mat_vec3(R r, M R_, V v) {
+  double v0 = v[0], v1 = v[1], v2 = v[2];
+  r[0] = R_[0] * v0 + R_[1] * v1 + R_[2] * v2;
+  r[1] = R_[3] * v0 + R_[4] * v1 + R_[5] * v2;
+  r[2] = R_[6] * v0 + R_[7] * v1 + R_[8] * v2;
 }
-__device__ __forceinline__ void matT_vec3(double* r, const double* R, const double* v) {
-  r[0] = R[0] * v[0] + R[3] * v[1] + R[6] * v[2];
-  r[1] = R[1] * v[0] + R[4] * v[1] + R[7] * v[2];
-  r[2] = R[2] * v[0] + R[5] * v[1] + R[8] * v[2];
+template <class R, class M, class V>
+__device__ __forceinline__ void matT_vec3(R r, M R_, V v) {
+  double v0 = v[0], v1 = v[1], v2 = v[2];
+  r[0] = R_[0] * v0 + R_[3] * v1 + R_[6] * v2;
+  r[1] = R_[1] * v0 + R_[4] * v1 + R_[7] * v2;
+  r[2] = R_[2] * v0 + R_[5] * v1 + R_[8] * v2;
 }
-__device__ __forceinline__ void axis_angle_quat(double* q, const double* axis, double ang) {
+template <class Q, class A>
+__device__ __forceinline__ void axis_angle_quat(Q q, A axis, double ang) {
   double s, co;
   sincos(0.5 * ang, &s, &co);
   q[0] = co; q[1] = axis[0] * s; q[2] = axis[1] * s; q[3] = axis[2] * s;
 }
 // q <- q * exp(w*dt/2), w in the body frame (free/ball joint velocity)
-__device__ __forceinline__ void quat_integrate(double* q, const double* w, double dt) {
+template <class Q, class W>
+__device__ __forceinline__ void quat_integrate(Q q, W w, double dt) {
   double v[3] = {w[0], w[1], w[2]};
   double n = norm3(v);
   if (n < BP_MINVAL) return;
@@ -79,20 +118,30 @@ __device__ __forceinline__ void quat_integrate(double* q, const double* w, doubl
   q[0] = qn[0]; q[1] = qn[1]; q[2] = qn[2]; q[3] = qn[3];
 }
 // spatial vectors are (angular; linear).  r = v x s (motion), r = v x* f (force)
-__device__ __forceinline__ void cross_motion(double* r, const double* v, const double* s) {
-  cross3(r, v, s);
-  double a[3], b[3];
-  cross3(a, v, s + 3); cross3(b, v + 3, s);
+template <class R, class V, class S_>
+__device__ __forceinline__ void cross_motion(R r, V v, S_ s) {
+  double vv[6], ss[6];
+  for (int i = 0; i < 6; i++) { vv[i] = v[i]; ss[i] = s[i]; }
+  double a[3], b[3], w[3];
+  cross3(w, vv, ss); cross3(a, vv, ss + 3); cross3(b, vv + 3, ss);
+  r[0] = w[0]; r[1] = w[1]; r[2] = w[2];
   r[3] = a[0] + b[0]; r[4] = a[1] + b[1]; r[5] = a[2] + b[2];
 }
-__device__ __forceinline__ void cross_force(double* r, const double* v, const double* f) {
-  double a[3], b[3];
-  cross3(a, v, f); cross3(b, v + 3, f + 3);
+template <class R, class V, class F>
+__device__ __forceinline__ void cross_force(R r, V v, F f) {
+  double vv[6], ff[6];
+  for (int i = 0; i < 6; i++) { vv[i] = v[i]; ff[i] = f[i]; }
+  double a[3], b[3], w[3];
+  cross3(a, vv, ff); cross3(b, vv + 3, ff + 3); cross3(w, vv, ff + 3);
   r[0] = a[0] + b[0]; r[1] = a[1] + b[1]; r[2] = a[2] + b[2];
-  cross3(r + 3, v, f + 3);
+  r[3] = w[0]; r[4] = w[1]; r[5] = w[2];
 }
 // 10-vector inertia (Ixx Iyy Izz Ixy Ixz Iyz, m*c, m) times a motion vector
-__device__ __forceinline__ void inert_mul(double* r, const double* I, const double* v) {
+template <class R, class I_, class V>
+__device__ __forceinline__ void inert_mul(R r, I_ Iin, V vin) {
+  double I[10], v[6];
+  for (int i = 0; i < 10; i++) I[i] = Iin[i];
+  for (int i = 0; i < 6; i++) v[i] = vin[i];
   r[0] = I[0] * v[0] + I[3] * v[1] + I[4] * v[2] - I[8] * v[4] + I[7] * v[5];
   r[1] = I[3] * v[0] + I[1] * v[1] + I[5] * v[2] + I[8] * v[3] - I[6] * v[5];
   r[2] = I[4] * v[0] + I[5] * v[1] + I[2] * v[2] - I[7] * v[3] + I[6] * v[4];
@@ -100,14 +149,33 @@ __device__ __forceinline__ void inert_mul(double* r, const double* I, const doub
   r[4] = I[6] * v[2] - I[8] * v[0] + I[9] * v[4];
   r[5] = I[7] * v[0] - I[6] * v[1] + I[9] * v[5];
 }
-__device__ __forceinline__ double dot6(const double* a, const double* b) {
+template <class A, class B>
+__device__ __forceinline__ double dot6(A a, B b) {
   return a[0] * b[0] + a[1] * b[1] + a[2] * b[2] + a[3] * b[3] + a[4] * b[4] +
          a[5] * b[5];
 }
-__device__ __forceinline__ double warp_sum(double v) {
+// group-wide reductions / scans (all lanes of the group must call them together)
+template <class C>
+__device__ __forceinline__ double group_sum(const C& c, double v) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL, v, o);
+  for (int o = C::G / 2; o > 0; o >>= 1) v += __shfl_xor_sync(c.mask, v, o, C::G);
   return v;
+}
+template <class C>
+__device__ __forceinline__ bool group_any(const C& c, bool x) {
+  if (C::G == 1) return x;
+  return (__ballot_sync(c.mask, x) & c.mask) != 0;
+}
+template <class C>
+__device__ __forceinline__ int group_excl_scan(const C& c, int n, int* total) {
+  int incl = n;
+#pragma unroll
+  for (int o = 1; o < C::G; o <<= 1) {
+    int t = __shfl_up_sync(c.mask, incl, o, C::G);
+    if (c.lane >= o) incl += t;
+  }
+  *total = __shfl_sync(c.mask, incl, C::G - 1, C::G);
+  return incl - n;
 }
 __device__ __forceinline__ bool is_bad(double x) {
   return isnan(x) || x > BP_MAXVAL || x < -BP_MAXVAL;

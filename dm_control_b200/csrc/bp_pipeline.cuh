@@ -1,0 +1,255 @@
+// The mj_step pipeline as ONE kernel, templated on the execution shape:
+//   G = 32, image staged in shared memory across all sub-steps of a launch
+//       (one warp per environment), or
+//   G < 32, image addressed in global memory through L1/L2 (32/G environments per
+//       warp; G = 1 is one thread per environment with warp-interleaved images).
+//
+// Replaces the three ctypes calls of the reference's Physics.step()
+// (/root/reference/dm_control/mujoco/engine.py:149-166: mj_step2 + mj_step1, or
+// mj_step + mj_step1 for RK4 models), Physics.forward() (engine.py:297-305) and the
+// sub-step loop of control.Environment.step (rl/control.py:100-106).
+#ifndef BP_PIPELINE_CUH_
+#define BP_PIPELINE_CUH_
+#include <cuda_runtime.h>
+
+#include "bp_collide.cuh"
+#include "bp_constraint.cuh"
+#include "bp_sensor.cuh"
+#include "bp_solver.cuh"
+
+BP_STAGE void bp_fwd_position(const C& c) {
+  bp_kinematics(c);
+  bp_com_pos(c);
+  bp_transmission(c);
+  bp_crb(c);
+  const BpModel& m = c.P.m;
+  auto qLD = DF(qLD), qM = DF(qM);
+  for (int i = c.lane; i < m.nM; i += C::G) qLD[i] = qM[i];
+  SYNC();
+  bp_factor_sparse(c, qLD, DF(qLDiagInv));
+  bp_collision(c);
+  bp_make_constraint(c);
+}
+
+BP_STAGE void bp_fwd_velocity(const C& c) {
+  bp_actuator_velocity(c);
+  bp_com_vel(c);
+  bp_passive(c);
+  bp_reference_constraint(c);
+  bp_rne(c, false, DF(s_cacc), DF(s_cfrc), c.null(), DF(qfrc_bias), 0);
+}
+
+BP_STAGE void bp_forward(const C& c, bool skipsensor) {
+  bp_fwd_position(c);
+  if (!skipsensor) bp_sensors(c, STAGE_POS);
+  bp_energy_pos(c);
+  bp_fwd_velocity(c);
+  if (!skipsensor) bp_sensors(c, STAGE_VEL);
+  bp_energy_vel(c);
+  bp_fwd_actuation(c);
+  bp_fwd_acceleration(c);
+  bp_fwd_constraint(c);
+  if (!skipsensor) bp_sensors(c, STAGE_ACC);
+}
+
+// zero the persistent image, qpos = qpos0 (mj_resetData, engine.py:268-289)
+BP_STAGE void bp_reset_image(const C& c) {
+  const BpModel& m = c.P.m;
+  typename C::DP img{c.sm};
+  for (int w = c.lane; w < c.P.L.persist; w += C::G) img[w] = 0;
+  SYNC();
+  for (int i = c.lane; i < m.nq; i += C::G) DF(qpos)[i] = m.qpos0[i];
+  SYNC();
+}
+
+// MuJoCo resets the data and raises a warning when the state is not finite
+BP_STAGE bool bp_check(const C& c, typename C::DP x, int n, int w) {
+  bool bad = false;
+  for (int i = c.lane; i < n; i += C::G) bad |= is_bad(x[i]);
+  if (!group_any(c, bad)) return false;
+  bp_reset_image(c);
+  if (c.lane == 0) IF(warning)[w] = 1;
+  SYNC();
+  return true;
+}
+
+BP_STAGE void bp_integrate_pos(const C& c, typename C::DP qpos, typename C::DP qvel,
+                               double dt) {
+  const BpModel& m = c.P.m;
+#pragma unroll 1
+  for (int j = c.lane; j < m.njnt; j += C::G) {
+    int qa = m.jnt_qposadr[j], da = m.jnt_dofadr[j];
+    switch (m.jnt_type[j]) {
+      case JNT_FREE:
+        for (int k = 0; k < 3; k++) qpos[qa + k] += dt * qvel[da + k];
+        quat_integrate(qpos + (qa + 3), qvel + (da + 3), dt);
+        break;
+      case JNT_BALL: quat_integrate(qpos + qa, qvel + da, dt); break;
+      default: qpos[qa] += dt * qvel[da];
+    }
+  }
+  SYNC();
+}
+
+BP_STAGE void bp_advance(const C& c, typename C::DP act_dot, typename C::DP qacc,
+                         typename C::DP qvel_for_pos) {
+  const BpModel& m = c.P.m;
+  double dt = m.opt_timestep;
+  for (int i = c.lane; i < m.na; i += C::G) DF(act)[i] += dt * act_dot[i];
+  for (int i = c.lane; i < m.nv; i += C::G) DF(qvel)[i] += dt * qacc[i];
+  SYNC();
+  bp_integrate_pos(c, DF(qpos), qvel_for_pos.valid() ? qvel_for_pos : DF(qvel), dt);
+  if (c.lane == 0) DF(time)[0] += dt;
+  SYNC();
+}
+
+BP_STAGE void bp_euler(const C& c) {
+  const BpModel& m = c.P.m;
+  auto qa = DF(s_tmp);
+  if (!m.any_damping) {
+    for (int i = c.lane; i < m.nv; i += C::G) qa[i] = DF(qacc)[i];
+    SYNC();
+  } else {
+    // implicit joint damping: (M + dt diag(damping)) a = f_smooth + f_constraint
+    auto MM = DF(s_MM), qM = DF(qM);
+    for (int i = c.lane; i < m.nM; i += C::G) MM[i] = qM[i];
+    SYNC();
+    for (int i = c.lane; i < m.nv; i += C::G) {
+      MM[m.dof_Madr[i]] += m.opt_timestep * m.dof_damping[i];
+      qa[i] = DF(qfrc_smooth)[i] + DF(qfrc_constraint)[i];
+    }
+    SYNC();
+    bp_factor_sparse(c, MM, DF(s_MMdinv));
+    bp_solve_sparse(c, MM, DF(s_MMdinv), qa);
+  }
+  bp_advance(c, DF(act_dot), qa, c.null());
+}
+
+BP_STAGE void bp_rk4(const C& c) {
+  const BpModel& m = c.P.m;
+  const double A[3][3] = {{0.5, 0, 0}, {0, 0.5, 0}, {0, 0, 1}};
+  const double B[4] = {1.0 / 6, 1.0 / 3, 1.0 / 3, 1.0 / 6};
+  const double Ct[3] = {0.5, 0.5, 1.0};
+  const int nq = m.nq, nv = m.nv, na = m.na, nf = 2 * nv + na;
+  const double h = m.opt_timestep, t0 = DF(time)[0];
+  auto q0 = DF(s_rk), v0 = q0 + nq, a0 = v0 + nv, F = a0 + na, dX = F + 4 * nf;
+  SYNC();
+  for (int i = c.lane; i < nq; i += C::G) q0[i] = DF(qpos)[i];
+  for (int i = c.lane; i < nv; i += C::G) {
+    double v = DF(qvel)[i];
+    v0[i] = v; F[i] = v; F[nv + i] = DF(qacc)[i];
+  }
+  for (int i = c.lane; i < na; i += C::G) { a0[i] = DF(act)[i]; F[2 * nv + i] = DF(act_dot)[i]; }
+  SYNC();
+#pragma unroll 1
+  for (int s = 1; s < 4; s++) {
+    for (int k = c.lane; k < nf; k += C::G) {
+      double x = 0;
+      for (int j = 0; j < s; j++) x += A[s - 1][j] * F[j * nf + k];
+      dX[k] = x;
+    }
+    for (int i = c.lane; i < nq; i += C::G) DF(qpos)[i] = q0[i];
+    SYNC();
+    bp_integrate_pos(c, DF(qpos), dX, h);
+    for (int k = c.lane; k < nv; k += C::G) DF(qvel)[k] = v0[k] + h * dX[nv + k];
+    for (int k = c.lane; k < na; k += C::G) DF(act)[k] = a0[k] + h * dX[2 * nv + k];
+    if (c.lane == 0) DF(time)[0] = t0 + h * Ct[s - 1];
+    SYNC();
+    bp_forward(c, true);
+    auto Fs = F + s * nf;
+    for (int i = c.lane; i < nv; i += C::G) { Fs[i] = DF(qvel)[i]; Fs[nv + i] = DF(qacc)[i]; }
+    for (int i = c.lane; i < na; i += C::G) Fs[2 * nv + i] = DF(act_dot)[i];
+    SYNC();
+  }
+  for (int k = c.lane; k < nf; k += C::G) {
+    double x = 0;
+    for (int j = 0; j < 4; j++) x += B[j] * F[j * nf + k];
+    dX[k] = x;
+  }
+  for (int i = c.lane; i < nq; i += C::G) DF(qpos)[i] = q0[i];
+  for (int i = c.lane; i < nv; i += C::G) DF(qvel)[i] = v0[i];
+  for (int i = c.lane; i < na; i += C::G) DF(act)[i] = a0[i];
+  if (c.lane == 0) DF(time)[0] = t0;
+  SYNC();
+  bp_advance(c, dX + 2 * nv, dX + nv, dX);
+}
+
+BP_STAGE void bp_check_acc(const C& c) {
+  if (bp_check(c, DF(qacc), c.P.m.nv, W_BADQACC)) bp_forward(c, false);
+}
+
+BP_STAGE void bp_mj_step(const C& c) {
+  const BpModel& m = c.P.m;
+  bp_check(c, DF(qpos), m.nq, W_BADQPOS);
+  bp_check(c, DF(qvel), m.nv, W_BADQVEL);
+  bp_forward(c, false);
+  bp_check_acc(c);
+  if (m.opt_integrator == 1) bp_rk4(c); else bp_euler(c);
+}
+
+BP_STAGE void bp_step1(const C& c) {
+  const BpModel& m = c.P.m;
+  bp_check(c, DF(qpos), m.nq, W_BADQPOS);
+  bp_check(c, DF(qvel), m.nv, W_BADQVEL);
+  bp_fwd_position(c);
+  bp_sensors(c, STAGE_POS);
+  bp_energy_pos(c);
+  bp_fwd_velocity(c);
+  bp_sensors(c, STAGE_VEL);
+  bp_energy_vel(c);
+}
+
+BP_STAGE void bp_step2(const C& c) {
+  bp_fwd_actuation(c);
+  bp_fwd_acceleration(c);
+  bp_fwd_constraint(c);
+  bp_sensors(c, STAGE_ACC);
+  bp_check_acc(c);
+  bp_euler(c);
+}
+
+template <class C>
+__device__ __forceinline__ void bp_run_mode(const C& c) {
+  const BpParams& P = c.P;
+  switch (P.mode) {
+    case BP_MODE_STEP:
+#pragma unroll 1
+      for (int s = 0; s < P.nsub; s++) {
+        if (P.m.opt_integrator == 0) bp_step2(c); else bp_mj_step(c);
+        bp_step1(c);
+      }
+      break;
+    case BP_MODE_FORWARD: bp_forward(c, false); break;
+    case BP_MODE_STEP1: bp_step1(c); break;
+    case BP_MODE_STEP2: bp_step2(c); break;
+    case BP_MODE_MJSTEP:
+#pragma unroll 1
+      for (int s = 0; s < P.nsub; s++) bp_mj_step(c);
+      break;
+  }
+}
+
+// ---- G < 32: image in global memory, 32/G environments per warp -----------------
+template <int G, int S>
+__global__ void __launch_bounds__(128)
+bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
+  const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long env = tid / G;
+  if (env >= P.nenv || (P.mask && !P.mask[env])) return;
+  const int wl = threadIdx.x & 31;
+  double* base;
+  int* ib;
+  if (S == 1) {
+    base = P.image + env * P.stride;
+    ib = (int*)(base + P.L.ints);
+  } else {          // S == 32: [warp][element][32 envs]
+    double* wb = P.image + (env / 32) * P.stride * 32;
+    base = wb + (env & 31);
+    ib = (int*)(wb + (long long)P.L.ints * 32) + (env & 31);
+  }
+  unsigned mask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (wl & ~(G - 1)));
+  Ctx<G, S> c{P, base, ib, wl & (G - 1), mask};
+  bp_run_mode(c);
+}
+
+#endif  // BP_PIPELINE_CUH_

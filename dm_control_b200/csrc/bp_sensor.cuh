@@ -5,33 +5,35 @@
 #define BP_SENSOR_CUH_
 #include "bp_dyn.cuh"
 
-__device__ void bp_subtree_vel(const Ctx& c) {
+BP_STAGE void bp_subtree_vel(const C& c) {
   const BpModel& m = c.P.m;
   int nb = m.nbody;
-  double *lv = DF(subtree_linvel), *cvel = DF(cvel), *com = DF(subtree_com), *xipos = DF(xipos);
-  for (int b = c.lane; b < nb; b += 32) {
-    const double* cv = cvel + 6 * b;
-    const double* cm = com + 3 * m.body_rootid[b];
-    double dif[3], t[3];
+  auto lv = DF(subtree_linvel), cvel = DF(cvel), com = DF(subtree_com), xipos = DF(xipos);
+#pragma unroll 1
+  for (int b = c.lane; b < nb; b += C::G) {
+    auto cm = com + 3 * m.body_rootid[b];
+    double dif[3], t[3], cv[6];
+    for (int k = 0; k < 6; k++) cv[k] = cvel[6 * b + k];
     for (int k = 0; k < 3; k++) dif[k] = xipos[3 * b + k] - cm[k];
     cross3(t, cv, dif);
     for (int k = 0; k < 3; k++) lv[3 * b + k] = m.body_mass[b] * (cv[3 + k] + t[k]);
   }
   SYNC();
   bp_tree_gather(c, lv, 3, 0);
-  for (int w = c.lane; w < 3 * nb; w += 32) {
+  for (int w = c.lane; w < 3 * nb; w += C::G) {
     double sm = m.body_subtreemass[w / 3];
     lv[w] /= (sm > BP_MINVAL ? sm : BP_MINVAL);
   }
   SYNC();
 }
 
-__device__ __forceinline__ void bp_contact_force(const Ctx& c, int ci, double* f6) {
+template <class C>
+__device__ __forceinline__ void bp_contact_force(const C& c, int ci, double* f6) {
   for (int k = 0; k < 6; k++) f6[k] = 0;
   int a = IF(contact_efc_address)[ci];
   if (a < 0) return;
   int dim = IF(contact_dim)[ci];
-  const double* ef = DF(efc_force);
+  auto ef = DF(efc_force);
   if (dim == 1) { f6[0] = ef[a]; return; }
   if (c.P.m.opt_cone == 0) {
     for (int k = 0; k < 2 * (dim - 1); k++) f6[0] += ef[a + k];
@@ -42,25 +44,27 @@ __device__ __forceinline__ void bp_contact_force(const Ctx& c, int ci, double* f
   }
 }
 
-__device__ void bp_rne_post_constraint(const Ctx& c) {
+BP_STAGE void bp_rne_post_constraint(const C& c) {
   const BpModel& m = c.P.m;
-  int nb = m.nbody, ncon = *IF(ncon);
-  double *ext = DF(cfrc_ext), *com = DF(subtree_com);
+  int nb = m.nbody, ncon = IF(ncon)[0];
+  auto ext = DF(cfrc_ext), com = DF(subtree_com);
   // each body gathers its own contacts in contact order (no atomics, fixed order)
-  for (int b = c.lane; b < nb; b += 32) {
+#pragma unroll 1
+  for (int b = c.lane; b < nb; b += C::G) {
     double acc[6] = {0, 0, 0, 0, 0, 0};
-    if (b > 0)
+    if (b > 0) {
+#pragma unroll 1
       for (int ci = 0; ci < ncon; ci++) {
         if (IF(contact_efc_address)[ci] < 0) continue;
         int b1 = m.geom_bodyid[IF(contact_geom1)[ci]], b2 = m.geom_bodyid[IF(contact_geom2)[ci]];
         if (b1 != b && b2 != b) continue;
-        double f6[6], fw[3], tw[3];
+        double f6[6], fw[3], tw[3], fr[9];
         bp_contact_force(c, ci, f6);
-        const double* fr = DF(contact_frame) + 9 * ci;
+        for (int k = 0; k < 9; k++) fr[k] = DF(contact_frame)[9 * ci + k];
         matT_vec3(fw, fr, f6);
         matT_vec3(tw, fr, f6 + 3);
-        const double* pos = DF(contact_pos) + 3 * ci;
-        const double* cm = com + 3 * m.body_rootid[b];
+        auto pos = DF(contact_pos) + 3 * ci;
+        auto cm = com + 3 * m.body_rootid[b];
         double dif[3] = {pos[0] - cm[0], pos[1] - cm[1], pos[2] - cm[2]}, t[3];
         cross3(t, dif, fw);
         for (int side = 0; side < 2; side++) {
@@ -69,15 +73,17 @@ __device__ void bp_rne_post_constraint(const Ctx& c) {
           for (int k = 0; k < 3; k++) { acc[k] += sgn * (tw[k] + t[k]); acc[3 + k] += sgn * fw[k]; }
         }
       }
+    }
     for (int k = 0; k < 6; k++) ext[6 * b + k] = acc[k];
   }
   SYNC();
-  bp_rne(c, true, DF(cacc), DF(cfrc_int), ext, nullptr, 1);
+  bp_rne(c, true, DF(cacc), DF(cfrc_int), ext, c.null(), 1);
 }
 
-__device__ __forceinline__ bool bp_inside_site(const Ctx& c, int s, const double* p) {
+template <class C>
+__device__ __forceinline__ bool bp_inside_site(const C& c, int s, const double* p) {
   const BpModel& m = c.P.m;
-  const double* sp = DF(site_xpos) + 3 * s;
+  auto sp = DF(site_xpos) + 3 * s;
   double dif[3] = {p[0] - sp[0], p[1] - sp[1], p[2] - sp[2]}, l[3];
   matT_vec3(l, DF(site_xmat) + 9 * s, dif);
   const double* sz = m.site_size + 3 * s;
@@ -98,28 +104,33 @@ __device__ __forceinline__ bool bp_inside_site(const Ctx& c, int s, const double
   return false;
 }
 
-__device__ __forceinline__ void bp_obj_frame(const Ctx& c, int objtype, int id,
-                                             const double** pos, const double** mat,
-                                             int* body) {
+// frame of a sensor's object copied to registers: pos[3], mat[9], owning body
+template <class C>
+__device__ __forceinline__ int bp_obj_frame(const C& c, int objtype, int id, double* pos,
+                                            double* mat) {
   const BpModel& m = c.P.m;
-  if (objtype == OBJ_SITE) { *pos = DF(site_xpos) + 3 * id; *mat = DF(site_xmat) + 9 * id; *body = m.site_bodyid[id]; }
-  else if (objtype == OBJ_GEOM) { *pos = DF(geom_xpos) + 3 * id; *mat = DF(geom_xmat) + 9 * id; *body = m.geom_bodyid[id]; }
-  else if (objtype == OBJ_XBODY) { *pos = DF(xpos) + 3 * id; *mat = DF(xmat) + 9 * id; *body = id; }
-  else { *pos = DF(xipos) + 3 * id; *mat = DF(ximat) + 9 * id; *body = id; }
+  typename C::DP p, R;
+  int body;
+  if (objtype == OBJ_SITE) { p = DF(site_xpos) + 3 * id; R = DF(site_xmat) + 9 * id; body = m.site_bodyid[id]; }
+  else if (objtype == OBJ_GEOM) { p = DF(geom_xpos) + 3 * id; R = DF(geom_xmat) + 9 * id; body = m.geom_bodyid[id]; }
+  else if (objtype == OBJ_XBODY) { p = DF(xpos) + 3 * id; R = DF(xmat) + 9 * id; body = id; }
+  else { p = DF(xipos) + 3 * id; R = DF(ximat) + 9 * id; body = id; }
+  for (int k = 0; k < 3; k++) pos[k] = p[k];
+  for (int k = 0; k < 9; k++) mat[k] = R[k];
+  return body;
 }
 
-__device__ void bp_sensors(const Ctx& c, int stage) {
+BP_STAGE void bp_sensors(const C& c, int stage) {
   const BpModel& m = c.P.m;
   if (m.nsensor == 0) return;
   if (stage == STAGE_VEL && m.need_subtreevel) bp_subtree_vel(c);
   if (stage == m.need_rnepost_stage) bp_rne_post_constraint(c);
-  double* sd = DF(sensordata);
-  for (int s = c.lane; s < m.nsensor; s += 32) {
+  auto sd = DF(sensordata);
+#pragma unroll 1
+  for (int s = c.lane; s < m.nsensor; s += C::G) {
     if (m.sensor_needstage[s] != stage) continue;
-    int t = m.sensor_type[s], id = m.sensor_objid[s];
-    double* out = sd + m.sensor_adr[s];
-    const double *pos, *mat;
-    int body;
+    int t = m.sensor_type[s], id = m.sensor_objid[s], dim = m.sensor_dim[s];
+    double out[3] = {0, 0, 0}, pos[3], mat[9];
     switch (t) {
       case SENS_JOINTPOS: out[0] = DF(qpos)[m.jnt_qposadr[id]]; break;
       case SENS_JOINTVEL: out[0] = DF(qvel)[m.jnt_dofadr[id]]; break;
@@ -127,13 +138,14 @@ __device__ void bp_sensors(const Ctx& c, int stage) {
       case SENS_SUBTREECOM: for (int k = 0; k < 3; k++) out[k] = DF(subtree_com)[3 * id + k]; break;
       case SENS_SUBTREELINVEL: for (int k = 0; k < 3; k++) out[k] = DF(subtree_linvel)[3 * id + k]; break;
       case SENS_FRAMEPOS:
-        bp_obj_frame(c, m.sensor_objtype[s], id, &pos, &mat, &body);
+        bp_obj_frame(c, m.sensor_objtype[s], id, pos, mat);
         for (int k = 0; k < 3; k++) out[k] = pos[k];
         break;
       case SENS_VELOCIMETER: case SENS_GYRO: case SENS_ACCELEROMETER: {
-        bp_obj_frame(c, OBJ_SITE, id, &pos, &mat, &body);
-        const double* cm = DF(subtree_com) + 3 * m.body_rootid[body];
-        const double* cv = DF(cvel) + 6 * body;
+        int body = bp_obj_frame(c, OBJ_SITE, id, pos, mat);
+        auto cm = DF(subtree_com) + 3 * m.body_rootid[body];
+        double cv[6];
+        for (int k = 0; k < 6; k++) cv[k] = DF(cvel)[6 * body + k];
         double dif[3] = {pos[0] - cm[0], pos[1] - cm[1], pos[2] - cm[2]};
         double t3[3], vlin[3], wl[3], vl[3];
         cross3(t3, cv, dif);
@@ -143,7 +155,8 @@ __device__ void bp_sensors(const Ctx& c, int stage) {
         if (t == SENS_GYRO) { for (int k = 0; k < 3; k++) out[k] = wl[k]; }
         else if (t == SENS_VELOCIMETER) { for (int k = 0; k < 3; k++) out[k] = vl[k]; }
         else {
-          const double* ca = DF(cacc) + 6 * body;
+          double ca[6];
+          for (int k = 0; k < 6; k++) ca[k] = DF(cacc)[6 * body + k];
           double alin[3], al[3], cor[3];
           cross3(t3, ca, dif);
           for (int k = 0; k < 3; k++) alin[k] = ca[3 + k] + t3[k];
@@ -154,31 +167,32 @@ __device__ void bp_sensors(const Ctx& c, int stage) {
         break;
       }
       case SENS_FORCE: case SENS_TORQUE: {
-        bp_obj_frame(c, OBJ_SITE, id, &pos, &mat, &body);
-        const double* cm = DF(subtree_com) + 3 * m.body_rootid[body];
-        const double* cf = DF(cfrc_int) + 6 * body;
-        double r3[3];
-        if (t == SENS_FORCE) matT_vec3(r3, mat, cf + 3);
+        int body = bp_obj_frame(c, OBJ_SITE, id, pos, mat);
+        auto cm = DF(subtree_com) + 3 * m.body_rootid[body];
+        double cf[6];
+        for (int k = 0; k < 6; k++) cf[k] = DF(cfrc_int)[6 * body + k];
+        if (t == SENS_FORCE) matT_vec3(out, mat, cf + 3);
         else {
           double dif[3] = {pos[0] - cm[0], pos[1] - cm[1], pos[2] - cm[2]}, t3[3], tq[3];
           cross3(t3, dif, cf + 3);
           for (int k = 0; k < 3; k++) tq[k] = cf[k] - t3[k];
-          matT_vec3(r3, mat, tq);
+          matT_vec3(out, mat, tq);
         }
-        for (int k = 0; k < 3; k++) out[k] = r3[k];
         break;
       }
       case SENS_TOUCH: {
-        int sb = m.site_bodyid[id], ncon = *IF(ncon);
+        int sb = m.site_bodyid[id], ncon = IF(ncon)[0];
         double tot = 0;
+#pragma unroll 1
         for (int ci = 0; ci < ncon; ci++) {
           if (IF(contact_efc_address)[ci] < 0) continue;
           if (m.geom_bodyid[IF(contact_geom1)[ci]] != sb &&
               m.geom_bodyid[IF(contact_geom2)[ci]] != sb) continue;
-          double f6[6];
+          double f6[6], cp[3];
           bp_contact_force(c, ci, f6);
           if (f6[0] <= 0) continue;
-          if (bp_inside_site(c, id, DF(contact_pos) + 3 * ci)) tot += f6[0];
+          for (int k = 0; k < 3; k++) cp[k] = DF(contact_pos)[3 * ci + k];
+          if (bp_inside_site(c, id, cp)) tot += f6[0];
         }
         out[0] = tot;
         break;
@@ -186,48 +200,55 @@ __device__ void bp_sensors(const Ctx& c, int stage) {
     }
     double cut = m.sensor_cutoff[s];
     if (cut > 0)
-      for (int k = 0; k < m.sensor_dim[s]; k++) {
+      for (int k = 0; k < 3; k++) {
         if (t == SENS_TOUCH) { if (out[k] > cut) out[k] = cut; }
         else out[k] = clampd(out[k], -cut, cut);
       }
+    int adr = m.sensor_adr[s];
+    for (int k = 0; k < dim && k < 3; k++) sd[adr + k] = out[k];
   }
   SYNC();
 }
 
-__device__ void bp_energy_pos(const Ctx& c) {
+BP_STAGE void bp_energy_pos(const C& c) {
   const BpModel& m = c.P.m;
-  double* en = DF(energy);
-  if (!(m.opt_enableflags & ENBL_ENERGY)) { if (c.lane < 2) en[c.lane] = 0; SYNC(); return; }
+  auto en = DF(energy);
+  if (!(m.opt_enableflags & ENBL_ENERGY)) {
+    for (int i = c.lane; i < 2; i += C::G) en[i] = 0;
+    SYNC();
+    return;
+  }
   double e = 0;
   if (!(m.opt_disableflags & DSBL_GRAVITY))
-    for (int b = 1 + c.lane; b < m.nbody; b += 32)
+    for (int b = 1 + c.lane; b < m.nbody; b += C::G)
       e -= m.body_mass[b] * dot3(m.opt_gravity, DF(xipos) + 3 * b);
   if (!(m.opt_disableflags & DSBL_PASSIVE))
-    for (int j = c.lane; j < m.njnt; j += 32) {
+    for (int j = c.lane; j < m.njnt; j += C::G) {
       int jt = m.jnt_type[j], qa = m.jnt_qposadr[j];
       if (jt == JNT_SLIDE || jt == JNT_HINGE) {
         double dq = DF(qpos)[qa] - m.qpos_spring[qa];
         e += 0.5 * m.jnt_stiffness[j] * dq * dq;
       }
     }
-  e = warp_sum(e);
+  e = group_sum(c, e);
   if (c.lane == 0) en[0] = e;
   SYNC();
 }
 
 // kinetic energy 0.5 v^T M v from the sparse qM
-__device__ void bp_energy_vel(const Ctx& c) {
+BP_STAGE void bp_energy_vel(const C& c) {
   const BpModel& m = c.P.m;
   if (!(m.opt_enableflags & ENBL_ENERGY)) return;
-  const double *qM = DF(qM), *v = DF(qvel);
+  auto qM = DF(qM), v = DF(qvel);
   double e = 0;
-  for (int i = c.lane; i < m.nv; i += 32) {
+#pragma unroll 1
+  for (int i = c.lane; i < m.nv; i += C::G) {
     int a = m.dof_Madr[i];
     double s = 0.5 * qM[a++] * v[i];
     for (int j = m.dof_parentid[i]; j >= 0; j = m.dof_parentid[j]) s += qM[a++] * v[j];
     e += s * v[i];
   }
-  e = warp_sum(e);
+  e = group_sum(c, e);
   if (c.lane == 0) DF(energy)[1] = e;
   SYNC();
 }

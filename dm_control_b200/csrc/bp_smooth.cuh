@@ -1,37 +1,42 @@
-// Position-stage smooth dynamics, one warp per environment, state in shared memory:
-// kinematics, mj_comPos, mj_crb, sparse L^T D L factor/solve.
+// Position-stage smooth dynamics: kinematics, mj_comPos, mj_crb, sparse L^T D L
+// factor/solve, for a group of G lanes per environment (bp_math.cuh).
 //
 // These are the stages the reference reaches through `mj_step1`
 // (/root/reference/dm_control/mujoco/engine.py:166).  Tree
 // recursions run level by level (bodies of equal depth on different lanes);
 // backward accumulations gather children in descending id, i.e. the order of a
-// serial loop over body ids, so sums are reproducible.
+// serial loop over body ids, so sums are reproducible for every G.
 #ifndef BP_SMOOTH_CUH_
 #define BP_SMOOTH_CUH_
 #include "bp_math.cuh"
 
-__device__ void bp_kinematics(const Ctx& c) {
+BP_STAGE void bp_kinematics(const C& c) {
   const BpModel& m = c.P.m;
-  double *qpos = DF(qpos), *xpos = DF(xpos), *xquat = DF(xquat), *xmat = DF(xmat);
-  double *xanchor = DF(xanchor), *xaxis = DF(xaxis);
-  for (int j = c.lane; j < m.njnt; j += 32) {
+  auto qpos = DF(qpos), xpos = DF(xpos), xquat = DF(xquat), xmat = DF(xmat);
+  auto xanchor = DF(xanchor), xaxis = DF(xaxis);
+  for (int j = c.lane; j < m.njnt; j += C::G) {
     int jt = m.jnt_type[j];
-    if (jt == JNT_FREE) normalize4(qpos + m.jnt_qposadr[j] + 3);
+    if (jt == JNT_FREE) normalize4(qpos + (m.jnt_qposadr[j] + 3));
     else if (jt == JNT_BALL) normalize4(qpos + m.jnt_qposadr[j]);
   }
-  if (c.lane < 3) xpos[c.lane] = 0;
-  if (c.lane < 4) xquat[c.lane] = c.lane == 0 ? 1.0 : 0.0;
-  if (c.lane < 9) xmat[c.lane] = (c.lane % 4 == 0) ? 1.0 : 0.0;
+  for (int i = c.lane; i < 9; i += C::G) {
+    if (i < 3) xpos[i] = 0;
+    if (i < 4) xquat[i] = i == 0 ? 1.0 : 0.0;
+    xmat[i] = (i % 4 == 0) ? 1.0 : 0.0;
+  }
   SYNC();
+#pragma unroll 1
   for (int lev = 1; lev < m.nlevel; lev++) {
+#pragma unroll 1
     for (int idx = m.body_level_adr[lev] + c.lane; idx < m.body_level_adr[lev + 1];
-         idx += 32) {
+         idx += C::G) {
       int b = m.body_level_list[idx], p = m.body_parentid[b];
       double pos[3], quat[4], R[9], t[3];
       mat_vec3(t, xmat + 9 * p, m.body_pos + 3 * b);
       for (int k = 0; k < 3; k++) pos[k] = xpos[3 * p + k] + t[k];
       quat_mul(quat, xquat + 4 * p, m.body_quat + 4 * b);
       int jn = m.body_jntnum[b], j0 = m.body_jntadr[b];
+#pragma unroll 1
       for (int k = 0; k < jn; k++) {
         int j = j0 + k, qa = m.jnt_qposadr[j], jt = m.jnt_type[j];
         if (jt == JNT_FREE) {
@@ -70,9 +75,10 @@ __device__ void bp_kinematics(const Ctx& c) {
   }
   // inertial frames, geoms and sites hang off finished body frames: one flat loop
   int nb = m.nbody, ng = m.ngeom, ns = m.nsite;
-  for (int w = c.lane; w < nb + ng + ns; w += 32) {
+#pragma unroll 1
+  for (int w = c.lane; w < nb + ng + ns; w += C::G) {
     const double *lp, *lq;
-    double *op, *om;
+    typename C::DP op, om;
     int b;
     if (w < nb) {
       b = w; lp = m.body_ipos + 3 * w; lq = m.body_iquat + 4 * w;
@@ -98,16 +104,18 @@ __device__ void bp_kinematics(const Ctx& c) {
 
 // vals[b*n .. b*n+n) += sum over children, from the deepest level up to `stop_level`
 // (stop_level = 0 also accumulates into the world body, 1 leaves it untouched)
-__device__ __forceinline__ void bp_tree_gather(const Ctx& c, double* vals, int n,
-                                               int stop_level) {
+BP_STAGE void bp_tree_gather(const C& c, typename C::DP vals, int n, int stop_level) {
   const BpModel& m = c.P.m;
+#pragma unroll 1
   for (int lev = m.nlevel - 2; lev >= stop_level; lev--) {
     int a0 = m.body_level_adr[lev], cnt = m.body_level_adr[lev + 1] - a0;
-    for (int w = c.lane; w < cnt * n; w += 32) {
+#pragma unroll 1
+    for (int w = c.lane; w < cnt * n; w += C::G) {
       int b = m.body_level_list[a0 + w / n], k = w % n;
       int c0 = m.body_child_adr[b], c1 = m.body_child_adr[b + 1];
       if (c1 > c0) {
         double s = vals[b * n + k];
+#pragma unroll 1
         for (int ci = c0; ci < c1; ci++) s += vals[m.body_child_list[ci] * n + k];
         vals[b * n + k] = s;
       }
@@ -116,30 +124,32 @@ __device__ __forceinline__ void bp_tree_gather(const Ctx& c, double* vals, int n
   }
 }
 
-__device__ void bp_com_pos(const Ctx& c) {
+BP_STAGE void bp_com_pos(const C& c) {
   const BpModel& m = c.P.m;
   int nb = m.nbody;
-  double *com = DF(subtree_com), *xipos = DF(xipos);
-  for (int w = c.lane; w < 3 * nb; w += 32) com[w] = m.body_mass[w / 3] * xipos[w];
+  auto com = DF(subtree_com), xipos = DF(xipos);
+  for (int w = c.lane; w < 3 * nb; w += C::G) com[w] = m.body_mass[w / 3] * xipos[w];
   SYNC();
   bp_tree_gather(c, com, 3, 0);
-  for (int w = c.lane; w < 3 * nb; w += 32) {
+  for (int w = c.lane; w < 3 * nb; w += C::G) {
     double sm = m.body_subtreemass[w / 3];
     com[w] = sm < BP_MINVAL ? xipos[w] : com[w] / sm;
   }
   SYNC();
-  double *cinert = DF(cinert), *ximat = DF(ximat);
-  for (int b = 1 + c.lane; b < nb; b += 32) {
-    const double* R = ximat + 9 * b;
+  auto cinert = DF(cinert), ximat = DF(ximat);
+#pragma unroll 1
+  for (int b = 1 + c.lane; b < nb; b += C::G) {
+    auto R = ximat + 9 * b;
     const double* I = m.body_inertia + 3 * b;
-    const double* cm = com + 3 * m.body_rootid[b];
-    double mass = m.body_mass[b], dif[3], T[9];
+    auto cm = com + 3 * m.body_rootid[b];
+    double mass = m.body_mass[b], dif[3], T[9], Rl[9];
+    for (int k = 0; k < 9; k++) Rl[k] = R[k];
     for (int k = 0; k < 3; k++) dif[k] = xipos[3 * b + k] - cm[k];
     for (int r = 0; r < 3; r++)
       for (int k = r; k < 3; k++)
-        T[3 * r + k] = R[3 * r] * I[0] * R[3 * k] + R[3 * r + 1] * I[1] * R[3 * k + 1] +
-                       R[3 * r + 2] * I[2] * R[3 * k + 2];
-    double* ci = cinert + 10 * b;
+        T[3 * r + k] = Rl[3 * r] * I[0] * Rl[3 * k] + Rl[3 * r + 1] * I[1] * Rl[3 * k + 1] +
+                       Rl[3 * r + 2] * I[2] * Rl[3 * k + 2];
+    auto ci = cinert + 10 * b;
     ci[0] = T[0] + mass * (dif[1] * dif[1] + dif[2] * dif[2]);
     ci[1] = T[4] + mass * (dif[0] * dif[0] + dif[2] * dif[2]);
     ci[2] = T[8] + mass * (dif[0] * dif[0] + dif[1] * dif[1]);
@@ -149,32 +159,33 @@ __device__ void bp_com_pos(const Ctx& c) {
     ci[6] = mass * dif[0]; ci[7] = mass * dif[1]; ci[8] = mass * dif[2];
     ci[9] = mass;
   }
-  if (c.lane < 10) cinert[c.lane] = 0;
-  double *cdof = DF(cdof), *xanchor = DF(xanchor), *xaxis = DF(xaxis), *xmat = DF(xmat);
-  for (int j = c.lane; j < m.njnt; j += 32) {
+  for (int i = c.lane; i < 10; i += C::G) cinert[i] = 0;
+  auto cdof = DF(cdof), xanchor = DF(xanchor), xaxis = DF(xaxis), xmat = DF(xmat);
+#pragma unroll 1
+  for (int j = c.lane; j < m.njnt; j += C::G) {
     int b = m.jnt_bodyid[j], da = m.jnt_dofadr[j], jt = m.jnt_type[j];
-    const double* cm = com + 3 * m.body_rootid[b];
+    auto cm = com + 3 * m.body_rootid[b];
     double off[3];
     for (int k = 0; k < 3; k++) off[k] = cm[k] - xanchor[3 * j + k];
     if (jt == JNT_SLIDE) {
-      double* cd = cdof + 6 * da;
+      auto cd = cdof + 6 * da;
       for (int k = 0; k < 3; k++) { cd[k] = 0; cd[3 + k] = xaxis[3 * j + k]; }
     } else if (jt == JNT_HINGE) {
-      double* cd = cdof + 6 * da;
+      auto cd = cdof + 6 * da;
       double ax[3] = {xaxis[3 * j], xaxis[3 * j + 1], xaxis[3 * j + 2]}, t[3];
       cross3(t, ax, off);
       for (int k = 0; k < 3; k++) { cd[k] = ax[k]; cd[3 + k] = t[k]; }
     } else {
       if (jt == JNT_FREE) {
         for (int k = 0; k < 3; k++) {
-          double* cd = cdof + 6 * (da + k);
+          auto cd = cdof + 6 * (da + k);
           for (int i = 0; i < 6; i++) cd[i] = (i == 3 + k) ? 1.0 : 0.0;
         }
         da += 3;
       }
-      const double* R = xmat + 9 * b;
+      auto R = xmat + 9 * b;
       for (int k = 0; k < 3; k++) {
-        double* cd = cdof + 6 * (da + k);
+        auto cd = cdof + 6 * (da + k);
         double ax[3] = {R[k], R[3 + k], R[6 + k]}, t[3];
         cross3(t, ax, off);
         for (int i = 0; i < 3; i++) { cd[i] = ax[i]; cd[3 + i] = t[i]; }
@@ -184,17 +195,19 @@ __device__ void bp_com_pos(const Ctx& c) {
   SYNC();
 }
 
-__device__ void bp_crb(const Ctx& c) {
+BP_STAGE void bp_crb(const C& c) {
   const BpModel& m = c.P.m;
-  double *crb = DF(crb), *cinert = DF(cinert), *cdof = DF(cdof), *qM = DF(qM);
-  for (int w = c.lane; w < 10 * m.nbody; w += 32) crb[w] = cinert[w];
+  auto crb = DF(crb), cinert = DF(cinert), cdof = DF(cdof), qM = DF(qM);
+  for (int w = c.lane; w < 10 * m.nbody; w += C::G) crb[w] = cinert[w];
   SYNC();
   bp_tree_gather(c, crb, 10, 1);
-  for (int i = c.lane; i < m.nv; i += 32) {
+#pragma unroll 1
+  for (int i = c.lane; i < m.nv; i += C::G) {
     double buf[6];
     inert_mul(buf, crb + 10 * m.dof_bodyid[i], cdof + 6 * i);
     int adr = m.dof_Madr[i];
     qM[adr++] = m.dof_armature[i] + dot6(cdof + 6 * i, buf);
+#pragma unroll 1
     for (int j = m.dof_parentid[i]; j >= 0; j = m.dof_parentid[j])
       qM[adr++] = dot6(cdof + 6 * j, buf);
   }
@@ -202,42 +215,46 @@ __device__ void bp_crb(const Ctx& c) {
 }
 
 // in-place sparse L^T D L of a matrix in qM layout; row k's ancestors on lanes
-__device__ void bp_factor_sparse(const Ctx& c, double* LD, double* diaginv) {
+BP_STAGE void bp_factor_sparse(const C& c, typename C::DP LD, typename C::DP diaginv) {
   const BpModel& m = c.P.m;
+#pragma unroll 1
   for (int k = m.nv - 1; k >= 0; k--) {
     int akk = m.dof_Madr[k], na = m.dof_depth[k];
     double dkk = LD[akk];
-    // lane a handles ancestor a (1-based position in row k)
-    double t = 0;
-    for (int a = 1 + c.lane; a <= na; a += 32) {
-      t = LD[akk + a] / dkk;
+#pragma unroll 1
+    for (int a = 1 + c.lane; a <= na; a += C::G) {
+      double t = LD[akk + a] / dkk;
       int i = m.M_col[akk + a];
       int aij = m.dof_Madr[i];
+#pragma unroll 1
       for (int b = a; b <= na; b++) LD[aij++] -= t * LD[akk + b];
     }
     SYNC();
-    for (int a = 1 + c.lane; a <= na; a += 32) LD[akk + a] = LD[akk + a] / dkk;
+    for (int a = 1 + c.lane; a <= na; a += C::G) LD[akk + a] = LD[akk + a] / dkk;
     if (c.lane == 0) diaginv[k] = 1.0 / dkk;
     SYNC();
   }
 }
 
 // x <- M^-1 x with the factor above
-__device__ void bp_solve_sparse(const Ctx& c, const double* LD, const double* diaginv,
-                                double* x) {
+BP_STAGE void bp_solve_sparse(const C& c, typename C::DP LD, typename C::DP diaginv,
+                              typename C::DP x) {
   const BpModel& m = c.P.m;
   int nv = m.nv;
+#pragma unroll 1
   for (int i = nv - 1; i >= 0; i--) {          // x <- L^-T x
     int a0 = m.dof_Madr[i] + 1, na = m.dof_depth[i];
     double xi = x[i];
-    for (int a = c.lane; a < na; a += 32) x[m.M_col[a0 + a]] -= LD[a0 + a] * xi;
+    for (int a = c.lane; a < na; a += C::G) x[m.M_col[a0 + a]] -= LD[a0 + a] * xi;
     SYNC();
   }
-  for (int i = c.lane; i < nv; i += 32) x[i] *= diaginv[i];
+  for (int i = c.lane; i < nv; i += C::G) x[i] *= diaginv[i];
   SYNC();
+#pragma unroll 1
   for (int lev = 1; lev < m.ndoflevel; lev++) { // x <- L^-1 x, depth by depth
+#pragma unroll 1
     for (int idx = m.dof_level_adr[lev] + c.lane; idx < m.dof_level_adr[lev + 1];
-         idx += 32) {
+         idx += C::G) {
       int i = m.dof_level_list[idx], a = m.dof_Madr[i] + 1;
       double s = x[i];
       for (int j = m.dof_parentid[i]; j >= 0; j = m.dof_parentid[j]) s -= LD[a++] * x[j];

@@ -1,6 +1,6 @@
 // mj_fwdConstraint: primal Newton solver in qacc with exact line search
-// (SURVEY.md §8a row a2, Appendix A.9).  One warp per environment:
-//   rows of J on lanes for J*x products, cost/line-search sums by warp shuffles,
+// (SURVEY.md §8a row a2, Appendix A.9).  Per environment group of G lanes:
+//   rows of J on lanes for J*x products, cost/line-search sums by group shuffles,
 //   Hessian M + J^T D J one lower-triangle entry per lane, dense Cholesky with
 //   rows on lanes.
 #ifndef BP_SOLVER_CUH_
@@ -8,10 +8,10 @@
 #include "bp_math.cuh"
 
 // y = Md * x, dense symmetric nv x nv with row stride nvp (odd => conflict free)
-__device__ __forceinline__ void bp_mul_md(const Ctx& c, const double* Md, double* y,
-                                          const double* x) {
+BP_STAGE void bp_mul_md(const C& c, typename C::DP Md, typename C::DP y, typename C::DP x) {
   const int nv = c.P.m.nv, nvp = c.P.m.nvp;
-  for (int i = c.lane; i < nv; i += 32) {
+#pragma unroll 1
+  for (int i = c.lane; i < nv; i += C::G) {
     double s = 0;
     for (int j = 0; j < nv; j++) s += Md[i * nvp + j] * x[j];
     y[i] = s;
@@ -20,26 +20,27 @@ __device__ __forceinline__ void bp_mul_md(const Ctx& c, const double* Md, double
 }
 
 // out[r] = J[r,:] x - (sub ? sub[r] : 0)
-__device__ __forceinline__ void bp_mul_j(const Ctx& c, double* out, const double* x,
-                                         const double* sub, int nefc) {
+BP_STAGE void bp_mul_j(const C& c, typename C::DP out, typename C::DP x, typename C::DP sub,
+                       int nefc) {
   const int nv = c.P.m.nv, nvp = c.P.m.nvp;
-  const double* J = DF(efc_J);
-  for (int r = c.lane; r < nefc; r += 32) {
+  auto J = DF(efc_J);
+#pragma unroll 1
+  for (int r = c.lane; r < nefc; r += C::G) {
     double s = 0;
     for (int i = 0; i < nv; i++) s += J[r * nvp + i] * x[i];
-    out[r] = sub ? s - sub[r] : s;
+    out[r] = sub.valid() ? s - sub[r] : s;
   }
   SYNC();
 }
 
 // constraint cost at residual jar; optionally writes force/state and J^T force
-__device__ double bp_update_constraint(const Ctx& c, const double* jar, int nefc,
-                                       bool write) {
+BP_STAGE double bp_update_constraint(const C& c, typename C::DP jar, int nefc, bool write) {
   const int nv = c.P.m.nv, nvp = c.P.m.nvp;
   double cost = 0;
-  double *force = DF(efc_force), *D = DF(efc_D), *R = DF(efc_R);
-  int *type = IF(efc_type), *state = IF(efc_state);
-  for (int r = c.lane; r < nefc; r += 32) {
+  auto force = DF(efc_force), D = DF(efc_D), R = DF(efc_R);
+  auto type = IF(efc_type), state = IF(efc_state);
+#pragma unroll 1
+  for (int r = c.lane; r < nefc; r += C::G) {
     double d = D[r], x = jar[r], f, cr = 0;
     int t = type[r], st;
     if (t == CN_EQUALITY) { f = -d * x; st = ST_QUADRATIC; cr = 0.5 * d * x * x; }
@@ -55,12 +56,13 @@ __device__ double bp_update_constraint(const Ctx& c, const double* jar, int nefc
     cost += cr;
     if (write) { force[r] = f; state[r] = st; }
   }
-  cost = warp_sum(cost);
+  cost = group_sum(c, cost);
   if (write) {
     SYNC();
-    const double* J = DF(efc_J);
-    double* qc = DF(qfrc_constraint);
-    for (int i = c.lane; i < nv; i += 32) {
+    auto J = DF(efc_J);
+    auto qc = DF(qfrc_constraint);
+#pragma unroll 1
+    for (int i = c.lane; i < nv; i += C::G) {
       double s = 0;
       for (int r = 0; r < nefc; r++) s += J[r * nvp + i] * force[r];
       qc[i] = s;
@@ -70,21 +72,23 @@ __device__ double bp_update_constraint(const Ctx& c, const double* jar, int nefc
   return cost;
 }
 
-__device__ __forceinline__ double bp_gauss_cost(const Ctx& c) {
+template <class C>
+__device__ __forceinline__ double bp_gauss_cost(const C& c) {
   double g = 0;
-  for (int i = c.lane; i < c.P.m.nv; i += 32)
+  for (int i = c.lane; i < c.P.m.nv; i += C::G)
     g += 0.5 * (DF(s_Ma)[i] - DF(qfrc_smooth)[i]) * (DF(qacc)[i] - DF(qacc_smooth)[i]);
-  return warp_sum(g);
+  return group_sum(c, g);
 }
 
 struct LSPoint { double cost, d0, d1; };
 
-__device__ LSPoint bp_ls_eval(const Ctx& c, double alpha, double g0, double g1, double g2,
-                              int nefc) {
+BP_STAGE LSPoint bp_ls_eval(const C& c, double alpha, double g0, double g1, double g2,
+                            int nefc) {
   double c0 = 0, c1 = 0, c2 = 0;
-  const double *D = DF(efc_D), *jar = DF(s_jar), *jvv = DF(s_jv);
-  const int* type = IF(efc_type);
-  for (int r = c.lane; r < nefc; r += 32) {
+  auto D = DF(efc_D), jar = DF(s_jar), jvv = DF(s_jv);
+  auto type = IF(efc_type);
+#pragma unroll 1
+  for (int r = c.lane; r < nefc; r += C::G) {
     double d = D[r], j0 = jar[r], jv = jvv[r], x = j0 + alpha * jv;
     int t = type[r];
     double q0 = 0.5 * d * j0 * j0, q1 = d * j0 * jv, q2 = 0.5 * d * jv * jv;
@@ -96,7 +100,7 @@ __device__ LSPoint bp_ls_eval(const Ctx& c, double alpha, double g0, double g1, 
       else { c0 += q0; c1 += q1; c2 += q2; }
     } else if (x < 0) { c0 += q0; c1 += q1; c2 += q2; }
   }
-  c0 = g0 + warp_sum(c0); c1 = g1 + warp_sum(c1); c2 = g2 + warp_sum(c2);
+  c0 = g0 + group_sum(c, c0); c1 = g1 + group_sum(c, c1); c2 = g2 + group_sum(c, c2);
   LSPoint p;
   p.cost = alpha * alpha * c2 + alpha * c1 + c0;
   p.d0 = 2 * alpha * c2 + c1;
@@ -105,23 +109,25 @@ __device__ LSPoint bp_ls_eval(const Ctx& c, double alpha, double g0, double g1, 
 }
 
 // exact 1-D minimisation along s_search (safeguarded Newton on the derivative)
-__device__ double bp_linesearch(const Ctx& c, double scale, int nefc) {
+BP_STAGE double bp_linesearch(const C& c, double scale, int nefc) {
   const BpModel& m = c.P.m;
   double sn = 0, g0 = 0, g1 = 0, g2 = 0;
-  for (int i = c.lane; i < m.nv; i += 32) {
+  for (int i = c.lane; i < m.nv; i += C::G) {
     double s = DF(s_search)[i], r = DF(s_Ma)[i] - DF(qfrc_smooth)[i];
     sn += s * s;
     g0 += 0.5 * r * (DF(qacc)[i] - DF(qacc_smooth)[i]);
     g1 += s * r;
     g2 += 0.5 * s * DF(s_Mv)[i];
   }
-  sn = sqrt(warp_sum(sn)); g0 = warp_sum(g0); g1 = warp_sum(g1); g2 = warp_sum(g2);
+  sn = sqrt(group_sum(c, sn)); g0 = group_sum(c, g0); g1 = group_sum(c, g1);
+  g2 = group_sum(c, g2);
   if (sn < BP_MINVAL) return 0;
   double gtol = m.opt_tolerance * m.opt_ls_tolerance * sn / scale;
   LSPoint p = bp_ls_eval(c, 0, g0, g1, g2, nefc);
   if (p.d1 < BP_MINVAL) return 0;
   double lo = 0, hi = 0, a = -p.d0 / p.d1;
   bool have_hi = false;
+#pragma unroll 1
   for (int it = 0; it < m.opt_ls_iterations; it++) {
     p = bp_ls_eval(c, a, g0, g1, g2, nefc);
     if (fabs(p.d0) < gtol) break;
@@ -135,18 +141,20 @@ __device__ double bp_linesearch(const Ctx& c, double scale, int nefc) {
 
 // dense Cholesky H = L L^T in place (lower); rows on lanes, right-looking.
 // Returns false when a pivot is not positive.
-__device__ bool bp_chol_factor(const Ctx& c, double* H, double* dinv) {
+BP_STAGE bool bp_chol_factor(const C& c, typename C::DP H, typename C::DP dinv) {
   const int n = c.P.m.nv, nvp = c.P.m.nvp;
+#pragma unroll 1
   for (int j = 0; j < n; j++) {
     double s = H[j * nvp + j];
-    if (s < BP_MINVAL) return false;      // uniform across the warp
+    if (s < BP_MINVAL) return false;      // uniform across the group
     s = sqrt(s);
     double inv = 1.0 / s;
     SYNC();
     if (c.lane == 0) { H[j * nvp + j] = s; dinv[j] = inv; }
-    for (int i = j + 1 + c.lane; i < n; i += 32) H[i * nvp + j] /= s;
+    for (int i = j + 1 + c.lane; i < n; i += C::G) H[i * nvp + j] /= s;
     SYNC();
-    for (int i = j + 1 + c.lane; i < n; i += 32) {
+#pragma unroll 1
+    for (int i = j + 1 + c.lane; i < n; i += C::G) {
       double lij = H[i * nvp + j];
       for (int k = j + 1; k <= i; k++) H[i * nvp + k] -= lij * H[k * nvp + j];
     }
@@ -155,38 +163,43 @@ __device__ bool bp_chol_factor(const Ctx& c, double* H, double* dinv) {
   return true;
 }
 
-__device__ void bp_chol_solve(const Ctx& c, const double* L, const double* dinv, double* x) {
+BP_STAGE void bp_chol_solve(const C& c, typename C::DP L, typename C::DP dinv,
+                            typename C::DP x) {
   const int n = c.P.m.nv, nvp = c.P.m.nvp;
+#pragma unroll 1
   for (int k = 0; k < n; k++) {
     double xk = x[k] * dinv[k];
     SYNC();
     if (c.lane == 0) x[k] = xk;
-    for (int i = k + 1 + c.lane; i < n; i += 32) x[i] -= L[i * nvp + k] * xk;
+    for (int i = k + 1 + c.lane; i < n; i += C::G) x[i] -= L[i * nvp + k] * xk;
     SYNC();
   }
+#pragma unroll 1
   for (int k = n - 1; k >= 0; k--) {
     double xk = x[k] * dinv[k];
     SYNC();
     if (c.lane == 0) x[k] = xk;
-    for (int i = c.lane; i < k; i += 32) x[i] -= L[k * nvp + i] * xk;
+    for (int i = c.lane; i < k; i += C::G) x[i] -= L[k * nvp + i] * xk;
     SYNC();
   }
 }
 
 // grad = Ma - qfrc_smooth - qfrc_constraint;  H = M + J^T D_active J;  Mgrad = H^-1 grad
-__device__ void bp_newton_gradient(const Ctx& c, int nefc) {
+BP_STAGE void bp_newton_gradient(const C& c, int nefc) {
   const BpModel& m = c.P.m;
   const int nv = m.nv, nvp = m.nvp;
-  double *H = DF(s_H), *Md = DF(s_Md), *grad = DF(s_grad), *Mgrad = DF(s_Mgrad);
-  const double *J = DF(efc_J), *D = DF(efc_D);
-  const int* state = IF(efc_state);
-  for (int i = c.lane; i < nv; i += 32) {
+  auto H = DF(s_H), Md = DF(s_Md), grad = DF(s_grad), Mgrad = DF(s_Mgrad);
+  auto J = DF(efc_J), D = DF(efc_D);
+  auto state = IF(efc_state);
+  for (int i = c.lane; i < nv; i += C::G) {
     double g = DF(s_Ma)[i] - DF(qfrc_smooth)[i] - DF(qfrc_constraint)[i];
     grad[i] = g; Mgrad[i] = g;
   }
-  for (int e = c.lane; e < m.ntri; e += 32) {
+#pragma unroll 1
+  for (int e = c.lane; e < m.ntri; e += C::G) {
     int i = m.tri_i[e], j = m.tri_j[e];
     double acc = Md[i * nvp + j];
+#pragma unroll 1
     for (int r = 0; r < nefc; r++)
       if (state[r] == ST_QUADRATIC) acc += D[r] * J[r * nvp + i] * J[r * nvp + j];
     H[i * nvp + j] = acc;
@@ -194,7 +207,7 @@ __device__ void bp_newton_gradient(const Ctx& c, int nefc) {
   SYNC();
   if (!bp_chol_factor(c, H, DF(s_Hdinv))) {
     SYNC();
-    for (int e = c.lane; e < m.ntri; e += 32) {
+    for (int e = c.lane; e < m.ntri; e += C::G) {
       int i = m.tri_i[e], j = m.tri_j[e];
       H[i * nvp + j] = Md[i * nvp + j];
     }
@@ -204,34 +217,36 @@ __device__ void bp_newton_gradient(const Ctx& c, int nefc) {
   bp_chol_solve(c, H, DF(s_Hdinv), Mgrad);
 }
 
-__device__ void bp_fwd_constraint(const Ctx& c) {
+BP_STAGE void bp_fwd_constraint(const C& c) {
   const BpModel& m = c.P.m;
-  const int nv = m.nv, nvp = m.nvp, nefc = *IF(nefc);
-  double *qacc = DF(qacc), *warm = DF(qacc_warmstart), *as = DF(qacc_smooth);
+  const int nv = m.nv, nvp = m.nvp, nefc = IF(nefc)[0];
+  auto qacc = DF(qacc), warm = DF(qacc_warmstart), as = DF(qacc_smooth);
   if (nefc == 0) {
-    for (int i = c.lane; i < nv; i += 32) {
+    for (int i = c.lane; i < nv; i += C::G) {
       double a = as[i];
       qacc[i] = a; warm[i] = a; DF(qfrc_constraint)[i] = 0;
     }
-    if (c.lane == 0) *IF(solver_iter) = 0;
+    if (c.lane == 0) IF(solver_iter)[0] = 0;
     SYNC();
     return;
   }
   // dense copy of M
-  double *Md = DF(s_Md), *qM = DF(qM);
-  for (int w = c.lane; w < nv * nvp; w += 32) Md[w] = 0;
+  auto Md = DF(s_Md), qM = DF(qM);
+  for (int w = c.lane; w < nv * nvp; w += C::G) Md[w] = 0;
   SYNC();
-  for (int i = c.lane; i < nv; i += 32) {
+#pragma unroll 1
+  for (int i = c.lane; i < nv; i += C::G) {
     int a = m.dof_Madr[i];
     for (int j = i; j >= 0; j = m.dof_parentid[j], a++) {
-      Md[i * nvp + j] = qM[a]; Md[j * nvp + i] = qM[a];
+      double v = qM[a];
+      Md[i * nvp + j] = v; Md[j * nvp + i] = v;
     }
   }
   SYNC();
-  double *Ma = DF(s_Ma), *jar = DF(s_jar), *search = DF(s_search);
+  auto Ma = DF(s_Ma), jar = DF(s_jar), search = DF(s_search);
   bool use_warm = false;
   if (!(m.opt_disableflags & DSBL_WARMSTART)) {
-    for (int i = c.lane; i < nv; i += 32) qacc[i] = warm[i];
+    for (int i = c.lane; i < nv; i += C::G) qacc[i] = warm[i];
     SYNC();
     bp_mul_md(c, Md, Ma, qacc);
     bp_mul_j(c, jar, qacc, DF(efc_aref), nefc);
@@ -241,45 +256,46 @@ __device__ void bp_fwd_constraint(const Ctx& c) {
     use_warm = cw < cs;
     SYNC();
   }
-  for (int i = c.lane; i < nv; i += 32) qacc[i] = use_warm ? warm[i] : as[i];
+  for (int i = c.lane; i < nv; i += C::G) qacc[i] = use_warm ? warm[i] : as[i];
   SYNC();
   bp_mul_md(c, Md, Ma, qacc);
   bp_mul_j(c, jar, qacc, DF(efc_aref), nefc);
   double cost = bp_update_constraint(c, jar, nefc, true) + bp_gauss_cost(c);
   bp_newton_gradient(c, nefc);
-  for (int i = c.lane; i < nv; i += 32) search[i] = -DF(s_Mgrad)[i];
+  for (int i = c.lane; i < nv; i += C::G) search[i] = -DF(s_Mgrad)[i];
   SYNC();
   const double scale = 1.0 / (m.stat_meaninertia * (nv > 1 ? nv : 1));
   int iter = 0;
   double improvement = 0, gradient = 0;
+#pragma unroll 1
   while (iter < m.opt_iterations) {
     bp_mul_md(c, Md, DF(s_Mv), search);
-    bp_mul_j(c, DF(s_jv), search, nullptr, nefc);
+    bp_mul_j(c, DF(s_jv), search, c.null(), nefc);
     double alpha = bp_linesearch(c, scale, nefc);
     if (alpha == 0) break;
-    for (int i = c.lane; i < nv; i += 32) {
+    for (int i = c.lane; i < nv; i += C::G) {
       qacc[i] += alpha * search[i];
       Ma[i] += alpha * DF(s_Mv)[i];
     }
-    for (int r = c.lane; r < nefc; r += 32) jar[r] += alpha * DF(s_jv)[r];
+    for (int r = c.lane; r < nefc; r += C::G) jar[r] += alpha * DF(s_jv)[r];
     SYNC();
     double old = cost;
     cost = bp_update_constraint(c, jar, nefc, true) + bp_gauss_cost(c);
     bp_newton_gradient(c, nefc);
     double gn = 0;
-    for (int i = c.lane; i < nv; i += 32) gn += DF(s_grad)[i] * DF(s_grad)[i];
-    gn = warp_sum(gn);
+    for (int i = c.lane; i < nv; i += C::G) gn += DF(s_grad)[i] * DF(s_grad)[i];
+    gn = group_sum(c, gn);
     improvement = scale * (old - cost); gradient = scale * sqrt(gn);
     iter++;
     if (improvement < m.opt_tolerance || gradient < m.opt_tolerance) break;
-    for (int i = c.lane; i < nv; i += 32) search[i] = -DF(s_Mgrad)[i];
+    for (int i = c.lane; i < nv; i += C::G) search[i] = -DF(s_Mgrad)[i];
     SYNC();
   }
   if (c.lane == 0) {
-    *IF(solver_iter) = iter;
+    IF(solver_iter)[0] = iter;
     DF(solver_stat)[0] = improvement; DF(solver_stat)[1] = gradient;
   }
-  for (int i = c.lane; i < nv; i += 32) warm[i] = qacc[i];
+  for (int i = c.lane; i < nv; i += C::G) warm[i] = qacc[i];
   SYNC();
 }
 

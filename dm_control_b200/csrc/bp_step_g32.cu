@@ -1,0 +1,32 @@
+// Instantiation: one warp per environment, image in shared memory (G = 32).
+#include "bp_pipeline.cuh"
+
+// ---- G = 32: one warp per environment, image staged in shared memory ---------
+__global__ void __launch_bounds__(32)
+bp_step_kernel_smem(const __grid_constant__ BpParams P) {
+  extern __shared__ double smem[];
+  const int lane = threadIdx.x;
+  const long long env = blockIdx.x;
+  if (env >= P.nenv || (P.mask && !P.mask[env])) return;
+  double* g = P.image + env * P.stride;
+  for (int w = lane; w < P.L.persist; w += 32) smem[w] = g[w];
+  __syncwarp();
+  Ctx<32, 1> c{P, smem, (int*)(smem + P.L.ints), lane, 0xffffffffu};
+  bp_run_mode(c);
+  __syncwarp();
+  for (int w = lane; w < P.L.persist; w += 32) g[w] = smem[w];
+}
+
+extern "C" int bp_launch_step_g32(const BpParams* P, cudaStream_t stream) {
+  size_t bytes = (size_t)P->L.total * sizeof(double);
+  static size_t configured = 0;
+  if (bytes > configured) {
+    cudaError_t e = cudaFuncSetAttribute(bp_step_kernel_smem,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)bytes);
+    if (e != cudaSuccess) return (int)e;
+    configured = bytes;
+  }
+  bp_step_kernel_smem<<<(unsigned)P->nenv, 32, bytes, stream>>>(*P);
+  return (int)cudaGetLastError();
+}

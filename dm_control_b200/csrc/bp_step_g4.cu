@@ -1,0 +1,10 @@
+// Instantiation: 4 lane(s) per environment, image in global memory (interleave 1).
+#include "bp_pipeline.cuh"
+
+extern "C" int bp_launch_step_g4(const BpParams* P, cudaStream_t stream) {
+  const int threads = 128;
+  long long total = P->nenv * 4;
+  unsigned blocks = (unsigned)((total + threads - 1) / threads);
+  bp_step_kernel_gmem<4, 1><<<blocks, threads, 0, stream>>>(*P);
+  return (int)cudaGetLastError();
+}

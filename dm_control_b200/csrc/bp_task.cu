@@ -15,6 +15,17 @@ enum { TASK_NONE = 0, TASK_CARTPOLE = 1, TASK_ACROBOT = 2, TASK_PENDULUM = 3,
        TASK_REACHER = 8 };
 enum { SIG_GAUSSIAN = 0, SIG_LINEAR = 1, SIG_QUADRATIC = 2 };
 
+// read-only strided window of one environment's image (see bp_math.cuh for layouts)
+struct ImgView {
+  const double* p; int S;
+  __device__ __forceinline__ double operator[](int i) const { return p[(long long)i * S]; }
+  __device__ __forceinline__ ImgView at(int off) const { return ImgView{p + (long long)off * S, S}; }
+};
+__device__ __forceinline__ double* bp_env_base(const BpParams& P, long long env) {
+  const int S = P.interleave;
+  return P.image + (env / S) * P.stride * S + (env % S);
+}
+
 __device__ __forceinline__ double sigmoid_(double x, double v1, int kind) {
   if (kind == SIG_GAUSSIAN) {
     double scale = sqrt(-2 * log(v1));
@@ -60,9 +71,9 @@ __global__ void bp_task_kernel(const __grid_constant__ BpParams P,
   if (env >= P.nenv) return;
   const BpModel& m = P.m;
   const BpLayout& L = P.L;
-  const double* d = P.image + env * (long long)L.persist;
-  const double *qpos = d + L.qpos, *qvel = d + L.qvel, *xmat = d + L.xmat, *xpos = d + L.xpos;
-  const double *ctrl = d + L.ctrl, *sens = d + L.sensordata;
+  const ImgView d{bp_env_base(P, env), P.interleave};
+  const ImgView qpos = d.at(L.qpos), qvel = d.at(L.qvel), xmat = d.at(L.xmat), xpos = d.at(L.xpos);
+  const ImgView ctrl = d.at(L.ctrl), sens = d.at(L.sensordata);
   double* o = obs_out ? obs_out + env * (long long)nobs : nullptr;
   double r = 0;
   int k = 0;
@@ -93,7 +104,7 @@ __global__ void bp_task_kernel(const __grid_constant__ BpParams P,
       break;
     }
     case TASK_ACROBOT: {    // suite/acrobot.py:59-78,108-119
-      const double* sx = d + L.site_xpos;
+      const ImgView sx = d.at(L.site_xpos);
       int ua = T.ip[0], la = T.ip[1], tgt = T.ip[2], tip = T.ip[3];
       if (o) {
         o[k++] = xmat[9 * ua + 2]; o[k++] = xmat[9 * la + 2];
@@ -140,8 +151,8 @@ __global__ void bp_task_kernel(const __grid_constant__ BpParams P,
     }
     case TASK_HUMANOID: {   // suite/humanoid.py:93-129,168-207
       int torso = T.ip[0], head = T.ip[1];
-      const double* R = xmat + 9 * torso;
-      const double* vel = sens + T.ip[6];
+      const ImgView R = xmat.at(9 * torso);
+      const ImgView vel = sens.at(T.ip[6]);
       if (o) {
         for (int i = 7; i < m.nq; i++) o[k++] = qpos[i];
         o[k++] = xpos[3 * head + 2];
@@ -193,18 +204,57 @@ __global__ void bp_reset_kernel(const __grid_constant__ BpParams P, const double
                                 const double* kv, const double* ka, double kt) {
   long long env = blockIdx.x;
   if (env >= P.nenv || (P.mask && !P.mask[env])) return;
-  double* d = P.image + env * (long long)P.L.persist;
-  for (int w = threadIdx.x; w < P.L.persist; w += blockDim.x) d[w] = 0;
+  double* d = bp_env_base(P, env);
+  const long long S = P.interleave;
+  // ints sit in 4-byte slots: zero them through the int view when interleaved
+  for (int w = threadIdx.x; w < P.L.ints; w += blockDim.x) d[w * S] = 0;
+  if (S == 1) {
+    for (int w = P.L.ints + threadIdx.x; w < P.stride; w += blockDim.x) d[w] = 0;
+  } else {
+    int* ib = (int*)(P.image + (env / S) * P.stride * S + (long long)P.L.ints * S) + (env % S);
+    int nints = (int)(P.L.persist - P.L.ints) * 2;
+    for (int w = threadIdx.x; w < nints; w += blockDim.x) ib[w * S] = 0;
+    for (int w = P.L.persist + threadIdx.x; w < P.stride; w += blockDim.x) d[w * S] = 0;
+  }
   __syncthreads();
-  for (int i = threadIdx.x; i < P.m.nq; i += blockDim.x) d[P.L.qpos + i] = kq ? kq[i] : P.m.qpos0[i];
-  if (kv) for (int i = threadIdx.x; i < P.m.nv; i += blockDim.x) d[P.L.qvel + i] = kv[i];
-  if (ka) for (int i = threadIdx.x; i < P.m.na; i += blockDim.x) d[P.L.act + i] = ka[i];
-  if (threadIdx.x == 0) d[P.L.time] = kt;
+  for (int i = threadIdx.x; i < P.m.nq; i += blockDim.x) d[(P.L.qpos + i) * S] = kq ? kq[i] : P.m.qpos0[i];
+  if (kv) for (int i = threadIdx.x; i < P.m.nv; i += blockDim.x) d[(P.L.qvel + i) * S] = kv[i];
+  if (ka) for (int i = threadIdx.x; i < P.m.na; i += blockDim.x) d[(P.L.act + i) * S] = ka[i];
+  if (threadIdx.x == 0) d[P.L.time * S] = kt;
 }
 
 extern "C" int bp_launch_reset(const BpParams* P, const double* kq, const double* kv,
                                const double* ka, double kt, cudaStream_t stream) {
   bp_reset_kernel<<<(unsigned)P->nenv, 64, 0, stream>>>(*P, kq, kv, ka, kt);
+  return (int)cudaGetLastError();
+}
+
+// dense [n][count] <-> image field copy for any layout (one thread per element)
+__global__ void bp_field_copy_kernel(const __grid_constant__ BpParams P, long long off, int count,
+                                     int is_int, void* dense, long long env0, long long n,
+                                     int to_image) {
+  long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= n * count) return;
+  long long e = t / count, env = env0 + e;
+  int k = (int)(t - e * count);
+  const long long S = P.interleave;
+  if (!is_int) {
+    double* q = bp_env_base(P, env) + (off + k) * S;
+    if (to_image) *q = ((const double*)dense)[t]; else ((double*)dense)[t] = *q;
+  } else {
+    int* q = (int*)(P.image + (env / S) * P.stride * S + (long long)P.L.ints * S) + (env % S) +
+             (off + k) * S;
+    if (to_image) *q = ((const int*)dense)[t]; else ((int*)dense)[t] = *q;
+  }
+}
+
+extern "C" int bp_launch_field_copy(const BpParams* P, long long off, int count, int is_int,
+                                    void* dense, long long env0, long long n, int to_image,
+                                    cudaStream_t stream) {
+  long long total = n * count;
+  if (total <= 0) return 0;
+  unsigned blocks = (unsigned)((total + 255) / 256);
+  bp_field_copy_kernel<<<blocks, 256, 0, stream>>>(*P, off, count, is_int, dense, env0, n, to_image);
   return (int)cudaGetLastError();
 }
 

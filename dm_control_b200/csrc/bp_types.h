@@ -151,9 +151,12 @@ struct BpLayout {   // offsets in doubles from the start of the env's image
 struct BpParams {
   BpModel m;
   BpLayout L;
-  double* image;     // [nenv][L.persist]
+  double* image;     // [nenv][stride] (or [nenv/32][stride][32] when interleave == 32)
   const unsigned char* mask;   // optional [nenv]; 0 = leave the env untouched
   long long nenv;
+  long long stride;  // doubles per env in `image` (persist for the smem variant, total otherwise)
+  int interleave;    // 1: env images contiguous; 32: images of a warp's 32 envs interleaved
+  int lanes;         // lanes per environment (group size G)
   int mode, nsub, disable_actuation, reserved;
 };
 

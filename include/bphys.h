@@ -49,10 +49,14 @@ int bp_model_set_field(bp_model* m, const char* name, const void* data, int64_t 
 int bp_model_get_field(bp_model* m, const char* name, void* data, int64_t nbytes);
 
 /* mj_makeData (wrapper/core.py:637-651) for nenv environments.  njmax/nconmax <= 0
- * take the model's values.  Fails with BP_ESMEM when one environment's image does
- * not fit the shared memory of an SM. */
-bp_batch* bp_batch_create(bp_model* m, int64_t nenv, int njmax, int nconmax, char* err,
-                          int errsz);
+ * take the model's values.  `lanes` is the execution shape: GPU lanes cooperating
+ * on one environment (1, 2, 4, 8, 16 or 32; <= 0 = default).  32 keeps the
+ * environment's image in shared memory (one warp per environment) and fails when
+ * the image does not fit an SM; smaller values address the image in global memory
+ * with 32/lanes environments per warp (lanes == 1 interleaves the images of the 32
+ * environments of a warp, see bp_batch_interleave). */
+bp_batch* bp_batch_create(bp_model* m, int64_t nenv, int njmax, int nconmax, int lanes,
+                          char* err, int errsz);
 /* mj_deleteData. */
 void bp_batch_free(bp_batch* b);
 
@@ -60,6 +64,10 @@ void bp_batch_free(bp_batch* b);
 void* bp_batch_image(bp_batch* b);
 int64_t bp_batch_stride(bp_batch* b);          /* doubles per environment        */
 int64_t bp_batch_nenv(bp_batch* b);
+int bp_batch_lanes(bp_batch* b);
+/* 1: env e's element i is image[e*stride + i]; 32: image[(e/32)*stride*32 + i*32 + e%32]
+ * (int32 fields: same rule in 4-byte units from the start of the int region). */
+int bp_batch_interleave(bp_batch* b);
 int64_t bp_batch_smem_bytes(bp_batch* b);      /* shared memory per environment  */
 /* Enumerate / look up fields of the image: byte offset inside one env's image,
  * element count, dtype (0 = float64, 1 = int32).  Names follow mjData. */

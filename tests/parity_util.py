@@ -119,7 +119,7 @@ def compare_env(cmp, m, oracle, gpu, e, nvp, skip=()):
 
 
 def run_parity(domain, nenv=32, nsteps=3, seed=0, njmax=0, nconmax=0, check_steps=None,
-               vel_scale=1.0, spread=1.0, mutate=None):
+               vel_scale=1.0, spread=1.0, mutate=None, lanes=0):
   """forward() then `nsteps` Physics.step() on both sides; returns (Comparison per
   phase, stats).  The GPU side goes through the C ABI (dm_control_b200.binding)."""
   from dm_control_b200 import binding
@@ -129,7 +129,7 @@ def run_parity(domain, nenv=32, nsteps=3, seed=0, njmax=0, nconmax=0, check_step
     mutate(m)
   qpos, qvel, ctrl = random_states(m, nenv, seed, vel_scale, spread)
   model = binding.Model(m)
-  batch = binding.Batch(model, nenv, njmax, nconmax)
+  batch = binding.Batch(model, nenv, njmax, nconmax, lanes)
   nvp = m.nv | 1
   batch.write("qpos", qpos); batch.write("qvel", qvel); batch.write("ctrl", ctrl)
   om = OracleModel(m)

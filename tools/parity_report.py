@@ -10,18 +10,20 @@ import parity_util as PU   # noqa: E402
 
 
 def main():
+  lanes_list = [int(x) for x in os.environ.get("BP_LANES", "32,1,2,4,8,16").split(",")]
   domains = sys.argv[1:] or ["pendulum", "cartpole", "acrobot", "cheetah", "walker",
                              "hopper", "humanoid"]
   os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
   with open(os.path.join(ROOT, "gpurun_out", "parity_report.txt"), "w") as f:
-    for d in domains:
+    for d, lanes in [(d, l) for d in domains for l in lanes_list]:
       t = time.time()
       kw = dict(njmax=120, nconmax=40) if d == "humanoid" else {}
       try:
         res, stats = PU.run_parity(d, nenv=64, nsteps=20, seed=1,
-                                   check_steps=[0, 1, 2, 5, 10, 20], **kw)
+                                   check_steps=[0, 1, 5, 20], lanes=lanes, **kw)
+        d = '%s/G%d' % (d, lanes)
       except Exception as e:   # keep going: this is a report, not a test
-        msg = "%s: FAILED %r" % (d, e)
+        msg = "%s/G%d: FAILED %r" % (d, lanes, e)
         print(msg); f.write(msg + "\n")
         continue
       for step, cmp in sorted(res.items()):
