@@ -63,6 +63,7 @@ _SIGNATURES = {
     "bp_set_task": (_i32, [_vp, _i32, _vp, _i32, _vp, _i32]),
     "bp_task_nobs": (_i32, [_vp]),
     "bp_obs_reward": (_i32, [_vp, _vp, _vp]),
+    "bp_obs_reward_host": (_i32, [_vp, _vp, _vp]),
     "bp_env_step_host": (_i32, [_vp, _i32, _vp, _vp, _vp]),
     "bp_warnings": (_i32, [_vp, _vp]),
     "bp_sync": (_i32, [_vp]),
@@ -245,6 +246,9 @@ class Batch:
 
   def obs_reward(self, obs_ptr, reward_ptr):
     check(load().bp_obs_reward(self.ptr, obs_ptr, reward_ptr))
+
+  def obs_reward_host(self, obs, reward):
+    check(load().bp_obs_reward_host(self.ptr, _ptr(obs), _ptr(reward)))
 
   def env_step_host(self, nsub, ctrl, obs, reward):
     check(load().bp_env_step_host(self.ptr, nsub, _ptr(ctrl), _ptr(obs), _ptr(reward)))

@@ -1,0 +1,124 @@
+"""Batched `control.Environment` (reference: /root/reference/dm_control/rl/control.py:33-193).
+
+Same episode logic — reset on the step after LAST (control.py:97-98), sub-step loop
+(:100-102), reward / observation / discount / time limit (:104-123) — for `nenv`
+environments at once.  The sub-step loop, the task's observation and its reward run
+on the device inside ONE C-ABI call (`bp_env_step_host`): actions go host->device,
+observations and rewards come back.
+"""
+
+import collections
+
+import numpy as np
+
+from dm_control_b200 import specs
+from dm_control_b200.physics import PhysicsError   # noqa: F401  (re-export)
+
+
+def compute_n_steps(control_timestep, physics_timestep, tolerance=1e-8):
+  """control.py:164-190."""
+  if control_timestep < physics_timestep:
+    raise ValueError("Control timestep ({}) cannot be smaller than physics timestep ({}).".
+                     format(control_timestep, physics_timestep))
+  ratio = control_timestep / physics_timestep
+  if abs(ratio - round(ratio)) > tolerance:
+    raise ValueError("Control timestep ({}) must be an integer multiple of physics timestep "
+                     "({})".format(control_timestep, physics_timestep))
+  return int(round(ratio))
+
+
+def flatten_observation(observation, output_key="observations"):
+  """control.py:368-393, batched: values are [nenv, ...] and are flattened per env."""
+  keys = observation.keys() if isinstance(observation, collections.OrderedDict) \
+      else sorted(observation.keys())
+  parts = [np.asarray(observation[k]).reshape(len(observation[k]), -1) for k in keys]
+  return type(observation)([(output_key, np.concatenate(parts, axis=1))])
+
+
+class Environment:
+  """`nenv` copies of one suite task stepping in lockstep."""
+
+  def __init__(self, physics, task, time_limit=float("inf"), control_timestep=None,
+               n_sub_steps=None, flat_observation=False):
+    self._physics, self._task = physics, task
+    self._flat_observation = flat_observation
+    if n_sub_steps is not None and control_timestep is not None:
+      raise ValueError("Both n_sub_steps and control_timestep were supplied.")
+    elif n_sub_steps is not None:
+      self._n_sub_steps = n_sub_steps
+    elif control_timestep is not None:
+      self._n_sub_steps = compute_n_steps(control_timestep, physics.timestep())
+    else:
+      self._n_sub_steps = 1
+    self._step_limit = float("inf") if time_limit == float("inf") else \
+        time_limit / (physics.timestep() * self._n_sub_steps)
+    self._step_count = 0
+    self._reset_next_step = True
+    task.bind(physics)
+    n = physics.nenv
+    self._obs = np.empty((n, task.nobs), dtype=np.float64)
+    self._rew = np.empty((n,), dtype=np.float64)
+
+  @property
+  def nenv(self): return self._physics.nenv
+  @property
+  def physics(self): return self._physics
+  @property
+  def task(self): return self._task
+
+  def _observation(self, flat):
+    obs = collections.OrderedDict()
+    k = 0
+    for name, width in self._task.obs_layout:
+      v = flat[:, k:k + width].copy()
+      obs[name] = v[:, 0] if width == 1 and name in self._task.scalar_obs else v
+      k += width
+    return flatten_observation(obs) if self._flat_observation else obs
+
+  def reset(self):
+    """control.py:77-92."""
+    self._reset_next_step = False
+    self._step_count = 0
+    with self._physics.reset_context():
+      self._task.initialize_episode(self._physics)
+    self._physics._batch.obs_reward_host(self._obs, self._rew)
+    n = self.nenv
+    return specs.TimeStep(np.full(n, specs.StepType.FIRST, dtype=np.int32), None, None,
+                          self._observation(self._obs))
+
+  def step(self, action):
+    """control.py:94-123 for every env; `action` is [nenv, nu]."""
+    if self._reset_next_step:
+      return self.reset()
+    action = np.ascontiguousarray(
+        np.broadcast_to(np.asarray(action, dtype=np.float64),
+                        (self.nenv, self._physics.model.nu)))
+    self._physics._batch.env_step_host(self._n_sub_steps, action, self._obs, self._rew)
+    self._physics.check_invalid_state()
+    self._step_count += 1
+    n = self.nenv
+    reward = self._rew.copy()
+    obs = self._observation(self._obs)
+    if self._step_count >= self._step_limit:
+      self._reset_next_step = True
+      return specs.TimeStep(np.full(n, specs.StepType.LAST, dtype=np.int32), reward,
+                            np.ones(n), obs)
+    return specs.TimeStep(np.full(n, specs.StepType.MID, dtype=np.int32), reward,
+                          np.ones(n), obs)
+
+  def action_spec(self):
+    return self._physics.action_spec()
+
+  def observation_spec(self):
+    """control.py:133-149: inferred from an observation (per-env shapes)."""
+    spec = collections.OrderedDict()
+    for name, width in self._task.obs_layout:
+      shape = () if width == 1 and name in self._task.scalar_obs else (width,)
+      spec[name] = specs.Array(shape, np.float64, name=name)
+    return spec
+
+  def control_timestep(self):
+    return self._physics.timestep() * self._n_sub_steps
+
+  def close(self):
+    self._physics.free()

@@ -573,6 +573,40 @@ extern "C" int bp_obs_reward(bp_batch* b, double* obs, double* reward) {
   return BP_OK;
 }
 
+static int ensure_task_buffers(bp_batch* b, int nobs) {
+  int nu = b->model->M.nu;
+  if (!b->ctrl_stage) {
+    CUDA_OK(cudaMalloc((void**)&b->ctrl_stage, (size_t)b->nenv * (nu > 0 ? nu : 1) * 8));
+    CUDA_OK(cudaMalloc((void**)&b->rew_dev, (size_t)b->nenv * 8));
+  }
+  if (nobs > b->obs_cap) {
+    if (b->obs_dev) cudaFree(b->obs_dev);
+    b->obs_dev = nullptr;
+    CUDA_OK(cudaMalloc((void**)&b->obs_dev, (size_t)b->nenv * nobs * 8));
+    b->obs_cap = nobs;
+  }
+  return BP_OK;
+}
+
+extern "C" int bp_obs_reward_host(bp_batch* b, double* obs_host, double* reward_host) {
+  if (!b) return fail(BP_EINVAL, "null batch");
+  cudaSetDevice(b->model->device);
+  int nobs = bp_task_nobs_impl(&b->model->M, b->task.kind);
+  if (nobs < 0) return fail(BP_EINVAL, "unknown task kind");
+  int e = ensure_task_buffers(b, nobs);
+  if (e != BP_OK) return e;
+  e = bp_obs_reward(b, nobs > 0 ? b->obs_dev : nullptr, b->rew_dev);
+  if (e != BP_OK) return e;
+  if (obs_host && nobs > 0)
+    CUDA_OK(cudaMemcpyAsync(obs_host, b->obs_dev, (size_t)b->nenv * nobs * 8,
+                            cudaMemcpyDeviceToHost, b->stream));
+  if (reward_host)
+    CUDA_OK(cudaMemcpyAsync(reward_host, b->rew_dev, (size_t)b->nenv * 8,
+                            cudaMemcpyDeviceToHost, b->stream));
+  CUDA_OK(cudaStreamSynchronize(b->stream));
+  return BP_OK;
+}
+
 extern "C" int bp_env_step_host(bp_batch* b, int nsub, const double* ctrl_host,
                                 double* obs_host, double* reward_host) {
   if (!b || !ctrl_host) return fail(BP_EINVAL, "null argument");
@@ -581,15 +615,8 @@ extern "C" int bp_env_step_host(bp_batch* b, int nsub, const double* ctrl_host,
   int nobs = bp_task_nobs_impl(&m->M, b->task.kind);
   if (nobs < 0) return fail(BP_EINVAL, "unknown task kind");
   int nu = m->M.nu;
-  if (!b->ctrl_stage) {
-    CUDA_OK(cudaMalloc((void**)&b->ctrl_stage, (size_t)b->nenv * (nu > 0 ? nu : 1) * 8));
-    CUDA_OK(cudaMalloc((void**)&b->rew_dev, (size_t)b->nenv * 8));
-  }
-  if (nobs > b->obs_cap) {
-    if (b->obs_dev) cudaFree(b->obs_dev);
-    CUDA_OK(cudaMalloc((void**)&b->obs_dev, (size_t)b->nenv * nobs * 8));
-    b->obs_cap = nobs;
-  }
+  int eb = ensure_task_buffers(b, nobs);
+  if (eb != BP_OK) return eb;
   const FieldInfo* f = find_field(b, "ctrl");
   if (nu > 0) {
     CUDA_OK(cudaMemcpyAsync(b->ctrl_stage, ctrl_host, (size_t)b->nenv * nu * 8,

@@ -1,0 +1,231 @@
+"""`BatchedPhysics`: dm_control's `mujoco.Physics` with a leading environment axis.
+
+Mirrors the reference facade (/root/reference/dm_control/mujoco/engine.py:108-573)
+method by method — step / forward / reset / after_reset / reset_context /
+set_control / control / position / velocity / activation / state / get_state /
+set_state / time / timestep / check_invalid_state / named — over a device batch
+behind the C ABI (binding.py).  State arrays carry a leading env dimension.
+There is no CPU path: constructing it without libbphys.so + a CUDA device raises.
+"""
+
+import contextlib
+
+import numpy as np
+
+from dm_control_b200 import binding
+from dm_control_b200 import index
+from dm_control_b200 import mjcf_compiler
+from dm_control_b200 import model as M
+
+_INVALID_PHYSICS_STATE = ("Physics state is invalid. Warning(s) raised: {warning_names} "
+                          "in environment(s) {envs}")   # engine.py:58-60
+
+
+class PhysicsError(RuntimeError):
+  """Raised if the state of the physics simulation becomes divergent
+  (rl/control.py:196-199)."""
+
+
+# default execution shape per model size: lanes per environment (DESIGN.md §Shapes;
+# chosen from the sweep in profiles/)
+def default_lanes(m):
+  return 4 if m.nv <= 12 else 8
+
+
+def default_sizes(m):
+  """(njmax, nconmax) that fit typical suite episodes; overflow raises the same
+  CNSTRFULL / CONTACTFULL warnings the reference surfaces (core_test.py:97-103)."""
+  nconmax = int(min(m.nconmax, max(8, 2 * m.ngeom)))
+  njmax = int(min(m.njmax, 4 * nconmax + int(np.sum(m.jnt_limited != 0)) +
+                  int(np.sum(m.dof_frictionloss > 0))))
+  return max(njmax, 1), max(nconmax, 1)
+
+
+class _Data:
+  """`physics.data.<field>`: host copies [nenv, n] (reads) / whole-field writes."""
+
+  def __init__(self, physics):
+    object.__setattr__(self, "_p", physics)
+
+  def __getattr__(self, name):
+    b = self._p._batch
+    if name in b.fields:
+      a = b.read(name)
+      return a[:, 0] if name in ("time", "ncon", "nefc", "ne", "nf", "solver_iter") else a
+    raise AttributeError(name)
+
+  def __setattr__(self, name, value):
+    b = self._p._batch
+    if name not in b.fields:
+      raise AttributeError(name)
+    cnt = b.fields[name][1]
+    a = np.asarray(value, dtype=b.fields[name][2])
+    if a.ndim == 0 or a.shape == (cnt,):
+      a = np.broadcast_to(a.reshape(-1) if a.ndim else a, (b.nenv, cnt))
+    b.write(name, np.ascontiguousarray(a).reshape(b.nenv, cnt))
+
+
+class _Named:
+  def __init__(self, physics):
+    self.data = index.data_indexer(physics)
+    self.model = index.model_indexer(physics)
+
+
+class BatchedPhysics:
+  """`nenv` independent simulations of one compiled model on one GPU."""
+
+  def __init__(self, flat_model, nenv, device=0, lanes=None, njmax=None, nconmax=None):
+    self.model = flat_model
+    self.nenv = int(nenv)
+    dj, dc = default_sizes(flat_model)
+    self._dev_model = binding.Model(flat_model, device)
+    self._batch = binding.Batch(self._dev_model, self.nenv, njmax or dj, nconmax or dc,
+                                lanes if lanes is not None else default_lanes(flat_model))
+    self._axes = index.make_axes(flat_model)
+    self.data = _Data(self)
+    self.named = _Named(self)
+    self._warnings_seen = np.zeros((self.nenv, 8), dtype=np.int64)
+    self._reset_mask = None
+    self.reset()
+
+  # ---- construction (engine.py:332-470 from_xml_string / from_xml_path / ...) ----
+  @classmethod
+  def from_xml_string(cls, xml_string, assets=None, **kw):
+    return cls(mjcf_compiler.compile_xml(xml_string, assets), **kw)
+
+  @classmethod
+  def from_xml_path(cls, path, **kw):
+    return cls(mjcf_compiler.compile_file(path), **kw)
+
+  @classmethod
+  def from_flat_model(cls, flat_model, **kw):
+    return cls(flat_model, **kw)
+
+  # ---- simulation (engine.py:141-166, 297-305) ---------------------------------------
+  def set_control(self, control):
+    """Sets the control signal of every env: [nenv, nu] (or [nu], broadcast)."""
+    c = np.asarray(control, dtype=np.float64)
+    if c.shape[-1:] != (self.model.nu,):
+      raise ValueError("control has shape {}, expected (..., {})".format(c.shape, self.model.nu))
+    self.data.ctrl = c
+
+  def step(self, n_sub_steps=1):
+    """Physics.step() of engine.py:149-166, `n_sub_steps` times in one launch."""
+    self._batch.step(int(n_sub_steps))
+    self.check_invalid_state()
+
+  def forward(self):
+    self._batch.forward(False)
+    self.check_invalid_state()
+
+  def reset(self, keyframe_id=None, mask=None):
+    """engine.py:268-289: mj_resetData(+Keyframe), then forward with actuation
+    disabled.  `mask` ([nenv] bool) restricts the reset to some envs."""
+    if keyframe_id is not None and not 0 <= keyframe_id < self.model.nkey:
+      raise ValueError("keyframe_id must be between 0 and {}".format(self.model.nkey - 1))
+    self._batch.set_mask(mask)
+    try:
+      self._batch.reset(-1 if keyframe_id is None else keyframe_id)
+      self._batch.forward(True)
+      self._batch.sync()
+    finally:
+      self._batch.set_mask(None)
+    if mask is None:
+      self._warnings_seen[:] = 0
+    else:
+      self._warnings_seen[np.asarray(mask, dtype=bool)] = 0
+
+  def after_reset(self):
+    """engine.py:291-295: forward() with actuation disabled."""
+    self._batch.set_mask(self._reset_mask)
+    try:
+      self._batch.forward(True)
+      self._batch.sync()
+    finally:
+      self._batch.set_mask(None)
+    self.check_invalid_state()
+
+  @contextlib.contextmanager
+  def reset_context(self, mask=None):
+    """engine.py:247-266: reset, let the caller edit the state, then after_reset."""
+    self.reset(mask=mask)
+    self._reset_mask = mask
+    try:
+      yield self
+    finally:
+      self.after_reset()
+      self._reset_mask = None
+
+  def check_invalid_state(self):
+    """engine.py:307-330: new warning counts become a PhysicsError."""
+    w = self._batch.warnings().astype(np.int64)
+    new = w > self._warnings_seen
+    self._warnings_seen = w
+    if new.any():
+      names = [M.WARNINGS[i] for i in np.flatnonzero(new.any(axis=0))]
+      envs = np.flatnonzero(new.any(axis=1))
+      raise PhysicsError(_INVALID_PHYSICS_STATE.format(
+          warning_names=", ".join(names), envs=envs[:16].tolist()))
+
+  # ---- state accessors (engine.py:217-245, 540-573) ---------------------------------------
+  def control(self): return self.data.ctrl
+  def position(self): return self.data.qpos
+  def velocity(self): return self.data.qvel
+  def activation(self): return self.data.act
+  def time(self): return self.data.time
+  def timestep(self): return self.model.opt_timestep
+
+  def state(self):
+    return np.concatenate([self.data.qpos, self.data.qvel, self.data.act], axis=1)
+
+  get_state = state
+
+  def set_state(self, physics_state):
+    s = np.asarray(physics_state, dtype=np.float64)
+    nq, nv, na = self.model.nq, self.model.nv, self.model.na
+    if s.shape[-1] != nq + nv + na:
+      raise ValueError("Input physics state has shape {}. Expected (..., {}).".format(
+          s.shape, nq + nv + na))
+    s = np.broadcast_to(s, (self.nenv, nq + nv + na))
+    self.data.qpos = s[:, :nq]
+    self.data.qvel = s[:, nq:nq + nv]
+    if na:
+      self.data.act = s[:, nq + nv:]
+
+  def set_model_field(self, name, value):
+    """Run-time model edit shared by all envs (core.py:581-620, finger.py:140-142)."""
+    self._dev_model.set_field(name, value)
+
+  @contextlib.contextmanager
+  def disable(self, *flags):
+    """model.disable('actuation', ...) context of core.py:581-620."""
+    old = self.model.opt_disableflags
+    new = old
+    for f in flags:
+      if f not in M.DSBL:
+        raise ValueError("'{}' is not a valid flag name; valid names: {}".format(
+            f, ", ".join(M.DISABLE_FLAGS)))
+      new |= M.DSBL[f]
+    self.set_model_field("opt_disableflags", new)
+    try:
+      yield
+    finally:
+      self.set_model_field("opt_disableflags", old)
+
+  def device_view(self, name):
+    """Zero-copy torch view [nenv, n] of a data field (contiguous images only)."""
+    return self._batch.view(name)
+
+  def action_spec(self):
+    """engine.py:1018-1028: bounds from ctrlrange where ctrllimited, else +-inf."""
+    from dm_control_b200 import specs
+    m = self.model
+    lim = np.asarray(m.actuator_ctrllimited).astype(bool)
+    rng = np.asarray(m.actuator_ctrlrange).reshape(-1, 2)
+    lo = np.where(lim, rng[:, 0], -np.inf)
+    hi = np.where(lim, rng[:, 1], np.inf)
+    return specs.BoundedArray(shape=(m.nu,), dtype=np.float64, minimum=lo, maximum=hi)
+
+  def free(self):
+    self._batch.free()
+    self._dev_model.free()

@@ -1,0 +1,158 @@
+"""`suite.load(domain, task)` for the device backend.
+
+Mirrors /root/reference/dm_control/suite/__init__.py:93-150 (`load`, `build_environment`)
+for the domains the batched backend serves (tasks.py).  Environments are batched:
+`load(..., nenv=N)` returns a `control.Environment` whose TimeSteps carry a leading
+env axis.  Models come from the compiled caches in `suite/models/` (built from the
+reference's XML by tools/compile_suite_models.py); episode initialisation restates
+each task's `initialize_episode` with one `numpy.random.RandomState` per env.
+"""
+
+import os
+
+import numpy as np
+
+from dm_control_b200 import control
+from dm_control_b200 import model as M
+from dm_control_b200.physics import BatchedPhysics
+from dm_control_b200.suite import tasks as T
+
+_MODELS = os.path.join(os.path.dirname(os.path.abspath(__file__)), "models")
+ALL_TASKS = T.ALL_TASKS
+BENCHMARKING = T.ALL_TASKS
+
+
+def _randomize_limited_and_rotational_joints(m, qpos, rng):
+  """suite/utils/randomizers.py:35-86 for one env (qpos: [nq], edited in place)."""
+  for j in range(m.njnt):
+    jt, qa = m.jnt_type[j], m.jnt_qposadr[j]
+    lo, hi = m.jnt_range[j]
+    if m.jnt_limited[j]:
+      if jt in (M.JNT_HINGE, M.JNT_SLIDE):
+        qpos[qa] = rng.uniform(lo, hi)
+      elif jt == M.JNT_BALL:
+        raise NotImplementedError("limited ball joints are not in the served domains")
+    else:
+      if jt == M.JNT_HINGE:
+        qpos[qa] = rng.uniform(-np.pi, np.pi)
+      elif jt == M.JNT_BALL:
+        q = rng.randn(4)
+        qpos[qa:qa + 4] = q / np.linalg.norm(q)
+      elif jt == M.JNT_FREE:
+        q = rng.rand(4)
+        qpos[qa + 3:qa + 7] = q / np.linalg.norm(q)
+
+
+class Task:
+  """Host side of a suite task: RNG streams, episode initialisation, obs layout.
+  Observation and reward themselves run on the device (csrc/bp_task.cu)."""
+
+  def __init__(self, tdef, random=None):
+    self.tdef = tdef
+    self._seed = random
+    self._rngs = None
+    self.scalar_obs = {"height", "head_height"}
+
+  def bind(self, physics):
+    m = physics.model
+    n = physics.nenv
+    if isinstance(self._seed, (list, tuple, np.ndarray)):
+      self._rngs = [r if isinstance(r, np.random.RandomState) else np.random.RandomState(r)
+                    for r in self._seed]
+    elif self._seed is None:
+      self._rngs = [np.random.RandomState(None) for _ in range(n)]
+    else:
+      self._rngs = [np.random.RandomState(int(self._seed) + i) for i in range(n)]
+    ip, fp = self.tdef.params(m)
+    physics._batch.set_task(self.tdef.kind, ip, fp)
+    self.nobs = physics._batch.nobs
+    self.obs_layout = self.tdef.obs(m)
+
+  @property
+  def random(self):
+    return self._rngs
+
+  def initialize_episode(self, physics):
+    m = physics.model
+    n = physics.nenv
+    qpos = physics.data.qpos
+    qvel = np.zeros((n, m.nv))
+    d, t = self.tdef.domain, self.tdef.task
+    if d == "cartpole":           # suite/cartpole.py:177-195
+      sl = m.jnt_qposadr[m.name2id("slider", "joint")]
+      h1 = m.jnt_qposadr[m.name2id("hinge_1", "joint")]
+      for e, rng in enumerate(self._rngs):
+        if t.startswith("swingup"):
+          qpos[e, sl] = .01 * rng.randn()
+          qpos[e, h1] = np.pi + .01 * rng.randn()
+          qpos[e, 2:] = .1 * rng.randn(m.nv - 2)
+        else:
+          qpos[e, sl] = rng.uniform(-.1, .1)
+          qpos[e, 1:] = rng.uniform(-.034, .034, m.nv - 1)
+        qvel[e] = 0.01 * rng.randn(m.nv)
+    elif d == "acrobot":          # suite/acrobot.py:96-106
+      ids = [m.jnt_qposadr[m.name2id(k, "joint")] for k in ("shoulder", "elbow")]
+      for e, rng in enumerate(self._rngs):
+        qpos[e, ids] = rng.uniform(-np.pi, np.pi, 2)
+    elif d == "pendulum":         # suite/pendulum.py:80-90
+      h = m.jnt_qposadr[m.name2id("hinge", "joint")]
+      for e, rng in enumerate(self._rngs):
+        qpos[e, h] = rng.uniform(-np.pi, np.pi)
+    elif d == "cheetah":          # suite/cheetah.py:63-77
+      lim = m.jnt_limited == 1
+      lo, hi = m.jnt_range[lim].T
+      for e, rng in enumerate(self._rngs):
+        qpos[e, lim] = rng.uniform(lo, hi)
+      physics.data.qpos = qpos
+      physics.after_reset()                 # derived quantities for the settle steps
+      for _ in range(4):
+        physics.step(50)                    # 200 physics steps, as the reference
+      physics.data.time = 0.0
+      return
+    elif d == "walker":           # suite/walker.py:118-129
+      for e, rng in enumerate(self._rngs):
+        _randomize_limited_and_rotational_joints(m, qpos[e], rng)
+    elif d == "humanoid":         # suite/humanoid.py:152-166: rejection on contacts
+      todo = np.ones(n, dtype=bool)
+      while todo.any():
+        for e in np.flatnonzero(todo):
+          _randomize_limited_and_rotational_joints(m, qpos[e], self._rngs[e])
+        physics.data.qpos = qpos
+        physics.after_reset()
+        todo &= physics.data.ncon > 0
+      return
+    physics.data.qpos = qpos
+    physics.data.qvel = qvel
+
+
+def _load_model(name):
+  return M.FlatModel.load(os.path.join(_MODELS, name + ".npz"))
+
+
+def build_environment(domain_name, task_name, task_kwargs=None, environment_kwargs=None,
+                      nenv=1, device=0, lanes=None, njmax=None, nconmax=None):
+  """suite/__init__.py:117-150."""
+  key = (domain_name, task_name)
+  if domain_name not in {d for d, _ in T.REGISTRY}:
+    raise ValueError("Domain {!r} does not exist.".format(domain_name))
+  if key not in T.REGISTRY:
+    raise ValueError("Level {!r} does not exist in domain {!r}.".format(task_name, domain_name))
+  tdef = T.REGISTRY[key]
+  task_kwargs = dict(task_kwargs or {})
+  environment_kwargs = dict(environment_kwargs or {})
+  m = _load_model(tdef.model)
+  physics = BatchedPhysics(m, nenv, device=device, lanes=lanes, njmax=njmax, nconmax=nconmax)
+  task = Task(tdef, random=task_kwargs.pop("random", None))
+  time_limit = task_kwargs.pop("time_limit", tdef.time_limit)
+  if task_kwargs:
+    raise TypeError("unexpected task_kwargs: {}".format(sorted(task_kwargs)))
+  return control.Environment(physics, task, time_limit=time_limit,
+                             control_timestep=tdef.control_timestep, **environment_kwargs)
+
+
+def load(domain_name, task_name, task_kwargs=None, environment_kwargs=None,
+         visualize_reward=False, **batch_kwargs):
+  """suite/__init__.py:93-114.  `visualize_reward` needs a renderer: unavailable."""
+  del visualize_reward
+  return build_environment(domain_name, task_name, task_kwargs, environment_kwargs,
+                           **batch_kwargs)

@@ -111,6 +111,8 @@ int bp_reset(bp_batch* b, int key);
 int bp_set_task(bp_batch* b, int kind, const int32_t* ip, int nip, const double* fp, int nfp);
 int bp_task_nobs(bp_batch* b);
 int bp_obs_reward(bp_batch* b, double* obs_dev, double* reward_dev);
+/* same, results copied to host buffers (synchronises) */
+int bp_obs_reward_host(bp_batch* b, double* obs_host, double* reward_host);
 
 /* End-to-end Environment.step for HOST buffers (rl/control.py:94-123): copy ctrl
  * [nenv][nu] to the device, nsub physics steps, observation/reward kernel, copy
