@@ -65,6 +65,8 @@ _SIGNATURES = {
     "bp_obs_reward": (_i32, [_vp, _vp, _vp]),
     "bp_obs_reward_host": (_i32, [_vp, _vp, _vp]),
     "bp_env_step_host": (_i32, [_vp, _i32, _vp, _vp, _vp]),
+    "bp_rewards_tolerance": (_i32, [_i32, _vp, _vp, _i64, ctypes.c_double, ctypes.c_double,
+                                    ctypes.c_double, _i32, ctypes.c_double]),
     "bp_warnings": (_i32, [_vp, _vp]),
     "bp_sync": (_i32, [_vp]),
     "bp_batch_stream": (_vp, [_vp]),
@@ -92,6 +94,22 @@ def fp64_peak_tflops(device=0):
   out = ctypes.c_double()
   check(load().bp_fp64_peak(device, ctypes.byref(out)))
   return out.value
+
+
+SIGMOIDS = {"gaussian": 0, "linear": 1, "quadratic": 2}
+
+
+def rewards_tolerance(x, bounds=(0.0, 0.0), margin=0.0, sigmoid="gaussian",
+                      value_at_margin=0.1, device=0):
+  """rewards.tolerance (utils/rewards.py:93-135) on the device."""
+  if sigmoid not in SIGMOIDS:
+    raise ValueError("Unknown sigmoid type {!r}.".format(sigmoid))
+  a = np.ascontiguousarray(x, dtype=np.float64)
+  out = np.empty_like(a)
+  check(load().bp_rewards_tolerance(device, _ptr(a), _ptr(out), a.size, float(bounds[0]),
+                                    float(bounds[1]), float(margin), SIGMOIDS[sigmoid],
+                                    float(value_at_margin)))
+  return out
 
 
 def last_error():

@@ -649,3 +649,26 @@ extern "C" int bp_sync(bp_batch* b) {
   CUDA_OK(cudaGetLastError());
   return BP_OK;
 }
+
+extern "C" int bp_launch_tolerance(const double* x, double* out, long long n, double lower,
+                                   double upper, double margin, int sig, double v1,
+                                   cudaStream_t stream);
+extern "C" int bp_rewards_tolerance(int device, const double* x_host, double* out_host,
+                                    int64_t n, double lower, double upper, double margin,
+                                    int sigmoid, double value_at_margin) {
+  if (!x_host || !out_host || n < 0) return fail(BP_EINVAL, "bad arguments");
+  if (lower > upper) return fail(BP_EINVAL, "Lower bound must be <= upper bound.");
+  if (margin < 0) return fail(BP_EINVAL, "`margin` must be non-negative.");
+  if (sigmoid < 0 || sigmoid > 2) return fail(BP_EINVAL, "Unknown sigmoid type");
+  if (n == 0) return BP_OK;
+  CUDA_OK(cudaSetDevice(device));
+  double *dx = nullptr, *dout = nullptr;
+  CUDA_OK(cudaMalloc((void**)&dx, n * 8));
+  CUDA_OK(cudaMalloc((void**)&dout, n * 8));
+  CUDA_OK(cudaMemcpy(dx, x_host, n * 8, cudaMemcpyHostToDevice));
+  int e = bp_launch_tolerance(dx, dout, n, lower, upper, margin, sigmoid, value_at_margin, 0);
+  cudaError_t ce = cudaMemcpy(out_host, dout, n * 8, cudaMemcpyDeviceToHost);
+  cudaFree(dx); cudaFree(dout);
+  if (e != 0 || ce != cudaSuccess) return fail(BP_ECUDA, "tolerance kernel failed");
+  return BP_OK;
+}

@@ -286,3 +286,21 @@ extern "C" int bp_dfma_bench(int blocks, int threads, int iters, double* scratch
   cudaEventDestroy(a); cudaEventDestroy(b);
   return (int)e;
 }
+
+// rewards.tolerance (utils/rewards.py:93-135) over a device array: the reward
+// building block of every suite task, exposed for parity tests against the
+// reference's own implementation (tests/golden/rewards_tolerance.npz).
+__global__ void bp_tolerance_kernel(const double* x, double* out, long long n, double lower,
+                                    double upper, double margin, int sig, double v1) {
+  long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i < n) out[i] = tolerance(x[i], lower, upper, margin, sig, v1);
+}
+
+extern "C" int bp_launch_tolerance(const double* x, double* out, long long n, double lower,
+                                   double upper, double margin, int sig, double v1,
+                                   cudaStream_t stream) {
+  if (n <= 0) return 0;
+  bp_tolerance_kernel<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(x, out, n, lower, upper,
+                                                                     margin, sig, v1);
+  return (int)cudaGetLastError();
+}

@@ -114,6 +114,12 @@ int bp_obs_reward(bp_batch* b, double* obs_dev, double* reward_dev);
 /* same, results copied to host buffers (synchronises) */
 int bp_obs_reward_host(bp_batch* b, double* obs_host, double* reward_host);
 
+/* rewards.tolerance (utils/rewards.py:93-135) evaluated on the device for host arrays;
+ * sigmoid: 0 gaussian, 1 linear, 2 quadratic (the kinds the served tasks use). */
+int bp_rewards_tolerance(int device, const double* x_host, double* out_host, int64_t n,
+                         double lower, double upper, double margin, int sigmoid,
+                         double value_at_margin);
+
 /* End-to-end Environment.step for HOST buffers (rl/control.py:94-123): copy ctrl
  * [nenv][nu] to the device, nsub physics steps, observation/reward kernel, copy
  * obs/reward back and synchronise.  This is the call the e2e benchmark times. */

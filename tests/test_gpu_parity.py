@@ -1,0 +1,148 @@
+"""GPU parity tests proper: the CUDA path behind include/bphys.h against the CPU
+oracle on identical seeded states, against the committed golden fixtures, and
+through size-independent properties at BASELINE.json's full sizes.
+
+Bars (BASELINE.json north_star): integer work bit-exact (contact pair ids and
+counts, constraint counts / types / ids, solver iteration count); fp64 single-step
+state within 1e-8 relative.  Tolerance used below: 1e-8 on every mjData field.
+"""
+
+import os
+
+import numpy as np
+import pytest
+
+import parity_util as PU
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-8
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+HUMANOID_SIZES = dict(njmax=120, nconmax=40)
+
+
+def _assert_parity(res):
+  for step, cmp in sorted(res.items()):
+    bad = {k: v for k, v in cmp.int_mismatch.items() if v}
+    assert not bad, "step %d integer mismatches %s\n%s" % (step, bad, cmp.report())
+    assert cmp.worst() <= TOL, "step %d\n%s" % (step, cmp.report())
+
+
+@pytest.mark.parametrize("domain", ["pendulum", "cartpole", "acrobot", "cheetah", "walker",
+                                    "hopper", "humanoid"])
+@pytest.mark.parametrize("lanes", [32, 8, 4, 1])
+def test_every_field_matches_oracle(domain, lanes):
+  kw = HUMANOID_SIZES if domain == "humanoid" else {}
+  res, stats = PU.run_parity(domain, nenv=48, nsteps=10, seed=5, check_steps=[0, 1, 2, 10],
+                             lanes=lanes, **kw)
+  _assert_parity(res)
+  if domain in ("cheetah", "walker", "hopper", "humanoid"):
+    assert max(stats["ncon"]) > 0.5 and max(stats["iter"]) > 0.5     # contacts exercised
+
+
+@pytest.mark.parametrize("lanes", [2, 16])
+def test_other_shapes_on_contact_model(lanes):
+  res, _ = PU.run_parity("cheetah", nenv=40, nsteps=5, seed=9, check_steps=[0, 5], lanes=lanes)
+  _assert_parity(res)
+
+
+def test_ragged_env_count_and_masked_envs():
+  """nenv not a multiple of 32 (partial warps) and a per-env mask."""
+  from dm_control_b200 import binding
+  m = PU.load_model("cheetah")
+  for lanes in (1, 4, 32):
+    model = binding.Model(m)
+    b = binding.Batch(model, 37, 64, 16, lanes)
+    qpos, qvel, ctrl = PU.random_states(m, 37, 2)
+    b.write("qpos", qpos); b.write("qvel", qvel); b.write("ctrl", ctrl)
+    b.forward()
+    before = b.read("qpos")
+    mask = np.zeros(37, dtype=np.uint8); mask[::3] = 1
+    b.set_mask(mask)
+    b.step(2)
+    b.set_mask(None)
+    after = b.read("qpos")
+    assert np.array_equal(after[mask == 0], before[mask == 0])
+    assert not np.array_equal(after[mask == 1], before[mask == 1])
+    assert np.allclose(b.read("time")[:, 0], 0.02 * mask)
+    b.free(); model.free()
+
+
+@pytest.mark.parametrize("domain", ["pendulum", "cartpole", "acrobot", "cheetah", "walker",
+                                    "hopper", "humanoid"])
+def test_golden_trajectories(domain):
+  """Committed oracle trajectories (tests/golden, tools/make_golden.py) replayed on
+  the GPU: ints exact, states to 1e-8 at steps 0/1/10; step 100 is reported as
+  divergence (chaotic dynamics, BASELINE.json north_star) with a loose bound."""
+  from dm_control_b200 import binding
+  g = np.load(os.path.join(GOLDEN, "traj_%s.npz" % domain))
+  m = PU.load_model(domain)
+  kw = HUMANOID_SIZES if domain == "humanoid" else {}
+  model = binding.Model(m)
+  nenv = g["qpos0"].shape[0]
+  b = binding.Batch(model, nenv, kw.get("njmax", 0), kw.get("nconmax", 0), 4)
+  b.write("qpos", g["qpos0"]); b.write("qvel", g["qvel0"]); b.write("ctrl", g["ctrl"])
+  b.forward()
+  steps = list(g["steps"])
+  done = 0
+  for k, s in enumerate(steps):
+    if s > done:
+      b.step(int(s - done)); done = int(s)
+    b.sync()
+    if s <= 10:
+      for name in ("ncon", "nefc", "solver_iter"):
+        assert np.array_equal(b.read(name), g[name][:, k]), (name, s)
+      for name in ("qpos", "qvel", "qacc", "sensordata"):
+        assert PU.rel_err(b.read(name), g[name][:, k]) <= TOL, (name, s)
+    else:
+      div = PU.rel_err(b.read("qpos"), g["qpos"][:, k])
+      print("%s: qpos divergence after %d steps: %.2e" % (domain, s, div))
+      assert div < 1e-3
+  b.free(); model.free()
+
+
+def test_readme_golden_through_cuda():
+  """The reference's only digit-level physics value (mujoco/README.md:9-49):
+  box z = 0.19996362, sphere z = 0.39996362 after 1 s — through the CUDA path."""
+  from dm_control_b200 import mjcf_compiler as C
+  from dm_control_b200.physics import BatchedPhysics
+  from test_oracle_pins import README_XML
+  m = C.compile_xml(README_XML)
+  for lanes in (32, 4, 1):
+    p = BatchedPhysics(m, nenv=3, lanes=lanes)
+    with p.reset_context():
+      p.named.data.qpos["up_down"] = 0.5
+    gx = p.named.data.geom_xpos[:, :]
+    np.testing.assert_allclose(gx[0], [[0, 0, 0], [0, 0, .8], [.2, .2, 1.]], atol=1e-15)
+    while p.time()[0] < 1.0 - 1e-12:
+      p.step()
+    z = p.named.data.geom_xpos[["box", "sphere"], "z"]
+    np.testing.assert_allclose(z, np.tile([0.19996362, 0.39996362], (3, 1)), atol=5e-9)
+    p.free()
+
+
+def test_tolerance_kernel_matches_reference_rewards_py():
+  from dm_control_b200 import binding
+  g = np.load(os.path.join(GOLDEN, "rewards_tolerance.npz"))
+  sig = {0: "gaussian", 1: "linear", 2: "quadratic"}
+  for (lo, hi, mg, sg, v1), want in zip(g["cases"], g["out"]):
+    got = binding.rewards_tolerance(g["x"], (lo, hi), mg, sig[int(sg)], v1)
+    np.testing.assert_allclose(got, want, rtol=1e-13, atol=1e-15)
+  assert binding.rewards_tolerance(np.zeros(0)).shape == (0,)            # empty input
+  with pytest.raises(binding.Error):
+    binding.rewards_tolerance(np.zeros(3), bounds=(1, 0))                # rewards_test.py
+
+
+def test_overflow_raises_reference_warnings():
+  """core_test.py:97-103: exhausted nconmax / njmax surface as warnings."""
+  from dm_control_b200 import binding
+  m = PU.load_model("humanoid")
+  model = binding.Model(m)
+  b = binding.Batch(model, 16, 6, 2, 8)           # absurdly small buffers
+  qpos, qvel, ctrl = PU.random_states(m, 16, 4)
+  qpos[:, 2] = 0.05                                # everyone lies in the floor
+  b.write("qpos", qpos)
+  b.forward()
+  w = b.warnings()
+  assert w[:, 1].sum() > 0 and w[:, 2].sum() > 0   # CONTACTFULL, CNSTRFULL
+  assert (b.read("ncon") <= 2).all() and (b.read("nefc") <= 6).all()
+  b.free(); model.free()

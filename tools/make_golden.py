@@ -1,0 +1,75 @@
+"""Generates the committed fixtures under tests/golden/ (run in the build container).
+
+1. rewards_tolerance.npz — outputs of the REFERENCE's own pure-numpy
+   `dm_control/utils/rewards.py` (imported by file path from /root/reference; it is
+   importable without MuJoCo) for the sigmoids / bounds / margins the served tasks use.
+2. traj_<domain>.npz — seeded trajectories of the CPU oracle (the reference's physics
+   engine is a closed binary that is absent): states at steps
+   0, 1, 10, 100 for 8 envs per suite model, with contact / constraint counts.
+"""
+import importlib.util
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+OUT = os.path.join(ROOT, "tests", "golden")
+
+CASES = [  # (lower, upper, margin, sigmoid, value_at_margin)
+    (0.0, 0.0, 2.0, "gaussian", 0.1), (0.0, 0.0, 1.0, "quadratic", 0.0),
+    (0.0, 0.0, 5.0, "gaussian", 0.1), (10.0, np.inf, 10.0, "linear", 0.0),
+    (1.2, np.inf, 0.6, "gaussian", 0.1), (1.0, np.inf, 0.5, "linear", 0.5),
+    (1.4, np.inf, 0.35, "gaussian", 0.1), (0.9, np.inf, 1.9, "linear", 0.0),
+    (-0.25, 0.25, 0.0, "gaussian", 0.1), (0.995, 1.0, 0.0, "gaussian", 0.1),
+    (0.0, 0.2, 1.0, "gaussian", 0.1), (0.0, 0.0, 2.0, "gaussian", 0.1)]
+
+
+def rewards_fixture():
+  spec = importlib.util.spec_from_file_location(
+      "ref_rewards", "/root/reference/dm_control/utils/rewards.py")
+  mod = importlib.util.module_from_spec(spec)
+  spec.loader.exec_module(mod)
+  x = np.concatenate([np.linspace(-12, 12, 97), [0.0, 0.2, 0.995, 1.0, 1.2, 1.4, 10.0]])
+  out = np.stack([mod.tolerance(x, bounds=(lo, hi), margin=mg, sigmoid=sg, value_at_margin=v1)
+                  for lo, hi, mg, sg, v1 in CASES])
+  np.savez(os.path.join(OUT, "rewards_tolerance.npz"), x=x, out=out,
+           cases=np.array([(lo, hi, mg, {"gaussian": 0, "linear": 1, "quadratic": 2}[sg], v1)
+                           for lo, hi, mg, sg, v1 in CASES]))
+  print("rewards_tolerance.npz", out.shape)
+
+
+def traj_fixture(domain, nenv=8, steps=(0, 1, 10, 100)):
+  import parity_util as PU
+  from oracle.oracle_py import Oracle, OracleModel
+  m = PU.load_model(domain)
+  qpos, qvel, ctrl = PU.random_states(m, nenv, seed=11)
+  om = OracleModel(m)
+  rec = {k: [] for k in ("qpos", "qvel", "qacc", "ncon", "nefc", "solver_iter", "sensordata")}
+  for e in range(nenv):
+    o = Oracle(om)
+    o.reset()
+    o.qpos[:] = qpos[e]; o.qvel[:] = qvel[e]; o.ctrl[:] = ctrl[e]
+    o.forward()
+    per = {k: [] for k in rec}
+    for s in range(max(steps) + 1):
+      if s > 0:
+        o.step()
+      if s in steps:
+        for k in rec:
+          per[k].append(np.array(getattr(o, k)))
+    for k in rec:
+      rec[k].append(np.stack(per[k]))
+  np.savez_compressed(os.path.join(OUT, "traj_%s.npz" % domain), qpos0=qpos, qvel0=qvel,
+                      ctrl=ctrl, steps=np.array(steps),
+                      **{k: np.stack(v) for k, v in rec.items()})     # [env][step][n]
+  print("traj_%s.npz" % domain, rec["qpos"][0].shape)
+
+
+if __name__ == "__main__":
+  os.makedirs(OUT, exist_ok=True)
+  rewards_fixture()
+  for d in ("pendulum", "cartpole", "acrobot", "cheetah", "walker", "hopper", "humanoid"):
+    traj_fixture(d)
