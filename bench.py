@@ -37,12 +37,17 @@ MODELS = os.path.join(ROOT, "dm_control_b200", "suite", "models")
 ALGO = {"cheetah": dict(bytes=648, flops=2.0e4), "humanoid": dict(bytes=2048, flops=2.3e5),
         "walker": dict(bytes=704, flops=1.8e4), "cartpole": dict(bytes=176, flops=1.0e4),
         "acrobot": dict(bytes=184, flops=1.0e4), "pendulum": dict(bytes=112, flops=1.5e3)}
-WORKLOADS = {"cheetah-run": dict(nenv=16384, njmax=64, nconmax=16, settle=200),
-             "humanoid-run": dict(nenv=8192, njmax=120, nconmax=40, settle=100),
-             "walker-walk": dict(nenv=16384, njmax=48, nconmax=12, settle=50),
-             "cartpole-swingup": dict(nenv=4096, njmax=4, nconmax=1, settle=0),
-             "acrobot-swingup": dict(nenv=4096, njmax=1, nconmax=1, settle=0),
-             "pendulum-swingup": dict(nenv=4096, njmax=1, nconmax=1, settle=0)}
+# `lanes`: execution shape picked from the lane sweep (profiles/r1b_sweep_lanes.jsonl)
+WORKLOADS = {"cheetah-run": dict(nenv=16384, njmax=64, nconmax=16, settle=200, lanes=4),
+             "humanoid-run": dict(nenv=8192, njmax=120, nconmax=40, settle=100, lanes=8),
+             "walker-walk": dict(nenv=16384, njmax=48, nconmax=12, settle=50, lanes=4),
+             "cartpole-swingup": dict(nenv=4096, njmax=4, nconmax=1, settle=0, lanes=2),
+             "acrobot-swingup": dict(nenv=4096, njmax=1, nconmax=1, settle=0, lanes=2),
+             "pendulum-swingup": dict(nenv=4096, njmax=1, nconmax=1, settle=0, lanes=1)}
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the step kernel from the
+# committed `ncu --set full` captures (profiles/), keyed by (task, lanes, envs per GPU)
+NCU_TRAFFIC = {("cheetah-run", 4, 16384): (321.1e6, "profiles/r1b_cheetah_g4.summary.txt"),
+               ("humanoid-run", 8, 8192): (5.70e9, "profiles/r1b_humanoid_g8.summary.txt")}
 
 
 def load_task(name):
@@ -105,12 +110,17 @@ class ClockSampler:
 LANES = {"value": 0}
 
 
+def workload_name(name, nenv, nsub):
+  return ("%s, %d envs per GPU, random actions U(-1,1), %d physics sub-step(s) per env-step"
+          % (name, nenv, nsub))
+
+
 def make_batch(name, nenv, device, seed):
   from dm_control_b200 import binding
   w = WORKLOADS[name]
   tdef, m = load_task(name)
   model = binding.Model(m, device)
-  batch = binding.Batch(model, nenv, w["njmax"], w["nconmax"], LANES["value"])
+  batch = binding.Batch(model, nenv, w["njmax"], w["nconmax"], LANES["value"] or w["lanes"])
   ip, fp = tdef.params(m)
   batch.set_task(tdef.kind, ip, fp)
   batch.write("qpos", initial_qpos(m, nenv, seed))
@@ -219,15 +229,21 @@ def cpu_run(name, nenv, steps, threads, seed=0):
   return nenv * steps / dt, dt, nsub
 
 
-def cpu_baseline(name, budget_s=12.0):
+def cpu_baseline(name, budget_s=15.0):
+  """~budget_s seconds of oracle work on every host thread: chunks of <= 1000 env-steps
+  of a 16-envs-per-thread batch (each chunk restarts from a fresh random state)."""
   threads = os.cpu_count() or 1
-  v, dt, _ = cpu_run(name, 8 * threads, 50, threads)          # calibration
   nenv = 16 * threads
-  steps = int(max(50, min(2000, budget_s * v / nenv)))
-  v, dt, nsub = cpu_run(name, nenv, steps, threads, seed=1)
-  return {"value": v, "unit": "env-steps/s", "cores": threads, "kind": "port",
-          "sample": "%s: %d envs x %d env-steps (x%d physics sub-steps), %d pthreads, "
-                    "%.1f s" % (name, nenv, steps, nsub, threads, dt)}
+  v, dt, nsub = cpu_run(name, nenv, 20, threads)               # calibration
+  chunk = int(max(20, min(1000, 1.0 * v / nenv)))              # ~1 s per chunk
+  done, spent, k = 0, 0.0, 0
+  while spent < budget_s:
+    _, dt, _ = cpu_run(name, nenv, chunk, threads, seed=1 + k)
+    done += nenv * chunk; spent += dt; k += 1
+  return {"value": done / spent, "unit": "env-steps/s", "cores": threads, "kind": "port",
+          "sample": "%s: %d envs x %d env-steps in %d chunks (x%d physics sub-steps each), "
+                    "%d pthreads, %.1f s of oracle time" % (name, nenv, chunk * k, k, nsub,
+                                                            threads, spent)}
 
 
 def reference_arm(args):
@@ -243,10 +259,9 @@ def reference_arm(args):
   for _ in range(args.warmup):
     cpu_run(name, nenv, 1, threads)
   reps = max(1, int(0.5 / max(per_step, 1e-6)))               # >= 0.5 s per timed step
-  t0 = time.perf_counter()
+  dt = 0.0
   for k in range(args.steps):
-    cpu_run(name, nenv, reps, threads, seed=k)
-  dt = time.perf_counter() - t0
+    dt += cpu_run(name, nenv, reps, threads, seed=k)[1]         # oracle time only
   value = nenv * reps * args.steps / dt
   sample = ("%s: %d envs x %d env-steps per step (x%d sub-steps), %d pthreads"
             % (name, nenv, reps, nsub, threads))
@@ -255,7 +270,8 @@ def reference_arm(args):
           "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
           "data": "synthetic",
-          "config": {"workload": sample, "note": "reference engine (MuJoCo 2.00) is a "
+          "config": {"workload": workload_name(name, WORKLOADS[name]["nenv"], nsub),
+                     "sample": sample, "note": "reference engine (MuJoCo 2.00) is a "
                      "closed binary absent from the reference tree; CPU oracle port timed"},
           "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": threads,
                            "kind": "port", "sample": sample},
@@ -331,13 +347,13 @@ def main():
   achieved = algo_bytes / (ms_kernel * 1e-3) / 1e9
   fp64_peak = binding.fp64_peak_tflops(local)
   fl = ALGO[domain]["flops"] * r["nsub"] * nenv / (ms_kernel * 1e-3) / 1e12
+  traffic, traffic_src = NCU_TRAFFIC.get((name, r["lanes"], nenv), (None, None))
   line = {
       "metric": "env-steps/sec (%s)" % name, "value": value, "unit": "env-steps/s",
       "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
       "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
       "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-      "config": {"workload": "%s, %d envs per GPU, random actions U(-1,1), %d physics "
-                             "sub-step(s) per env-step" % (name, nenv, r["nsub"]),
+      "config": {"workload": workload_name(name, nenv, r["nsub"]),
                  "envs_per_gpu": nenv, "n_sub_steps": r["nsub"],
                  "l2": "per-GPU image %.0f MB > 126 MB L2 (inputs larger than L2)"
                        % (nenv * r["stride"] * 8 / 1e6),
@@ -345,10 +361,12 @@ def main():
       "e2e": {"value": e2e, "unit": "env-steps/s",
               "h2d_bytes_per_step": nenv * r["nu"] * 8,
               "d2h_bytes_per_step": nenv * (r["nobs"] + 1) * 8},
-      "gpu_launches": 2 * args.steps,
+      # per env-step: ctrl scatter (bp_field_copy_kernel), bp_step_kernel, bp_task_kernel
+      "gpu_launches": 3 * args.steps,
       "clocks": r["clocks"],
       "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                   "frac": achieved / hbm_peak, "traffic": None,
+                   "frac": achieved / hbm_peak, "traffic": traffic,
+                   "traffic_source": traffic_src,
                    "peak_source": "measured" if peaks else "fallback",
                    "kernel": "bp_step_kernel", "kernel_ms": ms_kernel,
                    "algorithmic_bytes_per_launch": algo_bytes,

@@ -140,7 +140,14 @@ class FieldIndexer:
     a = self._array()
     k = self._convert(key)
     if self._batched:
-      a[(slice(None),) + k] = value
+      sel = (slice(None),) + k
+      value = np.asarray(value)
+      tgt = a[sel].shape
+      # one value per env for a single-element key: [nenv] -> [nenv, 1, ...]
+      if value.ndim == 1 and len(tgt) > 1 and value.shape[0] == tgt[0] and \
+          all(s == 1 for s in tgt[1:]):
+        value = value.reshape(tgt)
+      a[sel] = value
     else:
       a[k] = value
     self._set(a.reshape(a.shape[0], -1) if self._batched else a)
