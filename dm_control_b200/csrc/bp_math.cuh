@@ -29,6 +29,8 @@ struct Ctx {
   int* ip;         // element 0 of the int32 region
   int lane;        // lane inside the group, 0 .. G-1
   unsigned mask;   // warp lanes of this group
+  bool act;        // false: this group has no environment (ragged tail / masked out)
+  bool lock;       // true: the block's warps re-align at stage boundaries (BP_LOCK)
   __device__ __forceinline__ DP null() const { return DP{nullptr}; }
 };
 
@@ -36,6 +38,11 @@ struct Ctx {
 #define IF(f) (typename C::IP{c.ip + (long long)c.P.L.f * C::S})
 #define SYNC() do { if (C::G > 1) __syncwarp(c.mask); } while (0)
 #define BP_STAGE template <class C> __device__ __noinline__
+// Stage boundary of the lock-step shapes: every thread of the block (active or not)
+// arrives, so the block's warps execute the same stage -- and share its instruction
+// cache lines -- at the same time.  Only in code whose trip count is uniform per launch.
+#define BP_LOCK() do { if (c.lock) __syncthreads(); } while (0)
+#define RUN(call) do { if (c.act) { call; } } while (0)
 
 template <class A, class B>
 __device__ __forceinline__ double dot3(A a, B b) {

@@ -17,18 +17,26 @@
 #include "bp_sensor.cuh"
 #include "bp_solver.cuh"
 
-BP_STAGE void bp_fwd_position(const C& c) {
-  bp_kinematics(c);
-  bp_com_pos(c);
-  bp_transmission(c);
-  bp_crb(c);
-  const BpModel& m = c.P.m;
-  auto qLD = DF(qLD), qM = DF(qM);
-  for (int i = c.lane; i < m.nM; i += C::G) qLD[i] = qM[i];
-  SYNC();
-  bp_factor_sparse(c, qLD, DF(qLDiagInv));
-  bp_collision(c);
-  bp_make_constraint(c);
+// The composite functions below run for EVERY thread of a block, also for groups
+// without an environment (c.act false), which only take part in the BP_LOCK barriers.
+template <class C>
+__device__ __forceinline__ void bp_fwd_position(const C& c) {
+  if (c.act) {
+    bp_kinematics(c);
+    bp_com_pos(c);
+    bp_transmission(c);
+    bp_crb(c);
+    const BpModel& m = c.P.m;
+    auto qLD = DF(qLD), qM = DF(qM);
+    for (int i = c.lane; i < m.nM; i += C::G) qLD[i] = qM[i];
+    SYNC();
+    bp_factor_sparse(c, qLD, DF(qLDiagInv));
+  }
+  BP_LOCK();
+  RUN(bp_collision(c));
+  BP_LOCK();
+  RUN(bp_make_constraint(c));
+  BP_LOCK();
 }
 
 BP_STAGE void bp_fwd_velocity(const C& c) {
@@ -39,17 +47,25 @@ BP_STAGE void bp_fwd_velocity(const C& c) {
   bp_rne(c, false, DF(s_cacc), DF(s_cfrc), c.null(), DF(qfrc_bias), 0);
 }
 
-BP_STAGE void bp_forward(const C& c, bool skipsensor) {
+template <class C>
+__device__ __forceinline__ void bp_forward(const C& c, bool skipsensor) {
   bp_fwd_position(c);
-  if (!skipsensor) bp_sensors(c, STAGE_POS);
-  bp_energy_pos(c);
-  bp_fwd_velocity(c);
-  if (!skipsensor) bp_sensors(c, STAGE_VEL);
-  bp_energy_vel(c);
-  bp_fwd_actuation(c);
-  bp_fwd_acceleration(c);
-  bp_fwd_constraint(c);
-  if (!skipsensor) bp_sensors(c, STAGE_ACC);
+  if (c.act) {
+    if (!skipsensor) bp_sensors(c, STAGE_POS);
+    bp_energy_pos(c);
+    bp_fwd_velocity(c);
+    if (!skipsensor) bp_sensors(c, STAGE_VEL);
+    bp_energy_vel(c);
+  }
+  BP_LOCK();
+  if (c.act) {
+    bp_fwd_actuation(c);
+    bp_fwd_acceleration(c);
+  }
+  BP_LOCK();
+  RUN(bp_fwd_constraint(c));
+  BP_LOCK();
+  if (c.act && !skipsensor) bp_sensors(c, STAGE_ACC);
 }
 
 // zero the persistent image, qpos = qpos0 (mj_resetData, engine.py:268-289)
@@ -125,87 +141,145 @@ BP_STAGE void bp_euler(const C& c) {
   bp_advance(c, DF(act_dot), qa, c.null());
 }
 
-BP_STAGE void bp_rk4(const C& c) {
-  const BpModel& m = c.P.m;
-  const double A[3][3] = {{0.5, 0, 0}, {0, 0.5, 0}, {0, 0, 1}};
-  const double B[4] = {1.0 / 6, 1.0 / 3, 1.0 / 3, 1.0 / 6};
-  const double Ct[3] = {0.5, 0.5, 1.0};
-  const int nq = m.nq, nv = m.nv, na = m.na, nf = 2 * nv + na;
-  const double h = m.opt_timestep, t0 = DF(time)[0];
-  auto q0 = DF(s_rk), v0 = q0 + nq, a0 = v0 + nv, F = a0 + na, dX = F + 4 * nf;
+// ---- RK4 (mj_RungeKutta(4)): state saved in s_rk = [q0 | v0 | a0 | F[4][nf] | dX[nf]] ----
+template <class C>
+struct RkView {
+  typename C::DP q0, v0, a0, F, dX;
+  int nq, nv, na, nf;
+  __device__ __forceinline__ RkView(const C& c) {
+    const BpModel& m = c.P.m;
+    nq = m.nq; nv = m.nv; na = m.na; nf = 2 * nv + na;
+    q0 = DF(s_rk); v0 = q0 + nq; a0 = v0 + nv; F = a0 + na; dX = F + 4 * nf;
+  }
+};
+
+BP_STAGE void bp_rk4_begin(const C& c) {
+  RkView<C> r(c);
   SYNC();
-  for (int i = c.lane; i < nq; i += C::G) q0[i] = DF(qpos)[i];
-  for (int i = c.lane; i < nv; i += C::G) {
+  for (int i = c.lane; i < r.nq; i += C::G) r.q0[i] = DF(qpos)[i];
+  for (int i = c.lane; i < r.nv; i += C::G) {
     double v = DF(qvel)[i];
-    v0[i] = v; F[i] = v; F[nv + i] = DF(qacc)[i];
+    r.v0[i] = v; r.F[i] = v; r.F[r.nv + i] = DF(qacc)[i];
   }
-  for (int i = c.lane; i < na; i += C::G) { a0[i] = DF(act)[i]; F[2 * nv + i] = DF(act_dot)[i]; }
+  for (int i = c.lane; i < r.na; i += C::G) {
+    r.a0[i] = DF(act)[i]; r.F[2 * r.nv + i] = DF(act_dot)[i];
+  }
+  if (c.lane == 0) r.dX[r.nf] = DF(time)[0];        // t0 rides behind dX
   SYNC();
-#pragma unroll 1
-  for (int s = 1; s < 4; s++) {
-    for (int k = c.lane; k < nf; k += C::G) {
-      double x = 0;
-      for (int j = 0; j < s; j++) x += A[s - 1][j] * F[j * nf + k];
-      dX[k] = x;
-    }
-    for (int i = c.lane; i < nq; i += C::G) DF(qpos)[i] = q0[i];
-    SYNC();
-    bp_integrate_pos(c, DF(qpos), dX, h);
-    for (int k = c.lane; k < nv; k += C::G) DF(qvel)[k] = v0[k] + h * dX[nv + k];
-    for (int k = c.lane; k < na; k += C::G) DF(act)[k] = a0[k] + h * dX[2 * nv + k];
-    if (c.lane == 0) DF(time)[0] = t0 + h * Ct[s - 1];
-    SYNC();
-    bp_forward(c, true);
-    auto Fs = F + s * nf;
-    for (int i = c.lane; i < nv; i += C::G) { Fs[i] = DF(qvel)[i]; Fs[nv + i] = DF(qacc)[i]; }
-    for (int i = c.lane; i < na; i += C::G) Fs[2 * nv + i] = DF(act_dot)[i];
-    SYNC();
-  }
-  for (int k = c.lane; k < nf; k += C::G) {
+}
+
+// state <- x0 + h * sum_j A[s-1][j] F_j, time <- t0 + h * C[s-1]
+BP_STAGE void bp_rk4_stage(const C& c, int s) {
+  RkView<C> r(c);
+  const double A[3][3] = {{0.5, 0, 0}, {0, 0.5, 0}, {0, 0, 1}};
+  const double Ct[3] = {0.5, 0.5, 1.0};
+  const double h = c.P.m.opt_timestep, t0 = r.dX[r.nf];
+  for (int k = c.lane; k < r.nf; k += C::G) {
     double x = 0;
-    for (int j = 0; j < 4; j++) x += B[j] * F[j * nf + k];
-    dX[k] = x;
+    for (int j = 0; j < s; j++) x += A[s - 1][j] * r.F[j * r.nf + k];
+    r.dX[k] = x;
   }
-  for (int i = c.lane; i < nq; i += C::G) DF(qpos)[i] = q0[i];
-  for (int i = c.lane; i < nv; i += C::G) DF(qvel)[i] = v0[i];
-  for (int i = c.lane; i < na; i += C::G) DF(act)[i] = a0[i];
+  for (int i = c.lane; i < r.nq; i += C::G) DF(qpos)[i] = r.q0[i];
+  SYNC();
+  bp_integrate_pos(c, DF(qpos), r.dX, h);
+  for (int k = c.lane; k < r.nv; k += C::G) DF(qvel)[k] = r.v0[k] + h * r.dX[r.nv + k];
+  for (int k = c.lane; k < r.na; k += C::G) DF(act)[k] = r.a0[k] + h * r.dX[2 * r.nv + k];
+  if (c.lane == 0) DF(time)[0] = t0 + h * Ct[s - 1];
+  SYNC();
+}
+
+BP_STAGE void bp_rk4_collect(const C& c, int s) {
+  RkView<C> r(c);
+  auto Fs = r.F + s * r.nf;
+  for (int i = c.lane; i < r.nv; i += C::G) { Fs[i] = DF(qvel)[i]; Fs[r.nv + i] = DF(qacc)[i]; }
+  for (int i = c.lane; i < r.na; i += C::G) Fs[2 * r.nv + i] = DF(act_dot)[i];
+  SYNC();
+}
+
+BP_STAGE void bp_rk4_finish(const C& c) {
+  RkView<C> r(c);
+  const double B[4] = {1.0 / 6, 1.0 / 3, 1.0 / 3, 1.0 / 6};
+  const double t0 = r.dX[r.nf];
+  SYNC();
+  for (int k = c.lane; k < r.nf; k += C::G) {
+    double x = 0;
+    for (int j = 0; j < 4; j++) x += B[j] * r.F[j * r.nf + k];
+    r.dX[k] = x;
+  }
+  for (int i = c.lane; i < r.nq; i += C::G) DF(qpos)[i] = r.q0[i];
+  for (int i = c.lane; i < r.nv; i += C::G) DF(qvel)[i] = r.v0[i];
+  for (int i = c.lane; i < r.na; i += C::G) DF(act)[i] = r.a0[i];
   if (c.lane == 0) DF(time)[0] = t0;
   SYNC();
-  bp_advance(c, dX + 2 * nv, dX + nv, dX);
+  bp_advance(c, r.dX + 2 * r.nv, r.dX + r.nv, r.dX);
 }
 
+template <class C>
+__device__ __forceinline__ void bp_rk4(const C& c) {
+  RUN(bp_rk4_begin(c));
+#pragma unroll 1
+  for (int s = 1; s < 4; s++) {
+    RUN(bp_rk4_stage(c, s));
+    bp_forward(c, true);
+    RUN(bp_rk4_collect(c, s));
+  }
+  RUN(bp_rk4_finish(c));
+}
+
+// mj_checkAcc: a bad qacc resets the env and recomputes forward.  Data dependent, so
+// the recomputation runs without stage barriers.
 BP_STAGE void bp_check_acc(const C& c) {
-  if (bp_check(c, DF(qacc), c.P.m.nv, W_BADQACC)) bp_forward(c, false);
+  if (bp_check(c, DF(qacc), c.P.m.nv, W_BADQACC)) {
+    C solo = c;
+    solo.lock = false;
+    bp_forward(solo, false);
+  }
 }
 
-BP_STAGE void bp_mj_step(const C& c) {
+BP_STAGE void bp_check_state(const C& c) {
   const BpModel& m = c.P.m;
   bp_check(c, DF(qpos), m.nq, W_BADQPOS);
   bp_check(c, DF(qvel), m.nv, W_BADQVEL);
+}
+
+template <class C>
+__device__ __forceinline__ void bp_mj_step(const C& c) {
+  RUN(bp_check_state(c));
   bp_forward(c, false);
-  bp_check_acc(c);
-  if (m.opt_integrator == 1) bp_rk4(c); else bp_euler(c);
+  RUN(bp_check_acc(c));
+  if (c.P.m.opt_integrator == 1) bp_rk4(c); else RUN(bp_euler(c));
+  BP_LOCK();
 }
 
-BP_STAGE void bp_step1(const C& c) {
-  const BpModel& m = c.P.m;
-  bp_check(c, DF(qpos), m.nq, W_BADQPOS);
-  bp_check(c, DF(qvel), m.nv, W_BADQVEL);
+template <class C>
+__device__ __forceinline__ void bp_step1(const C& c) {
+  RUN(bp_check_state(c));
   bp_fwd_position(c);
-  bp_sensors(c, STAGE_POS);
-  bp_energy_pos(c);
-  bp_fwd_velocity(c);
-  bp_sensors(c, STAGE_VEL);
-  bp_energy_vel(c);
+  if (c.act) {
+    bp_sensors(c, STAGE_POS);
+    bp_energy_pos(c);
+    bp_fwd_velocity(c);
+    bp_sensors(c, STAGE_VEL);
+    bp_energy_vel(c);
+  }
+  BP_LOCK();
 }
 
-BP_STAGE void bp_step2(const C& c) {
-  bp_fwd_actuation(c);
-  bp_fwd_acceleration(c);
-  bp_fwd_constraint(c);
-  bp_sensors(c, STAGE_ACC);
-  bp_check_acc(c);
-  bp_euler(c);
+template <class C>
+__device__ __forceinline__ void bp_step2(const C& c) {
+  if (c.act) {
+    bp_fwd_actuation(c);
+    bp_fwd_acceleration(c);
+  }
+  BP_LOCK();
+  RUN(bp_fwd_constraint(c));
+  BP_LOCK();
+  if (c.act) {
+    bp_sensors(c, STAGE_ACC);
+    bp_check_acc(c);
+    bp_euler(c);
+  }
+  BP_LOCK();
 }
 
 template <class C>
@@ -230,12 +304,28 @@ __device__ __forceinline__ void bp_run_mode(const C& c) {
 }
 
 // ---- G < 32: image in global memory, 32/G environments per warp -----------------
+#ifndef BP_TPB
+#define BP_TPB 512       // upper bound of threads per block of the global-memory shapes
+#endif
+#ifndef BP_LOCKSTEP
+#define BP_LOCKSTEP 1    // 1: warps of a block re-align at stage boundaries (BP_LOCK)
+#endif
+#ifdef BP_MINB
+#define BP_BOUNDS __launch_bounds__(BP_TPB, BP_MINB)
+#else
+#define BP_BOUNDS __launch_bounds__(BP_TPB)
+#endif
 template <int G, int S>
-__global__ void __launch_bounds__(128)
+__global__ void BP_BOUNDS
 bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
   const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  const long long env = tid / G;
-  if (env >= P.nenv || (P.mask && !P.mask[env])) return;
+  long long env = tid / G;
+  const bool act = env < P.nenv && (!P.mask || P.mask[env]);
+  const bool lock = BP_LOCKSTEP != 0;
+  if (!act) {
+    if (!lock) return;
+    env = 0;                 // pointers stay valid; nothing is touched when !act
+  }
   const int wl = threadIdx.x & 31;
   double* base;
   int* ib;
@@ -248,8 +338,17 @@ bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
     ib = (int*)(wb + (long long)P.L.ints * 32) + (env & 31);
   }
   unsigned mask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (wl & ~(G - 1)));
-  Ctx<G, S> c{P, base, ib, wl & (G - 1), mask};
+  Ctx<G, S> c{P, base, ib, wl & (G - 1), mask, act, lock};
   bp_run_mode(c);
+}
+
+// Block size of a launch: as many warps per block as possible (they share instruction
+// cache lines between BP_LOCK barriers: +50..160 % measured, profiles/r1d_*) while the
+// grid still covers the 148 SMs.
+static inline int bp_block_threads(long long threads_total) {
+  int tpb = BP_TPB;
+  while (tpb > 64 && (threads_total + tpb - 1) / tpb < 148) tpb >>= 1;
+  return tpb;
 }
 
 #endif  // BP_PIPELINE_CUH_

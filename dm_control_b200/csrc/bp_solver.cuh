@@ -54,7 +54,10 @@ BP_STAGE double bp_update_constraint(const C& c, typename C::DP jar, int nefc, b
       else { f = -d * x; st = ST_QUADRATIC; cr = 0.5 * d * x * x; }
     }
     cost += cr;
-    if (write) { force[r] = f; state[r] = st; }
+    if (write) {
+      force[r] = f; state[r] = st;
+      DF(s_rmask)[r] = st == ST_QUADRATIC ? DF(s_rdof)[r] : 0.0;   // bit patterns, see below
+    }
   }
   cost = group_sum(c, cost);
   if (write) {
@@ -139,9 +142,27 @@ BP_STAGE double bp_linesearch(const C& c, double scale, int nefc) {
   return a;
 }
 
-// dense Cholesky H = L L^T in place (lower); rows on lanes, right-looking.
+// ---- dense Cholesky H = L L^T in place (lower triangle, row stride nvp) -------------
+// Row i of the system belongs to lane i % G, register slot i / G.  When nv <= 4 G every
+// lane owns at most BP_RS = 4 rows, so a column step keeps its 4 partial dot products in
+// registers (left-looking: one broadcast load of L[j][k] feeds 4 independent FMAs) and
+// the triangular solves keep the whole right-hand side in registers, exchanging pivots
+// by group shuffles instead of memory + barriers.  Larger systems fall back to the
+// generic right-looking code.
+#define BP_RS 4
+
+template <class C>
+__device__ __forceinline__ double bp_slot(const double (&v)[BP_RS], int s) {
+  return s == 0 ? v[0] : (s == 1 ? v[1] : (s == 2 ? v[2] : v[3]));
+}
+
+template <class C>
+__device__ __forceinline__ double group_bcast(const C& c, double v, int src) {
+  return C::G == 1 ? v : __shfl_sync(c.mask, v, src, C::G);
+}
+
 // Returns false when a pivot is not positive.
-BP_STAGE bool bp_chol_factor(const C& c, typename C::DP H, typename C::DP dinv) {
+BP_STAGE bool bp_chol_factor_generic(const C& c, typename C::DP H, typename C::DP dinv) {
   const int n = c.P.m.nv, nvp = c.P.m.nvp;
 #pragma unroll 1
   for (int j = 0; j < n; j++) {
@@ -163,8 +184,47 @@ BP_STAGE bool bp_chol_factor(const C& c, typename C::DP H, typename C::DP dinv) 
   return true;
 }
 
-BP_STAGE void bp_chol_solve(const C& c, typename C::DP L, typename C::DP dinv,
-                            typename C::DP x) {
+BP_STAGE bool bp_chol_factor(const C& c, typename C::DP H, typename C::DP dinv) {
+  const int n = c.P.m.nv, nvp = c.P.m.nvp;
+  if (n > BP_RS * C::G) return bp_chol_factor_generic(c, H, dinv);
+  int row[BP_RS];
+#pragma unroll
+  for (int s = 0; s < BP_RS; s++) row[s] = (c.lane + C::G * s) * nvp;
+#pragma unroll 1
+  for (int j = 0; j < n; j++) {
+    // acc[s] = H[i][j] - sum_{k<j} L[i][k] L[j][k] for this lane's rows i >= j
+    double acc[BP_RS];
+    bool on[BP_RS];
+#pragma unroll
+    for (int s = 0; s < BP_RS; s++) {
+      int i = c.lane + C::G * s;
+      on[s] = i >= j && i < n;
+      acc[s] = on[s] ? H[row[s] + j] : 0.0;
+    }
+    const int rj = j * nvp;
+#pragma unroll 2
+    for (int k = 0; k < j; k++) {
+      double ljk = H[rj + k];
+#pragma unroll
+      for (int s = 0; s < BP_RS; s++)
+        if (on[s]) acc[s] -= H[row[s] + k] * ljk;
+    }
+    double piv = group_bcast(c, bp_slot<C>(acc, j / C::G), j % C::G);
+    if (piv < BP_MINVAL) return false;     // uniform across the group
+    double d = sqrt(piv), inv = 1.0 / d;
+#pragma unroll
+    for (int s = 0; s < BP_RS; s++) {
+      int i = c.lane + C::G * s;
+      if (on[s]) H[row[s] + j] = i == j ? d : acc[s] * inv;
+    }
+    if (c.lane == 0) dinv[j] = inv;
+    SYNC();                                 // column j (and row j+1 up to it) visible
+  }
+  return true;
+}
+
+BP_STAGE void bp_chol_solve_generic(const C& c, typename C::DP L, typename C::DP dinv,
+                                    typename C::DP x) {
   const int n = c.P.m.nv, nvp = c.P.m.nvp;
 #pragma unroll 1
   for (int k = 0; k < n; k++) {
@@ -184,24 +244,72 @@ BP_STAGE void bp_chol_solve(const C& c, typename C::DP L, typename C::DP dinv,
   }
 }
 
+BP_STAGE void bp_chol_solve(const C& c, typename C::DP L, typename C::DP dinv,
+                            typename C::DP x) {
+  const int n = c.P.m.nv, nvp = c.P.m.nvp;
+  if (n > BP_RS * C::G) { bp_chol_solve_generic(c, L, dinv, x); return; }
+  double xs[BP_RS];
+#pragma unroll
+  for (int s = 0; s < BP_RS; s++) {
+    int i = c.lane + C::G * s;
+    xs[s] = i < n ? x[i] : 0.0;
+  }
+  // forward sweep L y = b by columns: pivot k is final on its owner, everyone below it
+  // subtracts L[i][k] y_k
+#pragma unroll 1
+  for (int k = 0; k < n; k++) {
+    double yk = group_bcast(c, bp_slot<C>(xs, k / C::G), k % C::G) * dinv[k];
+#pragma unroll
+    for (int s = 0; s < BP_RS; s++) {
+      int i = c.lane + C::G * s;
+      if (i == k) xs[s] = yk;
+      else if (i > k && i < n) xs[s] -= L[i * nvp + k] * yk;
+    }
+  }
+  // backward sweep L^T x = y by rows of L
+#pragma unroll 1
+  for (int k = n - 1; k >= 0; k--) {
+    double xk = group_bcast(c, bp_slot<C>(xs, k / C::G), k % C::G) * dinv[k];
+    const int rk = k * nvp;
+#pragma unroll
+    for (int s = 0; s < BP_RS; s++) {
+      int i = c.lane + C::G * s;
+      if (i == k) xs[s] = xk;
+      else if (i < k) xs[s] -= L[rk + i] * xk;
+    }
+  }
+#pragma unroll
+  for (int s = 0; s < BP_RS; s++) {
+    int i = c.lane + C::G * s;
+    if (i < n) x[i] = xs[s];
+  }
+  SYNC();
+}
+
 // grad = Ma - qfrc_smooth - qfrc_constraint;  H = M + J^T D_active J;  Mgrad = H^-1 grad
 BP_STAGE void bp_newton_gradient(const C& c, int nefc) {
   const BpModel& m = c.P.m;
   const int nv = m.nv, nvp = m.nvp;
   auto H = DF(s_H), Md = DF(s_Md), grad = DF(s_grad), Mgrad = DF(s_Mgrad);
   auto J = DF(efc_J), D = DF(efc_D);
-  auto state = IF(efc_state);
   for (int i = c.lane; i < nv; i += C::G) {
     double g = DF(s_Ma)[i] - DF(qfrc_smooth)[i] - DF(qfrc_constraint)[i];
     grad[i] = g; Mgrad[i] = g;
   }
+  // entry (i, j) only visits the active rows whose dof set holds both i and j
+  // (s_rmask: dof bit mask of quadratic rows, 0 for the others): limit and friction
+  // rows touch one diagonal entry, a contact row the ancestors of its two bodies.
+  auto rmask = DF(s_rmask);
 #pragma unroll 1
   for (int e = c.lane; e < m.ntri; e += C::G) {
     int i = m.tri_i[e], j = m.tri_j[e];
+    const unsigned long long bits = (1ull << i) | (1ull << j);
     double acc = Md[i * nvp + j];
-#pragma unroll 1
-    for (int r = 0; r < nefc; r++)
-      if (state[r] == ST_QUADRATIC) acc += D[r] * J[r * nvp + i] * J[r * nvp + j];
+#pragma unroll 2
+    for (int r = 0; r < nefc; r++) {
+      unsigned long long mk = (unsigned long long)__double_as_longlong(rmask[r]);
+      if ((mk & bits) == bits) acc += D[r] * J[r * nvp + i] * J[r * nvp + j];
+    }
     H[i * nvp + j] = acc;
   }
   SYNC();
@@ -229,6 +337,17 @@ BP_STAGE void bp_fwd_constraint(const C& c) {
     if (c.lane == 0) IF(solver_iter)[0] = 0;
     SYNC();
     return;
+  }
+  // dof set of every row as a bit mask (nv <= 64), stored bit-for-bit in a double slot
+#pragma unroll 1
+  for (int r = c.lane; r < nefc; r += C::G) {
+    int t = IF(efc_type)[r], id = IF(efc_id)[r];
+    unsigned long long mk;
+    if (t == CN_FRICTION_DOF) mk = 1ull << id;
+    else if (t == CN_LIMIT_JOINT) mk = 1ull << m.jnt_dofadr[id];
+    else mk = m.body_dofmask[m.geom_bodyid[IF(contact_geom1)[id]]] |
+              m.body_dofmask[m.geom_bodyid[IF(contact_geom2)[id]]];
+    DF(s_rdof)[r] = __longlong_as_double((long long)mk);
   }
   // dense copy of M
   auto Md = DF(s_Md), qM = DF(qM);
