@@ -41,7 +41,14 @@ struct Ctx {
 // Stage boundary of the lock-step shapes: every thread of the block (active or not)
 // arrives, so the block's warps execute the same stage -- and share its instruction
 // cache lines -- at the same time.  Only in code whose trip count is uniform per launch.
-#define BP_LOCK() do { if (c.lock) __syncthreads(); } while (0)
+// Barrier ids: 0 after kinematics..factorM, 1 after collision, 2 after makeConstraint,
+// 3 after the velocity stage, 4 before the solver, 5 after the solver, 6 end of a step,
+// 7 after mj_step1's velocity stage, 8 every Newton iteration, 9 after kinematics,
+// 10 after comPos..crb, 11 inside the velocity stage.  BP_LOCKMASK selects the ones that are compiled in.
+#ifndef BP_LOCKMASK
+#define BP_LOCKMASK 0x1ff
+#endif
+#define BP_LOCK(id) do { if (((BP_LOCKMASK) >> (id) & 1) && c.lock) __syncthreads(); } while (0)
 #define RUN(call) do { if (c.act) { call; } } while (0)
 
 template <class A, class B>

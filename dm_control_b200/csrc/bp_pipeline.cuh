@@ -23,48 +23,59 @@ template <class C>
 __device__ __forceinline__ void bp_fwd_position(const C& c) {
   if (c.act) {
     bp_kinematics(c);
+  }
+  BP_LOCK(9);
+  if (c.act) {
     bp_com_pos(c);
     bp_transmission(c);
     bp_crb(c);
+  }
+  BP_LOCK(10);
+  if (c.act) {
     const BpModel& m = c.P.m;
     auto qLD = DF(qLD), qM = DF(qM);
     for (int i = c.lane; i < m.nM; i += C::G) qLD[i] = qM[i];
     SYNC();
     bp_factor_sparse(c, qLD, DF(qLDiagInv));
   }
-  BP_LOCK();
+  BP_LOCK(0);
   RUN(bp_collision(c));
-  BP_LOCK();
+  BP_LOCK(1);
   RUN(bp_make_constraint(c));
-  BP_LOCK();
+  BP_LOCK(2);
 }
 
-BP_STAGE void bp_fwd_velocity(const C& c) {
-  bp_actuator_velocity(c);
-  bp_com_vel(c);
-  bp_passive(c);
-  bp_reference_constraint(c);
-  bp_rne(c, false, DF(s_cacc), DF(s_cfrc), c.null(), DF(qfrc_bias), 0);
+// position sensors / energy and mj_fwdVelocity, in two lock-step halves
+template <class C>
+__device__ __forceinline__ void bp_fwd_velocity(const C& c, bool skipsensor) {
+  if (c.act) {
+    if (!skipsensor) bp_sensors(c, STAGE_POS);
+    bp_energy_pos(c);
+    bp_actuator_velocity(c);
+    bp_com_vel(c);
+    bp_passive(c);
+  }
+  BP_LOCK(11);
+  if (c.act) {
+    bp_reference_constraint(c);
+    bp_rne(c, false, DF(s_cacc), DF(s_cfrc), c.null(), DF(qfrc_bias), 0);
+    if (!skipsensor) bp_sensors(c, STAGE_VEL);
+    bp_energy_vel(c);
+  }
 }
 
 template <class C>
 __device__ __forceinline__ void bp_forward(const C& c, bool skipsensor) {
   bp_fwd_position(c);
-  if (c.act) {
-    if (!skipsensor) bp_sensors(c, STAGE_POS);
-    bp_energy_pos(c);
-    bp_fwd_velocity(c);
-    if (!skipsensor) bp_sensors(c, STAGE_VEL);
-    bp_energy_vel(c);
-  }
-  BP_LOCK();
+  bp_fwd_velocity(c, skipsensor);
+  BP_LOCK(3);
   if (c.act) {
     bp_fwd_actuation(c);
     bp_fwd_acceleration(c);
   }
-  BP_LOCK();
-  RUN(bp_fwd_constraint(c));
-  BP_LOCK();
+  BP_LOCK(4);
+  bp_fwd_constraint(c);
+  BP_LOCK(5);
   if (c.act && !skipsensor) bp_sensors(c, STAGE_ACC);
 }
 
@@ -248,21 +259,15 @@ __device__ __forceinline__ void bp_mj_step(const C& c) {
   bp_forward(c, false);
   RUN(bp_check_acc(c));
   if (c.P.m.opt_integrator == 1) bp_rk4(c); else RUN(bp_euler(c));
-  BP_LOCK();
+  BP_LOCK(6);
 }
 
 template <class C>
 __device__ __forceinline__ void bp_step1(const C& c) {
   RUN(bp_check_state(c));
   bp_fwd_position(c);
-  if (c.act) {
-    bp_sensors(c, STAGE_POS);
-    bp_energy_pos(c);
-    bp_fwd_velocity(c);
-    bp_sensors(c, STAGE_VEL);
-    bp_energy_vel(c);
-  }
-  BP_LOCK();
+  bp_fwd_velocity(c, false);
+  BP_LOCK(7);
 }
 
 template <class C>
@@ -271,15 +276,15 @@ __device__ __forceinline__ void bp_step2(const C& c) {
     bp_fwd_actuation(c);
     bp_fwd_acceleration(c);
   }
-  BP_LOCK();
-  RUN(bp_fwd_constraint(c));
-  BP_LOCK();
+  BP_LOCK(4);
+  bp_fwd_constraint(c);
+  BP_LOCK(5);
   if (c.act) {
     bp_sensors(c, STAGE_ACC);
     bp_check_acc(c);
     bp_euler(c);
   }
-  BP_LOCK();
+  BP_LOCK(6);
 }
 
 template <class C>

@@ -34,9 +34,13 @@ BP_STAGE void bp_mul_j(const C& c, typename C::DP out, typename C::DP x, typenam
 }
 
 // constraint cost at residual jar; optionally writes force/state and J^T force
-BP_STAGE double bp_update_constraint(const C& c, typename C::DP jar, int nefc, bool write) {
+// *changed (write only): some row's Hessian weight differs from the previous call, i.e.
+// the factorisation of H is stale
+BP_STAGE double bp_update_constraint(const C& c, typename C::DP jar, int nefc, bool write,
+                                     bool* changed) {
   const int nv = c.P.m.nv, nvp = c.P.m.nvp;
   double cost = 0;
+  bool chg = false;
   auto force = DF(efc_force), D = DF(efc_D), R = DF(efc_R);
   auto type = IF(efc_type), state = IF(efc_state);
 #pragma unroll 1
@@ -56,11 +60,14 @@ BP_STAGE double bp_update_constraint(const C& c, typename C::DP jar, int nefc, b
     cost += cr;
     if (write) {
       force[r] = f; state[r] = st;
-      DF(s_rmask)[r] = st == ST_QUADRATIC ? DF(s_rdof)[r] : 0.0;   // bit patterns, see below
+      double w = st == ST_QUADRATIC ? d : 0.0;         // row weight in the Hessian
+      chg |= DF(s_rw)[r] != w;
+      DF(s_rw)[r] = w;
     }
   }
   cost = group_sum(c, cost);
   if (write) {
+    *changed = group_any(c, chg);
     SYNC();
     auto J = DF(efc_J);
     auto qc = DF(qfrc_constraint);
@@ -184,6 +191,21 @@ BP_STAGE bool bp_chol_factor_generic(const C& c, typename C::DP H, typename C::D
   return true;
 }
 
+// acc[s] -= sum_{k<j} L[i_s][k] L[j][k] for the register slots s >= S0 (slots below hold
+// rows that are already finished)
+template <class C, int S0>
+__device__ __forceinline__ void bp_chol_dots(typename C::DP H, const int (&row)[BP_RS],
+                                             const bool (&on)[BP_RS], double (&acc)[BP_RS],
+                                             int rj, int j) {
+#pragma unroll 2
+  for (int k = 0; k < j; k++) {
+    double ljk = H[rj + k];
+#pragma unroll
+    for (int s = S0; s < BP_RS; s++)
+      if (on[s]) acc[s] -= H[row[s] + k] * ljk;
+  }
+}
+
 BP_STAGE bool bp_chol_factor(const C& c, typename C::DP H, typename C::DP dinv) {
   const int n = c.P.m.nv, nvp = c.P.m.nvp;
   if (n > BP_RS * C::G) return bp_chol_factor_generic(c, H, dinv);
@@ -202,12 +224,11 @@ BP_STAGE bool bp_chol_factor(const C& c, typename C::DP H, typename C::DP dinv) 
       acc[s] = on[s] ? H[row[s] + j] : 0.0;
     }
     const int rj = j * nvp;
-#pragma unroll 2
-    for (int k = 0; k < j; k++) {
-      double ljk = H[rj + k];
-#pragma unroll
-      for (int s = 0; s < BP_RS; s++)
-        if (on[s]) acc[s] -= H[row[s] + k] * ljk;
+    switch (j / C::G) {
+      case 0: bp_chol_dots<C, 0>(H, row, on, acc, rj, j); break;
+      case 1: bp_chol_dots<C, 1>(H, row, on, acc, rj, j); break;
+      case 2: bp_chol_dots<C, 2>(H, row, on, acc, rj, j); break;
+      default: bp_chol_dots<C, 3>(H, row, on, acc, rj, j); break;
     }
     double piv = group_bcast(c, bp_slot<C>(acc, j / C::G), j % C::G);
     if (piv < BP_MINVAL) return false;     // uniform across the group
@@ -287,32 +308,81 @@ BP_STAGE void bp_chol_solve(const C& c, typename C::DP L, typename C::DP dinv,
 }
 
 // grad = Ma - qfrc_smooth - qfrc_constraint;  H = M + J^T D_active J;  Mgrad = H^-1 grad
-BP_STAGE void bp_newton_gradient(const C& c, int nefc) {
+//
+// The Hessian is assembled from the structure of J instead of a dense triple loop:
+// friction-loss and limit rows (the first `nsingle` rows) have one non-zero, +-1, and
+// add their weight to one diagonal entry; the rows of a contact are non-zero only on
+// the dofs that move its two bodies (body_dofmask), so a contact updates the
+// k (k + 1) / 2 entries of that dof set, split over the lanes by outer dof.
+BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refactor) {
   const BpModel& m = c.P.m;
   const int nv = m.nv, nvp = m.nvp;
   auto H = DF(s_H), Md = DF(s_Md), grad = DF(s_grad), Mgrad = DF(s_Mgrad);
-  auto J = DF(efc_J), D = DF(efc_D);
+  auto J = DF(efc_J), rw = DF(s_rw), rdof = DF(s_rdof);
   for (int i = c.lane; i < nv; i += C::G) {
     double g = DF(s_Ma)[i] - DF(qfrc_smooth)[i] - DF(qfrc_constraint)[i];
     grad[i] = g; Mgrad[i] = g;
   }
-  // entry (i, j) only visits the active rows whose dof set holds both i and j
-  // (s_rmask: dof bit mask of quadratic rows, 0 for the others): limit and friction
-  // rows touch one diagonal entry, a contact row the ancestors of its two bodies.
-  auto rmask = DF(s_rmask);
-#pragma unroll 1
+  if (!refactor) {            // same active set as last time: H and its factor stand
+    SYNC();
+    bp_chol_solve(c, H, DF(s_Hdinv), Mgrad);
+    return;
+  }
   for (int e = c.lane; e < m.ntri; e += C::G) {
-    int i = m.tri_i[e], j = m.tri_j[e];
-    const unsigned long long bits = (1ull << i) | (1ull << j);
-    double acc = Md[i * nvp + j];
-#pragma unroll 2
-    for (int r = 0; r < nefc; r++) {
-      unsigned long long mk = (unsigned long long)__double_as_longlong(rmask[r]);
-      if ((mk & bits) == bits) acc += D[r] * J[r * nvp + i] * J[r * nvp + j];
-    }
-    H[i * nvp + j] = acc;
+    int w = m.tri_i[e] * nvp + m.tri_j[e];
+    H[w] = Md[w];
   }
   SYNC();
+#pragma unroll 1
+  for (int i = c.lane; i < nv; i += C::G) {
+    double acc = 0;
+    for (int r = 0; r < nsingle; r++)
+      if ((int)rdof[r] == i) acc += rw[r];
+    if (acc != 0) H[i * nvp + i] += acc;
+  }
+  SYNC();
+  const int ncon = IF(ncon)[0];
+#pragma unroll 1
+  for (int ci = 0; ci < ncon; ci++) {
+    const int a = IF(contact_efc_address)[ci];
+    if (a < 0) continue;
+    const int dim = IF(contact_dim)[ci];
+    int n = dim == 1 ? 1 : (m.opt_cone == 0 ? 2 * (dim - 1) : dim);
+    if (a + n > nefc) n = nefc - a;
+    bool any = false;
+    for (int q = 0; q < n; q++) any |= rw[a + q] != 0;
+    if (!any) continue;                                   // uniform across the group
+    const unsigned long long mk = m.body_dofmask[m.geom_bodyid[IF(contact_geom1)[ci]]] |
+                                  m.body_dofmask[m.geom_bodyid[IF(contact_geom2)[ci]]];
+    const int k = __popcll(mk);
+#pragma unroll 1
+    for (int q0 = 0; q0 < n; q0 += 4) {                   // rows in chunks of 4
+      const int nq = n - q0 < 4 ? n - q0 : 4;
+      const int r0 = (a + q0) * nvp;
+      unsigned long long remi = mk;
+      for (int t = 0; t < c.lane; t++) remi &= remi - 1;
+#pragma unroll 1
+      for (int ap = c.lane; ap < k; ap += C::G) {
+        const int i = __ffsll((long long)remi) - 1;
+        double ji[4];
+#pragma unroll
+        for (int q = 0; q < 4; q++) ji[q] = q < nq ? rw[a + q0 + q] * J[r0 + q * nvp + i] : 0.0;
+        unsigned long long remj = mk;
+#pragma unroll 1
+        for (int bp = 0; bp <= ap; bp++) {
+          const int j = __ffsll((long long)remj) - 1;
+          remj &= remj - 1;
+          double sum = 0;
+#pragma unroll
+          for (int q = 0; q < 4; q++)
+            if (q < nq) sum += ji[q] * J[r0 + q * nvp + j];
+          H[i * nvp + j] += sum;
+        }
+        for (int t = 0; t < C::G; t++) remi &= remi - 1;
+      }
+      SYNC();
+    }
+  }
   if (!bp_chol_factor(c, H, DF(s_Hdinv))) {
     SYNC();
     for (int e = c.lane; e < m.ntri; e += C::G) {
@@ -325,10 +395,20 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc) {
   bp_chol_solve(c, H, DF(s_Hdinv), Mgrad);
 }
 
-BP_STAGE void bp_fwd_constraint(const C& c) {
+// Solver state that lives across Newton iterations (registers of the calling kernel)
+struct BpSolve {
+  double cost, improvement, gradient;
+  int iter, nefc, nsingle;
+  bool done;
+};
+
+// everything up to the first search direction; st.done when there is nothing to iterate
+BP_STAGE void bp_solver_begin(const C& c, BpSolve& st) {
   const BpModel& m = c.P.m;
   const int nv = m.nv, nvp = m.nvp, nefc = IF(nefc)[0];
   auto qacc = DF(qacc), warm = DF(qacc_warmstart), as = DF(qacc_smooth);
+  st.iter = 0; st.improvement = 0; st.gradient = 0; st.nefc = nefc; st.nsingle = 0;
+  st.cost = 0;
   if (nefc == 0) {
     for (int i = c.lane; i < nv; i += C::G) {
       double a = as[i];
@@ -336,19 +416,20 @@ BP_STAGE void bp_fwd_constraint(const C& c) {
     }
     if (c.lane == 0) IF(solver_iter)[0] = 0;
     SYNC();
+    st.done = true;
     return;
   }
-  // dof set of every row as a bit mask (nv <= 64), stored bit-for-bit in a double slot
+  // friction-loss and limit rows come first and have a single +-1 entry: remember
+  // its dof; `nsingle` = number of such rows
+  int nsingle = 0;
 #pragma unroll 1
   for (int r = c.lane; r < nefc; r += C::G) {
     int t = IF(efc_type)[r], id = IF(efc_id)[r];
-    unsigned long long mk;
-    if (t == CN_FRICTION_DOF) mk = 1ull << id;
-    else if (t == CN_LIMIT_JOINT) mk = 1ull << m.jnt_dofadr[id];
-    else mk = m.body_dofmask[m.geom_bodyid[IF(contact_geom1)[id]]] |
-              m.body_dofmask[m.geom_bodyid[IF(contact_geom2)[id]]];
-    DF(s_rdof)[r] = __longlong_as_double((long long)mk);
+    if (t == CN_FRICTION_DOF) { DF(s_rdof)[r] = id; nsingle++; }
+    else if (t == CN_LIMIT_JOINT) { DF(s_rdof)[r] = m.jnt_dofadr[id]; nsingle++; }
   }
+  nsingle = (int)(group_sum(c, (double)nsingle) + 0.5);
+  st.nsingle = nsingle;
   // dense copy of M
   auto Md = DF(s_Md), qM = DF(qM);
   for (int w = c.lane; w < nv * nvp; w += C::G) Md[w] = 0;
@@ -369,9 +450,9 @@ BP_STAGE void bp_fwd_constraint(const C& c) {
     SYNC();
     bp_mul_md(c, Md, Ma, qacc);
     bp_mul_j(c, jar, qacc, DF(efc_aref), nefc);
-    double cw = bp_update_constraint(c, jar, nefc, false) + bp_gauss_cost(c);
+    double cw = bp_update_constraint(c, jar, nefc, false, nullptr) + bp_gauss_cost(c);
     bp_mul_j(c, jar, as, DF(efc_aref), nefc);
-    double cs = bp_update_constraint(c, jar, nefc, false);
+    double cs = bp_update_constraint(c, jar, nefc, false, nullptr);
     use_warm = cw < cs;
     SYNC();
   }
@@ -379,43 +460,72 @@ BP_STAGE void bp_fwd_constraint(const C& c) {
   SYNC();
   bp_mul_md(c, Md, Ma, qacc);
   bp_mul_j(c, jar, qacc, DF(efc_aref), nefc);
-  double cost = bp_update_constraint(c, jar, nefc, true) + bp_gauss_cost(c);
-  bp_newton_gradient(c, nefc);
+  bool changed;
+  st.cost = bp_update_constraint(c, jar, nefc, true, &changed) + bp_gauss_cost(c);
+  bp_newton_gradient(c, nefc, nsingle, true);
   for (int i = c.lane; i < nv; i += C::G) search[i] = -DF(s_Mgrad)[i];
   SYNC();
+  st.done = m.opt_iterations <= 0;
+}
+
+// one Newton iteration: line search along s_search, new gradient and search direction
+BP_STAGE void bp_solver_iterate(const C& c, BpSolve& st) {
+  const BpModel& m = c.P.m;
+  const int nv = m.nv, nefc = st.nefc;
+  auto qacc = DF(qacc), Ma = DF(s_Ma), jar = DF(s_jar), search = DF(s_search);
   const double scale = 1.0 / (m.stat_meaninertia * (nv > 1 ? nv : 1));
-  int iter = 0;
-  double improvement = 0, gradient = 0;
-#pragma unroll 1
-  while (iter < m.opt_iterations) {
-    bp_mul_md(c, Md, DF(s_Mv), search);
-    bp_mul_j(c, DF(s_jv), search, c.null(), nefc);
-    double alpha = bp_linesearch(c, scale, nefc);
-    if (alpha == 0) break;
-    for (int i = c.lane; i < nv; i += C::G) {
-      qacc[i] += alpha * search[i];
-      Ma[i] += alpha * DF(s_Mv)[i];
-    }
-    for (int r = c.lane; r < nefc; r += C::G) jar[r] += alpha * DF(s_jv)[r];
-    SYNC();
-    double old = cost;
-    cost = bp_update_constraint(c, jar, nefc, true) + bp_gauss_cost(c);
-    bp_newton_gradient(c, nefc);
-    double gn = 0;
-    for (int i = c.lane; i < nv; i += C::G) gn += DF(s_grad)[i] * DF(s_grad)[i];
-    gn = group_sum(c, gn);
-    improvement = scale * (old - cost); gradient = scale * sqrt(gn);
-    iter++;
-    if (improvement < m.opt_tolerance || gradient < m.opt_tolerance) break;
-    for (int i = c.lane; i < nv; i += C::G) search[i] = -DF(s_Mgrad)[i];
-    SYNC();
+  bp_mul_md(c, DF(s_Md), DF(s_Mv), search);
+  bp_mul_j(c, DF(s_jv), search, c.null(), nefc);
+  double alpha = bp_linesearch(c, scale, nefc);
+  if (alpha == 0) { st.done = true; return; }
+  for (int i = c.lane; i < nv; i += C::G) {
+    qacc[i] += alpha * search[i];
+    Ma[i] += alpha * DF(s_Mv)[i];
   }
-  if (c.lane == 0) {
-    IF(solver_iter)[0] = iter;
-    DF(solver_stat)[0] = improvement; DF(solver_stat)[1] = gradient;
-  }
-  for (int i = c.lane; i < nv; i += C::G) warm[i] = qacc[i];
+  for (int r = c.lane; r < nefc; r += C::G) jar[r] += alpha * DF(s_jv)[r];
   SYNC();
+  double old = st.cost;
+  bool changed;
+  st.cost = bp_update_constraint(c, jar, nefc, true, &changed) + bp_gauss_cost(c);
+  bp_newton_gradient(c, nefc, st.nsingle, changed);
+  double gn = 0;
+  for (int i = c.lane; i < nv; i += C::G) gn += DF(s_grad)[i] * DF(s_grad)[i];
+  gn = group_sum(c, gn);
+  st.improvement = scale * (old - st.cost); st.gradient = scale * sqrt(gn);
+  st.iter++;
+  if (st.improvement < m.opt_tolerance || st.gradient < m.opt_tolerance ||
+      st.iter >= m.opt_iterations) { st.done = true; return; }
+  for (int i = c.lane; i < nv; i += C::G) search[i] = -DF(s_Mgrad)[i];
+  SYNC();
+}
+
+BP_STAGE void bp_solver_end(const C& c, const BpSolve& st) {
+  if (st.nefc == 0) return;
+  const int nv = c.P.m.nv;
+  if (c.lane == 0) {
+    IF(solver_iter)[0] = st.iter;
+    DF(solver_stat)[0] = st.improvement; DF(solver_stat)[1] = st.gradient;
+  }
+  for (int i = c.lane; i < nv; i += C::G) DF(qacc_warmstart)[i] = DF(qacc)[i];
+  SYNC();
+}
+
+// mj_fwdConstraint.  In the lock-step shapes the Newton loop runs until every
+// environment of the block has converged, and the block's warps re-align at every
+// iteration (environments that are done skip the body).
+template <class C>
+__device__ __forceinline__ void bp_fwd_constraint(const C& c) {
+  BpSolve st;
+  st.done = true; st.nefc = 0;
+  RUN(bp_solver_begin(c, st));
+  if (c.lock && (BP_LOCKMASK >> 8 & 1)) {
+    while (__syncthreads_or(!st.done))
+      if (!st.done) bp_solver_iterate(c, st);
+  } else {
+#pragma unroll 1
+    while (!st.done) bp_solver_iterate(c, st);
+  }
+  RUN(bp_solver_end(c, st));
 }
 
 #endif  // BP_SOLVER_CUH_
