@@ -46,8 +46,8 @@ WORKLOADS = {"cheetah-run": dict(nenv=16384, njmax=64, nconmax=16, settle=200, l
              "pendulum-swingup": dict(nenv=4096, njmax=1, nconmax=1, settle=0, lanes=1)}
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the step kernel from the
 # committed `ncu --set full` captures (profiles/), keyed by (task, lanes, envs per GPU)
-NCU_TRAFFIC = {("cheetah-run", 4, 16384): (321.1e6, "profiles/r1b_cheetah_g4.summary.txt"),
-               ("humanoid-run", 8, 8192): (5.70e9, "profiles/r1b_humanoid_g8.summary.txt")}
+NCU_TRAFFIC = {("cheetah-run", 4, 16384): (345.5e6, "profiles/r1g_cheetah_g4.summary.txt"),
+               ("humanoid-run", 8, 8192): (5.531e9, "profiles/r1g_humanoid_g8.summary.txt")}
 
 
 def load_task(name):

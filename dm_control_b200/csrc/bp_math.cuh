@@ -31,11 +31,14 @@ struct Ctx {
   unsigned mask;   // warp lanes of this group
   bool act;        // false: this group has no environment (ragged tail / masked out)
   bool lock;       // true: the block's warps re-align at stage boundaries (BP_LOCK)
+  double* hot;     // this env's shared-memory arena (nullptr: those arrays stay global)
   __device__ __forceinline__ DP null() const { return DP{nullptr}; }
 };
 
 #define DF(f) (typename C::DP{c.sm + (long long)c.P.L.f * C::S})
 #define IF(f) (typename C::IP{c.ip + (long long)c.P.L.f * C::S})
+// solver arrays that live in the shared-memory arena when there is one (S == 1 only)
+#define HOT(f, off) ((C::S == 1 && c.hot) ? typename C::DP{c.hot + (off)} : DF(f))
 #define SYNC() do { if (C::G > 1) __syncwarp(c.mask); } while (0)
 #define BP_STAGE template <class C> __device__ __noinline__
 // Stage boundary of the lock-step shapes: every thread of the block (active or not)

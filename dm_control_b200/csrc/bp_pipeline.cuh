@@ -11,6 +11,7 @@
 #ifndef BP_PIPELINE_CUH_
 #define BP_PIPELINE_CUH_
 #include <cuda_runtime.h>
+#include <cstdlib>
 
 #include "bp_collide.cuh"
 #include "bp_constraint.cuh"
@@ -343,7 +344,10 @@ bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
     ib = (int*)(wb + (long long)P.L.ints * 32) + (env & 31);
   }
   unsigned mask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (wl & ~(G - 1)));
-  Ctx<G, S> c{P, base, ib, wl & (G - 1), mask, act, lock};
+  extern __shared__ double bp_arena[];
+  double* hot = (S == 1 && P.hot_doubles > 0)
+      ? bp_arena + (long long)(threadIdx.x / G) * P.hot_doubles : nullptr;
+  Ctx<G, S> c{P, base, ib, wl & (G - 1), mask, act, lock, hot};
   bp_run_mode(c);
 }
 
@@ -351,9 +355,43 @@ bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
 // cache lines between BP_LOCK barriers: +50..160 % measured, profiles/r1d_*) while the
 // grid still covers the 148 SMs.
 static inline int bp_block_threads(long long threads_total) {
-  int tpb = BP_TPB;
-  while (tpb > 64 && (threads_total + tpb - 1) / tpb < 148) tpb >>= 1;
-  return tpb;
+  if (const char* e = getenv("BPHYS_BLOCK_THREADS")) {       // tuning knob (multiple of 32)
+    int v = atoi(e);
+    if (v >= 32 && v <= BP_TPB && v % 32 == 0) return v;
+  }
+  const long long warps = (threads_total + 31) / 32;
+  const long long per_sm = (warps + 147) / 148;        // 148 SMs
+  if (per_sm * 32 <= BP_TPB) return per_sm < 2 ? 64 : (int)per_sm * 32;   // one block per SM
+  return BP_TPB;
+}
+
+// Launch of one global-memory shape.  BPHYS_ARENA=1 moves the per-env solver arena
+// (packed Hessian + pivots + Mgrad) to shared memory when it fits; it is off by default
+// because the L1 capacity it takes costs more than the shorter latency gains
+// (humanoid-run: 710 k vs 790 k env-steps/s, profiles/r1_tuning.md).
+template <int G, int S>
+static int bp_launch_gmem(const BpParams* P, cudaStream_t stream) {
+  const long long total = P->nenv * G;
+  const int threads = bp_block_threads(total);
+  const unsigned blocks = (unsigned)((total + threads - 1) / threads);
+  BpParams Q = *P;
+  Q.hot_doubles = 0;
+  size_t bytes = 0;
+  if (S == 1 && getenv("BPHYS_ARENA")) {
+    const int hot = P->m.ntri + 2 * P->m.nv;
+    const size_t need = (size_t)(threads / G) * hot * sizeof(double);
+    if (need <= 200 * 1024) { Q.hot_doubles = hot; bytes = need; }
+  }
+  static size_t configured = 48 * 1024;
+  if (bytes > configured) {
+    cudaError_t e = cudaFuncSetAttribute(bp_step_kernel_gmem<G, S>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)bytes);
+    if (e != cudaSuccess) return (int)e;
+    configured = bytes;
+  }
+  bp_step_kernel_gmem<G, S><<<blocks, threads, bytes, stream>>>(Q);
+  return (int)cudaGetLastError();
 }
 
 #endif  // BP_PIPELINE_CUH_

@@ -157,6 +157,8 @@ BP_STAGE double bp_linesearch(const C& c, double scale, int nefc) {
 // by group shuffles instead of memory + barriers.  Larger systems fall back to the
 // generic right-looking code.
 #define BP_RS 4
+// the Hessian and its factor are stored as a packed lower triangle, row i at i (i + 1) / 2
+#define PK(i, j) ((i) * ((i) + 1) / 2 + (j))
 
 template <class C>
 __device__ __forceinline__ double bp_slot(const double (&v)[BP_RS], int s) {
@@ -170,21 +172,21 @@ __device__ __forceinline__ double group_bcast(const C& c, double v, int src) {
 
 // Returns false when a pivot is not positive.
 BP_STAGE bool bp_chol_factor_generic(const C& c, typename C::DP H, typename C::DP dinv) {
-  const int n = c.P.m.nv, nvp = c.P.m.nvp;
+  const int n = c.P.m.nv;
 #pragma unroll 1
   for (int j = 0; j < n; j++) {
-    double s = H[j * nvp + j];
+    double s = H[PK(j, j)];
     if (s < BP_MINVAL) return false;      // uniform across the group
     s = sqrt(s);
     double inv = 1.0 / s;
     SYNC();
-    if (c.lane == 0) { H[j * nvp + j] = s; dinv[j] = inv; }
-    for (int i = j + 1 + c.lane; i < n; i += C::G) H[i * nvp + j] /= s;
+    if (c.lane == 0) { H[PK(j, j)] = s; dinv[j] = inv; }
+    for (int i = j + 1 + c.lane; i < n; i += C::G) H[PK(i, j)] /= s;
     SYNC();
 #pragma unroll 1
     for (int i = j + 1 + c.lane; i < n; i += C::G) {
-      double lij = H[i * nvp + j];
-      for (int k = j + 1; k <= i; k++) H[i * nvp + k] -= lij * H[k * nvp + j];
+      double lij = H[PK(i, j)];
+      for (int k = j + 1; k <= i; k++) H[PK(i, k)] -= lij * H[PK(k, j)];
     }
     SYNC();
   }
@@ -197,7 +199,7 @@ template <class C, int S0>
 __device__ __forceinline__ void bp_chol_dots(typename C::DP H, const int (&row)[BP_RS],
                                              const bool (&on)[BP_RS], double (&acc)[BP_RS],
                                              int rj, int j) {
-#pragma unroll 2
+#pragma unroll 4
   for (int k = 0; k < j; k++) {
     double ljk = H[rj + k];
 #pragma unroll
@@ -207,11 +209,11 @@ __device__ __forceinline__ void bp_chol_dots(typename C::DP H, const int (&row)[
 }
 
 BP_STAGE bool bp_chol_factor(const C& c, typename C::DP H, typename C::DP dinv) {
-  const int n = c.P.m.nv, nvp = c.P.m.nvp;
+  const int n = c.P.m.nv;
   if (n > BP_RS * C::G) return bp_chol_factor_generic(c, H, dinv);
   int row[BP_RS];
 #pragma unroll
-  for (int s = 0; s < BP_RS; s++) row[s] = (c.lane + C::G * s) * nvp;
+  for (int s = 0; s < BP_RS; s++) { int i = c.lane + C::G * s; row[s] = i * (i + 1) / 2; }
 #pragma unroll 1
   for (int j = 0; j < n; j++) {
     // acc[s] = H[i][j] - sum_{k<j} L[i][k] L[j][k] for this lane's rows i >= j
@@ -223,7 +225,7 @@ BP_STAGE bool bp_chol_factor(const C& c, typename C::DP H, typename C::DP dinv) 
       on[s] = i >= j && i < n;
       acc[s] = on[s] ? H[row[s] + j] : 0.0;
     }
-    const int rj = j * nvp;
+    const int rj = j * (j + 1) / 2;
     switch (j / C::G) {
       case 0: bp_chol_dots<C, 0>(H, row, on, acc, rj, j); break;
       case 1: bp_chol_dots<C, 1>(H, row, on, acc, rj, j); break;
@@ -246,13 +248,13 @@ BP_STAGE bool bp_chol_factor(const C& c, typename C::DP H, typename C::DP dinv) 
 
 BP_STAGE void bp_chol_solve_generic(const C& c, typename C::DP L, typename C::DP dinv,
                                     typename C::DP x) {
-  const int n = c.P.m.nv, nvp = c.P.m.nvp;
+  const int n = c.P.m.nv;
 #pragma unroll 1
   for (int k = 0; k < n; k++) {
     double xk = x[k] * dinv[k];
     SYNC();
     if (c.lane == 0) x[k] = xk;
-    for (int i = k + 1 + c.lane; i < n; i += C::G) x[i] -= L[i * nvp + k] * xk;
+    for (int i = k + 1 + c.lane; i < n; i += C::G) x[i] -= L[PK(i, k)] * xk;
     SYNC();
   }
 #pragma unroll 1
@@ -260,14 +262,14 @@ BP_STAGE void bp_chol_solve_generic(const C& c, typename C::DP L, typename C::DP
     double xk = x[k] * dinv[k];
     SYNC();
     if (c.lane == 0) x[k] = xk;
-    for (int i = c.lane; i < k; i += C::G) x[i] -= L[k * nvp + i] * xk;
+    for (int i = c.lane; i < k; i += C::G) x[i] -= L[PK(k, i)] * xk;
     SYNC();
   }
 }
 
 BP_STAGE void bp_chol_solve(const C& c, typename C::DP L, typename C::DP dinv,
                             typename C::DP x) {
-  const int n = c.P.m.nv, nvp = c.P.m.nvp;
+  const int n = c.P.m.nv;
   if (n > BP_RS * C::G) { bp_chol_solve_generic(c, L, dinv, x); return; }
   double xs[BP_RS];
 #pragma unroll
@@ -284,14 +286,14 @@ BP_STAGE void bp_chol_solve(const C& c, typename C::DP L, typename C::DP dinv,
     for (int s = 0; s < BP_RS; s++) {
       int i = c.lane + C::G * s;
       if (i == k) xs[s] = yk;
-      else if (i > k && i < n) xs[s] -= L[i * nvp + k] * yk;
+      else if (i > k && i < n) xs[s] -= L[PK(i, k)] * yk;
     }
   }
   // backward sweep L^T x = y by rows of L
 #pragma unroll 1
   for (int k = n - 1; k >= 0; k--) {
     double xk = group_bcast(c, bp_slot<C>(xs, k / C::G), k % C::G) * dinv[k];
-    const int rk = k * nvp;
+    const int rk = PK(k, 0);
 #pragma unroll
     for (int s = 0; s < BP_RS; s++) {
       int i = c.lane + C::G * s;
@@ -317,7 +319,9 @@ BP_STAGE void bp_chol_solve(const C& c, typename C::DP L, typename C::DP dinv,
 BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refactor) {
   const BpModel& m = c.P.m;
   const int nv = m.nv, nvp = m.nvp;
-  auto H = DF(s_H), Md = DF(s_Md), grad = DF(s_grad), Mgrad = DF(s_Mgrad);
+  const int ntri = m.ntri;
+  auto H = HOT(s_H, 0), Hdinv = HOT(s_Hdinv, ntri), Mgrad = HOT(s_Mgrad, ntri + nv);
+  auto Md = DF(s_Md), grad = DF(s_grad);
   auto J = DF(efc_J), rw = DF(s_rw), rdof = DF(s_rdof);
   for (int i = c.lane; i < nv; i += C::G) {
     double g = DF(s_Ma)[i] - DF(qfrc_smooth)[i] - DF(qfrc_constraint)[i];
@@ -325,20 +329,17 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refacto
   }
   if (!refactor) {            // same active set as last time: H and its factor stand
     SYNC();
-    bp_chol_solve(c, H, DF(s_Hdinv), Mgrad);
+    bp_chol_solve(c, H, Hdinv, Mgrad);
     return;
   }
-  for (int e = c.lane; e < m.ntri; e += C::G) {
-    int w = m.tri_i[e] * nvp + m.tri_j[e];
-    H[w] = Md[w];
-  }
+  for (int e = c.lane; e < ntri; e += C::G) H[e] = Md[m.tri_i[e] * nvp + m.tri_j[e]];
   SYNC();
 #pragma unroll 1
   for (int i = c.lane; i < nv; i += C::G) {
     double acc = 0;
     for (int r = 0; r < nsingle; r++)
       if ((int)rdof[r] == i) acc += rw[r];
-    if (acc != 0) H[i * nvp + i] += acc;
+    if (acc != 0) H[PK(i, i)] += acc;
   }
   SYNC();
   const int ncon = IF(ncon)[0];
@@ -376,23 +377,20 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refacto
 #pragma unroll
           for (int q = 0; q < 4; q++)
             if (q < nq) sum += ji[q] * J[r0 + q * nvp + j];
-          H[i * nvp + j] += sum;
+          H[PK(i, j)] += sum;
         }
         for (int t = 0; t < C::G; t++) remi &= remi - 1;
       }
       SYNC();
     }
   }
-  if (!bp_chol_factor(c, H, DF(s_Hdinv))) {
+  if (!bp_chol_factor(c, H, Hdinv)) {
     SYNC();
-    for (int e = c.lane; e < m.ntri; e += C::G) {
-      int i = m.tri_i[e], j = m.tri_j[e];
-      H[i * nvp + j] = Md[i * nvp + j];
-    }
+    for (int e = c.lane; e < ntri; e += C::G) H[e] = Md[m.tri_i[e] * nvp + m.tri_j[e]];
     SYNC();
-    bp_chol_factor(c, H, DF(s_Hdinv));
+    bp_chol_factor(c, H, Hdinv);
   }
-  bp_chol_solve(c, H, DF(s_Hdinv), Mgrad);
+  bp_chol_solve(c, H, Hdinv, Mgrad);
 }
 
 // Solver state that lives across Newton iterations (registers of the calling kernel)
@@ -463,7 +461,7 @@ BP_STAGE void bp_solver_begin(const C& c, BpSolve& st) {
   bool changed;
   st.cost = bp_update_constraint(c, jar, nefc, true, &changed) + bp_gauss_cost(c);
   bp_newton_gradient(c, nefc, nsingle, true);
-  for (int i = c.lane; i < nv; i += C::G) search[i] = -DF(s_Mgrad)[i];
+  for (int i = c.lane; i < nv; i += C::G) search[i] = -HOT(s_Mgrad, m.ntri + nv)[i];
   SYNC();
   st.done = m.opt_iterations <= 0;
 }
@@ -495,7 +493,7 @@ BP_STAGE void bp_solver_iterate(const C& c, BpSolve& st) {
   st.iter++;
   if (st.improvement < m.opt_tolerance || st.gradient < m.opt_tolerance ||
       st.iter >= m.opt_iterations) { st.done = true; return; }
-  for (int i = c.lane; i < nv; i += C::G) search[i] = -DF(s_Mgrad)[i];
+  for (int i = c.lane; i < nv; i += C::G) search[i] = -HOT(s_Mgrad, m.ntri + nv)[i];
   SYNC();
 }
 

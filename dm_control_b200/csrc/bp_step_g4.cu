@@ -2,9 +2,5 @@
 #include "bp_pipeline.cuh"
 
 extern "C" int bp_launch_step_g4(const BpParams* P, cudaStream_t stream) {
-  long long total = P->nenv * 4;
-  const int threads = bp_block_threads(total);
-  unsigned blocks = (unsigned)((total + threads - 1) / threads);
-  bp_step_kernel_gmem<4, 1><<<blocks, threads, 0, stream>>>(*P);
-  return (int)cudaGetLastError();
+  return bp_launch_gmem<4, 1>(P, stream);
 }

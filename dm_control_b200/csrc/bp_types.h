@@ -157,8 +157,11 @@ struct BpParams {
   long long stride;  // doubles per env in `image` (persist for the smem variant, total otherwise)
   int interleave;    // 1: env images contiguous; 32: images of a warp's 32 envs interleaved
   int lanes;         // lanes per environment (group size G)
-  int mode, nsub, disable_actuation, reserved;
+  int mode, nsub, disable_actuation;
+  int hot_doubles;   // per-env shared-memory arena of the global-memory shapes (0 = none)
 };
+// arena layout: packed Hessian / Cholesky factor (ntri), its inverse pivots (nv), Mgrad (nv)
+
 
 // suite task descriptor: kind + ids / constants resolved by name on the host
 struct BpTask {
