@@ -362,7 +362,7 @@ def main():
               "h2d_bytes_per_step": nenv * r["nu"] * 8,
               "d2h_bytes_per_step": nenv * (r["nobs"] + 1) * 8},
       # per env-step: ctrl scatter (bp_field_copy_kernel), bp_step_kernel, bp_task_kernel
-      "gpu_launches": 3 * args.steps,
+      "gpu_launches": 3 * args.steps * world,
       "clocks": r["clocks"],
       "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                    "frac": achieved / hbm_peak, "traffic": traffic,
