@@ -184,6 +184,25 @@ __global__ void bp_task_kernel(const __grid_constant__ BpParams P,
       }
       break;
     }
+    case TASK_HOPPER: {     // suite/hopper.py:80-99,122-148
+      // ip: torso body, foot body, speed sensor adr, touch_toe adr, touch_heel adr; fp: hopping
+      const ImgView xipos = d.at(L.xipos);
+      double height = xipos[3 * T.ip[0] + 2] - xipos[3 * T.ip[1] + 2];
+      if (o) {
+        for (int i = 1; i < m.nq; i++) o[k++] = qpos[i];
+        for (int i = 0; i < m.nv; i++) o[k++] = qvel[i];
+        o[k++] = log1p(sens[T.ip[3]]); o[k++] = log1p(sens[T.ip[4]]);
+      }
+      double standing = tolerance(height, 0.6, 2, 0, SIG_GAUSSIAN, .1);
+      if (T.fp[0] != 0) {
+        r = standing * tolerance(sens[T.ip[2]], 2, INF, 1, SIG_LINEAR, .5);
+      } else {
+        double sc = 0;
+        for (int i = 0; i < m.nu; i++) sc += tolerance(ctrl[i], 0, 0, 1, SIG_QUADRATIC, 0);
+        r = standing * (sc / m.nu + 4) / 5;
+      }
+      break;
+    }
     default: break;
   }
   if (rew_out) rew_out[env] = r;

@@ -109,6 +109,9 @@ class Task:
         physics.step(50)                    # 200 physics steps, as the reference
       physics.data.time = 0.0
       return
+    elif d == "hopper":           # suite/hopper.py:116-120
+      for e, rng in enumerate(self._rngs):
+        _randomize_limited_and_rotational_joints(m, qpos[e], rng)
     elif d == "walker":           # suite/walker.py:118-129
       for e, rng in enumerate(self._rngs):
         _randomize_limited_and_rotational_joints(m, qpos[e], rng)

@@ -11,7 +11,7 @@ import collections
 import numpy as np
 
 # task kinds of csrc/bp_task.cu
-NONE, CARTPOLE, ACROBOT, PENDULUM, CHEETAH, WALKER, HUMANOID = range(7)
+NONE, CARTPOLE, ACROBOT, PENDULUM, CHEETAH, WALKER, HUMANOID, HOPPER = range(8)
 
 TaskDef = collections.namedtuple(
     "TaskDef", "domain task model kind time_limit control_timestep params obs")
@@ -60,6 +60,18 @@ def _humanoid(speed):
   return f
 
 
+def _hopper(hopping):
+  def f(m):
+    return ([m.name2id("torso", "body"), m.name2id("foot", "body"),
+             _sens_adr(m, "torso_subtreelinvel"), _sens_adr(m, "touch_toe"),
+             _sens_adr(m, "touch_heel")], [1.0 if hopping else 0.0])
+  return f
+
+
+def _obs_hopper(m):
+  return [("position", m.nq - 1), ("velocity", m.nv), ("touch", 2)]
+
+
 def _obs_cartpole(m):
   return [("position", 1 + 2 * (m.nbody - 2)), ("velocity", m.nv)]
 
@@ -88,6 +100,9 @@ _TASKS = [
             lambda m: [("orientations", 2 * (m.nbody - 1)), ("height", 1), ("velocity", m.nv)]),
     TaskDef("walker", "run", "walker", WALKER, 25, .025, _walker(8.0),
             lambda m: [("orientations", 2 * (m.nbody - 1)), ("height", 1), ("velocity", m.nv)]),
+    # hopper.py:32-41: 20 s, control timestep .02, stand height .6, hop speed 2
+    TaskDef("hopper", "stand", "hopper", HOPPER, 20, .02, _hopper(False), _obs_hopper),
+    TaskDef("hopper", "hop", "hopper", HOPPER, 20, .02, _hopper(True), _obs_hopper),
     # humanoid.py:28-35: 25 s, control timestep .025, speeds 0 / 1 / 10
     TaskDef("humanoid", "stand", "humanoid", HUMANOID, 25, .025, _humanoid(0.0), None),
     TaskDef("humanoid", "walk", "humanoid", HUMANOID, 25, .025, _humanoid(1.0), None),
