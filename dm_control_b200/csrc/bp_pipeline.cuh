@@ -254,25 +254,28 @@ BP_STAGE void bp_check_state(const C& c) {
   bp_check(c, DF(qvel), m.nv, W_BADQVEL);
 }
 
+// `skipsensor`: sensors and energy are outputs only; inside a multi-sub-step launch they
+// are evaluated on the last sub-step alone (the values every earlier one would have
+// written are overwritten before anyone can read them).
 template <class C>
-__device__ __forceinline__ void bp_mj_step(const C& c) {
+__device__ __forceinline__ void bp_mj_step(const C& c, bool skipsensor) {
   RUN(bp_check_state(c));
-  bp_forward(c, false);
+  bp_forward(c, skipsensor);
   RUN(bp_check_acc(c));
   if (c.P.m.opt_integrator == 1) bp_rk4(c); else RUN(bp_euler(c));
   BP_LOCK(6);
 }
 
 template <class C>
-__device__ __forceinline__ void bp_step1(const C& c) {
+__device__ __forceinline__ void bp_step1(const C& c, bool skipsensor) {
   RUN(bp_check_state(c));
   bp_fwd_position(c);
-  bp_fwd_velocity(c, false);
+  bp_fwd_velocity(c, skipsensor);
   BP_LOCK(7);
 }
 
 template <class C>
-__device__ __forceinline__ void bp_step2(const C& c) {
+__device__ __forceinline__ void bp_step2(const C& c, bool skipsensor) {
   if (c.act) {
     bp_fwd_actuation(c);
     bp_fwd_acceleration(c);
@@ -281,7 +284,7 @@ __device__ __forceinline__ void bp_step2(const C& c) {
   bp_fwd_constraint(c);
   BP_LOCK(5);
   if (c.act) {
-    bp_sensors(c, STAGE_ACC);
+    if (!skipsensor) bp_sensors(c, STAGE_ACC);
     bp_check_acc(c);
     bp_euler(c);
   }
@@ -295,16 +298,17 @@ __device__ __forceinline__ void bp_run_mode(const C& c) {
     case BP_MODE_STEP:
 #pragma unroll 1
       for (int s = 0; s < P.nsub; s++) {
-        if (P.m.opt_integrator == 0) bp_step2(c); else bp_mj_step(c);
-        bp_step1(c);
+        const bool skip = s + 1 < P.nsub;
+        if (P.m.opt_integrator == 0) bp_step2(c, skip); else bp_mj_step(c, skip);
+        bp_step1(c, skip);
       }
       break;
     case BP_MODE_FORWARD: bp_forward(c, false); break;
-    case BP_MODE_STEP1: bp_step1(c); break;
-    case BP_MODE_STEP2: bp_step2(c); break;
+    case BP_MODE_STEP1: bp_step1(c, false); break;
+    case BP_MODE_STEP2: bp_step2(c, false); break;
     case BP_MODE_MJSTEP:
 #pragma unroll 1
-      for (int s = 0; s < P.nsub; s++) bp_mj_step(c);
+      for (int s = 0; s < P.nsub; s++) bp_mj_step(c, s + 1 < P.nsub);
       break;
   }
 }
@@ -378,7 +382,7 @@ static int bp_launch_gmem(const BpParams* P, cudaStream_t stream) {
   Q.hot_doubles = 0;
   size_t bytes = 0;
   if (S == 1 && getenv("BPHYS_ARENA")) {
-    const int hot = P->m.ntri + 2 * P->m.nv;
+    const int hot = P->m.ntri + 3 * P->m.nv;
     const size_t need = (size_t)(threads / G) * hot * sizeof(double);
     if (need <= 200 * 1024) { Q.hot_doubles = hot; bytes = need; }
   }

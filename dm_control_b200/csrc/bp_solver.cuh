@@ -7,13 +7,17 @@
 #define BP_SOLVER_CUH_
 #include "bp_math.cuh"
 
-// y = Md * x, dense symmetric nv x nv with row stride nvp (odd => conflict free)
-BP_STAGE void bp_mul_md(const C& c, typename C::DP Md, typename C::DP y, typename C::DP x) {
-  const int nv = c.P.m.nv, nvp = c.P.m.nvp;
+// y = M x with M a packed lower triangle (row i at i (i + 1) / 2): row i reads its own
+// packed row up to the diagonal, then walks down column i
+BP_STAGE void bp_mul_md(const C& c, typename C::DP Mp, typename C::DP y, typename C::DP x) {
+  const int nv = c.P.m.nv;
 #pragma unroll 1
   for (int i = c.lane; i < nv; i += C::G) {
     double s = 0;
-    for (int j = 0; j < nv; j++) s += Md[i * nvp + j] * x[j];
+    const int ri = i * (i + 1) / 2;
+    for (int j = 0; j <= i; j++) s += Mp[ri + j] * x[j];
+    int a = ri + 2 * i + 1;                       // (i + 1, i)
+    for (int j = i + 1; j < nv; j++) { s += Mp[a] * x[j]; a += j + 1; }
     y[i] = s;
   }
   SYNC();
@@ -208,9 +212,16 @@ __device__ __forceinline__ void bp_chol_dots(typename C::DP H, const int (&row)[
   }
 }
 
+// The right-hand side of the solve that follows rides along as row n of the packed
+// matrix (H[ntri + k] = g[k]): factoring the bordered matrix leaves y = L^-1 g in that
+// row, which replaces the forward sweep.  bp_chol_fused says whether that applies.
+template <class C>
+__device__ __forceinline__ bool bp_chol_fused(int n) { return n + 1 <= BP_RS * C::G; }
+
 BP_STAGE bool bp_chol_factor(const C& c, typename C::DP H, typename C::DP dinv) {
   const int n = c.P.m.nv;
   if (n > BP_RS * C::G) return bp_chol_factor_generic(c, H, dinv);
+  const int nrows = bp_chol_fused<C>(n) ? n + 1 : n;
   int row[BP_RS];
 #pragma unroll
   for (int s = 0; s < BP_RS; s++) { int i = c.lane + C::G * s; row[s] = i * (i + 1) / 2; }
@@ -222,7 +233,7 @@ BP_STAGE bool bp_chol_factor(const C& c, typename C::DP H, typename C::DP dinv) 
 #pragma unroll
     for (int s = 0; s < BP_RS; s++) {
       int i = c.lane + C::G * s;
-      on[s] = i >= j && i < n;
+      on[s] = i >= j && i < nrows;
       acc[s] = on[s] ? H[row[s] + j] : 0.0;
     }
     const int rj = j * (j + 1) / 2;
@@ -267,20 +278,22 @@ BP_STAGE void bp_chol_solve_generic(const C& c, typename C::DP L, typename C::DP
   }
 }
 
+// x <- H^-1 x.  `fwd_done`: y = L^-1 x already sits in row n of L (see bp_chol_fused)
 BP_STAGE void bp_chol_solve(const C& c, typename C::DP L, typename C::DP dinv,
-                            typename C::DP x) {
+                            typename C::DP x, bool fwd_done) {
   const int n = c.P.m.nv;
   if (n > BP_RS * C::G) { bp_chol_solve_generic(c, L, dinv, x); return; }
   double xs[BP_RS];
+  const int rn = n * (n + 1) / 2;
 #pragma unroll
   for (int s = 0; s < BP_RS; s++) {
     int i = c.lane + C::G * s;
-    xs[s] = i < n ? x[i] : 0.0;
+    xs[s] = i < n ? (fwd_done ? L[rn + i] : x[i]) : 0.0;
   }
   // forward sweep L y = b by columns: pivot k is final on its owner, everyone below it
   // subtracts L[i][k] y_k
 #pragma unroll 1
-  for (int k = 0; k < n; k++) {
+  for (int k = 0; k < (fwd_done ? 0 : n); k++) {
     double yk = group_bcast(c, bp_slot<C>(xs, k / C::G), k % C::G) * dinv[k];
 #pragma unroll
     for (int s = 0; s < BP_RS; s++) {
@@ -320,7 +333,7 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refacto
   const BpModel& m = c.P.m;
   const int nv = m.nv, nvp = m.nvp;
   const int ntri = m.ntri;
-  auto H = HOT(s_H, 0), Hdinv = HOT(s_Hdinv, ntri), Mgrad = HOT(s_Mgrad, ntri + nv);
+  auto H = HOT(s_H, 0), Hdinv = HOT(s_Hdinv, ntri + nv), Mgrad = HOT(s_Mgrad, ntri + 2 * nv);
   auto Md = DF(s_Md), grad = DF(s_grad);
   auto J = DF(efc_J), rw = DF(s_rw), rdof = DF(s_rdof);
   for (int i = c.lane; i < nv; i += C::G) {
@@ -329,10 +342,11 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refacto
   }
   if (!refactor) {            // same active set as last time: H and its factor stand
     SYNC();
-    bp_chol_solve(c, H, Hdinv, Mgrad);
+    bp_chol_solve(c, H, Hdinv, Mgrad, false);
     return;
   }
-  for (int e = c.lane; e < ntri; e += C::G) H[e] = Md[m.tri_i[e] * nvp + m.tri_j[e]];
+  for (int e = c.lane; e < ntri; e += C::G) H[e] = Md[e];
+  for (int i = c.lane; i < nv; i += C::G) H[ntri + i] = grad[i];     // bordered rhs row
   SYNC();
 #pragma unroll 1
   for (int i = c.lane; i < nv; i += C::G) {
@@ -386,11 +400,12 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refacto
   }
   if (!bp_chol_factor(c, H, Hdinv)) {
     SYNC();
-    for (int e = c.lane; e < ntri; e += C::G) H[e] = Md[m.tri_i[e] * nvp + m.tri_j[e]];
+    for (int e = c.lane; e < ntri; e += C::G) H[e] = Md[e];
+    for (int i = c.lane; i < nv; i += C::G) H[ntri + i] = grad[i];
     SYNC();
     bp_chol_factor(c, H, Hdinv);
   }
-  bp_chol_solve(c, H, Hdinv, Mgrad);
+  bp_chol_solve(c, H, Hdinv, Mgrad, bp_chol_fused<C>(nv));
 }
 
 // Solver state that lives across Newton iterations (registers of the calling kernel)
@@ -428,17 +443,15 @@ BP_STAGE void bp_solver_begin(const C& c, BpSolve& st) {
   }
   nsingle = (int)(group_sum(c, (double)nsingle) + 0.5);
   st.nsingle = nsingle;
-  // dense copy of M
+  // dense copy of M as a packed lower triangle
   auto Md = DF(s_Md), qM = DF(qM);
-  for (int w = c.lane; w < nv * nvp; w += C::G) Md[w] = 0;
+  for (int w = c.lane; w < m.ntri; w += C::G) Md[w] = 0;
   SYNC();
 #pragma unroll 1
   for (int i = c.lane; i < nv; i += C::G) {
     int a = m.dof_Madr[i];
-    for (int j = i; j >= 0; j = m.dof_parentid[j], a++) {
-      double v = qM[a];
-      Md[i * nvp + j] = v; Md[j * nvp + i] = v;
-    }
+    const int ri = i * (i + 1) / 2;
+    for (int j = i; j >= 0; j = m.dof_parentid[j], a++) Md[ri + j] = qM[a];
   }
   SYNC();
   auto Ma = DF(s_Ma), jar = DF(s_jar), search = DF(s_search);
@@ -461,7 +474,7 @@ BP_STAGE void bp_solver_begin(const C& c, BpSolve& st) {
   bool changed;
   st.cost = bp_update_constraint(c, jar, nefc, true, &changed) + bp_gauss_cost(c);
   bp_newton_gradient(c, nefc, nsingle, true);
-  for (int i = c.lane; i < nv; i += C::G) search[i] = -HOT(s_Mgrad, m.ntri + nv)[i];
+  for (int i = c.lane; i < nv; i += C::G) search[i] = -HOT(s_Mgrad, m.ntri + 2 * nv)[i];
   SYNC();
   st.done = m.opt_iterations <= 0;
 }
@@ -493,7 +506,7 @@ BP_STAGE void bp_solver_iterate(const C& c, BpSolve& st) {
   st.iter++;
   if (st.improvement < m.opt_tolerance || st.gradient < m.opt_tolerance ||
       st.iter >= m.opt_iterations) { st.done = true; return; }
-  for (int i = c.lane; i < nv; i += C::G) search[i] = -HOT(s_Mgrad, m.ntri + nv)[i];
+  for (int i = c.lane; i < nv; i += C::G) search[i] = -HOT(s_Mgrad, m.ntri + 2 * nv)[i];
   SYNC();
 }
 

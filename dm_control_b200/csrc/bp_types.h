@@ -132,7 +132,7 @@ struct BpModel {
   X(nefc, 1) X(ne, 1) X(nf, 1) X(solver_iter, 1) X(warning, 8)
 #define BP_DATA_SCRATCH(X) \
   X(s_Ma, m.nv) X(s_jar, njmax) X(s_grad, m.nv) X(s_Mgrad, m.nv) \
-  X(s_search, m.nv) X(s_Mv, m.nv) X(s_jv, njmax) X(s_H, m.nv * m.nvp) \
+  X(s_search, m.nv) X(s_Mv, m.nv) X(s_jv, njmax) X(s_H, m.nv * m.nvp + m.nv) \
   X(s_Md, m.nv * m.nvp) X(s_Hdinv, m.nv) X(s_MM, m.nM) X(s_MMdinv, m.nv) \
   X(s_rdof, njmax) X(s_rw, njmax) X(s_tmp, 2 * m.nv + m.na) X(s_cacc, 6 * m.nbody) X(s_cfrc, 6 * m.nbody) X(s_rk, m.nq + m.nv + m.na + 5 * (2 * m.nv + m.na) + 1)
 
@@ -160,7 +160,7 @@ struct BpParams {
   int mode, nsub, disable_actuation;
   int hot_doubles;   // per-env shared-memory arena of the global-memory shapes (0 = none)
 };
-// arena layout: packed Hessian / Cholesky factor (ntri), its inverse pivots (nv), Mgrad (nv)
+// arena layout: packed Hessian / Cholesky factor + rhs row (ntri + nv), inverse pivots (nv), Mgrad (nv)
 
 
 // suite task descriptor: kind + ids / constants resolved by name on the host
