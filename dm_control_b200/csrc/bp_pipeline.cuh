@@ -35,7 +35,7 @@ __device__ __forceinline__ void bp_fwd_position(const C& c) {
   if (c.act) {
     const BpModel& m = c.P.m;
     auto qLD = DF(qLD), qM = DF(qM);
-    for (int i = c.lane; i < m.nM; i += C::G) qLD[i] = qM[i];
+    bp_copy(c, qLD, qM, m.nM);
     SYNC();
     bp_factor_sparse(c, qLD, DF(qLDiagInv));
   }
@@ -140,7 +140,7 @@ BP_STAGE void bp_euler(const C& c) {
   } else {
     // implicit joint damping: (M + dt diag(damping)) a = f_smooth + f_constraint
     auto MM = DF(s_MM), qM = DF(qM);
-    for (int i = c.lane; i < m.nM; i += C::G) MM[i] = qM[i];
+    bp_copy(c, MM, qM, m.nM);
     SYNC();
     for (int i = c.lane; i < m.nv; i += C::G) {
       MM[m.dof_Madr[i]] += m.opt_timestep * m.dof_damping[i];

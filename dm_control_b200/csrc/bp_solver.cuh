@@ -7,6 +7,18 @@
 #define BP_SOLVER_CUH_
 #include "bp_math.cuh"
 
+// dst[0..n) = src[0..n): four loads in flight per lane before the stores (the compiler
+// cannot reorder them itself, the two ranges might alias)
+template <class C>
+__device__ __forceinline__ void bp_copy(const C& c, typename C::DP dst, typename C::DP src, int n) {
+  int e = c.lane;
+  for (; e + 3 * C::G < n; e += 4 * C::G) {
+    double a0 = src[e], a1 = src[e + C::G], a2 = src[e + 2 * C::G], a3 = src[e + 3 * C::G];
+    dst[e] = a0; dst[e + C::G] = a1; dst[e + 2 * C::G] = a2; dst[e + 3 * C::G] = a3;
+  }
+  for (; e < n; e += C::G) dst[e] = src[e];
+}
+
 // y = M x with M a packed lower triangle (row i at i (i + 1) / 2): row i reads its own
 // packed row up to the diagonal, then walks down column i
 BP_STAGE void bp_mul_md(const C& c, typename C::DP Mp, typename C::DP y, typename C::DP x) {
@@ -15,8 +27,10 @@ BP_STAGE void bp_mul_md(const C& c, typename C::DP Mp, typename C::DP y, typenam
   for (int i = c.lane; i < nv; i += C::G) {
     double s = 0;
     const int ri = i * (i + 1) / 2;
+#pragma unroll 4
     for (int j = 0; j <= i; j++) s += Mp[ri + j] * x[j];
     int a = ri + 2 * i + 1;                       // (i + 1, i)
+#pragma unroll 4
     for (int j = i + 1; j < nv; j++) { s += Mp[a] * x[j]; a += j + 1; }
     y[i] = s;
   }
@@ -31,6 +45,7 @@ BP_STAGE void bp_mul_j(const C& c, typename C::DP out, typename C::DP x, typenam
 #pragma unroll 1
   for (int r = c.lane; r < nefc; r += C::G) {
     double s = 0;
+#pragma unroll 4
     for (int i = 0; i < nv; i++) s += J[r * nvp + i] * x[i];
     out[r] = sub.valid() ? s - sub[r] : s;
   }
@@ -78,6 +93,7 @@ BP_STAGE double bp_update_constraint(const C& c, typename C::DP jar, int nefc, b
 #pragma unroll 1
     for (int i = c.lane; i < nv; i += C::G) {
       double s = 0;
+#pragma unroll 4
       for (int r = 0; r < nefc; r++) s += J[r * nvp + i] * force[r];
       qc[i] = s;
     }
@@ -303,7 +319,7 @@ BP_STAGE void bp_chol_solve(const C& c, typename C::DP L, typename C::DP dinv,
     }
   }
   // backward sweep L^T x = y by rows of L
-#pragma unroll 1
+#pragma unroll 2
   for (int k = n - 1; k >= 0; k--) {
     double xk = group_bcast(c, bp_slot<C>(xs, k / C::G), k % C::G) * dinv[k];
     const int rk = PK(k, 0);
@@ -345,7 +361,7 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refacto
     bp_chol_solve(c, H, Hdinv, Mgrad, false);
     return;
   }
-  for (int e = c.lane; e < ntri; e += C::G) H[e] = Md[e];
+  bp_copy(c, H, Md, ntri);
   for (int i = c.lane; i < nv; i += C::G) H[ntri + i] = grad[i];     // bordered rhs row
   SYNC();
 #pragma unroll 1
@@ -400,7 +416,7 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refacto
   }
   if (!bp_chol_factor(c, H, Hdinv)) {
     SYNC();
-    for (int e = c.lane; e < ntri; e += C::G) H[e] = Md[e];
+    bp_copy(c, H, Md, ntri);
     for (int i = c.lane; i < nv; i += C::G) H[ntri + i] = grad[i];
     SYNC();
     bp_chol_factor(c, H, Hdinv);
