@@ -51,7 +51,16 @@ struct Ctx {
 #ifndef BP_LOCKMASK
 #define BP_LOCKMASK 0x1ff
 #endif
+#ifdef BP_TIMELINE   // debug builds: wall time of block 0 between consecutive barriers
+static __device__ unsigned long long bp_timeline[32];   // one copy per translation unit
+static __device__ long long bp_timeline_prev;
+#define BP_LOCK(id) do { if (((BP_LOCKMASK) >> (id) & 1) && c.lock) { __syncthreads(); \
+    if (blockIdx.x == 0 && threadIdx.x == 0) { long long t = clock64(); \
+      bp_timeline[id] += (unsigned long long)(t - bp_timeline_prev); bp_timeline[16 + (id)]++; \
+      bp_timeline_prev = t; } } } while (0)
+#else
 #define BP_LOCK(id) do { if (((BP_LOCKMASK) >> (id) & 1) && c.lock) __syncthreads(); } while (0)
+#endif
 #define RUN(call) do { if (c.act) { call; } } while (0)
 
 template <class A, class B>

@@ -33,11 +33,21 @@ __device__ __forceinline__ void bp_fwd_position(const C& c) {
   }
   BP_LOCK(10);
   if (c.act) {
+    // factor M and, for the implicit-damping Euler step, M + dt diag(damping) together
     const BpModel& m = c.P.m;
-    auto qLD = DF(qLD), qM = DF(qM);
+    auto qLD = DF(qLD), qM = DF(qM), MM = DF(s_MM);
+    // (not in the shared-memory shape: its scratch does not survive the launch)
+    const bool implicit = C::G != 32 && m.any_damping && m.opt_integrator == 0;
     bp_copy(c, qLD, qM, m.nM);
+    if (implicit) bp_copy(c, MM, qM, m.nM);
     SYNC();
-    bp_factor_sparse(c, qLD, DF(qLDiagInv));
+    if (implicit) {
+      for (int i = c.lane; i < m.nv; i += C::G)
+        MM[m.dof_Madr[i]] += m.opt_timestep * m.dof_damping[i];
+      SYNC();
+    }
+    bp_factor_sparse(c, qLD, DF(qLDiagInv), implicit ? MM : c.null(),
+                     implicit ? DF(s_MMdinv) : c.null());
   }
   BP_LOCK(0);
   RUN(bp_collision(c));
@@ -138,17 +148,21 @@ BP_STAGE void bp_euler(const C& c) {
     for (int i = c.lane; i < m.nv; i += C::G) qa[i] = DF(qacc)[i];
     SYNC();
   } else {
-    // implicit joint damping: (M + dt diag(damping)) a = f_smooth + f_constraint
-    auto MM = DF(s_MM), qM = DF(qM);
-    bp_copy(c, MM, qM, m.nM);
-    SYNC();
-    for (int i = c.lane; i < m.nv; i += C::G) {
-      MM[m.dof_Madr[i]] += m.opt_timestep * m.dof_damping[i];
-      qa[i] = DF(qfrc_smooth)[i] + DF(qfrc_constraint)[i];
+    // implicit joint damping: (M + dt diag(damping)) a = f_smooth + f_constraint, with the
+    // factor of that matrix left in s_MM by the position stage (bp_fwd_position)
+    if (C::G == 32) {
+      auto MM = DF(s_MM);
+      bp_copy(c, MM, DF(qM), m.nM);
+      SYNC();
+      for (int i = c.lane; i < m.nv; i += C::G)
+        MM[m.dof_Madr[i]] += m.opt_timestep * m.dof_damping[i];
+      SYNC();
+      bp_factor_sparse(c, MM, DF(s_MMdinv), c.null(), c.null());
     }
+    for (int i = c.lane; i < m.nv; i += C::G)
+      qa[i] = DF(qfrc_smooth)[i] + DF(qfrc_constraint)[i];
     SYNC();
-    bp_factor_sparse(c, MM, DF(s_MMdinv));
-    bp_solve_sparse(c, MM, DF(s_MMdinv), qa);
+    bp_solve_sparse(c, DF(s_MM), DF(s_MMdinv), qa);
   }
   bp_advance(c, DF(act_dot), qa, c.null());
 }

@@ -214,24 +214,43 @@ BP_STAGE void bp_crb(const C& c) {
   SYNC();
 }
 
-// in-place sparse L^T D L of a matrix in qM layout; row k's ancestors on lanes
-BP_STAGE void bp_factor_sparse(const C& c, typename C::DP LD, typename C::DP diaginv) {
+// in-place sparse L^T D L of a matrix in qM layout; row k's ancestors on lanes.  A second
+// matrix with the same layout (M + dt * damping for the implicit Euler step) can ride
+// along: it shares every index load and barrier of the first.
+BP_STAGE void bp_factor_sparse(const C& c, typename C::DP LD, typename C::DP diaginv,
+                               typename C::DP LD2, typename C::DP diaginv2) {
   const BpModel& m = c.P.m;
+  const bool two = LD2.valid();
 #pragma unroll 1
   for (int k = m.nv - 1; k >= 0; k--) {
     int akk = m.dof_Madr[k], na = m.dof_depth[k];
-    double dkk = LD[akk];
+    double dkk = LD[akk], dkk2 = two ? LD2[akk] : 1.0;
 #pragma unroll 1
     for (int a = 1 + c.lane; a <= na; a += C::G) {
       double t = LD[akk + a] / dkk;
       int i = m.M_col[akk + a];
       int aij = m.dof_Madr[i];
+      if (two) {
+        double t2 = LD2[akk + a] / dkk2;
 #pragma unroll 1
-      for (int b = a; b <= na; b++) LD[aij++] -= t * LD[akk + b];
+        for (int b = a; b <= na; b++, aij++) {
+          LD[aij] -= t * LD[akk + b];
+          LD2[aij] -= t2 * LD2[akk + b];
+        }
+      } else {
+#pragma unroll 1
+        for (int b = a; b <= na; b++) LD[aij++] -= t * LD[akk + b];
+      }
     }
     SYNC();
-    for (int a = 1 + c.lane; a <= na; a += C::G) LD[akk + a] = LD[akk + a] / dkk;
-    if (c.lane == 0) diaginv[k] = 1.0 / dkk;
+    for (int a = 1 + c.lane; a <= na; a += C::G) {
+      LD[akk + a] = LD[akk + a] / dkk;
+      if (two) LD2[akk + a] = LD2[akk + a] / dkk2;
+    }
+    if (c.lane == 0) {
+      diaginv[k] = 1.0 / dkk;
+      if (two) diaginv2[k] = 1.0 / dkk2;
+    }
     SYNC();
   }
 }

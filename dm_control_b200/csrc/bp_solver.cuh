@@ -338,7 +338,22 @@ BP_STAGE void bp_chol_solve(const C& c, typename C::DP L, typename C::DP dinv,
   SYNC();
 }
 
-// grad = Ma - qfrc_smooth - qfrc_constraint;  H = M + J^T D_active J;  Mgrad = H^-1 grad
+// grad = Ma - qfrc_smooth - qfrc_constraint; returns |grad|^2
+template <class C>
+__device__ __forceinline__ double bp_newton_grad(const C& c) {
+  auto grad = DF(s_grad);
+  double gn = 0;
+  for (int i = c.lane; i < c.P.m.nv; i += C::G) {
+    double g = DF(s_Ma)[i] - DF(qfrc_smooth)[i] - DF(qfrc_constraint)[i];
+    grad[i] = g;
+    gn += g * g;
+  }
+  gn = group_sum(c, gn);
+  SYNC();
+  return gn;
+}
+
+// H = M + J^T D_active J;  Mgrad = H^-1 grad  (grad from bp_newton_grad)
 //
 // The Hessian is assembled from the structure of J instead of a dense triple loop:
 // friction-loss and limit rows (the first `nsingle` rows) have one non-zero, +-1, and
@@ -352,10 +367,7 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refacto
   auto H = HOT(s_H, 0), Hdinv = HOT(s_Hdinv, ntri + nv), Mgrad = HOT(s_Mgrad, ntri + 2 * nv);
   auto Md = DF(s_Md), grad = DF(s_grad);
   auto J = DF(efc_J), rw = DF(s_rw), rdof = DF(s_rdof);
-  for (int i = c.lane; i < nv; i += C::G) {
-    double g = DF(s_Ma)[i] - DF(qfrc_smooth)[i] - DF(qfrc_constraint)[i];
-    grad[i] = g; Mgrad[i] = g;
-  }
+  for (int i = c.lane; i < nv; i += C::G) Mgrad[i] = grad[i];
   if (!refactor) {            // same active set as last time: H and its factor stand
     SYNC();
     bp_chol_solve(c, H, Hdinv, Mgrad, false);
@@ -428,7 +440,7 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refacto
 struct BpSolve {
   double cost, improvement, gradient;
   int iter, nefc, nsingle;
-  bool done;
+  bool done, stale;      // stale: the factorisation does not match the active set
 };
 
 // everything up to the first search direction; st.done when there is nothing to iterate
@@ -437,6 +449,7 @@ BP_STAGE void bp_solver_begin(const C& c, BpSolve& st) {
   const int nv = m.nv, nvp = m.nvp, nefc = IF(nefc)[0];
   auto qacc = DF(qacc), warm = DF(qacc_warmstart), as = DF(qacc_smooth);
   st.iter = 0; st.improvement = 0; st.gradient = 0; st.nefc = nefc; st.nsingle = 0;
+  st.stale = false;
   st.cost = 0;
   if (nefc == 0) {
     for (int i = c.lane; i < nv; i += C::G) {
@@ -478,17 +491,21 @@ BP_STAGE void bp_solver_begin(const C& c, BpSolve& st) {
     bp_mul_md(c, Md, Ma, qacc);
     bp_mul_j(c, jar, qacc, DF(efc_aref), nefc);
     double cw = bp_update_constraint(c, jar, nefc, false, nullptr) + bp_gauss_cost(c);
-    bp_mul_j(c, jar, as, DF(efc_aref), nefc);
-    double cs = bp_update_constraint(c, jar, nefc, false, nullptr);
+    // residual at qacc_smooth goes to s_jv so that Ma / jar of the warm start survive
+    bp_mul_j(c, DF(s_jv), as, DF(efc_aref), nefc);
+    double cs = bp_update_constraint(c, DF(s_jv), nefc, false, nullptr);
     use_warm = cw < cs;
     SYNC();
   }
-  for (int i = c.lane; i < nv; i += C::G) qacc[i] = use_warm ? warm[i] : as[i];
-  SYNC();
-  bp_mul_md(c, Md, Ma, qacc);
-  bp_mul_j(c, jar, qacc, DF(efc_aref), nefc);
+  if (!use_warm) {
+    for (int i = c.lane; i < nv; i += C::G) qacc[i] = as[i];
+    SYNC();
+    bp_mul_md(c, Md, Ma, qacc);
+    bp_mul_j(c, jar, qacc, DF(efc_aref), nefc);
+  }
   bool changed;
   st.cost = bp_update_constraint(c, jar, nefc, true, &changed) + bp_gauss_cost(c);
+  bp_newton_grad(c);
   bp_newton_gradient(c, nefc, nsingle, true);
   for (int i = c.lane; i < nv; i += C::G) search[i] = -HOT(s_Mgrad, m.ntri + 2 * nv)[i];
   SYNC();
@@ -514,14 +531,15 @@ BP_STAGE void bp_solver_iterate(const C& c, BpSolve& st) {
   double old = st.cost;
   bool changed;
   st.cost = bp_update_constraint(c, jar, nefc, true, &changed) + bp_gauss_cost(c);
-  bp_newton_gradient(c, nefc, st.nsingle, changed);
-  double gn = 0;
-  for (int i = c.lane; i < nv; i += C::G) gn += DF(s_grad)[i] * DF(s_grad)[i];
-  gn = group_sum(c, gn);
+  double gn = bp_newton_grad(c);
   st.improvement = scale * (old - st.cost); st.gradient = scale * sqrt(gn);
   st.iter++;
+  // the search direction (assembly, factorisation, solve) is only needed to go on
   if (st.improvement < m.opt_tolerance || st.gradient < m.opt_tolerance ||
       st.iter >= m.opt_iterations) { st.done = true; return; }
+  st.stale |= changed;
+  bp_newton_gradient(c, nefc, st.nsingle, st.stale);
+  st.stale = false;
   for (int i = c.lane; i < nv; i += C::G) search[i] = -HOT(s_Mgrad, m.ntri + 2 * nv)[i];
   SYNC();
 }
@@ -546,8 +564,12 @@ __device__ __forceinline__ void bp_fwd_constraint(const C& c) {
   st.done = true; st.nefc = 0;
   RUN(bp_solver_begin(c, st));
   if (c.lock && (BP_LOCKMASK >> 8 & 1)) {
-    while (__syncthreads_or(!st.done))
+    while (__syncthreads_or(!st.done)) {
+#ifdef BP_TIMELINE
+      if (blockIdx.x == 0 && threadIdx.x == 0) bp_timeline[16 + 8]++;
+#endif
       if (!st.done) bp_solver_iterate(c, st);
+    }
   } else {
 #pragma unroll 1
     while (!st.done) bp_solver_iterate(c, st);
