@@ -143,10 +143,8 @@ def run_gpu(name, nenv, steps, warmup, rank, world, device):
   rew = torch.empty((nenv,), device="cuda:%d" % device, dtype=torch.float64)
   torch.cuda.synchronize(device)
 
-  def env_step(k):
-    batch.copy_from_device("ctrl", ctrl[k].data_ptr())
-    batch.step(nsub)
-    batch.obs_reward(obs.data_ptr(), rew.data_ptr())
+  def env_step(k):          # ONE launch: ctrl scatter + nsub physics steps + obs / reward
+    batch.env_step(nsub, ctrl[k].data_ptr(), obs.data_ptr(), rew.data_ptr())
 
   # settle: the task's own warm-up of the physics (e.g. cheetah.py:73-75), untimed
   settle = WORKLOADS[name]["settle"]
@@ -170,11 +168,9 @@ def run_gpu(name, nenv, steps, warmup, rank, world, device):
   barrier()
   ev[0].record(stream)
   for k in range(steps):
-    batch.copy_from_device("ctrl", ctrl[warmup + k].data_ptr())
     kev[k][0].record(stream)
-    batch.step(nsub)
+    batch.env_step(nsub, ctrl[warmup + k].data_ptr(), obs.data_ptr(), rew.data_ptr())
     kev[k][1].record(stream)
-    batch.obs_reward(obs.data_ptr(), rew.data_ptr())
   ev[1].record(stream)
   batch.sync()
   barrier()
@@ -361,8 +357,8 @@ def main():
       "e2e": {"value": e2e, "unit": "env-steps/s",
               "h2d_bytes_per_step": nenv * r["nu"] * 8,
               "d2h_bytes_per_step": nenv * (r["nobs"] + 1) * 8},
-      # per env-step: ctrl scatter (bp_field_copy_kernel), bp_step_kernel, bp_task_kernel
-      "gpu_launches": 3 * args.steps * world,
+      # per env-step: ONE bp_step_kernel launch (ctrl scatter and obs / reward are fused in)
+      "gpu_launches": args.steps * world,
       "clocks": r["clocks"],
       "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                    "frac": achieved / hbm_peak, "traffic": traffic,

@@ -64,6 +64,7 @@ _SIGNATURES = {
     "bp_task_nobs": (_i32, [_vp]),
     "bp_obs_reward": (_i32, [_vp, _vp, _vp]),
     "bp_obs_reward_host": (_i32, [_vp, _vp, _vp]),
+    "bp_env_step": (_i32, [_vp, _i32, _vp, _vp, _vp]),
     "bp_env_step_host": (_i32, [_vp, _i32, _vp, _vp, _vp]),
     "bp_rewards_tolerance": (_i32, [_i32, _vp, _vp, _i64, ctypes.c_double, ctypes.c_double,
                                     ctypes.c_double, _i32, ctypes.c_double]),
@@ -267,6 +268,10 @@ class Batch:
 
   def obs_reward_host(self, obs, reward):
     check(load().bp_obs_reward_host(self.ptr, _ptr(obs), _ptr(reward)))
+
+  def env_step(self, nsub, ctrl_ptr, obs_ptr, reward_ptr):
+    """Fused Environment.step on device buffers (one launch); pointers are ints."""
+    check(load().bp_env_step(self.ptr, nsub, ctrl_ptr, obs_ptr, reward_ptr))
 
   def env_step_host(self, nsub, ctrl, obs, reward):
     check(load().bp_env_step_host(self.ptr, nsub, _ptr(ctrl), _ptr(obs), _ptr(reward)))

@@ -503,10 +503,18 @@ static BpParams make_params(bp_batch* b, int mode, int nsub, int disable_actuati
   return P;
 }
 
-static int launch(bp_batch* b, int mode, int nsub, int disable_actuation) {
+static int launch(bp_batch* b, int mode, int nsub, int disable_actuation,
+                  const double* ctrl_in = nullptr, double* obs_out = nullptr,
+                  double* rew_out = nullptr) {
   if (!b) return fail(BP_EINVAL, "null batch");
   cudaSetDevice(b->model->device);
   BpParams P = make_params(b, mode, nsub, disable_actuation);
+  P.ctrl_in = ctrl_in; P.obs_out = obs_out; P.rew_out = rew_out;
+  if (rew_out) {
+    P.task = b->task;
+    P.task_nobs = bp_task_nobs_impl(&b->model->M, b->task.kind);
+    if (P.task_nobs < 0) return fail(BP_EINVAL, "unknown task kind");
+  }
   int e;
   switch (b->lanes) {
     case 1: e = bp_launch_step_g1(&P, b->stream); break;
@@ -524,6 +532,13 @@ extern "C" int bp_mj_step(bp_batch* b, int nsub) { return launch(b, BP_MODE_MJST
 extern "C" int bp_forward(bp_batch* b, int da) { return launch(b, BP_MODE_FORWARD, 1, da); }
 extern "C" int bp_step1(bp_batch* b) { return launch(b, BP_MODE_STEP1, 1, 0); }
 extern "C" int bp_step2(bp_batch* b) { return launch(b, BP_MODE_STEP2, 1, 0); }
+
+extern "C" int bp_env_step(bp_batch* b, int nsub, const double* ctrl_dev, double* obs_dev,
+                           double* reward_dev) {
+  if (!b || !reward_dev) return fail(BP_EINVAL, "null argument");
+  return launch(b, BP_MODE_STEP, nsub, 0, b->model->M.nu > 0 ? ctrl_dev : nullptr, obs_dev,
+                reward_dev);
+}
 
 extern "C" int bp_reset(bp_batch* b, int key) {
   if (!b) return fail(BP_EINVAL, "null batch");
@@ -617,16 +632,10 @@ extern "C" int bp_env_step_host(bp_batch* b, int nsub, const double* ctrl_host,
   int nu = m->M.nu;
   int eb = ensure_task_buffers(b, nobs);
   if (eb != BP_OK) return eb;
-  const FieldInfo* f = find_field(b, "ctrl");
-  if (nu > 0) {
+  if (nu > 0)
     CUDA_OK(cudaMemcpyAsync(b->ctrl_stage, ctrl_host, (size_t)b->nenv * nu * 8,
                             cudaMemcpyHostToDevice, b->stream));
-    int ec = field_copy_dev(b, f, b->ctrl_stage, 0, b->nenv, true);
-    if (ec != BP_OK) return ec;
-  }
-  int e = launch(b, BP_MODE_STEP, nsub, 0);
-  if (e != BP_OK) return e;
-  e = bp_obs_reward(b, nobs > 0 ? b->obs_dev : nullptr, b->rew_dev);
+  int e = bp_env_step(b, nsub, b->ctrl_stage, nobs > 0 ? b->obs_dev : nullptr, b->rew_dev);
   if (e != BP_OK) return e;
   if (obs_host && nobs > 0)
     CUDA_OK(cudaMemcpyAsync(obs_host, b->obs_dev, (size_t)b->nenv * nobs * 8,

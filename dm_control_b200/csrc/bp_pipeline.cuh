@@ -17,6 +17,7 @@
 #include "bp_constraint.cuh"
 #include "bp_sensor.cuh"
 #include "bp_solver.cuh"
+#include "bp_task.cuh"
 
 // The composite functions below run for EVERY thread of a block, also for groups
 // without an environment (c.act false), which only take part in the BP_LOCK barriers.
@@ -305,6 +306,16 @@ __device__ __forceinline__ void bp_step2(const C& c, bool skipsensor) {
   BP_LOCK(6);
 }
 
+// prologue of the fused Environment.step: this env's row of the dense control array
+template <class C>
+__device__ __forceinline__ void bp_load_ctrl(const C& c, long long env) {
+  const BpParams& P = c.P;
+  if (!P.ctrl_in || !c.act) return;
+  const double* src = P.ctrl_in + env * P.m.nu;
+  for (int i = c.lane; i < P.m.nu; i += C::G) DF(ctrl)[i] = src[i];
+  SYNC();
+}
+
 template <class C>
 __device__ __forceinline__ void bp_run_mode(const C& c) {
   const BpParams& P = c.P;
@@ -366,7 +377,12 @@ bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
   double* hot = (S == 1 && P.hot_doubles > 0)
       ? bp_arena + (long long)(threadIdx.x / G) * P.hot_doubles : nullptr;
   Ctx<G, S> c{P, base, ib, wl & (G - 1), mask, act, lock, hot};
+  bp_load_ctrl(c, env);
   bp_run_mode(c);
+  if (P.rew_out && act) {           // epilogue: the task's observation and reward
+    if (G > 1) __syncwarp(mask);
+    if (c.lane == 0) bp_task_eval(P, P.task, env, P.task_nobs, P.obs_out, P.rew_out);
+  }
 }
 
 // Block size of a launch: as many warps per block as possible (they share instruction

@@ -12,9 +12,15 @@ bp_step_kernel_smem(const __grid_constant__ BpParams P) {
   for (int w = lane; w < P.L.persist; w += 32) smem[w] = g[w];
   __syncwarp();
   Ctx<32, 1> c{P, smem, (int*)(smem + P.L.ints), lane, 0xffffffffu, true, false, nullptr};
+  bp_load_ctrl(c, env);
   bp_run_mode(c);
   __syncwarp();
   for (int w = lane; w < P.L.persist; w += 32) g[w] = smem[w];
+  if (P.rew_out) {                  // epilogue reads the image just written back
+    __threadfence_block();
+    __syncwarp();
+    if (lane == 0) bp_task_eval(P, P.task, env, P.task_nobs, P.obs_out, P.rew_out);
+  }
 }
 
 extern "C" int bp_launch_step_g32(const BpParams* P, cudaStream_t stream) {

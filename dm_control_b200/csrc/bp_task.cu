@@ -8,46 +8,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 
-#include "bp_types.h"
-
-enum { TASK_NONE = 0, TASK_CARTPOLE = 1, TASK_ACROBOT = 2, TASK_PENDULUM = 3,
-       TASK_CHEETAH = 4, TASK_WALKER = 5, TASK_HUMANOID = 6, TASK_HOPPER = 7,
-       TASK_REACHER = 8 };
-enum { SIG_GAUSSIAN = 0, SIG_LINEAR = 1, SIG_QUADRATIC = 2 };
-
-// read-only strided window of one environment's image (see bp_math.cuh for layouts)
-struct ImgView {
-  const double* p; int S;
-  __device__ __forceinline__ double operator[](int i) const { return p[(long long)i * S]; }
-  __device__ __forceinline__ ImgView at(int off) const { return ImgView{p + (long long)off * S, S}; }
-};
-__device__ __forceinline__ double* bp_env_base(const BpParams& P, long long env) {
-  const int S = P.interleave;
-  return P.image + (env / S) * P.stride * S + (env % S);
-}
-
-__device__ __forceinline__ double sigmoid_(double x, double v1, int kind) {
-  if (kind == SIG_GAUSSIAN) {
-    double scale = sqrt(-2 * log(v1));
-    return exp(-0.5 * (x * scale) * (x * scale));
-  } else if (kind == SIG_LINEAR) {
-    double sx = x * (1 - v1);
-    return fabs(sx) < 1 ? 1 - sx : 0.0;
-  } else {
-    double sx = x * sqrt(1 - v1);
-    return fabs(sx) < 1 ? 1 - sx * sx : 0.0;
-  }
-}
-
-// rewards.tolerance (utils/rewards.py:93-135)
-__device__ __forceinline__ double tolerance(double x, double lower, double upper,
-                                            double margin, int sig, double v1) {
-  bool in = lower <= x && x <= upper;
-  if (in) return 1.0;
-  if (margin == 0) return 0.0;
-  double d = (x < lower ? lower - x : x - upper) / margin;
-  return sigmoid_(d, v1, sig);
-}
+#include "bp_task.cuh"
 
 extern "C" int bp_task_nobs_impl(const BpModel* m, int task) {
   switch (task) {
@@ -69,143 +30,7 @@ __global__ void bp_task_kernel(const __grid_constant__ BpParams P,
                                double* __restrict__ obs_out, double* __restrict__ rew_out) {
   long long env = blockIdx.x * (long long)blockDim.x + threadIdx.x;
   if (env >= P.nenv) return;
-  const BpModel& m = P.m;
-  const BpLayout& L = P.L;
-  const ImgView d{bp_env_base(P, env), P.interleave};
-  const ImgView qpos = d.at(L.qpos), qvel = d.at(L.qvel), xmat = d.at(L.xmat), xpos = d.at(L.xpos);
-  const ImgView ctrl = d.at(L.ctrl), sens = d.at(L.sensordata);
-  double* o = obs_out ? obs_out + env * (long long)nobs : nullptr;
-  double r = 0;
-  int k = 0;
-  const double INF = 1.0 / 0.0;
-  switch (T.kind) {
-    case TASK_CARTPOLE: {   // suite/cartpole.py:131-148,197-221
-      double cart = qpos[T.ip[0]];
-      if (o) {
-        o[k++] = cart;
-        for (int b = 2; b < m.nbody; b++) { o[k++] = xmat[9 * b + 8]; o[k++] = xmat[9 * b + 2]; }
-        for (int i = 0; i < m.nv; i++) o[k++] = qvel[i];
-      }
-      int npole = m.nbody - 2;
-      if (T.ip[1]) {        // sparse
-        double ang = 1;
-        for (int b = 2; b < m.nbody; b++) ang *= tolerance(xmat[9 * b + 8], .995, 1, 0, 0, .1);
-        r = tolerance(cart, -.25, .25, 0, 0, .1) * ang;
-      } else {
-        double up = 0;
-        for (int b = 2; b < m.nbody; b++) up += (xmat[9 * b + 8] + 1) / 2;
-        up /= npole;
-        double centered = (1 + tolerance(cart, 0, 0, 2, SIG_GAUSSIAN, .1)) / 2;
-        double small_control = (4 + tolerance(ctrl[0], 0, 0, 1, SIG_QUADRATIC, 0)) / 5;
-        double sv = 1;
-        for (int i = 1; i < m.nv; i++) sv = fmin(sv, tolerance(qvel[i], 0, 0, 5, SIG_GAUSSIAN, .1));
-        r = up * small_control * ((1 + sv) / 2) * centered;
-      }
-      break;
-    }
-    case TASK_ACROBOT: {    // suite/acrobot.py:59-78,108-119
-      const ImgView sx = d.at(L.site_xpos);
-      int ua = T.ip[0], la = T.ip[1], tgt = T.ip[2], tip = T.ip[3];
-      if (o) {
-        o[k++] = xmat[9 * ua + 2]; o[k++] = xmat[9 * la + 2];
-        o[k++] = xmat[9 * ua + 8]; o[k++] = xmat[9 * la + 8];
-        for (int i = 0; i < m.nv; i++) o[k++] = qvel[i];
-      }
-      double dx = sx[3 * tgt] - sx[3 * tip], dy = sx[3 * tgt + 1] - sx[3 * tip + 1],
-             dz = sx[3 * tgt + 2] - sx[3 * tip + 2];
-      r = tolerance(sqrt(dx * dx + dy * dy + dz * dz), 0, T.fp[0], T.fp[1], SIG_GAUSSIAN, .1);
-      break;
-    }
-    case TASK_PENDULUM: {   // suite/pendulum.py:51-64,104-110
-      int b = T.ip[0];
-      if (o) { o[k++] = xmat[9 * b + 8]; o[k++] = xmat[9 * b + 2]; o[k++] = qvel[T.ip[1]]; }
-      r = tolerance(xmat[9 * b + 8], T.fp[0], 1, 0, 0, .1);
-      break;
-    }
-    case TASK_CHEETAH: {    // suite/cheetah.py:52-57,79-93
-      if (o) {
-        for (int i = 1; i < m.nq; i++) o[k++] = qpos[i];
-        for (int i = 0; i < m.nv; i++) o[k++] = qvel[i];
-      }
-      r = tolerance(sens[T.ip[0]], T.fp[0], INF, T.fp[0], SIG_LINEAR, 0);
-      break;
-    }
-    case TASK_WALKER: {     // suite/walker.py:78-98,131-154
-      int torso = T.ip[0];
-      double height = xpos[3 * torso + 2];
-      if (o) {
-        for (int b = 1; b < m.nbody; b++) { o[k++] = xmat[9 * b]; o[k++] = xmat[9 * b + 2]; }
-        o[k++] = height;
-        for (int i = 0; i < m.nv; i++) o[k++] = qvel[i];
-      }
-      double standing = tolerance(height, 1.2, INF, 0.6, SIG_GAUSSIAN, .1);
-      double upright = (1 + xmat[9 * torso + 8]) / 2;
-      double stand = (3 * standing + upright) / 4;
-      double ms = T.fp[0];
-      if (ms == 0) r = stand;
-      else {
-        double mv = tolerance(sens[T.ip[1]], ms, INF, ms / 2, SIG_LINEAR, .5);
-        r = stand * (5 * mv + 1) / 6;
-      }
-      break;
-    }
-    case TASK_HUMANOID: {   // suite/humanoid.py:93-129,168-207
-      int torso = T.ip[0], head = T.ip[1];
-      const ImgView R = xmat.at(9 * torso);
-      const ImgView vel = sens.at(T.ip[6]);
-      if (o) {
-        for (int i = 7; i < m.nq; i++) o[k++] = qpos[i];
-        o[k++] = xpos[3 * head + 2];
-        for (int e = 0; e < 4; e++) {
-          int b = T.ip[2 + e];
-          double v[3] = {xpos[3 * b] - xpos[3 * torso], xpos[3 * b + 1] - xpos[3 * torso + 1],
-                         xpos[3 * b + 2] - xpos[3 * torso + 2]};
-          for (int cidx = 0; cidx < 3; cidx++)
-            o[k++] = v[0] * R[cidx] + v[1] * R[3 + cidx] + v[2] * R[6 + cidx];
-        }
-        o[k++] = R[6]; o[k++] = R[7]; o[k++] = R[8];
-        for (int i = 0; i < 3; i++) o[k++] = vel[i];
-        for (int i = 0; i < m.nv; i++) o[k++] = qvel[i];
-      }
-      double standing = tolerance(xpos[3 * head + 2], 1.4, INF, 1.4 / 4, SIG_GAUSSIAN, .1);
-      double upright = tolerance(R[8], 0.9, INF, 1.9, SIG_LINEAR, 0);
-      double sc = 0;
-      for (int i = 0; i < m.nu; i++) sc += tolerance(ctrl[i], 0, 0, 1, SIG_QUADRATIC, 0);
-      sc = (4 + sc / m.nu) / 5;
-      double ms = T.fp[0];
-      if (ms == 0) {
-        double dm = (tolerance(vel[0], 0, 0, 2, SIG_GAUSSIAN, .1) +
-                     tolerance(vel[1], 0, 0, 2, SIG_GAUSSIAN, .1)) / 2;
-        r = sc * standing * upright * dm;
-      } else {
-        double cv = sqrt(vel[0] * vel[0] + vel[1] * vel[1]);
-        double mv = (5 * tolerance(cv, ms, INF, ms, SIG_LINEAR, 0) + 1) / 6;
-        r = sc * standing * upright * mv;
-      }
-      break;
-    }
-    case TASK_HOPPER: {     // suite/hopper.py:80-99,122-148
-      // ip: torso body, foot body, speed sensor adr, touch_toe adr, touch_heel adr; fp: hopping
-      const ImgView xipos = d.at(L.xipos);
-      double height = xipos[3 * T.ip[0] + 2] - xipos[3 * T.ip[1] + 2];
-      if (o) {
-        for (int i = 1; i < m.nq; i++) o[k++] = qpos[i];
-        for (int i = 0; i < m.nv; i++) o[k++] = qvel[i];
-        o[k++] = log1p(sens[T.ip[3]]); o[k++] = log1p(sens[T.ip[4]]);
-      }
-      double standing = tolerance(height, 0.6, 2, 0, SIG_GAUSSIAN, .1);
-      if (T.fp[0] != 0) {
-        r = standing * tolerance(sens[T.ip[2]], 2, INF, 1, SIG_LINEAR, .5);
-      } else {
-        double sc = 0;
-        for (int i = 0; i < m.nu; i++) sc += tolerance(ctrl[i], 0, 0, 1, SIG_QUADRATIC, 0);
-        r = standing * (sc / m.nu + 4) / 5;
-      }
-      break;
-    }
-    default: break;
-  }
-  if (rew_out) rew_out[env] = r;
+  bp_task_eval(P, T, env, nobs, obs_out, rew_out);
 }
 
 extern "C" int bp_launch_task(const BpParams* P, const BpTask* T, double* obs, double* reward,

@@ -148,6 +148,13 @@ struct BpLayout {   // offsets in doubles from the start of the env's image
   int njmax, nconmax;
 };
 
+// suite task descriptor: kind + ids / constants resolved by name on the host
+struct BpTask {
+  int kind;
+  int ip[16];
+  double fp[8];
+};
+
 struct BpParams {
   BpModel m;
   BpLayout L;
@@ -159,15 +166,16 @@ struct BpParams {
   int lanes;         // lanes per environment (group size G)
   int mode, nsub, disable_actuation;
   int hot_doubles;   // per-env shared-memory arena of the global-memory shapes (0 = none)
+  // fused Environment.step (bp_env_step): dense [nenv][nu] controls scattered into the
+  // images before the first sub-step, task observation / reward written after the last
+  const double* ctrl_in;   // null: images keep their ctrl
+  double* obs_out;         // null: no observation
+  double* rew_out;         // null: no epilogue at all
+  int task_nobs;
+  BpTask task;
 };
 // arena layout: packed Hessian / Cholesky factor + rhs row (ntri + nv), inverse pivots (nv), Mgrad (nv)
 
 
-// suite task descriptor: kind + ids / constants resolved by name on the host
-struct BpTask {
-  int kind;
-  int ip[16];
-  double fp[8];
-};
 
 #endif  // BP_TYPES_H_

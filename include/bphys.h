@@ -120,6 +120,12 @@ int bp_rewards_tolerance(int device, const double* x_host, double* out_host, int
                          double lower, double upper, double margin, int sigmoid,
                          double value_at_margin);
 
+/* Fused Environment.step on DEVICE buffers, ONE kernel launch: scatter ctrl_dev
+ * [nenv][nu] into the images, nsub physics steps, then the bound task's observation
+ * ([nenv][nobs], may be NULL) and reward ([nenv]).  Asynchronous on the batch's stream. */
+int bp_env_step(bp_batch* b, int nsub, const double* ctrl_dev, double* obs_dev,
+                double* reward_dev);
+
 /* End-to-end Environment.step for HOST buffers (rl/control.py:94-123): copy ctrl
  * [nenv][nu] to the device, nsub physics steps, observation/reward kernel, copy
  * obs/reward back and synchronise.  This is the call the e2e benchmark times. */

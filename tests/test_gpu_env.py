@@ -225,3 +225,42 @@ def test_device_resident_stepping_matches_host_stepping():
                                   ts.observation["position"])
   del stream
   e1.close(); e2.close()
+
+
+def test_fused_env_step_equals_separate_launches():
+  """bp_env_step (ctrl scatter + sub-steps + obs/reward in one launch) is bit-identical
+  to bp_field_copy_device + bp_step + bp_obs_reward, for every execution shape."""
+  import torch
+  from dm_control_b200 import binding
+  from dm_control_b200.suite import tasks as T
+  for domain, task, lanes in (("cheetah", "run", 4), ("cheetah", "run", 1), ("walker", "walk", 32),
+                              ("humanoid", "run", 8)):
+    tdef = T.REGISTRY[(domain, task)]
+    m = PU.load_model(tdef.model)
+    kw = dict(njmax=120, nconmax=40) if domain == "humanoid" else dict(njmax=0, nconmax=0)
+    n = 37
+    qpos, qvel, ctrl = PU.random_states(m, n, 6)
+    outs = []
+    for fused in (False, True):
+      model = binding.Model(m)
+      b = binding.Batch(model, n, kw["njmax"], kw["nconmax"], lanes)
+      ip, fp = tdef.params(m)
+      b.set_task(tdef.kind, ip, fp)
+      b.write("qpos", qpos); b.write("qvel", qvel)
+      b.forward()
+      obs = torch.zeros((n, b.nobs), device="cuda", dtype=torch.float64)
+      rew = torch.zeros((n,), device="cuda", dtype=torch.float64)
+      nsub = T.n_sub_steps(tdef, m)
+      for k in range(3):
+        a = torch.from_numpy(np.roll(ctrl, k, axis=0).copy()).cuda()
+        torch.cuda.synchronize()
+        if fused:
+          b.env_step(nsub, a.data_ptr(), obs.data_ptr(), rew.data_ptr())
+        else:
+          b.copy_from_device("ctrl", a.data_ptr()); b.step(nsub)
+          b.obs_reward(obs.data_ptr(), rew.data_ptr())
+        b.sync()
+      outs.append((obs.cpu().numpy(), rew.cpu().numpy(), b.read("qpos"), b.read("sensordata")))
+      b.free(); model.free()
+    for x, y in zip(*outs):
+      np.testing.assert_array_equal(x, y)
