@@ -416,6 +416,13 @@ static int bp_launch_gmem(const BpParams* P, cudaStream_t stream) {
     const size_t need = (size_t)(threads / G) * hot * sizeof(double);
     if (need <= 200 * 1024) { Q.hot_doubles = hot; bytes = need; }
   }
+  static bool carved = false;
+  if (!carved) {            // no shared memory in the default shape: ask for all of it as L1
+    if (const char* e = getenv("BPHYS_CARVEOUT"))
+      cudaFuncSetAttribute(bp_step_kernel_gmem<G, S>,
+                           cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e));
+    carved = true;
+  }
   static size_t configured = 48 * 1024;
   if (bytes > configured) {
     cudaError_t e = cudaFuncSetAttribute(bp_step_kernel_gmem<G, S>,
