@@ -1,0 +1,155 @@
+"""Callers on the other side of the hot path.
+
+* `ActionScale` — /root/reference/dm_control/suite/wrappers/action_scale.py:29-110 for the
+  batched Environment: actions in [minimum, maximum] are mapped affinely onto the wrapped
+  env's action bounds (the same transform for every env of the batch).
+* `BatchedVecEnv` — the `VecEnv` interface of the fork's `SubprocVecEnv`
+  (/root/reference/dm_control/scripts/vec_env.py:22-194,396-472): `reset`, `step_async`,
+  `step_wait`, `step`, `seed`, `close`, with the worker's auto-reset contract
+  (`vec_env.py:347-352`: when an episode ends the final observation is returned in
+  `info["terminal_observation"]` and the env is reset).  One device batch replaces the
+  pool of worker processes: `num_envs` = the batch's env count, observations are the flat
+  `[num_envs, nobs]` array the device kernel wrote.
+"""
+
+import numpy as np
+
+from dm_control_b200 import specs
+
+_ACTION_SPEC_MUST_BE_BOUNDED_ARRAY = (
+    "`env.action_spec()` must return a single `BoundedArray`, got: {}.")
+_MUST_BE_FINITE = "All values in `{name}` must be finite, got: {bounds}."
+_MUST_BROADCAST = "`{name}` must be broadcastable to shape {shape}, got: {bounds}."
+
+
+class ActionScale:
+  """Wraps a batched control environment to rescale actions to a specific range."""
+
+  def __init__(self, env, minimum, maximum):
+    action_spec = env.action_spec()
+    if not isinstance(action_spec, specs.BoundedArray):
+      raise ValueError(_ACTION_SPEC_MUST_BE_BOUNDED_ARRAY.format(action_spec))
+    minimum = np.array(minimum)
+    maximum = np.array(maximum)
+    shape = action_spec.shape
+    orig_minimum, orig_maximum = action_spec.minimum, action_spec.maximum
+
+    def validate(bounds, name):
+      if not np.all(np.isfinite(bounds)):
+        raise ValueError(_MUST_BE_FINITE.format(name=name, bounds=bounds))
+      try:
+        np.broadcast_to(bounds, shape)
+      except ValueError:
+        raise ValueError(_MUST_BROADCAST.format(name=name, bounds=bounds, shape=shape))
+
+    validate(minimum, "minimum")
+    validate(maximum, "maximum")
+    validate(orig_minimum, "env.action_spec().minimum")
+    validate(orig_maximum, "env.action_spec().maximum")
+    scale = (orig_maximum - orig_minimum) / (maximum - minimum)
+    self._transform = lambda a: (orig_minimum + scale * (np.asarray(a) - minimum)).astype(
+        action_spec.dtype, copy=False)
+    self._action_spec = specs.BoundedArray(
+        shape=shape, dtype=np.result_type(minimum, maximum, action_spec.dtype),
+        minimum=np.broadcast_to(minimum, shape), maximum=np.broadcast_to(maximum, shape),
+        name=action_spec.name)
+    self._env = env
+
+  def step(self, action):
+    return self._env.step(self._transform(action))
+
+  def reset(self):
+    return self._env.reset()
+
+  def observation_spec(self):
+    return self._env.observation_spec()
+
+  def action_spec(self):
+    return self._action_spec
+
+  def __getattr__(self, name):
+    return getattr(self._env, name)
+
+
+def _flat(observation):
+  parts = [np.asarray(v).reshape(len(v), -1) for v in observation.values()]
+  return np.concatenate(parts, axis=1)
+
+
+class BatchedVecEnv:
+  """`VecEnv`-style facade over one batched Environment (all envs share the episode
+  clock, so every env of the batch finishes — and is reset — on the same step)."""
+
+  def __init__(self, env):
+    self._env = env
+    self.num_envs = env.nenv
+    spec = env.action_spec()
+    self.action_space = spec
+    self.observation_space = env.observation_spec()
+    self._pending = None
+    self.closed = False
+
+  def reset(self):
+    return _flat(self._env.reset().observation)
+
+  def step_async(self, actions):
+    if self._pending is not None:
+      raise RuntimeError("step_async called twice without step_wait")
+    actions = np.asarray(actions, dtype=np.float64)
+    if actions.shape != (self.num_envs,) + tuple(self.action_space.shape):
+      raise ValueError("actions have shape {}, expected {}".format(
+          actions.shape, (self.num_envs,) + tuple(self.action_space.shape)))
+    self._pending = actions
+
+  def step_wait(self):
+    if self._pending is None:
+      raise RuntimeError("step_wait called without step_async")
+    actions, self._pending = self._pending, None
+    ts = self._env.step(actions)
+    obs = _flat(ts.observation)
+    n = self.num_envs
+    reward = np.zeros(n) if ts.reward is None else np.asarray(ts.reward, dtype=np.float64)
+    done = np.asarray(ts.step_type) == specs.StepType.LAST
+    infos = [{} for _ in range(n)]
+    if done.any():                       # vec_env.py:347-352
+      for i in np.flatnonzero(done):
+        infos[i]["terminal_observation"] = obs[i].copy()
+      obs = _flat(self._env.reset().observation)
+    return obs, reward, done, infos
+
+  def step(self, actions):
+    self.step_async(actions)
+    return self.step_wait()
+
+  def seed(self, seed=None):
+    """vec_env.py:462-465: env i is seeded seed + i; takes effect at the next reset."""
+    if seed is None:
+      return [None] * self.num_envs
+    seeds = [int(seed) + i for i in range(self.num_envs)]
+    self._env.task._seed = seeds
+    self._env.task._rngs = [np.random.RandomState(s) for s in seeds]
+    return seeds
+
+  def get_attr(self, attr_name, indices=None):
+    value = getattr(self._env, attr_name)
+    return [value for _ in self._indices(indices)]
+
+  def env_method(self, method_name, *args, indices=None, **kwargs):
+    out = getattr(self._env, method_name)(*args, **kwargs)
+    return [out for _ in self._indices(indices)]
+
+  def _indices(self, indices):
+    if indices is None:
+      return range(self.num_envs)
+    if isinstance(indices, int):
+      return [indices]
+    return indices
+
+  def close(self):
+    if not self.closed:
+      self._env.close()
+      self.closed = True
+
+  @property
+  def unwrapped(self):
+    return self
