@@ -40,3 +40,25 @@ def test_oracle_reproduces_committed_trajectories(domain):
         np.testing.assert_allclose(o.qpos, g["qpos"][e, k], rtol=1e-10, atol=1e-12)
         np.testing.assert_array_equal(o.ncon, g["ncon"][e, k])
         np.testing.assert_array_equal(o.nefc, g["nefc"][e, k])
+
+
+def test_c1_trace_fixture_is_what_the_generator_makes():
+  """The committed C1 trace equals a fresh run of its generator for the first 50 steps
+  (oracle + task oracle + the product's own episode initialisation)."""
+  import sys
+  sys.path.insert(0, os.path.join(os.path.dirname(GOLDEN), "..", "tools"))
+  g = np.load(os.path.join(GOLDEN, "c1_cartpole_swingup.npz"))
+  from oracle.oracle_py import Oracle, OracleModel
+  m = PU.load_model("cartpole")
+  o = Oracle(OracleModel(m))
+  o.reset()
+  o.qpos[:] = g["qpos0"]; o.qvel[:] = g["qvel0"]
+  o.forward()
+  fields = ("qpos", "qvel", "ctrl", "xmat", "xpos", "site_xpos", "sensordata")
+  for k in range(50):
+    o.ctrl[:] = g["actions"][k]
+    o.step()
+    d = {f: np.array(getattr(o, f), dtype=np.float64).reshape(1, -1) for f in fields}
+    obs, r = task_oracle.obs_reward("cartpole", "swingup", m, d)
+    np.testing.assert_allclose(obs[0], g["obs"][k], rtol=1e-12, atol=1e-14)
+    np.testing.assert_allclose(r[0], g["reward"][k], rtol=1e-12, atol=1e-14)

@@ -264,3 +264,29 @@ def test_fused_env_step_equals_separate_launches():
       b.free(); model.free()
     for x, y in zip(*outs):
       np.testing.assert_array_equal(x, y)
+
+
+def test_config_c1_cartpole_trace_through_suite_load():
+  """BASELINE.json configs[0] / SURVEY.md 8d C1: cartpole-swingup, task seed 0, 1000 steps of
+  RandomState(0) actions through suite.load -> Environment.step, against the committed
+  CPU-oracle trace (tests/golden/c1_cartpole_swingup.npz, tools/make_golden.py)."""
+  import os
+  from dm_control_b200 import suite
+  g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden",
+                           "c1_cartpole_swingup.npz"))
+  env = suite.load("cartpole", "swingup", task_kwargs={"random": 0}, nenv=1)
+  ts = env.reset()
+  np.testing.assert_array_equal(env.physics.data.qpos[0], g["qpos0"])   # same episode start
+  worst = 0.0
+  for k in range(len(g["actions"])):
+    ts = env.step(g["actions"][k][None, :])
+    obs = np.concatenate([np.asarray(v).reshape(1, -1) for v in ts.observation.values()], axis=1)[0]
+    err = np.max(np.abs(obs - g["obs"][k]) / (1e-6 + np.abs(g["obs"][k])))
+    worst = max(worst, err, abs(ts.reward[0] - g["reward"][k]))
+    if k in (0, 9, 99):
+      assert worst <= 1e-8, (k, worst)            # single / short-horizon bar
+  print("C1 1000-step trace: worst relative obs / abs reward error %.3e" % worst)
+  assert worst < 1e-5                              # long-horizon divergence, reported
+  assert abs(np.sum(g["reward"]) - 27.6088597862409) < 1e-9
+  assert (ts.step_type == 2).all()                 # 1000 steps = the 10 s time limit
+  env.close()

@@ -68,8 +68,47 @@ def traj_fixture(domain, nenv=8, steps=(0, 1, 10, 100)):
   print("traj_%s.npz" % domain, rec["qpos"][0].shape)
 
 
+def c1_trace(steps=1000):
+  """cartpole-swingup, 1 env, task seed 0, actions
+  RandomState(0).uniform(-1, 1, (1000, 1)), through the CPU oracle + task oracle: per-step
+  qpos, qvel, observation and reward.  The episode start uses the same host code as the
+  product (suite.Task.initialize_episode) on a stand-in physics object."""
+  import types
+  import parity_util as PU
+  from oracle import task_oracle
+  from oracle.oracle_py import Oracle, OracleModel
+  from dm_control_b200 import suite
+  from dm_control_b200.suite import tasks as T
+  m = PU.load_model("cartpole")
+  task = suite.Task(T.REGISTRY[("cartpole", "swingup")], random=0)
+  phys = types.SimpleNamespace(
+      model=m, nenv=1, _batch=types.SimpleNamespace(nobs=5, set_task=lambda *a: None),
+      data=types.SimpleNamespace(qpos=np.tile(m.qpos0, (1, 1)), qvel=np.zeros((1, m.nv))))
+  task.bind(phys)
+  task.initialize_episode(phys)
+  o = Oracle(OracleModel(m))
+  o.reset()
+  o.qpos[:] = phys.data.qpos[0]; o.qvel[:] = phys.data.qvel[0]
+  o.forward()
+  actions = np.random.RandomState(0).uniform(-1, 1, size=(steps, 1))
+  fields = ("qpos", "qvel", "ctrl", "xmat", "xpos", "site_xpos", "sensordata")
+  rec = {k: [] for k in ("qpos", "qvel", "obs", "reward")}
+  for k in range(steps):
+    o.ctrl[:] = actions[k]
+    o.step()
+    d = {f: np.array(getattr(o, f), dtype=np.float64).reshape(1, -1) for f in fields}
+    obs, r = task_oracle.obs_reward("cartpole", "swingup", m, d)
+    rec["qpos"].append(np.array(o.qpos)); rec["qvel"].append(np.array(o.qvel))
+    rec["obs"].append(obs[0]); rec["reward"].append(r[0])
+  np.savez_compressed(os.path.join(OUT, "c1_cartpole_swingup.npz"), actions=actions,
+                      qpos0=phys.data.qpos[0], qvel0=phys.data.qvel[0],
+                      **{k: np.stack(v) for k, v in rec.items()})
+  print("c1_cartpole_swingup.npz", np.stack(rec["obs"]).shape, "reward sum", np.sum(rec["reward"]))
+
+
 if __name__ == "__main__":
   os.makedirs(OUT, exist_ok=True)
   rewards_fixture()
   for d in ("pendulum", "cartpole", "acrobot", "cheetah", "walker", "hopper", "humanoid"):
     traj_fixture(d)
+  c1_trace()
