@@ -1,6 +1,7 @@
 """Pins the CPU oracle against every known answer the reference holds for the
 physics path.  Citations are under /root/reference/dm_control/."""
 
+import os
 import numpy as np
 import pytest
 
@@ -282,3 +283,19 @@ def test_mass_matrix_and_bias_consistency():
     return Mx
   Mdot = (Mat(q + eps * v) - Mat(q - eps * v)) / (2 * eps)
   np.testing.assert_allclose(bias, Mdot @ v - dLdq, rtol=1e-6, atol=1e-6)
+
+
+_REF_HUMANOID = "/root/reference/dm_control/mujoco/testing/assets/humanoid.xml"
+
+
+@pytest.mark.skipif(not os.path.exists(_REF_HUMANOID), reason="reference tree not present")
+def test_compiler_object_ids_match_reference_expectations():
+  """core_test.py:226-235 testNamesIds: ids MuJoCo's compiler assigns in the reference's
+  own test humanoid (body / joint ordering of the MJCF compiler)."""
+  from dm_control_b200 import mjcf_compiler as C
+  m = C.compile_xml(open(_REF_HUMANOID).read())
+  assert m.name2id("right_foot", "body") == 6
+  assert m.name2id("left_knee", "joint") == 11
+  assert m.names["body"][6] == "right_foot" and m.names["joint"][11] == "left_knee"
+  with pytest.raises(ValueError, match="exists"):
+    m.name2id("nonexistent_body_name", "body")
