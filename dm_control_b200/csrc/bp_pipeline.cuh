@@ -339,17 +339,17 @@ __device__ __forceinline__ void bp_run_mode(const C& c) {
 }
 
 // ---- G < 32: image in global memory, 32/G environments per warp -----------------
+// Upper bound of threads per block = register budget of a shape: 512 threads -> 128
+// registers, 1024 -> 64.  The wide shapes (G >= 8) take the 64-register build: a one-block-
+// per-SM launch then holds twice the warps (humanoid G = 16: 28 warps per SM, 1.04 M vs
+// 0.96 M env-steps/s for G = 8 at 128 registers; walker G = 8: 2.41 M vs 2.25 M at G = 4).
 #ifndef BP_TPB
-#define BP_TPB 512       // upper bound of threads per block of the global-memory shapes
+#define BP_TPB(G) ((G) >= 8 ? 1024 : 512)
 #endif
 #ifndef BP_LOCKSTEP
 #define BP_LOCKSTEP 1    // 1: warps of a block re-align at stage boundaries (BP_LOCK)
 #endif
-#ifdef BP_MINB
-#define BP_BOUNDS __launch_bounds__(BP_TPB, BP_MINB)
-#else
-#define BP_BOUNDS __launch_bounds__(BP_TPB)
-#endif
+#define BP_BOUNDS __launch_bounds__(BP_TPB(G))
 template <int G, int S>
 __global__ void BP_BOUNDS
 bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
@@ -388,15 +388,15 @@ bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
 // Block size of a launch: as many warps per block as possible (they share instruction
 // cache lines between BP_LOCK barriers: +50..160 % measured, profiles/r1d_*) while the
 // grid still covers the 148 SMs.
-static inline int bp_block_threads(long long threads_total) {
+static inline int bp_block_threads(long long threads_total, int tpb_max) {
   if (const char* e = getenv("BPHYS_BLOCK_THREADS")) {       // tuning knob (multiple of 32)
     int v = atoi(e);
-    if (v >= 32 && v <= BP_TPB && v % 32 == 0) return v;
+    if (v >= 32 && v <= tpb_max && v % 32 == 0) return v;
   }
   const long long warps = (threads_total + 31) / 32;
   const long long per_sm = (warps + 147) / 148;        // 148 SMs
-  if (per_sm * 32 <= BP_TPB) return per_sm < 2 ? 64 : (int)per_sm * 32;   // one block per SM
-  return BP_TPB;
+  if (per_sm * 32 <= tpb_max) return per_sm < 2 ? 64 : (int)per_sm * 32;  // one block per SM
+  return tpb_max > 512 ? 512 : tpb_max;
 }
 
 // Launch of one global-memory shape.  BPHYS_ARENA=1 moves the per-env solver arena
@@ -406,7 +406,7 @@ static inline int bp_block_threads(long long threads_total) {
 template <int G, int S>
 static int bp_launch_gmem(const BpParams* P, cudaStream_t stream) {
   const long long total = P->nenv * G;
-  const int threads = bp_block_threads(total);
+  const int threads = bp_block_threads(total, BP_TPB(G));
   const unsigned blocks = (unsigned)((total + threads - 1) / threads);
   BpParams Q = *P;
   Q.hot_doubles = 0;

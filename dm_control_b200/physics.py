@@ -29,7 +29,9 @@ class PhysicsError(RuntimeError):
 # default execution shape per model size: lanes per environment (DESIGN.md §Shapes;
 # chosen from the sweep in profiles/)
 def default_lanes(m):
-  return 4 if m.nv <= 12 else 8
+  """Execution shape from the lane sweeps (profiles/r1_tuning.md): 8 lanes per env for the
+  planar models, 16 for humanoid-sized ones (both run the 64-register build)."""
+  return 8 if m.nv <= 12 else 16
 
 
 def default_sizes(m):
