@@ -46,7 +46,9 @@ WORKLOADS = {"cheetah-run": dict(nenv=16384, njmax=64, nconmax=16, settle=200, l
              "pendulum-swingup": dict(nenv=4096, njmax=1, nconmax=1, settle=0, lanes=1)}
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the step kernel from the
 # committed `ncu --set full` captures (profiles/), keyed by (task, lanes, envs per GPU)
-NCU_TRAFFIC = {("cheetah-run", 4, 16384): (345.5e6, "profiles/r1g_cheetah_g4.summary.txt"),
+NCU_TRAFFIC = {("cheetah-run", 8, 16384): (518.1e6, "profiles/r1m_cheetah_g8.summary.txt"),
+               ("cheetah-run", 4, 16384): (345.5e6, "profiles/r1g_cheetah_g4.summary.txt"),
+               ("humanoid-run", 16, 8192): (5.775e9, "profiles/r1m_humanoid_g16.summary.txt"),
                ("humanoid-run", 8, 8192): (5.531e9, "profiles/r1g_humanoid_g8.summary.txt")}
 
 
