@@ -169,20 +169,24 @@ BP_STAGE double bp_linesearch(const C& c, double scale, int nefc) {
   return a;
 }
 
-// ---- dense Cholesky H = L L^T in place (lower triangle, row stride nvp) -------------
-// Row i of the system belongs to lane i % G, register slot i / G.  When nv <= 4 G every
-// lane owns at most BP_RS = 4 rows, so a column step keeps its 4 partial dot products in
-// registers (left-looking: one broadcast load of L[j][k] feeds 4 independent FMAs) and
+// ---- dense Cholesky H = L L^T in place (packed lower triangle) ---------------------
+// Row i of the system belongs to lane i % G, register slot i / G.  When the rows fit
+// BP_RS = 4 slots per lane (nv <= 4 G) a column step keeps its partial dot products in
+// registers (left-looking: one broadcast load of L[j][k] feeds NS independent FMAs) and
 // the triangular solves keep the whole right-hand side in registers, exchanging pivots
-// by group shuffles instead of memory + barriers.  Larger systems fall back to the
-// generic right-looking code.
+// by group shuffles instead of memory + barriers.  The code is instantiated for the
+// number of slots NS a model really uses (humanoid on 16 lanes: 2), so dead slots cost no
+// instructions.  Larger systems fall back to the generic right-looking code.
 #define BP_RS 4
 // the Hessian and its factor are stored as a packed lower triangle, row i at i (i + 1) / 2
 #define PK(i, j) ((i) * ((i) + 1) / 2 + (j))
 
-template <class C>
-__device__ __forceinline__ double bp_slot(const double (&v)[BP_RS], int s) {
-  return s == 0 ? v[0] : (s == 1 ? v[1] : (s == 2 ? v[2] : v[3]));
+template <int NS>
+__device__ __forceinline__ double bp_slot(const double (&v)[NS], int s) {
+  double r = v[0];
+#pragma unroll
+  for (int t = 1; t < NS; t++) r = s == t ? v[t] : r;
+  return r;
 }
 
 template <class C>
@@ -213,57 +217,42 @@ BP_STAGE bool bp_chol_factor_generic(const C& c, typename C::DP H, typename C::D
   return true;
 }
 
-// acc[s] -= sum_{k<j} L[i_s][k] L[j][k] for the register slots s >= S0 (slots below hold
-// rows that are already finished)
-template <class C, int S0>
-__device__ __forceinline__ void bp_chol_dots(typename C::DP H, const int (&row)[BP_RS],
-                                             const bool (&on)[BP_RS], double (&acc)[BP_RS],
-                                             int rj, int j) {
-#pragma unroll 4
-  for (int k = 0; k < j; k++) {
-    double ljk = H[rj + k];
-#pragma unroll
-    for (int s = S0; s < BP_RS; s++)
-      if (on[s]) acc[s] -= H[row[s] + k] * ljk;
-  }
-}
-
 // The right-hand side of the solve that follows rides along as row n of the packed
 // matrix (H[ntri + k] = g[k]): factoring the bordered matrix leaves y = L^-1 g in that
 // row, which replaces the forward sweep.  bp_chol_fused says whether that applies.
 template <class C>
 __device__ __forceinline__ bool bp_chol_fused(int n) { return n + 1 <= BP_RS * C::G; }
 
-BP_STAGE bool bp_chol_factor(const C& c, typename C::DP H, typename C::DP dinv) {
-  const int n = c.P.m.nv;
-  if (n > BP_RS * C::G) return bp_chol_factor_generic(c, H, dinv);
-  const int nrows = bp_chol_fused<C>(n) ? n + 1 : n;
-  int row[BP_RS];
+template <class C, int NS>
+__device__ __forceinline__ bool bp_chol_factor_t(const C& c, typename C::DP H,
+                                                 typename C::DP dinv, int n, int nrows) {
+  int row[NS];
 #pragma unroll
-  for (int s = 0; s < BP_RS; s++) { int i = c.lane + C::G * s; row[s] = i * (i + 1) / 2; }
+  for (int s = 0; s < NS; s++) { int i = c.lane + C::G * s; row[s] = i * (i + 1) / 2; }
 #pragma unroll 1
   for (int j = 0; j < n; j++) {
     // acc[s] = H[i][j] - sum_{k<j} L[i][k] L[j][k] for this lane's rows i >= j
-    double acc[BP_RS];
-    bool on[BP_RS];
+    double acc[NS];
+    bool on[NS];
 #pragma unroll
-    for (int s = 0; s < BP_RS; s++) {
+    for (int s = 0; s < NS; s++) {
       int i = c.lane + C::G * s;
       on[s] = i >= j && i < nrows;
       acc[s] = on[s] ? H[row[s] + j] : 0.0;
     }
     const int rj = j * (j + 1) / 2;
-    switch (j / C::G) {
-      case 0: bp_chol_dots<C, 0>(H, row, on, acc, rj, j); break;
-      case 1: bp_chol_dots<C, 1>(H, row, on, acc, rj, j); break;
-      case 2: bp_chol_dots<C, 2>(H, row, on, acc, rj, j); break;
-      default: bp_chol_dots<C, 3>(H, row, on, acc, rj, j); break;
+#pragma unroll 4
+    for (int k = 0; k < j; k++) {
+      double ljk = H[rj + k];
+#pragma unroll
+      for (int s = 0; s < NS; s++)
+        if (on[s]) acc[s] -= H[row[s] + k] * ljk;
     }
-    double piv = group_bcast(c, bp_slot<C>(acc, j / C::G), j % C::G);
+    double piv = group_bcast(c, bp_slot<NS>(acc, j / C::G), j % C::G);
     if (piv < BP_MINVAL) return false;     // uniform across the group
     double d = sqrt(piv), inv = 1.0 / d;
 #pragma unroll
-    for (int s = 0; s < BP_RS; s++) {
+    for (int s = 0; s < NS; s++) {
       int i = c.lane + C::G * s;
       if (on[s]) H[row[s] + j] = i == j ? d : acc[s] * inv;
     }
@@ -271,6 +260,18 @@ BP_STAGE bool bp_chol_factor(const C& c, typename C::DP H, typename C::DP dinv) 
     SYNC();                                 // column j (and row j+1 up to it) visible
   }
   return true;
+}
+
+BP_STAGE bool bp_chol_factor(const C& c, typename C::DP H, typename C::DP dinv) {
+  const int n = c.P.m.nv;
+  if (n > BP_RS * C::G) return bp_chol_factor_generic(c, H, dinv);
+  const int nrows = bp_chol_fused<C>(n) ? n + 1 : n;
+  switch ((nrows + C::G - 1) / C::G) {
+    case 1: return bp_chol_factor_t<C, 1>(c, H, dinv, n, nrows);
+    case 2: return bp_chol_factor_t<C, 2>(c, H, dinv, n, nrows);
+    case 3: return bp_chol_factor_t<C, 3>(c, H, dinv, n, nrows);
+    default: return bp_chol_factor_t<C, 4>(c, H, dinv, n, nrows);
+  }
 }
 
 BP_STAGE void bp_chol_solve_generic(const C& c, typename C::DP L, typename C::DP dinv,
@@ -294,15 +295,13 @@ BP_STAGE void bp_chol_solve_generic(const C& c, typename C::DP L, typename C::DP
   }
 }
 
-// x <- H^-1 x.  `fwd_done`: y = L^-1 x already sits in row n of L (see bp_chol_fused)
-BP_STAGE void bp_chol_solve(const C& c, typename C::DP L, typename C::DP dinv,
-                            typename C::DP x, bool fwd_done) {
-  const int n = c.P.m.nv;
-  if (n > BP_RS * C::G) { bp_chol_solve_generic(c, L, dinv, x); return; }
-  double xs[BP_RS];
+template <class C, int NS>
+__device__ __forceinline__ void bp_chol_solve_t(const C& c, typename C::DP L, typename C::DP dinv,
+                                                typename C::DP x, bool fwd_done, int n) {
+  double xs[NS];
   const int rn = n * (n + 1) / 2;
 #pragma unroll
-  for (int s = 0; s < BP_RS; s++) {
+  for (int s = 0; s < NS; s++) {
     int i = c.lane + C::G * s;
     xs[s] = i < n ? (fwd_done ? L[rn + i] : x[i]) : 0.0;
   }
@@ -310,9 +309,9 @@ BP_STAGE void bp_chol_solve(const C& c, typename C::DP L, typename C::DP dinv,
   // subtracts L[i][k] y_k
 #pragma unroll 1
   for (int k = 0; k < (fwd_done ? 0 : n); k++) {
-    double yk = group_bcast(c, bp_slot<C>(xs, k / C::G), k % C::G) * dinv[k];
+    double yk = group_bcast(c, bp_slot<NS>(xs, k / C::G), k % C::G) * dinv[k];
 #pragma unroll
-    for (int s = 0; s < BP_RS; s++) {
+    for (int s = 0; s < NS; s++) {
       int i = c.lane + C::G * s;
       if (i == k) xs[s] = yk;
       else if (i > k && i < n) xs[s] -= L[PK(i, k)] * yk;
@@ -321,21 +320,34 @@ BP_STAGE void bp_chol_solve(const C& c, typename C::DP L, typename C::DP dinv,
   // backward sweep L^T x = y by rows of L
 #pragma unroll 2
   for (int k = n - 1; k >= 0; k--) {
-    double xk = group_bcast(c, bp_slot<C>(xs, k / C::G), k % C::G) * dinv[k];
+    double xk = group_bcast(c, bp_slot<NS>(xs, k / C::G), k % C::G) * dinv[k];
     const int rk = PK(k, 0);
 #pragma unroll
-    for (int s = 0; s < BP_RS; s++) {
+    for (int s = 0; s < NS; s++) {
       int i = c.lane + C::G * s;
       if (i == k) xs[s] = xk;
       else if (i < k) xs[s] -= L[rk + i] * xk;
     }
   }
 #pragma unroll
-  for (int s = 0; s < BP_RS; s++) {
+  for (int s = 0; s < NS; s++) {
     int i = c.lane + C::G * s;
     if (i < n) x[i] = xs[s];
   }
   SYNC();
+}
+
+// x <- H^-1 x.  `fwd_done`: y = L^-1 x already sits in row n of L (see bp_chol_fused)
+BP_STAGE void bp_chol_solve(const C& c, typename C::DP L, typename C::DP dinv,
+                            typename C::DP x, bool fwd_done) {
+  const int n = c.P.m.nv;
+  if (n > BP_RS * C::G) { bp_chol_solve_generic(c, L, dinv, x); return; }
+  switch ((n + C::G - 1) / C::G) {
+    case 1: bp_chol_solve_t<C, 1>(c, L, dinv, x, fwd_done, n); break;
+    case 2: bp_chol_solve_t<C, 2>(c, L, dinv, x, fwd_done, n); break;
+    case 3: bp_chol_solve_t<C, 3>(c, L, dinv, x, fwd_done, n); break;
+    default: bp_chol_solve_t<C, 4>(c, L, dinv, x, fwd_done, n); break;
+  }
 }
 
 // grad = Ma - qfrc_smooth - qfrc_constraint; returns |grad|^2
