@@ -414,26 +414,35 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refacto
     for (int q0 = 0; q0 < n; q0 += 4) {                   // rows in chunks of 4
       const int nq = n - q0 < 4 ? n - q0 : 4;
       const int r0 = (a + q0) * nvp;
+      // the k (k + 1) / 2 pairs (i >= j) of the dof set are tiled over a GA x GB grid of
+      // lanes: lane (la, lb) takes the outer dofs la, la + GA, ... and, for each, the inner
+      // dofs lb, lb + GB, ... up to the outer one
+      constexpr int GB = C::G >= 16 ? 4 : (C::G >= 4 ? 2 : 1), GA = C::G / GB;
+      const int la = c.lane / GB, lb = c.lane % GB;
       unsigned long long remi = mk;
-      for (int t = 0; t < c.lane; t++) remi &= remi - 1;
+      for (int t = 0; t < la; t++) remi &= remi - 1;
+      unsigned long long remj0 = mk;
+      for (int t = 0; t < lb; t++) remj0 &= remj0 - 1;
 #pragma unroll 1
-      for (int ap = c.lane; ap < k; ap += C::G) {
+      for (int ap = la; ap < k; ap += GA) {
         const int i = __ffsll((long long)remi) - 1;
         double ji[4];
 #pragma unroll
         for (int q = 0; q < 4; q++) ji[q] = q < nq ? rw[a + q0 + q] * J[r0 + q * nvp + i] : 0.0;
-        unsigned long long remj = mk;
+        unsigned long long remj = remj0;
 #pragma unroll 1
-        for (int bp = 0; bp <= ap; bp++) {
+        for (int bp = lb; bp <= ap; bp += GB) {
           const int j = __ffsll((long long)remj) - 1;
-          remj &= remj - 1;
+#pragma unroll
+          for (int t = 0; t < GB; t++) remj &= remj - 1;
           double sum = 0;
 #pragma unroll
           for (int q = 0; q < 4; q++)
             if (q < nq) sum += ji[q] * J[r0 + q * nvp + j];
           H[PK(i, j)] += sum;
         }
-        for (int t = 0; t < C::G; t++) remi &= remi - 1;
+#pragma unroll
+        for (int t = 0; t < GA; t++) remi &= remi - 1;
       }
       SYNC();
     }
