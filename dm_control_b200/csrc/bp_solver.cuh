@@ -533,8 +533,10 @@ BP_STAGE void bp_solver_begin(const C& c, BpSolve& st) {
   st.done = m.opt_iterations <= 0;
 }
 
-// one Newton iteration: line search along s_search, new gradient and search direction
-BP_STAGE void bp_solver_iterate(const C& c, BpSolve& st) {
+// One Newton iteration in two halves (the block re-aligns between them):
+//   step:      line search along s_search, state update, cost, gradient, convergence test
+//   direction: new search direction -- only for environments that go on
+BP_STAGE void bp_solver_step(const C& c, BpSolve& st) {
   const BpModel& m = c.P.m;
   const int nv = m.nv, nefc = st.nefc;
   auto qacc = DF(qacc), Ma = DF(s_Ma), jar = DF(s_jar), search = DF(s_search);
@@ -555,14 +557,25 @@ BP_STAGE void bp_solver_iterate(const C& c, BpSolve& st) {
   double gn = bp_newton_grad(c);
   st.improvement = scale * (old - st.cost); st.gradient = scale * sqrt(gn);
   st.iter++;
+  st.stale |= changed;
   // the search direction (assembly, factorisation, solve) is only needed to go on
   if (st.improvement < m.opt_tolerance || st.gradient < m.opt_tolerance ||
-      st.iter >= m.opt_iterations) { st.done = true; return; }
-  st.stale |= changed;
-  bp_newton_gradient(c, nefc, st.nsingle, st.stale);
+      st.iter >= m.opt_iterations) st.done = true;
+}
+
+BP_STAGE void bp_solver_direction(const C& c, BpSolve& st) {
+  const BpModel& m = c.P.m;
+  bp_newton_gradient(c, st.nefc, st.nsingle, st.stale);
   st.stale = false;
-  for (int i = c.lane; i < nv; i += C::G) search[i] = -HOT(s_Mgrad, m.ntri + 2 * nv)[i];
+  auto search = DF(s_search);
+  for (int i = c.lane; i < m.nv; i += C::G) search[i] = -HOT(s_Mgrad, m.ntri + 2 * m.nv)[i];
   SYNC();
+}
+
+template <class C>
+__device__ __forceinline__ void bp_solver_iterate(const C& c, BpSolve& st) {
+  bp_solver_step(c, st);
+  if (!st.done) bp_solver_direction(c, st);
 }
 
 BP_STAGE void bp_solver_end(const C& c, const BpSolve& st) {
