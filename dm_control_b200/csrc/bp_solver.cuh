@@ -223,6 +223,8 @@ BP_STAGE bool bp_chol_factor_generic(const C& c, typename C::DP H, typename C::D
 template <class C>
 __device__ __forceinline__ bool bp_chol_fused(int n) { return n + 1 <= BP_RS * C::G; }
 
+// Two columns per step: the dot products of columns j and j + 1 share the loads of the
+// lane's rows, and the pair costs one barrier.
 template <class C, int NS>
 __device__ __forceinline__ bool bp_chol_factor_t(const C& c, typename C::DP H,
                                                  typename C::DP dinv, int n, int nrows) {
@@ -230,34 +232,59 @@ __device__ __forceinline__ bool bp_chol_factor_t(const C& c, typename C::DP H,
 #pragma unroll
   for (int s = 0; s < NS; s++) { int i = c.lane + C::G * s; row[s] = i * (i + 1) / 2; }
 #pragma unroll 1
-  for (int j = 0; j < n; j++) {
-    // acc[s] = H[i][j] - sum_{k<j} L[i][k] L[j][k] for this lane's rows i >= j
-    double acc[NS];
-    bool on[NS];
+  for (int j = 0; j < n; j += 2) {
+    const bool pair = j + 1 < n;
+    // acc0[s] = H[i][j] - sum_{k<j} L[i][k] L[j][k], acc1 the same for column j + 1
+    double acc0[NS], acc1[NS];
+    bool on0[NS], on1[NS];
 #pragma unroll
     for (int s = 0; s < NS; s++) {
       int i = c.lane + C::G * s;
-      on[s] = i >= j && i < nrows;
-      acc[s] = on[s] ? H[row[s] + j] : 0.0;
+      on0[s] = i >= j && i < nrows;
+      on1[s] = pair && i > j && i < nrows;
+      acc0[s] = on0[s] ? H[row[s] + j] : 0.0;
+      acc1[s] = on1[s] ? H[row[s] + j + 1] : 0.0;
     }
-    const int rj = j * (j + 1) / 2;
-#pragma unroll 4
+    const int rj = j * (j + 1) / 2, rj1 = rj + j + 1;
+#pragma unroll 2
     for (int k = 0; k < j; k++) {
-      double ljk = H[rj + k];
+      double l0 = H[rj + k], l1 = pair ? H[rj1 + k] : 0.0;
 #pragma unroll
       for (int s = 0; s < NS; s++)
-        if (on[s]) acc[s] -= H[row[s] + k] * ljk;
+        if (on0[s]) {
+          double v = H[row[s] + k];
+          acc0[s] -= v * l0;
+          acc1[s] -= v * l1;
+        }
     }
-    double piv = group_bcast(c, bp_slot<NS>(acc, j / C::G), j % C::G);
-    if (piv < BP_MINVAL) return false;     // uniform across the group
-    double d = sqrt(piv), inv = 1.0 / d;
+    double piv0 = group_bcast(c, bp_slot<NS>(acc0, j / C::G), j % C::G);
+    if (piv0 < BP_MINVAL) return false;    // uniform across the group
+    double d0 = sqrt(piv0), inv0 = 1.0 / d0;
+    double lcol[NS];                       // column j of L on this lane's rows
 #pragma unroll
     for (int s = 0; s < NS; s++) {
       int i = c.lane + C::G * s;
-      if (on[s]) H[row[s] + j] = i == j ? d : acc[s] * inv;
+      lcol[s] = i == j ? d0 : acc0[s] * inv0;
+      if (on0[s]) H[row[s] + j] = lcol[s];
     }
-    if (c.lane == 0) dinv[j] = inv;
-    SYNC();                                 // column j (and row j+1 up to it) visible
+    if (c.lane == 0) dinv[j] = inv0;
+    if (pair) {
+      const int j1 = j + 1;
+      double l10 = group_bcast(c, bp_slot<NS>(lcol, j1 / C::G), j1 % C::G);   // L[j+1][j]
+#pragma unroll
+      for (int s = 0; s < NS; s++)
+        if (on1[s]) acc1[s] -= lcol[s] * l10;
+      double piv1 = group_bcast(c, bp_slot<NS>(acc1, j1 / C::G), j1 % C::G);
+      if (piv1 < BP_MINVAL) return false;
+      double d1 = sqrt(piv1), inv1 = 1.0 / d1;
+#pragma unroll
+      for (int s = 0; s < NS; s++) {
+        int i = c.lane + C::G * s;
+        if (on1[s]) H[row[s] + j1] = i == j1 ? d1 : acc1[s] * inv1;
+      }
+      if (c.lane == 0) dinv[j1] = inv1;
+    }
+    SYNC();                                 // columns j, j + 1 visible
   }
   return true;
 }
