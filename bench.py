@@ -36,14 +36,16 @@ MODELS = os.path.join(ROOT, "dm_control_b200", "suite", "models")
 # estimate v0 of fp64 flops per physics sub-step.
 ALGO = {"cheetah": dict(bytes=648, flops=2.0e4), "humanoid": dict(bytes=2048, flops=2.3e5),
         "walker": dict(bytes=704, flops=1.8e4), "cartpole": dict(bytes=176, flops=1.0e4),
-        "acrobot": dict(bytes=184, flops=1.0e4), "pendulum": dict(bytes=112, flops=1.5e3)}
+        "acrobot": dict(bytes=184, flops=1.0e4), "pendulum": dict(bytes=112, flops=1.5e3),
+        "finger": dict(bytes=264, flops=1.0e4)}
 # `lanes`: execution shape picked from the lane sweep (profiles/r1b_sweep_lanes.jsonl)
 WORKLOADS = {"cheetah-run": dict(nenv=16384, njmax=64, nconmax=16, settle=200, lanes=8),
              "humanoid-run": dict(nenv=8192, njmax=120, nconmax=40, settle=100, lanes=16),
              "walker-walk": dict(nenv=16384, njmax=48, nconmax=12, settle=50, lanes=8),
              "cartpole-swingup": dict(nenv=4096, njmax=4, nconmax=1, settle=0, lanes=8),
              "acrobot-swingup": dict(nenv=4096, njmax=1, nconmax=1, settle=0, lanes=8),
-             "pendulum-swingup": dict(nenv=4096, njmax=1, nconmax=1, settle=0, lanes=1)}
+             "pendulum-swingup": dict(nenv=4096, njmax=1, nconmax=1, settle=0, lanes=1),
+             "finger-spin": dict(nenv=8192, njmax=24, nconmax=6, settle=50, lanes=4)}
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the step kernel from the
 # committed `ncu --set full` captures (profiles/), keyed by (task, lanes, envs per GPU)
 NCU_TRAFFIC = {("cheetah-run", 8, 16384): (518.1e6, "profiles/r1m_cheetah_g8.summary.txt"),

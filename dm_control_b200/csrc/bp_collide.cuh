@@ -39,6 +39,134 @@ __device__ __forceinline__ int col_sphere_sphere(const double* c1, double r1,
   return 1;
 }
 
+// closest point of a solid cylinder (centre p, unit axis a, radius r, half length h) to q
+__device__ __forceinline__ double cyl_closest(const double* p, const double* a, double r,
+                                              double h, const double* q, double* cl) {
+  double dq[3] = {q[0] - p[0], q[1] - p[1], q[2] - p[2]};
+  double x = dot3(dq, a);
+  double w[3] = {dq[0] - x * a[0], dq[1] - x * a[1], dq[2] - x * a[2]};
+  double rho = norm3(w);
+  double xc = clampd(x, -h, h);
+  double sc = rho > r ? r / rho : 1.0;
+  for (int k = 0; k < 3; k++) cl[k] = p[k] + xc * a[k] + sc * w[k];
+  double e[3] = {q[0] - cl[0], q[1] - cl[1], q[2] - cl[2]};
+  return norm3(e);
+}
+
+// sphere (geom 1) against a cylinder (geom 2): along the closest-point direction; a
+// centre inside the cylinder leaves through the nearer of the side and the caps
+__device__ __forceinline__ int col_sphere_cylinder(const double* q, double rs, const double* p,
+                                                   const double* a, double r, double h,
+                                                   double margin, RawCon& o) {
+  double cl[3], nrm[3], dist;
+  double dd = cyl_closest(p, a, r, h, q, cl);
+  if (dd > BP_MINVAL) {
+    for (int k = 0; k < 3; k++) nrm[k] = (cl[k] - q[k]) / dd;
+    dist = dd - rs;
+  } else {
+    double dq[3] = {q[0] - p[0], q[1] - p[1], q[2] - p[2]};
+    double x = dot3(dq, a);
+    double w[3] = {dq[0] - x * a[0], dq[1] - x * a[1], dq[2] - x * a[2]};
+    double rho = norm3(w);
+    if (r - rho < h - fabs(x) && rho > BP_MINVAL) {
+      for (int k = 0; k < 3; k++) nrm[k] = -w[k] / rho;
+      dist = -(r - rho) - rs;
+    } else {
+      double sg = x >= 0 ? 1.0 : -1.0;
+      for (int k = 0; k < 3; k++) nrm[k] = -sg * a[k];
+      dist = -(h - fabs(x)) - rs;
+    }
+  }
+  if (dist > margin) return 0;
+  o.dist = dist;
+  for (int k = 0; k < 3; k++) {
+    o.pos[k] = q[k] + nrm[k] * (rs + 0.5 * dist);
+    o.n[k] = nrm[k];
+    o.hint[k] = 0;
+  }
+  return 1;
+}
+
+// Pairs whose second geom is a cylinder.  plane: analytic, up to four rim points.
+// sphere: closest point.  capsule: the distance from a point of the capsule's segment to
+// the cylinder is convex along the segment, so the closest point is bracketed by
+// bisection on the sign of the derivative.  cylinder - cylinder: geom 1 is replaced by
+// its enclosing capsule (exact while the two are apart).
+static __device__ __noinline__ int bp_collide_cylinder(int t1, const double* p1, const double* z1,
+                                                       const double* s1, const double* p2,
+                                                       const double* R2, const double* s2,
+                                                       double margin, RawCon* out) {
+  double a2[3] = {R2[2], R2[5], R2[8]};
+  if (t1 == GEOM_PLANE) {
+    double axis[3] = {a2[0], a2[1], a2[2]}, vec[3];
+    double prjaxis = dot3(z1, axis);
+    if (prjaxis > 0) { for (int k = 0; k < 3; k++) axis[k] = -axis[k]; prjaxis = -prjaxis; }
+    double dif[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
+    double dist0 = dot3(dif, z1);
+    for (int k = 0; k < 3; k++) vec[k] = axis[k] * prjaxis - z1[k];
+    double len = norm3(vec);
+    if (len >= BP_MINVAL) { for (int k = 0; k < 3; k++) vec[k] *= s2[0] / len; }
+    else { vec[0] = R2[0] * s2[0]; vec[1] = R2[3] * s2[0]; vec[2] = R2[6] * s2[0]; }
+    double prjvec = dot3(vec, z1);
+    for (int k = 0; k < 3; k++) axis[k] *= s2[1];
+    prjaxis *= s2[1];
+    if (dist0 + prjaxis + prjvec > margin) return 0;
+    int cnt = 0;
+    double dd = dist0 + prjaxis + prjvec;
+    out[cnt].dist = dd;
+    for (int k = 0; k < 3; k++) {
+      out[cnt].pos[k] = p2[k] + vec[k] + axis[k] - z1[k] * dd * 0.5;
+      out[cnt].n[k] = z1[k]; out[cnt].hint[k] = 0;
+    }
+    cnt++;
+    dd = dist0 - prjaxis + prjvec;
+    if (dd <= margin) {
+      out[cnt].dist = dd;
+      for (int k = 0; k < 3; k++) {
+        out[cnt].pos[k] = p2[k] + vec[k] - axis[k] - z1[k] * dd * 0.5;
+        out[cnt].n[k] = z1[k]; out[cnt].hint[k] = 0;
+      }
+      cnt++;
+    }
+    double prjvec1 = -prjvec * 0.5;
+    dd = dist0 + prjaxis + prjvec1;
+    if (dd <= margin) {
+      double vec1[3];
+      cross3(vec1, vec, axis);
+      normalize3(vec1);
+      for (int k = 0; k < 3; k++) vec1[k] *= s2[0] * sqrt(3.0) * 0.5;
+      for (int sgn = 1; sgn >= -1; sgn -= 2) {
+        out[cnt].dist = dd;
+        for (int k = 0; k < 3; k++) {
+          out[cnt].pos[k] = p2[k] + sgn * vec1[k] + axis[k] - vec[k] * 0.5 - z1[k] * dd * 0.5;
+          out[cnt].n[k] = z1[k]; out[cnt].hint[k] = 0;
+        }
+        cnt++;
+      }
+    }
+    return cnt;
+  }
+  if (t1 == GEOM_SPHERE)
+    return col_sphere_cylinder(p1, s1[0], p2, a2, s2[0], s2[1], margin, out[0]);
+  if (t1 == GEOM_CAPSULE || t1 == GEOM_CYLINDER) {
+    double lo = -s1[1], hi = s1[1], q[3], cl[3];
+#pragma unroll 1
+    for (int it = 0; it < 64; it++) {
+      double t = 0.5 * (lo + hi);
+      for (int k = 0; k < 3; k++) q[k] = p1[k] + t * z1[k];
+      cyl_closest(p2, a2, s2[0], s2[1], q, cl);
+      double g = (q[0] - cl[0]) * z1[0] + (q[1] - cl[1]) * z1[1] + (q[2] - cl[2]) * z1[2];
+      if (g >= 0) hi = t; else lo = t;
+    }
+    double t = 0.5 * (lo + hi);
+    for (int k = 0; k < 3; k++) q[k] = p1[k] + t * z1[k];
+    int n = col_sphere_cylinder(q, s1[0], p2, a2, s2[0], s2[1], margin, out[0]);
+    if (n) for (int k = 0; k < 3; k++) out[0].hint[k] = z1[k];
+    return n;
+  }
+  return 0;
+}
+
 // Narrowphase of ordered pair (type1 <= type2) on geom poses already copied to
 // registers (p = centre, z = local z axis, R2 = full frame of geom 2 for boxes).
 // Returns the number of raw contacts written to out[0..3].
@@ -47,6 +175,7 @@ static __device__ __noinline__ int bp_collide_prims(int t1, int t2, const double
                                                     const double* p2, const double* z2,
                                                     const double* R2, const double* s2,
                                                     double margin, RawCon* out) {
+  if (t2 == GEOM_CYLINDER) return bp_collide_cylinder(t1, p1, z1, s1, p2, R2, s2, margin, out);
   if (t1 == GEOM_PLANE) {
     if (t2 == GEOM_SPHERE) return col_plane_sphere(p1, z1, p2, s2[0], margin, out[0]);
     if (t2 == GEOM_CAPSULE) {

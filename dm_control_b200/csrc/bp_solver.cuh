@@ -7,6 +7,9 @@
 #define BP_SOLVER_CUH_
 #include "bp_math.cuh"
 
+// the Hessian and its factor are stored as a packed lower triangle, row i at i (i + 1) / 2
+#define PK(i, j) ((i) * ((i) + 1) / 2 + (j))
+
 // dst[0..n) = src[0..n): four loads in flight per lane before the stores (the compiler
 // cannot reorder them itself, the two ranges might alias)
 template <class C>
@@ -52,6 +55,145 @@ BP_STAGE void bp_mul_j(const C& c, typename C::DP out, typename C::DP x, typenam
   SYNC();
 }
 
+// ---- elliptic friction cones (opt_cone == 1; Appendix A.9) ---------------------------
+// In the scaled coordinates U = (mu x0, fri_j x_j), N = U0, T = |U_1..|: N >= mu T is the
+// top zone (no force), mu N + T <= 0 the bottom zone (every row plainly quadratic) and in
+// between the cost is 0.5 Dm (N - mu T)^2, Dm = D0 / (mu^2 (1 + mu^2)).  Contacts on lanes.
+// Kept out of line: the pyramidal models never execute any of it.
+BP_STAGE double bp_cone_update(const C& c, typename C::DP jar, int nefc, bool write, bool* chg) {
+  const int ncon = IF(ncon)[0];
+  auto force = DF(efc_force), D = DF(efc_D), rw = DF(s_rw);
+  auto state = IF(efc_state);
+  double cost = 0;
+#pragma unroll 1
+  for (int ci = c.lane; ci < ncon; ci += C::G) {
+    const int a = IF(contact_efc_address)[ci], dim = IF(contact_dim)[ci];
+    if (a < 0 || dim == 1 || a + dim > nefc) continue;
+    const double mu = DF(contact_mu)[ci];
+    auto fri = DF(contact_friction) + 5 * ci;
+    const double N = jar[a] * mu;
+    double tt = 0;
+    for (int j = 1; j < dim; j++) { double u = jar[a + j] * fri[j - 1]; tt += u * u; }
+    const double T = sqrt(tt);
+    if (N >= mu * T || (T <= 0 && N >= 0)) {
+      if (write)
+        for (int j = 0; j < dim; j++) {
+          force[a + j] = 0; state[a + j] = ST_SATISFIED;
+          *chg |= rw[a + j] != 0; rw[a + j] = 0;
+        }
+    } else if (mu * N + T <= 0 || (T <= 0 && N < 0)) {
+      for (int j = 0; j < dim; j++) {
+        double d = D[a + j], x = jar[a + j];
+        cost += 0.5 * d * x * x;
+        if (write) {
+          force[a + j] = -d * x; state[a + j] = ST_QUADRATIC;
+          *chg |= rw[a + j] != d; rw[a + j] = d;
+        }
+      }
+    } else {
+      const double Dm = D[a] / (mu * mu * (1 + mu * mu)), NmT = N - mu * T;
+      cost += 0.5 * Dm * NmT * NmT;
+      if (write) {
+        const double f0 = -Dm * NmT * mu;
+        force[a] = f0; state[a] = ST_CONE; rw[a] = 0;
+        for (int j = 1; j < dim; j++) {
+          force[a + j] = -f0 / T * (jar[a + j] * fri[j - 1]) * fri[j - 1];
+          state[a + j] = ST_CONE; rw[a + j] = 0;
+        }
+        *chg = true;                 // the cone Hessian moves with jar
+      }
+    }
+  }
+  return cost;
+}
+
+// line-search sums of the elliptic contacts at step alpha: bottom-zone rows add to the
+// quadratic coefficients q[0..2], middle-zone cones to the value / slope / curvature e[0..2]
+BP_STAGE void bp_cone_ls(const C& c, double alpha, int nefc, double* q, double* e) {
+  const int ncon = IF(ncon)[0];
+  auto D = DF(efc_D), jar = DF(s_jar), jvv = DF(s_jv);
+#pragma unroll 1
+  for (int ci = c.lane; ci < ncon; ci += C::G) {
+    const int a = IF(contact_efc_address)[ci], dim = IF(contact_dim)[ci];
+    if (a < 0 || dim == 1 || a + dim > nefc) continue;
+    const double mu = DF(contact_mu)[ci];
+    auto fri = DF(contact_friction) + 5 * ci;
+    const double U0 = jar[a] * mu, V0 = jvv[a] * mu;
+    double UU = 0, UV = 0, VV = 0;
+    for (int j = 1; j < dim; j++) {
+      double u = jar[a + j] * fri[j - 1], v = jvv[a + j] * fri[j - 1];
+      UU += u * u; UV += u * v; VV += v * v;
+    }
+    const double N = U0 + alpha * V0, Tsqr = UU + alpha * (2 * UV + alpha * VV);
+    const double T = Tsqr > 0 ? sqrt(Tsqr) : 0;
+    if (N >= mu * T || (T <= 0 && N >= 0)) continue;
+    if (mu * N + T <= 0 || (T <= 0 && N < 0)) {
+      for (int j = 0; j < dim; j++) {
+        double d = D[a + j], j0 = jar[a + j], jv = jvv[a + j];
+        q[0] += 0.5 * d * j0 * j0; q[1] += d * j0 * jv; q[2] += 0.5 * d * jv * jv;
+      }
+    } else {
+      const double Dm = D[a] / (mu * mu * (1 + mu * mu));
+      const double N1 = V0, T1 = (UV + alpha * VV) / T;
+      const double T2 = VV / T - (UV + alpha * VV) * T1 / (T * T);
+      const double NmT = N - mu * T, NmT1 = N1 - mu * T1;
+      e[0] += 0.5 * Dm * NmT * NmT;
+      e[1] += Dm * NmT * NmT1;
+      e[2] += Dm * (NmT1 * NmT1 - NmT * mu * T2);
+    }
+  }
+}
+
+// H += Jc^T Hc Jc for the contacts in the middle zone, Hc = Dm S (g g^T + kappa P) S with
+// S = diag(mu, fri), u = U_t / T, g = (1, -mu u), P = I - u u^T on the tangential block,
+// kappa = mu^2 - mu N / T.  One contact at a time; its dof-set pairs over the lanes.
+BP_STAGE void bp_cone_hessian(const C& c, typename C::DP H, int nefc) {
+  const BpModel& m = c.P.m;
+  const int ncon = IF(ncon)[0], nvp = m.nvp;
+  auto J = DF(efc_J), jar = DF(s_jar), D = DF(efc_D);
+#pragma unroll 1
+  for (int ci = 0; ci < ncon; ci++) {
+    const int a = IF(contact_efc_address)[ci], dim = IF(contact_dim)[ci];
+    if (a < 0 || dim == 1 || a + dim > nefc || IF(efc_state)[a] != ST_CONE) continue;
+    const double mu = DF(contact_mu)[ci];
+    auto fri = DF(contact_friction) + 5 * ci;
+    double S[6], g[6], u[6];
+    const double N = jar[a] * mu;
+    double tt = 0;
+    S[0] = mu; g[0] = 1; u[0] = 0;
+    for (int j = 1; j < dim; j++) { S[j] = fri[j - 1]; u[j] = jar[a + j] * S[j]; tt += u[j] * u[j]; }
+    const double T = sqrt(tt);
+    for (int j = 1; j < dim; j++) { u[j] /= T; g[j] = -mu * u[j]; }
+    const double Dm = D[a] / (mu * mu * (1 + mu * mu)), kappa = mu * mu - mu * N / T;
+    const unsigned long long mk = m.body_dofmask[m.geom_bodyid[IF(contact_geom1)[ci]]] |
+                                  m.body_dofmask[m.geom_bodyid[IF(contact_geom2)[ci]]];
+    unsigned long long remi = mk;
+#pragma unroll 1
+    for (int ap = 0; remi; ap++, remi &= remi - 1) {
+      const int i = __ffsll((long long)remi) - 1;
+      double y[6], gv = 0, ut = 0;
+      for (int q = 0; q < dim; q++) {
+        y[q] = S[q] * J[(a + q) * nvp + i];
+        gv += g[q] * y[q];
+        if (q > 0) ut += u[q] * y[q];
+      }
+      for (int q = 0; q < dim; q++)
+        y[q] = Dm * S[q] * (g[q] * gv + (q > 0 ? kappa * (y[q] - u[q] * ut) : 0.0));
+      unsigned long long remj = mk;
+      for (int t = 0; t < c.lane; t++) remj &= remj - 1;
+#pragma unroll 1
+      for (int bp = c.lane; bp <= ap; bp += C::G) {
+        const int j = __ffsll((long long)remj) - 1;
+        for (int t = 0; t < C::G; t++) remj &= remj - 1;
+        double sum = 0;
+        for (int q = 0; q < dim; q++) sum += y[q] * J[(a + q) * nvp + j];
+        H[PK(i, j)] += sum;
+      }
+    }
+    SYNC();
+  }
+}
+
 // constraint cost at residual jar; optionally writes force/state and J^T force
 // *changed (write only): some row's Hessian weight differs from the previous call, i.e.
 // the factorisation of H is stale
@@ -72,6 +214,8 @@ BP_STAGE double bp_update_constraint(const C& c, typename C::DP jar, int nefc, b
       if (x <= -rr * fl) { f = fl; st = ST_LINEARNEG; cr = -fl * (0.5 * rr * fl + x); }
       else if (x >= rr * fl) { f = -fl; st = ST_LINEARPOS; cr = -fl * (0.5 * rr * fl - x); }
       else { f = -d * x; st = ST_QUADRATIC; cr = 0.5 * d * x * x; }
+    } else if (t == CN_CONTACT_ELLIPTIC) {
+      continue;                                    // whole contacts: bp_cone_update
     } else {
       if (x >= 0) { f = 0; st = ST_SATISFIED; }
       else { f = -d * x; st = ST_QUADRATIC; cr = 0.5 * d * x * x; }
@@ -84,6 +228,7 @@ BP_STAGE double bp_update_constraint(const C& c, typename C::DP jar, int nefc, b
       DF(s_rw)[r] = w;
     }
   }
+  if (c.P.m.opt_cone == 1) cost += bp_cone_update(c, jar, nefc, write, &chg);
   cost = group_sum(c, cost);
   if (write) {
     *changed = group_any(c, chg);
@@ -128,13 +273,21 @@ BP_STAGE LSPoint bp_ls_eval(const C& c, double alpha, double g0, double g1, doub
       if (x <= -rr * f) { c0 += -f * (0.5 * rr * f + j0); c1 += -f * jv; }
       else if (x >= rr * f) { c0 += -f * (0.5 * rr * f - j0); c1 += f * jv; }
       else { c0 += q0; c1 += q1; c2 += q2; }
-    } else if (x < 0) { c0 += q0; c1 += q1; c2 += q2; }
+    } else if (t == CN_CONTACT_ELLIPTIC) continue;
+    else if (x < 0) { c0 += q0; c1 += q1; c2 += q2; }
+  }
+  double e[3] = {0, 0, 0};
+  if (c.P.m.opt_cone == 1) {
+    double q[3] = {0, 0, 0};
+    bp_cone_ls(c, alpha, nefc, q, e);
+    c0 += q[0]; c1 += q[1]; c2 += q[2];
+    e[0] = group_sum(c, e[0]); e[1] = group_sum(c, e[1]); e[2] = group_sum(c, e[2]);
   }
   c0 = g0 + group_sum(c, c0); c1 = g1 + group_sum(c, c1); c2 = g2 + group_sum(c, c2);
   LSPoint p;
-  p.cost = alpha * alpha * c2 + alpha * c1 + c0;
-  p.d0 = 2 * alpha * c2 + c1;
-  p.d1 = 2 * c2;
+  p.cost = alpha * alpha * c2 + alpha * c1 + c0 + e[0];
+  p.d0 = 2 * alpha * c2 + c1 + e[1];
+  p.d1 = 2 * c2 + e[2];
   return p;
 }
 
@@ -178,8 +331,6 @@ BP_STAGE double bp_linesearch(const C& c, double scale, int nefc) {
 // number of slots NS a model really uses (humanoid on 16 lanes: 2), so dead slots cost no
 // instructions.  Larger systems fall back to the generic right-looking code.
 #define BP_RS 4
-// the Hessian and its factor are stored as a packed lower triangle, row i at i (i + 1) / 2
-#define PK(i, j) ((i) * ((i) + 1) / 2 + (j))
 
 template <int NS>
 __device__ __forceinline__ double bp_slot(const double (&v)[NS], int s) {
@@ -474,6 +625,7 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refacto
       SYNC();
     }
   }
+  if (m.opt_cone == 1) bp_cone_hessian(c, H, nefc);
   if (!bp_chol_factor(c, H, Hdinv)) {
     SYNC();
     bp_copy(c, H, Md, ntri);

@@ -21,6 +21,7 @@ extern "C" int bp_task_nobs_impl(const BpModel* m, int task) {
     case TASK_HUMANOID: return (m->nq - 7) + 1 + 12 + 3 + 3 + m->nv;
     case TASK_HOPPER: return m->nq - 1 + m->nv + 2;
     case TASK_REACHER: return m->nq + 2 + m->nv;
+    case TASK_FINGER: return 9;
   }
   return -1;
 }

@@ -15,7 +15,7 @@
 
 enum { TASK_NONE = 0, TASK_CARTPOLE = 1, TASK_ACROBOT = 2, TASK_PENDULUM = 3,
        TASK_CHEETAH = 4, TASK_WALKER = 5, TASK_HUMANOID = 6, TASK_HOPPER = 7,
-       TASK_REACHER = 8 };
+       TASK_REACHER = 8, TASK_FINGER = 9 };
 enum { SIG_GAUSSIAN = 0, SIG_LINEAR = 1, SIG_QUADRATIC = 2 };
 
 // read-only strided window of one environment's image (see bp_math.cuh for layouts)
@@ -188,6 +188,19 @@ static __device__ __noinline__ void bp_task_eval(const BpParams& P, const BpTask
         for (int i = 0; i < m.nu; i++) sc += tolerance(ctrl[i], 0, 0, 1, SIG_QUADRATIC, 0);
         r = standing * (sc / m.nu + 4) / 5;
       }
+      break;
+    }
+    case TASK_FINGER: {     // suite/finger.py:87-112,139-156 (spin)
+      // ip: sensordata addresses of proximal, distal, proximal_velocity, distal_velocity,
+      // hinge_velocity, tip, spinner, touchtop, touchbottom; fp: spin velocity
+      if (o) {
+        o[k++] = sens[T.ip[0]]; o[k++] = sens[T.ip[1]];
+        o[k++] = sens[T.ip[5]] - sens[T.ip[6]];
+        o[k++] = sens[T.ip[5] + 2] - sens[T.ip[6] + 2];
+        o[k++] = sens[T.ip[2]]; o[k++] = sens[T.ip[3]]; o[k++] = sens[T.ip[4]];
+        o[k++] = log1p(sens[T.ip[7]]); o[k++] = log1p(sens[T.ip[8]]);
+      }
+      r = sens[T.ip[4]] <= -T.fp[0] ? 1.0 : 0.0;
       break;
     }
     default: break;

@@ -115,7 +115,12 @@ class Task:
     elif d == "walker":           # suite/walker.py:118-129
       for e, rng in enumerate(self._rngs):
         _randomize_limited_and_rotational_joints(m, qpos[e], rng)
-    elif d == "humanoid":         # suite/humanoid.py:152-166: rejection on contacts
+    elif d in ("humanoid", "finger"):
+      # suite/humanoid.py:152-166, suite/finger.py:139-144,201-212: rejection on contacts
+      if d == "finger":           # finger.py:142 (spin): the same edit for every env
+        damping = np.array(m.dof_damping, dtype=np.float64)
+        damping[m.jnt_dofadr[m.name2id("hinge", "joint")]] = .03
+        physics.set_model_field("dof_damping", damping)
       todo = np.ones(n, dtype=bool)
       while todo.any():
         for e in np.flatnonzero(todo):

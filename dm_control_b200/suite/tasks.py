@@ -12,6 +12,7 @@ import numpy as np
 
 # task kinds of csrc/bp_task.cu
 NONE, CARTPOLE, ACROBOT, PENDULUM, CHEETAH, WALKER, HUMANOID, HOPPER = range(8)
+FINGER = 9
 
 TaskDef = collections.namedtuple(
     "TaskDef", "domain task model kind time_limit control_timestep params obs")
@@ -68,6 +69,12 @@ def _hopper(hopping):
   return f
 
 
+def _finger(m):
+  names = ("proximal", "distal", "proximal_velocity", "distal_velocity", "hinge_velocity",
+           "tip", "spinner", "touchtop", "touchbottom")
+  return [_sens_adr(m, n) for n in names], [15.0]           # finger.py:38 _SPIN_VELOCITY
+
+
 def _obs_hopper(m):
   return [("position", m.nq - 1), ("velocity", m.nv), ("touch", 2)]
 
@@ -103,6 +110,10 @@ _TASKS = [
     # hopper.py:32-41: 20 s, control timestep .02, stand height .6, hop speed 2
     TaskDef("hopper", "stand", "hopper", HOPPER, 20, .02, _hopper(False), _obs_hopper),
     TaskDef("hopper", "hop", "hopper", HOPPER, 20, .02, _hopper(True), _obs_hopper),
+    # finger.py:28-29: 20 s, control timestep .02 (the turn tasks move a model site per
+    # episode and are not served)
+    TaskDef("finger", "spin", "finger", FINGER, 20, .02, _finger,
+            lambda m: [("position", 4), ("velocity", 3), ("touch", 2)]),
     # humanoid.py:28-35: 25 s, control timestep .025, speeds 0 / 1 / 10
     TaskDef("humanoid", "stand", "humanoid", HUMANOID, 25, .025, _humanoid(0.0), None),
     TaskDef("humanoid", "walk", "humanoid", HUMANOID, 25, .025, _humanoid(1.0), None),

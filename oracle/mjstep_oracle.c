@@ -758,6 +758,137 @@ static void geom_axis(const double* xmat, int col, double* ax) {
   ax[0] = xmat[col]; ax[1] = xmat[3 + col]; ax[2] = xmat[6 + col];
 }
 
+/* plane - cylinder [MJ-doc: analytic, up to four points]: the deepest rim point of the
+ * disk facing the plane, the matching point of the other disk, and two more points of
+ * the first disk at +-120 degrees when that disk lies nearly flat */
+static int col_plane_cylinder_raw(const double* ppos, const double* n, const double* cpos,
+                                  const double* cmat, const double* size, double margin,
+                                  RawCon* out) {
+  double axis[3], vec[3];
+  geom_axis(cmat, 2, axis);
+  double prjaxis = dot3(n, axis);
+  if (prjaxis > 0) { for (int k = 0; k < 3; k++) axis[k] = -axis[k]; prjaxis = -prjaxis; }
+  double dif[3] = {cpos[0] - ppos[0], cpos[1] - ppos[1], cpos[2] - ppos[2]};
+  double dist0 = dot3(dif, n);
+  for (int k = 0; k < 3; k++) vec[k] = axis[k] * prjaxis - n[k];
+  double len = norm3(vec);
+  if (len >= MINVAL) for (int k = 0; k < 3; k++) vec[k] *= size[0] / len;
+  else { geom_axis(cmat, 0, vec); for (int k = 0; k < 3; k++) vec[k] *= size[0]; }
+  double prjvec = dot3(vec, n);
+  for (int k = 0; k < 3; k++) axis[k] *= size[1];
+  prjaxis *= size[1];
+  if (dist0 + prjaxis + prjvec > margin) return 0;
+  int cnt = 0;
+  double dd = dist0 + prjaxis + prjvec;
+  out[cnt].dist = dd;
+  for (int k = 0; k < 3; k++) {
+    out[cnt].pos[k] = cpos[k] + vec[k] + axis[k] - n[k] * dd * 0.5;
+    out[cnt].frame[k] = n[k];
+  }
+  memset(out[cnt].frame + 3, 0, 48);
+  cnt++;
+  dd = dist0 - prjaxis + prjvec;
+  if (dd <= margin) {
+    out[cnt].dist = dd;
+    for (int k = 0; k < 3; k++) {
+      out[cnt].pos[k] = cpos[k] + vec[k] - axis[k] - n[k] * dd * 0.5;
+      out[cnt].frame[k] = n[k];
+    }
+    memset(out[cnt].frame + 3, 0, 48);
+    cnt++;
+  }
+  double prjvec1 = -prjvec * 0.5;
+  dd = dist0 + prjaxis + prjvec1;
+  if (dd <= margin) {
+    double vec1[3];
+    cross3(vec1, vec, axis);
+    normalize3(vec1);
+    for (int k = 0; k < 3; k++) vec1[k] *= size[0] * sqrt(3.0) * 0.5;
+    for (int sgn = 1; sgn >= -1; sgn -= 2) {
+      out[cnt].dist = dd;
+      for (int k = 0; k < 3; k++) {
+        out[cnt].pos[k] = cpos[k] + sgn * vec1[k] + axis[k] - vec[k] * 0.5 - n[k] * dd * 0.5;
+        out[cnt].frame[k] = n[k];
+      }
+      memset(out[cnt].frame + 3, 0, 48);
+      cnt++;
+    }
+  }
+  return cnt;
+}
+
+/* closest point of a solid cylinder (centre p, unit axis a, radius r, half length h) to q;
+ * returns the distance (0 inside) */
+static double cyl_closest(const double* p, const double* a, double r, double h,
+                          const double* q, double* cl) {
+  double dq[3] = {q[0] - p[0], q[1] - p[1], q[2] - p[2]};
+  double x = dot3(dq, a);
+  double w[3] = {dq[0] - x * a[0], dq[1] - x * a[1], dq[2] - x * a[2]};
+  double rho = norm3(w);
+  double xc = x < -h ? -h : (x > h ? h : x);
+  double sc = rho > r ? r / rho : 1.0;
+  for (int k = 0; k < 3; k++) cl[k] = p[k] + xc * a[k] + sc * w[k];
+  double e[3] = {q[0] - cl[0], q[1] - cl[1], q[2] - cl[2]};
+  return norm3(e);
+}
+
+/* sphere (centre q, radius rs; geom1) against a cylinder (geom2).  Outside: along the
+ * closest-point direction.  Centre inside the cylinder: pushed out through the nearer of
+ * the lateral surface and the caps (MuJoCo resolves deep convex overlaps with MPR; the
+ * suite models never reach this branch) */
+static int col_sphere_cylinder_raw(const double* q, double rs, const double* p,
+                                   const double* a, double r, double h, double margin,
+                                   RawCon* out) {
+  double cl[3], nrm[3], dist;
+  double dd = cyl_closest(p, a, r, h, q, cl);
+  if (dd > MINVAL) {
+    for (int k = 0; k < 3; k++) nrm[k] = (cl[k] - q[k]) / dd;
+    dist = dd - rs;
+  } else {
+    double dq[3] = {q[0] - p[0], q[1] - p[1], q[2] - p[2]};
+    double x = dot3(dq, a);
+    double w[3] = {dq[0] - x * a[0], dq[1] - x * a[1], dq[2] - x * a[2]};
+    double rho = norm3(w);
+    if (r - rho < h - fabs(x) && rho > MINVAL) {
+      for (int k = 0; k < 3; k++) nrm[k] = -w[k] / rho;
+      dist = -(r - rho) - rs;
+    } else {
+      double sg = x >= 0 ? 1.0 : -1.0;
+      for (int k = 0; k < 3; k++) nrm[k] = -sg * a[k];
+      dist = -(h - fabs(x)) - rs;
+    }
+  }
+  if (dist > margin) return 0;
+  out->dist = dist;
+  for (int k = 0; k < 3; k++) {
+    out->pos[k] = q[k] + nrm[k] * (rs + 0.5 * dist);
+    out->frame[k] = nrm[k];
+  }
+  memset(out->frame + 3, 0, 48);
+  return 1;
+}
+
+/* capsule (segment pc + t ac, |t| <= l, radius rc; geom1) against a cylinder: the
+ * distance from the segment point to the cylinder is convex in t, so the closest point
+ * is found by bisection on the sign of its derivative, then handled as a sphere */
+static int col_capsule_cylinder_raw(const double* pc, const double* ac, double rc, double l,
+                                    const double* p, const double* a, double r, double h,
+                                    double margin, RawCon* out) {
+  double lo = -l, hi = l, q[3], cl[3];
+  for (int it = 0; it < 64; it++) {
+    double t = 0.5 * (lo + hi);
+    for (int k = 0; k < 3; k++) q[k] = pc[k] + t * ac[k];
+    cyl_closest(p, a, r, h, q, cl);
+    double g = (q[0] - cl[0]) * ac[0] + (q[1] - cl[1]) * ac[1] + (q[2] - cl[2]) * ac[2];
+    if (g >= 0) hi = t; else lo = t;
+  }
+  double t = 0.5 * (lo + hi);
+  for (int k = 0; k < 3; k++) q[k] = pc[k] + t * ac[k];
+  int n = col_sphere_cylinder_raw(q, rc, p, a, r, h, margin, out);
+  if (n) memcpy(out->frame + 3, ac, 24);
+  return n;
+}
+
 static int collide_pair(const OModel* m, const OData* d, int g1, int g2,
                         double margin, RawCon* out) {
   int t1 = m->geom_type[g1], t2 = m->geom_type[g2];
@@ -781,6 +912,7 @@ static int collide_pair(const OModel* m, const OData* d, int g1, int g2,
       }
       return cnt;
     }
+    if (t2 == GEOM_CYLINDER) return col_plane_cylinder_raw(p1, n, p2, R2, s2, margin, out);
     if (t2 == GEOM_BOX) {
       double dif[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
       double dist = dot3(dif, n);
@@ -813,6 +945,16 @@ static int collide_pair(const OModel* m, const OData* d, int g1, int g2,
     x = x < -s2[1] ? -s2[1] : (x > s2[1] ? s2[1] : x);
     double c[3] = {p2[0] + ax[0] * x, p2[1] + ax[1] * x, p2[2] + ax[2] * x};
     return col_sphere_sphere_raw(p1, s1[0], c, s2[0], margin, out);
+  }
+  if (t2 == GEOM_CYLINDER && (t1 == GEOM_SPHERE || t1 == GEOM_CAPSULE || t1 == GEOM_CYLINDER)) {
+    double a2[3], a1[3];
+    geom_axis(R2, 2, a2);
+    if (t1 == GEOM_SPHERE)
+      return col_sphere_cylinder_raw(p1, s1[0], p2, a2, s2[0], s2[1], margin, out);
+    /* cylinder - cylinder: geom1 is replaced by its enclosing capsule, which is exact
+     * whenever the two are apart (all the suite models need) and approximate in contact */
+    geom_axis(R1, 2, a1);
+    return col_capsule_cylinder_raw(p1, a1, s1[0], s1[1], p2, a2, s2[0], s2[1], margin, out);
   }
   if (t1 == GEOM_CAPSULE && t2 == GEOM_CAPSULE) {
     /* closest points of two segments p1 + x1*a1, p2 + x2*a2, |xi| <= li */
@@ -1136,6 +1278,20 @@ static void o_reference_constraint(const OModel* m, OData* d) {
 
 typedef struct { double cost, d0, d1; } LSPoint;
 
+/* zone of an elliptic contact at residual x[0..dim): 0 top, 1 bottom, 2 middle */
+typedef struct { int zone; double N, T, U[6]; } ConeZone;
+static ConeZone cone_zone(const OContact* c, const double* x) {
+  ConeZone z;
+  z.U[0] = x[0] * c->mu;
+  double tt = 0;
+  for (int j = 1; j < c->dim; j++) { z.U[j] = x[j] * c->friction[j - 1]; tt += z.U[j] * z.U[j]; }
+  z.N = z.U[0]; z.T = sqrt(tt);
+  if (z.N >= c->mu * z.T || (z.T <= 0 && z.N >= 0)) z.zone = 0;
+  else if (c->mu * z.N + z.T <= 0 || (z.T <= 0 && z.N < 0)) z.zone = 1;
+  else z.zone = 2;
+  return z;
+}
+
 /* constraint cost / force / state at acceleration-space residual jar */
 static double update_constraint(const OModel* m, OData* d, const double* jar) {
   int nv = m->nv, nefc = d->nefc[0];
@@ -1150,11 +1306,43 @@ static double update_constraint(const OModel* m, OData* d, const double* jar) {
       if (x <= -R * f) { d->efc_force[r] = f; d->efc_state[r] = ST_LINEARNEG; cost += -f * (0.5 * R * f + x); }
       else if (x >= R * f) { d->efc_force[r] = -f; d->efc_state[r] = ST_LINEARPOS; cost += -f * (0.5 * R * f - x); }
       else { d->efc_force[r] = -D * x; d->efc_state[r] = ST_QUADRATIC; cost += 0.5 * D * x * x; }
+    } else if (type == CN_CONTACT_ELLIPTIC) {
+      continue;                                  /* whole contacts, below */
     } else {
       if (x >= 0) { d->efc_force[r] = 0; d->efc_state[r] = ST_SATISFIED; }
       else { d->efc_force[r] = -D * x; d->efc_state[r] = ST_QUADRATIC; cost += 0.5 * D * x * x; }
     }
   }
+  /* elliptic cones [A.9]: in the scaled coordinates U = (mu x0, fri_j x_j), N = U0 and
+   * T = |U_1..| the dual cone is N >= mu T (top zone: no force), its polar is
+   * mu N + T <= 0 (bottom zone: plain quadratic in all rows) and in between the cost is
+   * the squared distance to the cone, 0.5 Dm (N - mu T)^2 */
+  if (m->opt_cone == 1)
+    for (int ci = 0; ci < d->ncon[0]; ci++) {
+      const OContact* c = d->contact + ci;
+      int a = c->efc_address, dim = c->dim;
+      if (a < 0 || dim == 1) continue;
+      ConeZone z = cone_zone(c, jar + a);
+      if (z.zone == 0) {
+        for (int j = 0; j < dim; j++) { d->efc_force[a + j] = 0; d->efc_state[a + j] = ST_SATISFIED; }
+      } else if (z.zone == 1) {
+        for (int j = 0; j < dim; j++) {
+          double D = d->efc_D[a + j], x = jar[a + j];
+          d->efc_force[a + j] = -D * x; d->efc_state[a + j] = ST_QUADRATIC;
+          cost += 0.5 * D * x * x;
+        }
+      } else {
+        double Dm = d->efc_D[a] / (c->mu * c->mu * (1 + c->mu * c->mu));
+        double NmT = z.N - c->mu * z.T;
+        cost += 0.5 * Dm * NmT * NmT;
+        double f0 = -Dm * NmT * c->mu;
+        d->efc_force[a] = f0; d->efc_state[a] = ST_CONE;
+        for (int j = 1; j < dim; j++) {
+          d->efc_force[a + j] = -f0 / z.T * z.U[j] * c->friction[j - 1];
+          d->efc_state[a + j] = ST_CONE;
+        }
+      }
+    }
   for (int i = 0; i < nv; i++) {
     double s = 0;
     for (int r = 0; r < nefc; r++) s += d->efc_J[(size_t)r * nv + i] * d->efc_force[r];
@@ -1178,12 +1366,43 @@ static LSPoint ls_eval(const OModel* m, const OData* d, double alpha,
       if (x <= -R * f) { c0 += -f * (0.5 * R * f + j0); c1 += -f * jv; }
       else if (x >= R * f) { c0 += -f * (0.5 * R * f - j0); c1 += f * jv; }
       else { c0 += q0; c1 += q1; c2 += q2; }
-    } else if (x < 0) { c0 += q0; c1 += q1; c2 += q2; }
+    } else if (type == CN_CONTACT_ELLIPTIC) continue;
+    else if (x < 0) { c0 += q0; c1 += q1; c2 += q2; }
   }
+  double e0 = 0, e1 = 0, e2 = 0;       /* middle-zone cones: not quadratic in alpha */
+  if (m->opt_cone == 1)
+    for (int ci = 0; ci < d->ncon[0]; ci++) {
+      const OContact* c = d->contact + ci;
+      int a = c->efc_address, dim = c->dim;
+      if (a < 0 || dim == 1) continue;
+      double mu = c->mu;
+      double U0 = d->s_jar[a] * mu, V0 = d->s_jv[a] * mu, UU = 0, UV = 0, VV = 0;
+      for (int j = 1; j < dim; j++) {
+        double u = d->s_jar[a + j] * c->friction[j - 1], v = d->s_jv[a + j] * c->friction[j - 1];
+        UU += u * u; UV += u * v; VV += v * v;
+      }
+      double N = U0 + alpha * V0, Tsqr = UU + alpha * (2 * UV + alpha * VV);
+      double T = Tsqr > 0 ? sqrt(Tsqr) : 0;
+      if (N >= mu * T || (T <= 0 && N >= 0)) continue;
+      if (mu * N + T <= 0 || (T <= 0 && N < 0)) {
+        for (int j = 0; j < dim; j++) {
+          double D = d->efc_D[a + j], j0 = d->s_jar[a + j], jv = d->s_jv[a + j];
+          c0 += 0.5 * D * j0 * j0; c1 += D * j0 * jv; c2 += 0.5 * D * jv * jv;
+        }
+      } else {
+        double Dm = d->efc_D[a] / (mu * mu * (1 + mu * mu));
+        double N1 = V0, T1 = (UV + alpha * VV) / T;
+        double T2 = VV / T - (UV + alpha * VV) * T1 / (T * T);
+        double NmT = N - mu * T, NmT1 = N1 - mu * T1;
+        e0 += 0.5 * Dm * NmT * NmT;
+        e1 += Dm * NmT * NmT1;
+        e2 += Dm * (NmT1 * NmT1 - NmT * mu * T2);
+      }
+    }
   LSPoint p;
-  p.cost = alpha * alpha * c2 + alpha * c1 + c0;
-  p.d0 = 2 * alpha * c2 + c1;
-  p.d1 = 2 * c2;
+  p.cost = alpha * alpha * c2 + alpha * c1 + c0 + e0;
+  p.d0 = 2 * alpha * c2 + c1 + e1;
+  p.d1 = 2 * c2 + e2;
   return p;
 }
 
@@ -1272,6 +1491,43 @@ static void newton_gradient(const OModel* m, OData* d) {
       for (int j = 0; j <= i; j++) d->s_H[i * nv + j] += D * J[i] * J[j];
     }
   }
+  /* middle-zone cones: H += Jc^T Hc Jc with Hc = Dm S (g g^T + kappa (I - u u^T)_t) S,
+   * S = diag(mu, fri), g = (1, -mu u), u = U_t / T, kappa = mu^2 - mu N / T */
+  if (m->opt_cone == 1)
+    for (int ci = 0; ci < d->ncon[0]; ci++) {
+      const OContact* c = d->contact + ci;
+      int a = c->efc_address, dim = c->dim;
+      if (a < 0 || dim == 1 || d->efc_state[a] != ST_CONE) continue;
+      ConeZone z = cone_zone(c, d->s_jar + a);
+      double mu = c->mu, Dm = d->efc_D[a] / (mu * mu * (1 + mu * mu));
+      double kappa = mu * mu - mu * z.N / z.T;
+      double S[6], g[6], Hc[36];
+      S[0] = mu; g[0] = 1;
+      for (int j = 1; j < dim; j++) { S[j] = c->friction[j - 1]; g[j] = -mu * z.U[j] / z.T; }
+      for (int p = 0; p < dim; p++)
+        for (int q = 0; q < dim; q++) {
+          double h = g[p] * g[q];
+          if (p > 0 && q > 0)
+            h += kappa * ((p == q ? 1.0 : 0.0) - z.U[p] * z.U[q] / (z.T * z.T));
+          Hc[p * dim + q] = Dm * S[p] * S[q] * h;
+        }
+      const double* J = d->efc_J + (size_t)a * nv;
+      for (int i = 0; i < nv; i++) {
+        double y[6];
+        int nz = 0;
+        for (int p = 0; p < dim; p++) {
+          y[p] = 0;
+          for (int q = 0; q < dim; q++) y[p] += Hc[p * dim + q] * J[q * nv + i];
+          nz |= J[p * nv + i] != 0;
+        }
+        if (!nz) continue;
+        for (int j = 0; j <= i; j++) {
+          double sum = 0;
+          for (int p = 0; p < dim; p++) sum += y[p] * J[p * nv + j];
+          d->s_H[i * nv + j] += sum;
+        }
+      }
+    }
   if (!chol_factor(d->s_H, nv)) {
     /* not expected (M is PD); fall back to the unconstrained metric */
     memcpy(d->s_H, d->s_Mdense, sizeof(double) * nv * nv);

@@ -21,7 +21,7 @@ def test_tolerance_restatement_matches_reference_rewards_py():
     np.testing.assert_allclose(got, want, rtol=0, atol=1e-15)
 
 
-@pytest.mark.parametrize("domain", ["pendulum", "cartpole", "cheetah", "humanoid"])
+@pytest.mark.parametrize("domain", ["pendulum", "cartpole", "cheetah", "finger", "humanoid"])
 def test_oracle_reproduces_committed_trajectories(domain):
   g = np.load(os.path.join(GOLDEN, "traj_%s.npz" % domain))
   m = PU.load_model(domain)

@@ -19,7 +19,8 @@ pytestmark = pytest.mark.gpu
 SERVED = [("cartpole", "swingup"), ("cartpole", "swingup_sparse"), ("cartpole", "balance"),
           ("cartpole", "balance_sparse"), ("acrobot", "swingup"), ("acrobot", "swingup_sparse"),
           ("pendulum", "swingup"), ("cheetah", "run"), ("walker", "stand"), ("walker", "walk"),
-          ("walker", "run"), ("hopper", "stand"), ("hopper", "hop"), ("humanoid", "stand"), ("humanoid", "walk"), ("humanoid", "run")]
+          ("walker", "run"), ("hopper", "stand"), ("hopper", "hop"), ("finger", "spin"),
+          ("humanoid", "stand"), ("humanoid", "walk"), ("humanoid", "run")]
 FIELDS = ("qpos", "qvel", "ctrl", "xmat", "xpos", "xipos", "site_xpos", "sensordata")
 
 

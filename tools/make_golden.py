@@ -111,4 +111,5 @@ if __name__ == "__main__":
   rewards_fixture()
   for d in ("pendulum", "cartpole", "acrobot", "cheetah", "walker", "hopper", "humanoid"):
     traj_fixture(d)
+  traj_fixture("finger", nenv=32)       # a tenth of the random states start in contact
   c1_trace()
