@@ -38,6 +38,18 @@ ALGO = {"cheetah": dict(bytes=648, flops=2.0e4), "humanoid": dict(bytes=2048, fl
         "walker": dict(bytes=704, flops=1.8e4), "cartpole": dict(bytes=176, flops=1.0e4),
         "acrobot": dict(bytes=184, flops=1.0e4), "pendulum": dict(bytes=112, flops=1.5e3),
         "finger": dict(bytes=264, flops=1.0e4)}
+# SURVEY.md 8d binding rule: once the oracle's op counter exists its per-config mean
+# replaces the estimates (tools/count_ops.py -> profiles/r1_oracle_opcount.json)
+FLOPS_SOURCE = {}
+try:
+  with open(os.path.join(ROOT, "profiles", "r1_oracle_opcount.json")) as _f:
+    for _name, _rec in json.load(_f).items():
+      _dom = _name.split("-", 1)[0]
+      if _dom in ALGO and _dom not in FLOPS_SOURCE:
+        ALGO[_dom]["flops"] = _rec["flops_per_substep"]
+        FLOPS_SOURCE[_dom] = "oracle op counter, %s (%s)" % (_name, _rec["sample"])
+except (OSError, ValueError, KeyError):
+  pass
 # `lanes`: execution shape picked from the lane sweep (profiles/r1b_sweep_lanes.jsonl)
 WORKLOADS = {"cheetah-run": dict(nenv=16384, njmax=64, nconmax=16, settle=200, lanes=8),
              "humanoid-run": dict(nenv=8192, njmax=120, nconmax=40, settle=100, lanes=16),
@@ -374,8 +386,9 @@ def main():
       "roofline_fp64": {"bound": "fp64 vector pipe", "achieved": fl, "peak": fp64_peak,
                         "unit": "TFLOP/s", "frac": fl / fp64_peak,
                         "flops_per_substep": ALGO[domain]["flops"],
-                        "note": "flops = SURVEY 8d contract estimate v0; peak = DFMA "
-                                "microbenchmark in this run"},
+                        "flops_source": FLOPS_SOURCE.get(
+                            domain, "SURVEY 8d contract estimate v0"),
+                        "note": "peak = DFMA microbenchmark in this run"},
       "physics_steps_per_s": value * r["nsub"],
       "warnings": r["warnings"], "finite": r["finite"], "stats": r["stats"],
       "extra": extra,
