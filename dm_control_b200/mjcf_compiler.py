@@ -522,6 +522,7 @@ def compile_xml(xml_string, assets=None):
   m.model_name = root.get("model", "MuJoCo Model")
   _emit_tree(m, bodies, ctx)
   _emit_options(m, root)
+  _emit_tendons_equality(m, root, classes)
   _emit_actuators(m, root, classes)
   _emit_sensors(m, root, classes)
   _emit_pairs(m)
@@ -685,7 +686,7 @@ def _emit_tree(m, bodies, ctx):
     sub[body_f["parentid"][b]] += sub[b]
   m.set("body_subtreemass", sub)
   # unsupported-in-v1 sizes, present so the schema is stable
-  for k in ("ntendon", "nwrap", "neq", "nhfield", "nmocap"):
+  for k in ("nhfield", "nmocap"):
     m.set(k, 0)
 
 
@@ -736,6 +737,69 @@ def _emit_options(m, root):
   m.set("opt_ls_iterations", 50); m.set("opt_ls_tolerance", 0.01)
   m.set("opt_disableflags", dis); m.set("opt_enableflags", en)
   m.set("njmax_xml", njmax); m.set("nconmax_xml", nconmax)
+
+
+def _solimp(text):
+  si = _floats(text or "0.9 0.95 0.001 0.5 2")
+  return (si + [0.9, 0.95, 0.001, 0.5, 2][len(si):])[:5]
+
+
+def _emit_tendons_equality(m, root, classes):
+  """Fixed tendons (<tendon><fixed>) and tendon / joint equalities [MJ-doc: XML reference].
+  A fixed tendon's length is sum(coef * qpos[joint]); its Jacobian is constant.  Spatial
+  tendons, tendon limits / springs / friction are outside the served models."""
+  T = {"adr": [], "num": []}
+  wrap_obj, wrap_prm = [], []
+  for sec in root.findall("tendon"):
+    for el in sec:
+      if el.tag != "fixed":
+        raise ValueError("tendon <%s> unsupported (fixed tendons only)" % el.tag)
+      a = dict(classes[el.get("class") or "main"].get("tendon"))
+      a.update(classes[el.get("class") or "main"].get("fixed"))
+      a.update(el.attrib)
+      for k in ("limited", "stiffness", "damping", "frictionloss"):
+        if a.get(k, "false" if k == "limited" else "0") not in ("false", "0", "0.0"):
+          raise ValueError("tendon attribute %s unsupported" % k)
+      m.names["tendon"].append(a.get("name", ""))
+      T["adr"].append(len(wrap_obj))
+      for w in el:
+        if w.tag != "joint":
+          raise ValueError("fixed tendon child <%s>" % w.tag)
+        j = m.name2id(w.get("joint"), "joint")
+        if m.jnt_type[j] not in (M.JNT_SLIDE, M.JNT_HINGE):
+          raise ValueError("fixed tendons wrap scalar joints")
+        wrap_obj.append(j); wrap_prm.append(float(w.get("coef")))
+      T["num"].append(len(wrap_obj) - T["adr"][-1])
+  nt = len(T["adr"])
+  m.set("ntendon", nt); m.set("nwrap", len(wrap_obj))
+  m.set("tendon_adr", np.array(T["adr"], dtype=np.int32).reshape(nt))
+  m.set("tendon_num", np.array(T["num"], dtype=np.int32).reshape(nt))
+  m.set("wrap_objid", np.array(wrap_obj, dtype=np.int32).reshape(len(wrap_obj)))
+  m.set("wrap_prm", np.array(wrap_prm, dtype=np.float64).reshape(len(wrap_prm)))
+  # equalities: residual = (x1 - x1_0) - poly(x2 - x2_0), x = joint position / tendon length
+  E = {k: [] for k in ("type", "obj1id", "obj2id", "active", "solref", "solimp", "data")}
+  for sec in root.findall("equality"):
+    for el in sec:
+      if el.tag not in ("tendon", "joint"):
+        raise ValueError("equality <%s> unsupported" % el.tag)
+      a = dict(classes[el.get("class") or "main"].get("equality"))
+      a.update(el.attrib)
+      kind = "tendon" if el.tag == "tendon" else "joint"
+      m.names["equality"].append(a.get("name", ""))
+      E["type"].append(M.EQ_TENDON if kind == "tendon" else M.EQ_JOINT)
+      E["obj1id"].append(m.name2id(a[kind + "1"], kind))
+      E["obj2id"].append(m.name2id(a[kind + "2"], kind) if kind + "2" in a else -1)
+      E["active"].append(0 if a.get("active") == "false" else 1)
+      E["solref"].append(_floats(a.get("solref", "0.02 1"), 2))
+      E["solimp"].append(_solimp(a.get("solimp")))
+      E["data"].append(_floats(a.get("polycoef", "0 1 0 0 0"), 5))
+  ne = len(E["type"])
+  m.set("neq", ne)
+  for k in ("type", "obj1id", "obj2id", "active"):
+    m.set("eq_" + k, np.array(E[k], dtype=np.int32).reshape(ne))
+  m.set("eq_solref", np.array(E["solref"], dtype=np.float64).reshape(ne, 2))
+  m.set("eq_solimp", np.array(E["solimp"], dtype=np.float64).reshape(ne, 5))
+  m.set("eq_data", np.array(E["data"], dtype=np.float64).reshape(ne, 5))
 
 
 def _emit_actuators(m, root, classes):
@@ -998,6 +1062,7 @@ def _set_const(m):
   nv, nb = m.nv, m.nbody
   binv = np.zeros((nb, 2)); dinv = np.zeros(nv); m0 = np.zeros(nv)
   mean_inertia = 1.0
+  Minv = np.zeros((nv, nv))
   if nv > 0:
     kin = host_kinematics(m, np.array(m.qpos0))
     Mm = host_mass_matrix(m, kin)
@@ -1018,6 +1083,17 @@ def _set_const(m):
         dinv[da:da + 3] = np.mean(d[da:da + 3])
       else:
         dinv[da] = d[da]
+  # tendons at qpos0: length and J M^-1 J^T (the diagApprox of tendon equalities)
+  nt = m.ntendon
+  tlen = np.zeros(nt); tinv = np.zeros(nt)
+  for t in range(nt):
+    J = np.zeros(nv)
+    for w in range(m.tendon_adr[t], m.tendon_adr[t] + m.tendon_num[t]):
+      j = m.wrap_objid[w]
+      tlen[t] += m.wrap_prm[w] * m.qpos0[m.jnt_qposadr[j]]
+      J[m.jnt_dofadr[j]] += m.wrap_prm[w]
+    tinv[t] = J @ Minv @ J
+  m.set("tendon_length0", tlen.reshape(nt)); m.set("tendon_invweight0", tinv.reshape(nt))
   m.set("dof_M0", m0); m.set("dof_invweight0", dinv)
   m.set("body_invweight0", binv)
   m.set("stat_meaninertia", mean_inertia)

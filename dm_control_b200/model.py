@@ -64,6 +64,7 @@ SENS = {n: i for i, n in enumerate(SENSOR_TYPES)}
 STAGE_NONE, STAGE_POS, STAGE_VEL, STAGE_ACC = range(4)
 
 TRN_JOINT, TRN_JOINTINPARENT, TRN_SLIDERCRANK, TRN_TENDON, TRN_SITE = range(5)
+EQ_CONNECT, EQ_WELD, EQ_JOINT, EQ_TENDON, EQ_DISTANCE = range(5)
 DYN_NONE, DYN_INTEGRATOR, DYN_FILTER, DYN_MUSCLE, DYN_USER = range(5)
 GAIN_FIXED, GAIN_MUSCLE, GAIN_USER = range(3)
 BIAS_NONE, BIAS_AFFINE, BIAS_MUSCLE, BIAS_USER = range(4)

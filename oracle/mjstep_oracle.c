@@ -48,7 +48,7 @@ typedef struct {
 
 #define MODEL_INT_SCALARS(X) \
   X(nq) X(nv) X(nu) X(na) X(nbody) X(njnt) X(ngeom) X(nsite) X(nM) X(npair) \
-  X(nconmax) X(njmax) X(nsensor) X(nsensordata) X(nkey) \
+  X(nconmax) X(njmax) X(nsensor) X(nsensordata) X(nkey) X(ntendon) X(neq) \
   X(opt_integrator) X(opt_cone) X(opt_solver) X(opt_iterations) \
   X(opt_ls_iterations) X(opt_disableflags) X(opt_enableflags)
 #define MODEL_F64_SCALARS(X) \
@@ -63,7 +63,8 @@ typedef struct {
   X(actuator_trntype) X(actuator_dyntype) X(actuator_gaintype) \
   X(actuator_biastype) X(actuator_trnid) X(actuator_ctrllimited) \
   X(actuator_forcelimited) X(sensor_type) X(sensor_objtype) X(sensor_objid) \
-  X(sensor_dim) X(sensor_adr) X(sensor_needstage)
+  X(sensor_dim) X(sensor_adr) X(sensor_needstage) X(tendon_adr) X(tendon_num) \
+  X(wrap_objid) X(eq_type) X(eq_obj1id) X(eq_obj2id) X(eq_active)
 #define MODEL_F64_ARRAYS(X) \
   X(opt_gravity) X(body_pos) X(body_quat) X(body_ipos) X(body_iquat) \
   X(body_mass) X(body_subtreemass) X(body_inertia) X(body_invweight0) \
@@ -75,7 +76,8 @@ typedef struct {
   X(site_pos) X(site_quat) X(site_size) X(qpos0) X(qpos_spring) \
   X(actuator_dynprm) X(actuator_gainprm) X(actuator_biasprm) \
   X(actuator_ctrlrange) X(actuator_forcerange) X(actuator_gear) \
-  X(sensor_cutoff) X(key_qpos) X(key_qvel) X(key_act) X(key_time)
+  X(sensor_cutoff) X(key_qpos) X(key_qvel) X(key_act) X(key_time) X(wrap_prm) \
+  X(tendon_length0) X(tendon_invweight0) X(eq_solref) X(eq_solimp) X(eq_data)
 
 struct OModel {
   char* blob;
@@ -184,6 +186,7 @@ typedef struct {
   X(qacc_smooth, double, m->nv) X(qfrc_constraint, double, m->nv) \
   X(actuator_length, double, m->nu) X(actuator_velocity, double, m->nu) \
   X(actuator_moment, double, m->nu * m->nv) X(actuator_force, double, m->nu) \
+  X(ten_length, double, m->ntendon) X(ten_velocity, double, m->ntendon) \
   X(sensordata, double, m->nsensordata) \
   X(efc_J, double, m->njmax * m->nv) X(efc_pos, double, m->njmax) \
   X(efc_margin, double, m->njmax) X(efc_frictionloss, double, m->njmax) \
@@ -655,12 +658,28 @@ static void o_rne(const OModel* m, OData* d, int flg_acc, double* result) {
 
 /* ------------------------------------------------------ actuation [A.6] */
 
+/* fixed tendons: length = sum coef * qpos[joint]; the Jacobian is the constant coef row */
+static void o_tendon(const OModel* m, OData* d) {
+  for (int t = 0; t < m->ntendon; t++) {
+    double len = 0;
+    for (int w = m->tendon_adr[t]; w < m->tendon_adr[t] + m->tendon_num[t]; w++)
+      len += m->wrap_prm[w] * d->qpos[m->jnt_qposadr[m->wrap_objid[w]]];
+    d->ten_length[t] = len;
+  }
+}
+
 static void o_transmission(const OModel* m, OData* d) {
   int nv = m->nv;
   memset(d->actuator_moment, 0, sizeof(double) * m->nu * nv);
   for (int i = 0; i < m->nu; i++) {
     int j = m->actuator_trnid[2 * i];
     double g = m->actuator_gear[6 * i];
+    if (m->actuator_trntype[i] == 3) {          /* tendon transmission */
+      d->actuator_length[i] = g * d->ten_length[j];
+      for (int w = m->tendon_adr[j]; w < m->tendon_adr[j] + m->tendon_num[j]; w++)
+        d->actuator_moment[i * nv + m->jnt_dofadr[m->wrap_objid[w]]] += g * m->wrap_prm[w];
+      continue;
+    }
     /* joint transmission, scalar joints only in this subset */
     d->actuator_length[i] = g * d->qpos[m->jnt_qposadr[j]];
     d->actuator_moment[i * nv + m->jnt_dofadr[j]] = g;
@@ -1116,6 +1135,38 @@ static void o_make_constraint(const OModel* m, OData* d) {
   int nv = m->nv;
   d->nefc[0] = d->ne[0] = d->nf[0] = 0;
   if (m->opt_disableflags & DSBL_CONSTRAINT) return;
+  /* equalities between joints or (fixed) tendons:
+   * (x1 - x1_0) - poly(x2 - x2_0) = 0, poly(0) = data[0]; without a second object the
+   * residual is x1 - x1_0 - data[0] */
+  if (!(m->opt_disableflags & DSBL_EQUALITY))
+    for (int e = 0; e < m->neq; e++) {
+      if (!m->eq_active[e]) continue;
+      int o1 = m->eq_obj1id[e], o2 = m->eq_obj2id[e], tend = m->eq_type[e] == 3;
+      const double* c = m->eq_data + 5 * e;
+      double x1 = tend ? d->ten_length[o1] - m->tendon_length0[o1]
+                       : d->qpos[m->jnt_qposadr[o1]] - m->qpos0[m->jnt_qposadr[o1]];
+      double pos, deriv = 0;
+      if (o2 >= 0) {
+        double x2 = tend ? d->ten_length[o2] - m->tendon_length0[o2]
+                         : d->qpos[m->jnt_qposadr[o2]] - m->qpos0[m->jnt_qposadr[o2]];
+        pos = x1 - (c[0] + x2 * (c[1] + x2 * (c[2] + x2 * (c[3] + x2 * c[4]))));
+        deriv = c[1] + x2 * (2 * c[2] + x2 * (3 * c[3] + x2 * 4 * c[4]));
+      } else pos = x1 - c[0];
+      int r = add_row(m, d, CN_EQUALITY, e, pos, 0, 0);
+      if (r < 0) return;
+      double* J = d->efc_J + (size_t)r * nv;
+      if (tend) {
+        for (int w = m->tendon_adr[o1]; w < m->tendon_adr[o1] + m->tendon_num[o1]; w++)
+          J[m->jnt_dofadr[m->wrap_objid[w]]] += m->wrap_prm[w];
+        if (o2 >= 0)
+          for (int w = m->tendon_adr[o2]; w < m->tendon_adr[o2] + m->tendon_num[o2]; w++)
+            J[m->jnt_dofadr[m->wrap_objid[w]]] -= deriv * m->wrap_prm[w];
+      } else {
+        J[m->jnt_dofadr[o1]] += 1;
+        if (o2 >= 0) J[m->jnt_dofadr[o2]] -= deriv;
+      }
+      d->ne[0]++;
+    }
   /* friction loss */
   if (!(m->opt_disableflags & DSBL_FRICTIONLOSS))
     for (int i = 0; i < nv; i++)
@@ -1198,7 +1249,15 @@ done:
     int type = d->efc_type[r], id = d->efc_id[r];
     const double *solref, *solimp;
     double dA;
-    if (type == CN_FRICTION_DOF) {
+    if (type == CN_EQUALITY) {
+      solref = m->eq_solref + 2 * id; solimp = m->eq_solimp + 5 * id;
+      int o1 = m->eq_obj1id[id], o2 = m->eq_obj2id[id];
+      if (m->eq_type[id] == 3)
+        dA = m->tendon_invweight0[o1] + (o2 >= 0 ? m->tendon_invweight0[o2] : 0);
+      else
+        dA = m->dof_invweight0[m->jnt_dofadr[o1]] +
+             (o2 >= 0 ? m->dof_invweight0[m->jnt_dofadr[o2]] : 0);
+    } else if (type == CN_FRICTION_DOF) {
       solref = m->dof_solref + 2 * id; solimp = m->dof_solimp + 5 * id;
       dA = m->dof_invweight0[id];
     } else if (type == CN_LIMIT_JOINT) {
@@ -1861,6 +1920,7 @@ static int check_array(const OModel* m, OData* d, const double* x, int n, int w)
 static void fwd_position(const OModel* m, OData* d) {
   o_kinematics(m, d);
   o_com_pos(m, d);
+  o_tendon(m, d);
   o_transmission(m, d);
   o_crb(m, d);
   o_factor_m(m, d);
@@ -1874,6 +1934,12 @@ static void fwd_velocity(const OModel* m, OData* d) {
     double v = 0;
     for (int k = 0; k < nv; k++) v += d->actuator_moment[i * nv + k] * d->qvel[k];
     d->actuator_velocity[i] = v;
+  }
+  for (int t = 0; t < m->ntendon; t++) {
+    double v = 0;
+    for (int w = m->tendon_adr[t]; w < m->tendon_adr[t] + m->tendon_num[t]; w++)
+      v += m->wrap_prm[w] * d->qvel[m->jnt_dofadr[m->wrap_objid[w]]];
+    d->ten_velocity[t] = v;
   }
   o_com_vel(m, d);
   o_passive(m, d);

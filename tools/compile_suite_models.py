@@ -13,8 +13,35 @@ from dm_control_b200 import mjcf_compiler as C   # noqa: E402
 
 SUITE = "/root/reference/dm_control/suite"
 DOMAINS = ["cartpole", "acrobot", "pendulum", "cheetah", "walker", "humanoid",
-           "hopper", "reacher", "ball_in_cup", "finger", "swimmer"]
+           "hopper", "reacher", "finger", "swimmer"]
 OUT = os.path.join(ROOT, "dm_control_b200", "suite", "models")
+
+
+def quadruped_xml(floor_size=None, terrain=False, rangefinders=False, walls_and_ball=False):
+  """suite/quadruped.py:52-93 make_model: the same element removals on the XML tree."""
+  import xml.etree.ElementTree as ET
+  root = ET.fromstring(open(os.path.join(SUITE, "quadruped.xml")).read())
+  parent = {c: p for p in root.iter() for c in p}
+
+  def drop(el):
+    parent[el].remove(el)
+
+  def find(tag, name):
+    return next(e for e in root.iter(tag) if e.get("name") == name)
+
+  if floor_size is not None:
+    find("geom", "floor").set("size", "%g %g .5" % (floor_size, floor_size))
+  if not walls_and_ball:
+    for w in ("wall_px", "wall_py", "wall_nx", "wall_ny"):
+      drop(find("geom", w))
+    drop(find("body", "ball"))
+    drop(find("site", "target"))
+  if not terrain:
+    drop(find("geom", "terrain"))
+  if not rangefinders:
+    for rf in list(root.iter("rangefinder")):
+      drop(rf)
+  return ET.tostring(root, encoding="unicode")
 
 
 def main():
@@ -26,5 +53,27 @@ def main():
     print(d, "nq", m.nq, "nv", m.nv, "nbody", m.nbody, "->", os.path.getsize(path), "B")
 
 
+def quadruped():
+  # quadruped.py:96-105 walk (floor 20 * 0.5); run differs only in the floor size, which
+  # no computation depends on (infinite plane)
+  assets = C.compile_file.__globals__  # noqa: F841 (includes resolved relative to SUITE)
+  xml = quadruped_xml(floor_size=10)
+
+  class _Dir(dict):
+    def __contains__(self, k):
+      return os.path.exists(os.path.join(SUITE, k))
+
+    def __getitem__(self, k):
+      with open(os.path.join(SUITE, k)) as f:
+        return f.read()
+
+  m = C.compile_xml(xml, _Dir())
+  path = os.path.join(OUT, "quadruped.npz")
+  m.save(path)
+  print("quadruped nq", m.nq, "nv", m.nv, "nu", m.nu, "na", m.na, "nbody", m.nbody, "ngeom",
+        m.ngeom, "ntendon", m.ntendon, "neq", m.neq, "nsensordata", m.nsensordata)
+
+
 if __name__ == "__main__":
   main()
+  quadruped()
