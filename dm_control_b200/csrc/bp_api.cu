@@ -66,6 +66,10 @@ static void put_i(bp_model* m, const char* n, const std::vector<int32_t>& v) {
   HostField h; h.dtype = 1; h.i = v; if (h.i.empty()) h.i.push_back(0); m->fields[n] = h;
 }
 
+static void put_f(bp_model* m, const char* n, const std::vector<double>& v) {
+  HostField h; h.dtype = 0; h.f = v; if (h.f.empty()) h.f.push_back(0); m->fields[n] = h;
+}
+
 // scalars are refreshed from the host fields (after bp_model_set_field too)
 static int refresh_scalars(bp_model* m) {
   BpModel& M = m->M;
@@ -155,13 +159,33 @@ static int derive(bp_model* m) {
   auto& trntype = I(m, "actuator_trntype");
   auto& jdof = I(m, "jnt_dofadr");
   std::vector<int32_t> aadr(nv + 1, 0), alist;
+  std::vector<double> acoef;
+  auto& gear = F(m, "actuator_gear");
+  auto& tadr = I(m, "tendon_adr");
+  auto& tnum = I(m, "tendon_num");
+  auto& wobj = I(m, "wrap_objid");
+  auto& wprm = F(m, "wrap_prm");
   for (int u = 0; u < M.nu; u++)
-    if (trntype[u] != 0) return fail(BP_EINVAL, "only joint transmissions are supported");
+    if (trntype[u] != 0 && trntype[u] != 3)
+      return fail(BP_EINVAL, "only joint and tendon transmissions are supported");
   for (int d = 0; d < nv; d++) {
     aadr[d] = (int)alist.size();
-    for (int u = 0; u < M.nu; u++) if (jdof[trnid[2 * u]] == d) alist.push_back(u);
+    for (int u = 0; u < M.nu; u++) {
+      if (trntype[u] == 0) {
+        if (jdof[trnid[2 * u]] == d) { alist.push_back(u); acoef.push_back(gear[6 * u]); }
+      } else {
+        int t = trnid[2 * u];
+        double cf = 0; bool hit = false;
+        for (int w = tadr[t]; w < tadr[t] + tnum[t]; w++)
+          if (jdof[wobj[w]] == d) { cf += gear[6 * u] * wprm[w]; hit = true; }
+        if (hit) { alist.push_back(u); acoef.push_back(cf); }
+      }
+    }
   }
   aadr[nv] = (int)alist.size();
+  put_f(m, "dof_actcoef", acoef);
+  M.neq_active = 0;
+  if (M.neq > 0) { auto& ea = I(m, "eq_active"); for (int e = 0; e < M.neq; e++) M.neq_active += ea[e] != 0; }
   put_i(m, "dof_actadr", aadr); put_i(m, "dof_actlist", alist);
   M.need_subtreevel = 0; M.need_rnepost_stage = 0;
   auto& st = I(m, "sensor_type");
@@ -196,6 +220,7 @@ static int upload(bp_model* m) {
 #undef X
 #define X(n) M.n = (const double*)(m->dev + m->fields[#n].dev_off);
   BP_MODEL_F64_ARRAYS(X)
+  BP_MODEL_DERIVED_F64_ARRAYS(X)
 #undef X
   M.body_dofmask = (const unsigned long long*)(m->dev + mask_off);
   return BP_OK;

@@ -167,6 +167,140 @@ static __device__ __noinline__ int bp_collide_cylinder(int t1, const double* p1,
   return 0;
 }
 
+// ---- ellipsoids (MuJoCo: general convex routine; here the closest point directly) --------
+// Point q in the ellipsoid's frame, semi-axes a: the closest surface point is
+// x_i = a_i^2 q_i / (t + a_i^2), t >= 0 the root of F(t) = sum (a_i q_i / (t + a_i^2))^2 - 1
+// (convex and decreasing, so Newton from the left never overshoots).  t carries the
+// multiplier between neighbouring queries.  Returns the distance, 0 inside.
+__device__ __forceinline__ double ell_closest(const double* a, const double* q, double* x, double& t) {
+  double f0 = 0;
+  for (int k = 0; k < 3; k++) f0 += (q[k] / a[k]) * (q[k] / a[k]);
+  if (f0 <= 1) { for (int k = 0; k < 3; k++) x[k] = q[k]; t = 0; return 0; }
+  double tt = t > 0 ? t : 0;
+#pragma unroll 1
+  for (int it = 0; it < 100; it++) {
+    double F = -1, dF = 0;
+    for (int k = 0; k < 3; k++) {
+      double den = tt + a[k] * a[k], r = a[k] * q[k] / den;
+      F += r * r; dF -= 2 * r * r / den;
+    }
+    if (F < 0 && it == 0 && tt > 0) { tt = 0; continue; }
+    double step = -F / dF;
+    tt += step;
+    if (fabs(step) <= 1e-16 * (tt + a[0] * a[0])) break;
+  }
+  double dd = 0;
+  for (int k = 0; k < 3; k++) {
+    x[k] = a[k] * a[k] * q[k] / (tt + a[k] * a[k]);
+    dd += (q[k] - x[k]) * (q[k] - x[k]);
+  }
+  t = tt;
+  return sqrt(dd);
+}
+
+__device__ __forceinline__ int col_sphere_ellipsoid(const double* qw, double rs, const double* p,
+                                                    const double* R, const double* a,
+                                                    double margin, double& tmul, RawCon& o) {
+  double dq[3] = {qw[0] - p[0], qw[1] - p[1], qw[2] - p[2]}, q[3], x[3], nl[3], dist;
+  matT_vec3(q, R, dq);
+  double dd = ell_closest(a, q, x, tmul);
+  if (dd > BP_MINVAL) {
+    for (int k = 0; k < 3; k++) nl[k] = (x[k] - q[k]) / dd;
+    dist = dd - rs;
+  } else {
+    double s = 0;
+    for (int k = 0; k < 3; k++) s += (q[k] / a[k]) * (q[k] / a[k]);
+    s = sqrt(s);
+    double g[3], gl = 0, pen = 0;
+    for (int k = 0; k < 3; k++) {
+      double xs = s > BP_MINVAL ? q[k] / s : (k == 2 ? a[2] : 0.0);
+      g[k] = xs / (a[k] * a[k]); gl += g[k] * g[k];
+      pen += (xs - q[k]) * (xs - q[k]);
+    }
+    gl = sqrt(gl);
+    for (int k = 0; k < 3; k++) nl[k] = -g[k] / gl;
+    dist = -sqrt(pen) - rs;
+  }
+  if (dist > margin) return 0;
+  double nw[3];
+  mat_vec3(nw, R, nl);
+  o.dist = dist;
+  for (int k = 0; k < 3; k++) {
+    o.pos[k] = qw[k] + nw[k] * (rs + 0.5 * dist);
+    o.n[k] = nw[k];
+    o.hint[k] = 0;
+  }
+  return 1;
+}
+
+// slope of the distance from the capsule's segment point to the ellipsoid
+__device__ __forceinline__ double cap_ell_slope(const double* pc, const double* al, double t,
+                                                const double* ac, const double* p, const double* R,
+                                                const double* a, double& tmul) {
+  double dq[3] = {pc[0] + t * ac[0] - p[0], pc[1] + t * ac[1] - p[1], pc[2] + t * ac[2] - p[2]};
+  double q[3], x[3];
+  matT_vec3(q, R, dq);
+  double dd = ell_closest(a, q, x, tmul);
+  if (dd <= BP_MINVAL) return 0;
+  return ((q[0] - x[0]) * al[0] + (q[1] - x[1]) * al[1] + (q[2] - x[2]) * al[2]) / dd;
+}
+
+// Pairs whose second geom is an ellipsoid: plane (support point along -n), sphere
+// (closest point), capsule (the distance along the segment is convex: Illinois regula
+// falsi on its slope, then a sphere at the closest segment point).
+static __device__ __noinline__ int bp_collide_ellipsoid(int t1, const double* p1, const double* z1,
+                                                        const double* s1, const double* p2,
+                                                        const double* R2, const double* a,
+                                                        double margin, RawCon* out) {
+  if (t1 == GEOM_PLANE) {
+    double dl[3], x[3], xw[3], s = 0;
+    matT_vec3(dl, R2, z1);
+    for (int k = 0; k < 3; k++) s += a[k] * a[k] * dl[k] * dl[k];
+    s = sqrt(s);
+    for (int k = 0; k < 3; k++) x[k] = -a[k] * a[k] * dl[k] / s;
+    mat_vec3(xw, R2, x);
+    double dif[3] = {p2[0] + xw[0] - p1[0], p2[1] + xw[1] - p1[1], p2[2] + xw[2] - p1[2]};
+    double dist = dot3(dif, z1);
+    if (dist > margin) return 0;
+    out[0].dist = dist;
+    for (int k = 0; k < 3; k++) {
+      out[0].pos[k] = p2[k] + xw[k] - z1[k] * dist * 0.5;
+      out[0].n[k] = z1[k]; out[0].hint[k] = 0;
+    }
+    return 1;
+  }
+  double tmul = 0;
+  if (t1 == GEOM_SPHERE) return col_sphere_ellipsoid(p1, s1[0], p2, R2, a, margin, tmul, out[0]);
+  if (t1 == GEOM_CAPSULE) {
+    const double l = s1[1];
+    double al[3];
+    matT_vec3(al, R2, z1);
+    double lo = -l, hi = l;
+    double glo = cap_ell_slope(p1, al, lo, z1, p2, R2, a, tmul);
+    double ghi = cap_ell_slope(p1, al, hi, z1, p2, R2, a, tmul);
+    double t;
+    if (glo >= 0) t = lo;
+    else if (ghi <= 0) t = hi;
+    else {
+      int side = 0;
+      t = 0.5 * (lo + hi);
+#pragma unroll 1
+      for (int it = 0; it < 100; it++) {
+        t = (lo * ghi - hi * glo) / (ghi - glo);
+        double g = cap_ell_slope(p1, al, t, z1, p2, R2, a, tmul);
+        if (fabs(g) < 1e-15 || hi - lo < 1e-15 * l) break;
+        if (g > 0) { hi = t; ghi = g; if (side == 1) glo *= 0.5; side = 1; }
+        else { lo = t; glo = g; if (side == -1) ghi *= 0.5; side = -1; }
+      }
+    }
+    double q[3] = {p1[0] + t * z1[0], p1[1] + t * z1[1], p1[2] + t * z1[2]};
+    int n = col_sphere_ellipsoid(q, s1[0], p2, R2, a, margin, tmul, out[0]);
+    if (n) for (int k = 0; k < 3; k++) out[0].hint[k] = z1[k];
+    return n;
+  }
+  return 0;
+}
+
 // Narrowphase of ordered pair (type1 <= type2) on geom poses already copied to
 // registers (p = centre, z = local z axis, R2 = full frame of geom 2 for boxes).
 // Returns the number of raw contacts written to out[0..3].
@@ -176,6 +310,7 @@ static __device__ __noinline__ int bp_collide_prims(int t1, int t2, const double
                                                     const double* R2, const double* s2,
                                                     double margin, RawCon* out) {
   if (t2 == GEOM_CYLINDER) return bp_collide_cylinder(t1, p1, z1, s1, p2, R2, s2, margin, out);
+  if (t2 == GEOM_ELLIPSOID) return bp_collide_ellipsoid(t1, p1, z1, s1, p2, R2, s2, margin, out);
   if (t1 == GEOM_PLANE) {
     if (t2 == GEOM_SPHERE) return col_plane_sphere(p1, z1, p2, s2[0], margin, out[0]);
     if (t2 == GEOM_CAPSULE) {

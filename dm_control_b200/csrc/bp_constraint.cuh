@@ -1,4 +1,4 @@
-// mj_makeConstraint + reference acceleration: rows in the order friction loss,
+// mj_makeConstraint + reference acceleration: rows in the order equality, friction loss,
 // joint limits, contacts.  Row slots come from
 // group prefix sums so row ids are reproducible; Jacobian entries are produced one
 // (contact, dof) pair per lane using per-body dof-ancestry bit masks.
@@ -44,13 +44,36 @@ BP_STAGE void bp_make_constraint(const C& c) {
   if (m.opt_disableflags & DSBL_CONSTRAINT) return;
   int base = 0, nf = 0;
   // ---- pass 1: headers + slots -------------------------------------------------
+  // equalities between joints / fixed tendons: (x1 - x1_0) - poly(x2 - x2_0)
+  if (m.neq_active > 0 && !(m.opt_disableflags & DSBL_EQUALITY)) {
+    for (int e = c.lane; e < m.neq; e += C::G) {
+      if (!m.eq_active[e]) continue;
+      int r = 0;
+      for (int k = 0; k < e; k++) r += m.eq_active[k] != 0;
+      const int o1 = m.eq_obj1id[e], o2 = m.eq_obj2id[e];
+      const bool tend = m.eq_type[e] == 3;
+      const double* cf = m.eq_data + 5 * e;
+      double x1 = tend ? DF(ten_length)[o1] - m.tendon_length0[o1]
+                       : DF(qpos)[m.jnt_qposadr[o1]] - m.qpos0[m.jnt_qposadr[o1]];
+      double pos = x1 - cf[0];
+      if (o2 >= 0) {
+        double x2 = tend ? DF(ten_length)[o2] - m.tendon_length0[o2]
+                         : DF(qpos)[m.jnt_qposadr[o2]] - m.qpos0[m.jnt_qposadr[o2]];
+        pos = x1 - (cf[0] + x2 * (cf[1] + x2 * (cf[2] + x2 * (cf[3] + x2 * cf[4]))));
+      }
+      if (r < njmax) bp_row_header(c, r, CN_EQUALITY, e, pos, 0, 0);
+    }
+    base += m.neq_active;
+  }
+  const int eq_base = base;
+  if (c.lane == 0) IF(ne)[0] = eq_base < njmax ? eq_base : njmax;
   if (!(m.opt_disableflags & DSBL_FRICTIONLOSS)) {
     for (int k = c.lane; k < m.nfric; k += C::G) {
       int r = base + k, i = m.fric_dof[k];
       if (r < njmax) bp_row_header(c, r, CN_FRICTION_DOF, i, 0, 0, m.dof_frictionloss[i]);
     }
     base += m.nfric;
-    nf = base < njmax ? base : njmax;
+    nf = (base < njmax ? base : njmax) - (eq_base < njmax ? eq_base : njmax);
   }
   int lim_base = base;
   if (!(m.opt_disableflags & DSBL_LIMIT)) {
@@ -107,7 +130,29 @@ BP_STAGE void bp_make_constraint(const C& c) {
   // ---- pass 2: Jacobian ----------------------------------------------------------
   for (int w = c.lane; w < nefc * nvp; w += C::G) J[w] = 0;
   SYNC();
-  for (int r = c.lane; r < lim_base && r < nefc; r += C::G) J[r * nvp + IF(efc_id)[r]] = 1;
+  for (int r = c.lane; r < eq_base && r < nefc; r += C::G) {
+    const int e = IF(efc_id)[r], o1 = m.eq_obj1id[e], o2 = m.eq_obj2id[e];
+    const bool tend = m.eq_type[e] == 3;
+    const double* cf = m.eq_data + 5 * e;
+    double deriv = 0;
+    if (o2 >= 0) {
+      double x2 = tend ? DF(ten_length)[o2] - m.tendon_length0[o2]
+                       : DF(qpos)[m.jnt_qposadr[o2]] - m.qpos0[m.jnt_qposadr[o2]];
+      deriv = cf[1] + x2 * (2 * cf[2] + x2 * (3 * cf[3] + x2 * 4 * cf[4]));
+    }
+    if (tend) {
+      for (int w = m.tendon_adr[o1]; w < m.tendon_adr[o1] + m.tendon_num[o1]; w++)
+        J[r * nvp + m.jnt_dofadr[m.wrap_objid[w]]] += m.wrap_prm[w];
+      if (o2 >= 0)
+        for (int w = m.tendon_adr[o2]; w < m.tendon_adr[o2] + m.tendon_num[o2]; w++)
+          J[r * nvp + m.jnt_dofadr[m.wrap_objid[w]]] -= deriv * m.wrap_prm[w];
+    } else {
+      J[r * nvp + m.jnt_dofadr[o1]] += 1;
+      if (o2 >= 0) J[r * nvp + m.jnt_dofadr[o2]] -= deriv;
+    }
+  }
+  for (int r = eq_base + c.lane; r < lim_base && r < nefc; r += C::G)
+    J[r * nvp + IF(efc_id)[r]] = 1;
   // limit rows: the Jacobian entry is -side; a joint with both sides active owns two
   // adjacent rows, lower bound first
   for (int r = lim_base + c.lane; r < con_base && r < nefc; r += C::G) {
@@ -169,7 +214,16 @@ BP_STAGE void bp_make_constraint(const C& c) {
   for (int r = c.lane; r < nefc; r += C::G) {
     int type = IF(efc_type)[r], id = IF(efc_id)[r];
     double solref[2], solimp[5], dA;
-    if (type == CN_FRICTION_DOF) {
+    if (type == CN_EQUALITY) {
+      for (int k = 0; k < 2; k++) solref[k] = m.eq_solref[2 * id + k];
+      for (int k = 0; k < 5; k++) solimp[k] = m.eq_solimp[5 * id + k];
+      const int o1 = m.eq_obj1id[id], o2 = m.eq_obj2id[id];
+      if (m.eq_type[id] == 3)
+        dA = m.tendon_invweight0[o1] + (o2 >= 0 ? m.tendon_invweight0[o2] : 0.0);
+      else
+        dA = m.dof_invweight0[m.jnt_dofadr[o1]] +
+             (o2 >= 0 ? m.dof_invweight0[m.jnt_dofadr[o2]] : 0.0);
+    } else if (type == CN_FRICTION_DOF) {
       for (int k = 0; k < 2; k++) solref[k] = m.dof_solref[2 * id + k];
       for (int k = 0; k < 5; k++) solimp[k] = m.dof_solimp[5 * id + k];
       dA = m.dof_invweight0[id];

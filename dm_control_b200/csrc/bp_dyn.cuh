@@ -121,19 +121,49 @@ BP_STAGE void bp_rne(const C& c, bool with_acc, typename C::DP cacc, typename C:
 }
 
 // joint transmission with scalar joints (the only kind the compiled subset emits)
+// mj_tendon (fixed tendons: length = sum coef * qpos) + mj_transmission
 BP_STAGE void bp_transmission(const C& c) {
   const BpModel& m = c.P.m;
   auto len = DF(actuator_length), qpos = DF(qpos);
-  for (int i = c.lane; i < m.nu; i += C::G)
-    len[i] = m.actuator_gear[6 * i] * qpos[m.jnt_qposadr[m.actuator_trnid[2 * i]]];
+  if (m.ntendon > 0) {
+    auto tl = DF(ten_length);
+    for (int t = c.lane; t < m.ntendon; t += C::G) {
+      double s = 0;
+      for (int w = m.tendon_adr[t]; w < m.tendon_adr[t] + m.tendon_num[t]; w++)
+        s += m.wrap_prm[w] * qpos[m.jnt_qposadr[m.wrap_objid[w]]];
+      tl[t] = s;
+    }
+    SYNC();
+  }
+  for (int i = c.lane; i < m.nu; i += C::G) {
+    int id = m.actuator_trnid[2 * i];
+    len[i] = m.actuator_gear[6 * i] *
+             (m.actuator_trntype[i] == 3 ? DF(ten_length)[id] : qpos[m.jnt_qposadr[id]]);
+  }
   SYNC();
 }
 
 BP_STAGE void bp_actuator_velocity(const C& c) {
   const BpModel& m = c.P.m;
   auto vel = DF(actuator_velocity), qvel = DF(qvel);
-  for (int i = c.lane; i < m.nu; i += C::G)
-    vel[i] = m.actuator_gear[6 * i] * qvel[m.jnt_dofadr[m.actuator_trnid[2 * i]]];
+  for (int t = c.lane; t < m.ntendon; t += C::G) {
+    double s = 0;
+    for (int w = m.tendon_adr[t]; w < m.tendon_adr[t] + m.tendon_num[t]; w++)
+      s += m.wrap_prm[w] * qvel[m.jnt_dofadr[m.wrap_objid[w]]];
+    DF(ten_velocity)[t] = s;
+  }
+  for (int i = c.lane; i < m.nu; i += C::G) {
+    int id = m.actuator_trnid[2 * i];
+    const double g = m.actuator_gear[6 * i];
+    if (m.actuator_trntype[i] == 3) {           // moment row = gear * tendon coefficients
+      double s = 0;
+      for (int w = m.tendon_adr[id]; w < m.tendon_adr[id] + m.tendon_num[id]; w++)
+        s += g * m.wrap_prm[w] * qvel[m.jnt_dofadr[m.wrap_objid[w]]];
+      vel[i] = s;
+    } else {
+      vel[i] = g * qvel[m.jnt_dofadr[id]];
+    }
+  }
   SYNC();
 }
 
@@ -189,7 +219,7 @@ BP_STAGE void bp_fwd_actuation(const C& c) {
     double s = 0;
     for (int k = m.dof_actadr[d]; k < m.dof_actadr[d + 1]; k++) {
       int u = m.dof_actlist[k];
-      s += m.actuator_gear[6 * u] * force[u];
+      s += m.dof_actcoef[k] * force[u];
     }
     qa[d] = s;
   }

@@ -546,8 +546,8 @@ __device__ __forceinline__ double bp_newton_grad(const C& c) {
 // H = M + J^T D_active J;  Mgrad = H^-1 grad  (grad from bp_newton_grad)
 //
 // The Hessian is assembled from the structure of J instead of a dense triple loop:
-// friction-loss and limit rows (the first `nsingle` rows) have one non-zero, +-1, and
-// add their weight to one diagonal entry; the rows of a contact are non-zero only on
+// friction-loss and limit rows (`nsingle` rows after the equalities) have one non-zero,
+// +-1, and add their weight to one diagonal entry; the rows of a contact are non-zero only on
 // the dofs that move its two bodies (body_dofmask), so a contact updates the
 // k (k + 1) / 2 entries of that dof set, split over the lanes by outer dof.
 BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refactor) {
@@ -566,12 +566,24 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refacto
   bp_copy(c, H, Md, ntri);
   for (int i = c.lane; i < nv; i += C::G) H[ntri + i] = grad[i];     // bordered rhs row
   SYNC();
+  const int ne = IF(ne)[0];
 #pragma unroll 1
   for (int i = c.lane; i < nv; i += C::G) {
     double acc = 0;
-    for (int r = 0; r < nsingle; r++)
+    for (int r = ne; r < ne + nsingle; r++)
       if ((int)rdof[r] == i) acc += rw[r];
     if (acc != 0) H[PK(i, i)] += acc;
+    // equality rows (the first ne): a few non-zeros each, row i of the lower triangle
+#pragma unroll 1
+    for (int r = 0; r < ne; r++) {
+      const double ji = J[r * nvp + i];
+      if (ji == 0) continue;
+      const double w = rw[r] * ji;
+      for (int j = 0; j <= i; j++) {
+        const double jj = J[r * nvp + j];
+        if (jj != 0) H[PK(i, j)] += w * jj;
+      }
+    }
   }
   SYNC();
   const int ncon = IF(ncon)[0];

@@ -39,7 +39,7 @@ enum { BP_MODE_STEP = 0, BP_MODE_FORWARD = 1, BP_MODE_STEP1 = 2,
 // ---- model fields that arrive in the blob (dm_control_b200/model.py) ----------
 #define BP_MODEL_INT_SCALARS(X) \
   X(nq) X(nv) X(nu) X(na) X(nbody) X(njnt) X(ngeom) X(nsite) X(nM) X(npair) \
-  X(nconmax) X(njmax) X(nsensor) X(nsensordata) X(nkey) \
+  X(nconmax) X(njmax) X(nsensor) X(nsensordata) X(nkey) X(ntendon) X(neq) \
   X(opt_integrator) X(opt_cone) X(opt_solver) X(opt_iterations) \
   X(opt_ls_iterations) X(opt_disableflags) X(opt_enableflags)
 #define BP_MODEL_F64_SCALARS(X) \
@@ -54,7 +54,8 @@ enum { BP_MODE_STEP = 0, BP_MODE_FORWARD = 1, BP_MODE_STEP1 = 2,
   X(actuator_trntype) X(actuator_dyntype) X(actuator_gaintype) \
   X(actuator_biastype) X(actuator_trnid) X(actuator_ctrllimited) \
   X(actuator_forcelimited) X(sensor_type) X(sensor_objtype) X(sensor_objid) \
-  X(sensor_dim) X(sensor_adr) X(sensor_needstage)
+  X(sensor_dim) X(sensor_adr) X(sensor_needstage) X(tendon_adr) X(tendon_num) \
+  X(wrap_objid) X(eq_type) X(eq_obj1id) X(eq_obj2id) X(eq_active)
 #define BP_MODEL_F64_ARRAYS(X) \
   X(opt_gravity) X(body_pos) X(body_quat) X(body_ipos) X(body_iquat) \
   X(body_mass) X(body_subtreemass) X(body_inertia) X(body_invweight0) \
@@ -66,7 +67,8 @@ enum { BP_MODE_STEP = 0, BP_MODE_FORWARD = 1, BP_MODE_STEP1 = 2,
   X(site_pos) X(site_quat) X(site_size) X(qpos0) X(qpos_spring) \
   X(actuator_dynprm) X(actuator_gainprm) X(actuator_biasprm) \
   X(actuator_ctrlrange) X(actuator_forcerange) X(actuator_gear) \
-  X(sensor_cutoff)
+  X(sensor_cutoff) X(wrap_prm) X(tendon_length0) X(tendon_invweight0) X(eq_solref) \
+  X(eq_solimp) X(eq_data)
 // ---- arrays derived on the host when the model is created (bp_api.cu) ---------
 //   body_level_*: bodies grouped by tree depth (parents complete before children)
 //   body_child_*: children of each body, DESCENDING id (the accumulation order of a
@@ -79,6 +81,9 @@ enum { BP_MODE_STEP = 0, BP_MODE_FORWARD = 1, BP_MODE_STEP1 = 2,
   X(body_level_adr) X(body_level_list) X(body_child_adr) X(body_child_list) \
   X(dof_depth) X(M_col) X(dof_level_adr) X(dof_level_list) X(fric_dof) \
   X(lim_jnt) X(tri_i) X(tri_j) X(dof_actadr) X(dof_actlist)
+//   dof_actcoef: moment of actuator dof_actlist[k] on its dof (gear, times the tendon
+//                coefficient for tendon transmissions)
+#define BP_MODEL_DERIVED_F64_ARRAYS(X) X(dof_actcoef)
 
 struct BpModel {
 #define X(n) int n;
@@ -93,9 +98,10 @@ struct BpModel {
 #undef X
 #define X(n) const double* n;
   BP_MODEL_F64_ARRAYS(X)
+  BP_MODEL_DERIVED_F64_ARRAYS(X)
 #undef X
   const unsigned long long* body_dofmask;  // bit i set <=> dof i moves the body
-  int nlevel, ndoflevel, nfric, nlim, ntri, nvp;  // nvp: odd row stride >= nv
+  int nlevel, ndoflevel, nfric, nlim, ntri, nvp, neq_active;  // nvp: odd row stride >= nv
   int any_damping, need_subtreevel, need_rnepost_stage;  // sensor prerequisites
 };
 
@@ -117,6 +123,7 @@ struct BpModel {
   X(qfrc_bias, m.nv) X(qfrc_passive, m.nv) X(qfrc_actuator, m.nv) \
   X(qfrc_smooth, m.nv) X(qacc_smooth, m.nv) X(qfrc_constraint, m.nv) \
   X(actuator_length, m.nu) X(actuator_velocity, m.nu) X(actuator_force, m.nu) \
+  X(ten_length, m.ntendon) X(ten_velocity, m.ntendon) \
   X(sensordata, m.nsensordata) X(efc_J, njmax * m.nvp) X(efc_pos, njmax) \
   X(efc_margin, njmax) X(efc_frictionloss, njmax) X(efc_diagApprox, njmax) \
   X(efc_KBIP, 4 * njmax) X(efc_D, njmax) X(efc_R, njmax) X(efc_vel, njmax) \

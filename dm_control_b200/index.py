@@ -26,6 +26,7 @@ DATA_AXES = {
     "qLDiagInv": ("nv", None), "act": ("na", None), "act_dot": ("na", None),
     "ctrl": ("nu", None), "actuator_length": ("nu", None),
     "actuator_velocity": ("nu", None), "actuator_force": ("nu", None),
+    "ten_length": ("ntendon", None), "ten_velocity": ("ntendon", None),
     "xpos": ("nbody", "xyz"), "xquat": ("nbody", "quat"), "xmat": ("nbody", "mat"),
     "xipos": ("nbody", "xyz"), "ximat": ("nbody", "mat"),
     "subtree_com": ("nbody", "xyz"), "subtree_linvel": ("nbody", "xyz"),
@@ -90,6 +91,7 @@ def make_axes(model):
   axes["nsite"] = Axis(names["site"])
   axes["nu"] = Axis(names["actuator"])
   axes["nsensor"] = Axis(names["sensor"])
+  axes["ntendon"] = Axis(names["tendon"])
   if model.njnt:
     axes["nq"] = Axis(jn, np.diff(np.r_[model.jnt_qposadr, model.nq]))
     axes["nv"] = Axis(jn, np.diff(np.r_[model.jnt_dofadr, model.nv]))

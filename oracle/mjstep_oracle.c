@@ -908,6 +908,137 @@ static int col_capsule_cylinder_raw(const double* pc, const double* ac, double r
   return n;
 }
 
+/* ---- ellipsoids.  MuJoCo sends these pairs through its general convex routine (MPR,
+ * tolerance 1e-6); here the closest point is computed directly.  Point q in the
+ * ellipsoid's frame, semi-axes a: the closest surface point is x_i = a_i^2 q_i / (t + a_i^2)
+ * with t >= 0 the root of F(t) = sum (a_i q_i / (t + a_i^2))^2 - 1 (convex, decreasing:
+ * Newton from the left never overshoots).  *t carries the multiplier in and out so that
+ * neighbouring queries start close.  Returns the distance, 0 if q is inside. */
+static double ell_closest(const double* a, const double* q, double* x, double* t) {
+  double f0 = 0;
+  for (int k = 0; k < 3; k++) f0 += (q[k] / a[k]) * (q[k] / a[k]);
+  if (f0 <= 1) { for (int k = 0; k < 3; k++) x[k] = q[k]; *t = 0; return 0; }
+  double tt = *t > 0 ? *t : 0;
+  for (int it = 0; it < 100; it++) {
+    double F = -1, dF = 0;
+    for (int k = 0; k < 3; k++) {
+      double den = tt + a[k] * a[k], r = a[k] * q[k] / den;
+      F += r * r; dF -= 2 * r * r / den;
+    }
+    if (F < 0 && it == 0 && tt > 0) { tt = 0; continue; }   /* warm start overshot: restart */
+    double step = -F / dF;
+    tt += step;
+    if (fabs(step) <= 1e-16 * (tt + a[0] * a[0])) break;
+  }
+  double dd = 0;
+  for (int k = 0; k < 3; k++) {
+    x[k] = a[k] * a[k] * q[k] / (tt + a[k] * a[k]);
+    dd += (q[k] - x[k]) * (q[k] - x[k]);
+  }
+  *t = tt;
+  return sqrt(dd);
+}
+
+/* sphere (world centre qw, radius rs; geom1) against an ellipsoid (geom2: centre p, frame
+ * R row-major, semi-axes a) */
+static int col_sphere_ellipsoid_raw(const double* qw, double rs, const double* p,
+                                    const double* R, const double* a, double margin,
+                                    double* tmul, RawCon* out) {
+  double dq[3] = {qw[0] - p[0], qw[1] - p[1], qw[2] - p[2]}, q[3], x[3], nl[3], dist;
+  matT_vec3(q, R, dq);
+  double dd = ell_closest(a, q, x, tmul);
+  if (dd > MINVAL) {
+    for (int k = 0; k < 3; k++) nl[k] = (x[k] - q[k]) / dd;       /* sphere -> ellipsoid */
+    dist = dd - rs;
+  } else {
+    /* centre inside: pushed out along the surface normal of the radially scaled point */
+    double s = 0;
+    for (int k = 0; k < 3; k++) s += (q[k] / a[k]) * (q[k] / a[k]);
+    s = sqrt(s);
+    double g[3], gl = 0, pen = 0;
+    for (int k = 0; k < 3; k++) {
+      double xs = s > MINVAL ? q[k] / s : (k == 2 ? a[2] : 0);
+      g[k] = xs / (a[k] * a[k]); gl += g[k] * g[k];
+      pen += (xs - q[k]) * (xs - q[k]);
+    }
+    gl = sqrt(gl);
+    for (int k = 0; k < 3; k++) nl[k] = -g[k] / gl;
+    dist = -sqrt(pen) - rs;
+  }
+  if (dist > margin) return 0;
+  double nw[3];
+  mat_vec3(nw, R, nl);
+  out->dist = dist;
+  for (int k = 0; k < 3; k++) {
+    out->pos[k] = qw[k] + nw[k] * (rs + 0.5 * dist);
+    out->frame[k] = nw[k];
+  }
+  memset(out->frame + 3, 0, 48);
+  return 1;
+}
+
+/* capsule (geom1) against an ellipsoid: the distance from the segment point pc + t ac to
+ * the ellipsoid is convex in t; its derivative g(t) = n(t) . ac is driven to zero by the
+ * Illinois variant of regula falsi on [-l, l], then the point is handled as a sphere */
+static double cap_ell_slope(const double* pc, const double* ac, double t, const double* p,
+                            const double* R, const double* a, double* tmul) {
+  double dq[3] = {pc[0] + t * ac[0] - p[0], pc[1] + t * ac[1] - p[1], pc[2] + t * ac[2] - p[2]};
+  double q[3], x[3], al[3];
+  matT_vec3(q, R, dq);
+  matT_vec3(al, R, ac);
+  double dd = ell_closest(a, q, x, tmul);
+  if (dd <= MINVAL) return 0;
+  return ((q[0] - x[0]) * al[0] + (q[1] - x[1]) * al[1] + (q[2] - x[2]) * al[2]) / dd;
+}
+
+static int col_capsule_ellipsoid_raw(const double* pc, const double* ac, double rc, double l,
+                                     const double* p, const double* R, const double* a,
+                                     double margin, RawCon* out) {
+  double tmul = 0, lo = -l, hi = l;
+  double glo = cap_ell_slope(pc, ac, lo, p, R, a, &tmul);
+  double ghi = cap_ell_slope(pc, ac, hi, p, R, a, &tmul);
+  double t;
+  if (glo >= 0) t = lo;
+  else if (ghi <= 0) t = hi;
+  else {
+    int side = 0;
+    t = 0.5 * (lo + hi);
+    for (int it = 0; it < 100; it++) {
+      t = (lo * ghi - hi * glo) / (ghi - glo);
+      double g = cap_ell_slope(pc, ac, t, p, R, a, &tmul);
+      if (fabs(g) < 1e-15 || hi - lo < 1e-15 * l) break;
+      if (g > 0) { hi = t; ghi = g; if (side == 1) glo *= 0.5; side = 1; }
+      else { lo = t; glo = g; if (side == -1) ghi *= 0.5; side = -1; }
+    }
+  }
+  double q[3] = {pc[0] + t * ac[0], pc[1] + t * ac[1], pc[2] + t * ac[2]};
+  int n = col_sphere_ellipsoid_raw(q, rc, p, R, a, margin, &tmul, out);
+  if (n) memcpy(out->frame + 3, ac, 24);
+  return n;
+}
+
+/* plane against an ellipsoid: the support point of the ellipsoid along -n */
+static int col_plane_ellipsoid_raw(const double* ppos, const double* n, const double* p,
+                                   const double* R, const double* a, double margin,
+                                   RawCon* out) {
+  double dl[3], x[3], xw[3], s = 0;
+  matT_vec3(dl, R, n);
+  for (int k = 0; k < 3; k++) s += a[k] * a[k] * dl[k] * dl[k];
+  s = sqrt(s);
+  for (int k = 0; k < 3; k++) x[k] = -a[k] * a[k] * dl[k] / s;
+  mat_vec3(xw, R, x);
+  double dif[3] = {p[0] + xw[0] - ppos[0], p[1] + xw[1] - ppos[1], p[2] + xw[2] - ppos[2]};
+  double dist = dot3(dif, n);
+  if (dist > margin) return 0;
+  out->dist = dist;
+  for (int k = 0; k < 3; k++) {
+    out->pos[k] = p[k] + xw[k] - n[k] * dist * 0.5;
+    out->frame[k] = n[k];
+  }
+  memset(out->frame + 3, 0, 48);
+  return 1;
+}
+
 static int collide_pair(const OModel* m, const OData* d, int g1, int g2,
                         double margin, RawCon* out) {
   int t1 = m->geom_type[g1], t2 = m->geom_type[g2];
@@ -931,6 +1062,7 @@ static int collide_pair(const OModel* m, const OData* d, int g1, int g2,
       }
       return cnt;
     }
+    if (t2 == GEOM_ELLIPSOID) return col_plane_ellipsoid_raw(p1, n, p2, R2, s2, margin, out);
     if (t2 == GEOM_CYLINDER) return col_plane_cylinder_raw(p1, n, p2, R2, s2, margin, out);
     if (t2 == GEOM_BOX) {
       double dif[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
@@ -964,6 +1096,15 @@ static int collide_pair(const OModel* m, const OData* d, int g1, int g2,
     x = x < -s2[1] ? -s2[1] : (x > s2[1] ? s2[1] : x);
     double c[3] = {p2[0] + ax[0] * x, p2[1] + ax[1] * x, p2[2] + ax[2] * x};
     return col_sphere_sphere_raw(p1, s1[0], c, s2[0], margin, out);
+  }
+  if (t2 == GEOM_ELLIPSOID && t1 == GEOM_SPHERE) {
+    double tmul = 0;
+    return col_sphere_ellipsoid_raw(p1, s1[0], p2, R2, s2, margin, &tmul, out);
+  }
+  if (t2 == GEOM_ELLIPSOID && t1 == GEOM_CAPSULE) {
+    double a1[3];
+    geom_axis(R1, 2, a1);
+    return col_capsule_ellipsoid_raw(p1, a1, s1[0], s1[1], p2, R2, s2, margin, out);
   }
   if (t2 == GEOM_CYLINDER && (t1 == GEOM_SPHERE || t1 == GEOM_CAPSULE || t1 == GEOM_CYLINDER)) {
     double a2[3], a1[3];

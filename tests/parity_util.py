@@ -28,7 +28,8 @@ EFC_F64 = ["efc_pos", "efc_margin", "efc_frictionloss", "efc_diagApprox", "efc_D
 EFC_I32 = ["efc_type", "efc_id", "efc_state"]
 CON_F64 = [("contact_dist", 1), ("contact_pos", 3), ("contact_frame", 9)]
 CON_I32 = ["contact_geom1", "contact_geom2", "contact_dim", "contact_efc_address"]
-INT_SCALARS = ["ncon", "nefc", "nf", "solver_iter", "warning"]
+INT_SCALARS = ["ncon", "nefc", "ne", "nf", "solver_iter", "warning"]
+TENDON_F64 = ["ten_length", "ten_velocity"]
 
 
 def load_model(domain):
@@ -104,6 +105,9 @@ def compare_env(cmp, m, oracle, gpu, e, nvp, skip=()):
     cmp.add_f64(name, gpu[name][e], getattr(oracle, name))
   for name in INT_SCALARS:
     cmp.add_int(name, gpu[name][e], getattr(oracle, name))
+  if m.ntendon:
+    for name in TENDON_F64:
+      cmp.add_f64(name, gpu[name][e], getattr(oracle, name))
   nefc, ncon = int(oracle.nefc[0]), int(oracle.ncon[0])
   if int(gpu["nefc"][e, 0]) == nefc and int(gpu["ncon"][e, 0]) == ncon:
     for name in EFC_F64:
@@ -140,7 +144,7 @@ def run_parity(domain, nenv=32, nsteps=3, seed=0, njmax=0, nconmax=0, check_step
     o.qpos[:] = qpos[e]; o.qvel[:] = qvel[e]; o.ctrl[:] = ctrl[e]
     oracles.append(o)
   names = (F64_FIELDS + EFC_F64 + EFC_I32 + ["efc_J"] + [n for n, _ in CON_F64] +
-           CON_I32 + INT_SCALARS)
+           CON_I32 + INT_SCALARS + (TENDON_F64 if m.ntendon else []))
   out = {}
   check_steps = set(range(nsteps + 1)) if check_steps is None else set(check_steps)
   stats = {"ncon": [], "nefc": [], "iter": []}

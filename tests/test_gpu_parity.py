@@ -18,6 +18,7 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-8
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 HUMANOID_SIZES = dict(njmax=120, nconmax=40)
+SIZES = {"humanoid": HUMANOID_SIZES, "quadruped": dict(njmax=120, nconmax=40)}
 
 
 def _assert_parity(res):
@@ -28,10 +29,10 @@ def _assert_parity(res):
 
 
 @pytest.mark.parametrize("domain", ["pendulum", "cartpole", "acrobot", "cheetah", "walker",
-                                    "hopper", "finger", "humanoid"])
+                                    "hopper", "finger", "humanoid", "quadruped"])
 @pytest.mark.parametrize("lanes", [32, 8, 4, 1])
 def test_every_field_matches_oracle(domain, lanes):
-  kw = HUMANOID_SIZES if domain == "humanoid" else {}
+  kw = SIZES.get(domain, {})
   # finger (elliptic cones, friction loss): more envs, a tenth of the random states touch
   nenv = 160 if domain == "finger" else 48
   res, stats = PU.run_parity(domain, nenv=nenv, nsteps=10, seed=5, check_steps=[0, 1, 2, 10],
@@ -39,7 +40,7 @@ def test_every_field_matches_oracle(domain, lanes):
   _assert_parity(res)
   if domain == "finger":
     assert max(stats["ncon"]) > 0.05
-  if domain in ("cheetah", "walker", "hopper", "humanoid"):
+  if domain in ("cheetah", "walker", "hopper", "humanoid", "quadruped"):
     assert max(stats["ncon"]) > 0.5 and max(stats["iter"]) > 0.5     # contacts exercised
 
 
