@@ -54,6 +54,8 @@ _SIGNATURES = {
     "bp_field_copy_device": (_i32, [_vp, ctypes.c_char_p, _vp, _i32]),
     "bp_fp64_peak": (_i32, [_i32, ctypes.POINTER(ctypes.c_double)]),
     "bp_set_mask": (_i32, [_vp, _vp]),
+    "bp_hfield_write": (_i32, [_vp, _vp, _i64, _i64]),
+    "bp_hfield_read": (_i32, [_vp, _vp, _i64, _i64]),
     "bp_step": (_i32, [_vp, _i32]),
     "bp_mj_step": (_i32, [_vp, _i32]),
     "bp_forward": (_i32, [_vp, _i32]),
@@ -201,6 +203,18 @@ class Batch:
     a = a.reshape(-1, cnt)
     if cnt:
       check(load().bp_field_write(self.ptr, name.encode(), _ptr(a), env0, a.shape[0]))
+
+  def write_hfield(self, data, env0=0):
+    """Per-env `model.hfield_data` (quadruped.py:381): data [n, nhfielddata] float32."""
+    a = np.ascontiguousarray(data, dtype=np.float32)
+    a = a.reshape(-1, int(self.model.flat.nhfielddata))
+    check(load().bp_hfield_write(self.ptr, _ptr(a), env0, a.shape[0]))
+
+  def read_hfield(self, env0=0, n=None):
+    n = self.nenv - env0 if n is None else n
+    out = np.empty((n, int(self.model.flat.nhfielddata)), dtype=np.float32)
+    check(load().bp_hfield_read(self.ptr, _ptr(out), env0, n))
+    return out
 
   # ---- zero-copy device views ---------------------------------------------------
   def view(self, name):

@@ -320,6 +320,7 @@ struct bp_batch {
   int64_t stride = 0, nenv_alloc = 0;
   void* stage = nullptr;           // dense staging buffer for host <-> image copies
   size_t stage_bytes = 0;
+  float* hfield = nullptr;         // [nenv_alloc][nhfielddata] per-env elevation data
   BpTask task;
 };
 
@@ -389,6 +390,24 @@ extern "C" bp_batch* bp_batch_create(bp_model* m, int64_t nenv, int njmax, int n
   }
   cudaMemsetAsync(b->image, 0, bytes, b->stream);
   cudaMemsetAsync(b->mask, 1, nenv, b->stream);
+  if (m->M.nhfielddata > 0) {
+    // every env starts from the model's elevation data (mjModel.hfield_data is float32)
+    size_t nh = (size_t)m->M.nhfielddata;
+    std::vector<float> h0(nh);
+    auto& src = m->fields["hfield_data"].f;
+    for (size_t i = 0; i < nh; i++) h0[i] = (float)src[i];
+    if (cudaMalloc((void**)&b->hfield, (size_t)b->nenv_alloc * nh * 4) != cudaSuccess) {
+      cudaFree(b->image); cudaFree(b->mask);
+      delete b; return bail("device allocation of the height-field data failed");
+    }
+    bool zero = true;
+    for (float v : h0) if (v != 0) zero = false;
+    if (zero) cudaMemsetAsync(b->hfield, 0, (size_t)b->nenv_alloc * nh * 4, b->stream);
+    else
+      for (int64_t e = 0; e < b->nenv_alloc; e++)
+        cudaMemcpyAsync(b->hfield + e * nh, h0.data(), nh * 4, cudaMemcpyHostToDevice, b->stream);
+    cudaStreamSynchronize(b->stream);
+  }
   bp_reset(b, -1);
   cudaStreamSynchronize(b->stream);
   return b;
@@ -399,6 +418,7 @@ extern "C" void bp_batch_free(bp_batch* b) {
   cudaSetDevice(b->model->device);
   if (b->stream) { cudaStreamSynchronize(b->stream); cudaStreamDestroy(b->stream); }
   cudaFree(b->image); cudaFree(b->mask);
+  if (b->hfield) cudaFree(b->hfield);
   if (b->ctrl_stage) cudaFree(b->ctrl_stage);
   if (b->stage) cudaFree(b->stage);
   if (b->obs_dev) cudaFree(b->obs_dev);
@@ -525,7 +545,29 @@ static BpParams make_params(bp_batch* b, int mode, int nsub, int disable_actuati
   P.mask = b->use_mask ? b->mask : nullptr;
   P.nenv = b->nenv; P.mode = mode; P.nsub = nsub; P.disable_actuation = disable_actuation;
   P.stride = b->stride; P.interleave = b->interleave; P.lanes = b->lanes;
+  P.hfield = b->hfield;
   return P;
+}
+
+// per-env model data: elevation of every height field of envs [env0, env0 + n)
+static int hfield_copy(bp_batch* b, float* host, int64_t env0, int64_t n, bool to_device) {
+  if (!b || !host) return fail(BP_EINVAL, "null argument");
+  if (!b->hfield) return fail(BP_ENOFIELD, "the model has no height field");
+  if (env0 < 0 || n < 0 || env0 + n > b->nenv) return fail(BP_EINVAL, "env range out of bounds");
+  cudaSetDevice(b->model->device);
+  size_t nh = (size_t)b->model->M.nhfielddata;
+  if (to_device) CUDA_OK(cudaMemcpyAsync(b->hfield + env0 * nh, host, (size_t)n * nh * 4,
+                                         cudaMemcpyHostToDevice, b->stream));
+  else CUDA_OK(cudaMemcpyAsync(host, b->hfield + env0 * nh, (size_t)n * nh * 4,
+                               cudaMemcpyDeviceToHost, b->stream));
+  CUDA_OK(cudaStreamSynchronize(b->stream));
+  return BP_OK;
+}
+extern "C" int bp_hfield_write(bp_batch* b, const float* host, int64_t env0, int64_t n) {
+  return hfield_copy(b, (float*)host, env0, n, true);
+}
+extern "C" int bp_hfield_read(bp_batch* b, float* host, int64_t env0, int64_t n) {
+  return hfield_copy(b, host, env0, n, false);
 }
 
 static int launch(bp_batch* b, int mode, int nsub, int disable_actuation,

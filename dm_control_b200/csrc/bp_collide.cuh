@@ -4,8 +4,7 @@
 #ifndef BP_COLLIDE_CUH_
 #define BP_COLLIDE_CUH_
 #include "bp_math.cuh"
-
-struct RawCon { double dist, pos[3], n[3], hint[3]; };
+#include "bp_hfield.cuh"
 
 __device__ __forceinline__ int col_plane_sphere(const double* ppos, const double* pn,
                                                 const double* ctr, double r,
@@ -381,6 +380,76 @@ static __device__ __noinline__ int bp_collide_prims(int t1, int t2, const double
   return 0;
 }
 
+// geom (type gt, centre gp, frame gR row-major, sizes gs; all in the field's frame) against
+// one triangle; returns the number of contacts written (at most 4), normals pointing from
+// the terrain to the geom.  sphere: closest point of the triangle (face always, edge /
+// vertex when owned); capsule: both end spheres + the segment's interior against the owned
+// edges; ellipsoid, cylinder: support point(s) along -n against the face + the owned vertex
+// against the solid.
+static __device__ __noinline__ int hf_tri_geom(int half, const double* a, const double* b,
+                                               const double* c, int gt, const double* gp,
+                                               const double* gR, const double* gs, double margin,
+                                               RawCon* out) {
+  double ab[3], ac[3], nt[3];
+  for (int k = 0; k < 3; k++) { ab[k] = b[k] - a[k]; ac[k] = c[k] - a[k]; }
+  cross3(nt, ab, ac);
+  normalize3(nt);
+  int n = 0;
+  if (gt == GEOM_SPHERE)
+    return hf_sphere_tri(half, a, b, c, nt, gp, gs[0], margin, nullptr, out[0]);
+  if (gt == GEOM_CAPSULE) {
+    double ax[3] = {gR[2], gR[5], gR[8]}, e[3];
+#pragma unroll 1
+    for (int sgn = 1; sgn >= -1; sgn -= 2) {
+      for (int k = 0; k < 3; k++) e[k] = gp[k] + sgn * ax[k] * gs[1];
+      n += hf_sphere_tri(half, a, b, c, nt, e, gs[0], margin, ax, out[n]);
+    }
+    if (half == 0) n += hf_capsule_edge(gp, ax, gs[1], gs[0], a, b, 1, margin, out[n]);
+    n += hf_capsule_edge(gp, ax, gs[1], gs[0], c, a, 0, margin, out[n]);
+    return n;
+  }
+  if (gt == GEOM_ELLIPSOID) {
+    double dl[3], x[3], xw[3], s = 0;
+    matT_vec3(dl, gR, nt);
+    for (int k = 0; k < 3; k++) s += gs[k] * gs[k] * dl[k] * dl[k];
+    s = sqrt(s);
+    for (int k = 0; k < 3; k++) x[k] = -gs[k] * gs[k] * dl[k] / s;
+    mat_vec3(xw, gR, x);
+    for (int k = 0; k < 3; k++) xw[k] += gp[k];
+    n += hf_point_face(a, b, c, nt, xw, margin, out[n]);
+    if (half == 0) {
+      double tmul = 0;
+      n += col_sphere_ellipsoid(a, 0.0, gp, gR, gs, margin, tmul, out[n]);
+    }
+    return n;
+  }
+  if (gt == GEOM_CYLINDER) {
+    double axis[3] = {gR[2], gR[5], gR[8]}, vec[3], x[3];
+    double prj = dot3(nt, axis);
+    for (int k = 0; k < 3; k++) vec[k] = axis[k] * prj - nt[k];
+    double len = norm3(vec);
+    if (len >= BP_MINVAL) { for (int k = 0; k < 3; k++) vec[k] *= gs[0] / len; }
+    else { vec[0] = gR[0] * gs[0]; vec[1] = gR[3] * gs[0]; vec[2] = gR[6] * gs[0]; }
+#pragma unroll 1
+    for (int sgn = 1; sgn >= -1; sgn -= 2) {
+      for (int k = 0; k < 3; k++) x[k] = gp[k] + vec[k] + sgn * axis[k] * gs[1];
+      n += hf_point_face(a, b, c, nt, x, margin, out[n]);
+    }
+    if (half == 0) n += col_sphere_cylinder(a, 0.0, gp, axis, gs[0], gs[1], margin, out[n]);
+    return n;
+  }
+  return 0;
+}
+
+// cells of the grid under [lo, hi] along one axis: first cell and one past the last
+__device__ __forceinline__ void hf_range(double lo, double hi, double rad, double dd, int nn,
+                                         int& i0, int& i1) {
+  double f0 = floor((lo + rad) / dd), f1 = ceil((hi + rad) / dd);
+  if (f0 < 0) f0 = 0;
+  if (f1 > nn - 1) f1 = nn - 1;
+  i0 = (int)f0; i1 = (int)f1;
+}
+
 // frame rows: normal, tangent 1 (from the hint or a default axis), tangent 2
 __device__ __forceinline__ void make_frame(double* f) {
   normalize3(f);
@@ -394,6 +463,40 @@ __device__ __forceinline__ void make_frame(double* f) {
   cross3(f + 6, f, f + 3);
 }
 
+BP_STAGE void bp_write_contact(const C& c, int id, int g1, int g2, double margin, double gap,
+                               const RawCon& raw) {
+  const BpModel& m = c.P.m;
+  double f[9];
+  for (int k = 0; k < 3; k++) { f[k] = raw.n[k]; f[3 + k] = raw.hint[k]; f[6 + k] = 0; }
+  make_frame(f);
+  DF(contact_dist)[id] = raw.dist;
+  for (int k = 0; k < 3; k++) DF(contact_pos)[3 * id + k] = raw.pos[k];
+  for (int k = 0; k < 9; k++) DF(contact_frame)[9 * id + k] = f[k];
+  double inc = margin - gap;
+  DF(contact_includemargin)[id] = inc;
+  IF(contact_geom1)[id] = g1; IF(contact_geom2)[id] = g2;
+  int d1 = m.geom_condim[g1], d2 = m.geom_condim[g2];
+  IF(contact_dim)[id] = d1 > d2 ? d1 : d2;
+  const double *f1 = m.geom_friction + 3 * g1, *f2 = m.geom_friction + 3 * g2;
+  double fr[3];
+  for (int k = 0; k < 3; k++) fr[k] = fmax(f1[k], f2[k]);
+  auto cf = DF(contact_friction) + 5 * id;
+  cf[0] = fr[0]; cf[1] = fr[0]; cf[2] = fr[1]; cf[3] = fr[2]; cf[4] = fr[2];
+  double mix1 = m.geom_solmix[g1], mix2 = m.geom_solmix[g2], mix;
+  if (mix1 >= BP_MINVAL && mix2 >= BP_MINVAL) mix = mix1 / (mix1 + mix2);
+  else if (mix1 < BP_MINVAL && mix2 < BP_MINVAL) mix = 0.5;
+  else mix = mix1 < BP_MINVAL ? 0.0 : 1.0;
+  for (int k = 0; k < 2; k++)
+    DF(contact_solref)[2 * id + k] =
+        mix * m.geom_solref[2 * g1 + k] + (1 - mix) * m.geom_solref[2 * g2 + k];
+  for (int k = 0; k < 5; k++)
+    DF(contact_solimp)[5 * id + k] =
+        mix * m.geom_solimp[5 * g1 + k] + (1 - mix) * m.geom_solimp[5 * g2 + k];
+  IF(contact_exclude)[id] = raw.dist >= inc;
+  IF(contact_efc_address)[id] = -1;
+  DF(contact_mu)[id] = 0;
+}
+
 BP_STAGE void bp_collision(const C& c) {
   const BpModel& m = c.P.m;
   if (c.lane == 0) IF(ncon)[0] = 0;
@@ -404,11 +507,12 @@ BP_STAGE void bp_collision(const C& c) {
   bool full = false;
   auto gpos = DF(geom_xpos), gmat = DF(geom_xmat);
 #pragma unroll 1
-  for (int p0 = 0; p0 < m.npair; p0 += C::G) {
+  const int nprim = m.npair - m.nhfpair;
+  for (int p0 = 0; p0 < nprim; p0 += C::G) {
     int p = p0 + c.lane, n = 0, g1 = 0, g2 = 0;
     double margin = 0, gap = 0;
     RawCon raw[4];
-    if (p < m.npair && !(filterparent && m.pair_parentchild[p])) {
+    if (p < nprim && !(filterparent && m.pair_parentchild[p])) {
       g1 = m.pair_geom1[p]; g2 = m.pair_geom2[p];
       margin = fmax(m.geom_margin[g1], m.geom_margin[g2]);
       gap = fmax(m.geom_gap[g1], m.geom_gap[g2]);
@@ -442,37 +546,67 @@ BP_STAGE void bp_collision(const C& c) {
     for (int i = 0; i < n; i++) {
       int id = start + i;
       if (id >= nconmax) { full = true; break; }
-      double f[9];
-      for (int k = 0; k < 3; k++) { f[k] = raw[i].n[k]; f[3 + k] = raw[i].hint[k]; f[6 + k] = 0; }
-      make_frame(f);
-      DF(contact_dist)[id] = raw[i].dist;
-      for (int k = 0; k < 3; k++) DF(contact_pos)[3 * id + k] = raw[i].pos[k];
-      for (int k = 0; k < 9; k++) DF(contact_frame)[9 * id + k] = f[k];
-      double inc = margin - gap;
-      DF(contact_includemargin)[id] = inc;
-      IF(contact_geom1)[id] = g1; IF(contact_geom2)[id] = g2;
-      int d1 = m.geom_condim[g1], d2 = m.geom_condim[g2];
-      IF(contact_dim)[id] = d1 > d2 ? d1 : d2;
-      const double *f1 = m.geom_friction + 3 * g1, *f2 = m.geom_friction + 3 * g2;
-      double fr[3];
-      for (int k = 0; k < 3; k++) fr[k] = fmax(f1[k], f2[k]);
-      auto cf = DF(contact_friction) + 5 * id;
-      cf[0] = fr[0]; cf[1] = fr[0]; cf[2] = fr[1]; cf[3] = fr[2]; cf[4] = fr[2];
-      double mix1 = m.geom_solmix[g1], mix2 = m.geom_solmix[g2], mix;
-      if (mix1 >= BP_MINVAL && mix2 >= BP_MINVAL) mix = mix1 / (mix1 + mix2);
-      else if (mix1 < BP_MINVAL && mix2 < BP_MINVAL) mix = 0.5;
-      else mix = mix1 < BP_MINVAL ? 0.0 : 1.0;
-      for (int k = 0; k < 2; k++)
-        DF(contact_solref)[2 * id + k] =
-            mix * m.geom_solref[2 * g1 + k] + (1 - mix) * m.geom_solref[2 * g2 + k];
-      for (int k = 0; k < 5; k++)
-        DF(contact_solimp)[5 * id + k] =
-            mix * m.geom_solimp[5 * g1 + k] + (1 - mix) * m.geom_solimp[5 * g2 + k];
-      IF(contact_exclude)[id] = raw[i].dist >= inc;
-      IF(contact_efc_address)[id] = -1;
-      DF(contact_mu)[id] = 0;
+      bp_write_contact(c, id, g1, g2, margin, gap, raw[i]);
     }
     if (base > nconmax) break;    // uniform inside the group
+  }
+  // ---- height-field pairs (the last nhfpair of the list): one pair at a time, the
+  // triangles under the geom's bounding sphere spread over the lanes, contacts in
+  // (row, column, half) order
+  if (m.nhfpair > 0 && c.hf != nullptr) {
+#pragma unroll 1
+    for (int p = nprim; p < m.npair && base <= nconmax; p++) {
+      if (filterparent && m.pair_parentchild[p]) continue;
+      const int g1 = m.pair_geom1[p], g2 = m.pair_geom2[p];
+      const double margin = fmax(m.geom_margin[g1], m.geom_margin[g2]);
+      const double gap = fmax(m.geom_gap[g1], m.geom_gap[g2]);
+      HField h;
+      hf_init(m, c.hf, m.geom_dataid[g1], h);
+      double p1[3], R1[9], R2[9], dif[3], gp[3], gR[9], gs[3];
+      for (int k = 0; k < 3; k++) { p1[k] = gpos[3 * g1 + k]; dif[k] = gpos[3 * g2 + k] - p1[k]; }
+      for (int k = 0; k < 9; k++) { R1[k] = gmat[9 * g1 + k]; R2[k] = gmat[9 * g2 + k]; }
+      for (int k = 0; k < 3; k++) gs[k] = m.geom_size[3 * g2 + k];
+      matT_vec3(gp, R1, dif);
+      for (int i = 0; i < 3; i++)
+        for (int j = 0; j < 3; j++)
+          gR[3 * i + j] = R1[i] * R2[j] + R1[3 + i] * R2[3 + j] + R1[6 + i] * R2[6 + j];
+      const double rb = m.geom_rbound[g2] + margin;
+      if (gp[0] - rb > h.rx || gp[0] + rb < -h.rx || gp[1] - rb > h.ry || gp[1] + rb < -h.ry ||
+          gp[2] - rb > h.zs || gp[2] + rb < -h.base) continue;
+      int c0, c1, r0, r1;
+      hf_range(gp[0] - rb, gp[0] + rb, h.rx, h.dx, h.ncol, c0, c1);
+      hf_range(gp[1] - rb, gp[1] + rb, h.ry, h.dy, h.nrow, r0, r1);
+      const int ncol = c1 - c0, ntri = ncol > 0 && r1 > r0 ? 2 * ncol * (r1 - r0) : 0;
+      const int gt = m.geom_type[g2];
+#pragma unroll 1
+      for (int t0 = 0; t0 < ntri; t0 += C::G) {
+        const int t = t0 + c.lane;
+        int n = 0;
+        RawCon raw[4];
+        if (t < ntri) {
+          const int cell = t >> 1, half = t & 1;
+          double a[3], b[3], cc[3];
+          hf_triangle(h, r0 + cell / ncol, c0 + cell % ncol, half, a, b, cc);
+          if (!(fmax(a[2], fmax(b[2], cc[2])) < gp[2] - rb))
+            n = hf_tri_geom(half, a, b, cc, gt, gp, gR, gs, margin, raw);
+        }
+        int tot, start = base + group_excl_scan(c, n, &tot);
+        base += tot;
+#pragma unroll 1
+        for (int i = 0; i < n; i++) {
+          int id = start + i;
+          if (id >= nconmax) { full = true; break; }
+          RawCon w;
+          w.dist = raw[i].dist;
+          mat_vec3(w.pos, R1, raw[i].pos);
+          for (int k = 0; k < 3; k++) w.pos[k] += p1[k];
+          mat_vec3(w.n, R1, raw[i].n);
+          mat_vec3(w.hint, R1, raw[i].hint);
+          bp_write_contact(c, id, g1, g2, margin, gap, w);
+        }
+        if (base > nconmax) break;
+      }
+    }
   }
   full = group_any(c, full);
   if (c.lane == 0) {

@@ -32,6 +32,7 @@ struct Ctx {
   bool act;        // false: this group has no environment (ragged tail / masked out)
   bool lock;       // true: the block's warps re-align at stage boundaries (BP_LOCK)
   double* hot;     // this env's shared-memory arena (nullptr: those arrays stay global)
+  const float* hf; // this env's height-field elevation data (nullptr: none)
   __device__ __forceinline__ DP null() const { return DP{nullptr}; }
 };
 

@@ -376,7 +376,8 @@ bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
   extern __shared__ double bp_arena[];
   double* hot = (S == 1 && P.hot_doubles > 0)
       ? bp_arena + (long long)(threadIdx.x / G) * P.hot_doubles : nullptr;
-  Ctx<G, S> c{P, base, ib, wl & (G - 1), mask, act, lock, hot};
+  const float* hf = P.hfield ? P.hfield + env * (long long)P.m.nhfielddata : nullptr;
+  Ctx<G, S> c{P, base, ib, wl & (G - 1), mask, act, lock, hot, hf};
   bp_load_ctrl(c, env);
   bp_run_mode(c);
   if (P.rew_out && act) {           // epilogue: the task's observation and reward

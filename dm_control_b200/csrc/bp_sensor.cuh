@@ -4,6 +4,7 @@
 #ifndef BP_SENSOR_CUH_
 #define BP_SENSOR_CUH_
 #include "bp_dyn.cuh"
+#include "bp_hfield.cuh"
 
 BP_STAGE void bp_subtree_vel(const C& c) {
   const BpModel& m = c.P.m;
@@ -120,6 +121,35 @@ __device__ __forceinline__ int bp_obj_frame(const C& c, int objtype, int id, dou
   return body;
 }
 
+// mj_ray: nearest geom surface along the unit ray (pnt, vec), geoms of `bodyexclude`
+// skipped; -1 without a hit (the rangefinder's reading, quadruped.py:212-217)
+BP_STAGE double bp_ray(const C& c, const double* pnt, const double* vec, int bodyexclude) {
+  const BpModel& m = c.P.m;
+  auto gpos = DF(geom_xpos), gmat = DF(geom_xmat);
+  double best = -1;
+#pragma unroll 1
+  for (int g = 0; g < m.ngeom; g++) {
+    if (m.geom_bodyid[g] == bodyexclude) continue;
+    double R[9], dif[3], o[3], v[3], sz[3];
+    for (int k = 0; k < 9; k++) R[k] = gmat[9 * g + k];
+    for (int k = 0; k < 3; k++) { dif[k] = pnt[k] - gpos[3 * g + k]; sz[k] = m.geom_size[3 * g + k]; }
+    matT_vec3(o, R, dif);
+    matT_vec3(v, R, vec);
+    const int gt = m.geom_type[g];
+    double x;
+    if (gt == GEOM_HFIELD) {
+      if (c.hf == nullptr) continue;
+      HField h;
+      hf_init(m, c.hf, m.geom_dataid[g], h);
+      x = ray_hfield(h, o, v);
+    } else {
+      x = ray_prim(gt, sz, o, v);
+    }
+    best = ray_min(best, x);
+  }
+  return best;
+}
+
 BP_STAGE void bp_sensors(const C& c, int stage) {
   const BpModel& m = c.P.m;
   if (m.nsensor == 0) return;
@@ -136,6 +166,12 @@ BP_STAGE void bp_sensors(const C& c, int stage) {
       case SENS_JOINTVEL: out[0] = DF(qvel)[m.jnt_dofadr[id]]; break;
       case SENS_ACTUATORFRC: out[0] = DF(actuator_force)[id]; break;
       case SENS_SUBTREECOM: for (int k = 0; k < 3; k++) out[k] = DF(subtree_com)[3 * id + k]; break;
+      case SENS_RANGEFINDER: {
+        int body = bp_obj_frame(c, OBJ_SITE, id, pos, mat);
+        double zax[3] = {mat[2], mat[5], mat[8]};
+        out[0] = bp_ray(c, pos, zax, body);
+        break;
+      }
       case SENS_SUBTREELINVEL: for (int k = 0; k < 3; k++) out[k] = DF(subtree_linvel)[3 * id + k]; break;
       case SENS_FRAMEPOS:
         bp_obj_frame(c, m.sensor_objtype[s], id, pos, mat);

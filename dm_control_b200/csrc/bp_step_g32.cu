@@ -11,7 +11,8 @@ bp_step_kernel_smem(const __grid_constant__ BpParams P) {
   double* g = P.image + env * P.stride;
   for (int w = lane; w < P.L.persist; w += 32) smem[w] = g[w];
   __syncwarp();
-  Ctx<32, 1> c{P, smem, (int*)(smem + P.L.ints), lane, 0xffffffffu, true, false, nullptr};
+  const float* hf = P.hfield ? P.hfield + env * (long long)P.m.nhfielddata : nullptr;
+  Ctx<32, 1> c{P, smem, (int*)(smem + P.L.ints), lane, 0xffffffffu, true, false, nullptr, hf};
   bp_load_ctrl(c, env);
   bp_run_mode(c);
   __syncwarp();

@@ -28,7 +28,8 @@ enum { ST_SATISFIED, ST_QUADRATIC, ST_LINEARNEG, ST_LINEARPOS, ST_CONE };
 enum { W_INERTIA, W_CONTACTFULL, W_CNSTRFULL, W_VGEOMFULL, W_BADQPOS,
        W_BADQVEL, W_BADQACC, W_BADCTRL, W_COUNT };
 enum { SENS_TOUCH = 0, SENS_ACCELEROMETER = 1, SENS_VELOCIMETER = 2,
-       SENS_GYRO = 3, SENS_FORCE = 4, SENS_TORQUE = 5, SENS_JOINTPOS = 8,
+       SENS_GYRO = 3, SENS_FORCE = 4, SENS_TORQUE = 5, SENS_RANGEFINDER = 7,
+       SENS_JOINTPOS = 8,
        SENS_JOINTVEL = 9, SENS_ACTUATORFRC = 14, SENS_FRAMEPOS = 23,
        SENS_SUBTREECOM = 32, SENS_SUBTREELINVEL = 33 };
 enum { OBJ_BODY = 1, OBJ_XBODY = 2, OBJ_GEOM = 5, OBJ_SITE = 6 };
@@ -40,6 +41,7 @@ enum { BP_MODE_STEP = 0, BP_MODE_FORWARD = 1, BP_MODE_STEP1 = 2,
 #define BP_MODEL_INT_SCALARS(X) \
   X(nq) X(nv) X(nu) X(na) X(nbody) X(njnt) X(ngeom) X(nsite) X(nM) X(npair) \
   X(nconmax) X(njmax) X(nsensor) X(nsensordata) X(nkey) X(ntendon) X(neq) \
+  X(nhfield) X(nhfielddata) X(nhfpair) \
   X(opt_integrator) X(opt_cone) X(opt_solver) X(opt_iterations) \
   X(opt_ls_iterations) X(opt_disableflags) X(opt_enableflags)
 #define BP_MODEL_F64_SCALARS(X) \
@@ -55,7 +57,8 @@ enum { BP_MODE_STEP = 0, BP_MODE_FORWARD = 1, BP_MODE_STEP1 = 2,
   X(actuator_biastype) X(actuator_trnid) X(actuator_ctrllimited) \
   X(actuator_forcelimited) X(sensor_type) X(sensor_objtype) X(sensor_objid) \
   X(sensor_dim) X(sensor_adr) X(sensor_needstage) X(tendon_adr) X(tendon_num) \
-  X(wrap_objid) X(eq_type) X(eq_obj1id) X(eq_obj2id) X(eq_active)
+  X(wrap_objid) X(eq_type) X(eq_obj1id) X(eq_obj2id) X(eq_active) \
+  X(geom_dataid) X(hfield_nrow) X(hfield_ncol) X(hfield_adr)
 #define BP_MODEL_F64_ARRAYS(X) \
   X(opt_gravity) X(body_pos) X(body_quat) X(body_ipos) X(body_iquat) \
   X(body_mass) X(body_subtreemass) X(body_inertia) X(body_invweight0) \
@@ -68,7 +71,7 @@ enum { BP_MODE_STEP = 0, BP_MODE_FORWARD = 1, BP_MODE_STEP1 = 2,
   X(actuator_dynprm) X(actuator_gainprm) X(actuator_biasprm) \
   X(actuator_ctrlrange) X(actuator_forcerange) X(actuator_gear) \
   X(sensor_cutoff) X(wrap_prm) X(tendon_length0) X(tendon_invweight0) X(eq_solref) \
-  X(eq_solimp) X(eq_data)
+  X(eq_solimp) X(eq_data) X(hfield_size) X(hfield_data)
 // ---- arrays derived on the host when the model is created (bp_api.cu) ---------
 //   body_level_*: bodies grouped by tree depth (parents complete before children)
 //   body_child_*: children of each body, DESCENDING id (the accumulation order of a
@@ -173,6 +176,9 @@ struct BpParams {
   int lanes;         // lanes per environment (group size G)
   int mode, nsub, disable_actuation;
   int hot_doubles;   // per-env shared-memory arena of the global-memory shapes (0 = none)
+  // height-field elevation, one copy per env (float32 as in mjModel.hfield_data): the
+  // Escape task writes a different terrain into every episode (quadruped.py:371-382)
+  const float* hfield;     // [nenv][nhfielddata], null when the model has no height field
   // fused Environment.step (bp_env_step): dense [nenv][nu] controls scattered into the
   // images before the first sub-step, task observation / reward written after the last
   const double* ctrl_in;   // null: images keep their ctrl

@@ -200,6 +200,7 @@ class _Ctx:
     self.boundmass = 0.0
     self.boundinertia = 0.0
     self.balanceinertia = False
+    self.hfields = {}     # name -> (id, nrow, ncol, size[4])
 
 
 def _orientation(a, ctx):
@@ -310,6 +311,12 @@ def _compile_geom(a, ctx):
   g["group"] = int(a.get("group", 0))
   g["rbound"] = _rbound(gtype, g["size"])
   g["hfield"] = a.get("hfield")
+  g["dataid"] = -1
+  if gtype == M.GEOM_HFIELD:
+    # [MJ-doc] a height-field geom takes its size from the asset it references
+    hid, _, _, hsize = ctx.hfields[g["hfield"]]
+    g["dataid"] = hid
+    g["size"] = np.array(hsize[:3], dtype=np.float64)
   # mass properties
   vol, inertia = _geom_volume_inertia(gtype, g["size"])
   if "mass" in a:
@@ -509,6 +516,15 @@ def compile_xml(xml_string, assets=None):
     ctx.boundmass = float(comp.get("boundmass", ctx.boundmass))
     ctx.boundinertia = float(comp.get("boundinertia", ctx.boundinertia))
   classes = _parse_defaults(root)
+  hf_list = []
+  for sec in root.findall("asset"):
+    for h in sec.findall("hfield"):
+      if h.get("file"):
+        raise ValueError("height fields loaded from files are not supported")
+      name = h.get("name", "")
+      ctx.hfields[name] = (len(hf_list), int(h.get("nrow")), int(h.get("ncol")),
+                           _floats(h.get("size"), 4))
+      hf_list.append(name)
 
   bodies = []
   world = ET.Element("body", {"name": "world"})
@@ -521,6 +537,7 @@ def compile_xml(xml_string, assets=None):
   m = M.FlatModel()
   m.model_name = root.get("model", "MuJoCo Model")
   _emit_tree(m, bodies, ctx)
+  _emit_hfields(m, ctx, hf_list)
   _emit_options(m, root)
   _emit_tendons_equality(m, root, classes)
   _emit_actuators(m, root, classes)
@@ -622,7 +639,7 @@ def _emit_tree(m, bodies, ctx):
                 "solref", "solimp", "size", "rbound", "pos", "quat", "friction",
                 "margin", "gap"):
         G[k].append(g[k])
-      G["bodyid"].append(bid); G["dataid"].append(-1)
+      G["bodyid"].append(bid); G["dataid"].append(g.get("dataid", -1))
     for s in b["sites"]:
       names["site"].append(s["name"])
       for k in ("type", "size", "pos", "quat"):
@@ -686,8 +703,26 @@ def _emit_tree(m, bodies, ctx):
     sub[body_f["parentid"][b]] += sub[b]
   m.set("body_subtreemass", sub)
   # unsupported-in-v1 sizes, present so the schema is stable
-  for k in ("nhfield", "nmocap"):
-    m.set(k, 0)
+  m.set("nmocap", 0)
+
+
+def _emit_hfields(m, ctx, hf_list):
+  """<asset><hfield nrow ncol size="rx ry zmax zbase"/>: elevation data is all zero until
+  the task writes it (quadruped.py:371-382); normalised [0, 1] values as in mjModel."""
+  n = len(hf_list)
+  m.names["hfield"] = list(hf_list)
+  adr, tot = [], 0
+  for name in hf_list:
+    _, nrow, ncol, _ = ctx.hfields[name]
+    adr.append(tot)
+    tot += nrow * ncol
+  m.set("nhfield", n); m.set("nhfielddata", tot)
+  m.set("hfield_nrow", np.array([ctx.hfields[h][1] for h in hf_list], dtype=np.int32).reshape(n))
+  m.set("hfield_ncol", np.array([ctx.hfields[h][2] for h in hf_list], dtype=np.int32).reshape(n))
+  m.set("hfield_adr", np.array(adr, dtype=np.int32).reshape(n))
+  m.set("hfield_size", np.array([ctx.hfields[h][3] for h in hf_list],
+                                dtype=np.float64).reshape(n, 4))
+  m.set("hfield_data", np.zeros(tot, dtype=np.float64))
 
 
 def _emit_options(m, root):
@@ -920,6 +955,11 @@ def _emit_pairs(m):
       # order by geom type so that type1 <= type2 (function-table convention)
       a, b = (g1, g2) if m.geom_type[g1] <= m.geom_type[g2] else (g2, g1)
       pairs.append((a, b, pc))
+  # height-field pairs go last: the engine visits them in a second pass whose contacts
+  # follow those of the primitive pairs (csrc/bp_collide.cuh, oracle o_collision)
+  hf = [p for p in pairs if m.geom_type[p[0]] == M.GEOM_HFIELD]
+  pairs = [p for p in pairs if m.geom_type[p[0]] != M.GEOM_HFIELD] + hf
+  m.set("nhfpair", len(hf))
   npair = len(pairs)
   arr = np.array(pairs, dtype=np.int32).reshape(npair, 3)
   m.set("npair", npair)
@@ -934,6 +974,8 @@ def _emit_pairs(m):
     ta, tb = m.geom_type[a], m.geom_type[b]
     if ta == M.GEOM_PLANE:
       n = {M.GEOM_BOX: 4, M.GEOM_CAPSULE: 2, M.GEOM_CYLINDER: 4}.get(tb, 1)
+    elif ta == M.GEOM_HFIELD:
+      n = 2
     elif tb == M.GEOM_BOX:
       n = 8 if ta == M.GEOM_BOX else 1
     else:

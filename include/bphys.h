@@ -85,6 +85,13 @@ int bp_field_read(bp_batch* b, const char* name, void* host, int64_t env0, int64
  * (e.g. a torch tensor); asynchronous on the batch's stream. */
 int bp_field_copy_device(bp_batch* b, const char* name, void* dev, int to_image);
 
+/* Per-env height-field elevation data, the batched form of the run-time edit of
+ * `model.hfield_data` in suite/quadruped.py:371-382 (Escape.initialize_episode writes a
+ * new terrain every episode).  `host` is a dense [n][nhfielddata] float32 array
+ * (mjModel.hfield_data is float32, normalised to [0, 1]) for envs [env0, env0+n). */
+int bp_hfield_write(bp_batch* b, const float* host, int64_t env0, int64_t n);
+int bp_hfield_read(bp_batch* b, float* host, int64_t env0, int64_t n);
+
 /* Optional per-env mask (device or host bytes, nenv long; NULL = all envs): envs
  * whose byte is 0 are left untouched by the calls below. */
 int bp_set_mask(bp_batch* b, const uint8_t* mask_host);

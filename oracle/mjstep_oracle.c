@@ -32,7 +32,8 @@ enum { ST_SATISFIED, ST_QUADRATIC, ST_LINEARNEG, ST_LINEARPOS, ST_CONE };
 enum { W_INERTIA, W_CONTACTFULL, W_CNSTRFULL, W_VGEOMFULL, W_BADQPOS,
        W_BADQVEL, W_BADQACC, W_BADCTRL };
 enum { SENS_TOUCH = 0, SENS_ACCELEROMETER = 1, SENS_VELOCIMETER = 2,
-       SENS_GYRO = 3, SENS_FORCE = 4, SENS_TORQUE = 5, SENS_JOINTPOS = 8,
+       SENS_GYRO = 3, SENS_FORCE = 4, SENS_TORQUE = 5, SENS_RANGEFINDER = 7,
+       SENS_JOINTPOS = 8,
        SENS_JOINTVEL = 9, SENS_ACTUATORFRC = 14, SENS_FRAMEPOS = 23,
        SENS_SUBTREECOM = 32, SENS_SUBTREELINVEL = 33 };
 enum { OBJ_BODY = 1, OBJ_XBODY = 2, OBJ_GEOM = 5, OBJ_SITE = 6 };
@@ -49,6 +50,7 @@ typedef struct {
 #define MODEL_INT_SCALARS(X) \
   X(nq) X(nv) X(nu) X(na) X(nbody) X(njnt) X(ngeom) X(nsite) X(nM) X(npair) \
   X(nconmax) X(njmax) X(nsensor) X(nsensordata) X(nkey) X(ntendon) X(neq) \
+  X(nhfield) X(nhfielddata) X(nhfpair) \
   X(opt_integrator) X(opt_cone) X(opt_solver) X(opt_iterations) \
   X(opt_ls_iterations) X(opt_disableflags) X(opt_enableflags)
 #define MODEL_F64_SCALARS(X) \
@@ -64,7 +66,8 @@ typedef struct {
   X(actuator_biastype) X(actuator_trnid) X(actuator_ctrllimited) \
   X(actuator_forcelimited) X(sensor_type) X(sensor_objtype) X(sensor_objid) \
   X(sensor_dim) X(sensor_adr) X(sensor_needstage) X(tendon_adr) X(tendon_num) \
-  X(wrap_objid) X(eq_type) X(eq_obj1id) X(eq_obj2id) X(eq_active)
+  X(wrap_objid) X(eq_type) X(eq_obj1id) X(eq_obj2id) X(eq_active) \
+  X(geom_dataid) X(hfield_nrow) X(hfield_ncol) X(hfield_adr)
 #define MODEL_F64_ARRAYS(X) \
   X(opt_gravity) X(body_pos) X(body_quat) X(body_ipos) X(body_iquat) \
   X(body_mass) X(body_subtreemass) X(body_inertia) X(body_invweight0) \
@@ -77,7 +80,8 @@ typedef struct {
   X(actuator_dynprm) X(actuator_gainprm) X(actuator_biasprm) \
   X(actuator_ctrlrange) X(actuator_forcerange) X(actuator_gear) \
   X(sensor_cutoff) X(key_qpos) X(key_qvel) X(key_act) X(key_time) X(wrap_prm) \
-  X(tendon_length0) X(tendon_invweight0) X(eq_solref) X(eq_solimp) X(eq_data)
+  X(tendon_length0) X(tendon_invweight0) X(eq_solref) X(eq_solimp) X(eq_data) \
+  X(hfield_size) X(hfield_data)
 
 struct OModel {
   char* blob;
@@ -209,6 +213,7 @@ struct OData {
   DATA_FIELDS(X)
 #undef X
   OContact* contact;
+  double* hfield;   /* this env's elevation data (Escape writes it per episode) */
   /* solver scratch */
   double *s_Ma, *s_jar, *s_grad, *s_Mgrad, *s_search, *s_Mv, *s_jv, *s_H,
       *s_Mdense;
@@ -222,6 +227,8 @@ OData* od_create(const OModel* m) {
   DATA_FIELDS(X)
 #undef X
   d->contact = (OContact*)calloc(m->nconmax > 0 ? m->nconmax : 1, sizeof(OContact));
+  d->hfield = (double*)calloc(m->nhfielddata > 0 ? m->nhfielddata : 1, sizeof(double));
+  for (int i = 0; i < m->nhfielddata; i++) d->hfield[i] = m->hfield_data[i];
   int nv = m->nv > 0 ? m->nv : 1, nj = m->njmax > 0 ? m->njmax : 1;
   d->s_Ma = calloc(nv, 8); d->s_jar = calloc(nj, 8); d->s_grad = calloc(nv, 8);
   d->s_Mgrad = calloc(nv, 8); d->s_search = calloc(nv, 8); d->s_Mv = calloc(nv, 8);
@@ -237,6 +244,7 @@ void od_free(OData* d) {
   DATA_FIELDS(X)
 #undef X
   free(d->contact);
+  free(d->hfield);
   free(d->s_Ma); free(d->s_jar); free(d->s_grad); free(d->s_Mgrad);
   free(d->s_search); free(d->s_Mv); free(d->s_jv); free(d->s_H);
   free(d->s_Mdense);
@@ -244,6 +252,11 @@ void od_free(OData* d) {
 }
 
 void* od_field(OData* d, const char* name, int64_t* count, int* dtype) {
+  if (strcmp(name, "hfield_data") == 0) {
+    if (count) *count = d->m->nhfielddata;
+    if (dtype) *dtype = 0;
+    return d->hfield;
+  }
 #define X(n, t, c) if (strcmp(name, #n) == 0) { \
     if (count) *count = d->n##_count; \
     if (dtype) { *dtype = (sizeof(t) == 8) ? 0 : 1; } \
@@ -1039,6 +1052,243 @@ static int col_plane_ellipsoid_raw(const double* ppos, const double* n, const do
   return 1;
 }
 
+/* ------------------------------------------------ height fields [A.7h]
+ * MuJoCo walks the grid cells under the geom's bounding sphere, builds a triangular prism
+ * per half cell and sends prism-geom to its general convex routine (libccd MPR, closed).
+ * Here the same cell walk feeds closed-form tests against the prism's top triangle; the
+ * ground below the triangle counts as solid.  All of it in the height field's frame.
+ *   cell (r, c), half 0: a = v(r,c), b = v(r,c+1),   c = v(r+1,c+1)
+ *                half 1: a = v(r,c), b = v(r+1,c+1), c = v(r+1,c)        (both CCW from above)
+ * Features shared by neighbouring triangles are tested by ONE owner so that a contact is
+ * not reported twice: half 0 owns vertex a and edges ab, ca; half 1 owns edge ca.
+ *   sphere    closest point of the triangle (face always, edge / vertex when owned)
+ *   capsule   both end spheres + the segment's interior against the owned edges
+ *   ellipsoid, cylinder   support point(s) along -n against the face + the owned vertex
+ *             against the solid (edges of the terrain are not tested: documented gap)    */
+typedef struct {
+  const double* data;
+  int nrow, ncol;
+  double rx, ry, zs, base, dx, dy;
+} HField;
+
+static void hf_init(const OModel* m, const OData* d, int hid, HField* h) {
+  h->data = d->hfield + m->hfield_adr[hid];
+  h->nrow = m->hfield_nrow[hid]; h->ncol = m->hfield_ncol[hid];
+  h->rx = m->hfield_size[4 * hid]; h->ry = m->hfield_size[4 * hid + 1];
+  h->zs = m->hfield_size[4 * hid + 2]; h->base = m->hfield_size[4 * hid + 3];
+  h->dx = 2 * h->rx / (h->ncol - 1); h->dy = 2 * h->ry / (h->nrow - 1);
+}
+
+static void hf_vertex(const HField* h, int r, int c, double* v) {
+  v[0] = c * h->dx - h->rx; v[1] = r * h->dy - h->ry;
+  v[2] = h->data[r * h->ncol + c] * h->zs;
+}
+
+static void hf_triangle(const HField* h, int r, int c, int half, double* a, double* b,
+                        double* cc) {
+  hf_vertex(h, r, c, a);
+  if (half == 0) { hf_vertex(h, r, c + 1, b); hf_vertex(h, r + 1, c + 1, cc); }
+  else { hf_vertex(h, r + 1, c + 1, b); hf_vertex(h, r + 1, c, cc); }
+}
+
+/* closest point of triangle abc to p (Voronoi regions of the triangle's features);
+ * returns the region: 0 face, 1 / 2 / 3 vertex a / b / c, 4 edge ab, 5 edge bc, 6 edge ca */
+static int tri_closest(const double* p, const double* a, const double* b, const double* c,
+                       double* q) {
+  double ab[3], ac[3], ap[3], bp[3], cp[3];
+  for (int k = 0; k < 3; k++) {
+    ab[k] = b[k] - a[k]; ac[k] = c[k] - a[k];
+    ap[k] = p[k] - a[k]; bp[k] = p[k] - b[k]; cp[k] = p[k] - c[k];
+  }
+  double d1 = dot3(ab, ap), d2 = dot3(ac, ap);
+  if (d1 <= 0 && d2 <= 0) { memcpy(q, a, 24); return 1; }
+  double d3 = dot3(ab, bp), d4 = dot3(ac, bp);
+  if (d3 >= 0 && d4 <= d3) { memcpy(q, b, 24); return 2; }
+  double vc = d1 * d4 - d3 * d2;
+  if (vc <= 0 && d1 >= 0 && d3 <= 0) {
+    double v = d1 / (d1 - d3);
+    for (int k = 0; k < 3; k++) q[k] = a[k] + v * ab[k];
+    return 4;
+  }
+  double d5 = dot3(ab, cp), d6 = dot3(ac, cp);
+  if (d6 >= 0 && d5 <= d6) { memcpy(q, c, 24); return 3; }
+  double vb = d5 * d2 - d1 * d6;
+  if (vb <= 0 && d2 >= 0 && d6 <= 0) {
+    double w = d2 / (d2 - d6);
+    for (int k = 0; k < 3; k++) q[k] = a[k] + w * ac[k];
+    return 6;
+  }
+  double va = d3 * d6 - d5 * d4;
+  if (va <= 0 && (d4 - d3) >= 0 && (d5 - d6) >= 0) {
+    double w = (d4 - d3) / ((d4 - d3) + (d5 - d6));
+    for (int k = 0; k < 3; k++) q[k] = b[k] + w * (c[k] - b[k]);
+    return 5;
+  }
+  double den = 1.0 / (va + vb + vc), v = vb * den, w = vc * den;
+  for (int k = 0; k < 3; k++) q[k] = a[k] + ab[k] * v + ac[k] * w;
+  return 0;
+}
+
+#define HF_OWN0 ((1 << 0) | (1 << 1) | (1 << 4) | (1 << 6))
+#define HF_OWN1 ((1 << 0) | (1 << 6))
+
+static void raw_set(RawCon* o, double dist, const double* pos, const double* n,
+                    const double* hint) {
+  o->dist = dist;
+  memcpy(o->pos, pos, 24);
+  memcpy(o->frame, n, 24);
+  memset(o->frame + 3, 0, 48);
+  if (hint) memcpy(o->frame + 3, hint, 24);
+}
+
+/* sphere (centre q, radius r) against one triangle with unit normal nt */
+static int hf_sphere_tri(int half, const double* a, const double* b, const double* c,
+                         const double* nt, const double* q, double r, double margin,
+                         const double* hint, RawCon* out) {
+  double aq[3] = {q[0] - a[0], q[1] - a[1], q[2] - a[2]}, cl[3], nrm[3], dist;
+  double s = dot3(nt, aq);
+  int reg = tri_closest(q, a, b, c, cl);
+  if (s < 0) {                       /* centre under the surface: through the face only */
+    if (reg != 0) return 0;
+    memcpy(nrm, nt, 24);
+    dist = s - r;
+  } else {
+    if (!((half ? HF_OWN1 : HF_OWN0) >> reg & 1)) return 0;
+    double dv[3] = {q[0] - cl[0], q[1] - cl[1], q[2] - cl[2]};
+    double dd = norm3(dv);
+    if (dd < MINVAL) memcpy(nrm, nt, 24);
+    else for (int k = 0; k < 3; k++) nrm[k] = dv[k] / dd;
+    dist = dd - r;
+  }
+  if (dist > margin) return 0;
+  double pos[3];
+  for (int k = 0; k < 3; k++) pos[k] = q[k] - nrm[k] * (r + 0.5 * dist);
+  raw_set(out, dist, pos, nrm, hint);
+  return 1;
+}
+
+/* interior of the capsule's segment (p +- l ax) against the edge e0 -> e1; a hit at the
+ * start vertex counts when vertex0 is set (the edge that owns its first vertex) */
+static int hf_capsule_edge(const double* p, const double* ax, double l, double r,
+                           const double* e0, const double* e1, int vertex0, double margin,
+                           RawCon* out) {
+  double d1[3], d2[3], rr[3];
+  for (int k = 0; k < 3; k++) {
+    d1[k] = 2 * l * ax[k]; d2[k] = e1[k] - e0[k];
+    rr[k] = p[k] - l * ax[k] - e0[k];
+  }
+  double A = dot3(d1, d1), E = dot3(d2, d2), F = dot3(d2, rr), C = dot3(d1, rr),
+         B = dot3(d1, d2);
+  double den = A * E - B * B, s, t;
+  if (den > 1e-12 * A * E) {
+    s = (B * F - C * E) / den;
+    s = s < 0 ? 0 : (s > 1 ? 1 : s);
+  } else s = 0.5;
+  t = (B * s + F) / E;
+  if (t < 0) { t = 0; s = -C / A; s = s < 0 ? 0 : (s > 1 ? 1 : s); }
+  else if (t > 1) { t = 1; s = (B - C) / A; s = s < 0 ? 0 : (s > 1 ? 1 : s); }
+  if (!(s > 0 && s < 1)) return 0;                 /* the ends are tested as spheres */
+  if (!(t < 1 && (t > 0 || vertex0))) return 0;
+  double c1[3], c2[3], dv[3];
+  for (int k = 0; k < 3; k++) {
+    c1[k] = p[k] - l * ax[k] + s * d1[k]; c2[k] = e0[k] + t * d2[k];
+    dv[k] = c1[k] - c2[k];
+  }
+  double dd = norm3(dv);
+  if (dd < MINVAL || dv[2] <= 0) return 0;         /* the axis has sunk below the edge */
+  double dist = dd - r;
+  if (dist > margin) return 0;
+  double nrm[3], pos[3];
+  for (int k = 0; k < 3; k++) { nrm[k] = dv[k] / dd; pos[k] = c1[k] - nrm[k] * (r + 0.5 * dist); }
+  raw_set(out, dist, pos, nrm, ax);
+  return 1;
+}
+
+/* a surface point x of a convex geom against the face: inside the prism's footprint and
+ * below (or within margin of) the face */
+static int hf_point_face(const double* a, const double* b, const double* c, const double* nt,
+                         const double* x, double margin, RawCon* out) {
+  double cl[3];
+  if (tri_closest(x, a, b, c, cl) != 0) return 0;
+  double ax[3] = {x[0] - a[0], x[1] - a[1], x[2] - a[2]};
+  double dist = dot3(nt, ax);
+  if (dist > margin) return 0;
+  double pos[3];
+  for (int k = 0; k < 3; k++) pos[k] = x[k] - nt[k] * 0.5 * dist;
+  raw_set(out, dist, pos, nt, NULL);
+  return 1;
+}
+
+/* geom (type gt, centre gp, frame gR row-major, sizes gs; all in the field's frame) against
+ * one triangle; returns the number of contacts written (at most 4), normals pointing
+ * from the terrain to the geom */
+static int hf_tri_geom(int half, const double* a, const double* b, const double* c, int gt,
+                       const double* gp, const double* gR, const double* gs, double margin,
+                       RawCon* out) {
+  double ab[3], ac[3], nt[3];
+  for (int k = 0; k < 3; k++) { ab[k] = b[k] - a[k]; ac[k] = c[k] - a[k]; }
+  cross3(nt, ab, ac);
+  normalize3(nt);
+  int n = 0;
+  if (gt == GEOM_SPHERE)
+    return hf_sphere_tri(half, a, b, c, nt, gp, gs[0], margin, NULL, out);
+  if (gt == GEOM_CAPSULE) {
+    double ax[3], e[3];
+    geom_axis(gR, 2, ax);
+    for (int sgn = 1; sgn >= -1; sgn -= 2) {
+      for (int k = 0; k < 3; k++) e[k] = gp[k] + sgn * ax[k] * gs[1];
+      n += hf_sphere_tri(half, a, b, c, nt, e, gs[0], margin, ax, out + n);
+    }
+    if (half == 0) n += hf_capsule_edge(gp, ax, gs[1], gs[0], a, b, 1, margin, out + n);
+    n += hf_capsule_edge(gp, ax, gs[1], gs[0], c, a, 0, margin, out + n);
+    return n;
+  }
+  if (gt == GEOM_ELLIPSOID) {
+    double dl[3], x[3], xw[3], s = 0;
+    matT_vec3(dl, gR, nt);
+    for (int k = 0; k < 3; k++) s += gs[k] * gs[k] * dl[k] * dl[k];
+    s = sqrt(s);
+    for (int k = 0; k < 3; k++) x[k] = -gs[k] * gs[k] * dl[k] / s;
+    mat_vec3(xw, gR, x);
+    for (int k = 0; k < 3; k++) xw[k] += gp[k];
+    n += hf_point_face(a, b, c, nt, xw, margin, out + n);
+    if (half == 0) {
+      double tmul = 0;
+      RawCon tmp;
+      if (col_sphere_ellipsoid_raw(a, 0.0, gp, gR, gs, margin, &tmul, &tmp)) out[n++] = tmp;
+    }
+    return n;
+  }
+  if (gt == GEOM_CYLINDER) {
+    double axis[3], vec[3], x[3];
+    geom_axis(gR, 2, axis);
+    double prj = dot3(nt, axis);
+    for (int k = 0; k < 3; k++) vec[k] = axis[k] * prj - nt[k];
+    double len = norm3(vec);
+    if (len >= MINVAL) for (int k = 0; k < 3; k++) vec[k] *= gs[0] / len;
+    else { geom_axis(gR, 0, vec); for (int k = 0; k < 3; k++) vec[k] *= gs[0]; }
+    for (int sgn = 1; sgn >= -1; sgn -= 2) {
+      for (int k = 0; k < 3; k++) x[k] = gp[k] + vec[k] + sgn * axis[k] * gs[1];
+      n += hf_point_face(a, b, c, nt, x, margin, out + n);
+    }
+    if (half == 0) {
+      RawCon tmp;
+      if (col_sphere_cylinder_raw(a, 0.0, gp, axis, gs[0], gs[1], margin, &tmp)) out[n++] = tmp;
+    }
+    return n;
+  }
+  return 0;
+}
+
+/* cells of the grid under [lo, hi] along one axis (half extent rad, spacing dd, nn
+ * vertices): first cell and one past the last */
+static void hf_range(double lo, double hi, double rad, double dd, int nn, int* i0, int* i1) {
+  double f0 = floor((lo + rad) / dd), f1 = ceil((hi + rad) / dd);
+  if (f0 < 0) f0 = 0;
+  if (f1 > nn - 1) f1 = nn - 1;
+  *i0 = (int)f0; *i1 = (int)f1;
+}
+
 static int collide_pair(const OModel* m, const OData* d, int g1, int g2,
                         double margin, RawCon* out) {
   int t1 = m->geom_type[g1], t2 = m->geom_type[g2];
@@ -1161,6 +1411,83 @@ static void make_frame(double* f) {
   cross3(f + 6, f, f + 3);
 }
 
+/* appends one contact; returns 0 when the buffer is full */
+static int add_contact(const OModel* m, OData* d, int g1, int g2, double margin, double gap,
+                       const RawCon* raw) {
+  if (d->ncon[0] >= m->nconmax) { warn(d, W_CONTACTFULL); return 0; }
+  OContact* c = d->contact + d->ncon[0];
+  int id = d->ncon[0]++;
+  c->dist = raw->dist;
+  memcpy(c->pos, raw->pos, 24);
+  memcpy(c->frame, raw->frame, 72);
+  make_frame(c->frame);
+  c->includemargin = margin - gap;
+  c->geom1 = g1; c->geom2 = g2;
+  int dim1 = m->geom_condim[g1], dim2 = m->geom_condim[g2];
+  c->dim = dim1 > dim2 ? dim1 : dim2;
+  const double *f1 = m->geom_friction + 3 * g1, *f2 = m->geom_friction + 3 * g2;
+  double fr[3];
+  for (int k = 0; k < 3; k++) fr[k] = fmax(f1[k], f2[k]);
+  c->friction[0] = c->friction[1] = fr[0];
+  c->friction[2] = fr[1];
+  c->friction[3] = c->friction[4] = fr[2];
+  double mix1 = m->geom_solmix[g1], mix2 = m->geom_solmix[g2], mix;
+  if (mix1 >= MINVAL && mix2 >= MINVAL) mix = mix1 / (mix1 + mix2);
+  else if (mix1 < MINVAL && mix2 < MINVAL) mix = 0.5;
+  else mix = mix1 < MINVAL ? 0.0 : 1.0;
+  for (int k = 0; k < 2; k++)
+    c->solref[k] = mix * m->geom_solref[2 * g1 + k] + (1 - mix) * m->geom_solref[2 * g2 + k];
+  for (int k = 0; k < 5; k++)
+    c->solimp[k] = mix * m->geom_solimp[5 * g1 + k] + (1 - mix) * m->geom_solimp[5 * g2 + k];
+  c->exclude = c->dist >= c->includemargin;
+  c->efc_address = -1;
+  d->contact_geom1[id] = g1; d->contact_geom2[id] = g2;
+  d->contact_dim[id] = c->dim; d->contact_dist[id] = c->dist;
+  memcpy(d->contact_pos + 3 * id, c->pos, 24);
+  memcpy(d->contact_frame + 9 * id, c->frame, 72);
+  return 1;
+}
+
+/* height field g1 against geom g2: the cells under the geom's bounding sphere, row by row,
+ * two triangles each; contacts in that order, rotated back to the world frame */
+static int collide_hfield(const OModel* m, OData* d, int g1, int g2, double margin,
+                          double gap) {
+  HField h;
+  hf_init(m, d, m->geom_dataid[g1], &h);
+  const double *p1 = d->geom_xpos + 3 * g1, *R1 = d->geom_xmat + 9 * g1;
+  const double *p2 = d->geom_xpos + 3 * g2, *R2 = d->geom_xmat + 9 * g2;
+  double dif[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]}, gp[3], gR[9];
+  matT_vec3(gp, R1, dif);
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++)
+      gR[3 * i + j] = R1[i] * R2[j] + R1[3 + i] * R2[3 + j] + R1[6 + i] * R2[6 + j];
+  double rb = m->geom_rbound[g2] + margin;
+  if (gp[0] - rb > h.rx || gp[0] + rb < -h.rx || gp[1] - rb > h.ry || gp[1] + rb < -h.ry ||
+      gp[2] - rb > h.zs || gp[2] + rb < -h.base) return 1;
+  int c0, c1, r0, r1;
+  hf_range(gp[0] - rb, gp[0] + rb, h.rx, h.dx, h.ncol, &c0, &c1);
+  hf_range(gp[1] - rb, gp[1] + rb, h.ry, h.dy, h.nrow, &r0, &r1);
+  for (int r = r0; r < r1; r++)
+    for (int c = c0; c < c1; c++)
+      for (int half = 0; half < 2; half++) {
+        double a[3], b[3], cc[3];
+        hf_triangle(&h, r, c, half, a, b, cc);
+        if (fmax(a[2], fmax(b[2], cc[2])) < gp[2] - rb) continue;
+        RawCon raw[4];
+        int n = hf_tri_geom(half, a, b, cc, m->geom_type[g2], gp, gR, m->geom_size + 3 * g2,
+                            margin, raw);
+        for (int i = 0; i < n; i++) {
+          RawCon w = raw[i];
+          mat_vec3(w.pos, R1, raw[i].pos);
+          for (int k = 0; k < 3; k++) w.pos[k] += p1[k];
+          mat_vec3(w.frame, R1, raw[i].frame);
+          mat_vec3(w.frame + 3, R1, raw[i].frame + 3);
+          if (!add_contact(m, d, g1, g2, margin, gap, &w)) return 0;
+        }
+      }
+  return 1;
+}
+
 static void o_collision(const OModel* m, OData* d) {
   d->ncon[0] = 0;
   if (m->opt_disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT)) return;
@@ -1170,6 +1497,10 @@ static void o_collision(const OModel* m, OData* d) {
     if (filterparent && m->pair_parentchild[p]) continue;
     double margin = fmax(m->geom_margin[g1], m->geom_margin[g2]);
     double gap = fmax(m->geom_gap[g1], m->geom_gap[g2]);
+    if (m->geom_type[g1] == GEOM_HFIELD) {      /* the last nhfpair pairs of the list */
+      if (!collide_hfield(m, d, g1, g2, margin, gap)) return;
+      continue;
+    }
     /* bounding-sphere rejection */
     const double *p1 = d->geom_xpos + 3 * g1, *p2 = d->geom_xpos + 3 * g2;
     if (m->geom_type[g1] == GEOM_PLANE) {
@@ -1183,39 +1514,8 @@ static void o_collision(const OModel* m, OData* d) {
     }
     RawCon raw[8];
     int n = collide_pair(m, d, g1, g2, margin, raw);
-    for (int i = 0; i < n; i++) {
-      if (d->ncon[0] >= m->nconmax) { warn(d, W_CONTACTFULL); return; }
-      OContact* c = d->contact + d->ncon[0];
-      int id = d->ncon[0]++;
-      c->dist = raw[i].dist;
-      memcpy(c->pos, raw[i].pos, 24);
-      memcpy(c->frame, raw[i].frame, 72);
-      make_frame(c->frame);
-      c->includemargin = margin - gap;
-      c->geom1 = g1; c->geom2 = g2;
-      int dim1 = m->geom_condim[g1], dim2 = m->geom_condim[g2];
-      c->dim = dim1 > dim2 ? dim1 : dim2;
-      const double *f1 = m->geom_friction + 3 * g1, *f2 = m->geom_friction + 3 * g2;
-      double fr[3];
-      for (int k = 0; k < 3; k++) fr[k] = fmax(f1[k], f2[k]);
-      c->friction[0] = c->friction[1] = fr[0];
-      c->friction[2] = fr[1];
-      c->friction[3] = c->friction[4] = fr[2];
-      double mix1 = m->geom_solmix[g1], mix2 = m->geom_solmix[g2], mix;
-      if (mix1 >= MINVAL && mix2 >= MINVAL) mix = mix1 / (mix1 + mix2);
-      else if (mix1 < MINVAL && mix2 < MINVAL) mix = 0.5;
-      else mix = mix1 < MINVAL ? 0.0 : 1.0;
-      for (int k = 0; k < 2; k++)
-        c->solref[k] = mix * m->geom_solref[2 * g1 + k] + (1 - mix) * m->geom_solref[2 * g2 + k];
-      for (int k = 0; k < 5; k++)
-        c->solimp[k] = mix * m->geom_solimp[5 * g1 + k] + (1 - mix) * m->geom_solimp[5 * g2 + k];
-      c->exclude = c->dist >= c->includemargin;
-      c->efc_address = -1;
-      d->contact_geom1[id] = g1; d->contact_geom2[id] = g2;
-      d->contact_dim[id] = c->dim; d->contact_dist[id] = c->dist;
-      memcpy(d->contact_pos + 3 * id, c->pos, 24);
-      memcpy(d->contact_frame + 9 * id, c->frame, 72);
-    }
+    for (int i = 0; i < n; i++)
+      if (!add_contact(m, d, g1, g2, margin, gap, raw + i)) return;
   }
 }
 
@@ -1900,6 +2200,206 @@ static void o_rne_post_constraint(const OModel* m, OData* d) {
   }
 }
 
+/* ------------------------------------------------------- rays [mj_ray]
+ * Distance along a unit ray to the nearest geom surface, -1 without a hit; the
+ * rangefinder sensor casts it from its site along the site's z axis and skips the geoms
+ * of the site's own body [MJ-doc: mj_ray, mju_rayGeom].  Solutions of a quadratic: the
+ * smallest non-negative root, so a ray that starts inside a geom reports its exit. */
+static double ray_quad(double a, double b, double c) {   /* a x^2 + 2 b x + c = 0 */
+  double det = b * b - a * c;
+  if (det < 0 || a < MINVAL) return -1;
+  det = sqrt(det);
+  double x0 = (-b - det) / a, x1 = (-b + det) / a;
+  if (x0 >= 0) return x0;
+  if (x1 >= 0) return x1;
+  return -1;
+}
+
+static double ray_min(double x, double y) {   /* smaller non-negative of the two */
+  if (x < 0) return y;
+  if (y < 0) return x;
+  return x < y ? x : y;
+}
+
+/* ray against the top surface of one triangle (Moeller-Trumbore, both faces) */
+static double ray_triangle(const double* o, const double* v, const double* a,
+                           const double* b, const double* c) {
+  double e1[3], e2[3], pv[3], tv[3], qv[3];
+  for (int k = 0; k < 3; k++) { e1[k] = b[k] - a[k]; e2[k] = c[k] - a[k]; tv[k] = o[k] - a[k]; }
+  cross3(pv, v, e2);
+  double det = dot3(e1, pv);
+  if (fabs(det) < MINVAL) return -1;
+  double u = dot3(tv, pv) / det;
+  if (u < 0 || u > 1) return -1;
+  cross3(qv, tv, e1);
+  double w = dot3(v, qv) / det;
+  if (w < 0 || u + w > 1) return -1;
+  double t = dot3(e2, qv) / det;
+  return t >= 0 ? t : -1;
+}
+
+static int hf_cell(double u, double rad, double dd, int nn) {
+  double f = floor((u + rad) / dd);
+  if (f < 0) f = 0;
+  if (f > nn - 2) f = nn - 2;
+  return (int)f;
+}
+
+/* ray (origin o, unit direction v, field frame) against the height field: the box is
+ * entered through a wall or the bottom (solid), or the surface is hit further on.  The
+ * grid is swept slab by slab along the axis the ray advances fastest on. */
+static double ray_hfield(const HField* h, const double* o, const double* v) {
+  double lo[3] = {-h->rx, -h->ry, -h->base}, hi[3] = {h->rx, h->ry, h->zs};
+  double t0 = 0, t1 = 1e300;
+  int axis0 = -1;
+  for (int k = 0; k < 3; k++) {
+    if (fabs(v[k]) < MINVAL) {
+      if (o[k] < lo[k] || o[k] > hi[k]) return -1;
+      continue;
+    }
+    double ta = (lo[k] - o[k]) / v[k], tb = (hi[k] - o[k]) / v[k];
+    if (ta > tb) { double s = ta; ta = tb; tb = s; }
+    if (ta > t0) { t0 = ta; axis0 = k; }
+    if (tb < t1) t1 = tb;
+  }
+  if (t0 > t1) return -1;
+  double best = -1;
+  if (axis0 >= 0 && !(axis0 == 2 && v[2] < 0)) {
+    /* entering through a wall (below the local surface) or through the bottom */
+    if (axis0 == 2) return t0;
+    double x = o[0] + t0 * v[0], y = o[1] + t0 * v[1], z = o[2] + t0 * v[2];
+    int c = hf_cell(x, h->rx, h->dx, h->ncol), r = hf_cell(y, h->ry, h->dy, h->nrow);
+    double fx = (x + h->rx) / h->dx - c, fy = (y + h->ry) / h->dy - r;
+    fx = fx < 0 ? 0 : (fx > 1 ? 1 : fx); fy = fy < 0 ? 0 : (fy > 1 ? 1 : fy);
+    const double* dt = h->data;
+    double z00 = dt[r * h->ncol + c], z10 = dt[r * h->ncol + c + 1],
+           z01 = dt[(r + 1) * h->ncol + c], z11 = dt[(r + 1) * h->ncol + c + 1];
+    double zsurf = fx >= fy ? z00 + fx * (z10 - z00) + fy * (z11 - z10)
+                            : z00 + fx * (z11 - z01) + fy * (z01 - z00);
+    if (z <= zsurf * h->zs) return t0;
+  }
+  int am = fabs(v[0]) >= fabs(v[1]) ? 0 : 1, an = 1 - am;
+  double radm = am == 0 ? h->rx : h->ry, radn = am == 0 ? h->ry : h->rx;
+  double ddm = am == 0 ? h->dx : h->dy, ddn = am == 0 ? h->dy : h->dx;
+  int nm = am == 0 ? h->ncol : h->nrow, nn = am == 0 ? h->nrow : h->ncol;
+  int i0 = hf_cell(o[am] + t0 * v[am], radm, ddm, nm);
+  int i1 = hf_cell(o[am] + t1 * v[am], radm, ddm, nm);
+  int step = i1 >= i0 ? 1 : -1;
+  for (int i = i0; i != i1 + step; i += step) {
+    double ta = t0, tb = t1;
+    if (fabs(v[am]) >= MINVAL) {
+      double sa = (i * ddm - radm - o[am]) / v[am], sb = ((i + 1) * ddm - radm - o[am]) / v[am];
+      if (sa > sb) { double s = sa; sa = sb; sb = s; }
+      if (sa > ta) ta = sa;
+      if (sb < tb) tb = sb;
+    }
+    if (ta > tb) continue;
+    double na = o[an] + ta * v[an], nb = o[an] + tb * v[an];
+    int j0 = hf_cell(na < nb ? na : nb, radn, ddn, nn), j1 = hf_cell(na < nb ? nb : na, radn, ddn, nn);
+    for (int j = j0; j <= j1; j++) {
+      int r = am == 0 ? j : i, c = am == 0 ? i : j;
+      for (int half = 0; half < 2; half++) {
+        double a[3], b[3], cc[3];
+        hf_triangle(h, r, c, half, a, b, cc);
+        best = ray_min(best, ray_triangle(o, v, a, b, cc));
+      }
+    }
+    if (best >= 0) return best;
+  }
+  return -1;
+}
+
+static double ray_geom(const OModel* m, const OData* d, int g, const double* pnt,
+                       const double* vec) {
+  const double *pos = d->geom_xpos + 3 * g, *R = d->geom_xmat + 9 * g;
+  const double* sz = m->geom_size + 3 * g;
+  double dif[3] = {pnt[0] - pos[0], pnt[1] - pos[1], pnt[2] - pos[2]}, o[3], v[3];
+  matT_vec3(o, R, dif);
+  matT_vec3(v, R, vec);
+  switch (m->geom_type[g]) {
+    case GEOM_PLANE: {
+      if (v[2] > -MINVAL) return -1;            /* only the front face, from above */
+      double x = -o[2] / v[2];
+      if (x < 0) return -1;
+      double p0 = o[0] + x * v[0], p1 = o[1] + x * v[1];
+      if ((sz[0] <= 0 || fabs(p0) <= sz[0]) && (sz[1] <= 0 || fabs(p1) <= sz[1])) return x;
+      return -1;
+    }
+    case GEOM_HFIELD: {
+      HField h;
+      hf_init(m, d, m->geom_dataid[g], &h);
+      return ray_hfield(&h, o, v);
+    }
+    case GEOM_SPHERE:
+      return ray_quad(dot3(v, v), dot3(v, o), dot3(o, o) - sz[0] * sz[0]);
+    case GEOM_CAPSULE: {
+      /* side wall where |z| <= half length, else the end spheres */
+      double a = v[0] * v[0] + v[1] * v[1], b = v[0] * o[0] + v[1] * o[1],
+             c = o[0] * o[0] + o[1] * o[1] - sz[0] * sz[0];
+      double x = ray_quad(a, b, c);
+      if (x >= 0 && fabs(o[2] + x * v[2]) > sz[1]) x = -1;
+      for (int sgn = -1; sgn <= 1; sgn += 2) {
+        double oz = o[2] - sgn * sz[1];
+        double dd = dot3(v, v), db = v[0] * o[0] + v[1] * o[1] + v[2] * oz,
+               dc = o[0] * o[0] + o[1] * o[1] + oz * oz - sz[0] * sz[0];
+        double det = db * db - dd * dc;
+        if (det < 0) continue;
+        det = sqrt(det);
+        /* the near root if it lies on the cap's outer half, else the far one */
+        for (int root = 0; root < 2; root++) {
+          double xs = (root == 0 ? -db - det : -db + det) / dd;
+          if (xs >= 0 && sgn * (o[2] + xs * v[2]) >= sz[1]) { x = ray_min(x, xs); break; }
+        }
+      }
+      return x;
+    }
+    case GEOM_ELLIPSOID: {
+      double os[3] = {o[0] / sz[0], o[1] / sz[1], o[2] / sz[2]};
+      double vs[3] = {v[0] / sz[0], v[1] / sz[1], v[2] / sz[2]};
+      return ray_quad(dot3(vs, vs), dot3(vs, os), dot3(os, os) - 1);
+    }
+    case GEOM_CYLINDER: {
+      double a = v[0] * v[0] + v[1] * v[1], b = v[0] * o[0] + v[1] * o[1],
+             c = o[0] * o[0] + o[1] * o[1] - sz[0] * sz[0];
+      double x = ray_quad(a, b, c);
+      if (x >= 0 && fabs(o[2] + x * v[2]) > sz[1]) x = -1;
+      if (fabs(v[2]) >= MINVAL)
+        for (int sgn = -1; sgn <= 1; sgn += 2) {
+          double xs = (sgn * sz[1] - o[2]) / v[2];
+          if (xs < 0) continue;
+          double p0 = o[0] + xs * v[0], p1 = o[1] + xs * v[1];
+          if (p0 * p0 + p1 * p1 <= sz[0] * sz[0]) x = ray_min(x, xs);
+        }
+      return x;
+    }
+    case GEOM_BOX: {
+      double x = -1;
+      for (int k = 0; k < 3; k++) {
+        if (fabs(v[k]) < MINVAL) continue;
+        for (int sgn = -1; sgn <= 1; sgn += 2) {
+          double xs = (sgn * sz[k] - o[k]) / v[k];
+          if (xs < 0) continue;
+          int k1 = (k + 1) % 3, k2 = (k + 2) % 3;
+          if (fabs(o[k1] + xs * v[k1]) <= sz[k1] && fabs(o[k2] + xs * v[k2]) <= sz[k2])
+            x = ray_min(x, xs);
+        }
+      }
+      return x;
+    }
+  }
+  return -1;
+}
+
+static double o_ray(const OModel* m, const OData* d, const double* pnt, const double* vec,
+                    int bodyexclude) {
+  double best = -1;
+  for (int g = 0; g < m->ngeom; g++) {
+    if (m->geom_bodyid[g] == bodyexclude) continue;
+    best = ray_min(best, ray_geom(m, d, g, pnt, vec));
+  }
+  return best;
+}
+
 static int inside_site(const OModel* m, const OData* d, int s, const double* p) {
   double dif[3] = {p[0] - d->site_xpos[3 * s], p[1] - d->site_xpos[3 * s + 1],
                    p[2] - d->site_xpos[3 * s + 2]}, l[3];
@@ -1952,6 +2452,12 @@ static void o_sensors(const OModel* m, OData* d, int stage) {
       case SENS_JOINTVEL: out[0] = d->qvel[m->jnt_dofadr[id]]; break;
       case SENS_ACTUATORFRC: out[0] = d->actuator_force[id]; break;
       case SENS_SUBTREECOM: memcpy(out, d->subtree_com + 3 * id, 24); break;
+      case SENS_RANGEFINDER: {
+        double zax[3];
+        geom_axis(d->site_xmat + 9 * id, 2, zax);
+        out[0] = o_ray(m, d, d->site_xpos + 3 * id, zax, m->site_bodyid[id]);
+        break;
+      }
       case SENS_SUBTREELINVEL: memcpy(out, d->subtree_linvel + 3 * id, 24); break;
       case SENS_FRAMEPOS:
         obj_frame(m, d, m->sensor_objtype[s], id, &pos, &mat, &body);

@@ -64,6 +64,7 @@ BP_FN1(asin, OP_TRANS) BP_FN1(atan, OP_TRANS) BP_FN1(tanh, OP_TRANS) BP_FN1(asin
 #undef BP_FN1
 static inline cdouble fabs(cdouble a) { return cdouble(::fabs(a.v)); }
 static inline cdouble floor(cdouble a) { return cdouble(::floor(a.v)); }
+static inline cdouble ceil(cdouble a) { return cdouble(::ceil(a.v)); }
 static inline cdouble atan2(cdouble a, cdouble b) { o_ops[OP_TRANS]++; return cdouble(::atan2(a.v, b.v)); }
 static inline cdouble pow(cdouble a, cdouble b) { o_ops[OP_TRANS]++; return cdouble(::pow(a.v, b.v)); }
 static inline cdouble fmax(cdouble a, cdouble b) { o_ops[OP_CMP]++; return cdouble(::fmax(a.v, b.v)); }

@@ -61,6 +61,32 @@ def random_states(m, nenv, seed, vel_scale=1.0, spread=1.0):
   return qpos, qvel, ctrl
 
 
+def escape_terrain(rng, res=201, half_size=30.0):
+  """suite/quadruped.py:366-380 (Escape.initialize_episode): sinusoidal bowl times smooth
+  random bumps, as float32 like mjModel.hfield_data."""
+  from scipy import ndimage
+  row_grid, col_grid = np.ogrid[-1:1:res * 1j, -1:1:res * 1j]
+  radius = np.clip(np.sqrt(col_grid ** 2 + row_grid ** 2), .04, 1)
+  bowl_shape = .5 - np.cos(2 * np.pi * radius) / 2
+  bump_res = int(2 * half_size / 2)
+  bumps = rng.uniform(.15, 1, (bump_res, bump_res))
+  smooth_bumps = ndimage.zoom(bumps, res / float(bump_res))
+  return (bowl_shape * smooth_bumps).ravel().astype(np.float32)
+
+
+def terrain_states(m, qpos, hfield, seed):
+  """Moves the free root of every env to a random spot of its terrain, a little above
+  or slightly inside the surface, so that height-field contacts of every kind occur."""
+  rng = np.random.RandomState(seed + 77)
+  nrow, ncol = int(m.hfield_nrow[0]), int(m.hfield_ncol[0])
+  rx, ry, zs, _ = m.hfield_size[0]
+  for e in range(qpos.shape[0]):
+    x, y = rng.uniform(-0.8 * rx, 0.8 * rx), rng.uniform(-0.8 * ry, 0.8 * ry)
+    c = int(round((x + rx) / (2 * rx) * (ncol - 1))); r = int(round((y + ry) / (2 * ry) * (nrow - 1)))
+    z = float(hfield[e, r * ncol + c]) * zs
+    qpos[e, 0:3] = x, y, z + rng.uniform(0.05, 0.45)
+
+
 def rel_err(a, b):
   """max |a-b| scaled by the magnitude of the reference array b (>= 1e-12)."""
   a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
@@ -132,14 +158,27 @@ def run_parity(domain, nenv=32, nsteps=3, seed=0, njmax=0, nconmax=0, check_step
   if mutate:
     mutate(m)
   qpos, qvel, ctrl = random_states(m, nenv, seed, vel_scale, spread)
+  hfield = None
+  if int(m.nhfielddata) > 0:       # one terrain per env (quadruped.py:371-382)
+    hfield = np.stack([escape_terrain(np.random.RandomState(seed + 1000 + e))
+                       for e in range(nenv)])
+    terrain_states(m, qpos, hfield, seed)
   model = binding.Model(m)
   batch = binding.Batch(model, nenv, njmax, nconmax, lanes)
   nvp = m.nv | 1
   batch.write("qpos", qpos); batch.write("qvel", qvel); batch.write("ctrl", ctrl)
+  if hfield is not None:
+    batch.write_hfield(hfield)
+  if njmax or nconmax:             # the oracle sizes its buffers from the model
+    m = m.copy()
+    if njmax: m.arrays["njmax"][:] = njmax
+    if nconmax: m.arrays["nconmax"][:] = nconmax
   om = OracleModel(m)
   oracles = []
   for e in range(nenv):
     o = Oracle(om)
+    if hfield is not None:
+      o.hfield_data[:] = hfield[e]
     o.reset()
     o.qpos[:] = qpos[e]; o.qvel[:] = qvel[e]; o.ctrl[:] = ctrl[e]
     oracles.append(o)

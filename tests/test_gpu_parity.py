@@ -18,7 +18,8 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-8
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 HUMANOID_SIZES = dict(njmax=120, nconmax=40)
-SIZES = {"humanoid": HUMANOID_SIZES, "quadruped": dict(njmax=120, nconmax=40)}
+SIZES = {"humanoid": HUMANOID_SIZES, "quadruped": dict(njmax=120, nconmax=40),
+         "quadruped_escape": dict(njmax=300, nconmax=64)}
 
 
 def _assert_parity(res):
@@ -29,7 +30,8 @@ def _assert_parity(res):
 
 
 @pytest.mark.parametrize("domain", ["pendulum", "cartpole", "acrobot", "cheetah", "walker",
-                                    "hopper", "finger", "humanoid", "quadruped"])
+                                    "hopper", "finger", "humanoid", "quadruped",
+                                    "quadruped_escape"])
 @pytest.mark.parametrize("lanes", [32, 8, 4, 1])
 def test_every_field_matches_oracle(domain, lanes):
   kw = SIZES.get(domain, {})
@@ -40,7 +42,7 @@ def test_every_field_matches_oracle(domain, lanes):
   _assert_parity(res)
   if domain == "finger":
     assert max(stats["ncon"]) > 0.05
-  if domain in ("cheetah", "walker", "hopper", "humanoid", "quadruped"):
+  if domain in ("cheetah", "walker", "hopper", "humanoid", "quadruped", "quadruped_escape"):
     assert max(stats["ncon"]) > 0.5 and max(stats["iter"]) > 0.5     # contacts exercised
 
 

@@ -72,6 +72,11 @@ def quadruped():
   m.save(path)
   print("quadruped nq", m.nq, "nv", m.nv, "nu", m.nu, "na", m.na, "nbody", m.nbody, "ngeom",
         m.ngeom, "ntendon", m.ntendon, "neq", m.neq, "nsensordata", m.nsensordata)
+  # quadruped.py:121-130 escape: floor 40, terrain height field, rangefinders
+  m = C.compile_xml(quadruped_xml(floor_size=40, terrain=True, rangefinders=True), _Dir())
+  m.save(os.path.join(OUT, "quadruped_escape.npz"))
+  print("quadruped_escape ngeom", m.ngeom, "npair", m.npair, "nhfpair", m.nhfpair,
+        "nhfielddata", m.nhfielddata, "nsensordata", m.nsensordata)
 
 
 if __name__ == "__main__":

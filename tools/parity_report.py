@@ -17,7 +17,9 @@ def main():
   with open(os.path.join(ROOT, "gpurun_out", "parity_report.txt"), "w") as f:
     for d, lanes in [(d, l) for d in domains for l in lanes_list]:
       t = time.time()
-      kw = dict(njmax=120, nconmax=40) if d == "humanoid" else {}
+      kw = dict(njmax=120, nconmax=40) if d in ("humanoid", "quadruped") else {}
+      if d == "quadruped_escape":
+        kw = dict(njmax=300, nconmax=64)
       try:
         res, stats = PU.run_parity(d, nenv=64, nsteps=20, seed=1,
                                    check_steps=[0, 1, 5, 20], lanes=lanes, **kw)
