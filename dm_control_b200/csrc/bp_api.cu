@@ -188,10 +188,14 @@ static int derive(bp_model* m) {
   if (M.neq > 0) { auto& ea = I(m, "eq_active"); for (int e = 0; e < M.neq; e++) M.neq_active += ea[e] != 0; }
   put_i(m, "dof_actadr", aadr); put_i(m, "dof_actlist", alist);
   M.need_subtreevel = 0; M.need_rnepost_stage = 0;
+  M.nhinge = 0; M.nsens_ft = 0; M.nsens_rf = 0;
+  for (int j = 0; j < M.njnt; j++) M.nhinge += jt[j] == JNT_HINGE;
   auto& st = I(m, "sensor_type");
   auto& ss = I(m, "sensor_needstage");
   for (int s = 0; s < M.nsensor; s++) {
     if (st[s] == SENS_SUBTREELINVEL) M.need_subtreevel = 1;
+    if (st[s] == SENS_FORCE || st[s] == SENS_TORQUE) M.nsens_ft++;
+    if (st[s] == SENS_RANGEFINDER) M.nsens_rf++;
     if (st[s] == SENS_ACCELEROMETER || st[s] == SENS_FORCE || st[s] == SENS_TORQUE)
       M.need_rnepost_stage = ss[s];
   }

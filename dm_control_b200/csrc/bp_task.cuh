@@ -15,7 +15,7 @@
 
 enum { TASK_NONE = 0, TASK_CARTPOLE = 1, TASK_ACROBOT = 2, TASK_PENDULUM = 3,
        TASK_CHEETAH = 4, TASK_WALKER = 5, TASK_HUMANOID = 6, TASK_HOPPER = 7,
-       TASK_REACHER = 8, TASK_FINGER = 9 };
+       TASK_REACHER = 8, TASK_FINGER = 9, TASK_QUADRUPED = 10, TASK_QUADRUPED_ESCAPE = 11 };
 enum { SIG_GAUSSIAN = 0, SIG_LINEAR = 1, SIG_QUADRATIC = 2 };
 
 // read-only strided window of one environment's image (see bp_math.cuh for layouts)
@@ -201,6 +201,45 @@ static __device__ __noinline__ void bp_task_eval(const BpParams& P, const BpTask
         o[k++] = log1p(sens[T.ip[7]]); o[k++] = log1p(sens[T.ip[8]]);
       }
       r = sens[T.ip[4]] <= -T.fp[0] ? 1.0 : 0.0;
+      break;
+    }
+    case TASK_QUADRUPED: case TASK_QUADRUPED_ESCAPE: {
+      // suite/quadruped.py:163-216,280-288 (observations), 291-306,343-357 (Move reward),
+      // 399-418 (Escape).  ip: torso body, velocimeter adr, accelerometer adr, gyro adr,
+      // first force/torque adr, workspace site, first rangefinder adr;
+      // fp: desired speed, cos(deviation angle), terrain half size
+      const int torso = T.ip[0];
+      const ImgView R = xmat.at(9 * torso), vel = sens.at(T.ip[1]);
+      const bool escape = T.kind == TASK_QUADRUPED_ESCAPE;
+      if (o) {
+        const ImgView act = d.at(L.act);
+        for (int j = 0; j < m.njnt; j++) if (m.jnt_type[j] == JNT_HINGE) o[k++] = qpos[m.jnt_qposadr[j]];
+        for (int j = 0; j < m.njnt; j++) if (m.jnt_type[j] == JNT_HINGE) o[k++] = qvel[m.jnt_dofadr[j]];
+        for (int i = 0; i < m.na; i++) o[k++] = act[i];
+        for (int i = 0; i < 3; i++) o[k++] = vel[i];
+        o[k++] = R[8];
+        for (int i = 0; i < 3; i++) o[k++] = sens[T.ip[2] + i];
+        for (int i = 0; i < 3; i++) o[k++] = sens[T.ip[3] + i];
+        for (int i = 0; i < 3 * m.nsens_ft; i++) o[k++] = asinh(sens[T.ip[4] + i]);
+        if (escape) {
+          for (int cidx = 0; cidx < 3; cidx++)
+            o[k++] = -(xpos[3 * torso] * R[cidx] + xpos[3 * torso + 1] * R[3 + cidx] +
+                       xpos[3 * torso + 2] * R[6 + cidx]);
+          for (int i = 0; i < m.nsens_rf; i++) {
+            double rf = sens[T.ip[6] + i];
+            o[k++] = rf == -1.0 ? 1.0 : tanh(rf);
+          }
+        }
+      }
+      const double dev = T.fp[1];
+      double upright = tolerance(R[8], dev, INF, 1 + dev, SIG_LINEAR, 0);
+      if (escape) {
+        const ImgView ws = d.at(L.site_xpos + 3 * T.ip[5]);
+        double dist = sqrt(ws[0] * ws[0] + ws[1] * ws[1] + ws[2] * ws[2]);
+        r = upright * tolerance(dist, T.fp[2], INF, T.fp[2], SIG_LINEAR, 0);
+      } else {
+        r = upright * tolerance(vel[0], T.fp[0], INF, T.fp[0], SIG_LINEAR, .5);
+      }
       break;
     }
     default: break;

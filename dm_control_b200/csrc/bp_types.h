@@ -106,6 +106,7 @@ struct BpModel {
   const unsigned long long* body_dofmask;  // bit i set <=> dof i moves the body
   int nlevel, ndoflevel, nfric, nlim, ntri, nvp, neq_active;  // nvp: odd row stride >= nv
   int any_damping, need_subtreevel, need_rnepost_stage;  // sensor prerequisites
+  int nhinge, nsens_ft, nsens_rf;   // hinge joints; force + torque sensors; rangefinders
 };
 
 // ---- per-environment data image ---------------------------------------------

@@ -198,6 +198,14 @@ class BatchedPhysics:
     """Run-time model edit shared by all envs (core.py:581-620, finger.py:140-142)."""
     self._dev_model.set_field(name, value)
 
+  def set_hfield(self, data, env0=0):
+    """Per-env `model.hfield_data` (quadruped.py:381): [n, nhfielddata], stored as float32
+    like mjModel's."""
+    self._batch.write_hfield(np.asarray(data, dtype=np.float32), env0)
+
+  def hfield(self):
+    return self._batch.read_hfield()
+
   @contextlib.contextmanager
   def disable(self, *flags):
     """model.disable('actuation', ...) context of core.py:581-620."""

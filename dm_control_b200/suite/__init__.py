@@ -14,7 +14,7 @@ import numpy as np
 
 from dm_control_b200 import control
 from dm_control_b200 import model as M
-from dm_control_b200.physics import BatchedPhysics
+from dm_control_b200.physics import BatchedPhysics, PhysicsError
 from dm_control_b200.suite import tasks as T
 
 _MODELS = os.path.join(os.path.dirname(os.path.abspath(__file__)), "models")
@@ -51,7 +51,7 @@ class Task:
     self.tdef = tdef
     self._seed = random
     self._rngs = None
-    self.scalar_obs = {"height", "head_height"}
+    self.scalar_obs = {"height", "head_height", "torso_upright"}
 
   def bind(self, physics):
     m = physics.model
@@ -115,6 +115,9 @@ class Task:
     elif d == "walker":           # suite/walker.py:118-129
       for e, rng in enumerate(self._rngs):
         _randomize_limited_and_rotational_joints(m, qpos[e], rng)
+    elif d == "quadruped":
+      self._initialize_quadruped(physics, t)
+      return
     elif d in ("humanoid", "finger"):
       # suite/humanoid.py:152-166, suite/finger.py:139-144,201-212: rejection on contacts
       if d == "finger":           # finger.py:142 (spin): the same edit for every env
@@ -131,6 +134,54 @@ class Task:
       return
     physics.data.qpos = qpos
     physics.data.qvel = qvel
+
+
+def _escape_terrain(m, rng):
+  """suite/quadruped.py:366-380: sinusoidal bowl times smooth random bumps."""
+  from scipy import ndimage
+  res = int(m.hfield_nrow[0])
+  assert res == int(m.hfield_ncol[0])
+  row_grid, col_grid = np.ogrid[-1:1:res * 1j, -1:1:res * 1j]
+  radius = np.clip(np.sqrt(col_grid ** 2 + row_grid ** 2), .04, 1)
+  bowl_shape = .5 - np.cos(2 * np.pi * radius) / 2
+  terrain_size = 2 * m.hfield_size[0, 0]
+  bump_res = int(terrain_size / 2)                    # _TERRAIN_BUMP_SCALE = 2
+  bumps = rng.uniform(.15, 1, (bump_res, bump_res))   # _TERRAIN_SMOOTHNESS = .15
+  smooth_bumps = ndimage.zoom(bumps, res / float(bump_res))
+  return (bowl_shape * smooth_bumps).ravel()
+
+
+def _initialize_quadruped(self, physics, task_name):
+  """suite/quadruped.py:324-334 (Move) and 360-397 (Escape) for every env at once; the
+  height search of `_find_non_contacting_height` (quadruped.py:245-277) raises all envs
+  that still touch something by 1 cm per pass."""
+  m, n = physics.model, physics.nenv
+  if task_name == "escape":
+    terrain = np.stack([_escape_terrain(m, rng) for rng in self._rngs])
+    physics.set_hfield(terrain)
+  orientation = np.stack([rng.randn(4) for rng in self._rngs])
+  orientation /= np.linalg.norm(orientation, axis=1, keepdims=True)
+  root = m.jnt_qposadr[m.name2id("root", "joint")]
+  qpos = np.tile(np.asarray(m.qpos0, dtype=np.float64), (n, 1))
+  z = np.zeros(n)                       # start embedded in the floor
+  todo = np.ones(n, dtype=bool)
+  for _ in range(10001):
+    qpos[:, root:root + 3] = np.stack([np.zeros(n), np.zeros(n), z], axis=1)
+    qpos[:, root + 3:root + 7] = orientation
+    physics.data.qpos = qpos
+    physics.data.qvel = np.zeros((n, m.nv))
+    try:
+      physics.after_reset()
+    except PhysicsError:
+      pass                              # a full contact buffer: keep raising (quadruped.py:266-270)
+    todo &= physics.data.ncon > 0
+    if not todo.any():
+      return
+    z[todo] += 0.01
+  raise RuntimeError("Failed to find a non-contacting configuration.")
+
+
+Task._initialize_quadruped = _initialize_quadruped
 
 
 def _load_model(name):

@@ -13,6 +13,7 @@ import numpy as np
 # task kinds of csrc/bp_task.cu
 NONE, CARTPOLE, ACROBOT, PENDULUM, CHEETAH, WALKER, HUMANOID, HOPPER = range(8)
 FINGER = 9
+QUADRUPED, QUADRUPED_ESCAPE = 10, 11
 
 TaskDef = collections.namedtuple(
     "TaskDef", "domain task model kind time_limit control_timestep params obs")
@@ -75,6 +76,41 @@ def _finger(m):
   return [_sens_adr(m, n) for n in names], [15.0]           # finger.py:38 _SPIN_VELOCITY
 
 
+def _quadruped(speed=0.0, deviation_angle=0.0, escape=False):
+  """quadruped.py:291-306 _upright_reward, 343-357 Move.get_reward, 406-418 Escape."""
+  def f(m):
+    from dm_control_b200 import model as M
+    types = np.asarray(m.sensor_type)
+    ft = np.flatnonzero((types == M.SENS["force"]) | (types == M.SENS["torque"]))
+    adr = np.asarray(m.sensor_adr)
+    # force_torque() reads these sensors in model order; the kernel reads one window
+    assert np.array_equal(adr[ft], adr[ft[0]] + 3 * np.arange(len(ft)))
+    ip = [m.name2id("torso", "body"), _sens_adr(m, "velocimeter"), _sens_adr(m, "imu_accel"),
+          _sens_adr(m, "imu_gyro"), int(adr[ft[0]]), m.name2id("workspace", "site"), 0]
+    fp = [speed, float(np.cos(np.deg2rad(deviation_angle))), 0.0]
+    if escape:
+      rf = np.flatnonzero(types == M.SENS["rangefinder"])
+      assert np.array_equal(adr[rf], adr[rf[0]] + np.arange(len(rf)))
+      ip[6] = int(adr[rf[0]])
+      fp[2] = float(m.hfield_size[0, 0])          # quadruped.py:408 terrain_size
+    return ip, fp
+  return f
+
+
+def _obs_quadruped(escape):
+  def f(m):
+    from dm_control_b200 import model as M
+    nh = int(np.sum(np.asarray(m.jnt_type) == M.JNT_HINGE))
+    types = np.asarray(m.sensor_type)
+    nft = int(np.sum((types == M.SENS["force"]) | (types == M.SENS["torque"])))
+    obs = [("egocentric_state", 2 * nh + m.na), ("torso_velocity", 3), ("torso_upright", 1),
+           ("imu", 6), ("force_torque", 3 * nft)]
+    if escape:
+      obs += [("origin", 3), ("rangefinder", int(np.sum(types == M.SENS["rangefinder"])))]
+    return obs
+  return f
+
+
 def _obs_hopper(m):
   return [("position", m.nq - 1), ("velocity", m.nv), ("touch", 2)]
 
@@ -114,6 +150,15 @@ _TASKS = [
     # episode and are not served)
     TaskDef("finger", "spin", "finger", FINGER, 20, .02, _finger,
             lambda m: [("position", 4), ("velocity", 3), ("touch", 2)]),
+    # quadruped.py:36-44: 20 s, control timestep .02, walk speed 0.5, run speed 5; escape
+    # uses the terrain model and a 20 degree upright deviation (fetch: walls, ball and
+    # condim-6 contacts are not served)
+    TaskDef("quadruped", "walk", "quadruped", QUADRUPED, 20, .02, _quadruped(0.5),
+            _obs_quadruped(False)),
+    TaskDef("quadruped", "run", "quadruped", QUADRUPED, 20, .02, _quadruped(5.0),
+            _obs_quadruped(False)),
+    TaskDef("quadruped", "escape", "quadruped_escape", QUADRUPED_ESCAPE, 20, .02,
+            _quadruped(0.0, 20.0, True), _obs_quadruped(True)),
     # humanoid.py:28-35: 25 s, control timestep .025, speeds 0 / 1 / 10
     TaskDef("humanoid", "stand", "humanoid", HUMANOID, 25, .025, _humanoid(0.0), None),
     TaskDef("humanoid", "walk", "humanoid", HUMANOID, 25, .025, _humanoid(1.0), None),

@@ -20,8 +20,9 @@ SERVED = [("cartpole", "swingup"), ("cartpole", "swingup_sparse"), ("cartpole", 
           ("cartpole", "balance_sparse"), ("acrobot", "swingup"), ("acrobot", "swingup_sparse"),
           ("pendulum", "swingup"), ("cheetah", "run"), ("walker", "stand"), ("walker", "walk"),
           ("walker", "run"), ("hopper", "stand"), ("hopper", "hop"), ("finger", "spin"),
-          ("humanoid", "stand"), ("humanoid", "walk"), ("humanoid", "run")]
-FIELDS = ("qpos", "qvel", "ctrl", "xmat", "xpos", "xipos", "site_xpos", "sensordata")
+          ("humanoid", "stand"), ("humanoid", "walk"), ("humanoid", "run"),
+          ("quadruped", "walk"), ("quadruped", "run"), ("quadruped", "escape")]
+FIELDS = ("qpos", "qvel", "act", "ctrl", "xmat", "xpos", "xipos", "site_xpos", "sensordata")
 
 
 def _fields(physics):
@@ -37,7 +38,7 @@ def test_obs_reward_kernel_matches_task_oracle(domain, task):
   env = suite.load(domain, task, task_kwargs={"random": 11}, nenv=n)
   tdef = T.REGISTRY[(domain, task)]
   ip, fp = tdef.params(env.physics.model)
-  speed = fp[0] if domain in ("walker", "humanoid") else None
+  speed = fp[0] if domain in ("walker", "humanoid", "quadruped") else None
   rng = np.random.RandomState(3)
   ts = env.reset()
   spec = env.action_spec()
