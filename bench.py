@@ -37,14 +37,20 @@ MODELS = os.path.join(ROOT, "dm_control_b200", "suite", "models")
 ALGO = {"cheetah": dict(bytes=648, flops=2.0e4), "humanoid": dict(bytes=2048, flops=2.3e5),
         "walker": dict(bytes=704, flops=1.8e4), "cartpole": dict(bytes=176, flops=1.0e4),
         "acrobot": dict(bytes=184, flops=1.0e4), "pendulum": dict(bytes=112, flops=1.5e3),
-        "finger": dict(bytes=264, flops=1.0e4)}
+        "finger": dict(bytes=264, flops=1.0e4),
+        # quadruped-escape: 8 * (nu + 2 (nq + 2 nv + na + 1) + nobs + 2) with nobs = 101;
+        # per-env terrain (161 604 B float32) is resident and touched sparsely: not counted
+        "quadruped": dict(bytes=2200, flops=7.0e5)}
 # SURVEY.md 8d binding rule: once the oracle's op counter exists its per-config mean
 # replaces the estimates (tools/count_ops.py -> profiles/r1_oracle_opcount.json)
 FLOPS_SOURCE = {}
+FLOPS_BY_TASK = {}
 try:
   with open(os.path.join(ROOT, "profiles", "r1_oracle_opcount.json")) as _f:
     for _name, _rec in json.load(_f).items():
       _dom = _name.split("-", 1)[0]
+      FLOPS_BY_TASK[_name] = (_rec["flops_per_substep"],
+                              "oracle op counter, %s (%s)" % (_name, _rec["sample"]))
       if _dom in ALGO and _dom not in FLOPS_SOURCE:
         ALGO[_dom]["flops"] = _rec["flops_per_substep"]
         FLOPS_SOURCE[_dom] = "oracle op counter, %s (%s)" % (_name, _rec["sample"])
@@ -57,7 +63,10 @@ WORKLOADS = {"cheetah-run": dict(nenv=16384, njmax=64, nconmax=16, settle=200, l
              "cartpole-swingup": dict(nenv=4096, njmax=4, nconmax=1, settle=0, lanes=8),
              "acrobot-swingup": dict(nenv=4096, njmax=1, nconmax=1, settle=0, lanes=8),
              "pendulum-swingup": dict(nenv=4096, njmax=1, nconmax=1, settle=0, lanes=1),
-             "finger-spin": dict(nenv=8192, njmax=24, nconmax=6, settle=50, lanes=4)}
+             "finger-spin": dict(nenv=8192, njmax=24, nconmax=6, settle=50, lanes=4),
+             # BASELINE.json configs[4]: 65536 envs over 8 GPUs = 8192 per GPU
+             "quadruped-escape": dict(nenv=8192, njmax=184, nconmax=42, settle=100, lanes=16),
+             "quadruped-walk": dict(nenv=8192, njmax=120, nconmax=40, settle=100, lanes=16)}
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the step kernel from the
 # committed `ncu --set full` captures (profiles/), keyed by (task, lanes, envs per GPU)
 NCU_TRAFFIC = {("cheetah-run", 8, 16384): (518.1e6, "profiles/r1m_cheetah_g8.summary.txt"),
@@ -82,6 +91,38 @@ def initial_qpos(m, nenv, seed):
       lo, hi = m.jnt_range[j]
       qpos[:, m.jnt_qposadr[j]] = rng.uniform(lo, hi, nenv)
   return qpos
+
+
+def initial_state(name, m, nenv, seed):
+  """qpos of the bench batch.  quadruped: the model's standing pose with hinge angles
+  spread over the inner half of their ranges, dropped from 0.3 m above its rest height
+  with a random heading (random angles at rest height would start 0.3 m inside the
+  ground; the task itself starts from a non-contacting height, quadruped.py:245-277)."""
+  if not name.startswith("quadruped"):
+    return initial_qpos(m, nenv, seed)
+  rng = np.random.RandomState(seed)
+  qpos = np.tile(m.qpos0, (nenv, 1))
+  for j in range(m.njnt):
+    if m.jnt_type[j] >= 2 and m.jnt_limited[j]:
+      lo, hi = m.jnt_range[j]
+      mid, half = 0.5 * (lo + hi), 0.25 * (hi - lo)
+      qpos[:, m.jnt_qposadr[j]] = rng.uniform(mid - half, mid + half, nenv)
+  yaw = rng.uniform(0, 2 * np.pi, nenv)
+  qpos[:, 2] += 0.3
+  qpos[:, 3] = np.cos(yaw / 2); qpos[:, 4:6] = 0; qpos[:, 6] = np.sin(yaw / 2)
+  return qpos
+
+
+def initial_hfield(name, m, nenv, seed):
+  """quadruped-escape: one terrain per env, drawn as Escape.initialize_episode does
+  (quadruped.py:366-382) from RandomState(seed + env); float32 like mjModel.hfield_data."""
+  if int(m.nhfielddata) == 0:
+    return None
+  from dm_control_b200 import suite
+  out = np.empty((nenv, int(m.nhfielddata)), dtype=np.float32)
+  for e in range(nenv):
+    out[e] = suite._escape_terrain(m, np.random.RandomState(seed + e))
+  return out
 
 
 class ClockSampler:
@@ -139,7 +180,10 @@ def make_batch(name, nenv, device, seed):
   batch = binding.Batch(model, nenv, w["njmax"], w["nconmax"], LANES["value"] or w["lanes"])
   ip, fp = tdef.params(m)
   batch.set_task(tdef.kind, ip, fp)
-  batch.write("qpos", initial_qpos(m, nenv, seed))
+  batch.write("qpos", initial_state(name, m, nenv, seed))
+  hf = initial_hfield(name, m, nenv, seed)
+  if hf is not None:
+    batch.write_hfield(hf)
   batch.forward(disable_actuation=True)
   nsub = T.n_sub_steps(tdef, m)
   return tdef, m, model, batch, nsub
@@ -231,12 +275,13 @@ def cpu_run(name, nenv, steps, threads, seed=0):
   nsub = T.n_sub_steps(tdef, m)
   om = oracle_py.OracleModel(m)
   rng = np.random.RandomState(seed)
-  qpos = initial_qpos(m, nenv, seed)
+  qpos = initial_state(name, m, nenv, seed)
   qvel = np.zeros((nenv, m.nv)); act = np.zeros((nenv, max(m.na, 1)))
   warm = np.zeros((nenv, m.nv)); tm = np.zeros(nenv)
   ctrl = rng.uniform(-1, 1, (steps, nenv, m.nu))
+  hf = initial_hfield(name, m, nenv, seed)
   t0 = time.perf_counter()
-  oracle_py.run_batch(om, qpos, qvel, act, warm, tm, ctrl, steps, nsub, threads)
+  oracle_py.run_batch(om, qpos, qvel, act, warm, tm, ctrl, steps, nsub, threads, hfield=hf)
   dt = time.perf_counter() - t0
   return nenv * steps / dt, dt, nsub
 
@@ -358,7 +403,11 @@ def main():
   algo_bytes = ALGO[domain]["bytes"] * nenv
   achieved = algo_bytes / (ms_kernel * 1e-3) / 1e9
   fp64_peak = binding.fp64_peak_tflops(local)
-  fl = ALGO[domain]["flops"] * r["nsub"] * nenv / (ms_kernel * 1e-3) / 1e12
+  flops_sub, flops_src = FLOPS_BY_TASK.get(
+      name, (ALGO[domain]["flops"], FLOPS_SOURCE.get(domain, "SURVEY 8d contract estimate v0")))
+  algo_bytes = (2016 if name == "quadruped-walk" else ALGO[domain]["bytes"]) * nenv
+  achieved = algo_bytes / (ms_kernel * 1e-3) / 1e9
+  fl = flops_sub * r["nsub"] * nenv / (ms_kernel * 1e-3) / 1e12
   traffic, traffic_src = NCU_TRAFFIC.get((name, r["lanes"], nenv), (None, None))
   line = {
       "metric": "env-steps/sec (%s)" % name, "value": value, "unit": "env-steps/s",
@@ -385,9 +434,8 @@ def main():
                    "image_bytes_per_launch": 2 * nenv * r["stride"] * 8},
       "roofline_fp64": {"bound": "fp64 vector pipe", "achieved": fl, "peak": fp64_peak,
                         "unit": "TFLOP/s", "frac": fl / fp64_peak,
-                        "flops_per_substep": ALGO[domain]["flops"],
-                        "flops_source": FLOPS_SOURCE.get(
-                            domain, "SURVEY 8d contract estimate v0"),
+                        "flops_per_substep": flops_sub,
+                        "flops_source": flops_src,
                         "note": "peak = DFMA microbenchmark in this run"},
       "physics_steps_per_s": value * r["nsub"],
       "warnings": r["warnings"], "finite": r["finite"], "stats": r["stats"],

@@ -386,26 +386,27 @@ static __device__ __noinline__ int bp_collide_prims(int t1, int t2, const double
 // vertex when owned); capsule: both end spheres + the segment's interior against the owned
 // edges; ellipsoid, cylinder: support point(s) along -n against the face + the owned vertex
 // against the solid.
-static __device__ __noinline__ int hf_tri_geom(int half, const double* a, const double* b,
-                                               const double* c, int gt, const double* gp,
-                                               const double* gR, const double* gs, double margin,
-                                               RawCon* out) {
+static __device__ __noinline__ int hf_tri_geom(const HField& h, int tid, const double* a,
+                                               const double* b, const double* c, int gt,
+                                               const double* gp, const double* gR,
+                                               const double* gs, double margin, RawCon* out) {
+  const int half = tid & 1;
   double ab[3], ac[3], nt[3];
   for (int k = 0; k < 3; k++) { ab[k] = b[k] - a[k]; ac[k] = c[k] - a[k]; }
   cross3(nt, ab, ac);
   normalize3(nt);
   int n = 0;
   if (gt == GEOM_SPHERE)
-    return hf_sphere_tri(half, a, b, c, nt, gp, gs[0], margin, nullptr, out[0]);
+    return hf_sphere_tri(h, tid, a, b, c, nt, gp, gs[0], margin, nullptr, out[0]);
   if (gt == GEOM_CAPSULE) {
     double ax[3] = {gR[2], gR[5], gR[8]}, e[3];
 #pragma unroll 1
     for (int sgn = 1; sgn >= -1; sgn -= 2) {
       for (int k = 0; k < 3; k++) e[k] = gp[k] + sgn * ax[k] * gs[1];
-      n += hf_sphere_tri(half, a, b, c, nt, e, gs[0], margin, ax, out[n]);
+      n += hf_sphere_tri(h, tid, a, b, c, nt, e, gs[0], margin, ax, out[n]);
     }
-    if (half == 0) n += hf_capsule_edge(gp, ax, gs[1], gs[0], a, b, 1, margin, out[n]);
-    n += hf_capsule_edge(gp, ax, gs[1], gs[0], c, a, 0, margin, out[n]);
+    if (half == 0) n += hf_capsule_edge(h, gp, ax, gs[1], gs[0], a, b, 1, margin, out[n]);
+    n += hf_capsule_edge(h, gp, ax, gs[1], gs[0], c, a, 0, margin, out[n]);
     return n;
   }
   if (gt == GEOM_ELLIPSOID) {
@@ -586,9 +587,11 @@ BP_STAGE void bp_collision(const C& c) {
         if (t < ntri) {
           const int cell = t >> 1, half = t & 1;
           double a[3], b[3], cc[3];
-          hf_triangle(h, r0 + cell / ncol, c0 + cell % ncol, half, a, b, cc);
+          const int rr = r0 + cell / ncol, cl = c0 + cell % ncol;
+          hf_triangle(h, rr, cl, half, a, b, cc);
           if (!(fmax(a[2], fmax(b[2], cc[2])) < gp[2] - rb))
-            n = hf_tri_geom(half, a, b, cc, gt, gp, gR, gs, margin, raw);
+            n = hf_tri_geom(h, ((rr * h.ncol + cl) << 1) | half, a, b, cc, gt, gp, gR, gs, margin,
+                            raw);
         }
         int tot, start = base + group_excl_scan(c, n, &tot);
         base += tot;

@@ -41,6 +41,29 @@ __device__ __forceinline__ void hf_triangle(const HField& h, int r, int c, int h
   else { hf_vertex(h, r + 1, c + 1, b); hf_vertex(h, r + 1, c, cc); }
 }
 
+__device__ __forceinline__ int hf_cell(double u, double rad, double dd, int nn) {
+  double f = floor((u + rad) / dd);
+  if (f < 0) f = 0;
+  if (f > nn - 2) f = nn - 2;
+  return (int)f;
+}
+
+// elevation of the surface over (x, y); tid = id of the triangle that holds the point,
+// (cell index << 1) | half
+static __device__ __noinline__ double hf_surface(const HField& h, double x, double y, int& tid) {
+  int c = hf_cell(x, h.rx, h.dx, h.ncol), r = hf_cell(y, h.ry, h.dy, h.nrow);
+  double fx = (x + h.rx) / h.dx - c, fy = (y + h.ry) / h.dy - r;
+  fx = clampd(fx, 0.0, 1.0); fy = clampd(fy, 0.0, 1.0);
+  const float* dt = h.data;
+  double z00 = __ldg(dt + r * h.ncol + c), z10 = __ldg(dt + r * h.ncol + c + 1),
+         z01 = __ldg(dt + (r + 1) * h.ncol + c), z11 = __ldg(dt + (r + 1) * h.ncol + c + 1);
+  int half = fx >= fy ? 0 : 1;
+  double zsurf = half == 0 ? z00 + fx * (z10 - z00) + fy * (z11 - z10)
+                           : z00 + fx * (z11 - z01) + fy * (z01 - z00);
+  tid = ((r * h.ncol + c) << 1) | half;
+  return zsurf * h.zs;
+}
+
 // closest point of triangle abc to p; returns the Voronoi region: 0 face, 1 / 2 / 3 vertex
 // a / b / c, 4 edge ab, 5 edge bc, 6 edge ca
 static __device__ __noinline__ int tri_closest(const double* p, const double* a, const double* b,
@@ -88,20 +111,25 @@ __device__ __forceinline__ void raw_set(RawCon& o, double dist, const double* po
   for (int k = 0; k < 3; k++) { o.pos[k] = pos[k]; o.n[k] = n[k]; o.hint[k] = hint ? hint[k] : 0.0; }
 }
 
-// sphere (centre q, radius r) against one triangle with unit normal nt
-static __device__ __noinline__ int hf_sphere_tri(int half, const double* a, const double* b,
-                                                 const double* c, const double* nt, const double* q,
-                                                 double r, double margin, const double* hint,
-                                                 RawCon& out) {
+// sphere (centre q, radius r) against triangle `tid` with unit normal nt.  A centre above
+// the surface touches the closest point of the triangle (face always, edges / vertices when
+// owned); a centre that has sunk below the surface is pushed out through the face of the
+// one triangle that holds it, so no sideways normals from neighbouring edges
+static __device__ __noinline__ int hf_sphere_tri(const HField& h, int tid, const double* a,
+                                                 const double* b, const double* c, const double* nt,
+                                                 const double* q, double r, double margin,
+                                                 const double* hint, RawCon& out) {
   double aq[3] = {q[0] - a[0], q[1] - a[1], q[2] - a[2]}, cl[3], nrm[3], dist;
   double s = dot3(nt, aq);
-  int reg = tri_closest(q, a, b, c, cl);
-  if (s < 0) {                       // centre under the surface: through the face only
-    if (reg != 0) return 0;
+  int holder;
+  if (q[2] < hf_surface(h, q[0], q[1], holder)) {
+    if (holder != tid) return 0;
     for (int k = 0; k < 3; k++) nrm[k] = nt[k];
     dist = s - r;
   } else {
-    if (!((half ? HF_OWN1 : HF_OWN0) >> reg & 1)) return 0;
+    if (s < 0) return 0;
+    int reg = tri_closest(q, a, b, c, cl);
+    if (!(((tid & 1) ? HF_OWN1 : HF_OWN0) >> reg & 1)) return 0;
     double dv[3] = {q[0] - cl[0], q[1] - cl[1], q[2] - cl[2]};
     double dd = norm3(dv);
     if (dd < BP_MINVAL) { for (int k = 0; k < 3; k++) nrm[k] = nt[k]; }
@@ -117,8 +145,9 @@ static __device__ __noinline__ int hf_sphere_tri(int half, const double* a, cons
 
 // interior of the capsule's segment (p +- l ax) against the edge e0 -> e1; a hit at the
 // start vertex counts when vertex0 is set (the edge that owns its first vertex)
-static __device__ __noinline__ int hf_capsule_edge(const double* p, const double* ax, double l,
-                                                   double r, const double* e0, const double* e1,
+static __device__ __noinline__ int hf_capsule_edge(const HField& h, const double* p,
+                                                   const double* ax, double l, double r,
+                                                   const double* e0, const double* e1,
                                                    int vertex0, double margin, RawCon& out) {
   double d1[3], d2[3], rr[3];
   for (int k = 0; k < 3; k++) {
@@ -142,6 +171,8 @@ static __device__ __noinline__ int hf_capsule_edge(const double* p, const double
   }
   double dd = norm3(dv);
   if (dd < BP_MINVAL || dv[2] <= 0) return 0;      // the axis has sunk below the edge
+  int holder;
+  if (c1[2] < hf_surface(h, c1[0], c1[1], holder)) return 0;     // ... or the surface
   double dist = dd - r;
   if (dist > margin) return 0;
   double nrm[3], pos[3];
@@ -199,12 +230,6 @@ __device__ __forceinline__ double ray_triangle(const double* o, const double* v,
   double t = dot3(e2, qv) / det;
   return t >= 0 ? t : -1;
 }
-__device__ __forceinline__ int hf_cell(double u, double rad, double dd, int nn) {
-  double f = floor((u + rad) / dd);
-  if (f < 0) f = 0;
-  if (f > nn - 2) f = nn - 2;
-  return (int)f;
-}
 
 // ray (origin o, unit direction v, field frame): the box is entered through a wall or the
 // bottom (solid), or the surface is hit further on; the grid is swept slab by slab along
@@ -229,15 +254,8 @@ static __device__ __noinline__ double ray_hfield(const HField& h, const double* 
   if (axis0 >= 0 && !(axis0 == 2 && v[2] < 0)) {
     if (axis0 == 2) return t0;
     double x = o[0] + t0 * v[0], y = o[1] + t0 * v[1], z = o[2] + t0 * v[2];
-    int c = hf_cell(x, h.rx, h.dx, h.ncol), r = hf_cell(y, h.ry, h.dy, h.nrow);
-    double fx = (x + h.rx) / h.dx - c, fy = (y + h.ry) / h.dy - r;
-    fx = clampd(fx, 0.0, 1.0); fy = clampd(fy, 0.0, 1.0);
-    const float* dt = h.data;
-    double z00 = dt[r * h.ncol + c], z10 = dt[r * h.ncol + c + 1],
-           z01 = dt[(r + 1) * h.ncol + c], z11 = dt[(r + 1) * h.ncol + c + 1];
-    double zsurf = fx >= fy ? z00 + fx * (z10 - z00) + fy * (z11 - z10)
-                            : z00 + fx * (z11 - z01) + fy * (z01 - z00);
-    if (z <= zsurf * h.zs) return t0;
+    int holder;
+    if (z <= hf_surface(h, x, y, holder)) return t0;
   }
   const int am = fabs(v[0]) >= fabs(v[1]) ? 0 : 1, an = 1 - am;
   const double radm = am == 0 ? h.rx : h.ry, radn = am == 0 ? h.ry : h.rx;

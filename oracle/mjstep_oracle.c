@@ -1091,6 +1091,29 @@ static void hf_triangle(const HField* h, int r, int c, int half, double* a, doub
   else { hf_vertex(h, r + 1, c + 1, b); hf_vertex(h, r + 1, c, cc); }
 }
 
+static int hf_cell(double u, double rad, double dd, int nn) {
+  double f = floor((u + rad) / dd);
+  if (f < 0) f = 0;
+  if (f > nn - 2) f = nn - 2;
+  return (int)f;
+}
+
+/* elevation of the surface over (x, y); *tid = id of the triangle that holds the point,
+ * (cell index << 1) | half */
+static double hf_surface(const HField* h, double x, double y, int* tid) {
+  int c = hf_cell(x, h->rx, h->dx, h->ncol), r = hf_cell(y, h->ry, h->dy, h->nrow);
+  double fx = (x + h->rx) / h->dx - c, fy = (y + h->ry) / h->dy - r;
+  fx = fx < 0 ? 0 : (fx > 1 ? 1 : fx); fy = fy < 0 ? 0 : (fy > 1 ? 1 : fy);
+  const double* dt = h->data;
+  double z00 = dt[r * h->ncol + c], z10 = dt[r * h->ncol + c + 1],
+         z01 = dt[(r + 1) * h->ncol + c], z11 = dt[(r + 1) * h->ncol + c + 1];
+  int half = fx >= fy ? 0 : 1;
+  double zsurf = half == 0 ? z00 + fx * (z10 - z00) + fy * (z11 - z10)
+                           : z00 + fx * (z11 - z01) + fy * (z01 - z00);
+  if (tid) *tid = ((r * h->ncol + c) << 1) | half;
+  return zsurf * h->zs;
+}
+
 /* closest point of triangle abc to p (Voronoi regions of the triangle's features);
  * returns the region: 0 face, 1 / 2 / 3 vertex a / b / c, 4 edge ab, 5 edge bc, 6 edge ca */
 static int tri_closest(const double* p, const double* a, const double* b, const double* c,
@@ -1141,19 +1164,24 @@ static void raw_set(RawCon* o, double dist, const double* pos, const double* n,
   if (hint) memcpy(o->frame + 3, hint, 24);
 }
 
-/* sphere (centre q, radius r) against one triangle with unit normal nt */
-static int hf_sphere_tri(int half, const double* a, const double* b, const double* c,
-                         const double* nt, const double* q, double r, double margin,
-                         const double* hint, RawCon* out) {
+/* sphere (centre q, radius r) against triangle `tid` with unit normal nt.  A centre above
+ * the surface touches the closest point of the triangle (face always, edges / vertices
+ * when owned); a centre that has sunk below the surface is pushed out through the face of
+ * the one triangle that holds it, so no sideways normals from neighbouring edges */
+static int hf_sphere_tri(const HField* h, int tid, const double* a, const double* b,
+                         const double* c, const double* nt, const double* q, double r,
+                         double margin, const double* hint, RawCon* out) {
   double aq[3] = {q[0] - a[0], q[1] - a[1], q[2] - a[2]}, cl[3], nrm[3], dist;
   double s = dot3(nt, aq);
-  int reg = tri_closest(q, a, b, c, cl);
-  if (s < 0) {                       /* centre under the surface: through the face only */
-    if (reg != 0) return 0;
+  int holder;
+  if (q[2] < hf_surface(h, q[0], q[1], &holder)) {
+    if (holder != tid) return 0;
     memcpy(nrm, nt, 24);
     dist = s - r;
   } else {
-    if (!((half ? HF_OWN1 : HF_OWN0) >> reg & 1)) return 0;
+    if (s < 0) return 0;
+    int reg = tri_closest(q, a, b, c, cl);
+    if (!(((tid & 1) ? HF_OWN1 : HF_OWN0) >> reg & 1)) return 0;
     double dv[3] = {q[0] - cl[0], q[1] - cl[1], q[2] - cl[2]};
     double dd = norm3(dv);
     if (dd < MINVAL) memcpy(nrm, nt, 24);
@@ -1169,9 +1197,9 @@ static int hf_sphere_tri(int half, const double* a, const double* b, const doubl
 
 /* interior of the capsule's segment (p +- l ax) against the edge e0 -> e1; a hit at the
  * start vertex counts when vertex0 is set (the edge that owns its first vertex) */
-static int hf_capsule_edge(const double* p, const double* ax, double l, double r,
-                           const double* e0, const double* e1, int vertex0, double margin,
-                           RawCon* out) {
+static int hf_capsule_edge(const HField* h, const double* p, const double* ax, double l,
+                           double r, const double* e0, const double* e1, int vertex0,
+                           double margin, RawCon* out) {
   double d1[3], d2[3], rr[3];
   for (int k = 0; k < 3; k++) {
     d1[k] = 2 * l * ax[k]; d2[k] = e1[k] - e0[k];
@@ -1196,6 +1224,7 @@ static int hf_capsule_edge(const double* p, const double* ax, double l, double r
   }
   double dd = norm3(dv);
   if (dd < MINVAL || dv[2] <= 0) return 0;         /* the axis has sunk below the edge */
+  if (c1[2] < hf_surface(h, c1[0], c1[1], NULL)) return 0;       /* ... or the surface */
   double dist = dd - r;
   if (dist > margin) return 0;
   double nrm[3], pos[3];
@@ -1222,25 +1251,26 @@ static int hf_point_face(const double* a, const double* b, const double* c, cons
 /* geom (type gt, centre gp, frame gR row-major, sizes gs; all in the field's frame) against
  * one triangle; returns the number of contacts written (at most 4), normals pointing
  * from the terrain to the geom */
-static int hf_tri_geom(int half, const double* a, const double* b, const double* c, int gt,
-                       const double* gp, const double* gR, const double* gs, double margin,
-                       RawCon* out) {
+static int hf_tri_geom(const HField* h, int tid, const double* a, const double* b,
+                       const double* c, int gt, const double* gp, const double* gR,
+                       const double* gs, double margin, RawCon* out) {
+  const int half = tid & 1;
   double ab[3], ac[3], nt[3];
   for (int k = 0; k < 3; k++) { ab[k] = b[k] - a[k]; ac[k] = c[k] - a[k]; }
   cross3(nt, ab, ac);
   normalize3(nt);
   int n = 0;
   if (gt == GEOM_SPHERE)
-    return hf_sphere_tri(half, a, b, c, nt, gp, gs[0], margin, NULL, out);
+    return hf_sphere_tri(h, tid, a, b, c, nt, gp, gs[0], margin, NULL, out);
   if (gt == GEOM_CAPSULE) {
     double ax[3], e[3];
     geom_axis(gR, 2, ax);
     for (int sgn = 1; sgn >= -1; sgn -= 2) {
       for (int k = 0; k < 3; k++) e[k] = gp[k] + sgn * ax[k] * gs[1];
-      n += hf_sphere_tri(half, a, b, c, nt, e, gs[0], margin, ax, out + n);
+      n += hf_sphere_tri(h, tid, a, b, c, nt, e, gs[0], margin, ax, out + n);
     }
-    if (half == 0) n += hf_capsule_edge(gp, ax, gs[1], gs[0], a, b, 1, margin, out + n);
-    n += hf_capsule_edge(gp, ax, gs[1], gs[0], c, a, 0, margin, out + n);
+    if (half == 0) n += hf_capsule_edge(h, gp, ax, gs[1], gs[0], a, b, 1, margin, out + n);
+    n += hf_capsule_edge(h, gp, ax, gs[1], gs[0], c, a, 0, margin, out + n);
     return n;
   }
   if (gt == GEOM_ELLIPSOID) {
@@ -1474,8 +1504,8 @@ static int collide_hfield(const OModel* m, OData* d, int g1, int g2, double marg
         hf_triangle(&h, r, c, half, a, b, cc);
         if (fmax(a[2], fmax(b[2], cc[2])) < gp[2] - rb) continue;
         RawCon raw[4];
-        int n = hf_tri_geom(half, a, b, cc, m->geom_type[g2], gp, gR, m->geom_size + 3 * g2,
-                            margin, raw);
+        int n = hf_tri_geom(&h, ((r * h.ncol + c) << 1) | half, a, b, cc, m->geom_type[g2],
+                            gp, gR, m->geom_size + 3 * g2, margin, raw);
         for (int i = 0; i < n; i++) {
           RawCon w = raw[i];
           mat_vec3(w.pos, R1, raw[i].pos);
@@ -2238,13 +2268,6 @@ static double ray_triangle(const double* o, const double* v, const double* a,
   return t >= 0 ? t : -1;
 }
 
-static int hf_cell(double u, double rad, double dd, int nn) {
-  double f = floor((u + rad) / dd);
-  if (f < 0) f = 0;
-  if (f > nn - 2) f = nn - 2;
-  return (int)f;
-}
-
 /* ray (origin o, unit direction v, field frame) against the height field: the box is
  * entered through a wall or the bottom (solid), or the surface is hit further on.  The
  * grid is swept slab by slab along the axis the ray advances fastest on. */
@@ -2268,15 +2291,7 @@ static double ray_hfield(const HField* h, const double* o, const double* v) {
     /* entering through a wall (below the local surface) or through the bottom */
     if (axis0 == 2) return t0;
     double x = o[0] + t0 * v[0], y = o[1] + t0 * v[1], z = o[2] + t0 * v[2];
-    int c = hf_cell(x, h->rx, h->dx, h->ncol), r = hf_cell(y, h->ry, h->dy, h->nrow);
-    double fx = (x + h->rx) / h->dx - c, fy = (y + h->ry) / h->dy - r;
-    fx = fx < 0 ? 0 : (fx > 1 ? 1 : fx); fy = fy < 0 ? 0 : (fy > 1 ? 1 : fy);
-    const double* dt = h->data;
-    double z00 = dt[r * h->ncol + c], z10 = dt[r * h->ncol + c + 1],
-           z01 = dt[(r + 1) * h->ncol + c], z11 = dt[(r + 1) * h->ncol + c + 1];
-    double zsurf = fx >= fy ? z00 + fx * (z10 - z00) + fy * (z11 - z10)
-                            : z00 + fx * (z11 - z01) + fy * (z01 - z00);
-    if (z <= zsurf * h->zs) return t0;
+    if (z <= hf_surface(h, x, y, NULL)) return t0;
   }
   int am = fabs(v[0]) >= fabs(v[1]) ? 0 : 1, an = 1 - am;
   double radm = am == 0 ? h->rx : h->ry, radn = am == 0 ? h->ry : h->rx;
@@ -2735,6 +2750,7 @@ void o_physics_step(const OModel* m, OData* d) {
 typedef struct {
   const OModel* m; int lo, hi, nsteps, nsub, ctrl_per_step, nenv;
   double *qpos, *qvel, *act, *warm, *time; const double* ctrl;
+  const double* hfield;   /* [nenv][nhfielddata] per-env elevation data, or NULL */
 } BatchJob;
 
 static void* batch_worker(void* arg) {
@@ -2743,6 +2759,8 @@ static void* batch_worker(void* arg) {
   OData* d = od_create(m);
   for (int e = j->lo; e < j->hi; e++) {
     o_reset(m, d);
+    if (j->hfield)
+      memcpy(d->hfield, j->hfield + (size_t)e * m->nhfielddata, 8 * (size_t)m->nhfielddata);
     memcpy(d->qpos, j->qpos + (size_t)e * m->nq, 8 * m->nq);
     memcpy(d->qvel, j->qvel + (size_t)e * m->nv, 8 * m->nv);
     if (m->na) memcpy(d->act, j->act + (size_t)e * m->na, 8 * m->na);
@@ -2764,19 +2782,28 @@ static void* batch_worker(void* arg) {
   return NULL;
 }
 
-void o_run_batch(const OModel* m, int nenv, int nsteps, int nsub, double* qpos,
-                 double* qvel, double* act, double* warm, double* time,
-                 const double* ctrl, int ctrl_per_step, int nthreads) {
+void o_run_batch_hf(const OModel* m, int nenv, int nsteps, int nsub, double* qpos,
+                    double* qvel, double* act, double* warm, double* time,
+                    const double* ctrl, int ctrl_per_step, int nthreads,
+                    const double* hfield) {
   if (nthreads < 1) nthreads = 1;
   if (nthreads > nenv) nthreads = nenv;
   pthread_t* th = (pthread_t*)malloc(sizeof(pthread_t) * nthreads);
   BatchJob* jobs = (BatchJob*)malloc(sizeof(BatchJob) * nthreads);
   for (int t = 0; t < nthreads; t++) {
     BatchJob j = {m, (int)((long)nenv * t / nthreads), (int)((long)nenv * (t + 1) / nthreads),
-                  nsteps, nsub, ctrl_per_step, nenv, qpos, qvel, act, warm, time, ctrl};
+                  nsteps, nsub, ctrl_per_step, nenv, qpos, qvel, act, warm, time, ctrl,
+                  hfield};
     jobs[t] = j;
     pthread_create(&th[t], NULL, batch_worker, &jobs[t]);
   }
   for (int t = 0; t < nthreads; t++) pthread_join(th[t], NULL);
   free(th); free(jobs);
+}
+
+void o_run_batch(const OModel* m, int nenv, int nsteps, int nsub, double* qpos,
+                 double* qvel, double* act, double* warm, double* time,
+                 const double* ctrl, int ctrl_per_step, int nthreads) {
+  o_run_batch_hf(m, nenv, nsteps, nsub, qpos, qvel, act, warm, time, ctrl, ctrl_per_step,
+                 nthreads, NULL);
 }

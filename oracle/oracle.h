@@ -51,6 +51,13 @@ void o_run_batch(const OModel* m, int nenv, int nsteps, int nsub,
                  double* time, const double* ctrl, int ctrl_per_step,
                  int nthreads);
 
+/* the same with per-env height-field elevation data [nenv][nhfielddata] (NULL: the
+ * model's), the batched form of quadruped.py:381 */
+void o_run_batch_hf(const OModel* m, int nenv, int nsteps, int nsub,
+                    double* qpos, double* qvel, double* act, double* warm,
+                    double* time, const double* ctrl, int ctrl_per_step,
+                    int nthreads, const double* hfield);
+
 #ifdef __cplusplus
 }
 #endif

@@ -48,6 +48,8 @@ def lib():
     L.o_run_batch.argtypes = [vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, dp,
                               dp, dp, dp, dp, dp, ctypes.c_int, ctypes.c_int]
     L.o_run_batch.restype = None
+    L.o_run_batch_hf.argtypes = L.o_run_batch.argtypes + [dp]
+    L.o_run_batch_hf.restype = None
     _lib = L
   return _lib
 
@@ -116,13 +118,18 @@ class Oracle:
 
 
 def run_batch(omodel, qpos, qvel, act, warm, time, ctrl, nsteps, nsub,
-              nthreads):
+              nthreads, hfield=None):
   """In-place batched stepping on host cores (cpu_baseline driver)."""
   dp = ctypes.POINTER(ctypes.c_double)
   nenv = qpos.shape[0]
   per_step = 1 if ctrl.ndim == 3 else 0
   arrs = [np.ascontiguousarray(a, dtype=np.float64) for a in
           (qpos, qvel, act, warm, time, ctrl)]
-  lib().o_run_batch(omodel.ptr, nenv, nsteps, nsub,
-                    *[a.ctypes.data_as(dp) for a in arrs], per_step, nthreads)
+  hf = None
+  if hfield is not None:
+    hf = np.ascontiguousarray(hfield, dtype=np.float64)
+    assert hf.shape == (nenv, int(omodel.flat.nhfielddata))
+  lib().o_run_batch_hf(omodel.ptr, nenv, nsteps, nsub,
+                       *[a.ctypes.data_as(dp) for a in arrs], per_step, nthreads,
+                       hf.ctypes.data_as(dp) if hf is not None else None)
   return arrs[:5]

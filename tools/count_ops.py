@@ -25,7 +25,8 @@ from oracle import oracle_py  # noqa: E402
 
 CLASSES = ("add", "mul", "div", "sqrt", "transcendental", "compare")
 WORK = {"cheetah-run": 200, "walker-walk": 500, "humanoid-run": 500, "hopper-hop": 200,
-        "finger-spin": 100, "cartpole-swingup": 0, "acrobot-swingup": 0, "pendulum-swingup": 0}
+        "finger-spin": 100, "quadruped-walk": 400, "quadruped-escape": 400,
+        "cartpole-swingup": 0, "acrobot-swingup": 0, "pendulum-swingup": 0}
 
 
 def main(nenv=32, steps=200):
@@ -42,13 +43,16 @@ def main(nenv=32, steps=200):
   for name, settle in WORK.items():
     tdef, m = bench.load_task(name)
     nsub = T.n_sub_steps(tdef, m)
-    qpos = bench.initial_qpos(m, nenv, 0)
+    qpos = bench.initial_state(name, m, nenv, 0)
+    hf = bench.initial_hfield(name, m, nenv, 0)
     om = oracle_py.OracleModel(m)
     rng = np.random.RandomState(1)
     tot = np.zeros(len(CLASSES))
     stats = np.zeros(3)
     for e in range(nenv):
       o = oracle_py.Oracle(om)
+      if hf is not None:
+        o.hfield_data[:] = hf[e]
       o.reset(); o.qpos[:] = qpos[e]; o.forward()
       for k in range(settle + steps):
         if k % nsub == 0:
