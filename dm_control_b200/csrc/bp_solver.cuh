@@ -7,6 +7,17 @@
 #define BP_SOLVER_CUH_
 #include "bp_math.cuh"
 
+#ifndef BP_NEWTON_GROUP
+#define BP_NEWTON_GROUP 0     // warps that share the per-iteration barrier (0: the block)
+#endif
+// barrier `id` over `nthreads` threads with an OR reduction of pred (bar.red.or)
+__device__ __forceinline__ bool bp_bar_or(int id, int nthreads, bool pred) {
+  int r;
+  asm volatile("{ .reg .pred p, q; setp.ne.u32 q, %1, 0; bar.red.or.pred p, %2, %3, q; "
+               "selp.u32 %0, 1, 0, p; }" : "=r"(r) : "r"((int)pred), "r"(id), "r"(nthreads) : "memory");
+  return r != 0;
+}
+
 // the Hessian and its factor are stored as a packed lower triangle, row i at i (i + 1) / 2
 #define PK(i, j) ((i) * ((i) + 1) / 2 + (j))
 
@@ -789,6 +800,17 @@ __device__ __forceinline__ void bp_fwd_constraint(const C& c) {
   st.done = true; st.nefc = 0;
   RUN(bp_solver_begin(c, st));
   if (c.lock && (BP_LOCKMASK >> 8 & 1)) {
+#if BP_NEWTON_GROUP > 0
+    // the Newton loop re-aligns groups of BP_NEWTON_GROUP warps (named barriers 1..15), not
+    // the whole block: a group iterates as long as ITS slowest environment
+    const int warp = threadIdx.x >> 5, nwarp = (blockDim.x + 31) >> 5;
+    const int grp = warp / BP_NEWTON_GROUP;
+    const int gcount = min(BP_NEWTON_GROUP, nwarp - grp * BP_NEWTON_GROUP) * 32;
+    while (bp_bar_or(1 + grp, gcount, !st.done)) {
+      if (!st.done) bp_solver_iterate(c, st);
+    }
+  } else if (false) {
+#endif
     while (__syncthreads_or(!st.done)) {
 #ifdef BP_TIMELINE
       if (blockIdx.x == 0 && threadIdx.x == 0) bp_timeline[16 + 8]++;
