@@ -21,14 +21,19 @@ def test_tolerance_restatement_matches_reference_rewards_py():
     np.testing.assert_allclose(got, want, rtol=0, atol=1e-15)
 
 
-@pytest.mark.parametrize("domain", ["pendulum", "cartpole", "cheetah", "finger", "humanoid"])
+@pytest.mark.parametrize("domain", ["pendulum", "cartpole", "cheetah", "finger", "humanoid",
+                                    "quadruped_escape"])
 def test_oracle_reproduces_committed_trajectories(domain):
   g = np.load(os.path.join(GOLDEN, "traj_%s.npz" % domain))
   m = PU.load_model(domain)
+  if "sizes" in g.files:
+    m.arrays["njmax"][:] = g["sizes"][0]; m.arrays["nconmax"][:] = g["sizes"][1]
   om = OracleModel(m)
   steps = list(g["steps"])
   for e in range(2):                         # two envs keep the CPU suite fast
     o = Oracle(om)
+    if "hfield_seed" in g.files:
+      o.hfield_data[:] = PU.escape_terrain(np.random.RandomState(int(g["hfield_seed"][e])))
     o.reset()
     o.qpos[:] = g["qpos0"][e]; o.qvel[:] = g["qvel0"][e]; o.ctrl[:] = g["ctrl"][e]
     o.forward()

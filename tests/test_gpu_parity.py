@@ -75,7 +75,8 @@ def test_ragged_env_count_and_masked_envs():
 
 
 @pytest.mark.parametrize("domain", ["pendulum", "cartpole", "acrobot", "cheetah", "walker",
-                                    "hopper", "finger", "humanoid"])
+                                    "hopper", "finger", "humanoid", "quadruped",
+                                    "quadruped_escape"])
 def test_golden_trajectories(domain):
   """Committed oracle trajectories (tests/golden, tools/make_golden.py) replayed on
   the GPU: ints exact, states to 1e-8 at steps 0/1/10; step 100 is reported as
@@ -84,10 +85,15 @@ def test_golden_trajectories(domain):
   g = np.load(os.path.join(GOLDEN, "traj_%s.npz" % domain))
   m = PU.load_model(domain)
   kw = HUMANOID_SIZES if domain == "humanoid" else {}
+  if "sizes" in g.files:
+    kw = dict(njmax=int(g["sizes"][0]), nconmax=int(g["sizes"][1]))
   model = binding.Model(m)
   nenv = g["qpos0"].shape[0]
   b = binding.Batch(model, nenv, kw.get("njmax", 0), kw.get("nconmax", 0), 4)
   b.write("qpos", g["qpos0"]); b.write("qvel", g["qvel0"]); b.write("ctrl", g["ctrl"])
+  if "hfield_seed" in g.files:
+    b.write_hfield(np.stack([PU.escape_terrain(np.random.RandomState(int(sd)))
+                             for sd in g["hfield_seed"]]))
   b.forward()
   steps = list(g["steps"])
   done = 0

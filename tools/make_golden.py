@@ -41,15 +41,28 @@ def rewards_fixture():
   print("rewards_tolerance.npz", out.shape)
 
 
-def traj_fixture(domain, nenv=8, steps=(0, 1, 10, 100)):
+def traj_fixture(domain, nenv=8, steps=(0, 1, 10, 100), sizes=None):
   import parity_util as PU
   from oracle.oracle_py import Oracle, OracleModel
   m = PU.load_model(domain)
   qpos, qvel, ctrl = PU.random_states(m, nenv, seed=11)
+  hfield, extra = None, {}
+  if int(m.nhfielddata) > 0:
+    # terrains are regenerated from their seeds (parity_util.escape_terrain), not stored
+    seeds = 11 + 1000 + np.arange(nenv)
+    hfield = np.stack([PU.escape_terrain(np.random.RandomState(int(sd))) for sd in seeds])
+    PU.terrain_states(m, qpos, hfield, 11)
+    extra["hfield_seed"] = seeds
+  if sizes:
+    m = m.copy()
+    m.arrays["njmax"][:] = sizes[0]; m.arrays["nconmax"][:] = sizes[1]
+    extra["sizes"] = np.array(sizes)
   om = OracleModel(m)
   rec = {k: [] for k in ("qpos", "qvel", "qacc", "ncon", "nefc", "solver_iter", "sensordata")}
   for e in range(nenv):
     o = Oracle(om)
+    if hfield is not None:
+      o.hfield_data[:] = hfield[e]
     o.reset()
     o.qpos[:] = qpos[e]; o.qvel[:] = qvel[e]; o.ctrl[:] = ctrl[e]
     o.forward()
@@ -63,7 +76,7 @@ def traj_fixture(domain, nenv=8, steps=(0, 1, 10, 100)):
     for k in rec:
       rec[k].append(np.stack(per[k]))
   np.savez_compressed(os.path.join(OUT, "traj_%s.npz" % domain), qpos0=qpos, qvel0=qvel,
-                      ctrl=ctrl, steps=np.array(steps),
+                      ctrl=ctrl, steps=np.array(steps), **extra,
                       **{k: np.stack(v) for k, v in rec.items()})     # [env][step][n]
   print("traj_%s.npz" % domain, rec["qpos"][0].shape)
 
@@ -112,4 +125,6 @@ if __name__ == "__main__":
   for d in ("pendulum", "cartpole", "acrobot", "cheetah", "walker", "hopper", "humanoid"):
     traj_fixture(d)
   traj_fixture("finger", nenv=32)       # a tenth of the random states start in contact
+  traj_fixture("quadruped", sizes=(120, 40))
+  traj_fixture("quadruped_escape", sizes=(300, 64))
   c1_trace()
