@@ -103,8 +103,19 @@ class Environment:
       self._reset_next_step = True
       return specs.TimeStep(np.full(n, specs.StepType.LAST, dtype=np.int32), reward,
                             np.ones(n), obs)
-    return specs.TimeStep(np.full(n, specs.StepType.MID, dtype=np.int32), reward,
-                          np.ones(n), obs)
+    step_type = np.full(n, specs.StepType.MID, dtype=np.int32)
+    discount = np.ones(n)
+    # control.py:110-117 get_termination: a discount ends the episode of THAT env (LAST,
+    # discount as returned).  The batch is reset as a whole once every env has terminated;
+    # until then a terminated env keeps stepping.
+    terminal = self._task.get_termination(self._physics, self._obs)
+    if terminal is not None:
+      done = ~np.isnan(terminal)
+      step_type[done] = specs.StepType.LAST
+      discount[done] = terminal[done]
+      if done.all():
+        self._reset_next_step = True
+    return specs.TimeStep(step_type, reward, discount, obs)
 
   def action_spec(self):
     return self._physics.action_spec()

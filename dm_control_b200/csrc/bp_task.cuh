@@ -15,7 +15,8 @@
 
 enum { TASK_NONE = 0, TASK_CARTPOLE = 1, TASK_ACROBOT = 2, TASK_PENDULUM = 3,
        TASK_CHEETAH = 4, TASK_WALKER = 5, TASK_HUMANOID = 6, TASK_HOPPER = 7,
-       TASK_REACHER = 8, TASK_FINGER = 9, TASK_QUADRUPED = 10, TASK_QUADRUPED_ESCAPE = 11 };
+       TASK_REACHER = 8, TASK_FINGER = 9, TASK_QUADRUPED = 10, TASK_QUADRUPED_ESCAPE = 11,
+       TASK_LQR = 12 };
 enum { SIG_GAUSSIAN = 0, SIG_LINEAR = 1, SIG_QUADRATIC = 2 };
 
 // read-only strided window of one environment's image (see bp_math.cuh for layouts)
@@ -201,6 +202,17 @@ static __device__ __noinline__ void bp_task_eval(const BpParams& P, const BpTask
         o[k++] = log1p(sens[T.ip[7]]); o[k++] = log1p(sens[T.ip[8]]);
       }
       r = sens[T.ip[4]] <= -T.fp[0] ? 1.0 : 0.0;
+      break;
+    }
+    case TASK_LQR: {        // suite/lqr.py:236-250; fp: control cost coefficient
+      if (o) {
+        for (int i = 0; i < m.nq; i++) o[k++] = qpos[i];
+        for (int i = 0; i < m.nv; i++) o[k++] = qvel[i];
+      }
+      double sc = 0, cc = 0;
+      for (int i = 0; i < m.nq; i++) sc += qpos[i] * qpos[i];
+      for (int i = 0; i < m.nu; i++) cc += ctrl[i] * ctrl[i];
+      r = 1 - (0.5 * sc + 0.5 * cc * T.fp[0]);
       break;
     }
     case TASK_QUADRUPED: case TASK_QUADRUPED_ESCAPE: {

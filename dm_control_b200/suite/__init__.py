@@ -72,6 +72,15 @@ class Task:
   def random(self):
     return self._rngs
 
+  def get_termination(self, physics, obs):
+    """base.Task.get_termination: None (no task-defined termination) or a [nenv] array,
+    NaN where the episode goes on and the terminal discount where it ends.  Only the LQR
+    levels terminate (suite/lqr.py:256-259: state norm below 1e-6 -> discount 0)."""
+    if self.tdef.domain != "lqr":
+      return None
+    from dm_control_b200.suite import lqr
+    return np.where(np.linalg.norm(obs, axis=1) < lqr.TERMINAL_TOL, 0.0, np.nan)
+
   def initialize_episode(self, physics):
     m = physics.model
     n = physics.nenv
@@ -118,6 +127,10 @@ class Task:
     elif d == "quadruped":
       self._initialize_quadruped(physics, t)
       return
+    elif d == "lqr":              # suite/lqr.py:229-233: a random point of a sphere
+      for e, rng in enumerate(self._rngs):
+        unit = rng.randn(m.nq)
+        qpos[e] = np.sqrt(2) * unit / np.linalg.norm(unit)
     elif d in ("humanoid", "finger"):
       # suite/humanoid.py:152-166, suite/finger.py:139-144,201-212: rejection on contacts
       if d == "finger":           # finger.py:142 (spin): the same edit for every env
@@ -199,7 +212,16 @@ def build_environment(domain_name, task_name, task_kwargs=None, environment_kwar
   tdef = T.REGISTRY[key]
   task_kwargs = dict(task_kwargs or {})
   environment_kwargs = dict(environment_kwargs or {})
-  m = _load_model(tdef.model)
+  seed = task_kwargs.get("random", None)
+  if domain_name == "lqr":
+    # lqr.py:93-101: the model itself is random (spring stiffness), drawn from the task's
+    # RandomState before the task uses it; one model serves every env of the batch
+    from dm_control_b200 import mjcf_compiler
+    from dm_control_b200.suite import lqr
+    model_rng = seed if isinstance(seed, np.random.RandomState) else np.random.RandomState(seed)
+    m = mjcf_compiler.compile_xml(lqr.make_model(tdef.model[0], tdef.model[1], model_rng))
+  else:
+    m = _load_model(tdef.model)
   physics = BatchedPhysics(m, nenv, device=device, lanes=lanes, njmax=njmax, nconmax=nconmax)
   task = Task(tdef, random=task_kwargs.pop("random", None))
   time_limit = task_kwargs.pop("time_limit", tdef.time_limit)

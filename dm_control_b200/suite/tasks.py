@@ -14,6 +14,7 @@ import numpy as np
 NONE, CARTPOLE, ACROBOT, PENDULUM, CHEETAH, WALKER, HUMANOID, HOPPER = range(8)
 FINGER = 9
 QUADRUPED, QUADRUPED_ESCAPE = 10, 11
+LQR = 12
 
 TaskDef = collections.namedtuple(
     "TaskDef", "domain task model kind time_limit control_timestep params obs")
@@ -159,6 +160,12 @@ _TASKS = [
             _obs_quadruped(False)),
     TaskDef("quadruped", "escape", "quadruped_escape", QUADRUPED_ESCAPE, 20, .02,
             _quadruped(0.0, 20.0, True), _obs_quadruped(True)),
+    # lqr.py:31-60: no time limit, control cost 0.1; "model" = (n_bodies, n_actuators): the
+    # model is generated from the task's seed when the environment is built (suite/lqr.py)
+    TaskDef("lqr", "lqr_2_1", (2, 1), LQR, float("inf"), None, lambda m: ([], [0.1]),
+            lambda m: [("position", m.nq), ("velocity", m.nv)]),
+    TaskDef("lqr", "lqr_6_2", (6, 2), LQR, float("inf"), None, lambda m: ([], [0.1]),
+            lambda m: [("position", m.nq), ("velocity", m.nv)]),
     # humanoid.py:28-35: 25 s, control timestep .025, speeds 0 / 1 / 10
     TaskDef("humanoid", "stand", "humanoid", HUMANOID, 25, .025, _humanoid(0.0), None),
     TaskDef("humanoid", "walk", "humanoid", HUMANOID, 25, .025, _humanoid(1.0), None),

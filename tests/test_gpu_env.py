@@ -21,7 +21,8 @@ SERVED = [("cartpole", "swingup"), ("cartpole", "swingup_sparse"), ("cartpole", 
           ("pendulum", "swingup"), ("cheetah", "run"), ("walker", "stand"), ("walker", "walk"),
           ("walker", "run"), ("hopper", "stand"), ("hopper", "hop"), ("finger", "spin"),
           ("humanoid", "stand"), ("humanoid", "walk"), ("humanoid", "run"),
-          ("quadruped", "walk"), ("quadruped", "run"), ("quadruped", "escape")]
+          ("quadruped", "walk"), ("quadruped", "run"), ("quadruped", "escape"),
+          ("lqr", "lqr_2_1"), ("lqr", "lqr_6_2")]
 FIELDS = ("qpos", "qvel", "act", "ctrl", "xmat", "xpos", "xipos", "site_xpos", "sensordata")
 
 
@@ -50,7 +51,8 @@ def test_obs_reward_kernel_matches_task_oracle(domain, task):
     np.testing.assert_allclose(obs_flat, want_obs, rtol=1e-12, atol=1e-13)
     if ts.reward is not None:
       np.testing.assert_allclose(ts.reward, want_r, rtol=1e-12, atol=1e-13)
-      assert ((ts.reward >= 0) & (ts.reward <= 1)).all()            # domains_test.py
+      if domain != "lqr":                                             # quadratic cost
+        assert ((ts.reward >= 0) & (ts.reward <= 1)).all()            # domains_test.py
     assert np.isfinite(obs_flat).all()
     a = rng.uniform(np.maximum(spec.minimum, -1), np.minimum(spec.maximum, 1),
                     (n, spec.shape[0]))
@@ -292,3 +294,29 @@ def test_config_c1_cartpole_trace_through_suite_load():
   assert abs(np.sum(g["reward"]) - 27.6088597862409) < 1e-9
   assert (ts.step_type == 2).all()                 # 1000 steps = the 10 s time limit
   env.close()
+
+
+@pytest.mark.parametrize("level", ["lqr_2_1", "lqr_6_2"])
+def test_lqr_optimal_policy_on_device(level):
+  """suite/lqr_test.py:30-59 through suite.load on the GPU: the Riccati-optimal policy's
+  measured cost equals .5 x0' P x0 (rtol 1e-3) for every env of the batch."""
+  import math
+  from dm_control_b200 import suite
+  from dm_control_b200.suite import lqr
+  n = 6
+  env = suite.load("lqr", level, task_kwargs={"random": 4}, nenv=n)
+  ts = env.reset()
+  m = env.physics.model
+  p, k, beta = lqr.solve(m, env.physics.data.qM[0])
+  n_steps = int(math.ceil(math.log10(1e-3) / math.log10(beta)))
+  x0 = np.hstack((ts.observation["position"], ts.observation["velocity"]))
+  total = np.zeros(n)
+  for _ in range(n_steps):
+    x = np.hstack((ts.observation["position"], ts.observation["velocity"]))
+    total += 1 - (ts.reward if ts.reward is not None else 0.0)
+    ts = env.step(x.dot(k.T))
+  expected = .5 * np.einsum("ni,ij,nj->n", x0, p, x0)
+  np.testing.assert_allclose(expected, total, rtol=1e-3)
+  assert len(np.unique(np.round(expected, 6))) == n          # six different start states
+  env.close()
+

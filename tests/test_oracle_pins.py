@@ -299,3 +299,38 @@ def test_compiler_object_ids_match_reference_expectations():
   assert m.names["body"][6] == "right_foot" and m.names["joint"][11] == "left_knee"
   with pytest.raises(ValueError, match="exists"):
     m.name2id("nonexistent_body_name", "body")
+
+
+@pytest.mark.parametrize("n_bodies,n_actuators", [(2, 1), (6, 2)])
+def test_lqr_riccati_cost(n_bodies, n_actuators):
+  """suite/lqr_test.py:30-59 (lqr_2_1, lqr_6_2): under the optimal linear policy of the
+  discrete Riccati equation (suite/lqr_solver.py, built from the engine's mass matrix,
+  joint stiffness and actuator moment) the measured total cost equals .5 x0' P x0 to
+  rtol 1e-3 -- a known answer that the mass matrix, spring forces, actuation and the
+  Euler integrator of the oracle have to reproduce together."""
+  import math
+  from dm_control_b200 import mjcf_compiler as C
+  from dm_control_b200.suite import lqr
+  rng = np.random.RandomState(3)
+  m = C.compile_xml(lqr.make_model(n_bodies, n_actuators, rng))
+  o = Oracle(m)
+  o.forward()
+  np.testing.assert_allclose(o.actuator_moment.reshape(m.nu, m.nv),
+                             np.eye(n_bodies)[:n_actuators], atol=0)
+  p, k, beta = lqr.solve(m, o.qM.copy())
+  tolerance = 1e-3
+  n_steps = int(math.ceil(math.log10(tolerance) / math.log10(beta)))
+  unit = rng.randn(m.nq)
+  o.reset()
+  o.qpos[:] = np.sqrt(2) * unit / np.linalg.norm(unit)        # lqr.py:229-233
+  o.forward()
+  x0 = np.hstack((o.qpos, o.qvel)).copy()
+  total_loss, reward = 0.0, None
+  for _ in range(n_steps):
+    x = np.hstack((o.qpos, o.qvel))
+    total_loss += 1 - (reward or 0.0)
+    o.ctrl[:] = k.dot(x)
+    o.step()
+    reward = 1 - (0.5 * o.qpos.dot(o.qpos) + 0.5 * o.ctrl.dot(o.ctrl) * lqr.CONTROL_COST_COEF)
+  np.testing.assert_allclose(.5 * x0.dot(p).dot(x0), total_loss, rtol=tolerance)
+
