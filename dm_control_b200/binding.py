@@ -56,6 +56,8 @@ _SIGNATURES = {
     "bp_set_mask": (_i32, [_vp, _vp]),
     "bp_hfield_write": (_i32, [_vp, _vp, _i64, _i64]),
     "bp_hfield_read": (_i32, [_vp, _vp, _i64, _i64]),
+    "bp_env_model_write": (_i32, [_vp, ctypes.c_char_p, _vp, _i64, _i64]),
+    "bp_env_model_read": (_i32, [_vp, ctypes.c_char_p, _vp, _i64, _i64]),
     "bp_step": (_i32, [_vp, _i32]),
     "bp_mj_step": (_i32, [_vp, _i32]),
     "bp_forward": (_i32, [_vp, _i32]),
@@ -203,6 +205,19 @@ class Batch:
     a = a.reshape(-1, cnt)
     if cnt:
       check(load().bp_field_write(self.ptr, name.encode(), _ptr(a), env0, a.shape[0]))
+
+  def write_env_model(self, name, value, env0=0):
+    """Per-env copy of a model array ("geom_pos", "site_pos"): value [n, count]."""
+    cnt = self.model.flat.arrays[name].size
+    a = np.ascontiguousarray(value, dtype=np.float64).reshape(-1, cnt)
+    check(load().bp_env_model_write(self.ptr, name.encode(), _ptr(a), env0, a.shape[0]))
+
+  def read_env_model(self, name, env0=0, n=None):
+    n = self.nenv - env0 if n is None else n
+    shape = self.model.flat.arrays[name].shape
+    out = np.empty((n,) + tuple(shape), dtype=np.float64)
+    check(load().bp_env_model_read(self.ptr, name.encode(), _ptr(out), env0, n))
+    return out
 
   def write_hfield(self, data, env0=0):
     """Per-env `model.hfield_data` (quadruped.py:381): data [n, nhfielddata] float32."""

@@ -325,6 +325,7 @@ struct bp_batch {
   void* stage = nullptr;           // dense staging buffer for host <-> image copies
   size_t stage_bytes = 0;
   float* hfield = nullptr;         // [nenv_alloc][nhfielddata] per-env elevation data
+  double *env_geom_pos = nullptr, *env_site_pos = nullptr;   // per-env model frames (lazy)
   BpTask task;
 };
 
@@ -423,6 +424,8 @@ extern "C" void bp_batch_free(bp_batch* b) {
   if (b->stream) { cudaStreamSynchronize(b->stream); cudaStreamDestroy(b->stream); }
   cudaFree(b->image); cudaFree(b->mask);
   if (b->hfield) cudaFree(b->hfield);
+  if (b->env_geom_pos) cudaFree(b->env_geom_pos);
+  if (b->env_site_pos) cudaFree(b->env_site_pos);
   if (b->ctrl_stage) cudaFree(b->ctrl_stage);
   if (b->stage) cudaFree(b->stage);
   if (b->obs_dev) cudaFree(b->obs_dev);
@@ -550,7 +553,45 @@ static BpParams make_params(bp_batch* b, int mode, int nsub, int disable_actuati
   P.nenv = b->nenv; P.mode = mode; P.nsub = nsub; P.disable_actuation = disable_actuation;
   P.stride = b->stride; P.interleave = b->interleave; P.lanes = b->lanes;
   P.hfield = b->hfield;
+  P.env_geom_pos = b->env_geom_pos; P.env_site_pos = b->env_site_pos;
   return P;
+}
+
+// Per-env copy of a model array that a task edits per episode.  Allocated on the first
+// write, every env starting from the model's values.
+static int env_model_copy(bp_batch* b, const char* name, double* host, int64_t env0, int64_t n,
+                          bool to_device) {
+  if (!b || !name || !host) return fail(BP_EINVAL, "null argument");
+  double** slot; int cnt;
+  if (strcmp(name, "geom_pos") == 0) { slot = &b->env_geom_pos; cnt = 3 * b->model->M.ngeom; }
+  else if (strcmp(name, "site_pos") == 0) { slot = &b->env_site_pos; cnt = 3 * b->model->M.nsite; }
+  else return fail(BP_ENOFIELD, std::string("no per-env model field ") + name +
+                   " (geom_pos, site_pos; hfield_data has bp_hfield_write)");
+  if (env0 < 0 || n < 0 || env0 + n > b->nenv) return fail(BP_EINVAL, "env range out of bounds");
+  if (cnt == 0 || n == 0) return BP_OK;
+  cudaSetDevice(b->model->device);
+  if (!*slot) {
+    auto& src = b->model->fields[name].f;
+    std::vector<double> init((size_t)b->nenv_alloc * cnt);
+    for (int64_t e = 0; e < b->nenv_alloc; e++) memcpy(&init[(size_t)e * cnt], src.data(), cnt * 8);
+    CUDA_OK(cudaStreamSynchronize(b->stream));
+    CUDA_OK(cudaMalloc((void**)slot, init.size() * 8));
+    CUDA_OK(cudaMemcpy(*slot, init.data(), init.size() * 8, cudaMemcpyHostToDevice));
+  }
+  if (to_device) CUDA_OK(cudaMemcpyAsync(*slot + env0 * cnt, host, (size_t)n * cnt * 8,
+                                         cudaMemcpyHostToDevice, b->stream));
+  else CUDA_OK(cudaMemcpyAsync(host, *slot + env0 * cnt, (size_t)n * cnt * 8,
+                               cudaMemcpyDeviceToHost, b->stream));
+  CUDA_OK(cudaStreamSynchronize(b->stream));
+  return BP_OK;
+}
+extern "C" int bp_env_model_write(bp_batch* b, const char* name, const double* host,
+                                  int64_t env0, int64_t n) {
+  return env_model_copy(b, name, (double*)host, env0, n, true);
+}
+extern "C" int bp_env_model_read(bp_batch* b, const char* name, double* host, int64_t env0,
+                                 int64_t n) {
+  return env_model_copy(b, name, host, env0, n, false);
 }
 
 // per-env model data: elevation of every height field of envs [env0, env0 + n)

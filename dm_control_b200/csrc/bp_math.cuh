@@ -33,6 +33,8 @@ struct Ctx {
   bool lock;       // true: the block's warps re-align at stage boundaries (BP_LOCK)
   double* hot;     // this env's shared-memory arena (nullptr: those arrays stay global)
   const float* hf; // this env's height-field elevation data (nullptr: none)
+  const double* gpos;  // this env's geom_pos / site_pos (the model's unless overridden)
+  const double* spos;
   __device__ __forceinline__ DP null() const { return DP{nullptr}; }
 };
 

@@ -377,7 +377,9 @@ bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
   double* hot = (S == 1 && P.hot_doubles > 0)
       ? bp_arena + (long long)(threadIdx.x / G) * P.hot_doubles : nullptr;
   const float* hf = P.hfield ? P.hfield + env * (long long)P.m.nhfielddata : nullptr;
-  Ctx<G, S> c{P, base, ib, wl & (G - 1), mask, act, lock, hot, hf};
+  const double* gp = P.env_geom_pos ? P.env_geom_pos + env * 3LL * P.m.ngeom : P.m.geom_pos;
+  const double* sp = P.env_site_pos ? P.env_site_pos + env * 3LL * P.m.nsite : P.m.site_pos;
+  Ctx<G, S> c{P, base, ib, wl & (G - 1), mask, act, lock, hot, hf, gp, sp};
   bp_load_ctrl(c, env);
   bp_run_mode(c);
   if (P.rew_out && act) {           // epilogue: the task's observation and reward

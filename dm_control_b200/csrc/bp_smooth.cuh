@@ -85,11 +85,11 @@ BP_STAGE void bp_kinematics(const C& c) {
       op = DF(xipos) + 3 * w; om = DF(ximat) + 9 * w;
     } else if (w < nb + ng) {
       int g = w - nb;
-      b = m.geom_bodyid[g]; lp = m.geom_pos + 3 * g; lq = m.geom_quat + 4 * g;
+      b = m.geom_bodyid[g]; lp = c.gpos + 3 * g; lq = m.geom_quat + 4 * g;
       op = DF(geom_xpos) + 3 * g; om = DF(geom_xmat) + 9 * g;
     } else {
       int s = w - nb - ng;
-      b = m.site_bodyid[s]; lp = m.site_pos + 3 * s; lq = m.site_quat + 4 * s;
+      b = m.site_bodyid[s]; lp = c.spos + 3 * s; lq = m.site_quat + 4 * s;
       op = DF(site_xpos) + 3 * s; om = DF(site_xmat) + 9 * s;
     }
     double t[3], q[4], R[9];

@@ -12,7 +12,10 @@ bp_step_kernel_smem(const __grid_constant__ BpParams P) {
   for (int w = lane; w < P.L.persist; w += 32) smem[w] = g[w];
   __syncwarp();
   const float* hf = P.hfield ? P.hfield + env * (long long)P.m.nhfielddata : nullptr;
-  Ctx<32, 1> c{P, smem, (int*)(smem + P.L.ints), lane, 0xffffffffu, true, false, nullptr, hf};
+  const double* gp = P.env_geom_pos ? P.env_geom_pos + env * 3LL * P.m.ngeom : P.m.geom_pos;
+  const double* sp = P.env_site_pos ? P.env_site_pos + env * 3LL * P.m.nsite : P.m.site_pos;
+  Ctx<32, 1> c{P, smem, (int*)(smem + P.L.ints), lane, 0xffffffffu, true, false, nullptr, hf,
+               gp, sp};
   bp_load_ctrl(c, env);
   bp_run_mode(c);
   __syncwarp();

@@ -16,7 +16,7 @@
 enum { TASK_NONE = 0, TASK_CARTPOLE = 1, TASK_ACROBOT = 2, TASK_PENDULUM = 3,
        TASK_CHEETAH = 4, TASK_WALKER = 5, TASK_HUMANOID = 6, TASK_HOPPER = 7,
        TASK_REACHER = 8, TASK_FINGER = 9, TASK_QUADRUPED = 10, TASK_QUADRUPED_ESCAPE = 11,
-       TASK_LQR = 12 };
+       TASK_LQR = 12, TASK_POINT_MASS = 13 };
 enum { SIG_GAUSSIAN = 0, SIG_LINEAR = 1, SIG_QUADRATIC = 2 };
 
 // read-only strided window of one environment's image (see bp_math.cuh for layouts)
@@ -202,6 +202,36 @@ static __device__ __noinline__ void bp_task_eval(const BpParams& P, const BpTask
         o[k++] = log1p(sens[T.ip[7]]); o[k++] = log1p(sens[T.ip[8]]);
       }
       r = sens[T.ip[4]] <= -T.fp[0] ? 1.0 : 0.0;
+      break;
+    }
+    case TASK_REACHER: {    // suite/reacher.py:63-70,103-114; ip: target geom, finger geom;
+      // fp: radii = target size + finger size
+      const ImgView gx = d.at(L.geom_xpos);
+      double dx = gx[3 * T.ip[0]] - gx[3 * T.ip[1]], dy = gx[3 * T.ip[0] + 1] - gx[3 * T.ip[1] + 1];
+      if (o) {
+        for (int i = 0; i < m.nq; i++) o[k++] = qpos[i];
+        o[k++] = dx; o[k++] = dy;
+        for (int i = 0; i < m.nv; i++) o[k++] = qvel[i];
+      }
+      r = tolerance(sqrt(dx * dx + dy * dy), 0, T.fp[0], 0, SIG_GAUSSIAN, .1);
+      break;
+    }
+    case TASK_POINT_MASS: { // suite/point_mass.py:59-67,110-127; ip: target geom, pointmass
+      // geom; fp: target size
+      const ImgView gx = d.at(L.geom_xpos);
+      double dd = 0;
+      for (int i = 0; i < 3; i++) {
+        double e = gx[3 * T.ip[0] + i] - gx[3 * T.ip[1] + i];
+        dd += e * e;
+      }
+      if (o) {
+        for (int i = 0; i < m.nq; i++) o[k++] = qpos[i];
+        for (int i = 0; i < m.nv; i++) o[k++] = qvel[i];
+      }
+      double near_target = tolerance(sqrt(dd), 0, T.fp[0], T.fp[0], SIG_GAUSSIAN, .1);
+      double cr = 0;
+      for (int i = 0; i < m.nu; i++) cr += tolerance(ctrl[i], 0, 0, 1, SIG_QUADRATIC, 0);
+      r = near_target * (cr / m.nu + 4) / 5;
       break;
     }
     case TASK_LQR: {        // suite/lqr.py:236-250; fp: control cost coefficient

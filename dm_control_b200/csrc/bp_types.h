@@ -180,6 +180,10 @@ struct BpParams {
   // height-field elevation, one copy per env (float32 as in mjModel.hfield_data): the
   // Escape task writes a different terrain into every episode (quadruped.py:371-382)
   const float* hfield;     // [nenv][nhfielddata], null when the model has no height field
+  // per-env copies of model frames that tasks move per episode (reacher.py:96-101 target
+  // geom, finger.py turn target site); null: every env reads the model's
+  const double* env_geom_pos;   // [nenv][3 * ngeom]
+  const double* env_site_pos;   // [nenv][3 * nsite]
   // fused Environment.step (bp_env_step): dense [nenv][nu] controls scattered into the
   // images before the first sub-step, task observation / reward written after the last
   const double* ctrl_in;   // null: images keep their ctrl

@@ -198,6 +198,14 @@ class BatchedPhysics:
     """Run-time model edit shared by all envs (core.py:581-620, finger.py:140-142)."""
     self._dev_model.set_field(name, value)
 
+  def set_env_model_field(self, name, value, env0=0):
+    """Per-env run-time model edit (reacher.py:96-101 `geom_pos['target']`): value is
+    [n, ...] with the model field's trailing shape; supported: geom_pos, site_pos."""
+    self._batch.write_env_model(name, value, env0)
+
+  def env_model_field(self, name):
+    return self._batch.read_env_model(name)
+
   def set_hfield(self, data, env0=0):
     """Per-env `model.hfield_data` (quadruped.py:381): [n, nhfielddata], stored as float32
     like mjModel's."""

@@ -127,6 +127,22 @@ class Task:
     elif d == "quadruped":
       self._initialize_quadruped(physics, t)
       return
+    elif d == "point_mass":       # suite/point_mass.py:85-107 (easy: fixed gains)
+      for e, rng in enumerate(self._rngs):
+        _randomize_limited_and_rotational_joints(m, qpos[e], rng)
+    elif d == "reacher":          # suite/reacher.py:91-103
+      tgt = m.name2id("target", "geom")
+      size = np.array(m.geom_size, dtype=np.float64)
+      size[tgt, 0] = .05 if t == "easy" else .015
+      physics.set_model_field("geom_size", size)
+      gpos = np.tile(np.asarray(m.geom_pos, dtype=np.float64), (n, 1, 1))
+      for e, rng in enumerate(self._rngs):
+        _randomize_limited_and_rotational_joints(m, qpos[e], rng)
+        angle = rng.uniform(0, 2 * np.pi)
+        radius = rng.uniform(.05, .20)
+        gpos[e, tgt, 0] = radius * np.sin(angle)
+        gpos[e, tgt, 1] = radius * np.cos(angle)
+      physics.set_env_model_field("geom_pos", gpos)
     elif d == "lqr":              # suite/lqr.py:229-233: a random point of a sphere
       for e, rng in enumerate(self._rngs):
         unit = rng.randn(m.nq)

@@ -15,6 +15,7 @@ NONE, CARTPOLE, ACROBOT, PENDULUM, CHEETAH, WALKER, HUMANOID, HOPPER = range(8)
 FINGER = 9
 QUADRUPED, QUADRUPED_ESCAPE = 10, 11
 LQR = 12
+REACHER, POINT_MASS = 8, 13
 
 TaskDef = collections.namedtuple(
     "TaskDef", "domain task model kind time_limit control_timestep params obs")
@@ -112,6 +113,20 @@ def _obs_quadruped(escape):
   return f
 
 
+def _reacher(target_size):
+  def f(m):
+    # reacher.py:112-114: radii = the task's target size + the finger's
+    finger = m.name2id("finger", "geom")
+    return ([m.name2id("target", "geom"), finger],
+            [float(target_size + m.geom_size[finger, 0])])
+  return f
+
+
+def _point_mass(m):
+  tgt = m.name2id("target", "geom")
+  return [tgt, m.name2id("pointmass", "geom")], [float(m.geom_size[tgt, 0])]
+
+
 def _obs_hopper(m):
   return [("position", m.nq - 1), ("velocity", m.nv), ("touch", 2)]
 
@@ -160,6 +175,16 @@ _TASKS = [
             _obs_quadruped(False)),
     TaskDef("quadruped", "escape", "quadruped_escape", QUADRUPED_ESCAPE, 20, .02,
             _quadruped(0.0, 20.0, True), _obs_quadruped(True)),
+    # reacher.py:29-57: 20 s, target size .05 (easy) / .015 (hard); the target geom moves
+    # per episode and per env (bp_env_model_write)
+    TaskDef("reacher", "easy", "reacher", REACHER, 20, None, _reacher(.05),
+            lambda m: [("position", m.nq), ("to_target", 2), ("velocity", m.nv)]),
+    TaskDef("reacher", "hard", "reacher", REACHER, 20, None, _reacher(.015),
+            lambda m: [("position", m.nq), ("to_target", 2), ("velocity", m.nv)]),
+    # point_mass.py:29-43: 20 s; `hard` rewires the tendon coefficients per episode
+    # (model.wrap_prm) and is not served
+    TaskDef("point_mass", "easy", "point_mass", POINT_MASS, 20, None, _point_mass,
+            lambda m: [("position", m.nq), ("velocity", m.nv)]),
     # lqr.py:31-60: no time limit, control cost 0.1; "model" = (n_bodies, n_actuators): the
     # model is generated from the task's seed when the environment is built (suite/lqr.py)
     TaskDef("lqr", "lqr_2_1", (2, 1), LQR, float("inf"), None, lambda m: ([], [0.1]),

@@ -92,6 +92,15 @@ int bp_field_copy_device(bp_batch* b, const char* name, void* dev, int to_image)
 int bp_hfield_write(bp_batch* b, const float* host, int64_t env0, int64_t n);
 int bp_hfield_read(bp_batch* b, float* host, int64_t env0, int64_t n);
 
+/* Per-env copies of model arrays that tasks edit per episode
+ * (`physics.named.model.geom_pos['target', 'x'] = ...`, suite/reacher.py:96-101;
+ * `site_pos['target']`, suite/finger.py:180-181): name is "geom_pos" or "site_pos",
+ * `host` a dense [n][3 * ngeom | 3 * nsite] float64 array for envs [env0, env0+n).  Every
+ * env starts from the model's values; the copy is made on the first write. */
+int bp_env_model_write(bp_batch* b, const char* name, const double* host, int64_t env0,
+                       int64_t n);
+int bp_env_model_read(bp_batch* b, const char* name, double* host, int64_t env0, int64_t n);
+
 /* Optional per-env mask (device or host bytes, nenv long; NULL = all envs): envs
  * whose byte is 0 are left untouched by the calls below. */
 int bp_set_mask(bp_batch* b, const uint8_t* mask_host);

@@ -214,6 +214,7 @@ struct OData {
 #undef X
   OContact* contact;
   double* hfield;   /* this env's elevation data (Escape writes it per episode) */
+  double *geom_pos, *site_pos;   /* this env's copies (per-episode target moves) */
   /* solver scratch */
   double *s_Ma, *s_jar, *s_grad, *s_Mgrad, *s_search, *s_Mv, *s_jv, *s_H,
       *s_Mdense;
@@ -229,6 +230,10 @@ OData* od_create(const OModel* m) {
   d->contact = (OContact*)calloc(m->nconmax > 0 ? m->nconmax : 1, sizeof(OContact));
   d->hfield = (double*)calloc(m->nhfielddata > 0 ? m->nhfielddata : 1, sizeof(double));
   for (int i = 0; i < m->nhfielddata; i++) d->hfield[i] = m->hfield_data[i];
+  d->geom_pos = (double*)calloc(m->ngeom > 0 ? 3 * m->ngeom : 1, sizeof(double));
+  d->site_pos = (double*)calloc(m->nsite > 0 ? 3 * m->nsite : 1, sizeof(double));
+  for (int i = 0; i < 3 * m->ngeom; i++) d->geom_pos[i] = m->geom_pos[i];
+  for (int i = 0; i < 3 * m->nsite; i++) d->site_pos[i] = m->site_pos[i];
   int nv = m->nv > 0 ? m->nv : 1, nj = m->njmax > 0 ? m->njmax : 1;
   d->s_Ma = calloc(nv, 8); d->s_jar = calloc(nj, 8); d->s_grad = calloc(nv, 8);
   d->s_Mgrad = calloc(nv, 8); d->s_search = calloc(nv, 8); d->s_Mv = calloc(nv, 8);
@@ -244,7 +249,7 @@ void od_free(OData* d) {
   DATA_FIELDS(X)
 #undef X
   free(d->contact);
-  free(d->hfield);
+  free(d->hfield); free(d->geom_pos); free(d->site_pos);
   free(d->s_Ma); free(d->s_jar); free(d->s_grad); free(d->s_Mgrad);
   free(d->s_search); free(d->s_Mv); free(d->s_jv); free(d->s_H);
   free(d->s_Mdense);
@@ -252,6 +257,12 @@ void od_free(OData* d) {
 }
 
 void* od_field(OData* d, const char* name, int64_t* count, int* dtype) {
+  if (strcmp(name, "geom_pos") == 0 || strcmp(name, "site_pos") == 0) {
+    int g = name[0] == 'g';
+    if (count) *count = 3 * (g ? d->m->ngeom : d->m->nsite);
+    if (dtype) *dtype = 0;
+    return g ? d->geom_pos : d->site_pos;
+  }
   if (strcmp(name, "hfield_data") == 0) {
     if (count) *count = d->m->nhfielddata;
     if (dtype) *dtype = 0;
@@ -441,7 +452,7 @@ static void o_kinematics(const OModel* m, OData* d) {
   for (int g = 0; g < m->ngeom; g++) {
     int b = m->geom_bodyid[g];
     double t[3], q[4];
-    mat_vec3(t, d->xmat + 9 * b, m->geom_pos + 3 * g);
+    mat_vec3(t, d->xmat + 9 * b, d->geom_pos + 3 * g);
     for (int c = 0; c < 3; c++) d->geom_xpos[3 * g + c] = d->xpos[3 * b + c] + t[c];
     quat_mul(q, d->xquat + 4 * b, m->geom_quat + 4 * g);
     quat2mat(d->geom_xmat + 9 * g, q);
@@ -449,7 +460,7 @@ static void o_kinematics(const OModel* m, OData* d) {
   for (int s = 0; s < m->nsite; s++) {
     int b = m->site_bodyid[s];
     double t[3], q[4];
-    mat_vec3(t, d->xmat + 9 * b, m->site_pos + 3 * s);
+    mat_vec3(t, d->xmat + 9 * b, d->site_pos + 3 * s);
     for (int c = 0; c < 3; c++) d->site_xpos[3 * s + c] = d->xpos[3 * b + c] + t[c];
     quat_mul(q, d->xquat + 4 * b, m->site_quat + 4 * s);
     quat2mat(d->site_xmat + 9 * s, q);

@@ -149,7 +149,7 @@ def compare_env(cmp, m, oracle, gpu, e, nvp, skip=()):
 
 
 def run_parity(domain, nenv=32, nsteps=3, seed=0, njmax=0, nconmax=0, check_steps=None,
-               vel_scale=1.0, spread=1.0, mutate=None, lanes=0):
+               vel_scale=1.0, spread=1.0, mutate=None, lanes=0, env_model=None):
   """forward() then `nsteps` Physics.step() on both sides; returns (Comparison per
   phase, stats).  The GPU side goes through the C ABI (dm_control_b200.binding)."""
   from dm_control_b200 import binding
@@ -169,6 +169,8 @@ def run_parity(domain, nenv=32, nsteps=3, seed=0, njmax=0, nconmax=0, check_step
   batch.write("qpos", qpos); batch.write("qvel", qvel); batch.write("ctrl", ctrl)
   if hfield is not None:
     batch.write_hfield(hfield)
+  for k, v in (env_model or {}).items():     # per-env model frames (reacher's target)
+    batch.write_env_model(k, v)
   if njmax or nconmax:             # the oracle sizes its buffers from the model
     m = m.copy()
     if njmax: m.arrays["njmax"][:] = njmax
@@ -179,6 +181,8 @@ def run_parity(domain, nenv=32, nsteps=3, seed=0, njmax=0, nconmax=0, check_step
     o = Oracle(om)
     if hfield is not None:
       o.hfield_data[:] = hfield[e]
+    for k, v in (env_model or {}).items():
+      getattr(o, k)[:] = np.asarray(v[e]).ravel()
     o.reset()
     o.qpos[:] = qpos[e]; o.qvel[:] = qvel[e]; o.ctrl[:] = ctrl[e]
     oracles.append(o)

@@ -22,8 +22,10 @@ SERVED = [("cartpole", "swingup"), ("cartpole", "swingup_sparse"), ("cartpole", 
           ("walker", "run"), ("hopper", "stand"), ("hopper", "hop"), ("finger", "spin"),
           ("humanoid", "stand"), ("humanoid", "walk"), ("humanoid", "run"),
           ("quadruped", "walk"), ("quadruped", "run"), ("quadruped", "escape"),
-          ("lqr", "lqr_2_1"), ("lqr", "lqr_6_2")]
-FIELDS = ("qpos", "qvel", "act", "ctrl", "xmat", "xpos", "xipos", "site_xpos", "sensordata")
+          ("lqr", "lqr_2_1"), ("lqr", "lqr_6_2"), ("reacher", "easy"), ("reacher", "hard"),
+          ("point_mass", "easy")]
+FIELDS = ("qpos", "qvel", "act", "ctrl", "xmat", "xpos", "xipos", "site_xpos", "geom_xpos",
+          "sensordata")
 
 
 def _fields(physics):

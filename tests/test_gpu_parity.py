@@ -31,7 +31,7 @@ def _assert_parity(res):
 
 @pytest.mark.parametrize("domain", ["pendulum", "cartpole", "acrobot", "cheetah", "walker",
                                     "hopper", "finger", "humanoid", "quadruped",
-                                    "quadruped_escape"])
+                                    "quadruped_escape", "reacher", "point_mass"])
 @pytest.mark.parametrize("lanes", [32, 8, 4, 1])
 def test_every_field_matches_oracle(domain, lanes):
   kw = SIZES.get(domain, {})
@@ -44,6 +44,35 @@ def test_every_field_matches_oracle(domain, lanes):
     assert max(stats["ncon"]) > 0.05
   if domain in ("cheetah", "walker", "hopper", "humanoid", "quadruped", "quadruped_escape"):
     assert max(stats["ncon"]) > 0.5 and max(stats["iter"]) > 0.5     # contacts exercised
+
+
+@pytest.mark.parametrize("lanes", [32, 8, 1])
+def test_per_env_model_frames(lanes):
+  """bp_env_model_write: every env with its own target geom position
+  (suite/reacher.py:96-101) and its own site positions, against oracles that each hold
+  their own copy."""
+  m = PU.load_model("reacher")
+  rng = np.random.RandomState(2)
+  nenv = 40
+  gpos = np.tile(np.asarray(m.geom_pos), (nenv, 1, 1))
+  gpos[:, m.name2id("target", "geom"), :2] = rng.uniform(-.2, .2, (nenv, 2))
+  spos = np.tile(np.asarray(m.site_pos), (nenv, 1, 1)) + rng.uniform(-.1, .1, (nenv, 1, 3))
+  em = {"geom_pos": gpos}
+  if m.nsite:
+    em["site_pos"] = spos
+  res, _ = PU.run_parity("reacher", nenv=nenv, nsteps=3, seed=4, lanes=lanes, env_model=em)
+  _assert_parity(res)
+  from dm_control_b200 import binding
+  model = binding.Model(m)
+  b = binding.Batch(model, nenv, 0, 0, lanes)
+  np.testing.assert_array_equal(b.read_env_model("geom_pos"), np.tile(m.geom_pos, (nenv, 1, 1)))
+  b.write_env_model("geom_pos", gpos[5:9], env0=5)
+  got = b.read_env_model("geom_pos")
+  np.testing.assert_array_equal(got[5:9], gpos[5:9])
+  np.testing.assert_array_equal(got[9:], np.tile(m.geom_pos, (nenv - 9, 1, 1)))
+  with pytest.raises(binding.Error):
+    b.write_env_model("geom_size", np.zeros((nenv, m.ngeom, 3)))
+  b.free(); model.free()
 
 
 @pytest.mark.parametrize("lanes", [2, 16])
