@@ -22,6 +22,7 @@ extern "C" int bp_task_nobs_impl(const BpModel* m, int task) {
     case TASK_HOPPER: return m->nq - 1 + m->nv + 2;
     case TASK_REACHER: return m->nq + 2 + m->nv;
     case TASK_FINGER: return 9;
+    case TASK_FINGER_TURN: return 12;
     case TASK_LQR: return m->nq + m->nv;
     case TASK_POINT_MASS: return m->nq + m->nv;
     case TASK_QUADRUPED: return 2 * m->nhinge + m->na + 3 + 1 + 6 + 3 * m->nsens_ft;

@@ -16,7 +16,7 @@
 enum { TASK_NONE = 0, TASK_CARTPOLE = 1, TASK_ACROBOT = 2, TASK_PENDULUM = 3,
        TASK_CHEETAH = 4, TASK_WALKER = 5, TASK_HUMANOID = 6, TASK_HOPPER = 7,
        TASK_REACHER = 8, TASK_FINGER = 9, TASK_QUADRUPED = 10, TASK_QUADRUPED_ESCAPE = 11,
-       TASK_LQR = 12, TASK_POINT_MASS = 13 };
+       TASK_LQR = 12, TASK_POINT_MASS = 13, TASK_FINGER_TURN = 14 };
 enum { SIG_GAUSSIAN = 0, SIG_LINEAR = 1, SIG_QUADRATIC = 2 };
 
 // read-only strided window of one environment's image (see bp_math.cuh for layouts)
@@ -189,6 +189,21 @@ static __device__ __noinline__ void bp_task_eval(const BpParams& P, const BpTask
         for (int i = 0; i < m.nu; i++) sc += tolerance(ctrl[i], 0, 0, 1, SIG_QUADRATIC, 0);
         r = standing * (sc / m.nu + 4) / 5;
       }
+      break;
+    }
+    case TASK_FINGER_TURN: {  // suite/finger.py:87-126,196-215 (turn_easy / turn_hard)
+      // ip as TASK_FINGER plus ip[9] = sensordata address of the target site's framepos;
+      // fp[1] = target radius
+      double tx = sens[T.ip[9]] - sens[T.ip[6]], tz = sens[T.ip[9] + 2] - sens[T.ip[6] + 2];
+      double px = sens[T.ip[5]] - sens[T.ip[6]], pz = sens[T.ip[5] + 2] - sens[T.ip[6] + 2];
+      double dist = sqrt((tx - px) * (tx - px) + (tz - pz) * (tz - pz)) - T.fp[1];
+      if (o) {
+        o[k++] = sens[T.ip[0]]; o[k++] = sens[T.ip[1]]; o[k++] = px; o[k++] = pz;
+        o[k++] = sens[T.ip[2]]; o[k++] = sens[T.ip[3]]; o[k++] = sens[T.ip[4]];
+        o[k++] = log1p(sens[T.ip[7]]); o[k++] = log1p(sens[T.ip[8]]);
+        o[k++] = tx; o[k++] = tz; o[k++] = dist;
+      }
+      r = dist <= 0 ? 1.0 : 0.0;
       break;
     }
     case TASK_FINGER: {     // suite/finger.py:87-112,139-156 (spin)

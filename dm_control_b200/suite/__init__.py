@@ -51,7 +51,7 @@ class Task:
     self.tdef = tdef
     self._seed = random
     self._rngs = None
-    self.scalar_obs = {"height", "head_height", "torso_upright"}
+    self.scalar_obs = {"height", "head_height", "torso_upright", "dist_to_target"}
 
   def bind(self, physics):
     m = physics.model
@@ -149,10 +149,24 @@ class Task:
         qpos[e] = np.sqrt(2) * unit / np.linalg.norm(unit)
     elif d in ("humanoid", "finger"):
       # suite/humanoid.py:152-166, suite/finger.py:139-144,201-212: rejection on contacts
-      if d == "finger":           # finger.py:142 (spin): the same edit for every env
+      if d == "finger" and t == "spin":   # finger.py:142: the same edit for every env
         damping = np.array(m.dof_damping, dtype=np.float64)
         damping[m.jnt_dofadr[m.name2id("hinge", "joint")]] = .03
         physics.set_model_field("dof_damping", damping)
+      elif d == "finger":         # finger.py:172-181 (turn): a target per env
+        hinge = m.name2id("hinge", "joint")
+        anchor = physics.data.xanchor.reshape(n, -1, 3)[:, hinge]     # valid after reset()
+        radius = float(np.sum(m.geom_size[m.name2id("cap1", "geom")]))
+        tgt = m.name2id("target", "site")
+        spos = np.tile(np.asarray(m.site_pos, dtype=np.float64), (n, 1, 1))
+        for e, rng in enumerate(self._rngs):
+          angle = rng.uniform(-np.pi, np.pi)
+          spos[e, tgt, 0] = anchor[e, 0] + radius * np.sin(angle)
+          spos[e, tgt, 2] = anchor[e, 2] + radius * np.cos(angle)
+        physics.set_env_model_field("site_pos", spos)
+        size = np.array(m.site_size, dtype=np.float64)
+        size[tgt, 0] = self.tdef.params(m)[1][1]
+        physics.set_model_field("site_size", size)
       todo = np.ones(n, dtype=bool)
       while todo.any():
         for e in np.flatnonzero(todo):

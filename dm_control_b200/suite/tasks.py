@@ -16,6 +16,7 @@ FINGER = 9
 QUADRUPED, QUADRUPED_ESCAPE = 10, 11
 LQR = 12
 REACHER, POINT_MASS = 8, 13
+FINGER_TURN = 14
 
 TaskDef = collections.namedtuple(
     "TaskDef", "domain task model kind time_limit control_timestep params obs")
@@ -76,6 +77,13 @@ def _finger(m):
   names = ("proximal", "distal", "proximal_velocity", "distal_velocity", "hinge_velocity",
            "tip", "spinner", "touchtop", "touchbottom")
   return [_sens_adr(m, n) for n in names], [15.0]           # finger.py:38 _SPIN_VELOCITY
+
+
+def _finger_turn(target_radius):
+  def f(m):
+    ip, _ = _finger(m)
+    return ip + [_sens_adr(m, "target")], [15.0, target_radius]
+  return f
 
 
 def _quadruped(speed=0.0, deviation_angle=0.0, escape=False):
@@ -162,10 +170,16 @@ _TASKS = [
     # hopper.py:32-41: 20 s, control timestep .02, stand height .6, hop speed 2
     TaskDef("hopper", "stand", "hopper", HOPPER, 20, .02, _hopper(False), _obs_hopper),
     TaskDef("hopper", "hop", "hopper", HOPPER, 20, .02, _hopper(True), _obs_hopper),
-    # finger.py:28-29: 20 s, control timestep .02 (the turn tasks move a model site per
-    # episode and are not served)
+    # finger.py:28-33: 20 s, control timestep .02; turn targets of radius .07 / .03 sit on
+    # a per-env site (bp_env_model_write "site_pos")
     TaskDef("finger", "spin", "finger", FINGER, 20, .02, _finger,
             lambda m: [("position", 4), ("velocity", 3), ("touch", 2)]),
+    TaskDef("finger", "turn_easy", "finger", FINGER_TURN, 20, .02, _finger_turn(.07),
+            lambda m: [("position", 4), ("velocity", 3), ("touch", 2), ("target_position", 2),
+                       ("dist_to_target", 1)]),
+    TaskDef("finger", "turn_hard", "finger", FINGER_TURN, 20, .02, _finger_turn(.03),
+            lambda m: [("position", 4), ("velocity", 3), ("touch", 2), ("target_position", 2),
+                       ("dist_to_target", 1)]),
     # quadruped.py:36-44: 20 s, control timestep .02, walk speed 0.5, run speed 5; escape
     # uses the terrain model and a 20 degree upright deviation (fetch: walls, ball and
     # condim-6 contacts are not served)

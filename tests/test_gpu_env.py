@@ -23,7 +23,7 @@ SERVED = [("cartpole", "swingup"), ("cartpole", "swingup_sparse"), ("cartpole", 
           ("humanoid", "stand"), ("humanoid", "walk"), ("humanoid", "run"),
           ("quadruped", "walk"), ("quadruped", "run"), ("quadruped", "escape"),
           ("lqr", "lqr_2_1"), ("lqr", "lqr_6_2"), ("reacher", "easy"), ("reacher", "hard"),
-          ("point_mass", "easy")]
+          ("point_mass", "easy"), ("finger", "turn_easy"), ("finger", "turn_hard")]
 FIELDS = ("qpos", "qvel", "act", "ctrl", "xmat", "xpos", "xipos", "site_xpos", "geom_xpos",
           "sensordata")
 
