@@ -100,8 +100,10 @@ BP_STAGE void bp_make_constraint(const C& c) {
       base += tot;
     }
   }
-  int con_base = base, ncon = IF(ncon)[0];
+  int con_base = base, ncon = IF(ncon)[0], con_end = 0;
   const bool pyramidal = m.opt_cone == 0;
+  // a contact gets all of its rows or none (mj_addConstraint reserves the whole block);
+  // the running sum is monotone, so nothing fits after the first contact that does not
 #pragma unroll 1
   for (int c0 = 0; c0 < ncon; c0 += C::G) {
     int ci = c0 + c.lane, n = 0, dim = 0;
@@ -111,17 +113,25 @@ BP_STAGE void bp_make_constraint(const C& c) {
     }
     int tot, start = base + group_excl_scan(c, n, &tot);
     if (ci < ncon) {
-      int adr = (n > 0 && start < njmax) ? start : -1;
-      IF(contact_efc_address)[ci] = adr;
+      const bool fits = n > 0 && start + n <= njmax;
+      IF(contact_efc_address)[ci] = fits ? start : -1;
       int type = dim == 1 ? CN_CONTACT_FRICTIONLESS
                           : (pyramidal ? CN_CONTACT_PYRAMIDAL : CN_CONTACT_ELLIPTIC);
       double dist = DF(contact_dist)[ci], inc = DF(contact_includemargin)[ci];
-      for (int k = 0; k < n; k++)
-        if (start + k < njmax) bp_row_header(c, start + k, type, ci, dist, inc, 0);
+      if (fits) {
+        for (int k = 0; k < n; k++) bp_row_header(c, start + k, type, ci, dist, inc, 0);
+        con_end = start + n;
+      }
     }
     base += tot;
   }
-  int nefc = base < njmax ? base : njmax;
+#pragma unroll
+  for (int o = C::G / 2; o > 0; o >>= 1) {
+    int other = __shfl_xor_sync(c.mask, con_end, o, C::G);
+    con_end = other > con_end ? other : con_end;
+  }
+  int nefc = con_base < njmax ? con_base : njmax;
+  if (con_end > nefc) nefc = con_end;
   if (c.lane == 0) {
     IF(nefc)[0] = nefc; IF(nf)[0] = nf;
     if (base > njmax) IF(warning)[W_CNSTRFULL]++;

@@ -137,7 +137,7 @@ static __device__ __noinline__ void bp_task_eval(const BpParams& P, const BpTask
       }
       break;
     }
-    case TASK_HUMANOID: {   // suite/humanoid.py:93-129,168-207
+    case TASK_HUMANOID: {   // suite/humanoid.py:93-129,168-207; suite/humanoid_CMU.py:65-180
       int torso = T.ip[0], head = T.ip[1];
       const ImgView R = xmat.at(9 * torso);
       const ImgView vel = sens.at(T.ip[6]);
@@ -156,7 +156,9 @@ static __device__ __noinline__ void bp_task_eval(const BpParams& P, const BpTask
         for (int i = 0; i < m.nv; i++) o[k++] = qvel[i];
       }
       double standing = tolerance(xpos[3 * head + 2], 1.4, INF, 1.4 / 4, SIG_GAUSSIAN, .1);
-      double upright = tolerance(R[8], 0.9, INF, 1.9, SIG_LINEAR, 0);
+      // ip[7]: element of the torso frame read as "upright": zz for humanoid.py:96-98, zy
+      // for humanoid_CMU.py:68-70 (its root body is pitched by 90 degrees)
+      double upright = tolerance(R[T.ip[7]], 0.9, INF, 1.9, SIG_LINEAR, 0);
       double sc = 0;
       for (int i = 0; i < m.nu; i++) sc += tolerance(ctrl[i], 0, 0, 1, SIG_QUADRATIC, 0);
       sc = (4 + sc / m.nu) / 5;

@@ -542,7 +542,7 @@ def compile_xml(xml_string, assets=None):
   _emit_tendons_equality(m, root, classes)
   _emit_actuators(m, root, classes)
   _emit_sensors(m, root, classes)
-  _emit_pairs(m)
+  _emit_pairs(m, root)
   _emit_keyframes(m, root)
   _set_const(m)
   _emit_statistic(m, root)
@@ -928,7 +928,7 @@ def _emit_sensors(m, root, classes):
   m.set("sensor_cutoff", np.array(S["cutoff"], dtype=np.float64).reshape(ns))
 
 
-def _emit_pairs(m):
+def _emit_pairs(m, root=None):
   """Static candidate geom pairs, in the engine's contact order [MJ-doc A.7]:
   ascending (body1, body2), then geom order inside each body; filtered by
   contype/conaffinity, same-weld and (optionally, at run time) parent-child."""
@@ -936,6 +936,14 @@ def _emit_pairs(m):
   gb = m.geom_bodyid
   weld, par = m.body_weldid, m.body_parentid
   pairs = []
+  # <contact><exclude body1 body2/>: geoms of the two bodies never collide [MJ-doc]
+  excluded = set()
+  for sec in (root.findall("contact") if root is not None else []):
+    for ex in sec.findall("exclude"):
+      b1 = m.name2id(ex.get("body1"), "body"); b2 = m.name2id(ex.get("body2"), "body")
+      excluded.add((min(b1, b2), max(b1, b2)))
+    if sec.findall("pair"):
+      raise ValueError("explicit <contact><pair> elements are unsupported")
   order = sorted(range(ng), key=lambda g: (gb[g], g))
   for i1 in range(ng):
     for i2 in range(i1 + 1, ng):
@@ -944,6 +952,8 @@ def _emit_pairs(m):
       if b1 == b2:
         continue
       if weld[b1] == weld[b2]:
+        continue
+      if (min(b1, b2), max(b1, b2)) in excluded:
         continue
       if not ((m.geom_contype[g1] & m.geom_conaffinity[g2]) or
               (m.geom_contype[g2] & m.geom_conaffinity[g1])):

@@ -147,7 +147,7 @@ class Task:
       for e, rng in enumerate(self._rngs):
         unit = rng.randn(m.nq)
         qpos[e] = np.sqrt(2) * unit / np.linalg.norm(unit)
-    elif d in ("humanoid", "finger"):
+    elif d in ("humanoid", "finger", "humanoid_CMU"):
       # suite/humanoid.py:152-166, suite/finger.py:139-144,201-212: rejection on contacts
       if d == "finger" and t == "spin":   # finger.py:142: the same edit for every env
         damping = np.array(m.dof_damping, dtype=np.float64)

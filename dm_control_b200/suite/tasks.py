@@ -57,11 +57,14 @@ def _walker(speed):
   return f
 
 
-def _humanoid(speed):
+def _humanoid(speed, cmu=False):
   def f(m):
-    ids = [m.name2id(n, "body") for n in
-           ("torso", "head", "left_hand", "left_foot", "right_hand", "right_foot")]
-    return ids + [_sens_adr(m, "torso_subtreelinvel")], [speed]
+    names = ("thorax", "head", "lhand", "lfoot", "rhand", "rfoot") if cmu else \
+        ("torso", "head", "left_hand", "left_foot", "right_hand", "right_foot")
+    ids = [m.name2id(n, "body") for n in names]
+    # "upright": xmat[torso, 'zz'] (humanoid.py:96-98) / xmat[thorax, 'zy'] (humanoid_CMU.py:68-70)
+    return ids + [_sens_adr(m, "thorax_subtreelinvel" if cmu else "torso_subtreelinvel"),
+                  7 if cmu else 8], [speed]
   return f
 
 
@@ -209,6 +212,9 @@ _TASKS = [
     TaskDef("humanoid", "stand", "humanoid", HUMANOID, 25, .025, _humanoid(0.0), None),
     TaskDef("humanoid", "walk", "humanoid", HUMANOID, 25, .025, _humanoid(1.0), None),
     TaskDef("humanoid", "run", "humanoid", HUMANOID, 25, .025, _humanoid(10.0), None),
+    # humanoid_CMU.py:28-36: 20 s, control timestep .02, speeds 0 / 10 (nv = 62, 56 motors)
+    TaskDef("humanoid_CMU", "stand", "humanoid_CMU", HUMANOID, 20, .02, _humanoid(0.0, True), None),
+    TaskDef("humanoid_CMU", "run", "humanoid_CMU", HUMANOID, 20, .02, _humanoid(10.0, True), None),
 ]
 
 

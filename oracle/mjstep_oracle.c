@@ -1484,6 +1484,7 @@ static int add_contact(const OModel* m, OData* d, int g1, int g2, double margin,
   c->efc_address = -1;
   d->contact_geom1[id] = g1; d->contact_geom2[id] = g2;
   d->contact_dim[id] = c->dim; d->contact_dist[id] = c->dist;
+  d->contact_efc_address[id] = -1;
   memcpy(d->contact_pos + 3 * id, c->pos, 24);
   memcpy(d->contact_frame + 9 * id, c->frame, 72);
   return 1;
@@ -1697,6 +1698,9 @@ static void o_make_constraint(const OModel* m, OData* d) {
         Jc[k][i] = tp; Jc[3 + k][i] = tr;
       }
     int dim = c->dim;
+    /* a contact gets all of its rows or none [MJ-doc: mj_addConstraint reserves the block] */
+    int need = dim == 1 ? 1 : (m->opt_cone == 0 ? 2 * (dim - 1) : dim);
+    if (d->nefc[0] + need > m->njmax) { warn(d, W_CNSTRFULL); break; }
     if (dim == 1) {
       int r = add_row(m, d, CN_CONTACT_FRICTIONLESS, ci, c->dist, c->includemargin, 0);
       if (r < 0) break;

@@ -23,7 +23,8 @@ SERVED = [("cartpole", "swingup"), ("cartpole", "swingup_sparse"), ("cartpole", 
           ("humanoid", "stand"), ("humanoid", "walk"), ("humanoid", "run"),
           ("quadruped", "walk"), ("quadruped", "run"), ("quadruped", "escape"),
           ("lqr", "lqr_2_1"), ("lqr", "lqr_6_2"), ("reacher", "easy"), ("reacher", "hard"),
-          ("point_mass", "easy"), ("finger", "turn_easy"), ("finger", "turn_hard")]
+          ("point_mass", "easy"), ("finger", "turn_easy"), ("finger", "turn_hard"),
+          ("humanoid_CMU", "stand"), ("humanoid_CMU", "run")]
 FIELDS = ("qpos", "qvel", "act", "ctrl", "xmat", "xpos", "xipos", "site_xpos", "geom_xpos",
           "sensordata")
 
@@ -41,7 +42,7 @@ def test_obs_reward_kernel_matches_task_oracle(domain, task):
   env = suite.load(domain, task, task_kwargs={"random": 11}, nenv=n)
   tdef = T.REGISTRY[(domain, task)]
   ip, fp = tdef.params(env.physics.model)
-  speed = fp[0] if domain in ("walker", "humanoid", "quadruped") else None
+  speed = fp[0] if domain in ("walker", "humanoid", "quadruped", "humanoid_CMU") else None
   rng = np.random.RandomState(3)
   ts = env.reset()
   spec = env.action_spec()

@@ -19,7 +19,8 @@ TOL = 1e-8
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 HUMANOID_SIZES = dict(njmax=120, nconmax=40)
 SIZES = {"humanoid": HUMANOID_SIZES, "quadruped": dict(njmax=120, nconmax=40),
-         "quadruped_escape": dict(njmax=300, nconmax=64)}
+         "quadruped_escape": dict(njmax=300, nconmax=64),
+         "humanoid_CMU": dict(njmax=200, nconmax=48)}
 
 
 def _assert_parity(res):
@@ -72,6 +73,35 @@ def test_per_env_model_frames(lanes):
   np.testing.assert_array_equal(got[9:], np.tile(m.geom_pos, (nenv - 9, 1, 1)))
   with pytest.raises(binding.Error):
     b.write_env_model("geom_size", np.zeros((nenv, m.ngeom, 3)))
+  b.free(); model.free()
+
+
+@pytest.mark.parametrize("lanes", [16, 8, 1])
+def test_cmu_humanoid_matches_oracle(lanes):
+  """humanoid_CMU (nv = 62, 1188 candidate pairs, <contact><exclude>): the widest model
+  the 64-bit dof masks take; too large for the shared-memory shape (lanes = 32)."""
+  res, stats = PU.run_parity("humanoid_CMU", nenv=24, nsteps=10, seed=5, check_steps=[0, 1, 10],
+                             lanes=lanes, **SIZES["humanoid_CMU"])
+  _assert_parity(res)
+  assert max(stats["ncon"]) > 0.5
+
+
+@pytest.mark.parametrize("lanes", [32, 16, 4, 1])
+def test_full_contact_and_constraint_buffers(lanes):
+  """Buffers far too small for the scene (core_test.py:97-103 surfaces the same warnings):
+  contacts beyond nconmax are dropped in contact order, a contact whose rows do not all fit
+  in njmax gets none, CONTACTFULL / CNSTRFULL are counted -- identically on both sides."""
+  res, stats = PU.run_parity("humanoid", nenv=32, nsteps=6, seed=7, check_steps=[0, 1, 6],
+                             lanes=lanes, njmax=12, nconmax=3)
+  _assert_parity(res)
+  from dm_control_b200 import binding
+  m = PU.load_model("humanoid")
+  qpos, qvel, ctrl = PU.random_states(m, 32, 7)
+  model = binding.Model(m); b = binding.Batch(model, 32, 12, 3, lanes)
+  b.write("qpos", qpos); b.write("qvel", qvel); b.forward(); b.sync()
+  w = b.warnings().sum(axis=0)
+  assert w[1] > 0 and w[2] > 0                      # both kinds of overflow happened
+  assert (b.read("nefc") <= 12).all() and (b.read("ncon") <= 3).all()
   b.free(); model.free()
 
 

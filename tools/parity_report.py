@@ -20,8 +20,10 @@ def main():
       kw = dict(njmax=120, nconmax=40) if d in ("humanoid", "quadruped") else {}
       if d == "quadruped_escape":
         kw = dict(njmax=300, nconmax=64)
+      if d == "humanoid_CMU":
+        kw = dict(njmax=200, nconmax=48)
       try:
-        res, stats = PU.run_parity(d, nenv=64, nsteps=20, seed=1,
+        res, stats = PU.run_parity(d, nenv=int(os.environ.get('BP_NENV', 64)), nsteps=20, seed=int(os.environ.get('BP_SEED', 1)),
                                    check_steps=[0, 1, 5, 20], lanes=lanes, **kw)
         d = '%s/G%d' % (d, lanes)
       except Exception as e:   # keep going: this is a report, not a test
