@@ -101,7 +101,7 @@ def fp64_peak_tflops(device=0):
   return out.value
 
 
-SIGMOIDS = {"gaussian": 0, "linear": 1, "quadratic": 2}
+SIGMOIDS = {"gaussian": 0, "linear": 1, "quadratic": 2, "long_tail": 3}
 
 
 def rewards_tolerance(x, bounds=(0.0, 0.0), margin=0.0, sigmoid="gaussian",

@@ -793,7 +793,7 @@ extern "C" int bp_rewards_tolerance(int device, const double* x_host, double* ou
   if (!x_host || !out_host || n < 0) return fail(BP_EINVAL, "bad arguments");
   if (lower > upper) return fail(BP_EINVAL, "Lower bound must be <= upper bound.");
   if (margin < 0) return fail(BP_EINVAL, "`margin` must be non-negative.");
-  if (sigmoid < 0 || sigmoid > 2) return fail(BP_EINVAL, "Unknown sigmoid type");
+  if (sigmoid < 0 || sigmoid > 3) return fail(BP_EINVAL, "Unknown sigmoid type");
   if (n == 0) return BP_OK;
   CUDA_OK(cudaSetDevice(device));
   double *dx = nullptr, *dout = nullptr;

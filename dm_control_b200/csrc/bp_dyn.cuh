@@ -66,6 +66,67 @@ BP_STAGE void bp_passive(const C& c) {
     qp[i] = f;
   }
   SYNC();
+  // fluid forces [MJ-doc: inertia-box model of mj_passive]: every body is replaced by the
+  // box with its mass and inertia; viscous force / torque of the equivalent sphere plus
+  // quadratic drag per box face.  Bodies on lanes build their wrench (moved to the subtree
+  // centre the cdofs refer to) in scratch, then dofs on lanes gather over their subtree.
+  if (!off && (m.opt_density > 0 || m.opt_viscosity > 0)) {
+    const double PI = 3.14159265358979323846;
+    auto wr = DF(s_cfrc), cvel = DF(cvel), xipos = DF(xipos), ximat = DF(ximat), scom = DF(subtree_com);
+#pragma unroll 1
+    for (int b = 1 + c.lane; b < m.nbody; b += C::G) {
+      double w[6] = {0, 0, 0, 0, 0, 0};
+      const double mass = m.body_mass[b];
+      if (!(mass < BP_MINVAL)) {
+        const double* I = m.body_inertia + 3 * b;
+        double box[3] = {sqrt(fmax(BP_MINVAL, I[1] + I[2] - I[0]) / mass * 6.0),
+                         sqrt(fmax(BP_MINVAL, I[0] + I[2] - I[1]) / mass * 6.0),
+                         sqrt(fmax(BP_MINVAL, I[0] + I[1] - I[2]) / mass * 6.0)};
+        auto com = scom + 3 * m.body_rootid[b];
+        double cv[6], R[9], dif[3], t3[3], vlin[3], lw[3], lv[3], fa[3] = {0, 0, 0}, fl[3] = {0, 0, 0};
+        for (int k = 0; k < 6; k++) cv[k] = cvel[6 * b + k];
+        for (int k = 0; k < 9; k++) R[k] = ximat[9 * b + k];
+        for (int k = 0; k < 3; k++) dif[k] = xipos[3 * b + k] - com[k];
+        cross3(t3, cv, dif);
+        for (int k = 0; k < 3; k++) vlin[k] = cv[3 + k] + t3[k];
+        matT_vec3(lw, R, cv);
+        matT_vec3(lv, R, vlin);
+        if (m.opt_viscosity > 0) {
+          double diam = (box[0] + box[1] + box[2]) / 3.0;
+          for (int k = 0; k < 3; k++) {
+            fa[k] = -PI * diam * diam * diam * m.opt_viscosity * lw[k];
+            fl[k] = -3.0 * PI * diam * m.opt_viscosity * lv[k];
+          }
+        }
+        if (m.opt_density > 0) {
+          const double rho = m.opt_density;
+          fl[0] -= 0.5 * rho * box[1] * box[2] * fabs(lv[0]) * lv[0];
+          fl[1] -= 0.5 * rho * box[0] * box[2] * fabs(lv[1]) * lv[1];
+          fl[2] -= 0.5 * rho * box[0] * box[1] * fabs(lv[2]) * lv[2];
+          double b0 = box[0] * box[0], b1 = box[1] * box[1], b2 = box[2] * box[2];
+          fa[0] -= rho * box[0] * (b1 * b1 + b2 * b2) * fabs(lw[0]) * lw[0] / 64.0;
+          fa[1] -= rho * box[1] * (b0 * b0 + b2 * b2) * fabs(lw[1]) * lw[1] / 64.0;
+          fa[2] -= rho * box[2] * (b0 * b0 + b1 * b1) * fabs(lw[2]) * lw[2] / 64.0;
+        }
+        double ga[3], gl[3];
+        mat_vec3(ga, R, fa);
+        mat_vec3(gl, R, fl);
+        cross3(t3, dif, gl);
+        for (int k = 0; k < 3; k++) { w[k] = ga[k] + t3[k]; w[3 + k] = gl[k]; }
+      }
+      for (int k = 0; k < 6; k++) wr[6 * b + k] = w[k];
+    }
+    SYNC();
+    auto cdof = DF(cdof);
+#pragma unroll 1
+    for (int i = c.lane; i < m.nv; i += C::G) {
+      double acc = 0;
+      for (int b = 1; b < m.nbody; b++)
+        if (m.body_dofmask[b] >> i & 1ull) acc += dot6(cdof + 6 * i, wr + 6 * b);
+      qp[i] += acc;
+    }
+    SYNC();
+  }
 }
 
 // Recursive Newton-Euler.  with_acc adds cdof*qacc; cfrc_ext (may be null) is

@@ -177,6 +177,10 @@ BP_STAGE void bp_sensors(const C& c, int stage) {
         bp_obj_frame(c, m.sensor_objtype[s], id, pos, mat);
         for (int k = 0; k < 3; k++) out[k] = pos[k];
         break;
+      case SENS_FRAMEXAXIS: case SENS_FRAMEYAXIS: case SENS_FRAMEZAXIS:
+        bp_obj_frame(c, m.sensor_objtype[s], id, pos, mat);
+        for (int k = 0; k < 3; k++) out[k] = mat[3 * k + (t - SENS_FRAMEXAXIS)];
+        break;
       case SENS_VELOCIMETER: case SENS_GYRO: case SENS_ACCELEROMETER: {
         int body = bp_obj_frame(c, OBJ_SITE, id, pos, mat);
         auto cm = DF(subtree_com) + 3 * m.body_rootid[body];

@@ -16,8 +16,9 @@
 enum { TASK_NONE = 0, TASK_CARTPOLE = 1, TASK_ACROBOT = 2, TASK_PENDULUM = 3,
        TASK_CHEETAH = 4, TASK_WALKER = 5, TASK_HUMANOID = 6, TASK_HOPPER = 7,
        TASK_REACHER = 8, TASK_FINGER = 9, TASK_QUADRUPED = 10, TASK_QUADRUPED_ESCAPE = 11,
-       TASK_LQR = 12, TASK_POINT_MASS = 13, TASK_FINGER_TURN = 14 };
-enum { SIG_GAUSSIAN = 0, SIG_LINEAR = 1, SIG_QUADRATIC = 2 };
+       TASK_LQR = 12, TASK_POINT_MASS = 13, TASK_FINGER_TURN = 14,
+       TASK_SWIMMER = 15 };
+enum { SIG_GAUSSIAN = 0, SIG_LINEAR = 1, SIG_QUADRATIC = 2, SIG_LONG_TAIL = 3 };
 
 // read-only strided window of one environment's image (see bp_math.cuh for layouts)
 struct ImgView {
@@ -37,6 +38,9 @@ __device__ __forceinline__ double sigmoid_(double x, double v1, int kind) {
   } else if (kind == SIG_LINEAR) {
     double sx = x * (1 - v1);
     return fabs(sx) < 1 ? 1 - sx : 0.0;
+  } else if (kind == SIG_LONG_TAIL) {      // rewards.py:64-66
+    double scale = sqrt(1 / v1 - 1);
+    return 1 / ((x * scale) * (x * scale) + 1);
   } else {
     double sx = x * sqrt(1 - v1);
     return fabs(sx) < 1 ? 1 - sx * sx : 0.0;
@@ -249,6 +253,25 @@ static __device__ __noinline__ void bp_task_eval(const BpParams& P, const BpTask
       double cr = 0;
       for (int i = 0; i < m.nu; i++) cr += tolerance(ctrl[i], 0, 0, 1, SIG_QUADRATIC, 0);
       r = near_target * (cr / m.nu + 4) / 5;
+      break;
+    }
+    case TASK_SWIMMER: {    // suite/swimmer.py:139-160,199-213
+      // ip: target geom, nose geom, head body, sensordata address of head_vel; fp: target size
+      const ImgView gx = d.at(L.geom_xpos);
+      const ImgView R = xmat.at(9 * T.ip[2]);
+      double v[3], tt[2];
+      for (int i = 0; i < 3; i++) v[i] = gx[3 * T.ip[0] + i] - gx[3 * T.ip[1] + i];
+      for (int cidx = 0; cidx < 2; cidx++)
+        tt[cidx] = v[0] * R[cidx] + v[1] * R[3 + cidx] + v[2] * R[6 + cidx];
+      if (o) {
+        for (int i = 3; i < m.nq; i++) o[k++] = qpos[i];
+        o[k++] = tt[0]; o[k++] = tt[1];
+        for (int b = 0; b < m.nbody - 1; b++) {
+          int a = T.ip[3] + 6 * b;
+          o[k++] = sens[a]; o[k++] = sens[a + 1]; o[k++] = sens[a + 5];
+        }
+      }
+      r = tolerance(sqrt(tt[0] * tt[0] + tt[1] * tt[1]), 0, T.fp[0], 5 * T.fp[0], SIG_LONG_TAIL, .1);
       break;
     }
     case TASK_LQR: {        // suite/lqr.py:236-250; fp: control cost coefficient

@@ -31,6 +31,7 @@ enum { SENS_TOUCH = 0, SENS_ACCELEROMETER = 1, SENS_VELOCIMETER = 2,
        SENS_GYRO = 3, SENS_FORCE = 4, SENS_TORQUE = 5, SENS_RANGEFINDER = 7,
        SENS_JOINTPOS = 8,
        SENS_JOINTVEL = 9, SENS_ACTUATORFRC = 14, SENS_FRAMEPOS = 23,
+       SENS_FRAMEXAXIS = 25, SENS_FRAMEYAXIS = 26, SENS_FRAMEZAXIS = 27,
        SENS_SUBTREECOM = 32, SENS_SUBTREELINVEL = 33 };
 enum { OBJ_BODY = 1, OBJ_XBODY = 2, OBJ_GEOM = 5, OBJ_SITE = 6 };
 enum { STAGE_POS = 1, STAGE_VEL = 2, STAGE_ACC = 3 };
@@ -46,7 +47,7 @@ enum { BP_MODE_STEP = 0, BP_MODE_FORWARD = 1, BP_MODE_STEP1 = 2,
   X(opt_ls_iterations) X(opt_disableflags) X(opt_enableflags)
 #define BP_MODEL_F64_SCALARS(X) \
   X(opt_timestep) X(opt_impratio) X(opt_tolerance) X(opt_ls_tolerance) \
-  X(stat_meaninertia)
+  X(stat_meaninertia) X(opt_density) X(opt_viscosity)
 #define BP_MODEL_INT_ARRAYS(X) \
   X(body_parentid) X(body_rootid) X(body_weldid) X(body_jntnum) X(body_jntadr) \
   X(body_dofnum) X(body_dofadr) X(jnt_type) X(jnt_qposadr) X(jnt_dofadr) \

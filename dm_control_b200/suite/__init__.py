@@ -143,6 +143,15 @@ class Task:
         gpos[e, tgt, 0] = radius * np.sin(angle)
         gpos[e, tgt, 1] = radius * np.cos(angle)
       physics.set_env_model_field("geom_pos", gpos)
+    elif d == "swimmer":          # suite/swimmer.py:176-197
+      tgt = m.name2id("target", "geom")
+      gpos = np.tile(np.asarray(m.geom_pos, dtype=np.float64), (n, 1, 1))
+      for e, rng in enumerate(self._rngs):
+        _randomize_limited_and_rotational_joints(m, qpos[e], rng)
+        close_target = rng.rand() < .2
+        target_box = .3 if close_target else 2
+        gpos[e, tgt, :2] = rng.uniform(-target_box, target_box, size=2)
+      physics.set_env_model_field("geom_pos", gpos)
     elif d == "lqr":              # suite/lqr.py:229-233: a random point of a sphere
       for e, rng in enumerate(self._rngs):
         unit = rng.randn(m.nq)

@@ -17,6 +17,7 @@ QUADRUPED, QUADRUPED_ESCAPE = 10, 11
 LQR = 12
 REACHER, POINT_MASS = 8, 13
 FINGER_TURN = 14
+SWIMMER = 15
 
 TaskDef = collections.namedtuple(
     "TaskDef", "domain task model kind time_limit control_timestep params obs")
@@ -138,6 +139,18 @@ def _point_mass(m):
   return [tgt, m.name2id("pointmass", "geom")], [float(m.geom_size[tgt, 0])]
 
 
+def _swimmer(m):
+  tgt = m.name2id("target", "geom")
+  # body_velocities() reads sensordata[12:] as (velocimeter, gyro) pairs (swimmer.py:151-155)
+  assert _sens_adr(m, "head_vel") == 12 and m.nsensordata == 12 + 6 * (m.nbody - 1)
+  return ([tgt, m.name2id("nose", "geom"), m.name2id("head", "body"), 12],
+          [float(m.geom_size[tgt, 0])])
+
+
+def _obs_swimmer(m):
+  return [("joints", m.nq - 3), ("to_target", 2), ("body_velocities", 3 * (m.nbody - 1))]
+
+
 def _obs_hopper(m):
   return [("position", m.nq - 1), ("velocity", m.nv), ("touch", 2)]
 
@@ -202,6 +215,10 @@ _TASKS = [
     # (model.wrap_prm) and is not served
     TaskDef("point_mass", "easy", "point_mass", POINT_MASS, 20, None, _point_mass,
             lambda m: [("position", m.nq), ("velocity", m.nv)]),
+    # swimmer.py:28-30: 30 s, control timestep .03; fluid drag (option density), the target
+    # geom moves per episode and per env
+    TaskDef("swimmer", "swimmer6", "swimmer6", SWIMMER, 30, .03, _swimmer, _obs_swimmer),
+    TaskDef("swimmer", "swimmer15", "swimmer15", SWIMMER, 30, .03, _swimmer, _obs_swimmer),
     # lqr.py:31-60: no time limit, control cost 0.1; "model" = (n_bodies, n_actuators): the
     # model is generated from the task's seed when the environment is built (suite/lqr.py)
     TaskDef("lqr", "lqr_2_1", (2, 1), LQR, float("inf"), None, lambda m: ([], [0.1]),

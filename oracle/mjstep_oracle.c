@@ -35,6 +35,7 @@ enum { SENS_TOUCH = 0, SENS_ACCELEROMETER = 1, SENS_VELOCIMETER = 2,
        SENS_GYRO = 3, SENS_FORCE = 4, SENS_TORQUE = 5, SENS_RANGEFINDER = 7,
        SENS_JOINTPOS = 8,
        SENS_JOINTVEL = 9, SENS_ACTUATORFRC = 14, SENS_FRAMEPOS = 23,
+       SENS_FRAMEXAXIS = 25, SENS_FRAMEYAXIS = 26, SENS_FRAMEZAXIS = 27,
        SENS_SUBTREECOM = 32, SENS_SUBTREELINVEL = 33 };
 enum { OBJ_BODY = 1, OBJ_XBODY = 2, OBJ_GEOM = 5, OBJ_SITE = 6 };
 enum { STAGE_POS = 1, STAGE_VEL = 2, STAGE_ACC = 3 };
@@ -55,7 +56,7 @@ typedef struct {
   X(opt_ls_iterations) X(opt_disableflags) X(opt_enableflags)
 #define MODEL_F64_SCALARS(X) \
   X(opt_timestep) X(opt_impratio) X(opt_tolerance) X(opt_ls_tolerance) \
-  X(stat_meaninertia)
+  X(stat_meaninertia) X(opt_density) X(opt_viscosity)
 #define MODEL_INT_ARRAYS(X) \
   X(body_parentid) X(body_rootid) X(body_weldid) X(body_jntnum) X(body_jntadr) \
   X(body_dofnum) X(body_dofadr) X(jnt_type) X(jnt_qposadr) X(jnt_dofadr) \
@@ -217,7 +218,7 @@ struct OData {
   double *geom_pos, *site_pos;   /* this env's copies (per-episode target moves) */
   /* solver scratch */
   double *s_Ma, *s_jar, *s_grad, *s_Mgrad, *s_search, *s_Mv, *s_jv, *s_H,
-      *s_Mdense;
+      *s_Mdense, *s_fluid;
 };
 
 OData* od_create(const OModel* m) {
@@ -239,6 +240,7 @@ OData* od_create(const OModel* m) {
   d->s_Mgrad = calloc(nv, 8); d->s_search = calloc(nv, 8); d->s_Mv = calloc(nv, 8);
   d->s_jv = calloc(nj, 8); d->s_H = calloc((size_t)nv * nv, 8);
   d->s_Mdense = calloc((size_t)nv * nv, 8);
+  d->s_fluid = calloc((size_t)6 * (m->nbody > 0 ? m->nbody : 1), 8);
   o_reset(m, d);
   return d;
 }
@@ -252,7 +254,7 @@ void od_free(OData* d) {
   free(d->hfield); free(d->geom_pos); free(d->site_pos);
   free(d->s_Ma); free(d->s_jar); free(d->s_grad); free(d->s_Mgrad);
   free(d->s_search); free(d->s_Mv); free(d->s_jv); free(d->s_H);
-  free(d->s_Mdense);
+  free(d->s_Mdense); free(d->s_fluid);
   free(d);
 }
 
@@ -645,6 +647,64 @@ static void o_passive(const OModel* m, OData* d) {
       d->qfrc_passive[da] -= k * (d->qpos[qa] - m->qpos_spring[qa]);
   }
   for (int i = 0; i < m->nv; i++) d->qfrc_passive[i] -= m->dof_damping[i] * d->qvel[i];
+  /* fluid forces [MJ-doc: inertia-box model of mj_passive]: every body is replaced by the
+   * box with its mass and inertia; viscous force and torque of the equivalent sphere, plus
+   * quadratic drag per box face (density).  Wind is not served.  The wrench acts at the
+   * body's centre of mass; here it is moved to the subtree centre the cdofs refer to. */
+  if (m->opt_density > 0 || m->opt_viscosity > 0) {
+    double* wr = d->s_fluid;
+    for (int b = 1; b < m->nbody; b++) {
+      double* w = wr + 6 * b;
+      memset(w, 0, 48);
+      double mass = m->body_mass[b];
+      if (mass < MINVAL) continue;
+      const double* I = m->body_inertia + 3 * b;
+      double box[3] = {sqrt(fmax(MINVAL, I[1] + I[2] - I[0]) / mass * 6.0),
+                       sqrt(fmax(MINVAL, I[0] + I[2] - I[1]) / mass * 6.0),
+                       sqrt(fmax(MINVAL, I[0] + I[1] - I[2]) / mass * 6.0)};
+      const double* com = d->subtree_com + 3 * m->body_rootid[b];
+      const double *cv = d->cvel + 6 * b, *R = d->ximat + 9 * b;
+      double dif[3] = {d->xipos[3 * b] - com[0], d->xipos[3 * b + 1] - com[1],
+                       d->xipos[3 * b + 2] - com[2]};
+      double t3[3], vlin[3], lw[3], lv[3], fa[3] = {0, 0, 0}, fl[3] = {0, 0, 0};
+      cross3(t3, cv, dif);
+      for (int k = 0; k < 3; k++) vlin[k] = cv[3 + k] + t3[k];
+      matT_vec3(lw, R, cv);
+      matT_vec3(lv, R, vlin);
+      if (m->opt_viscosity > 0) {
+        double diam = (box[0] + box[1] + box[2]) / 3.0;
+        for (int k = 0; k < 3; k++) {
+          fa[k] = -PI * diam * diam * diam * m->opt_viscosity * lw[k];
+          fl[k] = -3.0 * PI * diam * m->opt_viscosity * lv[k];
+        }
+      }
+      if (m->opt_density > 0) {
+        double rho = m->opt_density;
+        fl[0] -= 0.5 * rho * box[1] * box[2] * fabs(lv[0]) * lv[0];
+        fl[1] -= 0.5 * rho * box[0] * box[2] * fabs(lv[1]) * lv[1];
+        fl[2] -= 0.5 * rho * box[0] * box[1] * fabs(lv[2]) * lv[2];
+        double b0 = box[0] * box[0], b1 = box[1] * box[1], b2 = box[2] * box[2];
+        fa[0] -= rho * box[0] * (b1 * b1 + b2 * b2) * fabs(lw[0]) * lw[0] / 64.0;
+        fa[1] -= rho * box[1] * (b0 * b0 + b2 * b2) * fabs(lw[1]) * lw[1] / 64.0;
+        fa[2] -= rho * box[2] * (b0 * b0 + b1 * b1) * fabs(lw[2]) * lw[2] / 64.0;
+      }
+      double ga[3], gl[3];
+      mat_vec3(ga, R, fa);
+      mat_vec3(gl, R, fl);
+      cross3(t3, dif, gl);
+      for (int k = 0; k < 3; k++) { w[k] = ga[k] + t3[k]; w[3 + k] = gl[k]; }
+    }
+    for (int i = 0; i < m->nv; i++) {
+      double acc = 0;
+      for (int b = 1; b < m->nbody; b++) {
+        int anc = 0;
+        for (int p = b; p > 0; p = m->body_parentid[p])
+          if (p == m->dof_bodyid[i]) { anc = 1; break; }
+        if (anc) acc += dot6(d->cdof + 6 * i, wr + 6 * b);
+      }
+      d->qfrc_passive[i] += acc;
+    }
+  }
 }
 
 /* recursive Newton-Euler; flg_acc adds cdof*qacc.  result = inverse-dynamics
@@ -2492,6 +2552,10 @@ static void o_sensors(const OModel* m, OData* d, int stage) {
       case SENS_FRAMEPOS:
         obj_frame(m, d, m->sensor_objtype[s], id, &pos, &mat, &body);
         memcpy(out, pos, 24);
+        break;
+      case SENS_FRAMEXAXIS: case SENS_FRAMEYAXIS: case SENS_FRAMEZAXIS:
+        obj_frame(m, d, m->sensor_objtype[s], id, &pos, &mat, &body);
+        geom_axis(mat, t - SENS_FRAMEXAXIS, out);
         break;
       case SENS_VELOCIMETER: case SENS_GYRO: case SENS_ACCELEROMETER: {
         obj_frame(m, d, OBJ_SITE, id, &pos, &mat, &body);

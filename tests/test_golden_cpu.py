@@ -10,7 +10,7 @@ from oracle import task_oracle
 from oracle.oracle_py import Oracle, OracleModel
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-SIG = {0: "gaussian", 1: "linear", 2: "quadratic"}
+SIG = {0: "gaussian", 1: "linear", 2: "quadratic", 3: "long_tail"}
 
 
 def test_tolerance_restatement_matches_reference_rewards_py():

@@ -24,7 +24,8 @@ SERVED = [("cartpole", "swingup"), ("cartpole", "swingup_sparse"), ("cartpole", 
           ("quadruped", "walk"), ("quadruped", "run"), ("quadruped", "escape"),
           ("lqr", "lqr_2_1"), ("lqr", "lqr_6_2"), ("reacher", "easy"), ("reacher", "hard"),
           ("point_mass", "easy"), ("finger", "turn_easy"), ("finger", "turn_hard"),
-          ("humanoid_CMU", "stand"), ("humanoid_CMU", "run")]
+          ("humanoid_CMU", "stand"), ("humanoid_CMU", "run"),
+          ("swimmer", "swimmer6"), ("swimmer", "swimmer15")]
 FIELDS = ("qpos", "qvel", "act", "ctrl", "xmat", "xpos", "xipos", "site_xpos", "geom_xpos",
           "sensordata")
 

@@ -20,7 +20,8 @@ GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 HUMANOID_SIZES = dict(njmax=120, nconmax=40)
 SIZES = {"humanoid": HUMANOID_SIZES, "quadruped": dict(njmax=120, nconmax=40),
          "quadruped_escape": dict(njmax=300, nconmax=64),
-         "humanoid_CMU": dict(njmax=200, nconmax=48)}
+         "humanoid_CMU": dict(njmax=200, nconmax=48),
+         "swimmer6": dict(njmax=32, nconmax=1), "swimmer15": dict(njmax=32, nconmax=1)}
 
 
 def _assert_parity(res):
@@ -32,14 +33,18 @@ def _assert_parity(res):
 
 @pytest.mark.parametrize("domain", ["pendulum", "cartpole", "acrobot", "cheetah", "walker",
                                     "hopper", "finger", "humanoid", "quadruped",
-                                    "quadruped_escape", "reacher", "point_mass"])
+                                    "quadruped_escape", "reacher", "point_mass", "swimmer6",
+                                    "swimmer15"])
 @pytest.mark.parametrize("lanes", [32, 8, 4, 1])
 def test_every_field_matches_oracle(domain, lanes):
   kw = SIZES.get(domain, {})
   # finger (elliptic cones, friction loss): more envs, a tenth of the random states touch
   nenv = 160 if domain == "finger" else 48
+  # swimmer: explicit quadratic drag on gram-scale links diverges from 1 rad/s joint speeds
+  # (BADQACC resets on both sides, at rounding-dependent steps): gentler start states
+  vel = 0.3 if domain.startswith("swimmer") else 1.0
   res, stats = PU.run_parity(domain, nenv=nenv, nsteps=10, seed=5, check_steps=[0, 1, 2, 10],
-                             lanes=lanes, **kw)
+                             lanes=lanes, vel_scale=vel, **kw)
   _assert_parity(res)
   if domain == "finger":
     assert max(stats["ncon"]) > 0.05
@@ -195,7 +200,7 @@ def test_readme_golden_through_cuda():
 def test_tolerance_kernel_matches_reference_rewards_py():
   from dm_control_b200 import binding
   g = np.load(os.path.join(GOLDEN, "rewards_tolerance.npz"))
-  sig = {0: "gaussian", 1: "linear", 2: "quadratic"}
+  sig = {0: "gaussian", 1: "linear", 2: "quadratic", 3: "long_tail"}
   for (lo, hi, mg, sg, v1), want in zip(g["cases"], g["out"]):
     got = binding.rewards_tolerance(g["x"], (lo, hi), mg, sig[int(sg)], v1)
     np.testing.assert_allclose(got, want, rtol=1e-13, atol=1e-15)

@@ -44,6 +44,45 @@ def quadruped_xml(floor_size=None, terrain=False, rangefinders=False, walls_and_
   return ET.tostring(root, encoding="unicode")
 
 
+def swimmer_xml(n_bodies):
+  """suite/swimmer.py:87-133 _make_model / _make_body: the same elements appended to
+  swimmer.xml (camera moves are rendering only and left out)."""
+  import xml.etree.ElementTree as ET
+  root = ET.fromstring(open(os.path.join(SUITE, "swimmer.xml")).read())
+  parent = root.find("./worldbody/body")
+  actuator = ET.SubElement(root, "actuator")
+  sensor = ET.SubElement(root, "sensor")
+  for i in range(n_bodies - 1):
+    child = ET.Element("body", name="segment_%d" % i, pos="0 .1 0")
+    ET.SubElement(child, "geom", {"class": "visual", "name": "visual_%d" % i})
+    ET.SubElement(child, "geom", {"class": "inertial", "name": "inertial_%d" % i})
+    child.append(ET.Element("site", name="site_%d" % i))
+    limit = 360.0 / n_bodies
+    child.append(ET.Element("joint", {"name": "joint_%d" % i, "range": "%r %r" % (-limit, limit)}))
+    actuator.append(ET.Element("motor", name="motor_%d" % i, joint="joint_%d" % i))
+    sensor.append(ET.Element("velocimeter", name="velocimeter_%d" % i, site="site_%d" % i))
+    sensor.append(ET.Element("gyro", name="gyro_%d" % i, site="site_%d" % i))
+    parent.append(child)
+    parent = child
+  return ET.tostring(root, encoding="unicode")
+
+
+def swimmers():
+  class _Dir(dict):
+    def __contains__(self, k):
+      return os.path.exists(os.path.join(SUITE, k))
+
+    def __getitem__(self, k):
+      with open(os.path.join(SUITE, k)) as f:
+        return f.read()
+
+  for n in (6, 15):
+    m = C.compile_xml(swimmer_xml(n), _Dir())
+    m.save(os.path.join(OUT, "swimmer%d.npz" % n))
+    print("swimmer%d nq" % n, m.nq, "nv", m.nv, "nu", m.nu, "nsensordata", m.nsensordata,
+          "density", m.opt_density)
+
+
 def main():
   os.makedirs(OUT, exist_ok=True)
   for d in DOMAINS:
@@ -82,3 +121,4 @@ def quadruped():
 if __name__ == "__main__":
   main()
   quadruped()
+  swimmers()

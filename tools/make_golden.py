@@ -24,7 +24,8 @@ CASES = [  # (lower, upper, margin, sigmoid, value_at_margin)
     (1.2, np.inf, 0.6, "gaussian", 0.1), (1.0, np.inf, 0.5, "linear", 0.5),
     (1.4, np.inf, 0.35, "gaussian", 0.1), (0.9, np.inf, 1.9, "linear", 0.0),
     (-0.25, 0.25, 0.0, "gaussian", 0.1), (0.995, 1.0, 0.0, "gaussian", 0.1),
-    (0.0, 0.2, 1.0, "gaussian", 0.1), (0.0, 0.0, 2.0, "gaussian", 0.1)]
+    (0.0, 0.2, 1.0, "gaussian", 0.1), (0.0, 0.0, 2.0, "gaussian", 0.1),
+    (0.0, 0.1, 0.5, "long_tail", 0.1), (-1.0, 1.0, 3.0, "long_tail", 0.3)]
 
 
 def rewards_fixture():
@@ -36,7 +37,7 @@ def rewards_fixture():
   out = np.stack([mod.tolerance(x, bounds=(lo, hi), margin=mg, sigmoid=sg, value_at_margin=v1)
                   for lo, hi, mg, sg, v1 in CASES])
   np.savez(os.path.join(OUT, "rewards_tolerance.npz"), x=x, out=out,
-           cases=np.array([(lo, hi, mg, {"gaussian": 0, "linear": 1, "quadratic": 2}[sg], v1)
+           cases=np.array([(lo, hi, mg, {"gaussian": 0, "linear": 1, "quadratic": 2, "long_tail": 3}[sg], v1)
                            for lo, hi, mg, sg, v1 in CASES]))
   print("rewards_tolerance.npz", out.shape)
 
