@@ -62,6 +62,14 @@ BP_STAGE void bp_passive(const C& c) {
         f -= k * (qpos[qa] - m.qpos_spring[qa]);
       }
       f -= m.dof_damping[i] * qvel[i];
+      // tendon spring-dampers: each dof gathers the tendons that wrap its joint
+      for (int t = 0; t < m.ntendon; t++) {
+        double kt = m.tendon_stiffness[t], bt = m.tendon_damping[t];
+        if (kt == 0 && bt == 0) continue;
+        double frc = -kt * (DF(ten_length)[t] - m.tendon_length0[t]) - bt * DF(ten_velocity)[t];
+        for (int w = m.tendon_adr[t]; w < m.tendon_adr[t] + m.tendon_num[t]; w++)
+          if (m.wrap_objid[w] == j) f += m.wrap_prm[w] * frc;
+      }
     }
     qp[i] = f;
   }

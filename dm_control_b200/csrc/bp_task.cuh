@@ -17,7 +17,8 @@ enum { TASK_NONE = 0, TASK_CARTPOLE = 1, TASK_ACROBOT = 2, TASK_PENDULUM = 3,
        TASK_CHEETAH = 4, TASK_WALKER = 5, TASK_HUMANOID = 6, TASK_HOPPER = 7,
        TASK_REACHER = 8, TASK_FINGER = 9, TASK_QUADRUPED = 10, TASK_QUADRUPED_ESCAPE = 11,
        TASK_LQR = 12, TASK_POINT_MASS = 13, TASK_FINGER_TURN = 14,
-       TASK_SWIMMER = 15 };
+       TASK_SWIMMER = 15, TASK_FISH_UPRIGHT = 16,
+       TASK_FISH_SWIM = 17 };
 enum { SIG_GAUSSIAN = 0, SIG_LINEAR = 1, SIG_QUADRATIC = 2, SIG_LONG_TAIL = 3 };
 
 // read-only strided window of one environment's image (see bp_math.cuh for layouts)
@@ -272,6 +273,36 @@ static __device__ __noinline__ void bp_task_eval(const BpParams& P, const BpTask
         }
       }
       r = tolerance(sqrt(tt[0] * tt[0] + tt[1] * tt[1]), 0, T.fp[0], 5 * T.fp[0], SIG_LONG_TAIL, .1);
+      break;
+    }
+    case TASK_FISH_UPRIGHT: case TASK_FISH_SWIM: {
+      // suite/fish.py:72-94 (observables), 114-125 (Upright), 155-171 (Swim)
+      // ip: torso body, first tail / fin joint qpos address, number of those joints,
+      // target geom, mouth geom; fp: radii = mouth size + target size
+      const bool swim = T.kind == TASK_FISH_SWIM;
+      const double up = xmat[9 * T.ip[0] + 8];
+      double tt[3] = {0, 0, 0};
+      if (swim) {
+        const ImgView gx = d.at(L.geom_xpos);
+        const ImgView R = d.at(L.geom_xmat).at(9 * T.ip[4]);
+        double v[3];
+        for (int i = 0; i < 3; i++) v[i] = gx[3 * T.ip[3] + i] - gx[3 * T.ip[4] + i];
+        for (int cidx = 0; cidx < 3; cidx++)
+          tt[cidx] = v[0] * R[cidx] + v[1] * R[3 + cidx] + v[2] * R[6 + cidx];
+      }
+      if (o) {
+        for (int i = 0; i < T.ip[2]; i++) o[k++] = qpos[T.ip[1] + i];
+        o[k++] = up;
+        if (swim) for (int i = 0; i < 3; i++) o[k++] = tt[i];
+        for (int i = 0; i < m.nv; i++) o[k++] = qvel[i];
+      }
+      if (swim) {
+        double in_target = tolerance(sqrt(tt[0] * tt[0] + tt[1] * tt[1] + tt[2] * tt[2]), 0,
+                                     T.fp[0], 2 * T.fp[0], SIG_GAUSSIAN, .1);
+        r = (7 * in_target + 0.5 * (up + 1)) / 8;
+      } else {
+        r = tolerance(up, 1, 1, 1, SIG_GAUSSIAN, .1);
+      }
       break;
     }
     case TASK_LQR: {        // suite/lqr.py:236-250; fp: control cost coefficient

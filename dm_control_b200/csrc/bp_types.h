@@ -71,7 +71,7 @@ enum { BP_MODE_STEP = 0, BP_MODE_FORWARD = 1, BP_MODE_STEP1 = 2,
   X(site_pos) X(site_quat) X(site_size) X(qpos0) X(qpos_spring) \
   X(actuator_dynprm) X(actuator_gainprm) X(actuator_biasprm) \
   X(actuator_ctrlrange) X(actuator_forcerange) X(actuator_gear) \
-  X(sensor_cutoff) X(wrap_prm) X(tendon_length0) X(tendon_invweight0) X(eq_solref) \
+  X(sensor_cutoff) X(wrap_prm) X(tendon_length0) X(tendon_invweight0) X(tendon_stiffness) X(tendon_damping) X(eq_solref) \
   X(eq_solimp) X(eq_data) X(hfield_size) X(hfield_data)
 // ---- arrays derived on the host when the model is created (bp_api.cu) ---------
 //   body_level_*: bodies grouped by tree depth (parents complete before children)

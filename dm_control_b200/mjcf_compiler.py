@@ -782,8 +782,8 @@ def _solimp(text):
 def _emit_tendons_equality(m, root, classes):
   """Fixed tendons (<tendon><fixed>) and tendon / joint equalities [MJ-doc: XML reference].
   A fixed tendon's length is sum(coef * qpos[joint]); its Jacobian is constant.  Spatial
-  tendons, tendon limits / springs / friction are outside the served models."""
-  T = {"adr": [], "num": []}
+  tendons, tendon limits / friction are outside the served models."""
+  T = {"adr": [], "num": [], "stiffness": [], "damping": []}
   wrap_obj, wrap_prm = [], []
   for sec in root.findall("tendon"):
     for el in sec:
@@ -792,7 +792,9 @@ def _emit_tendons_equality(m, root, classes):
       a = dict(classes[el.get("class") or "main"].get("tendon"))
       a.update(classes[el.get("class") or "main"].get("fixed"))
       a.update(el.attrib)
-      for k in ("limited", "stiffness", "damping", "frictionloss"):
+      T["stiffness"].append(float(a.get("stiffness", 0)))
+      T["damping"].append(float(a.get("damping", 0)))
+      for k in ("limited", "frictionloss"):
         if a.get(k, "false" if k == "limited" else "0") not in ("false", "0", "0.0"):
           raise ValueError("tendon attribute %s unsupported" % k)
       m.names["tendon"].append(a.get("name", ""))
@@ -809,6 +811,8 @@ def _emit_tendons_equality(m, root, classes):
   m.set("ntendon", nt); m.set("nwrap", len(wrap_obj))
   m.set("tendon_adr", np.array(T["adr"], dtype=np.int32).reshape(nt))
   m.set("tendon_num", np.array(T["num"], dtype=np.int32).reshape(nt))
+  m.set("tendon_stiffness", np.array(T["stiffness"], dtype=np.float64).reshape(nt))
+  m.set("tendon_damping", np.array(T["damping"], dtype=np.float64).reshape(nt))
   m.set("wrap_objid", np.array(wrap_obj, dtype=np.int32).reshape(len(wrap_obj)))
   m.set("wrap_prm", np.array(wrap_prm, dtype=np.float64).reshape(len(wrap_prm)))
   # equalities: residual = (x1 - x1_0) - poly(x2 - x2_0), x = joint position / tendon length

@@ -91,7 +91,7 @@ class Task:
       sl = m.jnt_qposadr[m.name2id("slider", "joint")]
       h1 = m.jnt_qposadr[m.name2id("hinge_1", "joint")]
       for e, rng in enumerate(self._rngs):
-        if t.startswith("swingup"):
+        if t.startswith("swingup") or t.endswith("_poles"):
           qpos[e, sl] = .01 * rng.randn()
           qpos[e, h1] = np.pi + .01 * rng.randn()
           qpos[e, 2:] = .1 * rng.randn(m.nv - 2)
@@ -152,6 +152,21 @@ class Task:
         target_box = .3 if close_target else 2
         gpos[e, tgt, :2] = rng.uniform(-target_box, target_box, size=2)
       physics.set_env_model_field("geom_pos", gpos)
+    elif d == "fish":             # suite/fish.py:107-116,139-150
+      tgt = m.name2id("target", "geom")
+      root = m.jnt_qposadr[m.name2id("root", "joint")]
+      gpos = np.tile(np.asarray(m.geom_pos, dtype=np.float64), (n, 1, 1))
+      for e, rng in enumerate(self._rngs):
+        quat = rng.randn(4)
+        qpos[e, root + 3:root + 7] = quat / np.linalg.norm(quat)
+        for j in range(7):
+          qpos[e, 7 + j] = rng.uniform(-.2, .2)
+        if t == "swim":
+          gpos[e, tgt, 0] = rng.uniform(-.4, .4)
+          gpos[e, tgt, 1] = rng.uniform(-.4, .4)
+          gpos[e, tgt, 2] = rng.uniform(.1, .3)
+      if t == "swim":
+        physics.set_env_model_field("geom_pos", gpos)
     elif d == "lqr":              # suite/lqr.py:229-233: a random point of a sphere
       for e, rng in enumerate(self._rngs):
         unit = rng.randn(m.nq)

@@ -18,6 +18,7 @@ LQR = 12
 REACHER, POINT_MASS = 8, 13
 FINGER_TURN = 14
 SWIMMER = 15
+FISH_UPRIGHT, FISH_SWIM = 16, 17
 
 TaskDef = collections.namedtuple(
     "TaskDef", "domain task model kind time_limit control_timestep params obs")
@@ -151,6 +152,26 @@ def _obs_swimmer(m):
   return [("joints", m.nq - 3), ("to_target", 2), ("body_velocities", 3 * (m.nbody - 1))]
 
 
+def _fish(m):
+  # fish.py:30-36 _JOINTS: the seven tail / fin hinges follow the free root joint
+  joints = ["tail1", "tail_twist", "tail2", "finright_roll", "finright_pitch",
+            "finleft_roll", "finleft_pitch"]
+  adr = [int(m.jnt_qposadr[m.name2id(j, "joint")]) for j in joints]
+  assert adr == list(range(7, 14)) and m.nq == 14
+  tgt, mouth = m.name2id("target", "geom"), m.name2id("mouth", "geom")
+  return ([m.name2id("torso", "body"), adr[0], len(adr), tgt, mouth],
+          [float(m.geom_size[mouth, 0] + m.geom_size[tgt, 0])])
+
+
+def _obs_fish(swim):
+  def f(m):
+    obs = [("joint_angles", 7), ("upright", 1)]
+    if swim:
+      obs.append(("target", 3))
+    return obs + [("velocity", m.nv)]
+  return f
+
+
 def _obs_hopper(m):
   return [("position", m.nq - 1), ("velocity", m.nv), ("touch", 2)]
 
@@ -165,6 +186,9 @@ _TASKS = [
     TaskDef("cartpole", "swingup_sparse", "cartpole", CARTPOLE, 10, None, _cartpole(True), _obs_cartpole),
     TaskDef("cartpole", "balance", "cartpole", CARTPOLE, 10, None, _cartpole(False), _obs_cartpole),
     TaskDef("cartpole", "balance_sparse", "cartpole", CARTPOLE, 10, None, _cartpole(True), _obs_cartpole),
+    # cartpole.py:84-103: swing-up with a chain of poles (_make_model, 105-127)
+    TaskDef("cartpole", "two_poles", "cartpole2", CARTPOLE, 10, None, _cartpole(False), _obs_cartpole),
+    TaskDef("cartpole", "three_poles", "cartpole3", CARTPOLE, 10, None, _cartpole(False), _obs_cartpole),
     # acrobot.py:28 time limit 10 s
     TaskDef("acrobot", "swingup", "acrobot", ACROBOT, 10, None, _acrobot(False),
             lambda m: [("orientations", 4), ("velocity", m.nv)]),
@@ -217,6 +241,10 @@ _TASKS = [
             lambda m: [("position", m.nq), ("velocity", m.nv)]),
     # swimmer.py:28-30: 30 s, control timestep .03; fluid drag (option density), the target
     # geom moves per episode and per env
+    # fish.py:28-29: 40 s, control timestep .04; gravity and constraints disabled, fluid
+    # density 5000, a tendon spring between the fins, position servos
+    TaskDef("fish", "upright", "fish", FISH_UPRIGHT, 40, .04, _fish, _obs_fish(False)),
+    TaskDef("fish", "swim", "fish", FISH_SWIM, 40, .04, _fish, _obs_fish(True)),
     TaskDef("swimmer", "swimmer6", "swimmer6", SWIMMER, 30, .03, _swimmer, _obs_swimmer),
     TaskDef("swimmer", "swimmer15", "swimmer15", SWIMMER, 30, .03, _swimmer, _obs_swimmer),
     # lqr.py:31-60: no time limit, control cost 0.1; "model" = (n_bodies, n_actuators): the

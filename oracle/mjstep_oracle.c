@@ -81,7 +81,7 @@ typedef struct {
   X(actuator_dynprm) X(actuator_gainprm) X(actuator_biasprm) \
   X(actuator_ctrlrange) X(actuator_forcerange) X(actuator_gear) \
   X(sensor_cutoff) X(key_qpos) X(key_qvel) X(key_act) X(key_time) X(wrap_prm) \
-  X(tendon_length0) X(tendon_invweight0) X(eq_solref) X(eq_solimp) X(eq_data) \
+  X(tendon_length0) X(tendon_invweight0) X(tendon_stiffness) X(tendon_damping) X(eq_solref) X(eq_solimp) X(eq_data) \
   X(hfield_size) X(hfield_data)
 
 struct OModel {
@@ -647,6 +647,15 @@ static void o_passive(const OModel* m, OData* d) {
       d->qfrc_passive[da] -= k * (d->qpos[qa] - m->qpos_spring[qa]);
   }
   for (int i = 0; i < m->nv; i++) d->qfrc_passive[i] -= m->dof_damping[i] * d->qvel[i];
+  /* tendon spring-dampers [MJ-doc: mj_passive]: the spring's rest length is the tendon's
+   * length at qpos0 */
+  for (int t = 0; t < m->ntendon; t++) {
+    double k = m->tendon_stiffness[t], b = m->tendon_damping[t];
+    if (k == 0 && b == 0) continue;
+    double frc = -k * (d->ten_length[t] - m->tendon_length0[t]) - b * d->ten_velocity[t];
+    for (int w = m->tendon_adr[t]; w < m->tendon_adr[t] + m->tendon_num[t]; w++)
+      d->qfrc_passive[m->jnt_dofadr[m->wrap_objid[w]]] += m->wrap_prm[w] * frc;
+  }
   /* fluid forces [MJ-doc: inertia-box model of mj_passive]: every body is replaced by the
    * box with its mass and inertia; viscous force and torque of the equivalent sphere, plus
    * quadratic drag per box face (density).  Wind is not served.  The wrench acts at the

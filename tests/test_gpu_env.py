@@ -25,9 +25,11 @@ SERVED = [("cartpole", "swingup"), ("cartpole", "swingup_sparse"), ("cartpole", 
           ("lqr", "lqr_2_1"), ("lqr", "lqr_6_2"), ("reacher", "easy"), ("reacher", "hard"),
           ("point_mass", "easy"), ("finger", "turn_easy"), ("finger", "turn_hard"),
           ("humanoid_CMU", "stand"), ("humanoid_CMU", "run"),
-          ("swimmer", "swimmer6"), ("swimmer", "swimmer15")]
+          ("swimmer", "swimmer6"), ("swimmer", "swimmer15"),
+          ("fish", "upright"), ("fish", "swim"),
+          ("cartpole", "two_poles"), ("cartpole", "three_poles")]
 FIELDS = ("qpos", "qvel", "act", "ctrl", "xmat", "xpos", "xipos", "site_xpos", "geom_xpos",
-          "sensordata")
+          "geom_xmat", "sensordata")
 
 
 def _fields(physics):

@@ -13,7 +13,7 @@ from dm_control_b200 import mjcf_compiler as C   # noqa: E402
 
 SUITE = "/root/reference/dm_control/suite"
 DOMAINS = ["cartpole", "acrobot", "pendulum", "cheetah", "walker", "humanoid",
-           "hopper", "reacher", "finger", "swimmer", "point_mass", "humanoid_CMU"]
+           "hopper", "reacher", "finger", "swimmer", "point_mass", "humanoid_CMU", "fish"]
 OUT = os.path.join(ROOT, "dm_control_b200", "suite", "models")
 
 
@@ -67,15 +67,38 @@ def swimmer_xml(n_bodies):
   return ET.tostring(root, encoding="unicode")
 
 
+class _Dir(dict):
+  def __contains__(self, k):
+    return os.path.exists(os.path.join(SUITE, k))
+
+  def __getitem__(self, k):
+    with open(os.path.join(SUITE, k)) as f:
+      return f.read()
+
+
+def cartpole_xml(n_poles):
+  """suite/cartpole.py:105-127 _make_model: a chain of pole bodies below the first one and
+  the floor moved down (camera moves are rendering only and left out)."""
+  import xml.etree.ElementTree as ET
+  root = ET.fromstring(open(os.path.join(SUITE, "cartpole.xml")).read())
+  parent = root.find("./worldbody/body/body")
+  for i in range(2, n_poles + 1):
+    child = ET.SubElement(parent, "body", name="pole_%d" % i, pos="0 0 1", childclass="pole")
+    ET.SubElement(child, "joint", name="hinge_%d" % i)
+    ET.SubElement(child, "geom", name="pole_%d" % i)
+    parent = child
+  root.find("./worldbody/geom").set("pos", "0 0 %s" % (1 - n_poles - .05))
+  return ET.tostring(root, encoding="unicode")
+
+
+def cartpoles():
+  for n in (2, 3):
+    m = C.compile_xml(cartpole_xml(n), _Dir())
+    m.save(os.path.join(OUT, "cartpole%d.npz" % n))
+    print("cartpole%d nq" % n, m.nq, "nbody", m.nbody, "npair", m.npair)
+
+
 def swimmers():
-  class _Dir(dict):
-    def __contains__(self, k):
-      return os.path.exists(os.path.join(SUITE, k))
-
-    def __getitem__(self, k):
-      with open(os.path.join(SUITE, k)) as f:
-        return f.read()
-
   for n in (6, 15):
     m = C.compile_xml(swimmer_xml(n), _Dir())
     m.save(os.path.join(OUT, "swimmer%d.npz" % n))
@@ -122,3 +145,4 @@ if __name__ == "__main__":
   main()
   quadruped()
   swimmers()
+  cartpoles()
