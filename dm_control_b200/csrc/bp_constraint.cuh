@@ -100,6 +100,31 @@ BP_STAGE void bp_make_constraint(const C& c) {
       base += tot;
     }
   }
+  // tendon limits, after the joint limits (tendons are few: one group pass each)
+  const int ten_base = base;
+  if (!(m.opt_disableflags & DSBL_LIMIT)) {
+#pragma unroll 1
+    for (int t0 = 0; t0 < m.ntendon; t0 += C::G) {
+      int t = t0 + c.lane, n = 0;
+      double dist0 = 0, dist1 = 0, margin = 0;
+      bool on0 = false, on1 = false;
+      if (t < m.ntendon && m.tendon_limited[t]) {
+        double len = DF(ten_length)[t];
+        margin = m.tendon_margin[t];
+        dist0 = -(m.tendon_range[2 * t] - len);
+        dist1 = m.tendon_range[2 * t + 1] - len;
+        on0 = dist0 < margin; on1 = dist1 < margin;
+        n = on0 + on1;
+      }
+      int tot, start = base + group_excl_scan(c, n, &tot);
+      if (on0) {
+        if (start < njmax) bp_row_header(c, start, CN_LIMIT_TENDON, t, dist0, margin, 0);
+        start++;
+      }
+      if (on1 && start < njmax) bp_row_header(c, start, CN_LIMIT_TENDON, t, dist1, margin, 0);
+      base += tot;
+    }
+  }
   int con_base = base, ncon = IF(ncon)[0], con_end = 0;
   const bool pyramidal = m.opt_cone == 0;
   // a contact gets all of its rows or none (mj_addConstraint reserves the whole block);
@@ -165,13 +190,26 @@ BP_STAGE void bp_make_constraint(const C& c) {
     J[r * nvp + IF(efc_id)[r]] = 1;
   // limit rows: the Jacobian entry is -side; a joint with both sides active owns two
   // adjacent rows, lower bound first
-  for (int r = lim_base + c.lane; r < con_base && r < nefc; r += C::G) {
+  for (int r = lim_base + c.lane; r < ten_base && r < nefc; r += C::G) {
     int j = IF(efc_id)[r];
     double q = DF(qpos)[m.jnt_qposadr[j]];
     bool lower_on = -(m.jnt_range[2 * j] - q) < m.jnt_margin[j];
     bool first = (r == lim_base) || IF(efc_id)[r - 1] != j;
     int side = (lower_on && first) ? -1 : 1;
     J[r * nvp + m.jnt_dofadr[j]] = -side;
+  }
+  // tendon limit rows: -side * (tendon Jacobian)
+  for (int r = ten_base + c.lane; r < con_base && r < nefc; r += C::G) {
+    int t = IF(efc_id)[r];
+    bool lower_on = -(m.tendon_range[2 * t] - DF(ten_length)[t]) < m.tendon_margin[t];
+    bool first = (r == ten_base) || IF(efc_id)[r - 1] != t;
+    double side = (lower_on && first) ? -1 : 1;
+    if (m.tendon_Jadr[t] >= 0) {
+      for (int i = 0; i < nv; i++) J[r * nvp + i] = -side * DF(ten_J)[m.tendon_Jadr[t] * nv + i];
+    } else {
+      for (int w = m.tendon_adr[t]; w < m.tendon_adr[t] + m.tendon_num[t]; w++)
+        J[r * nvp + m.jnt_dofadr[m.wrap_objid[w]]] += -side * m.wrap_prm[w];
+    }
   }
   auto cdof = DF(cdof), com = DF(subtree_com);
 #pragma unroll 1
@@ -241,6 +279,10 @@ BP_STAGE void bp_make_constraint(const C& c) {
       for (int k = 0; k < 2; k++) solref[k] = m.jnt_solref[2 * id + k];
       for (int k = 0; k < 5; k++) solimp[k] = m.jnt_solimp[5 * id + k];
       dA = m.dof_invweight0[m.jnt_dofadr[id]];
+    } else if (type == CN_LIMIT_TENDON) {
+      for (int k = 0; k < 2; k++) solref[k] = m.tendon_solref_lim[2 * id + k];
+      for (int k = 0; k < 5; k++) solimp[k] = m.tendon_solimp_lim[5 * id + k];
+      dA = m.tendon_invweight0[id];
     } else {
       for (int k = 0; k < 2; k++) solref[k] = DF(contact_solref)[2 * id + k];
       for (int k = 0; k < 5; k++) solimp[k] = DF(contact_solimp)[5 * id + k];

@@ -197,10 +197,56 @@ BP_STAGE void bp_transmission(const C& c) {
   if (m.ntendon > 0) {
     auto tl = DF(ten_length);
     for (int t = c.lane; t < m.ntendon; t += C::G) {
+      if (m.tendon_Jadr[t] >= 0) continue;
       double s = 0;
       for (int w = m.tendon_adr[t]; w < m.tendon_adr[t] + m.tendon_num[t]; w++)
         s += m.wrap_prm[w] * qpos[m.jnt_qposadr[m.wrap_objid[w]]];
       tl[t] = s;
+    }
+    // spatial tendons (straight segments between sites): dofs on lanes build the dense
+    // Jacobian row  sum_seg (jacp(p1) - jacp(p0))^T dir;  lane 0 keeps the length
+    if (m.nspatial > 0) {
+      auto sx = DF(site_xpos), cdof = DF(cdof), com = DF(subtree_com), tJ = DF(ten_J);
+#pragma unroll 1
+      for (int t = 0; t < m.ntendon; t++) {
+        const int ja = m.tendon_Jadr[t];
+        if (ja < 0) continue;
+        double length = 0;
+        for (int i0 = 0; i0 < m.nv; i0 += C::G) {
+          const int i = i0 + c.lane;
+          double acc = 0;
+          length = 0;
+#pragma unroll 1
+          for (int w = m.tendon_adr[t]; w + 1 < m.tendon_adr[t] + m.tendon_num[t]; w++) {
+            const int s0 = m.wrap_objid[w], s1 = m.wrap_objid[w + 1];
+            double p0[3], p1[3], dif[3];
+            for (int k = 0; k < 3; k++) { p0[k] = sx[3 * s0 + k]; p1[k] = sx[3 * s1 + k]; dif[k] = p1[k] - p0[k]; }
+            const double dist = sqrt(dif[0] * dif[0] + dif[1] * dif[1] + dif[2] * dif[2]);
+            if (dist < BP_MINVAL) { dif[0] = 1; dif[1] = 0; dif[2] = 0; }
+            else for (int k = 0; k < 3; k++) dif[k] /= dist;
+            length += dist;
+            if (i >= m.nv) continue;
+            const int b0 = m.site_bodyid[s0], b1 = m.site_bodyid[s1];
+            double cd[6], j0[3] = {0, 0, 0}, j1[3] = {0, 0, 0};
+            for (int k = 0; k < 6; k++) cd[k] = cdof[6 * i + k];
+            if ((m.body_dofmask[b0] >> i) & 1ull) {
+              auto cm = com + 3 * m.body_rootid[b0];
+              double off[3] = {p0[0] - cm[0], p0[1] - cm[1], p0[2] - cm[2]}, x[3];
+              cross3(x, cd, off);
+              for (int k = 0; k < 3; k++) j0[k] = cd[3 + k] + x[k];
+            }
+            if ((m.body_dofmask[b1] >> i) & 1ull) {
+              auto cm = com + 3 * m.body_rootid[b1];
+              double off[3] = {p1[0] - cm[0], p1[1] - cm[1], p1[2] - cm[2]}, x[3];
+              cross3(x, cd, off);
+              for (int k = 0; k < 3; k++) j1[k] = cd[3 + k] + x[k];
+            }
+            for (int k = 0; k < 3; k++) acc += (j1[k] - j0[k]) * dif[k];
+          }
+          if (i < m.nv) tJ[ja * m.nv + i] = acc;
+        }
+        if (c.lane == 0) tl[t] = length;
+      }
     }
     SYNC();
   }
@@ -217,8 +263,11 @@ BP_STAGE void bp_actuator_velocity(const C& c) {
   auto vel = DF(actuator_velocity), qvel = DF(qvel);
   for (int t = c.lane; t < m.ntendon; t += C::G) {
     double s = 0;
-    for (int w = m.tendon_adr[t]; w < m.tendon_adr[t] + m.tendon_num[t]; w++)
-      s += m.wrap_prm[w] * qvel[m.jnt_dofadr[m.wrap_objid[w]]];
+    if (m.tendon_Jadr[t] >= 0)
+      for (int i = 0; i < m.nv; i++) s += DF(ten_J)[m.tendon_Jadr[t] * m.nv + i] * qvel[i];
+    else
+      for (int w = m.tendon_adr[t]; w < m.tendon_adr[t] + m.tendon_num[t]; w++)
+        s += m.wrap_prm[w] * qvel[m.jnt_dofadr[m.wrap_objid[w]]];
     DF(ten_velocity)[t] = s;
   }
   for (int i = c.lane; i < m.nu; i += C::G) {

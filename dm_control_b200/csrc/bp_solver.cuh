@@ -561,7 +561,8 @@ __device__ __forceinline__ double bp_newton_grad(const C& c) {
 // +-1, and add their weight to one diagonal entry; the rows of a contact are non-zero only on
 // the dofs that move its two bodies (body_dofmask), so a contact updates the
 // k (k + 1) / 2 entries of that dof set, split over the lanes by outer dof.
-BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refactor) {
+BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, int ntenlim,
+                                  bool refactor) {
   const BpModel& m = c.P.m;
   const int nv = m.nv, nvp = m.nvp;
   const int ntri = m.ntri;
@@ -584,9 +585,12 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refacto
     for (int r = ne; r < ne + nsingle; r++)
       if ((int)rdof[r] == i) acc += rw[r];
     if (acc != 0) H[PK(i, i)] += acc;
-    // equality rows (the first ne): a few non-zeros each, row i of the lower triangle
+    // equality rows (the first ne) and tendon-limit rows (after the single-entry rows): a
+    // few non-zeros each, row i of the lower triangle
 #pragma unroll 1
-    for (int r = 0; r < ne; r++) {
+    for (int r = 0; r < ne + nsingle + ntenlim; r++) {
+      if (r == ne) r += nsingle;
+      if (r >= ne + nsingle + ntenlim) break;
       const double ji = J[r * nvp + i];
       if (ji == 0) continue;
       const double w = rw[r] * ji;
@@ -662,7 +666,7 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, bool refacto
 // Solver state that lives across Newton iterations (registers of the calling kernel)
 struct BpSolve {
   double cost, improvement, gradient;
-  int iter, nefc, nsingle;
+  int iter, nefc, nsingle, ntenlim;
   bool done, stale;      // stale: the factorisation does not match the active set
 };
 
@@ -671,7 +675,7 @@ BP_STAGE void bp_solver_begin(const C& c, BpSolve& st) {
   const BpModel& m = c.P.m;
   const int nv = m.nv, nvp = m.nvp, nefc = IF(nefc)[0];
   auto qacc = DF(qacc), warm = DF(qacc_warmstart), as = DF(qacc_smooth);
-  st.iter = 0; st.improvement = 0; st.gradient = 0; st.nefc = nefc; st.nsingle = 0;
+  st.iter = 0; st.improvement = 0; st.gradient = 0; st.nefc = nefc; st.nsingle = 0; st.ntenlim = 0;
   st.stale = false;
   st.cost = 0;
   if (nefc == 0) {
@@ -686,15 +690,17 @@ BP_STAGE void bp_solver_begin(const C& c, BpSolve& st) {
   }
   // friction-loss and limit rows come first and have a single +-1 entry: remember
   // its dof; `nsingle` = number of such rows
-  int nsingle = 0;
+  int nsingle = 0, ntenlim = 0;
 #pragma unroll 1
   for (int r = c.lane; r < nefc; r += C::G) {
     int t = IF(efc_type)[r], id = IF(efc_id)[r];
     if (t == CN_FRICTION_DOF) { DF(s_rdof)[r] = id; nsingle++; }
     else if (t == CN_LIMIT_JOINT) { DF(s_rdof)[r] = m.jnt_dofadr[id]; nsingle++; }
+    else if (t == CN_LIMIT_TENDON) ntenlim++;
   }
   nsingle = (int)(group_sum(c, (double)nsingle) + 0.5);
-  st.nsingle = nsingle;
+  if (m.ntendon > 0) ntenlim = (int)(group_sum(c, (double)ntenlim) + 0.5);
+  st.nsingle = nsingle; st.ntenlim = ntenlim;
   // dense copy of M as a packed lower triangle
   auto Md = DF(s_Md), qM = DF(qM);
   for (int w = c.lane; w < m.ntri; w += C::G) Md[w] = 0;
@@ -729,7 +735,7 @@ BP_STAGE void bp_solver_begin(const C& c, BpSolve& st) {
   bool changed;
   st.cost = bp_update_constraint(c, jar, nefc, true, &changed) + bp_gauss_cost(c);
   bp_newton_grad(c);
-  bp_newton_gradient(c, nefc, nsingle, true);
+  bp_newton_gradient(c, nefc, nsingle, ntenlim, true);
   for (int i = c.lane; i < nv; i += C::G) search[i] = -HOT(s_Mgrad, m.ntri + 2 * nv)[i];
   SYNC();
   st.done = m.opt_iterations <= 0;
@@ -767,7 +773,7 @@ BP_STAGE void bp_solver_step(const C& c, BpSolve& st) {
 
 BP_STAGE void bp_solver_direction(const C& c, BpSolve& st) {
   const BpModel& m = c.P.m;
-  bp_newton_gradient(c, st.nefc, st.nsingle, st.stale);
+  bp_newton_gradient(c, st.nefc, st.nsingle, st.ntenlim, st.stale);
   st.stale = false;
   auto search = DF(s_search);
   for (int i = c.lane; i < m.nv; i += C::G) search[i] = -HOT(s_Mgrad, m.ntri + 2 * m.nv)[i];

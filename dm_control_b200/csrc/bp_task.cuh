@@ -18,7 +18,7 @@ enum { TASK_NONE = 0, TASK_CARTPOLE = 1, TASK_ACROBOT = 2, TASK_PENDULUM = 3,
        TASK_REACHER = 8, TASK_FINGER = 9, TASK_QUADRUPED = 10, TASK_QUADRUPED_ESCAPE = 11,
        TASK_LQR = 12, TASK_POINT_MASS = 13, TASK_FINGER_TURN = 14,
        TASK_SWIMMER = 15, TASK_FISH_UPRIGHT = 16,
-       TASK_FISH_SWIM = 17 };
+       TASK_FISH_SWIM = 17, TASK_BALL_IN_CUP = 18 };
 enum { SIG_GAUSSIAN = 0, SIG_LINEAR = 1, SIG_QUADRATIC = 2, SIG_LONG_TAIL = 3 };
 
 // read-only strided window of one environment's image (see bp_math.cuh for layouts)
@@ -303,6 +303,18 @@ static __device__ __noinline__ void bp_task_eval(const BpParams& P, const BpTask
       } else {
         r = tolerance(up, 1, 1, 1, SIG_GAUSSIAN, .1);
       }
+      break;
+    }
+    case TASK_BALL_IN_CUP: {  // suite/ball_in_cup.py:49-63,99-110
+      // ip: target site, ball body; fp: target half sizes (x, z) minus the ball radius
+      const ImgView sx = d.at(L.site_xpos), xp = d.at(L.xpos);
+      if (o) {
+        for (int i = 0; i < m.nq; i++) o[k++] = qpos[i];
+        for (int i = 0; i < m.nv; i++) o[k++] = qvel[i];
+      }
+      double ex = fabs(sx[3 * T.ip[0]] - xp[3 * T.ip[1]]);
+      double ez = fabs(sx[3 * T.ip[0] + 2] - xp[3 * T.ip[1] + 2]);
+      r = (ex < T.fp[0] && ez < T.fp[1]) ? 1.0 : 0.0;
       break;
     }
     case TASK_LQR: {        // suite/lqr.py:236-250; fp: control cost coefficient

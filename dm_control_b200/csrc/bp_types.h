@@ -42,7 +42,7 @@ enum { BP_MODE_STEP = 0, BP_MODE_FORWARD = 1, BP_MODE_STEP1 = 2,
 #define BP_MODEL_INT_SCALARS(X) \
   X(nq) X(nv) X(nu) X(na) X(nbody) X(njnt) X(ngeom) X(nsite) X(nM) X(npair) \
   X(nconmax) X(njmax) X(nsensor) X(nsensordata) X(nkey) X(ntendon) X(neq) \
-  X(nhfield) X(nhfielddata) X(nhfpair) \
+  X(nhfield) X(nhfielddata) X(nhfpair) X(nspatial) \
   X(opt_integrator) X(opt_cone) X(opt_solver) X(opt_iterations) \
   X(opt_ls_iterations) X(opt_disableflags) X(opt_enableflags)
 #define BP_MODEL_F64_SCALARS(X) \
@@ -59,7 +59,8 @@ enum { BP_MODE_STEP = 0, BP_MODE_FORWARD = 1, BP_MODE_STEP1 = 2,
   X(actuator_forcelimited) X(sensor_type) X(sensor_objtype) X(sensor_objid) \
   X(sensor_dim) X(sensor_adr) X(sensor_needstage) X(tendon_adr) X(tendon_num) \
   X(wrap_objid) X(eq_type) X(eq_obj1id) X(eq_obj2id) X(eq_active) \
-  X(geom_dataid) X(hfield_nrow) X(hfield_ncol) X(hfield_adr)
+  X(geom_dataid) X(hfield_nrow) X(hfield_ncol) X(hfield_adr) X(wrap_type) \
+  X(tendon_limited) X(tendon_Jadr)
 #define BP_MODEL_F64_ARRAYS(X) \
   X(opt_gravity) X(body_pos) X(body_quat) X(body_ipos) X(body_iquat) \
   X(body_mass) X(body_subtreemass) X(body_inertia) X(body_invweight0) \
@@ -71,7 +72,8 @@ enum { BP_MODE_STEP = 0, BP_MODE_FORWARD = 1, BP_MODE_STEP1 = 2,
   X(site_pos) X(site_quat) X(site_size) X(qpos0) X(qpos_spring) \
   X(actuator_dynprm) X(actuator_gainprm) X(actuator_biasprm) \
   X(actuator_ctrlrange) X(actuator_forcerange) X(actuator_gear) \
-  X(sensor_cutoff) X(wrap_prm) X(tendon_length0) X(tendon_invweight0) X(tendon_stiffness) X(tendon_damping) X(eq_solref) \
+  X(sensor_cutoff) X(wrap_prm) X(tendon_length0) X(tendon_invweight0) X(tendon_stiffness) X(tendon_damping) X(tendon_range) X(tendon_margin) \
+  X(tendon_solref_lim) X(tendon_solimp_lim) X(eq_solref) \
   X(eq_solimp) X(eq_data) X(hfield_size) X(hfield_data)
 // ---- arrays derived on the host when the model is created (bp_api.cu) ---------
 //   body_level_*: bodies grouped by tree depth (parents complete before children)
@@ -128,7 +130,7 @@ struct BpModel {
   X(qfrc_bias, m.nv) X(qfrc_passive, m.nv) X(qfrc_actuator, m.nv) \
   X(qfrc_smooth, m.nv) X(qacc_smooth, m.nv) X(qfrc_constraint, m.nv) \
   X(actuator_length, m.nu) X(actuator_velocity, m.nu) X(actuator_force, m.nu) \
-  X(ten_length, m.ntendon) X(ten_velocity, m.ntendon) \
+  X(ten_length, m.ntendon) X(ten_velocity, m.ntendon) X(ten_J, m.nspatial * m.nv) \
   X(sensordata, m.nsensordata) X(efc_J, njmax * m.nvp) X(efc_pos, njmax) \
   X(efc_margin, njmax) X(efc_frictionloss, njmax) X(efc_diagApprox, njmax) \
   X(efc_KBIP, 4 * njmax) X(efc_D, njmax) X(efc_R, njmax) X(efc_vel, njmax) \

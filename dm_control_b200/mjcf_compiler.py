@@ -780,39 +780,67 @@ def _solimp(text):
 
 
 def _emit_tendons_equality(m, root, classes):
-  """Fixed tendons (<tendon><fixed>) and tendon / joint equalities [MJ-doc: XML reference].
-  A fixed tendon's length is sum(coef * qpos[joint]); its Jacobian is constant.  Spatial
-  tendons, tendon limits / friction are outside the served models."""
-  T = {"adr": [], "num": [], "stiffness": [], "damping": []}
-  wrap_obj, wrap_prm = [], []
+  """Tendons and tendon / joint equalities [MJ-doc: XML reference].  A fixed tendon's
+  length is sum(coef * qpos[joint]) with a constant Jacobian; a spatial tendon here is a
+  straight path through sites (wrapping geoms and pulleys are outside the served models).
+  Tendon limits and spring-dampers are emitted; tendon friction loss is not served."""
+  T = {k: [] for k in ("adr", "num", "stiffness", "damping", "limited", "range", "margin",
+                       "solref", "solimp", "jadr")}
+  wrap_obj, wrap_prm, wrap_type = [], [], []
+  nspatial = 0
   for sec in root.findall("tendon"):
     for el in sec:
-      if el.tag != "fixed":
-        raise ValueError("tendon <%s> unsupported (fixed tendons only)" % el.tag)
+      if el.tag not in ("fixed", "spatial"):
+        raise ValueError("tendon <%s> unsupported" % el.tag)
       a = dict(classes[el.get("class") or "main"].get("tendon"))
-      a.update(classes[el.get("class") or "main"].get("fixed"))
+      a.update(classes[el.get("class") or "main"].get(el.tag))
       a.update(el.attrib)
+      if a.get("frictionloss", "0") not in ("0", "0.0"):
+        raise ValueError("tendon attribute frictionloss unsupported")
       T["stiffness"].append(float(a.get("stiffness", 0)))
       T["damping"].append(float(a.get("damping", 0)))
-      for k in ("limited", "frictionloss"):
-        if a.get(k, "false" if k == "limited" else "0") not in ("false", "0", "0.0"):
-          raise ValueError("tendon attribute %s unsupported" % k)
+      T["limited"].append(1 if a.get("limited", "false") == "true" else 0)
+      T["range"].append(_floats(a.get("range", "0 0"), 2))
+      T["margin"].append(float(a.get("margin", 0)))
+      T["solref"].append(_floats(a.get("solreflimit", "0.02 1"), 2))
+      T["solimp"].append(_solimp(a.get("solimplimit")))
       m.names["tendon"].append(a.get("name", ""))
       T["adr"].append(len(wrap_obj))
-      for w in el:
-        if w.tag != "joint":
-          raise ValueError("fixed tendon child <%s>" % w.tag)
-        j = m.name2id(w.get("joint"), "joint")
-        if m.jnt_type[j] not in (M.JNT_SLIDE, M.JNT_HINGE):
-          raise ValueError("fixed tendons wrap scalar joints")
-        wrap_obj.append(j); wrap_prm.append(float(w.get("coef")))
+      if el.tag == "fixed":
+        T["jadr"].append(-1)
+        for w in el:
+          if w.tag != "joint":
+            raise ValueError("fixed tendon child <%s>" % w.tag)
+          j = m.name2id(w.get("joint"), "joint")
+          if m.jnt_type[j] not in (M.JNT_SLIDE, M.JNT_HINGE):
+            raise ValueError("fixed tendons wrap scalar joints")
+          wrap_obj.append(j); wrap_prm.append(float(w.get("coef")))
+          wrap_type.append(M.WRAP_JOINT)
+      else:
+        if T["stiffness"][-1] or T["damping"][-1]:
+          raise ValueError("spatial tendon spring-dampers unsupported")
+        T["jadr"].append(nspatial); nspatial += 1
+        for w in el:
+          if w.tag != "site":
+            raise ValueError("spatial tendon child <%s> unsupported (sites only)" % w.tag)
+          wrap_obj.append(m.name2id(w.get("site"), "site")); wrap_prm.append(0.0)
+          wrap_type.append(M.WRAP_SITE)
+        if len(wrap_obj) - T["adr"][-1] < 2:
+          raise ValueError("spatial tendon needs two sites")
       T["num"].append(len(wrap_obj) - T["adr"][-1])
   nt = len(T["adr"])
-  m.set("ntendon", nt); m.set("nwrap", len(wrap_obj))
+  m.set("ntendon", nt); m.set("nwrap", len(wrap_obj)); m.set("nspatial", nspatial)
   m.set("tendon_adr", np.array(T["adr"], dtype=np.int32).reshape(nt))
   m.set("tendon_num", np.array(T["num"], dtype=np.int32).reshape(nt))
+  m.set("tendon_limited", np.array(T["limited"], dtype=np.int32).reshape(nt))
+  m.set("tendon_Jadr", np.array(T["jadr"], dtype=np.int32).reshape(nt))
   m.set("tendon_stiffness", np.array(T["stiffness"], dtype=np.float64).reshape(nt))
   m.set("tendon_damping", np.array(T["damping"], dtype=np.float64).reshape(nt))
+  m.set("tendon_range", np.array(T["range"], dtype=np.float64).reshape(nt, 2))
+  m.set("tendon_margin", np.array(T["margin"], dtype=np.float64).reshape(nt))
+  m.set("tendon_solref_lim", np.array(T["solref"], dtype=np.float64).reshape(nt, 2))
+  m.set("tendon_solimp_lim", np.array(T["solimp"], dtype=np.float64).reshape(nt, 5))
+  m.set("wrap_type", np.array(wrap_type, dtype=np.int32).reshape(len(wrap_obj)))
   m.set("wrap_objid", np.array(wrap_obj, dtype=np.int32).reshape(len(wrap_obj)))
   m.set("wrap_prm", np.array(wrap_prm, dtype=np.float64).reshape(len(wrap_prm)))
   # equalities: residual = (x1 - x1_0) - poly(x2 - x2_0), x = joint position / tendon length
@@ -827,6 +855,9 @@ def _emit_tendons_equality(m, root, classes):
       m.names["equality"].append(a.get("name", ""))
       E["type"].append(M.EQ_TENDON if kind == "tendon" else M.EQ_JOINT)
       E["obj1id"].append(m.name2id(a[kind + "1"], kind))
+      if kind == "tendon" and any(m.tendon_Jadr[m.name2id(a[k], kind)] >= 0
+                                  for k in ("tendon1", "tendon2") if k in a):
+        raise ValueError("equality on a spatial tendon unsupported")
       E["obj2id"].append(m.name2id(a[kind + "2"], kind) if kind + "2" in a else -1)
       E["active"].append(0 if a.get("active") == "false" else 1)
       E["solref"].append(_floats(a.get("solref", "0.02 1"), 2))
@@ -878,6 +909,8 @@ def _emit_actuators(m, root, classes):
         trn, tid = M.TRN_JOINT, m.name2id(a["joint"], "joint")
       elif "tendon" in a:
         trn, tid = M.TRN_TENDON, m.name2id(a["tendon"], "tendon")
+        if m.tendon_Jadr[tid] >= 0:
+          raise ValueError("actuator on a spatial tendon unsupported")
       else:
         raise ValueError("actuator transmission unsupported")
       gear = _floats(a.get("gear", "1"))
@@ -1144,10 +1177,24 @@ def _set_const(m):
   tlen = np.zeros(nt); tinv = np.zeros(nt)
   for t in range(nt):
     J = np.zeros(nv)
-    for w in range(m.tendon_adr[t], m.tendon_adr[t] + m.tendon_num[t]):
-      j = m.wrap_objid[w]
-      tlen[t] += m.wrap_prm[w] * m.qpos0[m.jnt_qposadr[j]]
-      J[m.jnt_dofadr[j]] += m.wrap_prm[w]
+    w0, w1 = m.tendon_adr[t], m.tendon_adr[t] + m.tendon_num[t]
+    if m.tendon_Jadr[t] < 0:
+      for w in range(w0, w1):
+        j = m.wrap_objid[w]
+        tlen[t] += m.wrap_prm[w] * m.qpos0[m.jnt_qposadr[j]]
+        J[m.jnt_dofadr[j]] += m.wrap_prm[w]
+    else:                                  # straight segments between sites
+      def site_point(sid):
+        b = m.site_bodyid[sid]
+        return b, kin["xpos"][b] + quat_to_mat(kin["xquat"][b]) @ m.site_pos[sid]
+      for w in range(w0, w1 - 1):
+        b0, p0 = site_point(m.wrap_objid[w])
+        b1, p1 = site_point(m.wrap_objid[w + 1])
+        dif = p1 - p0
+        dist = float(np.linalg.norm(dif))
+        tlen[t] += dist
+        dirn = dif / dist if dist > M.MINVAL else np.array([1.0, 0, 0])
+        J += dirn @ (host_jac(m, kin, b1, p1)[0] - host_jac(m, kin, b0, p0)[0])
     tinv[t] = J @ Minv @ J
   m.set("tendon_length0", tlen.reshape(nt)); m.set("tendon_invweight0", tinv.reshape(nt))
   m.set("dof_M0", m0); m.set("dof_invweight0", dinv)

@@ -63,6 +63,7 @@ SENSOR_TYPES = ["touch", "accelerometer", "velocimeter", "gyro", "force",
 SENS = {n: i for i, n in enumerate(SENSOR_TYPES)}
 STAGE_NONE, STAGE_POS, STAGE_VEL, STAGE_ACC = range(4)
 
+WRAP_NONE, WRAP_JOINT, WRAP_PULLEY, WRAP_SITE, WRAP_SPHERE, WRAP_CYLINDER = range(6)
 TRN_JOINT, TRN_JOINTINPARENT, TRN_SLIDERCRANK, TRN_TENDON, TRN_SITE = range(5)
 EQ_CONNECT, EQ_WELD, EQ_JOINT, EQ_TENDON, EQ_DISTANCE = range(5)
 DYN_NONE, DYN_INTEGRATOR, DYN_FILTER, DYN_MUSCLE, DYN_USER = range(5)

@@ -152,6 +152,18 @@ class Task:
         target_box = .3 if close_target else 2
         gpos[e, tgt, :2] = rng.uniform(-target_box, target_box, size=2)
       physics.set_env_model_field("geom_pos", gpos)
+    elif d == "ball_in_cup":      # suite/ball_in_cup.py:69-84: a ball position without contacts
+      bx = m.jnt_qposadr[m.name2id("ball_x", "joint")]
+      bz = m.jnt_qposadr[m.name2id("ball_z", "joint")]
+      todo = np.ones(n, dtype=bool)
+      while todo.any():
+        for e in np.flatnonzero(todo):
+          qpos[e, bx] = self._rngs[e].uniform(-.2, .2)
+          qpos[e, bz] = self._rngs[e].uniform(.2, .5)
+        physics.data.qpos = qpos
+        physics.after_reset()
+        todo &= physics.data.ncon > 0
+      return
     elif d == "fish":             # suite/fish.py:107-116,139-150
       tgt = m.name2id("target", "geom")
       root = m.jnt_qposadr[m.name2id("root", "joint")]

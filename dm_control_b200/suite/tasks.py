@@ -19,6 +19,7 @@ REACHER, POINT_MASS = 8, 13
 FINGER_TURN = 14
 SWIMMER = 15
 FISH_UPRIGHT, FISH_SWIM = 16, 17
+BALL_IN_CUP = 18
 
 TaskDef = collections.namedtuple(
     "TaskDef", "domain task model kind time_limit control_timestep params obs")
@@ -152,6 +153,18 @@ def _obs_swimmer(m):
   return [("joints", m.nq - 3), ("to_target", 2), ("body_velocities", 3 * (m.nbody - 1))]
 
 
+def _ball_in_cup(m):
+  # ball_in_cup.py:57-62: |target - ball| < target size - ball size, on x and z
+  tgt = m.name2id("target", "site")
+  ball = float(m.geom_size[m.name2id("ball", "geom"), 0])
+  return ([tgt, m.name2id("ball", "body")],
+          [float(m.site_size[tgt, 0]) - ball, float(m.site_size[tgt, 2]) - ball])
+
+
+def _obs_ball_in_cup(m):
+  return [("position", m.nq), ("velocity", m.nv)]
+
+
 def _fish(m):
   # fish.py:30-36 _JOINTS: the seven tail / fin hinges follow the free root joint
   joints = ["tail1", "tail_twist", "tail2", "finright_roll", "finright_pitch",
@@ -241,6 +254,10 @@ _TASKS = [
             lambda m: [("position", m.nq), ("velocity", m.nv)]),
     # swimmer.py:28-30: 30 s, control timestep .03; fluid drag (option density), the target
     # geom moves per episode and per env
+    # ball_in_cup.py:29-30: 20 s, control timestep .02; the string is a spatial tendon with
+    # a length limit
+    TaskDef("ball_in_cup", "catch", "ball_in_cup", BALL_IN_CUP, 20, .02, _ball_in_cup,
+            _obs_ball_in_cup),
     # fish.py:28-29: 40 s, control timestep .04; gravity and constraints disabled, fluid
     # density 5000, a tendon spring between the fins, position servos
     TaskDef("fish", "upright", "fish", FISH_UPRIGHT, 40, .04, _fish, _obs_fish(False)),

@@ -51,7 +51,7 @@ typedef struct {
 #define MODEL_INT_SCALARS(X) \
   X(nq) X(nv) X(nu) X(na) X(nbody) X(njnt) X(ngeom) X(nsite) X(nM) X(npair) \
   X(nconmax) X(njmax) X(nsensor) X(nsensordata) X(nkey) X(ntendon) X(neq) \
-  X(nhfield) X(nhfielddata) X(nhfpair) \
+  X(nhfield) X(nhfielddata) X(nhfpair) X(nspatial) \
   X(opt_integrator) X(opt_cone) X(opt_solver) X(opt_iterations) \
   X(opt_ls_iterations) X(opt_disableflags) X(opt_enableflags)
 #define MODEL_F64_SCALARS(X) \
@@ -68,7 +68,8 @@ typedef struct {
   X(actuator_forcelimited) X(sensor_type) X(sensor_objtype) X(sensor_objid) \
   X(sensor_dim) X(sensor_adr) X(sensor_needstage) X(tendon_adr) X(tendon_num) \
   X(wrap_objid) X(eq_type) X(eq_obj1id) X(eq_obj2id) X(eq_active) \
-  X(geom_dataid) X(hfield_nrow) X(hfield_ncol) X(hfield_adr)
+  X(geom_dataid) X(hfield_nrow) X(hfield_ncol) X(hfield_adr) X(wrap_type) \
+  X(tendon_limited) X(tendon_Jadr)
 #define MODEL_F64_ARRAYS(X) \
   X(opt_gravity) X(body_pos) X(body_quat) X(body_ipos) X(body_iquat) \
   X(body_mass) X(body_subtreemass) X(body_inertia) X(body_invweight0) \
@@ -81,7 +82,8 @@ typedef struct {
   X(actuator_dynprm) X(actuator_gainprm) X(actuator_biasprm) \
   X(actuator_ctrlrange) X(actuator_forcerange) X(actuator_gear) \
   X(sensor_cutoff) X(key_qpos) X(key_qvel) X(key_act) X(key_time) X(wrap_prm) \
-  X(tendon_length0) X(tendon_invweight0) X(tendon_stiffness) X(tendon_damping) X(eq_solref) X(eq_solimp) X(eq_data) \
+  X(tendon_length0) X(tendon_invweight0) X(tendon_stiffness) X(tendon_damping) X(tendon_range) X(tendon_margin) \
+  X(tendon_solref_lim) X(tendon_solimp_lim) X(eq_solref) X(eq_solimp) X(eq_data) \
   X(hfield_size) X(hfield_data)
 
 struct OModel {
@@ -192,6 +194,7 @@ typedef struct {
   X(actuator_length, double, m->nu) X(actuator_velocity, double, m->nu) \
   X(actuator_moment, double, m->nu * m->nv) X(actuator_force, double, m->nu) \
   X(ten_length, double, m->ntendon) X(ten_velocity, double, m->ntendon) \
+  X(ten_J, double, m->nspatial * m->nv) \
   X(sensordata, double, m->nsensordata) \
   X(efc_J, double, m->njmax * m->nv) X(efc_pos, double, m->njmax) \
   X(efc_margin, double, m->njmax) X(efc_frictionloss, double, m->njmax) \
@@ -751,12 +754,41 @@ static void o_rne(const OModel* m, OData* d, int flg_acc, double* result) {
 
 /* ------------------------------------------------------ actuation [A.6] */
 
-/* fixed tendons: length = sum coef * qpos[joint]; the Jacobian is the constant coef row */
+static void o_jac(const OModel* m, const OData* d, double* jp, double* jr,
+                  const double* point, int body);
+
+/* mj_tendon.  Fixed tendons: length = sum coef * qpos[joint], the Jacobian is the constant
+ * coef row.  Spatial tendons (straight segments between sites, no wrapping geoms or
+ * pulleys): length = sum |p1 - p0|, Jacobian = sum (jacp(p1) - jacp(p0))^T dir, kept in
+ * ten_J (one dense row per spatial tendon). */
 static void o_tendon(const OModel* m, OData* d) {
+  int nv = m->nv;
   for (int t = 0; t < m->ntendon; t++) {
     double len = 0;
-    for (int w = m->tendon_adr[t]; w < m->tendon_adr[t] + m->tendon_num[t]; w++)
-      len += m->wrap_prm[w] * d->qpos[m->jnt_qposadr[m->wrap_objid[w]]];
+    int w0 = m->tendon_adr[t], w1 = w0 + m->tendon_num[t], ja = m->tendon_Jadr[t];
+    if (ja < 0) {
+      for (int w = w0; w < w1; w++)
+        len += m->wrap_prm[w] * d->qpos[m->jnt_qposadr[m->wrap_objid[w]]];
+    } else {
+      double* J = d->ten_J + (size_t)ja * nv;
+      double* jp0 = (double*)malloc(sizeof(double) * 6 * (nv + 1));
+      double* jp1 = jp0 + 3 * nv;
+      memset(J, 0, sizeof(double) * nv);
+      for (int w = w0; w + 1 < w1; w++) {
+        int s0 = m->wrap_objid[w], s1 = m->wrap_objid[w + 1];
+        const double *p0 = d->site_xpos + 3 * s0, *p1 = d->site_xpos + 3 * s1;
+        double dif[3] = {p1[0] - p0[0], p1[1] - p0[1], p1[2] - p0[2]};
+        double dist = sqrt(dif[0] * dif[0] + dif[1] * dif[1] + dif[2] * dif[2]);
+        if (dist < MINVAL) { dif[0] = 1; dif[1] = 0; dif[2] = 0; }
+        else for (int k = 0; k < 3; k++) dif[k] /= dist;
+        len += dist;
+        o_jac(m, d, jp0, NULL, p0, m->site_bodyid[s0]);
+        o_jac(m, d, jp1, NULL, p1, m->site_bodyid[s1]);
+        for (int i = 0; i < nv; i++)
+          for (int k = 0; k < 3; k++) J[i] += (jp1[k * nv + i] - jp0[k * nv + i]) * dif[k];
+      }
+      free(jp0);
+    }
     d->ten_length[t] = len;
   }
 }
@@ -1744,6 +1776,25 @@ static void o_make_constraint(const OModel* m, OData* d) {
         }
       }
     }
+  /* tendon limits: the row is -side * (tendon Jacobian) */
+  if (!(m->opt_disableflags & DSBL_LIMIT))
+    for (int t = 0; t < m->ntendon; t++) {
+      if (!m->tendon_limited[t]) continue;
+      double len = d->ten_length[t], margin = m->tendon_margin[t];
+      for (int side = -1; side <= 1; side += 2) {
+        double dist = side * (m->tendon_range[2 * t + (side + 1) / 2] - len);
+        if (dist < margin) {
+          int r = add_row(m, d, CN_LIMIT_TENDON, t, dist, margin, 0);
+          if (r < 0) return;
+          double* row = d->efc_J + (size_t)r * nv;
+          if (m->tendon_Jadr[t] >= 0)
+            for (int i = 0; i < nv; i++) row[i] = -side * d->ten_J[(size_t)m->tendon_Jadr[t] * nv + i];
+          else
+            for (int w = m->tendon_adr[t]; w < m->tendon_adr[t] + m->tendon_num[t]; w++)
+              row[m->jnt_dofadr[m->wrap_objid[w]]] += -side * m->wrap_prm[w];
+        }
+      }
+    }
   /* contacts */
   double* jp1 = malloc(sizeof(double) * 12 * (nv + 1));
   double *jr1 = jp1 + 3 * nv, *jp2 = jr1 + 3 * nv, *jr2 = jp2 + 3 * nv;
@@ -1818,6 +1869,9 @@ done:
     } else if (type == CN_LIMIT_JOINT) {
       solref = m->jnt_solref + 2 * id; solimp = m->jnt_solimp + 5 * id;
       dA = m->dof_invweight0[m->jnt_dofadr[id]];
+    } else if (type == CN_LIMIT_TENDON) {
+      solref = m->tendon_solref_lim + 2 * id; solimp = m->tendon_solimp_lim + 5 * id;
+      dA = m->tendon_invweight0[id];
     } else {
       OContact* c = d->contact + id;
       solref = c->solref; solimp = c->solimp;
@@ -2687,8 +2741,11 @@ static void fwd_velocity(const OModel* m, OData* d) {
   }
   for (int t = 0; t < m->ntendon; t++) {
     double v = 0;
-    for (int w = m->tendon_adr[t]; w < m->tendon_adr[t] + m->tendon_num[t]; w++)
-      v += m->wrap_prm[w] * d->qvel[m->jnt_dofadr[m->wrap_objid[w]]];
+    if (m->tendon_Jadr[t] >= 0)
+      for (int i = 0; i < nv; i++) v += d->ten_J[(size_t)m->tendon_Jadr[t] * nv + i] * d->qvel[i];
+    else
+      for (int w = m->tendon_adr[t]; w < m->tendon_adr[t] + m->tendon_num[t]; w++)
+        v += m->wrap_prm[w] * d->qvel[m->jnt_dofadr[m->wrap_objid[w]]];
     d->ten_velocity[t] = v;
   }
   o_com_vel(m, d);

@@ -29,7 +29,7 @@ EFC_I32 = ["efc_type", "efc_id", "efc_state"]
 CON_F64 = [("contact_dist", 1), ("contact_pos", 3), ("contact_frame", 9)]
 CON_I32 = ["contact_geom1", "contact_geom2", "contact_dim", "contact_efc_address"]
 INT_SCALARS = ["ncon", "nefc", "ne", "nf", "solver_iter", "warning"]
-TENDON_F64 = ["ten_length", "ten_velocity"]
+TENDON_F64 = ["ten_length", "ten_velocity", "ten_J"]
 
 
 def load_model(domain):

@@ -27,7 +27,7 @@ SERVED = [("cartpole", "swingup"), ("cartpole", "swingup_sparse"), ("cartpole", 
           ("humanoid_CMU", "stand"), ("humanoid_CMU", "run"),
           ("swimmer", "swimmer6"), ("swimmer", "swimmer15"),
           ("fish", "upright"), ("fish", "swim"),
-          ("cartpole", "two_poles"), ("cartpole", "three_poles")]
+          ("ball_in_cup", "catch"), ("cartpole", "two_poles"), ("cartpole", "three_poles")]
 FIELDS = ("qpos", "qvel", "act", "ctrl", "xmat", "xpos", "xipos", "site_xpos", "geom_xpos",
           "geom_xmat", "sensordata")
 

@@ -35,7 +35,7 @@ def _assert_parity(res):
 @pytest.mark.parametrize("domain", ["pendulum", "cartpole", "acrobot", "cheetah", "walker",
                                     "hopper", "finger", "humanoid", "quadruped",
                                     "quadruped_escape", "reacher", "point_mass", "swimmer6",
-                                    "swimmer15", "fish", "cartpole3"])
+                                    "swimmer15", "fish", "cartpole3", "ball_in_cup"])
 @pytest.mark.parametrize("lanes", [32, 8, 4, 1])
 def test_every_field_matches_oracle(domain, lanes):
   kw = SIZES.get(domain, {})

@@ -13,7 +13,7 @@ from dm_control_b200 import mjcf_compiler as C   # noqa: E402
 
 SUITE = "/root/reference/dm_control/suite"
 DOMAINS = ["cartpole", "acrobot", "pendulum", "cheetah", "walker", "humanoid",
-           "hopper", "reacher", "finger", "swimmer", "point_mass", "humanoid_CMU", "fish"]
+           "hopper", "reacher", "finger", "swimmer", "point_mass", "humanoid_CMU", "fish", "ball_in_cup"]
 OUT = os.path.join(ROOT, "dm_control_b200", "suite", "models")
 
 
