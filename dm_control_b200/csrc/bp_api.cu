@@ -326,6 +326,7 @@ struct bp_batch {
   size_t stage_bytes = 0;
   float* hfield = nullptr;         // [nenv_alloc][nhfielddata] per-env elevation data
   double *env_geom_pos = nullptr, *env_site_pos = nullptr;   // per-env model frames (lazy)
+  double *env_body_pos = nullptr, *env_body_quat = nullptr;
   BpTask task;
 };
 
@@ -426,6 +427,8 @@ extern "C" void bp_batch_free(bp_batch* b) {
   if (b->hfield) cudaFree(b->hfield);
   if (b->env_geom_pos) cudaFree(b->env_geom_pos);
   if (b->env_site_pos) cudaFree(b->env_site_pos);
+  if (b->env_body_pos) cudaFree(b->env_body_pos);
+  if (b->env_body_quat) cudaFree(b->env_body_quat);
   if (b->ctrl_stage) cudaFree(b->ctrl_stage);
   if (b->stage) cudaFree(b->stage);
   if (b->obs_dev) cudaFree(b->obs_dev);
@@ -554,6 +557,7 @@ static BpParams make_params(bp_batch* b, int mode, int nsub, int disable_actuati
   P.stride = b->stride; P.interleave = b->interleave; P.lanes = b->lanes;
   P.hfield = b->hfield;
   P.env_geom_pos = b->env_geom_pos; P.env_site_pos = b->env_site_pos;
+  P.env_body_pos = b->env_body_pos; P.env_body_quat = b->env_body_quat;
   return P;
 }
 
@@ -565,8 +569,10 @@ static int env_model_copy(bp_batch* b, const char* name, double* host, int64_t e
   double** slot; int cnt;
   if (strcmp(name, "geom_pos") == 0) { slot = &b->env_geom_pos; cnt = 3 * b->model->M.ngeom; }
   else if (strcmp(name, "site_pos") == 0) { slot = &b->env_site_pos; cnt = 3 * b->model->M.nsite; }
+  else if (strcmp(name, "body_pos") == 0) { slot = &b->env_body_pos; cnt = 3 * b->model->M.nbody; }
+  else if (strcmp(name, "body_quat") == 0) { slot = &b->env_body_quat; cnt = 4 * b->model->M.nbody; }
   else return fail(BP_ENOFIELD, std::string("no per-env model field ") + name +
-                   " (geom_pos, site_pos; hfield_data has bp_hfield_write)");
+                   " (geom_pos, site_pos, body_pos, body_quat; hfield_data has bp_hfield_write)");
   if (env0 < 0 || n < 0 || env0 + n > b->nenv) return fail(BP_EINVAL, "env range out of bounds");
   if (cnt == 0 || n == 0) return BP_OK;
   cudaSetDevice(b->model->device);

@@ -35,6 +35,8 @@ struct Ctx {
   const float* hf; // this env's height-field elevation data (nullptr: none)
   const double* gpos;  // this env's geom_pos / site_pos (the model's unless overridden)
   const double* spos;
+  const double* bpos;  // this env's body_pos / body_quat
+  const double* bquat;
   __device__ __forceinline__ DP null() const { return DP{nullptr}; }
 };
 

@@ -379,7 +379,9 @@ bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
   const float* hf = P.hfield ? P.hfield + env * (long long)P.m.nhfielddata : nullptr;
   const double* gp = P.env_geom_pos ? P.env_geom_pos + env * 3LL * P.m.ngeom : P.m.geom_pos;
   const double* sp = P.env_site_pos ? P.env_site_pos + env * 3LL * P.m.nsite : P.m.site_pos;
-  Ctx<G, S> c{P, base, ib, wl & (G - 1), mask, act, lock, hot, hf, gp, sp};
+  const double* bp = P.env_body_pos ? P.env_body_pos + env * 3LL * P.m.nbody : P.m.body_pos;
+  const double* bq = P.env_body_quat ? P.env_body_quat + env * 4LL * P.m.nbody : P.m.body_quat;
+  Ctx<G, S> c{P, base, ib, wl & (G - 1), mask, act, lock, hot, hf, gp, sp, bp, bq};
   bp_load_ctrl(c, env);
   bp_run_mode(c);
   if (P.rew_out && act) {           // epilogue: the task's observation and reward

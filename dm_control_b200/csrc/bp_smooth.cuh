@@ -32,9 +32,9 @@ BP_STAGE void bp_kinematics(const C& c) {
          idx += C::G) {
       int b = m.body_level_list[idx], p = m.body_parentid[b];
       double pos[3], quat[4], R[9], t[3];
-      mat_vec3(t, xmat + 9 * p, m.body_pos + 3 * b);
+      mat_vec3(t, xmat + 9 * p, c.bpos + 3 * b);
       for (int k = 0; k < 3; k++) pos[k] = xpos[3 * p + k] + t[k];
-      quat_mul(quat, xquat + 4 * p, m.body_quat + 4 * b);
+      quat_mul(quat, xquat + 4 * p, c.bquat + 4 * b);
       int jn = m.body_jntnum[b], j0 = m.body_jntadr[b];
 #pragma unroll 1
       for (int k = 0; k < jn; k++) {

@@ -14,8 +14,10 @@ bp_step_kernel_smem(const __grid_constant__ BpParams P) {
   const float* hf = P.hfield ? P.hfield + env * (long long)P.m.nhfielddata : nullptr;
   const double* gp = P.env_geom_pos ? P.env_geom_pos + env * 3LL * P.m.ngeom : P.m.geom_pos;
   const double* sp = P.env_site_pos ? P.env_site_pos + env * 3LL * P.m.nsite : P.m.site_pos;
+  const double* bp = P.env_body_pos ? P.env_body_pos + env * 3LL * P.m.nbody : P.m.body_pos;
+  const double* bq = P.env_body_quat ? P.env_body_quat + env * 4LL * P.m.nbody : P.m.body_quat;
   Ctx<32, 1> c{P, smem, (int*)(smem + P.L.ints), lane, 0xffffffffu, true, false, nullptr, hf,
-               gp, sp};
+               gp, sp, bp, bq};
   bp_load_ctrl(c, env);
   bp_run_mode(c);
   __syncwarp();

@@ -18,7 +18,8 @@ enum { TASK_NONE = 0, TASK_CARTPOLE = 1, TASK_ACROBOT = 2, TASK_PENDULUM = 3,
        TASK_REACHER = 8, TASK_FINGER = 9, TASK_QUADRUPED = 10, TASK_QUADRUPED_ESCAPE = 11,
        TASK_LQR = 12, TASK_POINT_MASS = 13, TASK_FINGER_TURN = 14,
        TASK_SWIMMER = 15, TASK_FISH_UPRIGHT = 16,
-       TASK_FISH_SWIM = 17, TASK_BALL_IN_CUP = 18 };
+       TASK_FISH_SWIM = 17, TASK_BALL_IN_CUP = 18,
+       TASK_MANIPULATOR = 19 };
 enum { SIG_GAUSSIAN = 0, SIG_LINEAR = 1, SIG_QUADRATIC = 2, SIG_LONG_TAIL = 3 };
 
 // read-only strided window of one environment's image (see bp_math.cuh for layouts)
@@ -315,6 +316,29 @@ static __device__ __noinline__ void bp_task_eval(const BpParams& P, const BpTask
       double ex = fabs(sx[3 * T.ip[0]] - xp[3 * T.ip[1]]);
       double ez = fabs(sx[3 * T.ip[0] + 2] - xp[3 * T.ip[1] + 2]);
       r = (ex < T.fp[0] && ez < T.fp[1]) ? 1.0 : 0.0;
+      break;
+    }
+    case TASK_MANIPULATOR: {  // suite/manipulator.py:133-163 (observables), 258-297
+      // ip[0..7]: qpos (= dof) address of the arm joints, [8] first touch sensor address,
+      // [9] hand body, [10] object body, [11] target body, [12] first object joint address,
+      // [13] object site, [14] target site; fp: _CLOSE
+      const ImgView sx = d.at(L.site_xpos), xp = d.at(L.xpos), xq = d.at(L.xquat);
+      if (o) {
+        for (int i = 0; i < 8; i++) { o[k++] = sin(qpos[T.ip[i]]); o[k++] = cos(qpos[T.ip[i]]); }
+        for (int i = 0; i < 8; i++) o[k++] = qvel[T.ip[i]];
+        for (int i = 0; i < 5; i++) o[k++] = log1p(sens[T.ip[8] + i]);
+        for (int q = 0; q < 3; q++) {
+          const int b = T.ip[9 + q];
+          o[k++] = xp[3 * b]; o[k++] = xp[3 * b + 2]; o[k++] = xq[4 * b]; o[k++] = xq[4 * b + 2];
+          if (q == 1) for (int i = 0; i < 3; i++) o[k++] = qvel[T.ip[12] + i];
+        }
+      }
+      double dd = 0;
+      for (int i = 0; i < 3; i++) {
+        double e = sx[3 * T.ip[13] + i] - sx[3 * T.ip[14] + i];
+        dd += e * e;
+      }
+      r = tolerance(sqrt(dd), 0, T.fp[0], 2 * T.fp[0], SIG_GAUSSIAN, .1);
       break;
     }
     case TASK_LQR: {        // suite/lqr.py:236-250; fp: control cost coefficient

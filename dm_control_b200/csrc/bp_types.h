@@ -187,6 +187,8 @@ struct BpParams {
   // geom, finger.py turn target site); null: every env reads the model's
   const double* env_geom_pos;   // [nenv][3 * ngeom]
   const double* env_site_pos;   // [nenv][3 * nsite]
+  const double* env_body_pos;   // [nenv][3 * nbody]   (manipulator.py:218-224 target body)
+  const double* env_body_quat;  // [nenv][4 * nbody]
   // fused Environment.step (bp_env_step): dense [nenv][nu] controls scattered into the
   // images before the first sub-step, task observation / reward written after the last
   const double* ctrl_in;   // null: images keep their ctrl

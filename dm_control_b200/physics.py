@@ -200,7 +200,8 @@ class BatchedPhysics:
 
   def set_env_model_field(self, name, value, env0=0):
     """Per-env run-time model edit (reacher.py:96-101 `geom_pos['target']`): value is
-    [n, ...] with the model field's trailing shape; supported: geom_pos, site_pos."""
+    [n, ...] with the model field's trailing shape; supported: geom_pos, site_pos,
+    body_pos, body_quat (manipulator.py:218-224)."""
     self._batch.write_env_model(name, value, env0)
 
   def env_model_field(self, name):

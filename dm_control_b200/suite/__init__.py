@@ -152,6 +152,9 @@ class Task:
         target_box = .3 if close_target else 2
         gpos[e, tgt, :2] = rng.uniform(-target_box, target_box, size=2)
       physics.set_env_model_field("geom_pos", gpos)
+    elif d == "manipulator":      # suite/manipulator.py:186-247 (bring_ball: no receptacle)
+      _initialize_manipulator(self, physics, qpos, qvel)
+      return
     elif d == "ball_in_cup":      # suite/ball_in_cup.py:69-84: a ball position without contacts
       bx = m.jnt_qposadr[m.name2id("ball_x", "joint")]
       bz = m.jnt_qposadr[m.name2id("ball_z", "joint")]
@@ -213,6 +216,65 @@ class Task:
       return
     physics.data.qpos = qpos
     physics.data.qvel = qvel
+
+
+def _initialize_manipulator(self, physics, qpos, qvel):
+  """suite/manipulator.py:186-247 for every env at once: each env draws from its own
+  generator in the reference's order until its configuration is collision-free; the
+  'in_hand' envs read the grasp site after a forward pass with their new arm angles."""
+  from dm_control_b200.suite.tasks import MANIPULATOR_ARM_JOINTS
+  m, n = physics.model, physics.nenv
+  arm = [m.name2id(j, "joint") for j in MANIPULATOR_ARM_JOINTS]
+  arm_adr = np.array([m.jnt_qposadr[j] for j in arm])
+  limited = np.asarray(m.jnt_limited)[arm].astype(bool)
+  rng_ = np.asarray(m.jnt_range)[arm]
+  lower = np.where(limited, rng_[:, 0], -np.pi)
+  upper = np.where(limited, rng_[:, 1], np.pi)
+  finger = m.jnt_qposadr[m.name2id("finger", "joint")]
+  thumb = m.jnt_qposadr[m.name2id("thumb", "joint")]
+  target = m.name2id("target_ball", "body")
+  obj = [m.jnt_qposadr[m.name2id("ball_" + k, "joint")] for k in "xzy"]
+  obj_xvel = m.jnt_dofadr[m.name2id("ball_x", "joint")]
+  grasp = m.name2id("grasp", "site")
+  bpos = np.tile(np.asarray(m.body_pos, dtype=np.float64), (n, 1, 1))
+  bquat = np.tile(np.asarray(m.body_quat, dtype=np.float64), (n, 1, 1))
+  todo = np.ones(n, dtype=bool)
+  while todo.any():
+    idx = np.flatnonzero(todo)
+    kind, pose = {}, {}
+    for e in idx:
+      rng = self._rngs[e]
+      qpos[e, arm_adr] = rng.uniform(lower, upper)
+      qpos[e, finger] = qpos[e, thumb]
+      tx, tz = rng.uniform(-.4, .4), rng.uniform(.1, .4)
+      ta = rng.uniform(-np.pi, np.pi)
+      bpos[e, target, 0], bpos[e, target, 2] = tx, tz
+      bquat[e, target, 0], bquat[e, target, 2] = np.cos(ta / 2), np.sin(ta / 2)
+      kind[e] = rng.choice(["in_hand", "in_target", "uniform"], p=[.1, .1, .8])
+      pose[e] = (tx, tz, ta)
+    physics.set_env_model_field("body_pos", bpos)
+    physics.set_env_model_field("body_quat", bquat)
+    if any(k == "in_hand" for k in kind.values()):
+      physics.data.qpos = qpos
+      physics.after_reset()
+      sx = np.asarray(physics.data.site_xpos).reshape(n, -1, 3)
+      sm = np.asarray(physics.data.site_xmat).reshape(n, -1, 9)
+    for e in idx:
+      rng = self._rngs[e]
+      if kind[e] == "in_target":
+        ox, oz, oa = pose[e]
+      elif kind[e] == "in_hand":
+        ox, oz = sx[e, grasp, 0], sx[e, grasp, 2]
+        oa = np.pi - np.arctan2(sm[e, grasp, 6], sm[e, grasp, 0])   # ('zx', 'xx')
+      else:
+        ox, oz = rng.uniform(-.5, .5), rng.uniform(0, .7)
+        oa = rng.uniform(0, 2 * np.pi)
+        qvel[e, obj_xvel] = rng.uniform(-5, 5)
+      qpos[e, obj] = ox, oz, oa
+    physics.data.qpos = qpos
+    physics.data.qvel = qvel
+    physics.after_reset()
+    todo &= physics.data.ncon > 0
 
 
 def _escape_terrain(m, rng):

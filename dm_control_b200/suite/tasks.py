@@ -20,6 +20,7 @@ FINGER_TURN = 14
 SWIMMER = 15
 FISH_UPRIGHT, FISH_SWIM = 16, 17
 BALL_IN_CUP = 18
+MANIPULATOR = 19
 
 TaskDef = collections.namedtuple(
     "TaskDef", "domain task model kind time_limit control_timestep params obs")
@@ -165,6 +166,29 @@ def _obs_ball_in_cup(m):
   return [("position", m.nq), ("velocity", m.nv)]
 
 
+MANIPULATOR_ARM_JOINTS = ["arm_root", "arm_shoulder", "arm_elbow", "arm_wrist",
+                          "finger", "fingertip", "thumb", "thumbtip"]   # manipulator.py:36-37
+
+
+def _manipulator(m):
+  # bring_ball (manipulator.py:70-82): object = ball, target = target_ball
+  arm = [int(m.jnt_qposadr[m.name2id(j, "joint")]) for j in MANIPULATOR_ARM_JOINTS]
+  assert arm == [int(m.jnt_dofadr[m.name2id(j, "joint")]) for j in MANIPULATOR_ARM_JOINTS]
+  touch = [_sens_adr(m, s) for s in ("palm_touch", "finger_touch", "thumb_touch",
+                                     "fingertip_touch", "thumbtip_touch")]
+  assert touch == list(range(touch[0], touch[0] + 5))
+  obj = [int(m.jnt_dofadr[m.name2id("ball_" + k, "joint")]) for k in "xzy"]
+  assert obj == list(range(obj[0], obj[0] + 3))
+  return (arm + [touch[0], m.name2id("hand", "body"), m.name2id("ball", "body"),
+                 m.name2id("target_ball", "body"), obj[0], m.name2id("ball", "site"),
+                 m.name2id("target_ball", "site")], [.01])
+
+
+def _obs_manipulator(m):
+  return [("arm_pos", 16), ("arm_vel", 8), ("touch", 5), ("hand_pos", 4), ("object_pos", 4),
+          ("object_vel", 3), ("target_pos", 4)]
+
+
 def _fish(m):
   # fish.py:30-36 _JOINTS: the seven tail / fin hinges follow the free root joint
   joints = ["tail1", "tail_twist", "tail2", "finright_roll", "finright_pitch",
@@ -258,6 +282,10 @@ _TASKS = [
     # a length limit
     TaskDef("ball_in_cup", "catch", "ball_in_cup", BALL_IN_CUP, 20, .02, _ball_in_cup,
             _obs_ball_in_cup),
+    # manipulator.py:32-33,70-82: 10 s, control timestep .01; fully observable bring_ball
+    # (the model keeps the ball and its target: make_model, 47-67)
+    TaskDef("manipulator", "bring_ball", "manipulator_ball", MANIPULATOR, 10, .01,
+            _manipulator, _obs_manipulator),
     # fish.py:28-29: 40 s, control timestep .04; gravity and constraints disabled, fluid
     # density 5000, a tendon spring between the fins, position servos
     TaskDef("fish", "upright", "fish", FISH_UPRIGHT, 40, .04, _fish, _obs_fish(False)),

@@ -219,6 +219,7 @@ struct OData {
   OContact* contact;
   double* hfield;   /* this env's elevation data (Escape writes it per episode) */
   double *geom_pos, *site_pos;   /* this env's copies (per-episode target moves) */
+  double *body_pos, *body_quat;
   /* solver scratch */
   double *s_Ma, *s_jar, *s_grad, *s_Mgrad, *s_search, *s_Mv, *s_jv, *s_H,
       *s_Mdense, *s_fluid;
@@ -238,6 +239,10 @@ OData* od_create(const OModel* m) {
   d->site_pos = (double*)calloc(m->nsite > 0 ? 3 * m->nsite : 1, sizeof(double));
   for (int i = 0; i < 3 * m->ngeom; i++) d->geom_pos[i] = m->geom_pos[i];
   for (int i = 0; i < 3 * m->nsite; i++) d->site_pos[i] = m->site_pos[i];
+  d->body_pos = (double*)calloc(3 * m->nbody + 1, sizeof(double));
+  d->body_quat = (double*)calloc(4 * m->nbody + 1, sizeof(double));
+  for (int i = 0; i < 3 * m->nbody; i++) d->body_pos[i] = m->body_pos[i];
+  for (int i = 0; i < 4 * m->nbody; i++) d->body_quat[i] = m->body_quat[i];
   int nv = m->nv > 0 ? m->nv : 1, nj = m->njmax > 0 ? m->njmax : 1;
   d->s_Ma = calloc(nv, 8); d->s_jar = calloc(nj, 8); d->s_grad = calloc(nv, 8);
   d->s_Mgrad = calloc(nv, 8); d->s_search = calloc(nv, 8); d->s_Mv = calloc(nv, 8);
@@ -255,6 +260,7 @@ void od_free(OData* d) {
 #undef X
   free(d->contact);
   free(d->hfield); free(d->geom_pos); free(d->site_pos);
+  free(d->body_pos); free(d->body_quat);
   free(d->s_Ma); free(d->s_jar); free(d->s_grad); free(d->s_Mgrad);
   free(d->s_search); free(d->s_Mv); free(d->s_jv); free(d->s_H);
   free(d->s_Mdense); free(d->s_fluid);
@@ -267,6 +273,12 @@ void* od_field(OData* d, const char* name, int64_t* count, int* dtype) {
     if (count) *count = 3 * (g ? d->m->ngeom : d->m->nsite);
     if (dtype) *dtype = 0;
     return g ? d->geom_pos : d->site_pos;
+  }
+  if (strcmp(name, "body_pos") == 0 || strcmp(name, "body_quat") == 0) {
+    int q = name[5] == 'q';
+    if (count) *count = (q ? 4 : 3) * d->m->nbody;
+    if (dtype) *dtype = 0;
+    return q ? d->body_quat : d->body_pos;
   }
   if (strcmp(name, "hfield_data") == 0) {
     if (count) *count = d->m->nhfielddata;
@@ -408,9 +420,9 @@ static void o_kinematics(const OModel* m, OData* d) {
   for (int b = 1; b < m->nbody; b++) {
     int p = m->body_parentid[b];
     double pos[3], quat[4], R[9], t[3];
-    mat_vec3(t, d->xmat + 9 * p, m->body_pos + 3 * b);
+    mat_vec3(t, d->xmat + 9 * p, d->body_pos + 3 * b);
     for (int k = 0; k < 3; k++) pos[k] = d->xpos[3 * p + k] + t[k];
-    quat_mul(quat, d->xquat + 4 * p, m->body_quat + 4 * b);
+    quat_mul(quat, d->xquat + 4 * p, d->body_quat + 4 * b);
     for (int k = 0; k < m->body_jntnum[b]; k++) {
       int j = m->body_jntadr[b] + k, qa = m->jnt_qposadr[j];
       int jt = m->jnt_type[j];

@@ -149,9 +149,16 @@ def compare_env(cmp, m, oracle, gpu, e, nvp, skip=()):
 
 
 def run_parity(domain, nenv=32, nsteps=3, seed=0, njmax=0, nconmax=0, check_steps=None,
-               vel_scale=1.0, spread=1.0, mutate=None, lanes=0, env_model=None):
+               vel_scale=1.0, spread=1.0, mutate=None, lanes=0, env_model=None,
+               iter_slack=False):
   """forward() then `nsteps` Physics.step() on both sides; returns (Comparison per
-  phase, stats).  The GPU side goes through the C ABI (dm_control_b200.binding)."""
+  phase, stats).  The GPU side goes through the C ABI (dm_control_b200.binding).
+
+  iter_slack: the Newton solver stops when improvement or gradient falls below
+  opt.tolerance; on a stiff model an env can sit on that threshold and stop one iteration
+  apart on the two sides, which leaves a tolerance-sized (not rounding-sized) difference.
+  With iter_slack those envs are taken out of the strict comparison from the step their
+  solver_iter first differs and collected in `cmp.loose`; stats["loose"] counts them."""
   from dm_control_b200 import binding
   from oracle.oracle_py import Oracle, OracleModel
   m = load_model(domain)
@@ -190,7 +197,8 @@ def run_parity(domain, nenv=32, nsteps=3, seed=0, njmax=0, nconmax=0, check_step
            CON_I32 + INT_SCALARS + (TENDON_F64 if m.ntendon else []))
   out = {}
   check_steps = set(range(nsteps + 1)) if check_steps is None else set(check_steps)
-  stats = {"ncon": [], "nefc": [], "iter": []}
+  stats = {"ncon": [], "nefc": [], "iter": [], "loose": 0}
+  loose = np.zeros(nenv, dtype=bool)
   for step in range(nsteps + 1):
     if step == 0:
       batch.forward()
@@ -200,12 +208,18 @@ def run_parity(domain, nenv=32, nsteps=3, seed=0, njmax=0, nconmax=0, check_step
       batch.step(1)
       for o in oracles:
         o.step()
+    if iter_slack:
+      batch.sync()
+      it = batch.read("solver_iter")[:, 0]
+      loose |= it != np.array([int(o.solver_iter[0]) for o in oracles])
+      stats["loose"] = int(loose.sum())
     if step in check_steps:
       batch.sync()
       gpu = {n: batch.read(n) for n in names}
       cmp = Comparison()
+      cmp.loose = Comparison()
       for e, o in enumerate(oracles):
-        compare_env(cmp, m, o, gpu, e, nvp)
+        compare_env(cmp.loose if loose[e] else cmp, m, o, gpu, e, nvp)
       out[step] = cmp
       stats["ncon"].append(float(np.mean(gpu["ncon"])))
       stats["nefc"].append(float(np.mean(gpu["nefc"])))

@@ -27,8 +27,8 @@ SERVED = [("cartpole", "swingup"), ("cartpole", "swingup_sparse"), ("cartpole", 
           ("humanoid_CMU", "stand"), ("humanoid_CMU", "run"),
           ("swimmer", "swimmer6"), ("swimmer", "swimmer15"),
           ("fish", "upright"), ("fish", "swim"),
-          ("ball_in_cup", "catch"), ("cartpole", "two_poles"), ("cartpole", "three_poles")]
-FIELDS = ("qpos", "qvel", "act", "ctrl", "xmat", "xpos", "xipos", "site_xpos", "geom_xpos",
+          ("ball_in_cup", "catch"), ("manipulator", "bring_ball"), ("cartpole", "two_poles"), ("cartpole", "three_poles")]
+FIELDS = ("qpos", "qvel", "act", "ctrl", "xmat", "xpos", "xquat", "xipos", "site_xpos", "geom_xpos",
           "geom_xmat", "sensordata")
 
 

@@ -91,6 +91,26 @@ def cartpole_xml(n_poles):
   return ET.tostring(root, encoding="unicode")
 
 
+def manipulator_xml(use_peg=False, insert=False):
+  """suite/manipulator.py:47-67 make_model: the props the task does not use are removed."""
+  import xml.etree.ElementTree as ET
+  root = ET.fromstring(open(os.path.join(SUITE, "manipulator.xml")).read())
+  required = ["peg", "target_peg"] + (["slot"] if insert else []) if use_peg else \
+             ["ball", "target_ball"] + (["cup"] if insert else [])
+  wb = root.find("worldbody")
+  for b in list(wb.findall("body")):
+    if b.get("name") in ("ball", "target_ball", "cup", "peg", "target_peg", "slot") and \
+       b.get("name") not in required:
+      wb.remove(b)
+  return ET.tostring(root, encoding="unicode")
+
+
+def manipulators():
+  m = C.compile_xml(manipulator_xml(), _Dir())
+  m.save(os.path.join(OUT, "manipulator_ball.npz"))
+  print("manipulator_ball nq", m.nq, "nbody", m.nbody, "npair", m.npair, "neq", m.neq)
+
+
 def cartpoles():
   for n in (2, 3):
     m = C.compile_xml(cartpole_xml(n), _Dir())
@@ -146,3 +166,4 @@ if __name__ == "__main__":
   quadruped()
   swimmers()
   cartpoles()
+  manipulators()
