@@ -3,6 +3,9 @@
 * `ActionScale` — /root/reference/dm_control/suite/wrappers/action_scale.py:29-110 for the
   batched Environment: actions in [minimum, maximum] are mapped affinely onto the wrapped
   env's action bounds (the same transform for every env of the batch).
+* `ActionNoise` — /root/reference/dm_control/suite/wrappers/action_noise.py:25-72: Gaussian
+  noise with std = scale * (max - min) per action dimension, drawn per env from that
+  env's task generator (`env.task.random`, one RandomState per env), then clipped.
 * `BatchedVecEnv` — the `VecEnv` interface of the fork's `SubprocVecEnv`
   (/root/reference/dm_control/scripts/vec_env.py:22-194,396-472): `reset`, `step_async`,
   `step_wait`, `step`, `seed`, `close`, with the worker's auto-reset contract
@@ -66,6 +69,44 @@ class ActionScale:
 
   def action_spec(self):
     return self._action_spec
+
+  def __getattr__(self, name):
+    return getattr(self._env, name)
+
+
+_BOUNDS_MUST_BE_FINITE = (
+    "All bounds in `env.action_spec()` must be finite, got: {action_spec}")
+
+
+class ActionNoise:
+  """Wraps a batched control environment and adds Gaussian noise to actions."""
+
+  def __init__(self, env, scale=0.01):
+    action_spec = env.action_spec()
+    if not (np.all(np.isfinite(action_spec.minimum)) and
+            np.all(np.isfinite(action_spec.maximum))):
+      raise ValueError(_BOUNDS_MUST_BE_FINITE.format(action_spec=action_spec))
+    self._minimum = action_spec.minimum
+    self._maximum = action_spec.maximum
+    self._noise_std = scale * (action_spec.maximum - action_spec.minimum)
+    self._env = env
+
+  def step(self, action):
+    action = np.asarray(action, dtype=np.float64)
+    noise = np.stack([np.broadcast_to(rng.normal(scale=self._noise_std), action.shape[1:])
+                      for rng in self._env.task.random])
+    noisy_action = action + noise
+    np.clip(noisy_action, self._minimum, self._maximum, out=noisy_action)
+    return self._env.step(noisy_action)
+
+  def reset(self):
+    return self._env.reset()
+
+  def observation_spec(self):
+    return self._env.observation_spec()
+
+  def action_spec(self):
+    return self._env.action_spec()
 
   def __getattr__(self, name):
     return getattr(self._env, name)

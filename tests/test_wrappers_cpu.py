@@ -75,6 +75,26 @@ def test_action_scale_rejects_bad_bounds():
     wrappers.ActionScale(env, -1, 1)
 
 
+def test_action_noise_matches_reference_formula():
+  """suite/wrappers/action_noise_test.py: noise std = scale * range, per env from the
+  task's generators, clipped to the bounds; zero scale leaves the actions alone."""
+  env = FakeEnv(nenv=4, nu=2, lo=-2.0, hi=4.0)
+  env.task.random = [np.random.RandomState(10 + e) for e in range(4)]
+  env.reset()
+  w = wrappers.ActionNoise(env, scale=0.1)
+  act = np.array([[0.0, 1.0], [3.99, -1.99], [4.0, -2.0], [1.0, 1.0]])
+  w.step(act)
+  expect = np.stack([np.random.RandomState(10 + e).normal(scale=0.1 * 6.0 * np.ones(2))
+                     for e in range(4)]) + act
+  np.testing.assert_allclose(env.actions[-1], np.clip(expect, -2.0, 4.0))
+  assert env.actions[-1].min() >= -2.0 and env.actions[-1].max() <= 4.0
+  wrappers.ActionNoise(env, scale=0.0).step(act)
+  np.testing.assert_array_equal(env.actions[-1], act)
+  with pytest.raises(ValueError):
+    wrappers.ActionNoise(FakeEnv(hi=np.inf))
+  assert w.action_spec() is env.action_spec()
+
+
 def test_vec_env_auto_reset_and_terminal_observation():
   env = FakeEnv(nenv=3, length=2)
   v = wrappers.BatchedVecEnv(env)
