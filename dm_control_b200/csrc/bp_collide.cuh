@@ -476,17 +476,21 @@ BP_STAGE void bp_write_contact(const C& c, int id, int g1, int g2, double margin
   double inc = margin - gap;
   DF(contact_includemargin)[id] = inc;
   IF(contact_geom1)[id] = g1; IF(contact_geom2)[id] = g2;
+  // equal priority: max condim, max friction, solmix-weighted solref / solimp; otherwise
+  // everything from the geom with the higher priority
   int d1 = m.geom_condim[g1], d2 = m.geom_condim[g2];
-  IF(contact_dim)[id] = d1 > d2 ? d1 : d2;
+  const int pr1 = m.geom_priority[g1], pr2 = m.geom_priority[g2];
+  IF(contact_dim)[id] = pr1 > pr2 ? d1 : pr2 > pr1 ? d2 : (d1 > d2 ? d1 : d2);
   const double *f1 = m.geom_friction + 3 * g1, *f2 = m.geom_friction + 3 * g2;
   double fr[3];
-  for (int k = 0; k < 3; k++) fr[k] = fmax(f1[k], f2[k]);
+  for (int k = 0; k < 3; k++) fr[k] = pr1 > pr2 ? f1[k] : pr2 > pr1 ? f2[k] : fmax(f1[k], f2[k]);
   auto cf = DF(contact_friction) + 5 * id;
   cf[0] = fr[0]; cf[1] = fr[0]; cf[2] = fr[1]; cf[3] = fr[2]; cf[4] = fr[2];
   double mix1 = m.geom_solmix[g1], mix2 = m.geom_solmix[g2], mix;
   if (mix1 >= BP_MINVAL && mix2 >= BP_MINVAL) mix = mix1 / (mix1 + mix2);
   else if (mix1 < BP_MINVAL && mix2 < BP_MINVAL) mix = 0.5;
   else mix = mix1 < BP_MINVAL ? 0.0 : 1.0;
+  if (pr1 != pr2) mix = pr1 > pr2 ? 1.0 : 0.0;
   for (int k = 0; k < 2; k++)
     DF(contact_solref)[2 * id + k] =
         mix * m.geom_solref[2 * g1 + k] + (1 - mix) * m.geom_solref[2 * g2 + k];

@@ -31,6 +31,8 @@ extern "C" int bp_task_nobs_impl(const BpModel* m, int task) {
     case TASK_FISH_SWIM: return (m->nq - 7) + 1 + 3 + m->nv;
     case TASK_POINT_MASS: return m->nq + m->nv;
     case TASK_QUADRUPED: return 2 * m->nhinge + m->na + 3 + 1 + 6 + 3 * m->nsens_ft;
+    case TASK_QUADRUPED_FETCH:
+      return 2 * m->nhinge + m->na + 3 + 1 + 6 + 3 * m->nsens_ft + 9 + 3;
     case TASK_QUADRUPED_ESCAPE:
       return 2 * m->nhinge + m->na + 3 + 1 + 6 + 3 * m->nsens_ft + 3 + m->nsens_rf;
   }

@@ -19,7 +19,7 @@ enum { TASK_NONE = 0, TASK_CARTPOLE = 1, TASK_ACROBOT = 2, TASK_PENDULUM = 3,
        TASK_LQR = 12, TASK_POINT_MASS = 13, TASK_FINGER_TURN = 14,
        TASK_SWIMMER = 15, TASK_FISH_UPRIGHT = 16,
        TASK_FISH_SWIM = 17, TASK_BALL_IN_CUP = 18,
-       TASK_MANIPULATOR = 19 };
+       TASK_MANIPULATOR = 19, TASK_QUADRUPED_FETCH = 20 };
 enum { SIG_GAUSSIAN = 0, SIG_LINEAR = 1, SIG_QUADRATIC = 2, SIG_LONG_TAIL = 3 };
 
 // read-only strided window of one environment's image (see bp_math.cuh for layouts)
@@ -352,14 +352,18 @@ static __device__ __noinline__ void bp_task_eval(const BpParams& P, const BpTask
       r = 1 - (0.5 * sc + 0.5 * cc * T.fp[0]);
       break;
     }
-    case TASK_QUADRUPED: case TASK_QUADRUPED_ESCAPE: {
+    case TASK_QUADRUPED: case TASK_QUADRUPED_ESCAPE: case TASK_QUADRUPED_FETCH: {
       // suite/quadruped.py:163-216,280-288 (observations), 291-306,343-357 (Move reward),
       // 399-418 (Escape).  ip: torso body, velocimeter adr, accelerometer adr, gyro adr,
       // first force/torque adr, workspace site, first rangefinder adr;
       // fp: desired speed, cos(deviation angle), terrain half size
+      // Fetch (quadruped.py:218-245,445-479) adds ip[7] ball body, [8] target site, [9] ball
+      // dof address, [10] root dof address; fp[3] workspace + ball radius, [4] arena
+      // radius, [5] target radius
       const int torso = T.ip[0];
       const ImgView R = xmat.at(9 * torso), vel = sens.at(T.ip[1]);
       const bool escape = T.kind == TASK_QUADRUPED_ESCAPE;
+      const bool fetch = T.kind == TASK_QUADRUPED_FETCH;
       if (o) {
         const ImgView act = d.at(L.act);
         for (int j = 0; j < m.njnt; j++) if (m.jnt_type[j] == JNT_HINGE) o[k++] = qpos[m.jnt_qposadr[j]];
@@ -379,6 +383,19 @@ static __device__ __noinline__ void bp_task_eval(const BpParams& P, const BpTask
             o[k++] = rf == -1.0 ? 1.0 : tanh(rf);
           }
         }
+        if (fetch) {
+          const ImgView tg = d.at(L.site_xpos + 3 * T.ip[8]);
+          double rows[4][3];
+          for (int i = 0; i < 3; i++) {
+            rows[0][i] = xpos[3 * T.ip[7] + i] - xpos[3 * torso + i];
+            rows[1][i] = qvel[T.ip[9] + i] - qvel[T.ip[10] + i];
+            rows[2][i] = qvel[T.ip[9] + 3 + i];
+            rows[3][i] = tg[i] - xpos[3 * torso + i];
+          }
+          for (int q = 0; q < 4; q++)
+            for (int cidx = 0; cidx < 3; cidx++)
+              o[k++] = rows[q][0] * R[cidx] + rows[q][1] * R[3 + cidx] + rows[q][2] * R[6 + cidx];
+        }
       }
       const double dev = T.fp[1];
       double upright = tolerance(R[8], dev, INF, 1 + dev, SIG_LINEAR, 0);
@@ -386,6 +403,14 @@ static __device__ __noinline__ void bp_task_eval(const BpParams& P, const BpTask
         const ImgView ws = d.at(L.site_xpos + 3 * T.ip[5]);
         double dist = sqrt(ws[0] * ws[0] + ws[1] * ws[1] + ws[2] * ws[2]);
         r = upright * tolerance(dist, T.fp[2], INF, T.fp[2], SIG_LINEAR, 0);
+      } else if (fetch) {
+        const ImgView ws = d.at(L.site_xpos + 3 * T.ip[5]), tg = d.at(L.site_xpos + 3 * T.ip[8]);
+        const double bx = xpos[3 * T.ip[7]], by = xpos[3 * T.ip[7] + 1];
+        double reach = tolerance(sqrt((ws[0] - bx) * (ws[0] - bx) + (ws[1] - by) * (ws[1] - by)),
+                                 0, T.fp[3], T.fp[4], SIG_LINEAR, 0);
+        double fetched = tolerance(sqrt((tg[0] - bx) * (tg[0] - bx) + (tg[1] - by) * (tg[1] - by)),
+                                   0, T.fp[5], T.fp[4], SIG_LINEAR, 0);
+        r = upright * (reach * (0.5 + 0.5 * fetched));
       } else {
         r = upright * tolerance(vel[0], T.fp[0], INF, T.fp[0], SIG_LINEAR, .5);
       }

@@ -52,7 +52,7 @@ enum { BP_MODE_STEP = 0, BP_MODE_FORWARD = 1, BP_MODE_STEP1 = 2,
   X(body_parentid) X(body_rootid) X(body_weldid) X(body_jntnum) X(body_jntadr) \
   X(body_dofnum) X(body_dofadr) X(jnt_type) X(jnt_qposadr) X(jnt_dofadr) \
   X(jnt_bodyid) X(jnt_limited) X(dof_bodyid) X(dof_jntid) X(dof_parentid) \
-  X(dof_Madr) X(geom_type) X(geom_condim) X(geom_bodyid) X(site_bodyid) \
+  X(dof_Madr) X(geom_type) X(geom_condim) X(geom_priority) X(geom_bodyid) X(site_bodyid) \
   X(site_type) X(pair_geom1) X(pair_geom2) X(pair_parentchild) \
   X(actuator_trntype) X(actuator_dyntype) X(actuator_gaintype) \
   X(actuator_biastype) X(actuator_trnid) X(actuator_ctrllimited) \

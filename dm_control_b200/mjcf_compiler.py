@@ -299,6 +299,7 @@ def _compile_geom(a, ctx):
   g["contype"] = int(a.get("contype", 1))
   g["conaffinity"] = int(a.get("conaffinity", 1))
   g["condim"] = int(a.get("condim", 3))
+  g["priority"] = int(a.get("priority", 0))
   fr = _floats(a.get("friction", "1 0.005 0.0001"))
   g["friction"] = np.array((fr + [0.005, 0.0001][len(fr) - 1:])[:3]
                            if len(fr) < 3 else fr[:3])
@@ -570,7 +571,7 @@ def _emit_tree(m, bodies, ctx):
                        "solimp")}
   D = {k: [] for k in ("bodyid", "jntid", "parentid", "armature", "damping",
                        "frictionloss", "solref", "solimp")}
-  G = {k: [] for k in ("type", "contype", "conaffinity", "condim", "bodyid",
+  G = {k: [] for k in ("type", "contype", "conaffinity", "condim", "priority", "bodyid",
                        "dataid", "group", "solmix", "solref", "solimp", "size",
                        "rbound", "pos", "quat", "friction", "margin", "gap")}
   S = {k: [] for k in ("type", "bodyid", "size", "pos", "quat")}
@@ -635,7 +636,7 @@ def _emit_tree(m, bodies, ctx):
       last_dof_of_body[bid] = nv - 1
     for g in b["geoms"]:
       names["geom"].append(g["name"])
-      for k in ("type", "contype", "conaffinity", "condim", "group", "solmix",
+      for k in ("type", "contype", "conaffinity", "condim", "priority", "group", "solmix",
                 "solref", "solimp", "size", "rbound", "pos", "quat", "friction",
                 "margin", "gap"):
         G[k].append(g[k])
@@ -684,7 +685,7 @@ def _emit_tree(m, bodies, ctx):
       n += 1
       k = D["parentid"][k]
   m.set("dof_Madr", arr(madr, (nv,), np.int32)); m.set("nM", n)
-  for k in ("type", "contype", "conaffinity", "condim", "bodyid", "dataid",
+  for k in ("type", "contype", "conaffinity", "condim", "priority", "bodyid", "dataid",
             "group"):
     m.set("geom_" + k, arr(G[k], (ng,), np.int32))
   for k, w in (("solref", 2), ("solimp", 5), ("size", 3), ("pos", 3),

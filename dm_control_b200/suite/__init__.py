@@ -300,14 +300,23 @@ def _initialize_quadruped(self, physics, task_name):
   if task_name == "escape":
     terrain = np.stack([_escape_terrain(m, rng) for rng in self._rngs])
     physics.set_hfield(terrain)
-  orientation = np.stack([rng.randn(4) for rng in self._rngs])
-  orientation /= np.linalg.norm(orientation, axis=1, keepdims=True)
+  xy = np.zeros((n, 2))
+  if task_name == "fetch":              # quadruped.py:431-436: random azimuth and position
+    spawn_radius = 0.9 * m.geom_size[m.name2id("floor", "geom"), 0]
+    orientation = np.zeros((n, 4))
+    for e, rng in enumerate(self._rngs):
+      azimuth = rng.uniform(0, 2 * np.pi)
+      orientation[e] = (np.cos(azimuth / 2), 0, 0, np.sin(azimuth / 2))
+      xy[e] = rng.uniform(-spawn_radius, spawn_radius, size=(2,))
+  else:
+    orientation = np.stack([rng.randn(4) for rng in self._rngs])
+    orientation /= np.linalg.norm(orientation, axis=1, keepdims=True)
   root = m.jnt_qposadr[m.name2id("root", "joint")]
   qpos = np.tile(np.asarray(m.qpos0, dtype=np.float64), (n, 1))
   z = np.zeros(n)                       # start embedded in the floor
   todo = np.ones(n, dtype=bool)
   for _ in range(10001):
-    qpos[:, root:root + 3] = np.stack([np.zeros(n), np.zeros(n), z], axis=1)
+    qpos[:, root:root + 3] = np.stack([xy[:, 0], xy[:, 1], z], axis=1)
     qpos[:, root + 3:root + 7] = orientation
     physics.data.qpos = qpos
     physics.data.qvel = np.zeros((n, m.nv))
@@ -317,6 +326,16 @@ def _initialize_quadruped(self, physics, task_name):
       pass                              # a full contact buffer: keep raising (quadruped.py:266-270)
     todo &= physics.data.ncon > 0
     if not todo.any():
+      if task_name == "fetch":          # quadruped.py:438-443: initial ball state
+        ball = m.jnt_qposadr[m.name2id("ball_root", "joint")]
+        ballv = m.jnt_dofadr[m.name2id("ball_root", "joint")]
+        qvel = np.zeros((n, m.nv))
+        for e, rng in enumerate(self._rngs):
+          qpos[e, ball:ball + 2] = rng.uniform(-spawn_radius, spawn_radius, size=(2,))
+          qpos[e, ball + 2] = 2
+          qvel[e, ballv:ballv + 2] = 5 * rng.randn(2)
+        physics.data.qpos = qpos
+        physics.data.qvel = qvel
       return
     z[todo] += 0.01
   raise RuntimeError("Failed to find a non-contacting configuration.")

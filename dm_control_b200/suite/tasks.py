@@ -21,6 +21,7 @@ SWIMMER = 15
 FISH_UPRIGHT, FISH_SWIM = 16, 17
 BALL_IN_CUP = 18
 MANIPULATOR = 19
+QUADRUPED_FETCH = 20
 
 TaskDef = collections.namedtuple(
     "TaskDef", "domain task model kind time_limit control_timestep params obs")
@@ -93,7 +94,7 @@ def _finger_turn(target_radius):
   return f
 
 
-def _quadruped(speed=0.0, deviation_angle=0.0, escape=False):
+def _quadruped(speed=0.0, deviation_angle=0.0, escape=False, fetch=False):
   """quadruped.py:291-306 _upright_reward, 343-357 Move.get_reward, 406-418 Escape."""
   def f(m):
     from dm_control_b200 import model as M
@@ -110,11 +111,19 @@ def _quadruped(speed=0.0, deviation_angle=0.0, escape=False):
       assert np.array_equal(adr[rf], adr[rf[0]] + np.arange(len(rf)))
       ip[6] = int(adr[rf[0]])
       fp[2] = float(m.hfield_size[0, 0])          # quadruped.py:408 terrain_size
+    if fetch:                                     # quadruped.py:455-479
+      ball = m.name2id("ball", "geom")
+      ip += [m.name2id("ball", "body"), m.name2id("target", "site"),
+             int(m.jnt_dofadr[m.name2id("ball_root", "joint")]),
+             int(m.jnt_dofadr[m.name2id("root", "joint")])]
+      fp += [float(m.site_size[m.name2id("workspace", "site"), 0] + m.geom_size[ball, 0]),
+             float(m.geom_size[m.name2id("floor", "geom"), 0] * np.sqrt(2)),
+             float(m.site_size[m.name2id("target", "site"), 0])]
     return ip, fp
   return f
 
 
-def _obs_quadruped(escape):
+def _obs_quadruped(escape, fetch=False):
   def f(m):
     from dm_control_b200 import model as M
     nh = int(np.sum(np.asarray(m.jnt_type) == M.JNT_HINGE))
@@ -124,6 +133,8 @@ def _obs_quadruped(escape):
            ("imu", 6), ("force_torque", 3 * nft)]
     if escape:
       obs += [("origin", 3), ("rangefinder", int(np.sum(types == M.SENS["rangefinder"])))]
+    if fetch:
+      obs += [("ball_state", 9), ("target_position", 3)]
     return obs
   return f
 
@@ -266,6 +277,10 @@ _TASKS = [
             _obs_quadruped(False)),
     TaskDef("quadruped", "escape", "quadruped_escape", QUADRUPED_ESCAPE, 20, .02,
             _quadruped(0.0, 20.0, True), _obs_quadruped(True)),
+    # quadruped.py:133-142 fetch: walls, a ball with a free joint (condim 6, priority 1,
+    # direct solref) and a target site
+    TaskDef("quadruped", "fetch", "quadruped_fetch", QUADRUPED_FETCH, 20, .02,
+            _quadruped(fetch=True), _obs_quadruped(False, True)),
     # reacher.py:29-57: 20 s, target size .05 (easy) / .015 (hard); the target geom moves
     # per episode and per env (bp_env_model_write)
     TaskDef("reacher", "easy", "reacher", REACHER, 20, None, _reacher(.05),

@@ -61,7 +61,7 @@ typedef struct {
   X(body_parentid) X(body_rootid) X(body_weldid) X(body_jntnum) X(body_jntadr) \
   X(body_dofnum) X(body_dofadr) X(jnt_type) X(jnt_qposadr) X(jnt_dofadr) \
   X(jnt_bodyid) X(jnt_limited) X(dof_bodyid) X(dof_jntid) X(dof_parentid) \
-  X(dof_Madr) X(geom_type) X(geom_condim) X(geom_bodyid) X(site_bodyid) \
+  X(dof_Madr) X(geom_type) X(geom_condim) X(geom_priority) X(geom_bodyid) X(site_bodyid) \
   X(site_type) X(pair_geom1) X(pair_geom2) X(pair_parentchild) \
   X(actuator_trntype) X(actuator_dyntype) X(actuator_gaintype) \
   X(actuator_biastype) X(actuator_trnid) X(actuator_ctrllimited) \
@@ -1577,11 +1577,14 @@ static int add_contact(const OModel* m, OData* d, int g1, int g2, double margin,
   make_frame(c->frame);
   c->includemargin = margin - gap;
   c->geom1 = g1; c->geom2 = g2;
+  /* [MJ-doc: contact parameters] equal priority: max condim, max friction, solmix-weighted
+   * solref / solimp; otherwise everything from the geom with the higher priority */
   int dim1 = m->geom_condim[g1], dim2 = m->geom_condim[g2];
-  c->dim = dim1 > dim2 ? dim1 : dim2;
+  int pr1 = m->geom_priority[g1], pr2 = m->geom_priority[g2];
+  c->dim = pr1 > pr2 ? dim1 : pr2 > pr1 ? dim2 : (dim1 > dim2 ? dim1 : dim2);
   const double *f1 = m->geom_friction + 3 * g1, *f2 = m->geom_friction + 3 * g2;
   double fr[3];
-  for (int k = 0; k < 3; k++) fr[k] = fmax(f1[k], f2[k]);
+  for (int k = 0; k < 3; k++) fr[k] = pr1 > pr2 ? f1[k] : pr2 > pr1 ? f2[k] : fmax(f1[k], f2[k]);
   c->friction[0] = c->friction[1] = fr[0];
   c->friction[2] = fr[1];
   c->friction[3] = c->friction[4] = fr[2];
@@ -1589,6 +1592,7 @@ static int add_contact(const OModel* m, OData* d, int g1, int g2, double margin,
   if (mix1 >= MINVAL && mix2 >= MINVAL) mix = mix1 / (mix1 + mix2);
   else if (mix1 < MINVAL && mix2 < MINVAL) mix = 0.5;
   else mix = mix1 < MINVAL ? 0.0 : 1.0;
+  if (pr1 != pr2) mix = pr1 > pr2 ? 1.0 : 0.0;
   for (int k = 0; k < 2; k++)
     c->solref[k] = mix * m->geom_solref[2 * g1 + k] + (1 - mix) * m->geom_solref[2 * g2 + k];
   for (int k = 0; k < 5; k++)

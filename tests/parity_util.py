@@ -150,7 +150,7 @@ def compare_env(cmp, m, oracle, gpu, e, nvp, skip=()):
 
 def run_parity(domain, nenv=32, nsteps=3, seed=0, njmax=0, nconmax=0, check_steps=None,
                vel_scale=1.0, spread=1.0, mutate=None, lanes=0, env_model=None,
-               iter_slack=False):
+               iter_slack=False, state_hook=None):
   """forward() then `nsteps` Physics.step() on both sides; returns (Comparison per
   phase, stats).  The GPU side goes through the C ABI (dm_control_b200.binding).
 
@@ -165,6 +165,8 @@ def run_parity(domain, nenv=32, nsteps=3, seed=0, njmax=0, nconmax=0, check_step
   if mutate:
     mutate(m)
   qpos, qvel, ctrl = random_states(m, nenv, seed, vel_scale, spread)
+  if state_hook:
+    state_hook(m, qpos, qvel, ctrl)
   hfield = None
   if int(m.nhfielddata) > 0:       # one terrain per env (quadruped.py:371-382)
     hfield = np.stack([escape_terrain(np.random.RandomState(seed + 1000 + e))

@@ -21,7 +21,7 @@ SERVED = [("cartpole", "swingup"), ("cartpole", "swingup_sparse"), ("cartpole", 
           ("pendulum", "swingup"), ("cheetah", "run"), ("walker", "stand"), ("walker", "walk"),
           ("walker", "run"), ("hopper", "stand"), ("hopper", "hop"), ("finger", "spin"),
           ("humanoid", "stand"), ("humanoid", "walk"), ("humanoid", "run"),
-          ("quadruped", "walk"), ("quadruped", "run"), ("quadruped", "escape"),
+          ("quadruped", "walk"), ("quadruped", "run"), ("quadruped", "escape"), ("quadruped", "fetch"),
           ("lqr", "lqr_2_1"), ("lqr", "lqr_6_2"), ("reacher", "easy"), ("reacher", "hard"),
           ("point_mass", "easy"), ("finger", "turn_easy"), ("finger", "turn_hard"),
           ("humanoid_CMU", "stand"), ("humanoid_CMU", "run"),

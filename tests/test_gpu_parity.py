@@ -23,7 +23,8 @@ SIZES = {"humanoid": HUMANOID_SIZES, "quadruped": dict(njmax=120, nconmax=40),
          "humanoid_CMU": dict(njmax=200, nconmax=48),
          "swimmer6": dict(njmax=32, nconmax=1), "swimmer15": dict(njmax=32, nconmax=1),
          "fish": dict(njmax=32, nconmax=1),
-         "manipulator_ball": dict(njmax=96, nconmax=24)}
+         "manipulator_ball": dict(njmax=96, nconmax=24),
+         "quadruped_fetch": dict(njmax=160, nconmax=40)}
 
 
 def _assert_parity(res):
@@ -59,6 +60,30 @@ def test_every_field_matches_oracle(domain, lanes):
     assert max(stats["ncon"]) > 0.05
   if domain in ("cheetah", "walker", "hopper", "humanoid", "quadruped", "quadruped_escape"):
     assert max(stats["ncon"]) > 0.5 and max(stats["iter"]) > 0.5     # contacts exercised
+
+
+@pytest.mark.parametrize("lanes", [32, 16, 4, 1])
+def test_condim6_ball_contacts(lanes):
+  """quadruped fetch's ball (condim 6, priority 1, direct solref: quadruped.xml:199-203)
+  rolling and spinning on the floor and against the quadruped: ten pyramid rows per contact
+  with torsional and rolling friction.  (The fetch model is not in the generic random-state
+  list above: two free bodies thrown at random give 16 contacts per env with limbs 7 cm
+  inside the torso, where the narrowphase normal is discontinuous and rounding noise is
+  amplified to O(1) within 10 steps on some seeds -- tools/debug_env_divergence.py.)"""
+  def hook(m, qpos, qvel, ctrl):
+    rng = np.random.RandomState(11)
+    n = qpos.shape[0]
+    ball = m.jnt_qposadr[m.name2id("ball_root", "joint")]
+    bv = m.jnt_dofadr[m.name2id("ball_root", "joint")]
+    root = m.jnt_qposadr[m.name2id("root", "joint")]
+    qpos[:, ball + 2] = 0.15 + rng.uniform(-.01, .002, n)       # resting on / in the floor
+    qpos[: n // 2, ball:ball + 2] = qpos[: n // 2, root:root + 2] + rng.uniform(-.4, .4, (n // 2, 2))
+    qpos[: n // 2, root + 2] = rng.uniform(.2, .6, n // 2)      # half of them under the body
+    qvel[:, bv:bv + 6] = rng.randn(n, 6) * [2, 2, .2, 10, 10, 10]
+  res, stats = PU.run_parity("quadruped_fetch", nenv=32, nsteps=4, seed=9, lanes=lanes,
+                             state_hook=hook, **SIZES["quadruped_fetch"])
+  _assert_parity(res)
+  assert max(stats["nefc"]) > 10
 
 
 @pytest.mark.parametrize("lanes", [32, 4])

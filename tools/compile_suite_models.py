@@ -157,6 +157,11 @@ def quadruped():
   # quadruped.py:121-130 escape: floor 40, terrain height field, rangefinders
   m = C.compile_xml(quadruped_xml(floor_size=40, terrain=True, rangefinders=True), _Dir())
   m.save(os.path.join(OUT, "quadruped_escape.npz"))
+  # quadruped.py:133-142 fetch: walls, ball and target kept, the XML's own floor size
+  mf = C.compile_xml(quadruped_xml(walls_and_ball=True), _Dir())
+  mf.save(os.path.join(OUT, "quadruped_fetch.npz"))
+  print("quadruped_fetch ngeom", mf.ngeom, "npair", mf.npair, "nq", mf.nq, "njmax", mf.njmax,
+        "nconmax", mf.nconmax)
   print("quadruped_escape ngeom", m.ngeom, "npair", m.npair, "nhfpair", m.nhfpair,
         "nhfielddata", m.nhfielddata, "nsensordata", m.nsensordata)
 
