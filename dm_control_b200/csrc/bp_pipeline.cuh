@@ -19,22 +19,9 @@
 #include "bp_solver.cuh"
 #include "bp_task.cuh"
 
-// The composite functions below run for EVERY thread of a block, also for groups
-// without an environment (c.act false), which only take part in the BP_LOCK barriers.
+// factor M and, for the implicit-damping Euler step, M + dt diag(damping) together
 template <class C>
-__device__ __forceinline__ void bp_fwd_position(const C& c) {
-  if (c.act) {
-    bp_kinematics(c);
-  }
-  BP_LOCK(9);
-  if (c.act) {
-    bp_com_pos(c);
-    bp_transmission(c);
-    bp_crb(c);
-  }
-  BP_LOCK(10);
-  if (c.act) {
-    // factor M and, for the implicit-damping Euler step, M + dt diag(damping) together
+__device__ __forceinline__ void bp_factor_stage(const C& c) {
     const BpModel& m = c.P.m;
     auto qLD = DF(qLD), qM = DF(qM), MM = DF(s_MM);
     // (not in the shared-memory shape: its scratch does not survive the launch)
@@ -49,7 +36,23 @@ __device__ __forceinline__ void bp_fwd_position(const C& c) {
     }
     bp_factor_sparse(c, qLD, DF(qLDiagInv), implicit ? MM : c.null(),
                      implicit ? DF(s_MMdinv) : c.null());
+}
+
+// The composite functions below run for EVERY thread of a block, also for groups
+// without an environment (c.act false), which only take part in the BP_LOCK barriers.
+template <class C>
+__device__ __forceinline__ void bp_fwd_position(const C& c) {
+  if (c.act) {
+    bp_kinematics(c);
   }
+  BP_LOCK(9);
+  if (c.act) {
+    bp_com_pos(c);
+    bp_transmission(c);
+    bp_crb(c);
+  }
+  BP_LOCK(10);
+  if (c.act) bp_factor_stage(c);
   BP_LOCK(0);
   RUN(bp_collision(c));
   BP_LOCK(1);
@@ -390,6 +393,114 @@ bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
   }
 }
 
+
+// ---- split pipeline: one kernel per stage ---------------------------------------------
+// The same stage functions, cut at the BP_LOCK points of Physics.step() for Euler models
+// (mj_step2 then mj_step1, engine.py:149-166) into separate launches on the batch's stream.
+// Each launch runs one stage's code only, so the instruction cache holds it without the
+// block-wide re-alignment barriers of the fused kernel, and the grid no longer has to be
+// one block per SM.  The image lives in global memory in these shapes anyway.  The solver
+// segment keeps its block-uniform Newton loop.
+enum { SEG_ACT = 0, SEG_SOLVE, SEG_INTEGRATE, SEG_COM, SEG_FACTOR, SEG_COLLIDE, SEG_CONSTRAINT,
+       SEG_VEL1, SEG_VEL2, SEG_COUNT };
+
+template <int G, int SEG>
+__global__ void BP_BOUNDS
+bp_seg_kernel(const __grid_constant__ BpParams P, int first, int last) {
+  const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  long long env = tid / G;
+  const bool act = env < P.nenv && (!P.mask || P.mask[env]);
+  const bool lock = SEG == SEG_SOLVE;
+  if (!act) {
+    if (!lock) return;
+    env = 0;
+  }
+  const int wl = threadIdx.x & 31;
+  double* base = P.image + env * P.stride;
+  int* ib = (int*)(base + P.L.ints);
+  unsigned mask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (wl & ~(G - 1)));
+  const float* hf = P.hfield ? P.hfield + env * (long long)P.m.nhfielddata : nullptr;
+  const double* gp = P.env_geom_pos ? P.env_geom_pos + env * 3LL * P.m.ngeom : P.m.geom_pos;
+  const double* sp = P.env_site_pos ? P.env_site_pos + env * 3LL * P.m.nsite : P.m.site_pos;
+  const double* bp = P.env_body_pos ? P.env_body_pos + env * 3LL * P.m.nbody : P.m.body_pos;
+  const double* bq = P.env_body_quat ? P.env_body_quat + env * 4LL * P.m.nbody : P.m.body_quat;
+  using C = Ctx<G, 1>;
+  C c{P, base, ib, wl & (G - 1), mask, act, lock, nullptr, hf, gp, sp, bp, bq};
+  const bool skip = !last;          // sensors / energy on the last sub-step only
+  if (SEG == SEG_ACT) {
+    if (first) bp_load_ctrl(c, env);
+    bp_fwd_actuation(c);
+    bp_fwd_acceleration(c);
+  } else if (SEG == SEG_SOLVE) {
+    bp_fwd_constraint(c);
+  } else if (SEG == SEG_INTEGRATE) {
+    if (!skip) bp_sensors(c, STAGE_ACC);
+    bp_check_acc(c);
+    bp_euler(c);
+    bp_check_state(c);
+    bp_kinematics(c);
+  } else if (SEG == SEG_COM) {
+    bp_com_pos(c);
+    bp_transmission(c);
+    bp_crb(c);
+  } else if (SEG == SEG_FACTOR) {
+    bp_factor_stage(c);
+  } else if (SEG == SEG_COLLIDE) {
+    bp_collision(c);
+  } else if (SEG == SEG_CONSTRAINT) {
+    bp_make_constraint(c);
+  } else if (SEG == SEG_VEL1) {
+    if (!skip) bp_sensors(c, STAGE_POS);
+    bp_energy_pos(c);
+    bp_actuator_velocity(c);
+    bp_com_vel(c);
+    bp_passive(c);
+  } else if (SEG == SEG_VEL2) {
+    bp_reference_constraint(c);
+    bp_rne(c, false, DF(s_cacc), DF(s_cfrc), c.null(), DF(qfrc_bias), 0);
+    if (!skip) bp_sensors(c, STAGE_VEL);
+    bp_energy_vel(c);
+    if (last && P.rew_out) {        // epilogue: the task's observation and reward
+      if (G > 1) __syncwarp(mask);
+      __threadfence_block();
+      if (c.lane == 0) bp_task_eval(P, P.task, env, P.task_nobs, P.obs_out, P.rew_out);
+    }
+  }
+}
+
+template <int G, int SEG>
+static inline void bp_launch_seg(const BpParams& Q, int threads, int first, int last,
+                                 cudaStream_t stream) {
+  const long long total = Q.nenv * G;
+  const unsigned blocks = (unsigned)((total + threads - 1) / threads);
+  bp_seg_kernel<G, SEG><<<blocks, threads, 0, stream>>>(Q, first, last);
+}
+
+// nsub x 9 launches.  BPHYS_SEG_THREADS: block size of the non-solver segments.
+template <int G>
+static int bp_launch_split(const BpParams* P, cudaStream_t stream, int solver_threads) {
+  BpParams Q = *P;
+  Q.hot_doubles = 0;
+  int t = 256;
+  if (const char* e = getenv("BPHYS_SEG_THREADS")) {
+    int v = atoi(e);
+    if (v >= 32 && v <= BP_TPB(G) && v % 32 == 0) t = v;
+  }
+  for (int s = 0; s < Q.nsub; s++) {
+    const int first = s == 0, last = s + 1 == Q.nsub;
+    bp_launch_seg<G, SEG_ACT>(Q, t, first, last, stream);
+    bp_launch_seg<G, SEG_SOLVE>(Q, solver_threads, first, last, stream);
+    bp_launch_seg<G, SEG_INTEGRATE>(Q, t, first, last, stream);
+    bp_launch_seg<G, SEG_COM>(Q, t, first, last, stream);
+    bp_launch_seg<G, SEG_FACTOR>(Q, t, first, last, stream);
+    bp_launch_seg<G, SEG_COLLIDE>(Q, t, first, last, stream);
+    bp_launch_seg<G, SEG_CONSTRAINT>(Q, t, first, last, stream);
+    bp_launch_seg<G, SEG_VEL1>(Q, t, first, last, stream);
+    bp_launch_seg<G, SEG_VEL2>(Q, t, first, last, stream);
+  }
+  return (int)cudaGetLastError();
+}
+
 // Block size of a launch: as many warps per block as possible (they share instruction
 // cache lines between BP_LOCK barriers: +50..160 % measured, profiles/r1d_*) while the
 // grid still covers the 148 SMs.
@@ -413,6 +524,10 @@ static int bp_launch_gmem(const BpParams* P, cudaStream_t stream) {
   const long long total = P->nenv * G;
   const int threads = bp_block_threads(total, BP_TPB(G));
   const unsigned blocks = (unsigned)((total + threads - 1) / threads);
+  if constexpr (S == 1 && G >= 4) {
+    if (P->mode == BP_MODE_STEP && P->m.opt_integrator == 0 && getenv("BPHYS_SPLIT"))
+      return bp_launch_split<G>(P, stream, threads);
+  }
   BpParams Q = *P;
   Q.hot_doubles = 0;
   size_t bytes = 0;
