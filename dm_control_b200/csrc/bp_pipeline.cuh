@@ -476,27 +476,64 @@ static inline void bp_launch_seg(const BpParams& Q, int threads, int first, int 
   bp_seg_kernel<G, SEG><<<blocks, threads, 0, stream>>>(Q, first, last);
 }
 
-// nsub x 9 launches.  BPHYS_SEG_THREADS: block size of the non-solver segments.
+// one segment at this TU's lane width (called across TUs: a stage may run at its own G)
 template <int G>
-static int bp_launch_split(const BpParams* P, cudaStream_t stream, int solver_threads) {
+static int bp_launch_seg_any(const BpParams* P, int seg, int threads, int first, int last,
+                             cudaStream_t stream) {
   BpParams Q = *P;
   Q.hot_doubles = 0;
+  switch (seg) {
+    case SEG_ACT: bp_launch_seg<G, SEG_ACT>(Q, threads, first, last, stream); break;
+    case SEG_SOLVE: bp_launch_seg<G, SEG_SOLVE>(Q, threads, first, last, stream); break;
+    case SEG_INTEGRATE: bp_launch_seg<G, SEG_INTEGRATE>(Q, threads, first, last, stream); break;
+    case SEG_COM: bp_launch_seg<G, SEG_COM>(Q, threads, first, last, stream); break;
+    case SEG_FACTOR: bp_launch_seg<G, SEG_FACTOR>(Q, threads, first, last, stream); break;
+    case SEG_COLLIDE: bp_launch_seg<G, SEG_COLLIDE>(Q, threads, first, last, stream); break;
+    case SEG_CONSTRAINT: bp_launch_seg<G, SEG_CONSTRAINT>(Q, threads, first, last, stream); break;
+    case SEG_VEL1: bp_launch_seg<G, SEG_VEL1>(Q, threads, first, last, stream); break;
+    case SEG_VEL2: bp_launch_seg<G, SEG_VEL2>(Q, threads, first, last, stream); break;
+  }
+  return 0;
+}
+
+extern "C" int bp_launch_seg_g4(const BpParams*, int, int, int, int, cudaStream_t);
+extern "C" int bp_launch_seg_g8(const BpParams*, int, int, int, int, cudaStream_t);
+extern "C" int bp_launch_seg_g16(const BpParams*, int, int, int, int, cudaStream_t);
+
+static inline int bp_block_threads(long long threads_total, int tpb_max);
+
+// nsub x 9 launches.  BPHYS_SEG_THREADS: block size of the non-solver segments;
+// BPHYS_SEG_G: lane width per segment, e.g. "8,8,4,4,8,16,8,8,8" (4, 8 or 16; the image
+// layout does not depend on it), default the batch's.
+template <int G>
+static int bp_launch_split(const BpParams* P, cudaStream_t stream, int solver_threads) {
   int t = 256;
   if (const char* e = getenv("BPHYS_SEG_THREADS")) {
     int v = atoi(e);
-    if (v >= 32 && v <= BP_TPB(G) && v % 32 == 0) t = v;
+    if (v >= 32 && v <= 512 && v % 32 == 0) t = v;
   }
-  for (int s = 0; s < Q.nsub; s++) {
-    const int first = s == 0, last = s + 1 == Q.nsub;
-    bp_launch_seg<G, SEG_ACT>(Q, t, first, last, stream);
-    bp_launch_seg<G, SEG_SOLVE>(Q, solver_threads, first, last, stream);
-    bp_launch_seg<G, SEG_INTEGRATE>(Q, t, first, last, stream);
-    bp_launch_seg<G, SEG_COM>(Q, t, first, last, stream);
-    bp_launch_seg<G, SEG_FACTOR>(Q, t, first, last, stream);
-    bp_launch_seg<G, SEG_COLLIDE>(Q, t, first, last, stream);
-    bp_launch_seg<G, SEG_CONSTRAINT>(Q, t, first, last, stream);
-    bp_launch_seg<G, SEG_VEL1>(Q, t, first, last, stream);
-    bp_launch_seg<G, SEG_VEL2>(Q, t, first, last, stream);
+  int g[SEG_COUNT];
+  for (int k = 0; k < SEG_COUNT; k++) g[k] = G;
+  if (const char* e = getenv("BPHYS_SEG_G")) {
+    int k = 0;
+    for (const char* q = e; *q && k < SEG_COUNT; k++) {
+      int v = atoi(q);
+      if (v == 4 || v == 8 || v == 16) g[k] = v;
+      while (*q && *q != ',') q++;
+      if (*q == ',') q++;
+    }
+  }
+  for (int s = 0; s < P->nsub; s++) {
+    const int first = s == 0, last = s + 1 == P->nsub;
+    for (int k = 0; k < SEG_COUNT; k++) {
+      int th = t;
+      if (k == SEG_SOLVE)
+        th = g[k] == G ? solver_threads
+                       : bp_block_threads(P->nenv * g[k], g[k] >= 8 ? 1024 : 512);
+      if (g[k] == 4) bp_launch_seg_g4(P, k, th, first, last, stream);
+      else if (g[k] == 8) bp_launch_seg_g8(P, k, th, first, last, stream);
+      else bp_launch_seg_g16(P, k, th, first, last, stream);
+    }
   }
   return (int)cudaGetLastError();
 }

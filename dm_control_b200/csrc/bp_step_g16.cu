@@ -5,6 +5,11 @@ extern "C" int bp_launch_step_g16(const BpParams* P, cudaStream_t stream) {
   return bp_launch_gmem<16, 1>(P, stream);
 }
 
+extern "C" int bp_launch_seg_g16(const BpParams* P, int seg, int threads, int first, int last,
+                                cudaStream_t stream) {
+  return bp_launch_seg_any<16>(P, seg, threads, first, last, stream);
+}
+
 #ifdef BP_TIMELINE
 extern "C" int bp_debug_timeline_g16(unsigned long long* out, int reset) {
   cudaDeviceSynchronize();

@@ -62,6 +62,54 @@ def test_every_field_matches_oracle(domain, lanes):
     assert max(stats["ncon"]) > 0.5 and max(stats["iter"]) > 0.5     # contacts exercised
 
 
+@pytest.mark.parametrize("domain,lanes,seg_g", [
+    ("cheetah", 8, None), ("humanoid", 16, "16,8,4,4,16,16,8,8,16"),
+    ("quadruped_escape", 16, "4,4,4,8,8,16,16,8,8"), ("finger", 4, None)])
+def test_split_pipeline_bit_identical(domain, lanes, seg_g, monkeypatch):
+  """BPHYS_SPLIT=1 (one launch per stage, csrc/bp_pipeline.cuh bp_launch_split), also with a
+  different lane width per stage.  At the batch's own lane width it is the same arithmetic
+  in the same order as the fused kernel: every field bit-identical after 5 x 3 sub-steps.
+  A stage at another lane width sums its lane reductions in another order: 1e-8 after two
+  steps, integers exact."""
+  from dm_control_b200 import binding
+  m = PU.load_model(domain)
+  kw = SIZES.get(domain, dict(njmax=64, nconmax=16))
+  nenv = 40
+  qpos, qvel, ctrl = PU.random_states(m, nenv, 21)
+  hfield = None
+  if int(m.nhfielddata) > 0:
+    hfield = np.stack([PU.escape_terrain(np.random.RandomState(50 + e)) for e in range(nenv)])
+    PU.terrain_states(m, qpos, hfield, 21)
+  model = binding.Model(m)
+  names = ["qpos", "qvel", "qacc", "qacc_warmstart", "sensordata", "efc_force", "xpos",
+           "cfrc_ext", "nefc", "ncon", "solver_iter", "warning"]
+  out = []
+  for split in (False, True):
+    if split:
+      monkeypatch.setenv("BPHYS_SPLIT", "1")
+      if seg_g:
+        monkeypatch.setenv("BPHYS_SEG_G", seg_g)
+    else:
+      monkeypatch.delenv("BPHYS_SPLIT", raising=False)
+    b = binding.Batch(model, nenv, kw["njmax"], kw["nconmax"], lanes)
+    b.write("qpos", qpos); b.write("qvel", qvel); b.write("ctrl", ctrl)
+    if hfield is not None:
+      b.write_hfield(hfield)
+    b.forward()
+    for _ in range(2 if seg_g else 5):
+      b.step(1 if seg_g else 3)
+    b.sync()
+    out.append({n: b.read(n) for n in names})
+    b.free()
+  model.free()
+  assert out[0]["nefc"].max() > 0
+  for n in names:
+    if seg_g and out[0][n].dtype.kind == "f":
+      assert PU.rel_err(out[1][n], out[0][n]) <= TOL, n
+    else:
+      np.testing.assert_array_equal(out[0][n], out[1][n], err_msg=n)
+
+
 @pytest.mark.parametrize("lanes", [32, 16, 4, 1])
 def test_condim6_ball_contacts(lanes):
   """quadruped fetch's ball (condim 6, priority 1, direct solref: quadruped.xml:199-203)
