@@ -17,6 +17,9 @@ extern "C" int bp_launch_step_g8(const BpParams* P, cudaStream_t stream);
 extern "C" int bp_launch_step_g4(const BpParams* P, cudaStream_t stream);
 extern "C" int bp_launch_step_g2(const BpParams* P, cudaStream_t stream);
 extern "C" int bp_launch_step_g1(const BpParams* P, cudaStream_t stream);
+extern "C" int bp_launch_step_g16_lean(const BpParams* P, cudaStream_t stream);
+extern "C" int bp_launch_step_g8_lean(const BpParams* P, cudaStream_t stream);
+extern "C" int bp_launch_step_g4_lean(const BpParams* P, cudaStream_t stream);
 extern "C" int bp_launch_field_copy(const BpParams* P, long long off, int count, int is_int,
                                     void* dense, long long env0, long long n, int to_image,
                                     cudaStream_t stream);
@@ -199,6 +202,14 @@ static int derive(bp_model* m) {
     if (st[s] == SENS_ACCELEROMETER || st[s] == SENS_FORCE || st[s] == SENS_TORQUE)
       M.need_rnepost_stage = ss[s];
   }
+  // LEAN shape: plane / sphere / capsule geoms of equal priority, no tendons, equalities,
+  // height fields, rangefinders or actuator dynamics (cone and fluid are checked per launch)
+  M.lean_static = M.ntendon == 0 && M.neq == 0 && M.nhfield == 0 && M.nsens_rf == 0 && M.na == 0;
+  auto& gt = I(m, "geom_type");
+  auto& gpr = I(m, "geom_priority");
+  for (int g = 0; g < M.ngeom; g++)
+    if ((gt[g] != GEOM_PLANE && gt[g] != GEOM_SPHERE && gt[g] != GEOM_CAPSULE) || gpr[g] != 0)
+      M.lean_static = 0;
   return BP_OK;
 }
 
@@ -634,6 +645,17 @@ static int launch(bp_batch* b, int mode, int nsub, int disable_actuation,
     if (P.task_nobs < 0) return fail(BP_EINVAL, "unknown task kind");
   }
   int e;
+  const BpModel& M = b->model->M;
+  // BPHYS_NO_LEAN=1 / BPHYS_SPLIT=1 keep the full instantiation
+  const bool lean = M.lean_static && M.opt_cone == 0 && M.opt_density == 0 &&
+                    M.opt_viscosity == 0 && !P.env_geom_pos && !P.env_site_pos &&
+                    !P.env_body_pos && !P.env_body_quat && !getenv("BPHYS_NO_LEAN") &&
+                    !getenv("BPHYS_SPLIT");
+  if (lean && (b->lanes == 4 || b->lanes == 8 || b->lanes == 16)) {
+    e = b->lanes == 4 ? bp_launch_step_g4_lean(&P, b->stream)
+        : b->lanes == 8 ? bp_launch_step_g8_lean(&P, b->stream)
+                        : bp_launch_step_g16_lean(&P, b->stream);
+  } else
   switch (b->lanes) {
     case 1: e = bp_launch_step_g1(&P, b->stream); break;
     case 2: e = bp_launch_step_g2(&P, b->stream); break;

@@ -303,13 +303,16 @@ static __device__ __noinline__ int bp_collide_ellipsoid(int t1, const double* p1
 // Narrowphase of ordered pair (type1 <= type2) on geom poses already copied to
 // registers (p = centre, z = local z axis, R2 = full frame of geom 2 for boxes).
 // Returns the number of raw contacts written to out[0..3].
+template <bool LEAN>
 static __device__ __noinline__ int bp_collide_prims(int t1, int t2, const double* p1,
                                                     const double* z1, const double* s1,
                                                     const double* p2, const double* z2,
                                                     const double* R2, const double* s2,
                                                     double margin, RawCon* out) {
-  if (t2 == GEOM_CYLINDER) return bp_collide_cylinder(t1, p1, z1, s1, p2, R2, s2, margin, out);
-  if (t2 == GEOM_ELLIPSOID) return bp_collide_ellipsoid(t1, p1, z1, s1, p2, R2, s2, margin, out);
+  if constexpr (!LEAN) {
+    if (t2 == GEOM_CYLINDER) return bp_collide_cylinder(t1, p1, z1, s1, p2, R2, s2, margin, out);
+    if (t2 == GEOM_ELLIPSOID) return bp_collide_ellipsoid(t1, p1, z1, s1, p2, R2, s2, margin, out);
+  }
   if (t1 == GEOM_PLANE) {
     if (t2 == GEOM_SPHERE) return col_plane_sphere(p1, z1, p2, s2[0], margin, out[0]);
     if (t2 == GEOM_CAPSULE) {
@@ -324,7 +327,7 @@ static __device__ __noinline__ int bp_collide_prims(int t1, int t2, const double
       }
       return cnt;
     }
-    if (t2 == GEOM_BOX) {
+    if (!LEAN && t2 == GEOM_BOX) {
       double dif[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
       double dist = dot3(dif, z1);
       int cnt = 0;
@@ -479,7 +482,7 @@ BP_STAGE void bp_write_contact(const C& c, int id, int g1, int g2, double margin
   // equal priority: max condim, max friction, solmix-weighted solref / solimp; otherwise
   // everything from the geom with the higher priority
   int d1 = m.geom_condim[g1], d2 = m.geom_condim[g2];
-  const int pr1 = m.geom_priority[g1], pr2 = m.geom_priority[g2];
+  const int pr1 = C::LEAN ? 0 : m.geom_priority[g1], pr2 = C::LEAN ? 0 : m.geom_priority[g2];
   IF(contact_dim)[id] = pr1 > pr2 ? d1 : pr2 > pr1 ? d2 : (d1 > d2 ? d1 : d2);
   const double *f1 = m.geom_friction + 3 * g1, *f2 = m.geom_friction + 3 * g2;
   double fr[3];
@@ -512,7 +515,7 @@ BP_STAGE void bp_collision(const C& c) {
   bool full = false;
   auto gpos = DF(geom_xpos), gmat = DF(geom_xmat);
 #pragma unroll 1
-  const int nprim = m.npair - m.nhfpair;
+  const int nprim = C::LEAN ? m.npair : m.npair - m.nhfpair;
   for (int p0 = 0; p0 < nprim; p0 += C::G) {
     int p = p0 + c.lane, n = 0, g1 = 0, g2 = 0;
     double margin = 0, gap = 0;
@@ -536,12 +539,13 @@ BP_STAGE void bp_collision(const C& c) {
       }
       if (keep) {
         double R2[9], z2[3], s1[3], s2[3];
-        for (int k = 0; k < 9; k++) R2[k] = gmat[9 * g2 + k];
+        if constexpr (!C::LEAN)
+          for (int k = 0; k < 9; k++) R2[k] = gmat[9 * g2 + k];
         for (int k = 0; k < 3; k++) {
-          z2[k] = R2[3 * k + 2];
+          z2[k] = gmat[9 * g2 + 3 * k + 2];
           s1[k] = m.geom_size[3 * g1 + k]; s2[k] = m.geom_size[3 * g2 + k];
         }
-        n = bp_collide_prims(t1, t2, p1, z1, s1, p2, z2, R2, s2, margin, raw);
+        n = bp_collide_prims<C::LEAN>(t1, t2, p1, z1, s1, p2, z2, R2, s2, margin, raw);
       }
     }
     // exclusive prefix sum of n over the group -> slots in pair order
@@ -558,7 +562,7 @@ BP_STAGE void bp_collision(const C& c) {
   // ---- height-field pairs (the last nhfpair of the list): one pair at a time, the
   // triangles under the geom's bounding sphere spread over the lanes, contacts in
   // (row, column, half) order
-  if (m.nhfpair > 0 && c.hf != nullptr) {
+  if constexpr (!C::LEAN) if (m.nhfpair > 0 && c.hf != nullptr) {
 #pragma unroll 1
     for (int p = nprim; p < m.npair && base <= nconmax; p++) {
       if (filterparent && m.pair_parentchild[p]) continue;

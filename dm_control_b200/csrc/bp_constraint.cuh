@@ -45,7 +45,7 @@ BP_STAGE void bp_make_constraint(const C& c) {
   int base = 0, nf = 0;
   // ---- pass 1: headers + slots -------------------------------------------------
   // equalities between joints / fixed tendons: (x1 - x1_0) - poly(x2 - x2_0)
-  if (m.neq_active > 0 && !(m.opt_disableflags & DSBL_EQUALITY)) {
+  if constexpr (!C::LEAN) if (m.neq_active > 0 && !(m.opt_disableflags & DSBL_EQUALITY)) {
     for (int e = c.lane; e < m.neq; e += C::G) {
       if (!m.eq_active[e]) continue;
       int r = 0;
@@ -102,7 +102,7 @@ BP_STAGE void bp_make_constraint(const C& c) {
   }
   // tendon limits, after the joint limits (tendons are few: one group pass each)
   const int ten_base = base;
-  if (!(m.opt_disableflags & DSBL_LIMIT)) {
+  if constexpr (!C::LEAN) if (!(m.opt_disableflags & DSBL_LIMIT)) {
 #pragma unroll 1
     for (int t0 = 0; t0 < m.ntendon; t0 += C::G) {
       int t = t0 + c.lane, n = 0;
@@ -126,7 +126,7 @@ BP_STAGE void bp_make_constraint(const C& c) {
     }
   }
   int con_base = base, ncon = IF(ncon)[0], con_end = 0;
-  const bool pyramidal = m.opt_cone == 0;
+  const bool pyramidal = C::LEAN || m.opt_cone == 0;
   // a contact gets all of its rows or none (mj_addConstraint reserves the whole block);
   // the running sum is monotone, so nothing fits after the first contact that does not
 #pragma unroll 1
@@ -165,7 +165,7 @@ BP_STAGE void bp_make_constraint(const C& c) {
   // ---- pass 2: Jacobian ----------------------------------------------------------
   for (int w = c.lane; w < nefc * nvp; w += C::G) J[w] = 0;
   SYNC();
-  for (int r = c.lane; r < eq_base && r < nefc; r += C::G) {
+  if constexpr (!C::LEAN) for (int r = c.lane; r < eq_base && r < nefc; r += C::G) {
     const int e = IF(efc_id)[r], o1 = m.eq_obj1id[e], o2 = m.eq_obj2id[e];
     const bool tend = m.eq_type[e] == 3;
     const double* cf = m.eq_data + 5 * e;
@@ -199,7 +199,7 @@ BP_STAGE void bp_make_constraint(const C& c) {
     J[r * nvp + m.jnt_dofadr[j]] = -side;
   }
   // tendon limit rows: -side * (tendon Jacobian)
-  for (int r = ten_base + c.lane; r < con_base && r < nefc; r += C::G) {
+  if constexpr (!C::LEAN) for (int r = ten_base + c.lane; r < con_base && r < nefc; r += C::G) {
     int t = IF(efc_id)[r];
     bool lower_on = -(m.tendon_range[2 * t] - DF(ten_length)[t]) < m.tendon_margin[t];
     bool first = (r == ten_base) || IF(efc_id)[r - 1] != t;
@@ -262,7 +262,7 @@ BP_STAGE void bp_make_constraint(const C& c) {
   for (int r = c.lane; r < nefc; r += C::G) {
     int type = IF(efc_type)[r], id = IF(efc_id)[r];
     double solref[2], solimp[5], dA;
-    if (type == CN_EQUALITY) {
+    if (!C::LEAN && type == CN_EQUALITY) {
       for (int k = 0; k < 2; k++) solref[k] = m.eq_solref[2 * id + k];
       for (int k = 0; k < 5; k++) solimp[k] = m.eq_solimp[5 * id + k];
       const int o1 = m.eq_obj1id[id], o2 = m.eq_obj2id[id];
@@ -279,7 +279,7 @@ BP_STAGE void bp_make_constraint(const C& c) {
       for (int k = 0; k < 2; k++) solref[k] = m.jnt_solref[2 * id + k];
       for (int k = 0; k < 5; k++) solimp[k] = m.jnt_solimp[5 * id + k];
       dA = m.dof_invweight0[m.jnt_dofadr[id]];
-    } else if (type == CN_LIMIT_TENDON) {
+    } else if (!C::LEAN && type == CN_LIMIT_TENDON) {
       for (int k = 0; k < 2; k++) solref[k] = m.tendon_solref_lim[2 * id + k];
       for (int k = 0; k < 5; k++) solimp[k] = m.tendon_solimp_lim[5 * id + k];
       dA = m.tendon_invweight0[id];

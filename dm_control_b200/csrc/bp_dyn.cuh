@@ -63,7 +63,7 @@ BP_STAGE void bp_passive(const C& c) {
       }
       f -= m.dof_damping[i] * qvel[i];
       // tendon spring-dampers: each dof gathers the tendons that wrap its joint
-      for (int t = 0; t < m.ntendon; t++) {
+      if constexpr (!C::LEAN) for (int t = 0; t < m.ntendon; t++) {
         double kt = m.tendon_stiffness[t], bt = m.tendon_damping[t];
         if (kt == 0 && bt == 0) continue;
         double frc = -kt * (DF(ten_length)[t] - m.tendon_length0[t]) - bt * DF(ten_velocity)[t];
@@ -78,7 +78,7 @@ BP_STAGE void bp_passive(const C& c) {
   // box with its mass and inertia; viscous force / torque of the equivalent sphere plus
   // quadratic drag per box face.  Bodies on lanes build their wrench (moved to the subtree
   // centre the cdofs refer to) in scratch, then dofs on lanes gather over their subtree.
-  if (!off && (m.opt_density > 0 || m.opt_viscosity > 0)) {
+  if constexpr (!C::LEAN) if (!off && (m.opt_density > 0 || m.opt_viscosity > 0)) {
     const double PI = 3.14159265358979323846;
     auto wr = DF(s_cfrc), cvel = DF(cvel), xipos = DF(xipos), ximat = DF(ximat), scom = DF(subtree_com);
 #pragma unroll 1
@@ -194,7 +194,7 @@ BP_STAGE void bp_rne(const C& c, bool with_acc, typename C::DP cacc, typename C:
 BP_STAGE void bp_transmission(const C& c) {
   const BpModel& m = c.P.m;
   auto len = DF(actuator_length), qpos = DF(qpos);
-  if (m.ntendon > 0) {
+  if constexpr (!C::LEAN) if (m.ntendon > 0) {
     auto tl = DF(ten_length);
     for (int t = c.lane; t < m.ntendon; t += C::G) {
       if (m.tendon_Jadr[t] >= 0) continue;
@@ -253,7 +253,8 @@ BP_STAGE void bp_transmission(const C& c) {
   for (int i = c.lane; i < m.nu; i += C::G) {
     int id = m.actuator_trnid[2 * i];
     len[i] = m.actuator_gear[6 * i] *
-             (m.actuator_trntype[i] == 3 ? DF(ten_length)[id] : qpos[m.jnt_qposadr[id]]);
+             (!C::LEAN && m.actuator_trntype[i] == 3 ? DF(ten_length)[id]
+                                                     : qpos[m.jnt_qposadr[id]]);
   }
   SYNC();
 }
@@ -261,7 +262,7 @@ BP_STAGE void bp_transmission(const C& c) {
 BP_STAGE void bp_actuator_velocity(const C& c) {
   const BpModel& m = c.P.m;
   auto vel = DF(actuator_velocity), qvel = DF(qvel);
-  for (int t = c.lane; t < m.ntendon; t += C::G) {
+  if constexpr (!C::LEAN) for (int t = c.lane; t < m.ntendon; t += C::G) {
     double s = 0;
     if (m.tendon_Jadr[t] >= 0)
       for (int i = 0; i < m.nv; i++) s += DF(ten_J)[m.tendon_Jadr[t] * m.nv + i] * qvel[i];
@@ -273,7 +274,7 @@ BP_STAGE void bp_actuator_velocity(const C& c) {
   for (int i = c.lane; i < m.nu; i += C::G) {
     int id = m.actuator_trnid[2 * i];
     const double g = m.actuator_gear[6 * i];
-    if (m.actuator_trntype[i] == 3) {           // moment row = gear * tendon coefficients
+    if (!C::LEAN && m.actuator_trntype[i] == 3) {   // moment row = gear * tendon coefficients
       double s = 0;
       for (int w = m.tendon_adr[id]; w < m.tendon_adr[id] + m.tendon_num[id]; w++)
         s += g * m.wrap_prm[w] * qvel[m.jnt_dofadr[m.wrap_objid[w]]];
@@ -314,7 +315,7 @@ BP_STAGE void bp_fwd_actuation(const C& c) {
     if (m.actuator_ctrllimited[i] && !(m.opt_disableflags & DSBL_CLAMPCTRL))
       x = clampd(x, m.actuator_ctrlrange[2 * i], m.actuator_ctrlrange[2 * i + 1]);
     double in = x;
-    int dyn = m.actuator_dyntype[i];
+    int dyn = C::LEAN ? 0 : m.actuator_dyntype[i];
     if (dyn != 0) {
       int ia = 0;   // activation index: count of stateful actuators before i
       for (int k = 0; k < i; k++) ia += m.actuator_dyntype[k] != 0;

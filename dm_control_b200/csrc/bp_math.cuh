@@ -19,9 +19,15 @@ struct SP {
   __device__ __forceinline__ bool valid() const { return p != nullptr; }
 };
 
-template <int G_, int S_>
+// LEAN: a second instantiation of every stage for models that use none of: height fields,
+// rangefinders, tendons, equalities, elliptic cones, geoms other than plane / sphere /
+// capsule, fluid forces, actuator dynamics, geom priorities, per-env model frames.  Those
+// branches are compiled out of the hot functions (each of them cost the plain locomotion
+// models ~2 % when it was added, profiles/r1_tuning.md r1u); bp_api.cu picks the shape.
+template <int G_, int S_, bool LEAN_ = false>
 struct Ctx {
   static constexpr int G = G_, S = S_;
+  static constexpr bool LEAN = LEAN_;
   using DP = SP<double, S_>;
   using IP = SP<int, S_>;
   const BpParams& P;

@@ -166,12 +166,11 @@ BP_STAGE void bp_sensors(const C& c, int stage) {
       case SENS_JOINTVEL: out[0] = DF(qvel)[m.jnt_dofadr[id]]; break;
       case SENS_ACTUATORFRC: out[0] = DF(actuator_force)[id]; break;
       case SENS_SUBTREECOM: for (int k = 0; k < 3; k++) out[k] = DF(subtree_com)[3 * id + k]; break;
-      case SENS_RANGEFINDER: {
+      case SENS_RANGEFINDER: if constexpr (!C::LEAN) {
         int body = bp_obj_frame(c, OBJ_SITE, id, pos, mat);
         double zax[3] = {mat[2], mat[5], mat[8]};
         out[0] = bp_ray(c, pos, zax, body);
-        break;
-      }
+      } break;
       case SENS_SUBTREELINVEL: for (int k = 0; k < 3; k++) out[k] = DF(subtree_linvel)[3 * id + k]; break;
       case SENS_FRAMEPOS:
         bp_obj_frame(c, m.sensor_objtype[s], id, pos, mat);
