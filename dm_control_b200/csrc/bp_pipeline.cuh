@@ -343,11 +343,13 @@ __device__ __forceinline__ void bp_run_mode(const C& c) {
 
 // ---- G < 32: image in global memory, 32/G environments per warp -----------------
 // Upper bound of threads per block = register budget of a shape: 512 threads -> 128
-// registers, 1024 -> 64.  The wide shapes (G >= 8) take the 64-register build: a one-block-
-// per-SM launch then holds twice the warps (humanoid G = 16: 28 warps per SM, 1.04 M vs
-// 0.96 M env-steps/s for G = 8 at 128 registers; walker G = 8: 2.41 M vs 2.25 M at G = 4).
+// registers, 896 -> 72, 1024 -> 64.  The wide shapes (G >= 8) take the 72-register build: a
+// one-block-per-SM launch of 16384 x 8 or 8192 x 16 threads is 28 warps = 896 threads per SM
+// (humanoid G = 16 at 64 registers: 1.04 M vs 0.96 M env-steps/s for G = 8 at 128 registers;
+// 72 instead of 64 registers: cheetah 28.3 -> 29.6 M, humanoid 1.152 -> 1.189 M, quadruped-
+// escape 1.39 -> 1.42 M, profiles/r1_tuning.md r1w).
 #ifndef BP_TPB
-#define BP_TPB(G) ((G) >= 8 ? 1024 : 512)
+#define BP_TPB(G) ((G) >= 8 ? 896 : 512)
 #endif
 #ifndef BP_LOCKSTEP
 #define BP_LOCKSTEP 1    // 1: warps of a block re-align at stage boundaries (BP_LOCK)
@@ -529,7 +531,7 @@ static int bp_launch_split(const BpParams* P, cudaStream_t stream, int solver_th
       int th = t;
       if (k == SEG_SOLVE)
         th = g[k] == G ? solver_threads
-                       : bp_block_threads(P->nenv * g[k], g[k] >= 8 ? 1024 : 512);
+                       : bp_block_threads(P->nenv * g[k], BP_TPB(g[k]));
       if (g[k] == 4) bp_launch_seg_g4(P, k, th, first, last, stream);
       else if (g[k] == 8) bp_launch_seg_g8(P, k, th, first, last, stream);
       else bp_launch_seg_g16(P, k, th, first, last, stream);
