@@ -360,6 +360,8 @@ def main():
   local = int(os.environ.get("LOCAL_RANK", "0"))
   torch.cuda.set_device(local)
   if world > 1:
+    # NCCL's version banner goes to stdout; the bench's stdout is the one JSON line
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local))
 
   def reduce_max(x):
