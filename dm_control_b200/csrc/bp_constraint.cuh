@@ -17,7 +17,10 @@ static __device__ __noinline__ void bp_impedance(const double* si, double pos, d
   if (x >= 1 || x <= 0) { *imp = x >= 1 ? si[1] : si[0]; *impP = 0; return; }
   double y, yP, p = si[4], mid = si[3];
   if (p == 1) { y = x; yP = 1; }
-  else if (x <= mid) {
+  else if (p == 2) {          // the default power: pow(x, 2) = x * x and pow(x, 1) = x exactly
+    if (x <= mid) { double a = 1 / mid; y = a * (x * x); yP = p * a * x; }
+    else { double b = 1 / (1 - mid), xm = 1 - x; y = 1 - b * (xm * xm); yP = p * b * xm; }
+  } else if (x <= mid) {
     double a = 1 / bp_pow(mid, p - 1);
     y = a * bp_pow(x, p); yP = p * a * bp_pow(x, p - 1);
   } else {
