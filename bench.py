@@ -57,6 +57,7 @@ try:
 except (OSError, ValueError, KeyError):
   pass
 # `lanes`: execution shape picked from the lane sweep (profiles/r1b_sweep_lanes.jsonl)
+_JSON_OUT = None     # the process's original stdout when fd 1 has been pointed at stderr
 WORKLOADS = {"cheetah-run": dict(nenv=16384, njmax=64, nconmax=16, settle=200, lanes=8),
              "humanoid-run": dict(nenv=8192, njmax=120, nconmax=40, settle=100, lanes=16),
              "walker-walk": dict(nenv=16384, njmax=48, nconmax=12, settle=50, lanes=8),
@@ -334,7 +335,8 @@ def reference_arm(args):
                            "kind": "port", "sample": sample},
           "e2e": {"value": value, "unit": "env-steps/s", "h2d_bytes_per_step": 0,
                   "d2h_bytes_per_step": 0}}
-  print(json.dumps(line))
+  print(json.dumps(line), file=_JSON_OUT or sys.stdout)
+  (_JSON_OUT or sys.stdout).flush()
 
 
 def main():
@@ -360,8 +362,12 @@ def main():
   local = int(os.environ.get("LOCAL_RANK", "0"))
   torch.cuda.set_device(local)
   if world > 1:
-    # NCCL's version banner goes to stdout; the bench's stdout is the one JSON line
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    # libraries (NCCL's version banner) write to fd 1; the bench's stdout is the one JSON
+    # line: keep the real stdout aside and point fd 1 at stderr for everything else
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     torch.distributed.init_process_group("nccl", device_id=torch.device("cuda", local))
 
   def reduce_max(x):
@@ -445,7 +451,8 @@ def main():
   }
   if world == 1 and not args.no_cpu:
     line["cpu_baseline"] = cpu_baseline(name)
-  print(json.dumps(line))
+  print(json.dumps(line), file=_JSON_OUT or sys.stdout)
+  (_JSON_OUT or sys.stdout).flush()
   if world > 1:
     torch.distributed.destroy_process_group()
 
