@@ -20,6 +20,8 @@ extern "C" int bp_launch_step_g1(const BpParams* P, cudaStream_t stream);
 extern "C" int bp_launch_step_g16_lean(const BpParams* P, cudaStream_t stream);
 extern "C" int bp_launch_step_g8_lean(const BpParams* P, cudaStream_t stream);
 extern "C" int bp_launch_step_g4_lean(const BpParams* P, cudaStream_t stream);
+extern "C" int bp_launch_step_g16_mid(const BpParams* P, cudaStream_t stream);
+extern "C" int bp_launch_step_g8_mid(const BpParams* P, cudaStream_t stream);
 extern "C" int bp_launch_field_copy(const BpParams* P, long long off, int count, int is_int,
                                     void* dense, long long env0, long long n, int to_image,
                                     cudaStream_t stream);
@@ -210,6 +212,17 @@ static int derive(bp_model* m) {
   for (int g = 0; g < M.ngeom; g++)
     if ((gt[g] != GEOM_PLANE && gt[g] != GEOM_SPHERE && gt[g] != GEOM_CAPSULE) || gpr[g] != 0)
       M.lean_static = 0;
+  // MID shape: everything but spatial tendons, tendon limits / springs, box geoms, priorities
+  M.mid_static = M.nspatial == 0;
+  for (int g = 0; g < M.ngeom; g++)
+    if (gt[g] == GEOM_BOX || gpr[g] != 0) M.mid_static = 0;
+  if (M.ntendon > 0) {
+    auto& tl = I(m, "tendon_limited");
+    auto& tk = F(m, "tendon_stiffness");
+    auto& tb = F(m, "tendon_damping");
+    for (int t = 0; t < M.ntendon; t++)
+      if (tl[t] != 0 || tk[t] != 0 || tb[t] != 0) M.mid_static = 0;
+  }
   return BP_OK;
 }
 
@@ -647,14 +660,16 @@ static int launch(bp_batch* b, int mode, int nsub, int disable_actuation,
   int e;
   const BpModel& M = b->model->M;
   // BPHYS_NO_LEAN=1 / BPHYS_SPLIT=1 keep the full instantiation
-  const bool lean = M.lean_static && M.opt_cone == 0 && M.opt_density == 0 &&
-                    M.opt_viscosity == 0 && !P.env_geom_pos && !P.env_site_pos &&
-                    !P.env_body_pos && !P.env_body_quat && !getenv("BPHYS_NO_LEAN") &&
-                    !getenv("BPHYS_SPLIT");
-  if (lean && (b->lanes == 4 || b->lanes == 8 || b->lanes == 16)) {
+  const bool plain = M.opt_cone == 0 && M.opt_density == 0 && M.opt_viscosity == 0 &&
+                     !P.env_geom_pos && !P.env_site_pos && !P.env_body_pos && !P.env_body_quat &&
+                     !getenv("BPHYS_NO_LEAN") && !getenv("BPHYS_SPLIT");
+  if (plain && M.lean_static && (b->lanes == 4 || b->lanes == 8 || b->lanes == 16)) {
     e = b->lanes == 4 ? bp_launch_step_g4_lean(&P, b->stream)
         : b->lanes == 8 ? bp_launch_step_g8_lean(&P, b->stream)
                         : bp_launch_step_g16_lean(&P, b->stream);
+  } else if (plain && M.mid_static && (b->lanes == 8 || b->lanes == 16)) {
+    e = b->lanes == 8 ? bp_launch_step_g8_mid(&P, b->stream)
+                      : bp_launch_step_g16_mid(&P, b->stream);
   } else
   switch (b->lanes) {
     case 1: e = bp_launch_step_g1(&P, b->stream); break;

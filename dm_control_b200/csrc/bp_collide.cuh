@@ -303,13 +303,13 @@ static __device__ __noinline__ int bp_collide_ellipsoid(int t1, const double* p1
 // Narrowphase of ordered pair (type1 <= type2) on geom poses already copied to
 // registers (p = centre, z = local z axis, R2 = full frame of geom 2 for boxes).
 // Returns the number of raw contacts written to out[0..3].
-template <bool LEAN>
+template <int SHAPE>
 static __device__ __noinline__ int bp_collide_prims(int t1, int t2, const double* p1,
                                                     const double* z1, const double* s1,
                                                     const double* p2, const double* z2,
                                                     const double* R2, const double* s2,
                                                     double margin, RawCon* out) {
-  if constexpr (!LEAN) {
+  if constexpr (SHAPE != 1) {
     if (t2 == GEOM_CYLINDER) return bp_collide_cylinder(t1, p1, z1, s1, p2, R2, s2, margin, out);
     if (t2 == GEOM_ELLIPSOID) return bp_collide_ellipsoid(t1, p1, z1, s1, p2, R2, s2, margin, out);
   }
@@ -327,7 +327,7 @@ static __device__ __noinline__ int bp_collide_prims(int t1, int t2, const double
       }
       return cnt;
     }
-    if (!LEAN && t2 == GEOM_BOX) {
+    if (SHAPE == 0 && t2 == GEOM_BOX) {
       double dif[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
       double dist = dot3(dif, z1);
       int cnt = 0;
@@ -482,7 +482,7 @@ BP_STAGE void bp_write_contact(const C& c, int id, int g1, int g2, double margin
   // equal priority: max condim, max friction, solmix-weighted solref / solimp; otherwise
   // everything from the geom with the higher priority
   int d1 = m.geom_condim[g1], d2 = m.geom_condim[g2];
-  const int pr1 = C::LEAN ? 0 : m.geom_priority[g1], pr2 = C::LEAN ? 0 : m.geom_priority[g2];
+  const int pr1 = C::FULL ? m.geom_priority[g1] : 0, pr2 = C::FULL ? m.geom_priority[g2] : 0;
   IF(contact_dim)[id] = pr1 > pr2 ? d1 : pr2 > pr1 ? d2 : (d1 > d2 ? d1 : d2);
   const double *f1 = m.geom_friction + 3 * g1, *f2 = m.geom_friction + 3 * g2;
   double fr[3];
@@ -545,7 +545,7 @@ BP_STAGE void bp_collision(const C& c) {
           z2[k] = gmat[9 * g2 + 3 * k + 2];
           s1[k] = m.geom_size[3 * g1 + k]; s2[k] = m.geom_size[3 * g2 + k];
         }
-        n = bp_collide_prims<C::LEAN>(t1, t2, p1, z1, s1, p2, z2, R2, s2, margin, raw);
+        n = bp_collide_prims<(C::FULL ? 0 : C::LEAN ? 1 : 2)>(t1, t2, p1, z1, s1, p2, z2, R2, s2, margin, raw);
       }
     }
     // exclusive prefix sum of n over the group -> slots in pair order

@@ -105,7 +105,7 @@ BP_STAGE void bp_make_constraint(const C& c) {
   }
   // tendon limits, after the joint limits (tendons are few: one group pass each)
   const int ten_base = base;
-  if constexpr (!C::LEAN) if (!(m.opt_disableflags & DSBL_LIMIT)) {
+  if constexpr (C::FULL) if (!(m.opt_disableflags & DSBL_LIMIT)) {
 #pragma unroll 1
     for (int t0 = 0; t0 < m.ntendon; t0 += C::G) {
       int t = t0 + c.lane, n = 0;
@@ -129,7 +129,7 @@ BP_STAGE void bp_make_constraint(const C& c) {
     }
   }
   int con_base = base, ncon = IF(ncon)[0], con_end = 0;
-  const bool pyramidal = C::LEAN || m.opt_cone == 0;
+  const bool pyramidal = !C::FULL || m.opt_cone == 0;
   // a contact gets all of its rows or none (mj_addConstraint reserves the whole block);
   // the running sum is monotone, so nothing fits after the first contact that does not
 #pragma unroll 1
@@ -202,7 +202,7 @@ BP_STAGE void bp_make_constraint(const C& c) {
     J[r * nvp + m.jnt_dofadr[j]] = -side;
   }
   // tendon limit rows: -side * (tendon Jacobian)
-  if constexpr (!C::LEAN) for (int r = ten_base + c.lane; r < con_base && r < nefc; r += C::G) {
+  if constexpr (C::FULL) for (int r = ten_base + c.lane; r < con_base && r < nefc; r += C::G) {
     int t = IF(efc_id)[r];
     bool lower_on = -(m.tendon_range[2 * t] - DF(ten_length)[t]) < m.tendon_margin[t];
     bool first = (r == ten_base) || IF(efc_id)[r - 1] != t;
@@ -282,7 +282,7 @@ BP_STAGE void bp_make_constraint(const C& c) {
       for (int k = 0; k < 2; k++) solref[k] = m.jnt_solref[2 * id + k];
       for (int k = 0; k < 5; k++) solimp[k] = m.jnt_solimp[5 * id + k];
       dA = m.dof_invweight0[m.jnt_dofadr[id]];
-    } else if (!C::LEAN && type == CN_LIMIT_TENDON) {
+    } else if (C::FULL && type == CN_LIMIT_TENDON) {
       for (int k = 0; k < 2; k++) solref[k] = m.tendon_solref_lim[2 * id + k];
       for (int k = 0; k < 5; k++) solimp[k] = m.tendon_solimp_lim[5 * id + k];
       dA = m.tendon_invweight0[id];

@@ -63,7 +63,7 @@ BP_STAGE void bp_passive(const C& c) {
       }
       f -= m.dof_damping[i] * qvel[i];
       // tendon spring-dampers: each dof gathers the tendons that wrap its joint
-      if constexpr (!C::LEAN) for (int t = 0; t < m.ntendon; t++) {
+      if constexpr (C::FULL) for (int t = 0; t < m.ntendon; t++) {
         double kt = m.tendon_stiffness[t], bt = m.tendon_damping[t];
         if (kt == 0 && bt == 0) continue;
         double frc = -kt * (DF(ten_length)[t] - m.tendon_length0[t]) - bt * DF(ten_velocity)[t];
@@ -78,7 +78,7 @@ BP_STAGE void bp_passive(const C& c) {
   // box with its mass and inertia; viscous force / torque of the equivalent sphere plus
   // quadratic drag per box face.  Bodies on lanes build their wrench (moved to the subtree
   // centre the cdofs refer to) in scratch, then dofs on lanes gather over their subtree.
-  if constexpr (!C::LEAN) if (!off && (m.opt_density > 0 || m.opt_viscosity > 0)) {
+  if constexpr (C::FULL) if (!off && (m.opt_density > 0 || m.opt_viscosity > 0)) {
     const double PI = 3.14159265358979323846;
     auto wr = DF(s_cfrc), cvel = DF(cvel), xipos = DF(xipos), ximat = DF(ximat), scom = DF(subtree_com);
 #pragma unroll 1
@@ -197,7 +197,7 @@ BP_STAGE void bp_transmission(const C& c) {
   if constexpr (!C::LEAN) if (m.ntendon > 0) {
     auto tl = DF(ten_length);
     for (int t = c.lane; t < m.ntendon; t += C::G) {
-      if (m.tendon_Jadr[t] >= 0) continue;
+      if (C::FULL && m.tendon_Jadr[t] >= 0) continue;
       double s = 0;
       for (int w = m.tendon_adr[t]; w < m.tendon_adr[t] + m.tendon_num[t]; w++)
         s += m.wrap_prm[w] * qpos[m.jnt_qposadr[m.wrap_objid[w]]];
@@ -205,7 +205,7 @@ BP_STAGE void bp_transmission(const C& c) {
     }
     // spatial tendons (straight segments between sites): dofs on lanes build the dense
     // Jacobian row  sum_seg (jacp(p1) - jacp(p0))^T dir;  lane 0 keeps the length
-    if (m.nspatial > 0) {
+    if constexpr (C::FULL) if (m.nspatial > 0) {
       auto sx = DF(site_xpos), cdof = DF(cdof), com = DF(subtree_com), tJ = DF(ten_J);
 #pragma unroll 1
       for (int t = 0; t < m.ntendon; t++) {
@@ -264,7 +264,7 @@ BP_STAGE void bp_actuator_velocity(const C& c) {
   auto vel = DF(actuator_velocity), qvel = DF(qvel);
   if constexpr (!C::LEAN) for (int t = c.lane; t < m.ntendon; t += C::G) {
     double s = 0;
-    if (m.tendon_Jadr[t] >= 0)
+    if (C::FULL && m.tendon_Jadr[t] >= 0)
       for (int i = 0; i < m.nv; i++) s += DF(ten_J)[m.tendon_Jadr[t] * m.nv + i] * qvel[i];
     else
       for (int w = m.tendon_adr[t]; w < m.tendon_adr[t] + m.tendon_num[t]; w++)

@@ -24,10 +24,14 @@ struct SP {
 // capsule, fluid forces, actuator dynamics, geom priorities, per-env model frames.  Those
 // branches are compiled out of the hot functions (each of them cost the plain locomotion
 // models ~2 % when it was added, profiles/r1_tuning.md r1u); bp_api.cu picks the shape.
-template <int G_, int S_, bool LEAN_ = false>
+// SHAPE 2 (MID) keeps height fields, rangefinders, fixed tendons, equalities, ellipsoid /
+// cylinder geoms and actuator dynamics (the quadruped) and drops what only FULL has:
+// elliptic cones, fluid forces, spatial tendons, tendon limits and springs, box geoms, geom
+// priorities, per-env model frames.
+template <int G_, int S_, int SHAPE_ = 0>
 struct Ctx {
   static constexpr int G = G_, S = S_;
-  static constexpr bool LEAN = LEAN_;
+  static constexpr bool LEAN = SHAPE_ == 1, FULL = SHAPE_ == 0;
   using DP = SP<double, S_>;
   using IP = SP<int, S_>;
   const BpParams& P;

@@ -355,7 +355,7 @@ __device__ __forceinline__ void bp_run_mode(const C& c) {
 #define BP_LOCKSTEP 1    // 1: warps of a block re-align at stage boundaries (BP_LOCK)
 #endif
 #define BP_BOUNDS __launch_bounds__(BP_TPB(G))
-template <int G, int S, bool LEAN>
+template <int G, int S, int SHAPE>
 __global__ void BP_BOUNDS
 bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
   const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
@@ -386,7 +386,7 @@ bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
   const double* sp = P.env_site_pos ? P.env_site_pos + env * 3LL * P.m.nsite : P.m.site_pos;
   const double* bp = P.env_body_pos ? P.env_body_pos + env * 3LL * P.m.nbody : P.m.body_pos;
   const double* bq = P.env_body_quat ? P.env_body_quat + env * 4LL * P.m.nbody : P.m.body_quat;
-  Ctx<G, S, LEAN> c{P, base, ib, wl & (G - 1), mask, act, lock, hot, hf, gp, sp, bp, bq};
+  Ctx<G, S, SHAPE> c{P, base, ib, wl & (G - 1), mask, act, lock, hot, hf, gp, sp, bp, bq};
   bp_load_ctrl(c, env);
   bp_run_mode(c);
   if (P.rew_out && act) {           // epilogue: the task's observation and reward
@@ -558,12 +558,12 @@ static inline int bp_block_threads(long long threads_total, int tpb_max) {
 // (packed Hessian + pivots + Mgrad) to shared memory when it fits; it is off by default
 // because the L1 capacity it takes costs more than the shorter latency gains
 // (humanoid-run: 710 k vs 790 k env-steps/s, profiles/r1_tuning.md).
-template <int G, int S, bool LEAN = false>
+template <int G, int S, int SHAPE = 0>
 static int bp_launch_gmem(const BpParams* P, cudaStream_t stream) {
   const long long total = P->nenv * G;
   const int threads = bp_block_threads(total, BP_TPB(G));
   const unsigned blocks = (unsigned)((total + threads - 1) / threads);
-  if constexpr (S == 1 && G >= 4 && !LEAN) {
+  if constexpr (S == 1 && G >= 4 && SHAPE == 0) {
     if (P->mode == BP_MODE_STEP && P->m.opt_integrator == 0 && getenv("BPHYS_SPLIT"))
       return bp_launch_split<G>(P, stream, threads);
   }
@@ -578,19 +578,19 @@ static int bp_launch_gmem(const BpParams* P, cudaStream_t stream) {
   static bool carved = false;
   if (!carved) {            // no shared memory in the default shape: ask for all of it as L1
     if (const char* e = getenv("BPHYS_CARVEOUT"))
-      cudaFuncSetAttribute(bp_step_kernel_gmem<G, S, LEAN>,
+      cudaFuncSetAttribute(bp_step_kernel_gmem<G, S, SHAPE>,
                            cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e));
     carved = true;
   }
   static size_t configured = 48 * 1024;
   if (bytes > configured) {
-    cudaError_t e = cudaFuncSetAttribute(bp_step_kernel_gmem<G, S, LEAN>,
+    cudaError_t e = cudaFuncSetAttribute(bp_step_kernel_gmem<G, S, SHAPE>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)bytes);
     if (e != cudaSuccess) return (int)e;
     configured = bytes;
   }
-  bp_step_kernel_gmem<G, S, LEAN><<<blocks, threads, bytes, stream>>>(Q);
+  bp_step_kernel_gmem<G, S, SHAPE><<<blocks, threads, bytes, stream>>>(Q);
   return (int)cudaGetLastError();
 }
 

@@ -239,7 +239,7 @@ BP_STAGE double bp_update_constraint(const C& c, typename C::DP jar, int nefc, b
       DF(s_rw)[r] = w;
     }
   }
-  if constexpr (!C::LEAN) if (c.P.m.opt_cone == 1) cost += bp_cone_update(c, jar, nefc, write, &chg);
+  if constexpr (C::FULL) if (c.P.m.opt_cone == 1) cost += bp_cone_update(c, jar, nefc, write, &chg);
   cost = group_sum(c, cost);
   if (write) {
     *changed = group_any(c, chg);
@@ -288,7 +288,7 @@ BP_STAGE LSPoint bp_ls_eval(const C& c, double alpha, double g0, double g1, doub
     else if (x < 0) { c0 += q0; c1 += q1; c2 += q2; }
   }
   double e[3] = {0, 0, 0};
-  if constexpr (!C::LEAN) if (c.P.m.opt_cone == 1) {
+  if constexpr (C::FULL) if (c.P.m.opt_cone == 1) {
     double q[3] = {0, 0, 0};
     bp_cone_ls(c, alpha, nefc, q, e);
     c0 += q[0]; c1 += q[1]; c2 += q[2];
@@ -652,7 +652,7 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, int ntenlim,
       SYNC();
     }
   }
-  if constexpr (!C::LEAN) if (m.opt_cone == 1) bp_cone_hessian(c, H, nefc);
+  if constexpr (C::FULL) if (m.opt_cone == 1) bp_cone_hessian(c, H, nefc);
   if (!bp_chol_factor(c, H, Hdinv)) {
     SYNC();
     bp_copy(c, H, Md, ntri);
@@ -699,7 +699,7 @@ BP_STAGE void bp_solver_begin(const C& c, BpSolve& st) {
     else if (t == CN_LIMIT_TENDON) ntenlim++;
   }
   nsingle = (int)(group_sum(c, (double)nsingle) + 0.5);
-  if (!C::LEAN && m.ntendon > 0) ntenlim = (int)(group_sum(c, (double)ntenlim) + 0.5);
+  if (C::FULL && m.ntendon > 0) ntenlim = (int)(group_sum(c, (double)ntenlim) + 0.5);
   st.nsingle = nsingle; st.ntenlim = ntenlim;
   // dense copy of M as a packed lower triangle
   auto Md = DF(s_Md), qM = DF(qM);

@@ -3,5 +3,5 @@
 #include "bp_pipeline.cuh"
 
 extern "C" int bp_launch_step_g8_lean(const BpParams* P, cudaStream_t stream) {
-  return bp_launch_gmem<8, 1, true>(P, stream);
+  return bp_launch_gmem<8, 1, 1>(P, stream);
 }

@@ -110,7 +110,8 @@ struct BpModel {
   int nlevel, ndoflevel, nfric, nlim, ntri, nvp, neq_active;  // nvp: odd row stride >= nv
   int any_damping, need_subtreevel, need_rnepost_stage;  // sensor prerequisites
   int nhinge, nsens_ft, nsens_rf;   // hinge joints; force + torque sensors; rangefinders
-  int lean_static;   // structure fits the LEAN instantiation (Ctx<G, S, true>, bp_math.cuh)
+  int lean_static;   // structure fits the LEAN instantiation (Ctx<G, S, 1>, bp_math.cuh)
+  int mid_static;    // structure fits the MID instantiation (Ctx<G, S, 2>)
 };
 
 // ---- per-environment data image ---------------------------------------------
