@@ -551,7 +551,9 @@ static inline int bp_block_threads(long long threads_total, int tpb_max) {
   const long long warps = (threads_total + 31) / 32;
   const long long per_sm = (warps + 147) / 148;        // 148 SMs
   if (per_sm * 32 <= tpb_max) return per_sm < 2 ? 64 : (int)per_sm * 32;  // one block per SM
-  return tpb_max > 512 ? 512 : tpb_max;
+  // larger batches: blocks that fit twice per SM at the shape's register budget
+  // (2 x 448 x 72 registers for the wide shapes)
+  return tpb_max > 512 ? 448 : tpb_max;
 }
 
 // Launch of one global-memory shape.  BPHYS_ARENA=1 moves the per-env solver arena
