@@ -38,6 +38,19 @@ def test_library_exports_every_declared_symbol():
   assert lib.bp_version() == 100
 
 
+def test_library_holds_every_execution_shape():
+  """One launcher per lane width, plus the LEAN (G = 4, 8, 16) and MID (G = 8, 16)
+  instantiations of the step kernel and the per-stage launchers of the split pipeline
+  (csrc/bp_pipeline.cuh, bp_api.cu launch())."""
+  lib = binding.load()
+  shapes = ["bp_launch_step_g%d" % g for g in (1, 2, 4, 8, 16, 32)]
+  shapes += ["bp_launch_step_g%d_lean" % g for g in (4, 8, 16)]
+  shapes += ["bp_launch_step_g%d_mid" % g for g in (8, 16)]
+  shapes += ["bp_launch_seg_g%d" % g for g in (4, 8, 16)]
+  for n in shapes:
+    assert hasattr(lib, n), "libbphys.so lacks %s" % n
+
+
 def test_no_cpu_fallback_without_device():
   lib = binding.load()
   if lib.bp_device_count() > 0:
