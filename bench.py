@@ -72,7 +72,7 @@ WORKLOADS = {"cheetah-run": dict(nenv=16384, njmax=64, nconmax=16, settle=200, l
 # committed `ncu --set full` captures (profiles/), keyed by (task, lanes, envs per GPU)
 NCU_TRAFFIC = {("cheetah-run", 8, 16384): (470.8e6, "profiles/r1z_cheetah_g8_lean.summary.txt"),
                ("cheetah-run", 4, 16384): (345.5e6, "profiles/r1g_cheetah_g4.summary.txt"),
-               ("humanoid-run", 16, 8192): (5.775e9, "profiles/r1m_humanoid_g16.summary.txt"),
+               ("humanoid-run", 16, 8192): (5.239e9, "profiles/r1z_humanoid_g16_lean.summary.txt"),
                ("humanoid-run", 8, 8192): (5.531e9, "profiles/r1g_humanoid_g8.summary.txt")}
 
 
