@@ -72,6 +72,10 @@ _SIGNATURES = {
     "bp_env_step_host": (_i32, [_vp, _i32, _vp, _vp, _vp]),
     "bp_rewards_tolerance": (_i32, [_i32, _vp, _vp, _i64, ctypes.c_double, ctypes.c_double,
                                     ctypes.c_double, _i32, ctypes.c_double]),
+    "bp_rewards_tolerance_noalloc": (_i32, [_i32, _vp, _vp, _i64, ctypes.c_double,
+                                            ctypes.c_double, ctypes.c_double, _i32,
+                                            ctypes.c_double]),
+    "bp_rewards_tolerance_noalloc_max": (_i32, []),
     "bp_warnings": (_i32, [_vp, _vp]),
     "bp_sync": (_i32, [_vp]),
     "bp_batch_stream": (_vp, [_vp]),
@@ -114,6 +118,20 @@ def rewards_tolerance(x, bounds=(0.0, 0.0), margin=0.0, sigmoid="gaussian",
   check(load().bp_rewards_tolerance(device, _ptr(a), _ptr(out), a.size, float(bounds[0]),
                                     float(bounds[1]), float(margin), SIGMOIDS[sigmoid],
                                     float(value_at_margin)))
+  return out
+
+
+def rewards_tolerance_noalloc(x, bounds=(0.0, 0.0), margin=0.0, sigmoid="gaussian",
+                              value_at_margin=0.1, device=0):
+  """rewards_tolerance() through the entry point that allocates no device memory (fixed
+  scratch of bp_rewards_tolerance_noalloc_max() elements; larger inputs raise)."""
+  if sigmoid not in SIGMOIDS:
+    raise ValueError("Unknown sigmoid type {!r}.".format(sigmoid))
+  a = np.ascontiguousarray(x, dtype=np.float64)
+  out = np.empty_like(a)
+  check(load().bp_rewards_tolerance_noalloc(device, _ptr(a), _ptr(out), a.size,
+                                            float(bounds[0]), float(bounds[1]), float(margin),
+                                            SIGMOIDS[sigmoid], float(value_at_margin)))
   return out
 
 

@@ -34,6 +34,8 @@ extern "C" int bp_task_nobs_impl(const BpModel* m, int task);
 
 static thread_local std::string g_err;
 static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+// for the library's other translation units (bp_noalloc.cu); not part of include/bphys.h
+extern "C" void bp_set_last_error_(const char* msg) { g_err = msg ? msg : ""; }
 #define CUDA_OK(expr)                                                        \
   do {                                                                       \
     cudaError_t e_ = (expr);                                                 \

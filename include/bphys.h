@@ -138,6 +138,23 @@ int bp_rewards_tolerance(int device, const double* x_host, double* out_host, int
                          double lower, double upper, double margin, int sigmoid,
                          double value_at_margin);
 
+/* bp_rewards_tolerance for callers that may not allocate device memory (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid cudaMalloc).  NO counterpart in
+ * the reference.  Same arguments and results
+ * as bp_rewards_tolerance, but the device staging of x / out lives in one file-scope device
+ * array (csrc/bp_noalloc.cu) instead of a cudaMalloc per call: it calls no cudaMalloc /
+ * cudaFree / allocating library routine.  Limit: n <= BP_REWARDS_TOLERANCE_NOALLOC_MAX
+ * (65536 elements; larger n returns BP_EINVAL with a message); every GPU that loads the
+ * library holds the 1 MiB array until exit.  All calls share the array and it keeps the
+ * previous call's contents (every element a call reads is written by that call first, so
+ * nothing needs clearing); calls are serialised inside the library, and anything else that
+ * would overlap with one on the GPU races. */
+#define BP_REWARDS_TOLERANCE_NOALLOC_MAX 65536
+int bp_rewards_tolerance_noalloc(int device, const double* x_host, double* out_host, int64_t n,
+                                 double lower, double upper, double margin, int sigmoid,
+                                 double value_at_margin);
+int bp_rewards_tolerance_noalloc_max(void);   /* = BP_REWARDS_TOLERANCE_NOALLOC_MAX */
+
 /* Fused Environment.step on DEVICE buffers, ONE kernel launch: scatter ctrl_dev
  * [nenv][nu] into the images, nsub physics steps, then the bound task's observation
  * ([nenv][nobs], may be NULL) and reward ([nenv]).  Asynchronous on the batch's stream. */
