@@ -168,6 +168,10 @@ class Model:
                                              old.shape))
     check(load().bp_model_set_field(self.ptr, name.encode(), _ptr(a), a.nbytes))
     self.flat.arrays[name] = a.copy()
+    if name in ("geom_size", "geom_type"):      # the library re-derives the bounding radii
+      rb = np.empty_like(self.flat.arrays["geom_rbound"])
+      check(load().bp_model_get_field(self.ptr, b"geom_rbound", _ptr(rb), rb.nbytes))
+      self.flat.arrays["geom_rbound"] = rb
 
   def free(self):
     if getattr(self, "ptr", None):

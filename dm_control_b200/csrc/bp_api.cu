@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdio.h>
 #include <string.h>
+#include <math.h>
 
 #include <map>
 #include <string>
@@ -228,6 +229,70 @@ static int derive(bp_model* m) {
   return BP_OK;
 }
 
+// What the kernels implement.  Everything else must fail loudly instead of running other
+// physics (the reference surfaces engine errors, wrapper/core_test.py:97-103).
+//   pairs: the narrowphase table of csrc/bp_collide.cuh / bp_hfield.cuh
+#ifndef BP_HAVE_BOX_PAIRS
+#define BP_HAVE_BOX_PAIRS 0      // sphere / capsule / box against box
+#endif
+#ifndef BP_HAVE_PGS_CG
+#define BP_HAVE_PGS_CG 0         // opt_solver 0 (PGS) and 1 (CG)
+#endif
+static bool pair_supported(int t1, int t2) {
+  if (t1 > t2) { int t = t1; t1 = t2; t2 = t; }
+  if (!BP_HAVE_BOX_PAIRS && t2 == GEOM_BOX && t1 != GEOM_PLANE) return false;
+  if (t1 == GEOM_PLANE)
+    return t2 == GEOM_SPHERE || t2 == GEOM_CAPSULE || t2 == GEOM_ELLIPSOID ||
+           t2 == GEOM_CYLINDER || t2 == GEOM_BOX;
+  if (t1 == GEOM_HFIELD)
+    return t2 == GEOM_SPHERE || t2 == GEOM_CAPSULE || t2 == GEOM_ELLIPSOID || t2 == GEOM_CYLINDER;
+  if (t1 == GEOM_SPHERE)
+    return t2 == GEOM_SPHERE || t2 == GEOM_CAPSULE || t2 == GEOM_ELLIPSOID ||
+           t2 == GEOM_CYLINDER || t2 == GEOM_BOX;
+  if (t1 == GEOM_CAPSULE)
+    return t2 == GEOM_CAPSULE || t2 == GEOM_ELLIPSOID || t2 == GEOM_CYLINDER || t2 == GEOM_BOX;
+  if (t1 == GEOM_CYLINDER) return t2 == GEOM_CYLINDER;
+  if (t1 == GEOM_BOX) return t2 == GEOM_BOX;
+  return false;
+}
+
+static int validate(bp_model* m) {
+  const BpModel& M = m->M;
+  static const char* tn[] = {"plane", "hfield", "sphere", "capsule", "ellipsoid", "cylinder",
+                             "box", "mesh"};
+  auto& gt = I(m, "geom_type");
+  for (int g = 0; g < M.ngeom; g++)
+    if (gt[g] < 0 || gt[g] >= GEOM_MESH)
+      return fail(BP_EINVAL, "geom " + std::to_string(g) + ": mesh geoms are not supported");
+  if (M.opt_solver < 0 || M.opt_solver > 2)
+    return fail(BP_EINVAL, "opt_solver must be 0 (PGS), 1 (CG) or 2 (Newton)");
+  if (!BP_HAVE_PGS_CG && M.opt_solver != 2)
+    return fail(BP_EINVAL, "only the Newton solver is implemented (opt_solver = PGS / CG)");
+  if (M.opt_solver != 2 && M.opt_cone != 0)
+    return fail(BP_EINVAL, "the PGS and CG solvers are implemented for pyramidal cones only");
+  auto ns = m->fields.find("opt_noslip_iterations");
+  if (ns != m->fields.end() && !ns->second.i.empty() && ns->second.i[0] > 0)
+    return fail(BP_EINVAL, "noslip_iterations > 0 is not supported (the noslip post-solver is "
+                           "not implemented)");
+  // colliding pairs without a narrowphase: only acceptable while contacts cannot occur
+  const bool contacts_on = !(M.opt_disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT));
+  if (contacts_on) {
+    auto& p1 = I(m, "pair_geom1");
+    auto& p2 = I(m, "pair_geom2");
+    auto& pc = I(m, "pair_parentchild");
+    const bool filt = !(M.opt_disableflags & DSBL_FILTERPARENT);
+    for (int p = 0; p < M.npair; p++) {
+      if (filt && pc[p]) continue;      // parent-child pairs are filtered out at run time
+      const int t1 = gt[p1[p]], t2 = gt[p2[p]];
+      if (!pair_supported(t1, t2))
+        return fail(BP_EINVAL, std::string("geom pair (") + std::to_string(p1[p]) + ", " +
+                    std::to_string(p2[p]) + ") of types " + tn[t1] + " - " + tn[t2] +
+                    " has no narrowphase: exclude the pair, or disable contacts");
+    }
+  }
+  return BP_OK;
+}
+
 static int upload(bp_model* m) {
   size_t off = 0;
   for (auto& kv : m->fields) { kv.second.dev_off = off; off += (kv.second.nbytes() + 15) / 16 * 16; }
@@ -298,7 +363,8 @@ extern "C" bp_model* bp_model_create(const void* blob, int64_t nbytes, int devic
   BP_MODEL_F64_ARRAYS(X)
 #undef X
   if (missing) { std::string s = std::string("model blob lacks field ") + missing; delete m; return bail(s); }
-  if (refresh_scalars(m) != BP_OK || derive(m) != BP_OK || upload(m) != BP_OK) {
+  if (refresh_scalars(m) != BP_OK || derive(m) != BP_OK || validate(m) != BP_OK ||
+      upload(m) != BP_OK) {
     std::string s = g_err; if (m->dev) cudaFree(m->dev); delete m; return bail(s);
   }
   return m;
@@ -310,17 +376,73 @@ extern "C" void bp_model_free(bp_model* m) {
   delete m;
 }
 
+// geom_rbound as the compiler derives it (mjcf_compiler.py _rbound) -- recomputed when a
+// geom_size / geom_type edit arrives at run time (the broadphase reads it)
+static void recompute_rbound(bp_model* m) {
+  auto& gt = I(m, "geom_type");
+  auto& gs = F(m, "geom_size");
+  auto& rb = m->fields["geom_rbound"].f;
+  for (int g = 0; g < m->M.ngeom; g++) {
+    const double* z = &gs[3 * g];
+    double r = 0;
+    switch (gt[g]) {
+      case GEOM_SPHERE: r = z[0]; break;
+      case GEOM_CAPSULE: r = z[0] + z[1]; break;
+      case GEOM_CYLINDER: r = sqrt(z[0] * z[0] + z[1] * z[1]); break;
+      case GEOM_BOX: r = sqrt(z[0] * z[0] + z[1] * z[1] + z[2] * z[2]); break;
+      case GEOM_ELLIPSOID: r = z[0] > z[1] ? (z[0] > z[2] ? z[0] : z[2]) : (z[1] > z[2] ? z[1] : z[2]); break;
+      default: r = 0;
+    }
+    rb[g] = r;
+  }
+}
+
+// Run-time model edit.  The arrays derived on the host (dof_actcoef from actuator_gear /
+// wrap_prm, fric_dof, lim_jnt, neq_active, the LEAN / MID shape flags, geom_rbound) are
+// rebuilt and the whole model is uploaded again, so no stale copy survives an edit; an edit
+// that produces a model the kernels cannot run (validate) is rolled back and rejected.
+// Structural fields (sizes, tree topology, addresses) cannot be edited.
 extern "C" int bp_model_set_field(bp_model* m, const char* name, const void* data,
                                   int64_t nbytes) {
   if (!m || !name || !data) return fail(BP_EINVAL, "null argument");
   auto it = m->fields.find(name);
   if (it == m->fields.end()) return fail(BP_ENOFIELD, std::string("no model field ") + name);
+  static const char* structural[] = {
+      "nq", "nv", "nu", "na", "nbody", "njnt", "ngeom", "nsite", "nM", "npair", "nconmax",
+      "njmax", "nsensor", "nsensordata", "nkey", "ntendon", "neq", "nhfield", "nhfielddata",
+      "nhfpair", "nspatial", "body_parentid", "body_rootid", "body_weldid", "body_jntnum",
+      "body_jntadr", "body_dofnum", "body_dofadr", "jnt_type", "jnt_qposadr", "jnt_dofadr",
+      "jnt_bodyid", "dof_bodyid", "dof_jntid", "dof_parentid", "dof_Madr", "geom_bodyid",
+      "site_bodyid", "pair_geom1", "pair_geom2", "pair_parentchild", "actuator_trntype",
+      "actuator_trnid", "sensor_type", "sensor_objtype", "sensor_objid", "sensor_dim",
+      "sensor_adr", "sensor_needstage", "tendon_adr", "tendon_num", "wrap_objid", "wrap_type",
+      "tendon_Jadr", "eq_type", "eq_obj1id", "eq_obj2id", "geom_dataid", "hfield_nrow",
+      "hfield_ncol", "hfield_adr"};
+  for (const char* sname : structural)
+    if (strcmp(sname, name) == 0)
+      return fail(BP_EINVAL, std::string("model field ") + name +
+                  " is structural and cannot be edited at run time");
   HostField& h = it->second;
   if ((int64_t)h.nbytes() != nbytes) return fail(BP_EINVAL, std::string("size mismatch for ") + name);
+  HostField saved = h;
   memcpy(h.dtype == 0 ? (void*)h.f.data() : (void*)h.i.data(), data, nbytes);
+  std::vector<double> saved_rbound;
+  const bool resize = strcmp(name, "geom_size") == 0 || strcmp(name, "geom_type") == 0;
+  if (resize) { saved_rbound = m->fields["geom_rbound"].f; recompute_rbound(m); }
   cudaSetDevice(m->device);
-  CUDA_OK(cudaMemcpy(m->dev + h.dev_off, data, nbytes, cudaMemcpyHostToDevice));
-  return refresh_scalars(m);
+  int e = refresh_scalars(m);
+  if (e == BP_OK) e = derive(m);
+  if (e == BP_OK) e = validate(m);
+  if (e != BP_OK) {                      // roll back: the model stays what it was
+    std::string msg = g_err;
+    m->fields[name] = saved;
+    if (resize) m->fields["geom_rbound"].f = saved_rbound;
+    refresh_scalars(m); derive(m);
+    return fail(e, msg);
+  }
+  // launches already queued on batch streams may still read the old buffer
+  CUDA_OK(cudaDeviceSynchronize());
+  return upload(m);
 }
 
 extern "C" int bp_model_get_field(bp_model* m, const char* name, void* data, int64_t nbytes) {

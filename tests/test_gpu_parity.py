@@ -32,6 +32,8 @@ def _assert_parity(res):
     bad = {k: v for k, v in cmp.int_mismatch.items() if v}
     assert not bad, "step %d integer mismatches %s\n%s" % (step, bad, cmp.report())
     assert cmp.worst() <= TOL, "step %d\n%s" % (step, cmp.report())
+    # element-wise: |a - b| <= 1e-8 |b| + 1e-10 max(1, max|b|) for every element
+    assert cmp.worst_elem() <= 1.0, "step %d (element-wise)\n%s" % (step, cmp.report())
 
 
 @pytest.mark.parametrize("domain", ["pendulum", "cartpole", "acrobot", "cheetah", "walker",

@@ -1,0 +1,169 @@
+"""Oracle parity AT THE LAUNCH SHAPE THE BENCHMARK TIMES (VERDICT r1 "next" item 1).
+
+The batches are built exactly as bench.py builds them (bench.make_batch: same models, env
+counts, njmax / nconmax, lane widths, seeds and initial states => the same kernel
+instantiation -- LEAN / MID shape, one 896-thread lock-step block per SM -- and the same
+`bp_env_step` entry point), run through the task's settle steps, and then >= 256 sampled
+envs -- always including the first and last env of the first and last block -- are
+replayed through the CPU oracle: the oracle starts from the GPU's (qpos, qvel, act,
+qacc_warmstart, time) at the checkpoint, recomputes mj_step1 on its own (step 0: every
+position / velocity stage field compared), then both sides take the same random actions.
+
+Bars: steps 0, 1 and 10 -- integers exact, fp64 <= 1e-8 array-normalised and the
+element-wise bar of parity_util.elem_err; step 100 (chaotic by then) is reported (median /
+90 % / max of the per-env qpos divergence) and only its median is held to 1e-6.
+"""
+
+import concurrent.futures
+import os
+import sys
+
+import numpy as np
+import pytest
+
+import parity_util as PU
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+  sys.path.insert(0, ROOT)
+
+# fields that only exist after mj_step2 (the oracle has not run one at step 0)
+STEP2_ONLY = ("qacc", "act_dot", "qfrc_actuator", "qfrc_smooth", "qacc_smooth",
+              "qfrc_constraint", "actuator_force", "sensordata", "cacc", "cfrc_int", "cfrc_ext",
+              "efc_force", "efc_state", "solver_iter", "energy", "qacc_warmstart", "warning")
+
+
+def _block_envs(nenv, lanes):
+  """envs per block of the gmem launch (csrc/bp_pipeline.cuh bp_block_threads)."""
+  tpb_max = 896 if lanes >= 8 else 512
+  warps = (nenv * lanes + 31) // 32
+  per_sm = (warps + 147) // 148
+  if per_sm * 32 <= tpb_max:
+    threads = 64 if per_sm < 2 else per_sm * 32
+  else:
+    threads = 448 if tpb_max > 512 else tpb_max
+  return threads // lanes, threads
+
+
+def _sample(nenv, lanes, n, seed):
+  epb, threads = _block_envs(nenv, lanes)
+  last0 = ((nenv - 1) // epb) * epb
+  must = {0, min(epb - 1, nenv - 1), last0, nenv - 1}
+  rng = np.random.RandomState(seed)
+  ids = set(must)
+  for x in rng.permutation(nenv):
+    if len(ids) >= n:
+      break
+    ids.add(int(x))
+  return np.array(sorted(ids)), epb, threads
+
+
+@pytest.mark.parametrize("name,nsample,nsteps", [
+    ("cheetah-run", 256, 100), ("humanoid-run", 256, 100), ("walker-walk", 256, 10),
+    ("quadruped-escape", 256, 10)])
+def test_bench_batch_matches_oracle(name, nsample, nsteps, request):
+  import torch
+  import bench
+  from oracle.oracle_py import Oracle, OracleModel
+  w = bench.WORKLOADS[name]
+  nenv = w["nenv"]
+  tdef, m, model, batch, nsub = bench.make_batch(name, nenv, 0, seed=1000)
+  lanes = batch.lanes
+  assert lanes == w["lanes"]
+  ids, epb, threads = _sample(nenv, lanes, nsample, 5)
+  assert len(ids) >= nsample
+  nu = m.nu
+  dev = "cuda:0"
+  gen = torch.Generator(device=dev); gen.manual_seed(0)
+  settle = w["settle"]
+  total = settle + nsteps
+  # the settle steps as bench.run_gpu takes them (untimed there too)
+  for k in range(settle):
+    c = torch.rand((nenv, nu), generator=gen, device=dev, dtype=torch.float64) * 2 - 1
+    batch.copy_from_device("ctrl", c.data_ptr())
+    batch.step(1 if name.startswith("cheetah") else nsub)
+  batch.sync()
+  # ---- checkpoint: the oracle takes over the sampled envs' state -------------------------
+  state = {f: batch.read(f)[ids] for f in ("qpos", "qvel", "act", "qacc_warmstart", "time")}
+  hfield = batch.read_hfield()[ids] if int(m.nhfielddata) > 0 else None
+  mo = m.copy()
+  mo.arrays["njmax"][:] = w["njmax"]; mo.arrays["nconmax"][:] = w["nconmax"]
+  om = OracleModel(mo)
+  oracles = []
+  for k, e in enumerate(ids):
+    o = Oracle(om)
+    if hfield is not None:
+      o.hfield_data[:] = hfield[k]
+    o.reset()
+    o.qpos[:] = state["qpos"][k]; o.qvel[:] = state["qvel"][k]
+    if m.na:
+      o.act[:] = state["act"][k]
+    o.qacc_warmstart[:] = state["qacc_warmstart"][k]
+    o.time[:] = state["time"][k]
+    o.step1()
+    oracles.append(o)
+  names = (PU.F64_FIELDS + PU.EFC_F64 + PU.EFC_I32 + ["efc_J"] + [n for n, _ in PU.CON_F64] +
+           PU.CON_I32 + PU.INT_SCALARS + (PU.TENDON_F64 if m.ntendon else []))
+  nvp = m.nv | 1
+
+  # efc_force / efc_state are one mj_step2 old after Physics.step() (step2 fills the rows of
+  # the previous state, step1 then rebuilds the row set): rows beyond the previous nefc hold
+  # older history on the GPU and zeros in the freshly started oracle, so those two fields
+  # are compared on the rows the last step2 wrote (prev_nefc, recorded by advance()).
+  prev_nefc = np.zeros(len(ids), dtype=np.int64)
+
+  def compare(skip=()):
+    batch.sync()
+    gpu = {n: batch.read(n)[ids] for n in names}
+    cmp = PU.Comparison()
+    for k, o in enumerate(oracles):
+      PU.compare_env(cmp, m, o, gpu, k, nvp, skip=tuple(skip) + ("efc_force", "efc_state"))
+      if "efc_force" not in skip:
+        n = int(min(prev_nefc[k], int(o.nefc[0])))
+        cmp.add_f64("efc_force", gpu["efc_force"][k, :n], np.array(o.efc_force[:n]))
+        cmp.add_int("efc_state", gpu["efc_state"][k, :n], np.array(o.efc_state[:n]))
+    return cmp, gpu
+
+  obs = torch.empty((nenv, batch.nobs), device=dev, dtype=torch.float64)
+  rew = torch.empty((nenv,), device=dev, dtype=torch.float64)
+  request.addfinalizer(lambda: (batch.free(), model.free()))
+  results = {}
+  results[0], gpu0 = compare(skip=STEP2_ONLY)
+  ncon_mean = float(gpu0["ncon"].mean())
+  pool = concurrent.futures.ThreadPoolExecutor(8)
+
+  def advance(args):
+    k, o, c = args
+    o.ctrl[:] = c
+    for _ in range(nsub):
+      prev_nefc[k] = int(o.nefc[0])
+      o.step()
+
+  for step in range(1, nsteps + 1):
+    c = torch.rand((nenv, nu), generator=gen, device=dev, dtype=torch.float64) * 2 - 1
+    batch.env_step(nsub, c.data_ptr(), obs.data_ptr(), rew.data_ptr())   # the timed call
+    ch = c[torch.as_tensor(ids, device=dev)].cpu().numpy()
+    list(pool.map(advance, [(k, o, ch[k]) for k, o in enumerate(oracles)]))
+    if step in (1, 10):
+      results[step], _ = compare()
+    elif step == nsteps:
+      batch.sync()
+      q = batch.read("qpos")[ids]
+      qo = np.stack([np.array(o.qpos) for o in oracles])
+      div = np.max(np.abs(q - qo), axis=1)
+      # chaotic by now (north_star: reported, not held to a tolerance): one contact that
+      # switches a step apart separates an env by O(0.1); the typical env stays at rounding
+      print("\n%s: qpos divergence GPU vs oracle after %d env-steps (%d sub-steps): median "
+            "%.2e, 90 %% %.2e, max %.2e over %d envs" % (name, nsteps, nsteps * nsub,
+            np.median(div), np.percentile(div, 90), div.max(), len(div)))
+      assert np.median(div) < 1e-6
+  pool.shutdown()
+  for step, cmp in sorted(results.items()):
+    bad = {k: v for k, v in cmp.int_mismatch.items() if v}
+    print("%s step %d: worst %.2e, element-wise %.2e of its bar (%d envs of %d, %d-thread "
+          "blocks of %d envs, mean ncon %.2f)" % (name, step, cmp.worst(), cmp.worst_elem(),
+                                                  len(ids), nenv, threads, epb, ncon_mean))
+    assert not bad, "step %d integer mismatches %s\n%s" % (step, bad, cmp.report())
+    assert cmp.worst() <= 1e-8, "step %d\n%s" % (step, cmp.report())
+    assert cmp.worst_elem() <= 1.0, "step %d (element-wise)\n%s" % (step, cmp.report())

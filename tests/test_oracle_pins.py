@@ -293,7 +293,8 @@ def test_compiler_object_ids_match_reference_expectations():
   """core_test.py:226-235 testNamesIds: ids MuJoCo's compiler assigns in the reference's
   own test humanoid (body / joint ordering of the MJCF compiler)."""
   from dm_control_b200 import mjcf_compiler as C
-  m = C.compile_xml(open(_REF_HUMANOID).read())
+  # structure only (the asset asks for solver="PGS"): no simulation here
+  m = C.compile_xml(open(_REF_HUMANOID).read(), validate=False)
   assert m.name2id("right_foot", "body") == 6
   assert m.name2id("left_knee", "joint") == 11
   assert m.names["body"][6] == "right_foot" and m.names["joint"][11] == "left_knee"

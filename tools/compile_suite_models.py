@@ -129,7 +129,10 @@ def swimmers():
 def main():
   os.makedirs(OUT, exist_ok=True)
   for d in DOMAINS:
-    m = C.compile_file(os.path.join(SUITE, d + ".xml"))
+    # humanoid_CMU: the two hand ellipsoids are the one live pair without a narrowphase
+    # (ellipsoid - ellipsoid); it is dropped explicitly (DESIGN.md §2 departures)
+    m = C.compile_file(os.path.join(SUITE, d + ".xml"),
+                       unsupported_pairs="drop" if d == "humanoid_CMU" else "error")
     path = os.path.join(OUT, d + ".npz")
     m.save(path)
     print(d, "nq", m.nq, "nv", m.nv, "nbody", m.nbody, "->", os.path.getsize(path), "B")
