@@ -81,6 +81,7 @@ def test_bench_batch_matches_oracle(name, nsample, nsteps, request):
   # the settle steps as bench.run_gpu takes them (untimed there too)
   for k in range(settle):
     c = torch.rand((nenv, nu), generator=gen, device=dev, dtype=torch.float64) * 2 - 1
+    torch.cuda.synchronize()      # the batch runs on its own (non-blocking) stream
     batch.copy_from_device("ctrl", c.data_ptr())
     batch.step(1 if name.startswith("cheetah") else nsub)
   batch.sync()
@@ -142,6 +143,7 @@ def test_bench_batch_matches_oracle(name, nsample, nsteps, request):
 
   for step in range(1, nsteps + 1):
     c = torch.rand((nenv, nu), generator=gen, device=dev, dtype=torch.float64) * 2 - 1
+    torch.cuda.synchronize()
     batch.env_step(nsub, c.data_ptr(), obs.data_ptr(), rew.data_ptr())   # the timed call
     ch = c[torch.as_tensor(ids, device=dev)].cpu().numpy()
     list(pool.map(advance, [(k, o, ch[k]) for k, o in enumerate(oracles)]))
