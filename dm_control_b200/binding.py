@@ -221,6 +221,8 @@ class Batch:
 
   def write(self, name, value, env0=0):
     _, cnt, dt = self.fields[name]
+    if cnt == 0:
+      return
     a = np.ascontiguousarray(value, dtype=dt)
     if a.ndim == 1:
       a = np.ascontiguousarray(np.broadcast_to(a, (self.nenv - env0, cnt)))

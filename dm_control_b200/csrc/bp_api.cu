@@ -233,7 +233,7 @@ static int derive(bp_model* m) {
 // physics (the reference surfaces engine errors, wrapper/core_test.py:97-103).
 //   pairs: the narrowphase table of csrc/bp_collide.cuh / bp_hfield.cuh
 #ifndef BP_HAVE_BOX_PAIRS
-#define BP_HAVE_BOX_PAIRS 0      // sphere / capsule / box against box
+#define BP_HAVE_BOX_PAIRS 1      // sphere / capsule / box against box
 #endif
 #ifndef BP_HAVE_PGS_CG
 #define BP_HAVE_PGS_CG 0         // opt_solver 0 (PGS) and 1 (CG)

@@ -300,6 +300,283 @@ static __device__ __noinline__ int bp_collide_ellipsoid(int t1, const double* p1
   return 0;
 }
 
+// ---- box narrowphase: sphere / capsule / box against a box (FULL shape only) ------------
+// [MJ-doc] MuJoCo's mjc_SphereBox / mjc_CapsuleBox / mjc_BoxBox are not in the reference;
+// the geometry is restated from first principles (oracle/mjstep_oracle.c holds the same
+// restatement):
+//   sphere - box   closest point of the solid box; a centre inside leaves through the
+//                  nearest face
+//   capsule - box  squared distance from the segment to the box is convex along the segment:
+//                  the ends of its minimiser set (bisection on the derivative's sign) and the
+//                  segment ends are candidate sphere centres; the deepest hit and the hit
+//                  farthest from it along the axis are kept (<= 2, ascending along the axis)
+//   box - box      separating-axis test (15 axes, faces preferred); face case: incident face
+//                  clipped against the reference face (<= 8, clipping order); edge case:
+//                  closest points of the two edges (1)
+static __device__ __noinline__ int col_sphere_box(const double* c, double r, const double* pb,
+                                                  const double* Rb, const double* h,
+                                                  double margin, RawCon& o) {
+  double dif[3] = {c[0] - pb[0], c[1] - pb[1], c[2] - pb[2]}, d[3], del[3], nl[3], pl[3];
+  matT_vec3(d, Rb, dif);
+  for (int k = 0; k < 3; k++) {
+    double q = d[k] < -h[k] ? -h[k] : (d[k] > h[k] ? h[k] : d[k]);
+    del[k] = d[k] - q;
+  }
+  double dd = norm3(del), dist;
+  if (dd > 1e-12) {
+    for (int k = 0; k < 3; k++) nl[k] = -del[k] / dd;
+    dist = dd - r;
+  } else {
+    int best = 0;
+    double depth = h[0] - fabs(d[0]);
+    for (int k = 1; k < 3; k++) {
+      double dk = h[k] - fabs(d[k]);
+      if (dk < depth) { depth = dk; best = k; }
+    }
+    for (int k = 0; k < 3; k++) nl[k] = k == best ? (d[k] >= 0 ? -1.0 : 1.0) : 0.0;
+    dist = -depth - r;
+  }
+  if (dist > margin) return 0;
+  for (int k = 0; k < 3; k++) pl[k] = d[k] + nl[k] * (r + 0.5 * dist);
+  o.dist = dist;
+  mat_vec3(o.pos, Rb, pl);
+  for (int k = 0; k < 3; k++) { o.pos[k] += pb[k]; o.hint[k] = 0; }
+  mat_vec3(o.n, Rb, nl);
+  return 1;
+}
+
+__device__ __forceinline__ double capbox_dg(const double* c0, const double* u, const double* h,
+                                            double t) {
+  double s = 0;
+  for (int k = 0; k < 3; k++) {
+    double v = c0[k] + t * u[k];
+    double e = v > h[k] ? v - h[k] : (v < -h[k] ? v + h[k] : 0.0);
+    s += e * u[k];
+  }
+  return s;
+}
+__device__ __forceinline__ double capbox_g(const double* c0, const double* u, const double* h,
+                                           double t) {
+  double s = 0;
+  for (int k = 0; k < 3; k++) {
+    double v = c0[k] + t * u[k];
+    double e = v > h[k] ? v - h[k] : (v < -h[k] ? v + h[k] : 0.0);
+    s += e * e;
+  }
+  return s;
+}
+
+static __device__ __noinline__ int col_capsule_box(const double* p1, const double* a1, double r,
+                                                   double l, const double* pb, const double* Rb,
+                                                   const double* h, double margin, RawCon* out) {
+  double dif[3] = {p1[0] - pb[0], p1[1] - pb[1], p1[2] - pb[2]}, c0[3], u[3];
+  matT_vec3(c0, Rb, dif);
+  matT_vec3(u, Rb, a1);
+  double tlo, thi;
+  if (capbox_dg(c0, u, h, -l) >= 0) tlo = -l;
+  else if (capbox_dg(c0, u, h, l) < 0) tlo = l;
+  else {
+    double lo = -l, hi = l;
+#pragma unroll 1
+    for (int it = 0; it < 60; it++) {
+      double t = 0.5 * (lo + hi);
+      if (capbox_dg(c0, u, h, t) >= 0) hi = t; else lo = t;
+    }
+    tlo = hi;
+  }
+  if (capbox_dg(c0, u, h, -l) > 0) thi = -l;
+  else if (!(capbox_dg(c0, u, h, l) > 0)) thi = l;
+  else {
+    double lo = -l, hi = l;
+#pragma unroll 1
+    for (int it = 0; it < 60; it++) {
+      double t = 0.5 * (lo + hi);
+      if (capbox_dg(c0, u, h, t) > 0) hi = t; else lo = t;
+    }
+    thi = lo;
+  }
+  double cand[4] = {-l, l, tlo, thi};
+  int nc = 4;
+  if (!(capbox_g(c0, u, h, tlo) > 1e-24)) { cand[2] = 0.5 * (tlo + thi); nc = 3; }
+  RawCon hit[4];
+  double th[4];
+  int nh = 0;
+#pragma unroll 1
+  for (int i = 0; i < nc; i++) {
+    double q[3] = {p1[0] + cand[i] * a1[0], p1[1] + cand[i] * a1[1], p1[2] + cand[i] * a1[2]};
+    if (col_sphere_box(q, r, pb, Rb, h, margin, hit[nh])) {
+      for (int k = 0; k < 3; k++) hit[nh].hint[k] = a1[k];
+      th[nh++] = cand[i];
+    }
+  }
+  if (!nh) return 0;
+  int first = 0, second = -1;
+  for (int i = 1; i < nh; i++) if (hit[i].dist < hit[first].dist) first = i;
+  double sep = 1e-6 * (l + r);
+  for (int i = 0; i < nh; i++) {
+    double si = fabs(th[i] - th[first]);
+    if (i != first && si > sep) { sep = si; second = i; }
+  }
+  if (second < 0) { out[0] = hit[first]; return 1; }
+  if (th[first] < th[second]) { out[0] = hit[first]; out[1] = hit[second]; }
+  else { out[0] = hit[second]; out[1] = hit[first]; }
+  return 2;
+}
+
+// clips the polygon (x, y, z)[n] against sgn * coord <= lim (coord = x or y)
+static __device__ __noinline__ int boxbox_clip(const double* xi, const double* yi,
+                                               const double* zi, int n, int usey, double sgn,
+                                               double lim, double* xo, double* yo, double* zo) {
+  int m = 0;
+#pragma unroll 1
+  for (int i = 0; i < n; i++) {
+    int j = (i + 1) % n;
+    double ci = sgn * (usey ? yi[i] : xi[i]) - lim, cj = sgn * (usey ? yi[j] : xi[j]) - lim;
+    if (ci <= 0) { xo[m] = xi[i]; yo[m] = yi[i]; zo[m] = zi[i]; m++; }
+    if ((ci <= 0) != (cj <= 0)) {
+      double w = ci / (ci - cj);
+      xo[m] = xi[i] + w * (xi[j] - xi[i]);
+      yo[m] = yi[i] + w * (yi[j] - yi[i]);
+      zo[m] = zi[i] + w * (zi[j] - zi[i]);
+      m++;
+    }
+  }
+  return m;
+}
+
+__device__ __forceinline__ void col_axis(const double* R, int col, double* ax) {
+  ax[0] = R[col]; ax[1] = R[3 + col]; ax[2] = R[6 + col];
+}
+
+static __device__ __noinline__ int col_box_box(const double* pa, const double* Ra,
+                                               const double* ha, const double* pb,
+                                               const double* Rb, const double* hb, double margin,
+                                               RawCon* out) {
+  double R[9], Q[9], t[3], dw[3] = {pb[0] - pa[0], pb[1] - pa[1], pb[2] - pa[2]};
+  matT_vec3(t, Ra, dw);
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 3; j++) {
+      R[3 * i + j] = Ra[i] * Rb[j] + Ra[3 + i] * Rb[3 + j] + Ra[6 + i] * Rb[6 + j];
+      Q[3 * i + j] = fabs(R[3 * i + j]);
+    }
+  double best = -1e300;
+  int code = -1;
+  for (int i = 0; i < 3; i++) {
+    double s = fabs(t[i]) - (ha[i] + hb[0] * Q[3 * i] + hb[1] * Q[3 * i + 1] + hb[2] * Q[3 * i + 2]);
+    if (s > margin) return 0;
+    if (s > best) { best = s; code = i; }
+  }
+  for (int j = 0; j < 3; j++) {
+    double tb = t[0] * R[j] + t[1] * R[3 + j] + t[2] * R[6 + j];
+    double s = fabs(tb) - (hb[j] + ha[0] * Q[j] + ha[1] * Q[3 + j] + ha[2] * Q[6 + j]);
+    if (s > margin) return 0;
+    if (s > best) { best = s; code = 3 + j; }
+  }
+#pragma unroll 1
+  for (int i = 0; i < 3; i++)
+#pragma unroll 1
+    for (int j = 0; j < 3; j++) {
+      int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+      double len2 = 1.0 - R[3 * i + j] * R[3 * i + j];
+      if (len2 < 1e-12) continue;
+      double len = sqrt(len2);
+      double tl = fabs(t[i2] * R[3 * i1 + j] - t[i1] * R[3 * i2 + j]);
+      double ra = ha[i1] * Q[3 * i2 + j] + ha[i2] * Q[3 * i1 + j];
+      double rb = hb[j1] * Q[3 * i + j2] + hb[j2] * Q[3 * i + j1];
+      double s = (tl - ra - rb) / len;
+      if (s > margin) return 0;
+      if (s > best + 0.05 * fabs(best) + 1e-10) { best = s; code = 6 + 3 * i + j; }
+    }
+  if (code < 6) {
+    const bool refA = code < 3;
+    const int ai = refA ? code : code - 3;
+    const double *pr = refA ? pa : pb, *Rr = refA ? Ra : Rb, *hr = refA ? ha : hb;
+    const double *pi = refA ? pb : pa, *Ri = refA ? Rb : Ra, *hi = refA ? hb : ha;
+    double ax[3], nref[3], dc[3] = {pi[0] - pr[0], pi[1] - pr[1], pi[2] - pr[2]};
+    col_axis(Rr, ai, ax);
+    double sg = dot3(dc, ax) > 0 ? 1.0 : -1.0;
+    for (int k = 0; k < 3; k++) nref[k] = sg * ax[k];
+    int kf = 0;
+    double bestdot = -1;
+    for (int k = 0; k < 3; k++) {
+      double ak[3];
+      col_axis(Ri, k, ak);
+      double dk = fabs(dot3(nref, ak));
+      if (dk > bestdot) { bestdot = dk; kf = k; }
+    }
+    double af[3], a1[3], a2[3], fc[3];
+    const int k1 = (kf + 1) % 3, k2 = (kf + 2) % 3, r1 = (ai + 1) % 3, r2 = (ai + 2) % 3;
+    col_axis(Ri, kf, af); col_axis(Ri, k1, a1); col_axis(Ri, k2, a2);
+    double sf = dot3(nref, af) > 0 ? -1.0 : 1.0;
+    for (int k = 0; k < 3; k++) fc[k] = pi[k] + sf * hi[kf] * af[k] - pr[k];
+    double t1[3], t2[3];
+    col_axis(Rr, r1, t1); col_axis(Rr, r2, t2);
+    double x[2][9], y[2][9], z[2][9];
+#pragma unroll 1
+    for (int v = 0; v < 4; v++) {
+      const double S1 = (v == 0 || v == 3) ? 1.0 : -1.0, S2 = v < 2 ? 1.0 : -1.0;
+      double w[3];
+      for (int k = 0; k < 3; k++) w[k] = fc[k] + S1 * hi[k1] * a1[k] + S2 * hi[k2] * a2[k];
+      x[0][v] = dot3(w, t1); y[0][v] = dot3(w, t2); z[0][v] = dot3(w, nref) - hr[ai];
+    }
+    int n = 4;
+    n = boxbox_clip(x[0], y[0], z[0], n, 0, 1.0, hr[r1], x[1], y[1], z[1]);
+    n = boxbox_clip(x[1], y[1], z[1], n, 0, -1.0, hr[r1], x[0], y[0], z[0]);
+    n = boxbox_clip(x[0], y[0], z[0], n, 1, 1.0, hr[r2], x[1], y[1], z[1]);
+    n = boxbox_clip(x[1], y[1], z[1], n, 1, -1.0, hr[r2], x[0], y[0], z[0]);
+    int cnt = 0;
+#pragma unroll 1
+    for (int v = 0; v < n && cnt < 8; v++) {
+      if (z[0][v] > margin) continue;
+      out[cnt].dist = z[0][v];
+      for (int k = 0; k < 3; k++) {
+        out[cnt].pos[k] = pr[k] + x[0][v] * t1[k] + y[0][v] * t2[k] +
+                          (hr[ai] + 0.5 * z[0][v]) * nref[k];
+        out[cnt].n[k] = refA ? nref[k] : -nref[k];
+        out[cnt].hint[k] = 0;
+      }
+      cnt++;
+    }
+    return cnt;
+  }
+  const int i = (code - 6) / 3, j = (code - 6) % 3;
+  double ua[3], ub[3], L[3];
+  col_axis(Ra, i, ua); col_axis(Rb, j, ub);
+  cross3(L, ua, ub);
+  normalize3(L);
+  if (dot3(L, dw) < 0) { L[0] = -L[0]; L[1] = -L[1]; L[2] = -L[2]; }
+  double ea[3] = {pa[0], pa[1], pa[2]}, eb[3] = {pb[0], pb[1], pb[2]};
+  for (int k = 0; k < 3; k++) {
+    double ak[3], bk[3];
+    if (k != i) {
+      col_axis(Ra, k, ak);
+      double sgk = dot3(L, ak) > 0 ? 1.0 : -1.0;
+      for (int q = 0; q < 3; q++) ea[q] += sgk * ha[k] * ak[q];
+    }
+    if (k != j) {
+      col_axis(Rb, k, bk);
+      double sgk = dot3(L, bk) > 0 ? -1.0 : 1.0;
+      for (int q = 0; q < 3; q++) eb[q] += sgk * hb[k] * bk[q];
+    }
+  }
+  double d[3] = {eb[0] - ea[0], eb[1] - ea[1], eb[2] - ea[2]};
+  double uaub = dot3(ua, ub), q1 = dot3(ua, d), q2 = -dot3(ub, d), den = 1.0 - uaub * uaub;
+  double al = (q1 + uaub * q2) / den, be = (uaub * q1 + q2) / den;
+  al = clampd(al, -ha[i], ha[i]);
+  be = clampd(be, -hb[j], hb[j]);
+  double ca[3], cb[3], sepv[3];
+  for (int k = 0; k < 3; k++) {
+    ca[k] = ea[k] + al * ua[k]; cb[k] = eb[k] + be * ub[k]; sepv[k] = cb[k] - ca[k];
+  }
+  double dist = dot3(sepv, L);
+  if (dist > margin) return 0;
+  out[0].dist = dist;
+  for (int k = 0; k < 3; k++) {
+    out[0].pos[k] = 0.5 * (ca[k] + cb[k]); out[0].n[k] = L[k]; out[0].hint[k] = 0;
+  }
+  return 1;
+}
+
 // Narrowphase of ordered pair (type1 <= type2) on geom poses already copied to
 // registers (p = centre, z = local z axis, R2 = full frame of geom 2 for boxes).
 // Returns the number of raw contacts written to out[0..3].
@@ -308,7 +585,16 @@ static __device__ __noinline__ int bp_collide_prims(int t1, int t2, const double
                                                     const double* z1, const double* s1,
                                                     const double* p2, const double* z2,
                                                     const double* R2, const double* s2,
-                                                    double margin, RawCon* out) {
+                                                    double margin, RawCon* out,
+                                                    const double* R1) {
+  if constexpr (SHAPE == 0) {
+    if (t2 == GEOM_BOX && t1 != GEOM_PLANE) {
+      if (t1 == GEOM_SPHERE) return col_sphere_box(p1, s1[0], p2, R2, s2, margin, out[0]);
+      if (t1 == GEOM_CAPSULE) return col_capsule_box(p1, z1, s1[0], s1[1], p2, R2, s2, margin, out);
+      if (t1 == GEOM_BOX) return col_box_box(p1, R1, s1, p2, R2, s2, margin, out);
+      return 0;
+    }
+  }
   if constexpr (SHAPE != 1) {
     if (t2 == GEOM_CYLINDER) return bp_collide_cylinder(t1, p1, z1, s1, p2, R2, s2, margin, out);
     if (t2 == GEOM_ELLIPSOID) return bp_collide_ellipsoid(t1, p1, z1, s1, p2, R2, s2, margin, out);
@@ -519,7 +805,7 @@ BP_STAGE void bp_collision(const C& c) {
   for (int p0 = 0; p0 < nprim; p0 += C::G) {
     int p = p0 + c.lane, n = 0, g1 = 0, g2 = 0;
     double margin = 0, gap = 0;
-    RawCon raw[4];
+    RawCon raw[C::FULL ? 8 : 4];           // box - box: up to 8
     if (p < nprim && !(filterparent && m.pair_parentchild[p])) {
       g1 = m.pair_geom1[p]; g2 = m.pair_geom2[p];
       margin = fmax(m.geom_margin[g1], m.geom_margin[g2]);
@@ -538,14 +824,16 @@ BP_STAGE void bp_collision(const C& c) {
         keep = !(dot3(dif, dif) > bound * bound);
       }
       if (keep) {
-        double R2[9], z2[3], s1[3], s2[3];
+        double R2[9], R1[C::FULL ? 9 : 1], z2[3], s1[3], s2[3];
         if constexpr (!C::LEAN)
           for (int k = 0; k < 9; k++) R2[k] = gmat[9 * g2 + k];
+        if constexpr (C::FULL)
+          if (t1 == GEOM_BOX) for (int k = 0; k < 9; k++) R1[k] = gmat[9 * g1 + k];
         for (int k = 0; k < 3; k++) {
           z2[k] = gmat[9 * g2 + 3 * k + 2];
           s1[k] = m.geom_size[3 * g1 + k]; s2[k] = m.geom_size[3 * g2 + k];
         }
-        n = bp_collide_prims<(C::FULL ? 0 : C::LEAN ? 1 : 2)>(t1, t2, p1, z1, s1, p2, z2, R2, s2, margin, raw);
+        n = bp_collide_prims<(C::FULL ? 0 : C::LEAN ? 1 : 2)>(t1, t2, p1, z1, s1, p2, z2, R2, s2, margin, raw, R1);
       }
     }
     // exclusive prefix sum of n over the group -> slots in pair order

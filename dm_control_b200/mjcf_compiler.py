@@ -505,7 +505,7 @@ _SENSOR_SPEC = {
 
 
 # What the kernels (and the oracle) implement; kept in step with csrc/bp_api.cu validate().
-HAVE_BOX_PAIRS = False       # sphere / capsule / box against box
+HAVE_BOX_PAIRS = True        # sphere / capsule / box against box
 HAVE_PGS_CG = False          # solver="PGS" / "CG"
 
 
@@ -1112,7 +1112,7 @@ def _emit_pairs(m, root=None):
     elif ta == M.GEOM_HFIELD:
       n = 2
     elif tb == M.GEOM_BOX:
-      n = 8 if ta == M.GEOM_BOX else 1
+      n = 8 if ta == M.GEOM_BOX else (2 if ta == M.GEOM_CAPSULE else 1)
     else:
       n = 1
     dim = max(m.geom_condim[a], m.geom_condim[b])

@@ -179,7 +179,7 @@ def compare_env(cmp, m, oracle, gpu, e, nvp, skip=()):
 
 def run_parity(domain, nenv=32, nsteps=3, seed=0, njmax=0, nconmax=0, check_steps=None,
                vel_scale=1.0, spread=1.0, mutate=None, lanes=0, env_model=None,
-               iter_slack=False, state_hook=None):
+               iter_slack=False, state_hook=None, flat_model=None):
   """forward() then `nsteps` Physics.step() on both sides; returns (Comparison per
   phase, stats).  The GPU side goes through the C ABI (dm_control_b200.binding).
 
@@ -190,7 +190,7 @@ def run_parity(domain, nenv=32, nsteps=3, seed=0, njmax=0, nconmax=0, check_step
   solver_iter first differs and collected in `cmp.loose`; stats["loose"] counts them."""
   from dm_control_b200 import binding
   from oracle.oracle_py import Oracle, OracleModel
-  m = load_model(domain)
+  m = flat_model.copy() if flat_model is not None else load_model(domain)
   if mutate:
     mutate(m)
   qpos, qvel, ctrl = random_states(m, nenv, seed, vel_scale, spread)

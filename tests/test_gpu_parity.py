@@ -327,3 +327,28 @@ def test_overflow_raises_reference_warnings():
   assert w[:, 1].sum() > 0 and w[:, 2].sum() > 0   # CONTACTFULL, CNSTRFULL
   assert (b.read("ncon") <= 2).all() and (b.read("nefc") <= 6).all()
   b.free(); model.free()
+
+
+@pytest.mark.parametrize("lanes", [32, 8, 4, 1])
+def test_box_narrowphase_matches_oracle(lanes):
+  """sphere / capsule / box against box (csrc/bp_collide.cuh col_sphere_box,
+  col_capsule_box, col_box_box): a pile of free boxes, a sphere and two capsules dropped on
+  each other from random poses; every field after 0, 1, 2 and 10 steps."""
+  from box_models import BOX_PILE
+  from dm_control_b200 import mjcf_compiler as C
+  m = C.compile_xml(BOX_PILE)
+
+  def hook(mm, qpos, qvel, ctrl):       # bring the bodies together so that they touch
+    rng = np.random.RandomState(3)
+    n = qpos.shape[0]
+    for b in range(6):
+      qpos[:, 7 * b:7 * b + 2] = rng.uniform(-.12, .12, (n, 2))
+      qpos[:, 7 * b + 2] = 0.1 + 0.14 * b + rng.uniform(-.03, .03, n)
+    qpos[: n // 3, 3:7] = [1, 0, 0, 0]              # a third start with b1 flat on the floor
+    qpos[: n // 3, 2] = 0.079
+    qvel *= 0.3
+
+  res, stats = PU.run_parity("box_pile", nenv=48, nsteps=10, seed=8, check_steps=[0, 1, 2, 10],
+                             lanes=lanes, njmax=300, nconmax=64, flat_model=m, state_hook=hook)
+  _assert_parity(res)
+  assert max(stats["ncon"]) > 6, stats

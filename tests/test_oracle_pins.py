@@ -335,3 +335,31 @@ def test_lqr_riccati_cost(n_bodies, n_actuators):
     reward = 1 - (0.5 * o.qpos.dot(o.qpos) + 0.5 * o.ctrl.dot(o.ctrl) * lqr.CONTROL_COST_COEF)
   np.testing.assert_allclose(.5 * x0.dot(p).dot(x0), total_loss, rtol=tolerance)
 
+
+
+def test_box_stack_at_rest_carries_the_weight_above_it():
+  """Known answer for the box narrowphase (sphere / capsule / box against box), in the
+  style of core_test.py:461-484: at rest the summed normal force of every support equals
+  the weight it carries -- floor: b1 + b2 + sphere, b1 <- b2 + sphere, b2 <- sphere, and a
+  capsule lying on a box rests on two contacts."""
+  from box_models import BOX_STACK
+  m = C.compile_xml(BOX_STACK)
+  o = Oracle(m)
+  for _ in range(1500):
+    o.mj_step()
+  o.forward()
+  ncon = int(o.ncon[0])
+  g1, g2 = o.contact_geom1[:ncon], o.contact_geom2[:ncon]
+  adr, dim = o.contact_efc_address[:ncon], o.contact_dim[:ncon]
+
+  def support(a, b):
+    idx = [i for i in range(ncon) if (g1[i], g2[i]) == (a, b)]
+    return len(idx), sum(o.efc_force[adr[i]:adr[i] + 2 * (dim[i] - 1)].sum() for i in idx)
+
+  g = 9.81
+  assert support(0, 1) == (4, pytest.approx((2.5 + 1.5 + 0.5) * g, abs=1e-5))    # floor - b1
+  assert support(1, 2) == (4, pytest.approx((1.5 + 0.5) * g, abs=1e-5))          # b1 - b2
+  assert support(3, 2) == (1, pytest.approx(0.5 * g, abs=1e-5))                  # sphere - b2
+  assert support(0, 4) == (4, pytest.approx((1.0 + 0.3) * g, abs=1e-5))          # floor - c
+  assert support(5, 4) == (2, pytest.approx(0.3 * g, abs=1e-5))                  # capsule - c
+  assert ncon == 15
