@@ -236,7 +236,7 @@ static int derive(bp_model* m) {
 #define BP_HAVE_BOX_PAIRS 1      // sphere / capsule / box against box
 #endif
 #ifndef BP_HAVE_PGS_CG
-#define BP_HAVE_PGS_CG 0         // opt_solver 0 (PGS) and 1 (CG)
+#define BP_HAVE_PGS_CG 1         // opt_solver 0 (PGS) and 1 (CG)
 #endif
 static bool pair_supported(int t1, int t2) {
   if (t1 > t2) { int t = t1; t1 = t2; t2 = t; }
@@ -268,8 +268,8 @@ static int validate(bp_model* m) {
     return fail(BP_EINVAL, "opt_solver must be 0 (PGS), 1 (CG) or 2 (Newton)");
   if (!BP_HAVE_PGS_CG && M.opt_solver != 2)
     return fail(BP_EINVAL, "only the Newton solver is implemented (opt_solver = PGS / CG)");
-  if (M.opt_solver != 2 && M.opt_cone != 0)
-    return fail(BP_EINVAL, "the PGS and CG solvers are implemented for pyramidal cones only");
+  if (M.opt_solver == 0 && M.opt_cone != 0)
+    return fail(BP_EINVAL, "the PGS solver is implemented for pyramidal cones only");
   auto ns = m->fields.find("opt_noslip_iterations");
   if (ns != m->fields.end() && !ns->second.i.empty() && ns->second.i[0] > 0)
     return fail(BP_EINVAL, "noslip_iterations > 0 is not supported (the noslip post-solver is "
@@ -410,7 +410,7 @@ extern "C" int bp_model_set_field(bp_model* m, const char* name, const void* dat
   static const char* structural[] = {
       "nq", "nv", "nu", "na", "nbody", "njnt", "ngeom", "nsite", "nM", "npair", "nconmax",
       "njmax", "nsensor", "nsensordata", "nkey", "ntendon", "neq", "nhfield", "nhfielddata",
-      "nhfpair", "nspatial", "body_parentid", "body_rootid", "body_weldid", "body_jntnum",
+      "nhfpair", "nspatial", "opt_solver", "body_parentid", "body_rootid", "body_weldid", "body_jntnum",
       "body_jntadr", "body_dofnum", "body_dofadr", "jnt_type", "jnt_qposadr", "jnt_dofadr",
       "jnt_bodyid", "dof_bodyid", "dof_jntid", "dof_parentid", "dof_Madr", "geom_bodyid",
       "site_bodyid", "pair_geom1", "pair_geom2", "pair_parentchild", "actuator_trntype",
@@ -784,7 +784,7 @@ static int launch(bp_batch* b, int mode, int nsub, int disable_actuation,
   int e;
   const BpModel& M = b->model->M;
   // BPHYS_NO_LEAN=1 / BPHYS_SPLIT=1 keep the full instantiation
-  const bool plain = M.opt_cone == 0 && M.opt_density == 0 && M.opt_viscosity == 0 &&
+  const bool plain = M.opt_solver == 2 && M.opt_cone == 0 && M.opt_density == 0 && M.opt_viscosity == 0 &&
                      !P.env_geom_pos && !P.env_site_pos && !P.env_body_pos && !P.env_body_quat &&
                      !getenv("BPHYS_NO_LEAN") && !getenv("BPHYS_SPLIT");
   if (plain && M.lean_static && (b->lanes == 4 || b->lanes == 8 || b->lanes == 16)) {

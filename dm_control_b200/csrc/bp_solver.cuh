@@ -663,11 +663,139 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, int ntenlim,
   bp_chol_solve(c, H, Hdinv, Mgrad, bp_chol_fused<C>(nv));
 }
 
+// CG [MJ-doc A.9]: the primal gradient preconditioned by the sparse factor of M
+BP_STAGE void bp_cg_gradient(const C& c) {
+  const BpModel& m = c.P.m;
+  auto Mg = HOT(s_Mgrad, m.ntri + 2 * m.nv), grad = DF(s_grad);
+  for (int i = c.lane; i < m.nv; i += C::G) Mg[i] = grad[i];
+  SYNC();
+  bp_solve_sparse(c, DF(qLD), DF(qLDiagInv), Mg);
+}
+
+// PGS [MJ-doc A.9]: dual projected Gauss-Seidel on 0.5 f^T AR f + f^T b with
+// AR = J M^-1 J^T + diag(R), b = J qacc_smooth - aref; rows in order, equality rows free,
+// friction-loss rows clamped to +-frictionloss, limit / contact rows to f >= 0 (pyramidal
+// cones only).  The warm start maps qacc_warmstart to forces through the primal update and is
+// kept when its dual cost is negative (f = 0 costs 0).  Rows are sequential by nature; the
+// row dot products run on the lanes.  oracle/mjstep_oracle.c pgs_solve is the restatement
+// this is held to.
+BP_STAGE void bp_solver_pgs(const C& c) {
+  const BpModel& m = c.P.m;
+  const int nv = m.nv, nvp = m.nvp, nefc = IF(nefc)[0];
+  auto qacc = DF(qacc), warm = DF(qacc_warmstart), as = DF(qacc_smooth);
+  if (nefc == 0) {
+    for (int i = c.lane; i < nv; i += C::G) {
+      double a = as[i];
+      qacc[i] = a; warm[i] = a; DF(qfrc_constraint)[i] = 0;
+    }
+    if (c.lane == 0) IF(solver_iter)[0] = 0;
+    SYNC();
+    return;
+  }
+  auto AR = DF(s_AR), b = DF(s_jv), x = DF(s_grad), f = DF(efc_force), J = DF(efc_J);
+  auto R = DF(efc_R), jar = DF(s_jar);
+  auto type = IF(efc_type), state = IF(efc_state);
+#pragma unroll 1
+  for (int i = 0; i < nefc; i++) {
+    for (int k = c.lane; k < nv; k += C::G) x[k] = J[i * nvp + k];
+    SYNC();
+    bp_solve_sparse(c, DF(qLD), DF(qLDiagInv), x);
+#pragma unroll 1
+    for (int j = c.lane; j < nefc; j += C::G) {
+      double s = 0;
+      for (int k = 0; k < nv; k++) s += J[j * nvp + k] * x[k];
+      AR[i * nefc + j] = j == i ? s + R[i] : s;
+    }
+    SYNC();
+  }
+  bp_mul_j(c, b, as, DF(efc_aref), nefc);
+  bool use_warm = false;
+  if (!(m.opt_disableflags & DSBL_WARMSTART)) {
+    for (int i = c.lane; i < nv; i += C::G) qacc[i] = warm[i];
+    SYNC();
+    bp_mul_j(c, jar, qacc, DF(efc_aref), nefc);
+    bool chg;
+    bp_update_constraint(c, jar, nefc, true, &chg);
+    double cost = 0;
+#pragma unroll 1
+    for (int i = c.lane; i < nefc; i += C::G) {
+      double s = 0;
+      for (int j = 0; j < nefc; j++) s += AR[i * nefc + j] * f[j];
+      cost += f[i] * (0.5 * s + b[i]);
+    }
+    use_warm = group_sum(c, cost) < 0;
+  }
+  if (!use_warm) {
+    for (int i = c.lane; i < nefc; i += C::G) f[i] = 0;
+  }
+  SYNC();
+  const double scale = 1.0 / (m.stat_meaninertia * (nv > 1 ? nv : 1));
+  int iter = 0;
+  double improvement = 0;
+#pragma unroll 1
+  while (iter < m.opt_iterations) {
+    improvement = 0;
+#pragma unroll 1
+    for (int i = 0; i < nefc; i++) {
+      double res = 0;
+      for (int j = c.lane; j < nefc; j += C::G) res += AR[i * nefc + j] * f[j];
+      res = b[i] + group_sum(c, res);
+      const double aii = AR[i * nefc + i], old = f[i];
+      double fn = old - res / aii;
+      const int t = type[i];
+      if (t == CN_FRICTION_DOF || t == CN_FRICTION_TENDON) {
+        const double fl = DF(efc_frictionloss)[i];
+        fn = fn < -fl ? -fl : (fn > fl ? fl : fn);
+      } else if (t != CN_EQUALITY) {
+        if (fn < 0) fn = 0;
+      }
+      const double delta = fn - old;
+      SYNC();                       // every lane has read f[i]
+      if (c.lane == 0) f[i] = fn;
+      SYNC();
+      improvement -= 0.5 * delta * delta * aii + delta * res;
+    }
+    improvement *= scale;
+    iter++;
+    if (improvement < m.opt_tolerance) break;
+  }
+  for (int i = c.lane; i < nefc; i += C::G) {
+    const int t = type[i];
+    const double fi = f[i];
+    int st;
+    if (t == CN_EQUALITY) st = ST_QUADRATIC;
+    else if (t == CN_FRICTION_DOF || t == CN_FRICTION_TENDON) {
+      const double fl = DF(efc_frictionloss)[i];
+      st = fi >= fl ? ST_LINEARNEG : (fi <= -fl ? ST_LINEARPOS : ST_QUADRATIC);
+    } else st = fi > 0 ? ST_QUADRATIC : ST_SATISFIED;
+    state[i] = st;
+  }
+  auto qc = DF(qfrc_constraint);
+#pragma unroll 1
+  for (int i = c.lane; i < nv; i += C::G) {
+    double s = 0;
+    for (int r = 0; r < nefc; r++) s += J[r * nvp + i] * f[r];
+    qc[i] = s; x[i] = s;
+  }
+  SYNC();
+  bp_solve_sparse(c, DF(qLD), DF(qLDiagInv), x);
+  for (int i = c.lane; i < nv; i += C::G) {
+    double a = as[i] + x[i];
+    qacc[i] = a; warm[i] = a;
+  }
+  if (c.lane == 0) {
+    IF(solver_iter)[0] = iter;
+    DF(solver_stat)[0] = improvement; DF(solver_stat)[1] = 0;
+  }
+  SYNC();
+}
+
 // Solver state that lives across Newton iterations (registers of the calling kernel)
 struct BpSolve {
   double cost, improvement, gradient;
   int iter, nefc, nsingle, ntenlim;
   bool done, stale;      // stale: the factorisation does not match the active set
+  double cg_den;         // CG: grad . Mgrad of the previous iterate (FULL shape only)
 };
 
 // everything up to the first search direction; st.done when there is nothing to iterate
@@ -735,7 +863,8 @@ BP_STAGE void bp_solver_begin(const C& c, BpSolve& st) {
   bool changed;
   st.cost = bp_update_constraint(c, jar, nefc, true, &changed) + bp_gauss_cost(c);
   bp_newton_grad(c);
-  bp_newton_gradient(c, nefc, nsingle, ntenlim, true);
+  if (C::FULL && m.opt_solver == 1) bp_cg_gradient(c);
+  else bp_newton_gradient(c, nefc, nsingle, ntenlim, true);
   for (int i = c.lane; i < nv; i += C::G) search[i] = -HOT(s_Mgrad, m.ntri + 2 * nv)[i];
   SYNC();
   st.done = m.opt_iterations <= 0;
@@ -761,6 +890,13 @@ BP_STAGE void bp_solver_step(const C& c, BpSolve& st) {
   SYNC();
   double old = st.cost;
   bool changed;
+  if constexpr (C::FULL) if (m.opt_solver == 1) {   // Polak-Ribiere needs the previous pair
+    double den = 0;
+    auto Mg = HOT(s_Mgrad, m.ntri + 2 * nv), Mgold = DF(s_tmp);
+    for (int i = c.lane; i < nv; i += C::G) { double v = Mg[i]; den += DF(s_grad)[i] * v; Mgold[i] = v; }
+    st.cg_den = group_sum(c, den);
+    SYNC();
+  }
   st.cost = bp_update_constraint(c, jar, nefc, true, &changed) + bp_gauss_cost(c);
   double gn = bp_newton_grad(c);
   st.improvement = scale * (old - st.cost); st.gradient = scale * sqrt(gn);
@@ -773,6 +909,18 @@ BP_STAGE void bp_solver_step(const C& c, BpSolve& st) {
 
 BP_STAGE void bp_solver_direction(const C& c, BpSolve& st) {
   const BpModel& m = c.P.m;
+  if constexpr (C::FULL) if (m.opt_solver == 1) {     // CG: search = -Mgrad + beta search
+    bp_cg_gradient(c);
+    auto Mg = HOT(s_Mgrad, m.ntri + 2 * m.nv), Mgold = DF(s_tmp), sr = DF(s_search);
+    double num = 0;
+    for (int i = c.lane; i < m.nv; i += C::G) num += DF(s_grad)[i] * (Mg[i] - Mgold[i]);
+    num = group_sum(c, num);
+    double beta = num / (st.cg_den > BP_MINVAL ? st.cg_den : BP_MINVAL);
+    if (beta < 0) beta = 0;
+    for (int i = c.lane; i < m.nv; i += C::G) sr[i] = -Mg[i] + beta * sr[i];
+    SYNC();
+    return;
+  }
   bp_newton_gradient(c, st.nefc, st.nsingle, st.ntenlim, st.stale);
   st.stale = false;
   auto search = DF(s_search);
@@ -802,8 +950,12 @@ BP_STAGE void bp_solver_end(const C& c, const BpSolve& st) {
 // iteration (environments that are done skip the body).
 template <class C>
 __device__ __forceinline__ void bp_fwd_constraint(const C& c) {
+  if constexpr (C::FULL) if (c.P.m.opt_solver == 0) {    // uniform per launch
+    RUN(bp_solver_pgs(c));
+    return;
+  }
   BpSolve st;
-  st.done = true; st.nefc = 0;
+  st.done = true; st.nefc = 0; st.cg_den = 0;
   RUN(bp_solver_begin(c, st));
   if (c.lock && (BP_LOCKMASK >> 8 & 1)) {
 #if BP_NEWTON_GROUP > 0

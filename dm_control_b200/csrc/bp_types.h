@@ -150,7 +150,8 @@ struct BpModel {
   X(s_Ma, m.nv) X(s_jar, njmax) X(s_grad, m.nv) X(s_Mgrad, m.nv) \
   X(s_search, m.nv) X(s_Mv, m.nv) X(s_jv, njmax) X(s_H, m.nv * m.nvp + m.nv) \
   X(s_Md, m.nv * m.nvp) X(s_Hdinv, m.nv) X(s_MM, m.nM) X(s_MMdinv, m.nv) \
-  X(s_rdof, njmax) X(s_rw, njmax) X(s_tmp, 2 * m.nv + m.na) X(s_cacc, 6 * m.nbody) X(s_cfrc, 6 * m.nbody) X(s_rk, m.nq + m.nv + m.na + 5 * (2 * m.nv + m.na) + 1)
+  X(s_rdof, njmax) X(s_rw, njmax) X(s_tmp, 2 * m.nv + m.na) X(s_cacc, 6 * m.nbody) X(s_cfrc, 6 * m.nbody) X(s_rk, m.nq + m.nv + m.na + 5 * (2 * m.nv + m.na) + 1) \
+  X(s_AR, m.opt_solver == 0 ? njmax * njmax : 0)   /* PGS only: efc_AR = J M^-1 J^T + R */
 
 struct BpLayout {   // offsets in doubles from the start of the env's image
 #define X(n, c) int n;

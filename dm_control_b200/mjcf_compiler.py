@@ -506,7 +506,7 @@ _SENSOR_SPEC = {
 
 # What the kernels (and the oracle) implement; kept in step with csrc/bp_api.cu validate().
 HAVE_BOX_PAIRS = True        # sphere / capsule / box against box
-HAVE_PGS_CG = False          # solver="PGS" / "CG"
+HAVE_PGS_CG = True           # solver="PGS" / "CG"
 
 
 def pair_supported(t1, t2):
@@ -544,8 +544,8 @@ def check_supported(m, unsupported_pairs="error"):
   if int(m.opt_solver) != M.SOL_NEWTON and not HAVE_PGS_CG:
     raise ValueError("solver=%r is not implemented (only Newton)"
                      % ["PGS", "CG", "Newton"][int(m.opt_solver)])
-  if int(m.opt_solver) != M.SOL_NEWTON and int(m.opt_cone) != M.CONE_PYRAMIDAL:
-    raise ValueError("the PGS and CG solvers are implemented for pyramidal cones only")
+  if int(m.opt_solver) == M.SOL_PGS and int(m.opt_cone) != M.CONE_PYRAMIDAL:
+    raise ValueError("the PGS solver is implemented for pyramidal cones only")
   if int(m.opt_noslip_iterations) > 0:
     raise ValueError("noslip_iterations > 0 is not supported (the noslip post-solver is not "
                      "implemented)")

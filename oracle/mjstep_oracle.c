@@ -222,7 +222,7 @@ struct OData {
   double *body_pos, *body_quat;
   /* solver scratch */
   double *s_Ma, *s_jar, *s_grad, *s_Mgrad, *s_search, *s_Mv, *s_jv, *s_H,
-      *s_Mdense, *s_fluid;
+      *s_Mdense, *s_fluid, *s_AR, *s_Mgold;
 };
 
 OData* od_create(const OModel* m) {
@@ -249,6 +249,8 @@ OData* od_create(const OModel* m) {
   d->s_jv = calloc(nj, 8); d->s_H = calloc((size_t)nv * nv, 8);
   d->s_Mdense = calloc((size_t)nv * nv, 8);
   d->s_fluid = calloc((size_t)6 * (m->nbody > 0 ? m->nbody : 1), 8);
+  d->s_AR = calloc(m->opt_solver == 0 ? (size_t)nj * nj : 1, 8);     /* PGS only */
+  d->s_Mgold = calloc(nv, 8);
   o_reset(m, d);
   return d;
 }
@@ -263,7 +265,7 @@ void od_free(OData* d) {
   free(d->body_pos); free(d->body_quat);
   free(d->s_Ma); free(d->s_jar); free(d->s_grad); free(d->s_Mgrad);
   free(d->s_search); free(d->s_Mv); free(d->s_jv); free(d->s_H);
-  free(d->s_Mdense); free(d->s_fluid);
+  free(d->s_Mdense); free(d->s_fluid); free(d->s_AR); free(d->s_Mgold);
   free(d);
 }
 
@@ -2513,8 +2515,102 @@ static void jar_from_qacc(const OModel* m, OData* d) {
   }
 }
 
+/* CG [MJ-doc A.9: "same cost, Polak-Ribiere with M^-1 preconditioner"]: the gradient of the
+ * primal cost preconditioned by the sparse factor of M instead of the Newton Hessian */
+static void cg_gradient(const OModel* m, OData* d) {
+  int nv = m->nv;
+  for (int i = 0; i < nv; i++)
+    d->s_grad[i] = d->s_Ma[i] - d->qfrc_smooth[i] - d->qfrc_constraint[i];
+  memcpy(d->s_Mgrad, d->s_grad, sizeof(double) * nv);
+  solve_sparse(m, d->qLD, d->qLDiagInv, d->s_Mgrad);
+}
+
+/* PGS [MJ-doc A.9: "dual, needs efc_AR = J M^-1 J^T + R, Gauss-Seidel with projection"]:
+ * minimise 0.5 f^T AR f + f^T b over the constraint set, b = J qacc_smooth - aref, one
+ * row at a time in row order: equality rows unconstrained, friction-loss rows clamped to
+ * +-frictionloss, limit / contact rows (frictionless, pyramid edges) to f >= 0.  The warm
+ * start maps qacc_warmstart to forces through the primal constraint update and is kept
+ * when its dual cost is below that of f = 0 (zero).  Stops when the scaled cost decrease
+ * of a sweep falls below opt.tolerance.  Pyramidal cones only (validate()). */
+static void pgs_solve(const OModel* m, OData* d) {
+  int nv = m->nv, nefc = d->nefc[0];
+  double *AR = d->s_AR, *b = d->s_jv, *x = d->s_grad, *f = d->efc_force;
+  for (int i = 0; i < nefc; i++) {
+    memcpy(x, d->efc_J + (size_t)i * nv, sizeof(double) * nv);
+    solve_sparse(m, d->qLD, d->qLDiagInv, x);
+    for (int j = 0; j < nefc; j++) {
+      double s = 0;
+      for (int k = 0; k < nv; k++) s += d->efc_J[(size_t)j * nv + k] * x[k];
+      AR[(size_t)i * nefc + j] = s;
+    }
+    AR[(size_t)i * nefc + i] += d->efc_R[i];
+  }
+  for (int r = 0; r < nefc; r++) {
+    double s = 0;
+    for (int i = 0; i < nv; i++) s += d->efc_J[(size_t)r * nv + i] * d->qacc_smooth[i];
+    b[r] = s - d->efc_aref[r];
+  }
+  int warm = 0;
+  if (!(m->opt_disableflags & DSBL_WARMSTART)) {
+    memcpy(d->qacc, d->qacc_warmstart, sizeof(double) * nv);
+    jar_from_qacc(m, d);
+    update_constraint(m, d, d->s_jar);
+    double cost = 0;
+    for (int i = 0; i < nefc; i++) {
+      double s = 0;
+      for (int j = 0; j < nefc; j++) s += AR[(size_t)i * nefc + j] * f[j];
+      cost += f[i] * (0.5 * s + b[i]);
+    }
+    warm = cost < 0;
+  }
+  if (!warm) memset(f, 0, sizeof(double) * nefc);
+  double scale = 1.0 / (m->stat_meaninertia * (nv > 1 ? nv : 1));
+  int iter = 0;
+  while (iter < m->opt_iterations) {
+    double improvement = 0;
+    for (int i = 0; i < nefc; i++) {
+      double res = b[i];
+      for (int j = 0; j < nefc; j++) res += AR[(size_t)i * nefc + j] * f[j];
+      double aii = AR[(size_t)i * nefc + i], old = f[i], fn = old - res / aii;
+      int t = d->efc_type[i];
+      if (t == CN_FRICTION_DOF || t == CN_FRICTION_TENDON) {
+        double fl = d->efc_frictionloss[i];
+        fn = fn < -fl ? -fl : (fn > fl ? fl : fn);
+      } else if (t != CN_EQUALITY) {
+        if (fn < 0) fn = 0;
+      }
+      double delta = fn - old;
+      f[i] = fn;
+      improvement -= 0.5 * delta * delta * aii + delta * res;
+    }
+    improvement *= scale;
+    d->solver_improvement[0] = improvement; d->solver_gradient[0] = 0;
+    iter++;
+    if (improvement < m->opt_tolerance) break;
+  }
+  for (int i = 0; i < nefc; i++) {
+    int t = d->efc_type[i];
+    if (t == CN_EQUALITY) d->efc_state[i] = ST_QUADRATIC;
+    else if (t == CN_FRICTION_DOF || t == CN_FRICTION_TENDON) {
+      double fl = d->efc_frictionloss[i];
+      d->efc_state[i] = f[i] >= fl ? ST_LINEARNEG : (f[i] <= -fl ? ST_LINEARPOS : ST_QUADRATIC);
+    } else d->efc_state[i] = f[i] > 0 ? ST_QUADRATIC : ST_SATISFIED;
+  }
+  for (int i = 0; i < nv; i++) {
+    double s = 0;
+    for (int r = 0; r < nefc; r++) s += d->efc_J[(size_t)r * nv + i] * f[r];
+    d->qfrc_constraint[i] = s;
+    x[i] = s;
+  }
+  solve_sparse(m, d->qLD, d->qLDiagInv, x);
+  for (int i = 0; i < nv; i++) d->qacc[i] = d->qacc_smooth[i] + x[i];
+  d->solver_iter[0] = iter;
+  memcpy(d->qacc_warmstart, d->qacc, sizeof(double) * nv);
+}
+
 static void o_fwd_constraint(const OModel* m, OData* d) {
   int nv = m->nv, nefc = d->nefc[0];
+  const int cg = m->opt_solver == 1;
   d->solver_iter[0] = 0;
   if (nefc == 0) {
     memcpy(d->qacc, d->qacc_smooth, sizeof(double) * nv);
@@ -2522,6 +2618,7 @@ static void o_fwd_constraint(const OModel* m, OData* d) {
     memset(d->qfrc_constraint, 0, sizeof(double) * nv);
     return;
   }
+  if (m->opt_solver == 0) { pgs_solve(m, d); return; }
   dense_m(m, d->qM, d->s_Mdense);
   /* warm start: the cheaper of qacc_warmstart and qacc_smooth */
   double cost;
@@ -2541,7 +2638,7 @@ static void o_fwd_constraint(const OModel* m, OData* d) {
   mul_m(m, d->qM, d->s_Ma, d->qacc);
   jar_from_qacc(m, d);
   cost = total_cost(m, d, update_constraint(m, d, d->s_jar));
-  newton_gradient(m, d);
+  if (cg) cg_gradient(m, d); else newton_gradient(m, d);
   for (int i = 0; i < nv; i++) d->s_search[i] = -d->s_Mgrad[i];
   double scale = 1.0 / (m->stat_meaninertia * (nv > 1 ? nv : 1));
   int iter = 0;
@@ -2559,16 +2656,28 @@ static void o_fwd_constraint(const OModel* m, OData* d) {
       d->s_Ma[i] += alpha * d->s_Mv[i];
     }
     for (int r = 0; r < nefc; r++) d->s_jar[r] += alpha * d->s_jv[r];
-    double old = cost;
+    double old = cost, cg_den = 0;
+    if (cg) {                     /* Polak-Ribiere needs the previous gradient pair */
+      for (int i = 0; i < nv; i++) cg_den += d->s_grad[i] * d->s_Mgrad[i];
+      memcpy(d->s_Mgold, d->s_Mgrad, sizeof(double) * nv);
+    }
     cost = total_cost(m, d, update_constraint(m, d, d->s_jar));
-    newton_gradient(m, d);
+    if (cg) cg_gradient(m, d); else newton_gradient(m, d);
     double gn = 0;
     for (int i = 0; i < nv; i++) gn += d->s_grad[i] * d->s_grad[i];
     double improvement = scale * (old - cost), gradient = scale * sqrt(gn);
     d->solver_improvement[0] = improvement; d->solver_gradient[0] = gradient;
     iter++;
     if (improvement < m->opt_tolerance || gradient < m->opt_tolerance) break;
-    for (int i = 0; i < nv; i++) d->s_search[i] = -d->s_Mgrad[i];
+    if (cg) {
+      double num = 0;
+      for (int i = 0; i < nv; i++) num += d->s_grad[i] * (d->s_Mgrad[i] - d->s_Mgold[i]);
+      double beta = num / (cg_den > MINVAL ? cg_den : MINVAL);
+      if (beta < 0) beta = 0;
+      for (int i = 0; i < nv; i++) d->s_search[i] = -d->s_Mgrad[i] + beta * d->s_search[i];
+    } else {
+      for (int i = 0; i < nv; i++) d->s_search[i] = -d->s_Mgrad[i];
+    }
   }
   d->solver_iter[0] = iter;
   memcpy(d->qacc_warmstart, d->qacc, sizeof(double) * nv);

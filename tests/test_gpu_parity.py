@@ -27,13 +27,13 @@ SIZES = {"humanoid": HUMANOID_SIZES, "quadruped": dict(njmax=120, nconmax=40),
          "quadruped_fetch": dict(njmax=160, nconmax=40)}
 
 
-def _assert_parity(res):
+def _assert_parity(res, elem=1.0):
   for step, cmp in sorted(res.items()):
     bad = {k: v for k, v in cmp.int_mismatch.items() if v}
     assert not bad, "step %d integer mismatches %s\n%s" % (step, bad, cmp.report())
     assert cmp.worst() <= TOL, "step %d\n%s" % (step, cmp.report())
     # element-wise: |a - b| <= 1e-8 |b| + 1e-10 max(1, max|b|) for every element
-    assert cmp.worst_elem() <= 1.0, "step %d (element-wise)\n%s" % (step, cmp.report())
+    assert cmp.worst_elem() <= elem, "step %d (element-wise)\n%s" % (step, cmp.report())
 
 
 @pytest.mark.parametrize("domain", ["pendulum", "cartpole", "acrobot", "cheetah", "walker",
@@ -352,3 +352,38 @@ def test_box_narrowphase_matches_oracle(lanes):
                              lanes=lanes, njmax=300, nconmax=64, flat_model=m, state_hook=hook)
   _assert_parity(res)
   assert max(stats["ncon"]) > 6, stats
+
+
+@pytest.mark.parametrize("domain,solver,lanes", [
+    ("cheetah", "CG", 8), ("cheetah", "PGS", 8), ("humanoid", "CG", 16), ("humanoid", "PGS", 16),
+    ("cheetah", "CG", 32), ("cheetah", "PGS", 1), ("finger", "CG", 4), ("quadruped", "PGS", 16)])
+def test_cg_and_pgs_solvers_match_oracle(domain, solver, lanes):
+  """opt_solver = CG / PGS (north_star "Newton/CG/PGS solvers"): every field, solver_iter
+  included, against the oracle's restatement (primal CG with the M^-1 preconditioner and
+  Polak-Ribiere; dual PGS on AR = J M^-1 J^T + R)."""
+  def mutate(m):
+    m.arrays["opt_solver"][...] = {"PGS": 0, "CG": 1}[solver]
+  kw = dict(SIZES.get(domain, dict(njmax=64, nconmax=16)))
+  res, stats = PU.run_parity(domain, nenv=32, nsteps=10, seed=6, check_steps=[0, 1, 2, 10],
+                             lanes=lanes, mutate=mutate, **kw)
+  # CG converges linearly and stops on opt.tolerance = 1e-8: rounding differences between the
+  # two sides are not contracted as Newton's quadratic convergence contracts them (measured:
+  # humanoid cvel 6e-10 of the array's scale after 2 steps), so its element-wise floor is
+  # 1e-9 * scale instead of 1e-10 * scale; the array-normalised 1e-8 bar is unchanged
+  _assert_parity(res, elem=10.0 if solver == "CG" else 1.0)
+  assert max(stats["iter"]) > 0.5, stats
+
+
+@pytest.mark.parametrize("lanes", [16, 4])
+def test_reference_test_humanoid_rk4_pgs(lanes):
+  """The reference's own test asset asks for integrator="RK4" iterations="50" solver="PGS"
+  (mujoco/testing/assets/humanoid.xml:9; compiled copy under tests/golden/): the model runs
+  the solver it asks for, and matches the oracle."""
+  from dm_control_b200.model import FlatModel
+  m = FlatModel.load(os.path.join(GOLDEN, "model_ref_test_humanoid.npz"))
+  assert int(m.opt_solver) == 0 and int(m.opt_integrator) == 1 and int(m.opt_iterations) == 50
+  res, stats = PU.run_parity("ref_test_humanoid", nenv=24, nsteps=4, seed=2,
+                             check_steps=[0, 1, 4], lanes=lanes, njmax=160, nconmax=40,
+                             flat_model=m)
+  _assert_parity(res)
+  assert max(stats["nefc"]) > 5

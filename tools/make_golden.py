@@ -120,7 +120,18 @@ def c1_trace(steps=1000):
   print("c1_cartpole_swingup.npz", np.stack(rec["obs"]).shape, "reward sum", np.sum(rec["reward"]))
 
 
+def ref_test_humanoid_model():
+  """The reference's own test model that asks for RK4 + PGS
+  (/root/reference/dm_control/mujoco/testing/assets/humanoid.xml:9), compiled here because
+  the GPU box has no reference tree."""
+  from dm_control_b200 import mjcf_compiler as C
+  m = C.compile_file("/root/reference/dm_control/mujoco/testing/assets/humanoid.xml")
+  m.save(os.path.join(OUT, "model_ref_test_humanoid.npz"))
+  print("model_ref_test_humanoid.npz solver", int(m.opt_solver), "integrator", int(m.opt_integrator))
+
+
 if __name__ == "__main__":
+  ref_test_humanoid_model()
   os.makedirs(OUT, exist_ok=True)
   rewards_fixture()
   for d in ("pendulum", "cartpole", "acrobot", "cheetah", "walker", "hopper", "humanoid"):
