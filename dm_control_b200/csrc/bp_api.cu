@@ -771,11 +771,13 @@ extern "C" int bp_hfield_read(bp_batch* b, float* host, int64_t env0, int64_t n)
 
 static int launch(bp_batch* b, int mode, int nsub, int disable_actuation,
                   const double* ctrl_in = nullptr, double* obs_out = nullptr,
-                  double* rew_out = nullptr) {
+                  double* rew_out = nullptr, double* obs_host = nullptr,
+                  double* rew_host = nullptr) {
   if (!b) return fail(BP_EINVAL, "null batch");
   cudaSetDevice(b->model->device);
   BpParams P = make_params(b, mode, nsub, disable_actuation);
   P.ctrl_in = ctrl_in; P.obs_out = obs_out; P.rew_out = rew_out;
+  P.obs_host = obs_host; P.rew_host = rew_host;
   if (rew_out) {
     P.task = b->task;
     P.task_nobs = bp_task_nobs_impl(&b->model->M, b->task.kind);
@@ -927,12 +929,30 @@ extern "C" int bp_env_step_host(bp_batch* b, int nsub, const double* ctrl_host,
   if (nu > 0 && ctrl_src == b->ctrl_stage)
     CUDA_OK(cudaMemcpyAsync(b->ctrl_stage, ctrl_host, (size_t)b->nenv * nu * 8,
                             cudaMemcpyHostToDevice, b->stream));
-  int e = bp_env_step(b, nsub, ctrl_src, nobs > 0 ? b->obs_dev : nullptr, b->rew_dev);
+  // Pinned (mapped) result buffers are filled by the kernel itself, block by block, while
+  // other blocks still compute (BpParams.obs_host); pageable ones by D2H copies afterwards.
+  // The global-memory shapes support it (every thread of a lock-step block reaches the end).
+  double *obs_map = nullptr, *rew_map = nullptr;
+  static const bool direct = getenv("BPHYS_NO_DIRECT_OUT") == nullptr;
+  if (direct && b->lanes != 32 && !b->use_mask && !getenv("BPHYS_SPLIT")) {
+    auto mapped = [](const void* p) -> double* {
+      cudaPointerAttributes a;
+      if (p && cudaPointerGetAttributes(&a, p) == cudaSuccess && a.type == cudaMemoryTypeHost &&
+          a.devicePointer != nullptr)
+        return (double*)a.devicePointer;
+      cudaGetLastError();
+      return nullptr;
+    };
+    if (nobs > 0) obs_map = mapped(obs_host);
+    rew_map = mapped(reward_host);
+  }
+  int e = launch(b, BP_MODE_STEP, nsub, 0, nu > 0 ? ctrl_src : nullptr,
+                 nobs > 0 ? b->obs_dev : nullptr, b->rew_dev, obs_map, rew_map);
   if (e != BP_OK) return e;
-  if (obs_host && nobs > 0)
+  if (obs_host && nobs > 0 && !obs_map)
     CUDA_OK(cudaMemcpyAsync(obs_host, b->obs_dev, (size_t)b->nenv * nobs * 8,
                             cudaMemcpyDeviceToHost, b->stream));
-  if (reward_host)
+  if (reward_host && !rew_map)
     CUDA_OK(cudaMemcpyAsync(reward_host, b->rew_dev, (size_t)b->nenv * 8,
                             cudaMemcpyDeviceToHost, b->stream));
   CUDA_OK(cudaStreamSynchronize(b->stream));

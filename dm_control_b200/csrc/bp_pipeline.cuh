@@ -393,6 +393,25 @@ bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
     if (G > 1) __syncwarp(mask);
     if (c.lane == 0) bp_task_eval(P, P.task, env, P.task_nobs, P.obs_out, P.rew_out);
   }
+  // results straight to pinned host memory, block by block (BpParams.obs_host); every thread
+  // of a lock-step block is still here
+  if (lock && (P.obs_host || P.rew_host)) {
+    __syncthreads();
+    const long long e0 = blockIdx.x * (long long)blockDim.x / G;
+    long long cnt = blockDim.x / G;
+    if (e0 + cnt > P.nenv) cnt = P.nenv - e0;
+    if (cnt > 0) {
+      if (P.obs_host && P.obs_out) {
+        const double* src = P.obs_out + e0 * P.task_nobs;
+        double* dst = P.obs_host + e0 * P.task_nobs;
+        for (long long i = threadIdx.x; i < cnt * P.task_nobs; i += blockDim.x) dst[i] = __ldcg(src + i);
+      }
+      if (P.rew_host) {
+        for (long long i = threadIdx.x; i < cnt; i += blockDim.x)
+          P.rew_host[e0 + i] = __ldcg(P.rew_out + e0 + i);
+      }
+    }
+  }
 }
 
 

@@ -199,6 +199,12 @@ struct BpParams {
   double* rew_out;         // null: no epilogue at all
   int task_nobs;
   BpTask task;
+  // End-to-end step (bp_env_step_host) with pinned, mapped host result buffers: every block
+  // copies the rows of ITS environments from obs_out / rew_out to these host-mapped
+  // addresses with warp-contiguous stores as soon as it is done, so the PCIe transfer of the
+  // results overlaps the blocks still computing and no D2H copy follows the kernel.
+  double* obs_host;        // null: results stay on the device
+  double* rew_host;
 };
 // arena layout: packed Hessian / Cholesky factor + rhs row (ntri + nv), inverse pivots (nv), Mgrad (nv)
 

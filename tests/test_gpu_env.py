@@ -326,3 +326,34 @@ def test_lqr_optimal_policy_on_device(level):
   assert len(np.unique(np.round(expected, 6))) == n          # six different start states
   env.close()
 
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,nenv", [("cheetah-run", 1000), ("humanoid-run", 300),
+                                       ("pendulum-swingup", 77)])
+def test_env_step_host_direct_results_equal_copied_results(name, nenv):
+  """bp_env_step_host with pinned (mapped) result buffers -- filled by the kernel's blocks
+  themselves -- against pageable buffers filled by D2H copies: identical bits, also for the
+  ragged last block."""
+  import torch
+  import bench
+  from dm_control_b200 import binding
+  outs = []
+  for pinned in (True, False):
+    tdef, m, model, batch, nsub = bench.make_batch(name, nenv, 0, seed=5)
+    rng = np.random.RandomState(3)
+    obs = torch.zeros((nenv, batch.nobs), dtype=torch.float64)
+    rew = torch.zeros((nenv,), dtype=torch.float64)
+    if pinned:
+      obs, rew = obs.pin_memory(), rew.pin_memory()
+    seq = []
+    for k in range(3):
+      ctrl = rng.uniform(-1, 1, (nenv, m.nu))
+      batch.env_step_host(nsub, ctrl, obs.numpy(), rew.numpy())
+      seq.append((obs.numpy().copy(), rew.numpy().copy()))
+    outs.append(seq)
+    batch.free(); model.free()
+  for (o1, r1), (o2, r2) in zip(*outs):
+    assert np.all(np.isfinite(o1)) and np.abs(o1).max() > 0
+    np.testing.assert_array_equal(o1, o2)
+    np.testing.assert_array_equal(r1, r2)
