@@ -7,8 +7,12 @@ One "step" = one `Environment.step` for every environment of the batch: copy of 
 step's actions into the images, `n_sub_steps` physics steps in ONE kernel launch
 (engine.py:149-166 inside rl/control.py:100-106) and the task's observation/reward
 kernel.  Workload at every N: cheetah-run at 16384 envs per GPU (BASELINE.json
-configs[2]; weak scaling, no per-step collective); humanoid-run at 8192 envs per GPU
-(configs[3]) is reported in "extra".
+configs[2]; weak scaling, no per-step collective).  "extra" carries, measured the same way
+in the same run: humanoid-run at 8192 envs per GPU (configs[3]; with its own FP64 roofline,
+CPU baseline and ratio), walker-walk (configs[2]), cartpole / acrobot / pendulum swing-up at
+4096 envs (configs[1]), quadruped-escape and finger-spin at 8192 envs per GPU (configs[4]:
+65536 envs over 8 GPUs), and a CONTACT-RICH variant of cheetah-run and humanoid-run
+(actions 0.1 * U(-1, 1): the robots rest on the ground instead of bouncing).
 
 The reference's own engine (MuJoCo 2.00) is a closed binary that is absent here
 (SURVEY.md §0.2), so the reference arm and `cpu_baseline` time the CPU oracle port
@@ -45,17 +49,18 @@ ALGO = {"cheetah": dict(bytes=648, flops=2.0e4), "humanoid": dict(bytes=2048, fl
 # replaces the estimates (tools/count_ops.py -> profiles/r1_oracle_opcount.json)
 FLOPS_SOURCE = {}
 FLOPS_BY_TASK = {}
-try:
-  with open(os.path.join(ROOT, "profiles", "r1_oracle_opcount.json")) as _f:
-    for _name, _rec in json.load(_f).items():
-      _dom = _name.split("-", 1)[0]
-      FLOPS_BY_TASK[_name] = (_rec["flops_per_substep"],
-                              "oracle op counter, %s (%s)" % (_name, _rec["sample"]))
-      if _dom in ALGO and _dom not in FLOPS_SOURCE:
-        ALGO[_dom]["flops"] = _rec["flops_per_substep"]
-        FLOPS_SOURCE[_dom] = "oracle op counter, %s (%s)" % (_name, _rec["sample"])
-except (OSError, ValueError, KeyError):
-  pass
+for _file in ("r1_oracle_opcount.json", "r2_oracle_opcount.json"):
+  try:
+    with open(os.path.join(ROOT, "profiles", _file)) as _f:
+      for _name, _rec in json.load(_f).items():
+        _dom = _name.split("-", 1)[0]
+        FLOPS_BY_TASK[_name] = (_rec["flops_per_substep"],
+                                "oracle op counter, %s (%s)" % (_name, _rec["sample"]))
+        if _dom in ALGO and _dom not in FLOPS_SOURCE and "@" not in _name:
+          ALGO[_dom]["flops"] = _rec["flops_per_substep"]
+          FLOPS_SOURCE[_dom] = "oracle op counter, %s (%s)" % (_name, _rec["sample"])
+  except (OSError, ValueError, KeyError):
+    pass
 # `lanes`: execution shape picked from the lane sweep (profiles/r1b_sweep_lanes.jsonl)
 _JSON_OUT = None     # the process's original stdout when fd 1 has been pointed at stderr
 WORKLOADS = {"cheetah-run": dict(nenv=16384, njmax=64, nconmax=16, settle=200, lanes=8),
@@ -168,9 +173,10 @@ class ClockSampler:
 LANES = {"value": 0}
 
 
-def workload_name(name, nenv, nsub):
-  return ("%s, %d envs per GPU, random actions U(-1,1), %d physics sub-step(s) per env-step"
-          % (name, nenv, nsub))
+def workload_name(name, nenv, nsub, scale=1.0):
+  act = "U(-1,1)" if scale == 1.0 else "%g * U(-1,1)" % scale
+  return ("%s, %d envs per GPU, random actions %s, %d physics sub-step(s) per env-step"
+          % (name, nenv, act, nsub))
 
 
 def make_batch(name, nenv, device, seed):
@@ -190,7 +196,7 @@ def make_batch(name, nenv, device, seed):
   return tdef, m, model, batch, nsub
 
 
-def run_gpu(name, nenv, steps, warmup, rank, world, device):
+def run_gpu(name, nenv, steps, warmup, rank, world, device, action_scale=1.0):
   import torch
   from dm_control_b200 import binding
   tdef, m, model, batch, nsub = make_batch(name, nenv, device, seed=1000 + rank)
@@ -199,7 +205,7 @@ def run_gpu(name, nenv, steps, warmup, rank, world, device):
   gen = torch.Generator(device="cuda:%d" % device); gen.manual_seed(rank)
   total = steps + warmup
   ctrl = (torch.rand((total, nenv, nu), generator=gen, device="cuda:%d" % device,
-                     dtype=torch.float64) * 2 - 1)
+                     dtype=torch.float64) * 2 - 1) * action_scale
   obs = torch.empty((nenv, nobs), device="cuda:%d" % device, dtype=torch.float64)
   rew = torch.empty((nenv,), device="cuda:%d" % device, dtype=torch.float64)
   torch.cuda.synchronize(device)
@@ -244,7 +250,7 @@ def run_gpu(name, nenv, steps, warmup, rank, world, device):
   # timed region is the public host call: H2D of that buffer, the fused step, D2H of
   # observations and rewards into pinned host buffers, stream synchronisation
   rng = np.random.RandomState(7 + rank)
-  h_ctrl = torch.from_numpy(rng.uniform(-1, 1, (steps + 2, nenv, nu))).pin_memory()
+  h_ctrl = torch.from_numpy(action_scale * rng.uniform(-1, 1, (steps + 2, nenv, nu))).pin_memory()
   h_obs = torch.empty((nenv, nobs), dtype=torch.float64).pin_memory()
   h_rew = torch.empty((nenv,), dtype=torch.float64).pin_memory()
   hc, ho, hr = h_ctrl.numpy(), h_obs.numpy(), h_rew.numpy()
@@ -269,7 +275,7 @@ def run_gpu(name, nenv, steps, warmup, rank, world, device):
   return out
 
 
-def cpu_run(name, nenv, steps, threads, seed=0):
+def cpu_run(name, nenv, steps, threads, seed=0, action_scale=1.0):
   """Times the oracle port on host threads: `steps` env-steps of `nenv` envs."""
   from oracle import oracle_py
   tdef, m = load_task(name)
@@ -279,7 +285,7 @@ def cpu_run(name, nenv, steps, threads, seed=0):
   qpos = initial_state(name, m, nenv, seed)
   qvel = np.zeros((nenv, m.nv)); act = np.zeros((nenv, max(m.na, 1)))
   warm = np.zeros((nenv, m.nv)); tm = np.zeros(nenv)
-  ctrl = rng.uniform(-1, 1, (steps, nenv, m.nu))
+  ctrl = action_scale * rng.uniform(-1, 1, (steps, nenv, m.nu))
   hf = initial_hfield(name, m, nenv, seed)
   t0 = time.perf_counter()
   oracle_py.run_batch(om, qpos, qvel, act, warm, tm, ctrl, steps, nsub, threads, hfield=hf)
@@ -302,6 +308,72 @@ def cpu_baseline(name, budget_s=15.0):
           "sample": "%s: %d envs x %d env-steps in %d chunks (x%d physics sub-steps each), "
                     "%d pthreads, %.1f s of oracle time" % (name, nenv, chunk * k, k, nsub,
                                                             threads, spent)}
+
+
+def _vecenv_worker(conn, name, seed):
+  """One process = one environment, as scripts/vec_env.py:346-394 (`_subproc_worker`): waits
+  for an action, takes one Environment.step (n_sub_steps physics steps, observation, reward
+  -- the Python of rl/control.py:94-123 around the engine calls), sends the TimeStep back."""
+  from oracle import oracle_py, task_oracle
+  tdef, m = load_task(name)
+  nsub = T.n_sub_steps(tdef, m)
+  o = oracle_py.Oracle(oracle_py.OracleModel(m))
+  o.reset()
+  o.qpos[:] = initial_state(name, m, 1, seed)[0]
+  o.forward()
+  fields = ("qpos", "qvel", "ctrl", "xmat", "xpos", "xquat", "site_xpos", "site_xmat",
+            "sensordata", "subtree_com", "geom_xpos", "act", "cvel", "xipos")
+  while True:
+    a = conn.recv()
+    if a is None:
+      break
+    o.ctrl[:] = a
+    for _ in range(nsub):
+      o.step()
+    d = {f: np.array(getattr(o, f), dtype=np.float64).reshape(1, -1) for f in fields}
+    obs, r = task_oracle.obs_reward(tdef.domain, tdef.task, m, d)
+    conn.send((obs[0], float(r[0])))
+  conn.close()
+
+
+def cpu_python_vecenv(name, budget_s=6.0):
+  """The number a dm_control user gets on the host (SURVEY.md 8d second CPU figure): the
+  Python Environment.step loop in the SubprocVecEnv shape of scripts/vec_env.py:396-459 --
+  one process per core, one env per process, actions and TimeSteps through pipes,
+  step_async to all then step_wait on all.  Engine = the CPU oracle port, observation /
+  reward = oracle/task_oracle.py (numpy, like the reference's task classes)."""
+  import multiprocessing as mp
+  ctx = mp.get_context("fork")
+  nproc = os.cpu_count() or 1
+  tdef, m = load_task(name)
+  pipes, procs = [], []
+  for i in range(nproc):
+    a, b = ctx.Pipe()
+    pr = ctx.Process(target=_vecenv_worker, args=(b, name, 100 + i), daemon=True)
+    pr.start(); b.close()
+    pipes.append(a); procs.append(pr)
+  rng = np.random.RandomState(0)
+
+  def step():
+    acts = rng.uniform(-1, 1, (nproc, m.nu))
+    for c, a in zip(pipes, acts):          # step_async
+      c.send(a)
+    return [c.recv() for c in pipes]       # step_wait
+
+  for _ in range(5):
+    step()
+  n, t0 = 0, time.perf_counter()
+  while time.perf_counter() - t0 < budget_s:
+    step(); n += 1
+  dt = time.perf_counter() - t0
+  for c in pipes:
+    c.send(None)
+  for pr in procs:
+    pr.join(timeout=5)
+  return {"value": nproc * n / dt, "unit": "env-steps/s", "cores": nproc, "kind": "port",
+          "shape": "SubprocVecEnv: one Python process per core, one env per process, pipes "
+                   "(scripts/vec_env.py:396-459)",
+          "sample": "%s: %d processes x %d env-steps, %.1f s" % (name, nproc, n, dt)}
 
 
 def reference_arm(args):
@@ -379,78 +451,112 @@ def main():
 
   name = args.task
   nenv = args.nenv or WORKLOADS[name]["nenv"]
-  r = run_gpu(name, nenv, args.steps, args.warmup, rank, world, local)
-  ms_total = reduce_max(r["ms_total"]); e2e_s = reduce_max(r["e2e_s"])
-  ms_kernel = reduce_max(r["ms_kernel"])
-  extra = {}
-  if not args.no_extra and name == "cheetah-run":
-    n2 = "humanoid-run"
-    r2 = run_gpu(n2, WORKLOADS[n2]["nenv"], args.steps, args.warmup, rank, world, local)
-    ms2 = reduce_max(r2["ms_total"]); e2 = reduce_max(r2["e2e_s"])
-    extra[n2] = {"value": WORKLOADS[n2]["nenv"] * world * args.steps / (ms2 * 1e-3),
-                 "e2e": WORKLOADS[n2]["nenv"] * world * args.steps / e2,
-                 "unit": "env-steps/s", "envs_per_gpu": WORKLOADS[n2]["nenv"],
-                 "n_sub_steps": r2["nsub"], "ms_per_step": ms2 / args.steps,
-                 "step_kernel_ms": reduce_max(r2["ms_kernel"]), "warnings": r2["warnings"],
-                 "finite": r2["finite"], "stats": r2["stats"], "smem_bytes_per_env": r2["smem"]}
-  if rank != 0:
-    if world > 1:
-      torch.distributed.destroy_process_group()
-    return
   from dm_control_b200 import binding
-  domain = name.split("-")[0]
-  total_envs = nenv * world
-  value = total_envs * args.steps / (ms_total * 1e-3)
-  e2e = total_envs * args.steps / e2e_s
   peaks = {}
   try:
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
   except (OSError, ValueError):
     pass
   hbm_peak = peaks.get("hbm_gbs", 6650.0)
-  algo_bytes = ALGO[domain]["bytes"] * nenv
-  achieved = algo_bytes / (ms_kernel * 1e-3) / 1e9
   fp64_peak = binding.fp64_peak_tflops(local)
-  flops_sub, flops_src = FLOPS_BY_TASK.get(
-      name, (ALGO[domain]["flops"], FLOPS_SOURCE.get(domain, "SURVEY 8d contract estimate v0")))
-  algo_bytes = (2016 if name == "quadruped-walk" else ALGO[domain]["bytes"]) * nenv
-  achieved = algo_bytes / (ms_kernel * 1e-3) / 1e9
-  fl = flops_sub * r["nsub"] * nenv / (ms_kernel * 1e-3) / 1e12
-  traffic, traffic_src = NCU_TRAFFIC.get((name, r["lanes"], nenv), (None, None))
+
+  def measure(task, n_env, scale=1.0):
+    """One workload on every rank; returns the whole-job record (max over ranks)."""
+    r = run_gpu(task, n_env, args.steps, args.warmup, rank, world, local, scale)
+    ms_total = reduce_max(r["ms_total"]); e2e_s = reduce_max(r["e2e_s"])
+    ms_kernel = reduce_max(r["ms_kernel"])
+    domain = task.split("-")[0]
+    key = task if scale == 1.0 else task + "@rest"
+    flops_sub, flops_src = FLOPS_BY_TASK.get(
+        key, FLOPS_BY_TASK.get(task, (ALGO[domain]["flops"],
+                                      FLOPS_SOURCE.get(domain, "SURVEY 8d contract estimate v0"))))
+    algo_bytes = (2016 if task == "quadruped-walk" else ALGO[domain]["bytes"]) * n_env
+    fl = flops_sub * r["nsub"] * n_env / (ms_kernel * 1e-3) / 1e12
+    hb = algo_bytes / (ms_kernel * 1e-3) / 1e9
+    traffic, traffic_src = NCU_TRAFFIC.get((task, r["lanes"], n_env), (None, None))
+    if scale != 1.0:
+      traffic, traffic_src = None, None
+    rec = {
+        "value": n_env * world * args.steps / (ms_total * 1e-3),
+        "e2e": n_env * world * args.steps / e2e_s, "unit": "env-steps/s",
+        "workload": workload_name(task, n_env, r["nsub"], scale),
+        "envs_per_gpu": n_env, "n_sub_steps": r["nsub"], "lanes_per_env": r["lanes"],
+        "ms_per_step": ms_total / args.steps, "step_kernel_ms": ms_kernel,
+        "h2d_bytes_per_step": n_env * r["nu"] * 8, "d2h_bytes_per_step": n_env * (r["nobs"] + 1) * 8,
+        "warnings": r["warnings"], "finite": r["finite"], "stats": r["stats"],
+        "smem_bytes_per_env": r["smem"], "stride": r["stride"], "clocks": r["clocks"],
+        # the binding roofline (SURVEY.md 8d): the FP64 vector pipe
+        "roofline": {"bound": "fp64", "achieved": fl, "peak": fp64_peak, "unit": "TFLOP/s",
+                     "frac": fl / fp64_peak, "traffic": traffic, "traffic_source": traffic_src,
+                     "kernel": "bp_step_kernel", "kernel_ms": ms_kernel,
+                     "flops_per_substep": flops_sub, "flops_source": flops_src,
+                     "peak_source": "DFMA microbenchmark in this run (bp_fp64_peak)"},
+        # secondary: algorithmic bytes (state + obs I/O) against the measured HBM copy peak
+        "roofline_hbm": {"bound": "hbm", "achieved": hb, "peak": hbm_peak, "unit": "GB/s",
+                         "frac": hb / hbm_peak, "algorithmic_bytes_per_launch": algo_bytes,
+                         "image_bytes_per_launch": 2 * n_env * r["stride"] * 8,
+                         "peak_source": "measured" if peaks else "fallback"}}
+    return rec
+
+  main_rec = measure(name, nenv)
+  extra = {}
+  if not args.no_extra and name == "cheetah-run":
+    for task in ("humanoid-run", "walker-walk", "cartpole-swingup", "acrobot-swingup",
+                 "pendulum-swingup", "quadruped-escape", "finger-spin"):
+      extra[task] = measure(task, WORKLOADS[task]["nenv"])
+    # contact-rich variants: small actions, the robots rest on the ground (VERDICT r1 weak 3)
+    for task in ("cheetah-run", "humanoid-run"):
+      extra[task + " (contact-rich)"] = measure(task, WORKLOADS[task]["nenv"], 0.1)
+  # the design's one collective: all-gather of episode statistics over NCCL (sharding.py)
+  gathered = None
+  if world > 1:
+    from dm_control_b200 import sharding
+    st = torch.tensor([main_rec["stats"]["reward_mean"], float(rank)], dtype=torch.float64,
+                      device="cuda:%d" % local)
+    g = sharding.gather_episode_stats(st)
+    gathered = {"ranks_seen": int(g.shape[0]), "rank_ids": [int(x) for x in g[:, 1].tolist()]}
+  if rank != 0:
+    if world > 1:
+      torch.distributed.destroy_process_group()
+    return
+  r = main_rec
   line = {
-      "metric": "env-steps/sec (%s)" % name, "value": value, "unit": "env-steps/s",
+      "metric": "env-steps/sec (%s)" % name, "value": r["value"], "unit": "env-steps/s",
       "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-      "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+      "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
       "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-      "config": {"workload": workload_name(name, nenv, r["nsub"]),
-                 "envs_per_gpu": nenv, "n_sub_steps": r["nsub"],
+      "config": {"workload": r["workload"],
+                 "envs_per_gpu": nenv, "n_sub_steps": r["n_sub_steps"],
                  "l2": "per-GPU image %.0f MB > 126 MB L2 (inputs larger than L2)"
                        % (nenv * r["stride"] * 8 / 1e6),
-                 "smem_bytes_per_env": r["smem"], "lanes_per_env": r["lanes"]},
-      "e2e": {"value": e2e, "unit": "env-steps/s",
-              "h2d_bytes_per_step": nenv * r["nu"] * 8,
-              "d2h_bytes_per_step": nenv * (r["nobs"] + 1) * 8},
+                 "smem_bytes_per_env": r["smem_bytes_per_env"],
+                 "lanes_per_env": r["lanes_per_env"]},
+      "e2e": {"value": r["e2e"], "unit": "env-steps/s",
+              "h2d_bytes_per_step": r["h2d_bytes_per_step"],
+              "d2h_bytes_per_step": r["d2h_bytes_per_step"]},
       # per env-step: ONE bp_step_kernel launch (ctrl scatter and obs / reward are fused in)
       "gpu_launches": args.steps * world,
       "clocks": r["clocks"],
-      "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                   "frac": achieved / hbm_peak, "traffic": traffic,
-                   "traffic_source": traffic_src,
-                   "peak_source": "measured" if peaks else "fallback",
-                   "kernel": "bp_step_kernel", "kernel_ms": ms_kernel,
-                   "algorithmic_bytes_per_launch": algo_bytes,
-                   "image_bytes_per_launch": 2 * nenv * r["stride"] * 8},
-      "roofline_fp64": {"bound": "fp64 vector pipe", "achieved": fl, "peak": fp64_peak,
-                        "unit": "TFLOP/s", "frac": fl / fp64_peak,
-                        "flops_per_substep": flops_sub,
-                        "flops_source": flops_src,
-                        "note": "peak = DFMA microbenchmark in this run"},
-      "physics_steps_per_s": value * r["nsub"],
+      "roofline": r["roofline"], "roofline_hbm": r["roofline_hbm"],
+      "physics_steps_per_s": r["value"] * r["n_sub_steps"],
       "warnings": r["warnings"], "finite": r["finite"], "stats": r["stats"],
       "extra": extra,
   }
+  if gathered is not None:
+    line["episode_stats_allgather"] = gathered
   if world == 1 and not args.no_cpu:
     line["cpu_baseline"] = cpu_baseline(name)
+    line["cpu_baseline_python_vecenv"] = cpu_python_vecenv(name)
+    line["vs_cpu"] = {"e2e_over_c_loop": line["e2e"]["value"] / line["cpu_baseline"]["value"],
+                      "e2e_over_python_vecenv":
+                          line["e2e"]["value"] / line["cpu_baseline_python_vecenv"]["value"]}
+    if "humanoid-run" in extra:      # the other half of the metric gets the same anchors
+      h = extra["humanoid-run"]
+      h["cpu_baseline"] = cpu_baseline("humanoid-run", budget_s=12.0)
+      h["cpu_baseline_python_vecenv"] = cpu_python_vecenv("humanoid-run", budget_s=5.0)
+      h["vs_cpu"] = {"e2e_over_c_loop": h["e2e"] / h["cpu_baseline"]["value"],
+                     "e2e_over_python_vecenv":
+                         h["e2e"] / h["cpu_baseline_python_vecenv"]["value"]}
   print(json.dumps(line), file=_JSON_OUT or sys.stdout)
   (_JSON_OUT or sys.stdout).flush()
   if world > 1:

@@ -29,7 +29,12 @@ WORK = {"cheetah-run": 200, "walker-walk": 500, "humanoid-run": 500, "hopper-hop
         "cartpole-swingup": 0, "acrobot-swingup": 0, "pendulum-swingup": 0}
 
 
-def main(nenv=32, steps=200):
+# r2: the contact-rich variants of the bench (actions 0.1 * U(-1, 1): the robots rest on the
+# ground) -> profiles/r2_oracle_opcount.json
+WORK_REST = {"cheetah-run@rest": 400, "humanoid-run@rest": 500}
+
+
+def main(nenv=32, steps=200, work=WORK, scale=1.0, out_name="r1_oracle_opcount.json"):
   so = os.path.join(ROOT, "oracle", "_build", "liboracle_ops.so")
   subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "oracle"),
                          "_build/liboracle_ops.so"])
@@ -40,7 +45,8 @@ def main(nenv=32, steps=200):
   import bench
   from dm_control_b200.suite import tasks as T
   out = {}
-  for name, settle in WORK.items():
+  for key, settle in work.items():
+    name = key.split("@")[0]
     tdef, m = bench.load_task(name)
     nsub = T.n_sub_steps(tdef, m)
     qpos = bench.initial_state(name, m, nenv, 0)
@@ -56,7 +62,7 @@ def main(nenv=32, steps=200):
       o.reset(); o.qpos[:] = qpos[e]; o.forward()
       for k in range(settle + steps):
         if k % nsub == 0:
-          o.ctrl[:] = rng.uniform(-1, 1, m.nu)
+          o.ctrl[:] = scale * rng.uniform(-1, 1, m.nu)
         if k == settle:
           L.o_opcount_reset()
         o.step()
@@ -68,19 +74,22 @@ def main(nenv=32, steps=200):
     per = tot / (nenv * steps)
     flops = float(per[:5].sum())
     st = stats / (nenv * steps)
-    out[name] = {"flops_per_substep": flops, "nsub": nsub,
+    out[key] = {"flops_per_substep": flops, "nsub": nsub,
                  "flops_per_env_step": flops * nsub,
                  "classes": dict(zip(CLASSES, [float(x) for x in per])),
                  "mean_ncon": float(st[0]), "mean_nefc": float(st[1]),
                  "mean_solver_iter": float(st[2]),
                  "sample": "%d envs x %d sub-steps after %d settle sub-steps" % (nenv, steps, settle)}
     print("%-18s %10.0f flops/sub-step  (add %.0f mul %.0f div %.0f sqrt %.0f trans %.0f) "
-          "ncon %.2f nefc %.2f iter %.2f" % ((name, flops) + tuple(per[:5]) + tuple(st)))
-  path = os.path.join(ROOT, "profiles", "r1_oracle_opcount.json")
+          "ncon %.2f nefc %.2f iter %.2f" % ((key, flops) + tuple(per[:5]) + tuple(st)))
+  path = os.path.join(ROOT, "profiles", out_name)
   with open(path, "w") as f:
     json.dump(out, f, indent=1, sort_keys=True)
   print("wrote", path)
 
 
 if __name__ == "__main__":
-  main()
+  if "--rest" in sys.argv:
+    main(work=WORK_REST, scale=0.1, out_name="r2_oracle_opcount.json")
+  else:
+    main()
