@@ -323,6 +323,8 @@ def _vecenv_worker(conn, name, seed):
   o.forward()
   fields = ("qpos", "qvel", "ctrl", "xmat", "xpos", "xquat", "site_xpos", "site_xmat",
             "sensordata", "subtree_com", "geom_xpos", "act", "cvel", "xipos")
+  _, fp = tdef.params(m)
+  speed = fp[0] if tdef.domain in ("walker", "humanoid", "quadruped", "humanoid_CMU") else None
   while True:
     a = conn.recv()
     if a is None:
@@ -331,7 +333,7 @@ def _vecenv_worker(conn, name, seed):
     for _ in range(nsub):
       o.step()
     d = {f: np.array(getattr(o, f), dtype=np.float64).reshape(1, -1) for f in fields}
-    obs, r = task_oracle.obs_reward(tdef.domain, tdef.task, m, d)
+    obs, r = task_oracle.obs_reward(tdef.domain, tdef.task, m, d, speed)
     conn.send((obs[0], float(r[0])))
   conn.close()
 
