@@ -513,8 +513,8 @@ def main():
   gathered = None
   if world > 1:
     from dm_control_b200 import sharding
-    st = torch.tensor([main_rec["stats"]["reward_mean"], float(rank)], dtype=torch.float64,
-                      device="cuda:%d" % local)
+    st = torch.tensor([[main_rec["stats"]["reward_mean"], float(rank)]], dtype=torch.float64,
+                      device="cuda:%d" % local)          # one row of statistics per rank
     g = sharding.gather_episode_stats(st)
     gathered = {"ranks_seen": int(g.shape[0]), "rank_ids": [int(x) for x in g[:, 1].tolist()]}
   if rank != 0:

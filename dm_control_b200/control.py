@@ -52,12 +52,16 @@ class Environment:
       self._n_sub_steps = 1
     self._step_limit = float("inf") if time_limit == float("inf") else \
         time_limit / (physics.timestep() * self._n_sub_steps)
-    self._step_count = 0
-    self._reset_next_step = True
     task.bind(physics)
     n = physics.nenv
+    # per-env episode clocks: an env is reset on the step after ITS LAST (control.py:97-98)
+    self._step_count = np.zeros(n, dtype=np.int64)
+    self._reset_next = np.ones(n, dtype=bool)
     self._obs = np.empty((n, task.nobs), dtype=np.float64)
     self._rew = np.empty((n,), dtype=np.float64)
+    # Physics.check_invalid_state every k-th step (and at every episode end): a sync and a
+    # [nenv, 8] device read each time (SURVEY.md 8b "lazy / every-k checking")
+    self.check_every = 1
 
   @property
   def nenv(self): return self._physics.nenv
@@ -76,9 +80,9 @@ class Environment:
     return flatten_observation(obs) if self._flat_observation else obs
 
   def reset(self):
-    """control.py:77-92."""
-    self._reset_next_step = False
-    self._step_count = 0
+    """control.py:77-92 for the whole batch."""
+    self._reset_next[:] = False
+    self._step_count[:] = 0
     with self._physics.reset_context():
       self._task.initialize_episode(self._physics)
     self._physics._batch.obs_reward_host(self._obs, self._rew)
@@ -86,35 +90,62 @@ class Environment:
     return specs.TimeStep(np.full(n, specs.StepType.FIRST, dtype=np.int32), None, None,
                           self._observation(self._obs))
 
+  def reset_envs(self, mask):
+    """Resets the envs of `mask` only (masked mj_resetData + the task's initialize_episode
+    for those envs, each from its own generator); the others keep their state.  Returns the
+    flat observation array [nenv, nobs] with the reset envs' rows renewed."""
+    mask = np.asarray(mask, dtype=bool)
+    if mask.any():
+      with self._physics.reset_context(mask=mask):
+        self._task.initialize_episode(self._physics, mask)
+      self._physics._batch.obs_reward_host(self._obs, self._rew)
+      self._step_count[mask] = 0
+      self._reset_next[mask] = False
+    return self._obs
+
   def step(self, action):
-    """control.py:94-123 for every env; `action` is [nenv, nu]."""
-    if self._reset_next_step:
+    """control.py:94-123 for every env; `action` is [nenv, nu].  An env whose previous
+    TimeStep was LAST is reset instead of stepped (its action is ignored) and returns FIRST
+    with reward and discount NaN (the reference's None); the others step normally."""
+    if self._reset_next.all():
       return self.reset()
     action = np.ascontiguousarray(
         np.broadcast_to(np.asarray(action, dtype=np.float64),
                         (self.nenv, self._physics.model.nu)))
-    self._physics._batch.env_step_host(self._n_sub_steps, action, self._obs, self._rew)
-    self._physics.check_invalid_state()
-    self._step_count += 1
+    first = self._reset_next.copy()
+    batch = self._physics._batch
+    if first.any():
+      self.reset_envs(first)
+      batch.set_mask(~first)               # only the running envs take the step
+      try:
+        batch.env_step_host(self._n_sub_steps, action, self._obs, self._rew)
+      finally:
+        batch.set_mask(None)
+      batch.obs_reward_host(self._obs, self._rew)     # rows of every env, reset ones included
+    else:
+      batch.env_step_host(self._n_sub_steps, action, self._obs, self._rew)
+    running = ~first
+    self._step_count[running] += 1
     n = self.nenv
     reward = self._rew.copy()
     obs = self._observation(self._obs)
-    if self._step_count >= self._step_limit:
-      self._reset_next_step = True
-      return specs.TimeStep(np.full(n, specs.StepType.LAST, dtype=np.int32), reward,
-                            np.ones(n), obs)
     step_type = np.full(n, specs.StepType.MID, dtype=np.int32)
     discount = np.ones(n)
-    # control.py:110-117 get_termination: a discount ends the episode of THAT env (LAST,
-    # discount as returned).  The batch is reset as a whole once every env has terminated;
-    # until then a terminated env keeps stepping.
+    timeout = running & (self._step_count >= self._step_limit)
+    step_type[timeout] = specs.StepType.LAST
+    # control.py:110-117 get_termination: a discount ends the episode of THAT env
     terminal = self._task.get_termination(self._physics, self._obs)
     if terminal is not None:
-      done = ~np.isnan(terminal)
+      done = running & ~np.isnan(terminal) & ~timeout
       step_type[done] = specs.StepType.LAST
       discount[done] = terminal[done]
-      if done.all():
-        self._reset_next_step = True
+    last = step_type == specs.StepType.LAST
+    self._reset_next |= last
+    step_type[first] = specs.StepType.FIRST
+    reward[first] = np.nan
+    discount[first] = np.nan
+    if last.any() or self.check_every <= 1 or int(self._step_count.max()) % self.check_every == 0:
+      self._physics.check_invalid_state()
     return specs.TimeStep(step_type, reward, discount, obs)
 
   def action_spec(self):

@@ -64,7 +64,15 @@ class _Data:
     a = np.asarray(value, dtype=b.fields[name][2])
     if a.ndim == 0 or a.shape == (cnt,):
       a = np.broadcast_to(a.reshape(-1) if a.ndim else a, (b.nenv, cnt))
-    b.write(name, np.ascontiguousarray(a).reshape(b.nenv, cnt))
+    a = np.ascontiguousarray(a).reshape(b.nenv, cnt)
+    mask = self._p._reset_mask
+    if mask is not None and cnt:
+      # inside reset_context(mask=...): only the envs being reset are written
+      cur = b.read(name)
+      rows = np.asarray(mask, dtype=bool)
+      cur[rows] = a[rows]
+      a = cur
+    b.write(name, a)
 
 
 class _Named:
@@ -112,13 +120,25 @@ class BatchedPhysics:
     self.data.ctrl = c
 
   def step(self, n_sub_steps=1):
-    """Physics.step() of engine.py:149-166, `n_sub_steps` times in one launch."""
-    self._batch.step(int(n_sub_steps))
+    """Physics.step() of engine.py:149-166, `n_sub_steps` times in one launch.  Inside
+    reset_context(mask=...) only the envs being reset advance (cheetah.py:73-75 settles the
+    model inside initialize_episode)."""
+    self._masked(lambda: self._batch.step(int(n_sub_steps)))
     self.check_invalid_state()
 
   def forward(self):
-    self._batch.forward(False)
+    self._masked(lambda: self._batch.forward(False))
     self.check_invalid_state()
+
+  def _masked(self, call):
+    if self._reset_mask is None:
+      return call()
+    self._batch.set_mask(self._reset_mask)
+    try:
+      call()
+      self._batch.sync()
+    finally:
+      self._batch.set_mask(None)
 
   def reset(self, keyframe_id=None, mask=None):
     """engine.py:268-289: mj_resetData(+Keyframe), then forward with actuation
@@ -201,7 +221,13 @@ class BatchedPhysics:
   def set_env_model_field(self, name, value, env0=0):
     """Per-env run-time model edit (reacher.py:96-101 `geom_pos['target']`): value is
     [n, ...] with the model field's trailing shape; supported: geom_pos, site_pos,
-    body_pos, body_quat (manipulator.py:218-224)."""
+    body_pos, body_quat (manipulator.py:218-224).  Inside reset_context(mask=...) a
+    full-batch value only reaches the envs being reset."""
+    if self._reset_mask is not None and env0 == 0 and len(value) == self.nenv:
+      cur = self._batch.read_env_model(name)
+      rows = np.asarray(self._reset_mask, dtype=bool)
+      cur[rows] = np.asarray(value, dtype=np.float64).reshape(cur.shape)[rows]
+      value = cur
     self._batch.write_env_model(name, value, env0)
 
   def env_model_field(self, name):

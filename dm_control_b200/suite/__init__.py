@@ -51,6 +51,7 @@ class Task:
     self.tdef = tdef
     self._seed = random
     self._rngs = None
+    self._mask = None
     self.scalar_obs = {"height", "head_height", "torso_upright", "dist_to_target"}
 
   def bind(self, physics):
@@ -81,7 +82,26 @@ class Task:
     from dm_control_b200.suite import lqr
     return np.where(np.linalg.norm(obs, axis=1) < lqr.TERMINAL_TOL, 0.0, np.nan)
 
-  def initialize_episode(self, physics):
+  def _each(self):
+    """(env, generator) of the envs this initialisation covers (all, or the masked ones)."""
+    if self._mask is None:
+      return list(enumerate(self._rngs))
+    return [(int(e), self._rngs[e]) for e in np.flatnonzero(self._mask)]
+
+  def _todo(self, n):
+    return np.ones(n, dtype=bool) if self._mask is None else self._mask.copy()
+
+  def initialize_episode(self, physics, mask=None):
+    """`mask` ([nenv] bool): per-env auto-reset -- only those envs draw from their
+    generators and are written (the caller holds physics.reset_context(mask=mask), inside
+    which data writes, model-frame writes and steps reach the masked envs only)."""
+    self._mask = None if mask is None else np.asarray(mask, dtype=bool)
+    try:
+      self._initialize_episode(physics)
+    finally:
+      self._mask = None
+
+  def _initialize_episode(self, physics):
     m = physics.model
     n = physics.nenv
     qpos = physics.data.qpos
@@ -90,7 +110,7 @@ class Task:
     if d == "cartpole":           # suite/cartpole.py:177-195
       sl = m.jnt_qposadr[m.name2id("slider", "joint")]
       h1 = m.jnt_qposadr[m.name2id("hinge_1", "joint")]
-      for e, rng in enumerate(self._rngs):
+      for e, rng in self._each():
         if t.startswith("swingup") or t.endswith("_poles"):
           qpos[e, sl] = .01 * rng.randn()
           qpos[e, h1] = np.pi + .01 * rng.randn()
@@ -101,16 +121,16 @@ class Task:
         qvel[e] = 0.01 * rng.randn(m.nv)
     elif d == "acrobot":          # suite/acrobot.py:96-106
       ids = [m.jnt_qposadr[m.name2id(k, "joint")] for k in ("shoulder", "elbow")]
-      for e, rng in enumerate(self._rngs):
+      for e, rng in self._each():
         qpos[e, ids] = rng.uniform(-np.pi, np.pi, 2)
     elif d == "pendulum":         # suite/pendulum.py:80-90
       h = m.jnt_qposadr[m.name2id("hinge", "joint")]
-      for e, rng in enumerate(self._rngs):
+      for e, rng in self._each():
         qpos[e, h] = rng.uniform(-np.pi, np.pi)
     elif d == "cheetah":          # suite/cheetah.py:63-77
       lim = m.jnt_limited == 1
       lo, hi = m.jnt_range[lim].T
-      for e, rng in enumerate(self._rngs):
+      for e, rng in self._each():
         qpos[e, lim] = rng.uniform(lo, hi)
       physics.data.qpos = qpos
       physics.after_reset()                 # derived quantities for the settle steps
@@ -119,16 +139,16 @@ class Task:
       physics.data.time = 0.0
       return
     elif d == "hopper":           # suite/hopper.py:116-120
-      for e, rng in enumerate(self._rngs):
+      for e, rng in self._each():
         _randomize_limited_and_rotational_joints(m, qpos[e], rng)
     elif d == "walker":           # suite/walker.py:118-129
-      for e, rng in enumerate(self._rngs):
+      for e, rng in self._each():
         _randomize_limited_and_rotational_joints(m, qpos[e], rng)
     elif d == "quadruped":
       self._initialize_quadruped(physics, t)
       return
     elif d == "point_mass":       # suite/point_mass.py:85-107 (easy: fixed gains)
-      for e, rng in enumerate(self._rngs):
+      for e, rng in self._each():
         _randomize_limited_and_rotational_joints(m, qpos[e], rng)
     elif d == "reacher":          # suite/reacher.py:91-103
       tgt = m.name2id("target", "geom")
@@ -136,7 +156,7 @@ class Task:
       size[tgt, 0] = .05 if t == "easy" else .015
       physics.set_model_field("geom_size", size)
       gpos = np.tile(np.asarray(m.geom_pos, dtype=np.float64), (n, 1, 1))
-      for e, rng in enumerate(self._rngs):
+      for e, rng in self._each():
         _randomize_limited_and_rotational_joints(m, qpos[e], rng)
         angle = rng.uniform(0, 2 * np.pi)
         radius = rng.uniform(.05, .20)
@@ -146,7 +166,7 @@ class Task:
     elif d == "swimmer":          # suite/swimmer.py:176-197
       tgt = m.name2id("target", "geom")
       gpos = np.tile(np.asarray(m.geom_pos, dtype=np.float64), (n, 1, 1))
-      for e, rng in enumerate(self._rngs):
+      for e, rng in self._each():
         _randomize_limited_and_rotational_joints(m, qpos[e], rng)
         close_target = rng.rand() < .2
         target_box = .3 if close_target else 2
@@ -158,7 +178,7 @@ class Task:
     elif d == "ball_in_cup":      # suite/ball_in_cup.py:69-84: a ball position without contacts
       bx = m.jnt_qposadr[m.name2id("ball_x", "joint")]
       bz = m.jnt_qposadr[m.name2id("ball_z", "joint")]
-      todo = np.ones(n, dtype=bool)
+      todo = self._todo(n)
       while todo.any():
         for e in np.flatnonzero(todo):
           qpos[e, bx] = self._rngs[e].uniform(-.2, .2)
@@ -171,7 +191,7 @@ class Task:
       tgt = m.name2id("target", "geom")
       root = m.jnt_qposadr[m.name2id("root", "joint")]
       gpos = np.tile(np.asarray(m.geom_pos, dtype=np.float64), (n, 1, 1))
-      for e, rng in enumerate(self._rngs):
+      for e, rng in self._each():
         quat = rng.randn(4)
         qpos[e, root + 3:root + 7] = quat / np.linalg.norm(quat)
         for j in range(7):
@@ -183,7 +203,7 @@ class Task:
       if t == "swim":
         physics.set_env_model_field("geom_pos", gpos)
     elif d == "lqr":              # suite/lqr.py:229-233: a random point of a sphere
-      for e, rng in enumerate(self._rngs):
+      for e, rng in self._each():
         unit = rng.randn(m.nq)
         qpos[e] = np.sqrt(2) * unit / np.linalg.norm(unit)
     elif d in ("humanoid", "finger", "humanoid_CMU"):
@@ -198,7 +218,7 @@ class Task:
         radius = float(np.sum(m.geom_size[m.name2id("cap1", "geom")]))
         tgt = m.name2id("target", "site")
         spos = np.tile(np.asarray(m.site_pos, dtype=np.float64), (n, 1, 1))
-        for e, rng in enumerate(self._rngs):
+        for e, rng in self._each():
           angle = rng.uniform(-np.pi, np.pi)
           spos[e, tgt, 0] = anchor[e, 0] + radius * np.sin(angle)
           spos[e, tgt, 2] = anchor[e, 2] + radius * np.cos(angle)
@@ -206,7 +226,7 @@ class Task:
         size = np.array(m.site_size, dtype=np.float64)
         size[tgt, 0] = self.tdef.params(m)[1][1]
         physics.set_model_field("site_size", size)
-      todo = np.ones(n, dtype=bool)
+      todo = self._todo(n)
       while todo.any():
         for e in np.flatnonzero(todo):
           _randomize_limited_and_rotational_joints(m, qpos[e], self._rngs[e])
@@ -238,7 +258,7 @@ def _initialize_manipulator(self, physics, qpos, qvel):
   grasp = m.name2id("grasp", "site")
   bpos = np.tile(np.asarray(m.body_pos, dtype=np.float64), (n, 1, 1))
   bquat = np.tile(np.asarray(m.body_quat, dtype=np.float64), (n, 1, 1))
-  todo = np.ones(n, dtype=bool)
+  todo = self._todo(n)
   while todo.any():
     idx = np.flatnonzero(todo)
     kind, pose = {}, {}
@@ -298,23 +318,31 @@ def _initialize_quadruped(self, physics, task_name):
   that still touch something by 1 cm per pass."""
   m, n = physics.model, physics.nenv
   if task_name == "escape":
-    terrain = np.stack([_escape_terrain(m, rng) for rng in self._rngs])
-    physics.set_hfield(terrain)
+    if self._mask is None:
+      physics.set_hfield(np.stack([_escape_terrain(m, rng) for rng in self._rngs]))
+    else:
+      for e, rng in self._each():
+        physics.set_hfield(_escape_terrain(m, rng)[None], env0=e)
   xy = np.zeros((n, 2))
   if task_name == "fetch":              # quadruped.py:431-436: random azimuth and position
     spawn_radius = 0.9 * m.geom_size[m.name2id("floor", "geom"), 0]
     orientation = np.zeros((n, 4))
-    for e, rng in enumerate(self._rngs):
+    for e, rng in self._each():
       azimuth = rng.uniform(0, 2 * np.pi)
       orientation[e] = (np.cos(azimuth / 2), 0, 0, np.sin(azimuth / 2))
       xy[e] = rng.uniform(-spawn_radius, spawn_radius, size=(2,))
   else:
-    orientation = np.stack([rng.randn(4) for rng in self._rngs])
+    orientation = np.tile([1.0, 0, 0, 0], (n, 1))
+    for e, rng in self._each():
+      orientation[e] = rng.randn(4)
     orientation /= np.linalg.norm(orientation, axis=1, keepdims=True)
   root = m.jnt_qposadr[m.name2id("root", "joint")]
   qpos = np.tile(np.asarray(m.qpos0, dtype=np.float64), (n, 1))
+  if self._mask is not None:            # the other envs keep their state
+    cur = physics.data.qpos
+    qpos[~self._mask] = cur[~self._mask]
   z = np.zeros(n)                       # start embedded in the floor
-  todo = np.ones(n, dtype=bool)
+  todo = self._todo(n)
   for _ in range(10001):
     qpos[:, root:root + 3] = np.stack([xy[:, 0], xy[:, 1], z], axis=1)
     qpos[:, root + 3:root + 7] = orientation
@@ -330,7 +358,7 @@ def _initialize_quadruped(self, physics, task_name):
         ball = m.jnt_qposadr[m.name2id("ball_root", "joint")]
         ballv = m.jnt_dofadr[m.name2id("ball_root", "joint")]
         qvel = np.zeros((n, m.nv))
-        for e, rng in enumerate(self._rngs):
+        for e, rng in self._each():
           qpos[e, ball:ball + 2] = rng.uniform(-spawn_radius, spawn_radius, size=(2,))
           qpos[e, ball + 2] = 2
           qvel[e, ballv:ballv + 2] = 5 * rng.randn(2)

@@ -118,8 +118,10 @@ def _flat(observation):
 
 
 class BatchedVecEnv:
-  """`VecEnv`-style facade over one batched Environment (all envs share the episode
-  clock, so every env of the batch finishes — and is reset — on the same step)."""
+  """`VecEnv`-style facade over one batched Environment (scripts/vec_env.py:22-194).  Every
+  env has its own episode clock: an env that finishes is reset on the spot -- and only that
+  env -- its last observation goes to infos[i]["terminal_observation"] and the returned
+  observation row is the first of its next episode (vec_env.py:346-352)."""
 
   def __init__(self, env):
     self._env = env
@@ -152,10 +154,11 @@ class BatchedVecEnv:
     reward = np.zeros(n) if ts.reward is None else np.asarray(ts.reward, dtype=np.float64)
     done = np.asarray(ts.step_type) == specs.StepType.LAST
     infos = [{} for _ in range(n)]
-    if done.any():                       # vec_env.py:347-352
+    if done.any():                       # vec_env.py:347-352: only the envs that are done
       for i in np.flatnonzero(done):
         infos[i]["terminal_observation"] = obs[i].copy()
-      obs = _flat(self._env.reset().observation)
+      obs = obs.copy()
+      obs[done] = self._env.reset_envs(done)[done]
     return obs, reward, done, infos
 
   def step(self, actions):
@@ -194,3 +197,91 @@ class BatchedVecEnv:
   @property
   def unwrapped(self):
     return self
+
+
+class TorchVecEnv:
+  """Device-resident VecEnv for learners that keep their data on the GPU (the fork's PPO,
+  scripts/rl/ppo/ppo.py, consumes SubprocVecEnv output as torch tensors): actions come in as
+  a CUDA float64 tensor [num_envs, nu] and observations / rewards / dones go out as CUDA
+  tensors -- no host copy of either on the step path.  One `bp_env_step` launch per step on
+  the batch's stream, ordered against torch's current stream with stream waits.
+
+  Episode ends: time limits are counted on the host (no device read); a task with its own
+  termination (lqr) is checked on the device and read back as one flag.  Envs that are done
+  are reset on the spot -- only those -- by the task's own initialize_episode on the host
+  (per-env generators); `terminal_observation` is returned as a tensor [num_envs, nobs]
+  whose rows are valid where `done` is set.  Physics.check_invalid_state runs every
+  `check_every` steps and at every episode end."""
+
+  def __init__(self, env, check_every=100):
+    import torch
+    self._torch = torch
+    self._env = env
+    self.num_envs = env.nenv
+    self.action_space = env.action_spec()
+    self.observation_space = env.observation_spec()
+    self.check_every = int(check_every)
+    physics = env.physics
+    self._batch = physics._batch
+    self._dev = torch.device("cuda", physics._dev_model.device)
+    n = self.num_envs
+    self._obs = torch.empty((n, env.task.nobs), dtype=torch.float64, device=self._dev)
+    self._rew = torch.empty((n,), dtype=torch.float64, device=self._dev)
+    self._stream = torch.cuda.ExternalStream(self._batch.stream, device=self._dev)
+    self._steps = 0
+    self.closed = False
+
+  def _sync_out(self):
+    self._torch.cuda.current_stream(self._dev).wait_stream(self._stream)
+
+  def _observe(self):
+    self._stream.wait_stream(self._torch.cuda.current_stream(self._dev))
+    self._batch.obs_reward(self._obs.data_ptr() if self._obs.numel() else None,
+                           self._rew.data_ptr())
+    self._sync_out()
+
+  def reset(self):
+    self._env.reset()
+    self._observe()
+    return self._obs.clone()
+
+  def step(self, actions):
+    torch = self._torch
+    env = self._env
+    if actions.shape != (self.num_envs,) + tuple(self.action_space.shape):
+      raise ValueError("actions have shape {}, expected {}".format(
+          tuple(actions.shape), (self.num_envs,) + tuple(self.action_space.shape)))
+    if actions.device != self._dev or actions.dtype != torch.float64 or \
+        not actions.is_contiguous():
+      actions = actions.to(device=self._dev, dtype=torch.float64).contiguous()
+    self._stream.wait_stream(torch.cuda.current_stream(self._dev))
+    self._batch.env_step(env._n_sub_steps, actions.data_ptr(),
+                         self._obs.data_ptr() if self._obs.numel() else None,
+                         self._rew.data_ptr())
+    self._sync_out()
+    actions.record_stream(self._stream)
+    self._steps += 1
+    env._step_count += 1
+    done_host = env._step_count >= env._step_limit
+    obs, reward = self._obs.clone(), self._rew.clone()
+    done = torch.as_tensor(done_host, device=self._dev)
+    if env.task.tdef.domain == "lqr":                 # task termination: checked on the device
+      from dm_control_b200.suite import lqr
+      term = torch.linalg.vector_norm(obs, dim=1) < lqr.TERMINAL_TOL
+      if bool(term.any()):                             # one flag crosses to the host
+        done = done | term
+        done_host = done.cpu().numpy()
+    terminal_observation = obs
+    if done_host.any() or self._steps % self.check_every == 0:
+      env.physics.check_invalid_state()
+    if done_host.any():
+      env.reset_envs(done_host)                        # masked reset, host-side episode init
+      self._observe()
+      rows = torch.as_tensor(done_host, device=self._dev)
+      obs = torch.where(rows[:, None], self._obs, obs)
+    return obs, reward, done, terminal_observation
+
+  def close(self):
+    if not self.closed:
+      self._env.close()
+      self.closed = True

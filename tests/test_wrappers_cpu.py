@@ -11,12 +11,14 @@ from dm_control_b200 import specs, wrappers
 
 
 class FakeEnv:
-  """Batched env with an episode of `length` steps; records the actions it receives."""
+  """Batched env with per-env episodes of `length[e]` steps; records the actions it gets."""
 
   def __init__(self, nenv=3, nu=2, length=3, lo=-2.0, hi=4.0):
-    self.nenv, self.nu, self.length = nenv, nu, length
+    self.nenv, self.nu = nenv, nu
+    self.length = np.broadcast_to(np.asarray(length), (nenv,)).copy()
     self._spec = specs.BoundedArray((nu,), np.float64, lo, hi, name="action")
     self.actions, self.resets, self._t = [], 0, None
+    self.env_resets = np.zeros(nenv, dtype=int)
     self.task = type("T", (), {"_seed": None, "_rngs": None})()
     self.closed = False
 
@@ -28,20 +30,27 @@ class FakeEnv:
 
   def _obs(self):
     base = np.arange(self.nenv, dtype=np.float64)[:, None]
-    return collections.OrderedDict(position=np.concatenate([base, base + self._t], axis=1),
+    return collections.OrderedDict(position=np.concatenate([base, base + self._t[:, None]], axis=1),
                                    height=base[:, 0] * 10 + self._t)
 
   def reset(self):
-    self.resets += 1; self._t = 0
+    self.resets += 1; self._t = np.zeros(self.nenv)
+    self.env_resets += 1
     return specs.TimeStep(np.full(self.nenv, specs.StepType.FIRST), None, None, self._obs())
 
+  def reset_envs(self, mask):
+    mask = np.asarray(mask, dtype=bool)
+    self._t[mask] = 0
+    self.env_resets[mask] += 1
+    o = self._obs()
+    return np.concatenate([np.asarray(v).reshape(self.nenv, -1) for v in o.values()], axis=1)
+
   def step(self, action):
-    if self._t is None or self._t >= self.length:
+    if self._t is None:
       return self.reset()
-    self.actions.append(np.array(action)); self._t += 1
-    st = specs.StepType.LAST if self._t >= self.length else specs.StepType.MID
-    return specs.TimeStep(np.full(self.nenv, st), np.full(self.nenv, 0.5 * self._t),
-                          np.ones(self.nenv), self._obs())
+    self.actions.append(np.array(action)); self._t = self._t + 1
+    st = np.where(self._t >= self.length, specs.StepType.LAST, specs.StepType.MID)
+    return specs.TimeStep(st, 0.5 * self._t, np.ones(self.nenv), self._obs())
 
   def close(self): self.closed = True
 
@@ -112,7 +121,7 @@ def test_vec_env_auto_reset_and_terminal_observation():
   # final observation is handed back in info, the returned one is the reset observation
   np.testing.assert_array_equal(infos[1]["terminal_observation"], [1.0, 3.0, 12.0])
   np.testing.assert_array_equal(obs[1], [1.0, 1.0, 10.0])
-  assert env.resets == 2
+  assert env.resets == 1 and env.env_resets.tolist() == [2, 2, 2]
   with pytest.raises(RuntimeError):
     v.step_wait()
   with pytest.raises(ValueError):
@@ -121,3 +130,20 @@ def test_vec_env_auto_reset_and_terminal_observation():
   assert v.get_attr("nu") == [2, 2, 2] and v.get_attr("nu", indices=1) == [2]
   v.close()
   assert env.closed and v.closed
+
+
+def test_vec_env_resets_only_the_envs_that_are_done():
+  """scripts/vec_env.py:346-352 is per worker: an env that finishes is reset, the others go on
+  (step_wait used to reset the whole batch when any env was done)."""
+  env = FakeEnv(nenv=3, length=[2, 3, 2])
+  v = wrappers.BatchedVecEnv(env)
+  v.reset()
+  a = np.zeros((3, 2))
+  v.step(a)
+  obs, rew, done, infos = v.step(a)
+  assert done.tolist() == [True, False, True]
+  assert "terminal_observation" in infos[0] and infos[1] == {}
+  np.testing.assert_array_equal(obs[:, 1], [0.0, 3.0, 2.0])      # env 1 is still at t = 2
+  assert env.env_resets.tolist() == [2, 1, 2]
+  obs, rew, done, infos = v.step(a)
+  assert done.tolist() == [False, True, False] and rew.tolist() == [0.5, 1.5, 0.5]
