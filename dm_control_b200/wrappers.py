@@ -258,8 +258,7 @@ class TorchVecEnv:
     self._batch.env_step(env._n_sub_steps, actions.data_ptr(),
                          self._obs.data_ptr() if self._obs.numel() else None,
                          self._rew.data_ptr())
-    self._sync_out()
-    actions.record_stream(self._stream)
+    self._sync_out()      # torch's stream is now ordered after the launch: `actions` may be reused
     self._steps += 1
     env._step_count += 1
     done_host = env._step_count >= env._step_limit
@@ -283,5 +282,7 @@ class TorchVecEnv:
 
   def close(self):
     if not self.closed:
+      self._torch.cuda.synchronize(self._dev)
+      self._stream = None
       self._env.close()
       self.closed = True
