@@ -76,6 +76,9 @@ _SIGNATURES = {
                                             ctypes.c_double, ctypes.c_double, _i32,
                                             ctypes.c_double]),
     "bp_rewards_tolerance_noalloc_max": (_i32, []),
+    "bp_batch_copy": (_i32, [_vp, _vp]),
+    "bp_contact_force": (_i32, [_vp, _i32, _vp]),
+    "bp_object_velocity": (_i32, [_vp, _i32, _i32, _i32, _vp]),
     "bp_warnings": (_i32, [_vp, _vp]),
     "bp_sync": (_i32, [_vp]),
     "bp_batch_stream": (_vp, [_vp]),
@@ -235,6 +238,7 @@ class Batch:
     cnt = self.model.flat.arrays[name].size
     a = np.ascontiguousarray(value, dtype=np.float64).reshape(-1, cnt)
     check(load().bp_env_model_write(self.ptr, name.encode(), _ptr(a), env0, a.shape[0]))
+    self._env_model_written = set(getattr(self, "_env_model_written", ())) | {name}
 
   def read_env_model(self, name, env0=0, n=None):
     n = self.nenv - env0 if n is None else n
@@ -242,6 +246,10 @@ class Batch:
     out = np.empty((n,) + tuple(shape), dtype=np.float64)
     check(load().bp_env_model_read(self.ptr, name.encode(), _ptr(out), env0, n))
     return out
+
+  def has_env_model(self, name):
+    """True once a per-env copy of the model array exists (made on the first write)."""
+    return name in getattr(self, "_env_model_written", ())
 
   def write_hfield(self, data, env0=0):
     """Per-env `model.hfield_data` (quadruped.py:381): data [n, nhfielddata] float32."""
@@ -328,6 +336,26 @@ class Batch:
 
   def env_step_host(self, nsub, ctrl, obs, reward):
     check(load().bp_env_step_host(self.ptr, nsub, _ptr(ctrl), _ptr(obs), _ptr(reward)))
+
+  def copy_from(self, other):
+    """mj_copyData: this batch becomes a bit copy of `other` (same shapes)."""
+    check(load().bp_batch_copy(self.ptr, other.ptr))
+    self.nobs = getattr(other, "nobs", None)
+    self._env_model_written = set(getattr(other, "_env_model_written", ()))
+
+  def contact_force(self, contact_id):
+    """[nenv, 2, 3] (force, torque) of contact `contact_id` in its frame; NaN rows where an
+    env has fewer contacts (wrapper/core.py:747-769)."""
+    out = np.empty((self.nenv, 6), dtype=np.float64)
+    check(load().bp_contact_force(self.ptr, int(contact_id), _ptr(out)))
+    return out.reshape(self.nenv, 2, 3)
+
+  def object_velocity(self, object_id, object_type, local_frame=False):
+    """[nenv, 2, 3] (linear, angular) velocity of an object (wrapper/core.py:713-745)."""
+    out = np.empty((self.nenv, 6), dtype=np.float64)
+    check(load().bp_object_velocity(self.ptr, int(object_type), int(object_id),
+                                    int(bool(local_frame)), _ptr(out)))
+    return out.reshape(self.nenv, 2, 3)[:, ::-1]
 
   def warnings(self):
     out = np.empty((self.nenv, 8), dtype=np.int32)

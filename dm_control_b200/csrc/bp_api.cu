@@ -959,6 +959,89 @@ extern "C" int bp_env_step_host(bp_batch* b, int nsub, const double* ctrl_host,
   return BP_OK;
 }
 
+// mj_copyData (wrapper/core.py:653-685 MjData.copy / engine.py:332-339 Physics.copy): every
+// env image, the per-env model arrays (height fields, frames) and the bound task of `src`
+// into `dst`, which must have been created with the same model sizes, nenv, njmax / nconmax
+// and lanes.  Device-to-device; synchronises.
+extern "C" int bp_batch_copy(bp_batch* dst, bp_batch* src) {
+  if (!dst || !src) return fail(BP_EINVAL, "null batch");
+  if (dst->nenv != src->nenv || dst->stride != src->stride || dst->lanes != src->lanes ||
+      dst->L.total != src->L.total || dst->L.persist != src->L.persist ||
+      dst->model->M.nhfielddata != src->model->M.nhfielddata)
+    return fail(BP_EINVAL, "bp_batch_copy: the two batches differ in shape");
+  cudaSetDevice(src->model->device);
+  CUDA_OK(cudaStreamSynchronize(src->stream));
+  CUDA_OK(cudaStreamSynchronize(dst->stream));
+  CUDA_OK(cudaMemcpy(dst->image, src->image, (size_t)src->nenv_alloc * src->stride * 8,
+                     cudaMemcpyDeviceToDevice));
+  if (src->hfield)
+    CUDA_OK(cudaMemcpy(dst->hfield, src->hfield,
+                       (size_t)src->nenv_alloc * src->model->M.nhfielddata * 4,
+                       cudaMemcpyDeviceToDevice));
+  struct { double** d; double** s; int cnt; } slots[] = {
+      {&dst->env_geom_pos, &src->env_geom_pos, 3 * src->model->M.ngeom},
+      {&dst->env_site_pos, &src->env_site_pos, 3 * src->model->M.nsite},
+      {&dst->env_body_pos, &src->env_body_pos, 3 * src->model->M.nbody},
+      {&dst->env_body_quat, &src->env_body_quat, 4 * src->model->M.nbody}};
+  for (auto& sl : slots) {
+    if (!*sl.s) {
+      if (*sl.d) { cudaFree(*sl.d); *sl.d = nullptr; }
+      continue;
+    }
+    size_t bytes = (size_t)src->nenv_alloc * sl.cnt * 8;
+    if (!*sl.d) CUDA_OK(cudaMalloc((void**)sl.d, bytes));
+    CUDA_OK(cudaMemcpy(*sl.d, *sl.s, bytes, cudaMemcpyDeviceToDevice));
+  }
+  dst->task = src->task;
+  return BP_OK;
+}
+
+extern "C" int bp_launch_contact_force(const BpParams* P, int ci, double* out, cudaStream_t stream);
+extern "C" int bp_launch_object_velocity(const BpParams* P, int objtype, int id, int flg_local,
+                                         double* out, cudaStream_t stream);
+
+// [nenv][6] results of a per-env query kernel -> host, through the batch's staging buffer
+static int query6(bp_batch* b, double* out_host, int (*go)(const BpParams*, double*, void*),
+                  void* arg) {
+  cudaSetDevice(b->model->device);
+  size_t bytes = (size_t)b->nenv * 6 * 8;
+  if (bytes > b->stage_bytes) {
+    if (b->stage) { cudaStreamSynchronize(b->stream); cudaFree(b->stage); b->stage = nullptr; }
+    CUDA_OK(cudaMalloc(&b->stage, bytes));
+    b->stage_bytes = bytes;
+  }
+  BpParams P = make_params(b, 0, 0, 0);
+  int e = go(&P, (double*)b->stage, arg);
+  if (e != 0) return fail(BP_ECUDA, std::string("query launch: ") + cudaGetErrorString((cudaError_t)e));
+  CUDA_OK(cudaMemcpyAsync(out_host, b->stage, bytes, cudaMemcpyDeviceToHost, b->stream));
+  CUDA_OK(cudaStreamSynchronize(b->stream));
+  return BP_OK;
+}
+
+extern "C" int bp_contact_force(bp_batch* b, int contact_id, double* out_host) {
+  if (!b || !out_host) return fail(BP_EINVAL, "null argument");
+  if (contact_id < 0 || contact_id >= b->L.nconmax)
+    return fail(BP_EINVAL, "contact_id must be an integer in range [0, " +
+                std::to_string(b->L.nconmax - 1) + "] (inclusive), got: " +
+                std::to_string(contact_id) + ".");
+  struct A { int ci; cudaStream_t s; } a{contact_id, b->stream};
+  return query6(b, out_host, [](const BpParams* P, double* out, void* arg) {
+    A* q = (A*)arg; return bp_launch_contact_force(P, q->ci, out, q->s); }, &a);
+}
+
+extern "C" int bp_object_velocity(bp_batch* b, int objtype, int objid, int flg_local,
+                                  double* out_host) {
+  if (!b || !out_host) return fail(BP_EINVAL, "null argument");
+  const BpModel& M = b->model->M;
+  int n = objtype == OBJ_SITE ? M.nsite : objtype == OBJ_GEOM ? M.ngeom :
+          (objtype == OBJ_BODY || objtype == OBJ_XBODY) ? M.nbody : -1;
+  if (n < 0) return fail(BP_EINVAL, "object type must be body (1), xbody (2), geom (5) or site (6)");
+  if (objid < 0 || objid >= n) return fail(BP_EINVAL, "object id out of range");
+  struct A { int t, id, loc; cudaStream_t s; } a{objtype, objid, flg_local, b->stream};
+  return query6(b, out_host, [](const BpParams* P, double* out, void* arg) {
+    A* q = (A*)arg; return bp_launch_object_velocity(P, q->t, q->id, q->loc, out, q->s); }, &a);
+}
+
 extern "C" int bp_warnings(bp_batch* b, int32_t* out_host) {
   return bp_field_read(b, "warning", out_host, 0, b ? b->nenv : 0);
 }

@@ -162,3 +162,88 @@ extern "C" int bp_launch_tolerance(const double* x, double* out, long long n, do
                                                                      margin, sig, v1);
   return (int)cudaGetLastError();
 }
+
+// mj_contactForce / mj_objectVelocity for every env of the batch (wrapper/core.py:713-769):
+// one thread per env reads its image.
+__device__ __forceinline__ const int* bp_env_ints(const BpParams& P, long long env) {
+  const long long S = P.interleave;
+  return (const int*)(P.image + (env / S) * P.stride * S + (long long)P.L.ints * S) + (env % S);
+}
+
+__global__ void bp_contact_force_kernel(const __grid_constant__ BpParams P, int ci,
+                                        double* __restrict__ out) {
+  long long env = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (env >= P.nenv) return;
+  const long long S = P.interleave;
+  const double* d = bp_env_base(P, env);
+  const int* ib = bp_env_ints(P, env);
+  double f[6] = {0, 0, 0, 0, 0, 0};
+  const int ncon = ib[(long long)P.L.ncon * S];
+  if (ci >= ncon) {                     // the reference raises for such an id (core.py:761-764)
+    for (int k = 0; k < 6; k++) out[env * 6 + k] = nan("");
+    return;
+  }
+  const int a = ib[(long long)(P.L.contact_efc_address + ci) * S];
+  const int dim = ib[(long long)(P.L.contact_dim + ci) * S];
+  if (a >= 0) {
+    const double* force = d + (long long)P.L.efc_force * S;
+    if (dim == 1) f[0] = force[(long long)a * S];
+    else if (P.m.opt_cone == 0) {
+      const double* fri = d + (long long)(P.L.contact_friction + 5 * ci) * S;
+      for (int k = 0; k < 2 * (dim - 1); k++) f[0] += force[(long long)(a + k) * S];
+      for (int k = 1; k < dim; k++)
+        f[k] = fri[(long long)(k - 1) * S] *
+               (force[(long long)(a + 2 * k - 2) * S] - force[(long long)(a + 2 * k - 1) * S]);
+    } else {
+      for (int k = 0; k < dim; k++) f[k] = force[(long long)(a + k) * S];
+    }
+  }
+  for (int k = 0; k < 6; k++) out[env * 6 + k] = f[k];
+}
+
+extern "C" int bp_launch_contact_force(const BpParams* P, int ci, double* out,
+                                       cudaStream_t stream) {
+  unsigned blocks = (unsigned)((P->nenv + 127) / 128);
+  bp_contact_force_kernel<<<blocks, 128, 0, stream>>>(*P, ci, out);
+  return (int)cudaGetLastError();
+}
+
+__global__ void bp_object_velocity_kernel(const __grid_constant__ BpParams P, int objtype, int id,
+                                          int flg_local, double* __restrict__ out) {
+  long long env = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (env >= P.nenv) return;
+  const long long S = P.interleave;
+  const double* d = bp_env_base(P, env);
+  int body, po, mo;
+  if (objtype == OBJ_SITE) { body = P.m.site_bodyid[id]; po = P.L.site_xpos; mo = P.L.site_xmat; }
+  else if (objtype == OBJ_GEOM) { body = P.m.geom_bodyid[id]; po = P.L.geom_xpos; mo = P.L.geom_xmat; }
+  else if (objtype == OBJ_XBODY) { body = id; po = P.L.xpos; mo = P.L.xmat; }
+  else { body = id; po = P.L.xipos; mo = P.L.ximat; }
+  double pos[3], R[9], com[3], cv[6];
+  for (int k = 0; k < 3; k++) {
+    pos[k] = d[(long long)(po + 3 * id + k) * S];
+    com[k] = d[(long long)(P.L.subtree_com + 3 * P.m.body_rootid[body] + k) * S];
+  }
+  for (int k = 0; k < 9; k++) R[k] = d[(long long)(mo + 9 * id + k) * S];
+  for (int k = 0; k < 6; k++) cv[k] = d[(long long)(P.L.cvel + 6 * body + k) * S];
+  const double dif[3] = {pos[0] - com[0], pos[1] - com[1], pos[2] - com[2]};
+  double vlin[3] = {cv[3] + cv[1] * dif[2] - cv[2] * dif[1], cv[4] + cv[2] * dif[0] - cv[0] * dif[2],
+                    cv[5] + cv[0] * dif[1] - cv[1] * dif[0]};
+  double res[6];
+  if (flg_local) {
+    for (int k = 0; k < 3; k++) {
+      res[k] = R[k] * cv[0] + R[3 + k] * cv[1] + R[6 + k] * cv[2];
+      res[3 + k] = R[k] * vlin[0] + R[3 + k] * vlin[1] + R[6 + k] * vlin[2];
+    }
+  } else {
+    for (int k = 0; k < 3; k++) { res[k] = cv[k]; res[3 + k] = vlin[k]; }
+  }
+  for (int k = 0; k < 6; k++) out[env * 6 + k] = res[k];
+}
+
+extern "C" int bp_launch_object_velocity(const BpParams* P, int objtype, int id, int flg_local,
+                                         double* out, cudaStream_t stream) {
+  unsigned blocks = (unsigned)((P->nenv + 127) / 128);
+  bp_object_velocity_kernel<<<blocks, 128, 0, stream>>>(*P, objtype, id, flg_local, out);
+  return (int)cudaGetLastError();
+}

@@ -56,6 +56,36 @@ class _Data:
       return a[:, 0] if name in ("time", "ncon", "nefc", "ne", "nf", "solver_iter") else a
     raise AttributeError(name)
 
+  _OBJ = {"body": 1, "xbody": 2, "geom": 5, "site": 6}
+
+  def object_velocity(self, object_id, object_type, local_frame=False):
+    """MjData.object_velocity (wrapper/core.py:713-745) for every env: [nenv, 2, 3] stacked
+    (linear_velocity, angular_velocity); object_type 'body' | 'xbody' | 'geom' | 'site' (or
+    the mjtObj value), object_id an id or a name."""
+    p = self._p
+    if not isinstance(object_type, (int, np.integer)):
+      if object_type not in self._OBJ:
+        raise binding.Error("{!r} is not a valid object type name.".format(object_type))
+      kind = "body" if object_type == "xbody" else object_type
+      object_type = self._OBJ[object_type]
+    else:
+      kind = {1: "body", 2: "body", 5: "geom", 6: "site"}.get(int(object_type), "body")
+    if not isinstance(object_id, (int, np.integer)):
+      object_id = p.model.name2id(object_id, kind)
+    return p._batch.object_velocity(object_id, object_type, local_frame)
+
+  def contact_force(self, contact_id):
+    """MjData.contact_force (wrapper/core.py:747-769) for every env: [nenv, 2, 3] stacked
+    (force, torque) in the contact's frame.  contact_id must be a valid index in EVERY env
+    (0 <= contact_id < min ncon), else ValueError as in the reference."""
+    p = self._p
+    ncon = int(p._batch.read("ncon").min())
+    if not 0 <= contact_id < ncon:
+      raise ValueError("`contact_id` must be an integer in range [0, {max_valid}] "
+                       "(inclusive), got: {actual}.".format(max_valid=ncon - 1,
+                                                             actual=contact_id))
+    return p._batch.contact_force(contact_id)
+
   def __setattr__(self, name, value):
     b = self._p._batch
     if name not in b.fields:
@@ -88,9 +118,11 @@ class BatchedPhysics:
     self.model = flat_model
     self.nenv = int(nenv)
     dj, dc = default_sizes(flat_model)
+    self._ctor = dict(device=device, njmax=njmax or dj, nconmax=nconmax or dc,
+                      lanes=lanes if lanes is not None else default_lanes(flat_model))
     self._dev_model = binding.Model(flat_model, device)
-    self._batch = binding.Batch(self._dev_model, self.nenv, njmax or dj, nconmax or dc,
-                                lanes if lanes is not None else default_lanes(flat_model))
+    self._batch = binding.Batch(self._dev_model, self.nenv, self._ctor["njmax"],
+                                self._ctor["nconmax"], self._ctor["lanes"])
     self._axes = index.make_axes(flat_model)
     self.data = _Data(self)
     self.named = _Named(self)
@@ -202,6 +234,64 @@ class BatchedPhysics:
 
   get_state = state
 
+  # ---- copies and resumable state (engine.py:247-266, 332-339; wrapper/core.py:653-685) ----
+  FULL_STATE_FIELDS = ("qpos", "qvel", "act", "ctrl", "qacc_warmstart", "qfrc_applied", "time")
+
+  def copy(self, share_model=False):
+    """Physics.copy (engine.py:332-339): a new BatchedPhysics with a bit copy of every env's
+    data (mj_copyData: bp_batch_copy).  share_model=True makes the copy use this object's
+    device model instead of uploading its own."""
+    cls = type(self)
+    new = cls.__new__(cls)
+    new.model = self.model if share_model else self.model.copy()
+    new.nenv = self.nenv
+    new._ctor = dict(self._ctor)
+    new._dev_model = self._dev_model if share_model else \
+        binding.Model(new.model, self._ctor["device"])
+    new._owns_model = not share_model
+    new._batch = binding.Batch(new._dev_model, self.nenv, self._ctor["njmax"],
+                               self._ctor["nconmax"], self._ctor["lanes"])
+    new._batch.copy_from(self._batch)
+    new._axes = self._axes
+    new.data = _Data(new)
+    new.named = _Named(new)
+    new._warnings_seen = self._warnings_seen.copy()
+    new._reset_mask = None
+    return new
+
+  def get_full_state(self):
+    """Everything a bit-exact resume needs: qpos, qvel, act, ctrl, the
+    solver's warm start, applied forces and time, plus the per-env model data tasks edit."""
+    st = {f: getattr(self.data, f) for f in self.FULL_STATE_FIELDS}
+    for name in ("geom_pos", "site_pos", "body_pos", "body_quat"):
+      if self._batch.has_env_model(name):
+        st["env_" + name] = self._batch.read_env_model(name)
+    if int(self.model.nhfielddata) > 0:
+      st["hfield"] = self._batch.read_hfield()
+    return st
+
+  def set_full_state(self, st):
+    """Restores get_full_state() and recomputes what Physics.step() leaves behind (mj_step1 of
+    the restored state), so that stepping on continues bit for bit."""
+    for name in ("geom_pos", "site_pos", "body_pos", "body_quat"):
+      if "env_" + name in st:
+        self._batch.write_env_model(name, st["env_" + name])
+    if "hfield" in st:
+      self._batch.write_hfield(st["hfield"])
+    for f in self.FULL_STATE_FIELDS:
+      setattr(self.data, f, st[f])
+    self._batch.step1()
+    self._batch.sync()
+
+  def __getstate__(self):
+    return {"model": self.model, "nenv": self.nenv, "ctor": self._ctor,
+            "state": self.get_full_state(), "warnings_seen": self._warnings_seen}
+
+  def __setstate__(self, d):
+    self.__init__(d["model"], d["nenv"], **d["ctor"])
+    self.set_full_state(d["state"])
+    self._warnings_seen = d["warnings_seen"]
+
   def set_state(self, physics_state):
     s = np.asarray(physics_state, dtype=np.float64)
     nq, nv, na = self.model.nq, self.model.nv, self.model.na
@@ -273,4 +363,5 @@ class BatchedPhysics:
 
   def free(self):
     self._batch.free()
-    self._dev_model.free()
+    if getattr(self, "_owns_model", True):
+      self._dev_model.free()

@@ -45,7 +45,8 @@ def load_shard(domain_name, task_name, total_envs, seed, rank=None, world_size=N
   rank = r if rank is None else rank
   world_size = w if world_size is None else world_size
   seeds = env_seeds(seed, total_envs, rank, world_size)
-  return suite.load(domain_name, task_name, task_kwargs={"random": seeds}, nenv=len(seeds),
+  return suite.load(domain_name, task_name,
+                    task_kwargs={"random": seeds, "model_seed": seed}, nenv=len(seeds),
                     device=local if device is None else device, **kw)
 
 

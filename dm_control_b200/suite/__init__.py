@@ -30,8 +30,12 @@ def _randomize_limited_and_rotational_joints(m, qpos, rng):
     if m.jnt_limited[j]:
       if jt in (M.JNT_HINGE, M.JNT_SLIDE):
         qpos[qa] = rng.uniform(lo, hi)
-      elif jt == M.JNT_BALL:
-        raise NotImplementedError("limited ball joints are not in the served domains")
+      elif jt == M.JNT_BALL:     # randomizers.py:23-33 random_limited_quaternion
+        axis = rng.randn(3)
+        axis /= np.linalg.norm(axis)
+        angle = rng.rand() * hi
+        qpos[qa] = np.cos(angle / 2)             # mju_axisAngle2Quat
+        qpos[qa + 1:qa + 4] = axis * np.sin(angle / 2)
     else:
       if jt == M.JNT_HINGE:
         qpos[qa] = rng.uniform(-np.pi, np.pi)
@@ -60,6 +64,11 @@ class Task:
     if isinstance(self._seed, (list, tuple, np.ndarray)):
       self._rngs = [r if isinstance(r, np.random.RandomState) else np.random.RandomState(r)
                     for r in self._seed]
+    elif isinstance(self._seed, np.random.RandomState):
+      # base.Task accepts a RandomState (suite/base.py:40-50); the batch needs one stream per
+      # env, drawn from it
+      self._rngs = [np.random.RandomState(int(s))
+                    for s in self._seed.randint(0, 2 ** 31 - 1, size=n)]
     elif self._seed is None:
       self._rngs = [np.random.RandomState(None) for _ in range(n)]
     else:
@@ -133,7 +142,8 @@ class Task:
       for e, rng in self._each():
         qpos[e, lim] = rng.uniform(lo, hi)
       physics.data.qpos = qpos
-      physics.after_reset()                 # derived quantities for the settle steps
+      # cheetah.py:73-75 steps straight away: the first mj_step2 of the settle run still sees
+      # the quantities reset() derived at qpos0 (actuation disabled), as in the reference
       for _ in range(4):
         physics.step(50)                    # 200 physics steps, as the reference
       physics.data.time = 0.0
@@ -393,12 +403,21 @@ def build_environment(domain_name, task_name, task_kwargs=None, environment_kwar
     # RandomState before the task uses it; one model serves every env of the batch
     from dm_control_b200 import mjcf_compiler
     from dm_control_b200.suite import lqr
-    model_rng = seed if isinstance(seed, np.random.RandomState) else np.random.RandomState(seed)
+    # a sharded job passes its job-level seed as `model_seed` so that every rank and every
+    # world size generates the SAME model (sharding.load_shard)
+    model_seed = task_kwargs.pop("model_seed", None)
+    if model_seed is not None:
+      model_rng = np.random.RandomState(model_seed)
+    elif isinstance(seed, np.random.RandomState):
+      model_rng = seed
+    else:
+      model_rng = np.random.RandomState(seed)
     m = mjcf_compiler.compile_xml(lqr.make_model(tdef.model[0], tdef.model[1], model_rng))
   else:
     m = _load_model(tdef.model)
   physics = BatchedPhysics(m, nenv, device=device, lanes=lanes, njmax=njmax, nconmax=nconmax)
   task = Task(tdef, random=task_kwargs.pop("random", None))
+  task_kwargs.pop("model_seed", None)
   time_limit = task_kwargs.pop("time_limit", tdef.time_limit)
   if task_kwargs:
     raise TypeError("unexpected task_kwargs: {}".format(sorted(task_kwargs)))

@@ -167,6 +167,22 @@ int bp_env_step(bp_batch* b, int nsub, const double* ctrl_dev, double* obs_dev,
 int bp_env_step_host(bp_batch* b, int nsub, const double* ctrl_host, double* obs_host,
                      double* reward_host);
 
+/* mj_copyData (wrapper/core.py:653-685 MjData.copy; engine.py:332-339 Physics.copy): the whole
+ * state of `src` -- every env image, per-env height fields and model frames, the bound task --
+ * into `dst`, created with the same sizes.  Device-to-device; synchronises. */
+int bp_batch_copy(bp_batch* dst, bp_batch* src);
+
+/* mj_contactForce as MjData.contact_force wraps it (wrapper/core.py:747-769): wrench of
+ * contact `contact_id` of every env in the contact's frame, out_host [nenv][6] =
+ * (normal, tangent, tangent, torsional, roll, roll).  Rows of envs that hold fewer contacts
+ * than contact_id + 1 are NaN (the reference raises for such an id).  Synchronises. */
+int bp_contact_force(bp_batch* b, int contact_id, double* out_host);
+/* mj_objectVelocity as MjData.object_velocity wraps it (wrapper/core.py:713-745): 6D velocity
+ * (angular, linear -- MuJoCo's order) of an object in a frame centred on it, world-aligned or
+ * object-aligned (flg_local); objtype is an mjtObj value: 1 body (inertial frame), 2 xbody,
+ * 5 geom, 6 site.  out_host [nenv][6].  Synchronises. */
+int bp_object_velocity(bp_batch* b, int objtype, int objid, int flg_local, double* out_host);
+
 /* Physics.check_invalid_state (engine.py:307-330): per-env warning counters
  * [nenv][8] int32 copied to the host (synchronises). */
 int bp_warnings(bp_batch* b, int32_t* out_host);

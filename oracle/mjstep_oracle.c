@@ -3291,6 +3291,30 @@ void o_physics_step(const OModel* m, OData* d) {
   o_step1(m, d);
 }
 
+/* mj_contactForce (wrapper/core.py:747-769): wrench of contact `ci` in the contact frame,
+ * (normal, tangent, tangent | torsional, roll, roll) */
+void o_contact_force(const OModel* m, const OData* d, int ci, double* f6) {
+  if (ci < 0 || ci >= d->ncon[0]) { memset(f6, 0, 48); return; }
+  contact_force(m, d, ci, f6);
+}
+
+/* mj_objectVelocity (wrapper/core.py:713-745): 6D velocity (angular; linear) of an object in
+ * an object-centred frame, world-aligned or (flg_local) object-aligned.  objtype as mjtObj:
+ * 1 body (inertial frame), 2 xbody, 5 geom, 6 site. */
+void o_object_velocity(const OModel* m, const OData* d, int objtype, int id, double* res,
+                       int flg_local) {
+  const double *pos, *mat;
+  int body;
+  obj_frame(m, d, objtype, id, &pos, &mat, &body);
+  const double* com = d->subtree_com + 3 * m->body_rootid[body];
+  const double* cv = d->cvel + 6 * body;
+  double dif[3] = {pos[0] - com[0], pos[1] - com[1], pos[2] - com[2]}, t3[3], vlin[3];
+  cross3(t3, cv, dif);
+  for (int c = 0; c < 3; c++) vlin[c] = cv[3 + c] + t3[c];
+  if (flg_local) { matT_vec3(res, mat, cv); matT_vec3(res + 3, mat, vlin); }
+  else { memcpy(res, cv, 24); memcpy(res + 3, vlin, 24); }
+}
+
 /* -------------------------------------------------- CPU-baseline driver */
 
 typedef struct {

@@ -43,6 +43,11 @@ void o_step2(const OModel* m, OData* d);              /* mj_step2          */
 /* Physics.step() of engine.py:149-166: Euler -> step2 ; RK4 -> step, then step1 */
 void o_physics_step(const OModel* m, OData* d);
 
+/* mj_contactForce / mj_objectVelocity (wrapper/core.py:713-769) */
+void o_contact_force(const OModel* m, const OData* d, int contact_id, double* f6);
+void o_object_velocity(const OModel* m, const OData* d, int objtype, int objid, double* res6,
+                       int flg_local);
+
 /* CPU-baseline driver: nenv independent environments, `nsteps` calls of
  * o_physics_step x nsub each, ctrl[nsteps or 1][nenv][nu]; state arrays are
  * [nenv][n] row-major and updated in place; nthreads pthreads. */

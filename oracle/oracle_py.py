@@ -50,6 +50,10 @@ def lib():
     L.o_run_batch.restype = None
     L.o_run_batch_hf.argtypes = L.o_run_batch.argtypes + [dp]
     L.o_run_batch_hf.restype = None
+    L.o_contact_force.argtypes = [vp, vp, ctypes.c_int, dp]
+    L.o_contact_force.restype = None
+    L.o_object_velocity.argtypes = [vp, vp, ctypes.c_int, ctypes.c_int, dp, ctypes.c_int]
+    L.o_object_velocity.restype = None
     _lib = L
   return _lib
 
@@ -110,6 +114,22 @@ class Oracle:
   def step1(self): lib().o_step1(self.model.ptr, self.ptr)
   def step2(self): lib().o_step2(self.model.ptr, self.ptr)
   def step(self): lib().o_physics_step(self.model.ptr, self.ptr)
+
+  def contact_force(self, contact_id):
+    """wrapper/core.py:747-769: 2 x 3 (force, torque) in the contact frame."""
+    out = np.zeros(6)
+    lib().o_contact_force(self.model.ptr, self.ptr, int(contact_id),
+                          out.ctypes.data_as(ctypes.POINTER(ctypes.c_double)))
+    return out.reshape(2, 3)
+
+  def object_velocity(self, object_id, object_type, local_frame=False):
+    """wrapper/core.py:713-745: 2 x 3 (linear, angular); object_type is an mjtObj value
+    (1 body, 2 xbody, 5 geom, 6 site)."""
+    out = np.zeros(6)
+    lib().o_object_velocity(self.model.ptr, self.ptr, int(object_type), int(object_id),
+                            out.ctypes.data_as(ctypes.POINTER(ctypes.c_double)),
+                            int(bool(local_frame)))
+    return out.reshape(2, 3)[::-1]
 
   def __del__(self):
     if getattr(self, "ptr", None) and _lib is not None:

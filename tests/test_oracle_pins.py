@@ -363,3 +363,103 @@ def test_box_stack_at_rest_carries_the_weight_above_it():
   assert support(0, 4) == (4, pytest.approx((1.0 + 0.3) * g, abs=1e-5))          # floor - c
   assert support(5, 4) == (2, pytest.approx(0.3 * g, abs=1e-5))                  # capsule - c
   assert ncon == 15
+
+
+@pytest.mark.parametrize("condim,expected_torques", [(3, [False, False, False]),
+                                                      (4, [True, False, False]),
+                                                      (6, [True, True, True])])
+def test_contact_torque_sparsity_by_condim(condim, expected_torques):
+  """core_test.py:494-530 testContactTorque: a spinning ball on the floor; sliding friction
+  only gives no contact torque, condim 4 adds the torsional one, condim 6 all three."""
+  xml = """
+  <mujoco>
+    <worldbody>
+      <geom name='floor' type='plane' size='1 1 1'/>
+      <body name='ball' pos='0 0 .1'>
+        <freejoint/>
+        <geom name='ball' size='.1' friction='1 .1 .1'/>
+      </body>
+    </worldbody>
+  </mujoco>""".replace("<geom name=", "<geom condim='%d' name=" % condim)   # buffers sized for it
+  m = C.compile_xml(xml)
+  assert (np.asarray(m.geom_condim) == condim).all()
+  o = Oracle(m)
+  o.qvel[3:] = (1., 1., 1.)
+  for _ in range(10):
+    o.mj_step()
+  assert int(o.ncon[0]) == 1
+  force, torque = o.contact_force(0)
+  np.testing.assert_array_equal(torque != 0, expected_torques)
+  assert force[0] > 0
+
+
+def test_free_humanoid_momentum_drift_vanishes_at_the_integrators_order():
+  """Engine-independent, on the ORACLE (the GPU side holds the same invariant in
+  test_gpu_invariants.py): without gravity and contacts every force of the suite humanoid is
+  internal, so the continuous dynamics conserve the centre-of-mass velocity; the discrete
+  drift is first order in dt for semi-implicit Euler and far smaller for RK4."""
+  import parity_util as PU
+  from dm_control_b200 import model as MD
+
+  def drift(integrator, dt_div, n=8, steps=40):
+    m = PU.load_model("humanoid")
+    m.arrays["opt_disableflags"][...] = int(m.opt_disableflags) | MD.DSBL["contact"] | MD.DSBL["gravity"]
+    m.arrays["opt_integrator"][...] = integrator
+    m.arrays["opt_timestep"][...] = m.opt_timestep / dt_div
+    qpos, qvel, ctrl = PU.random_states(m, n, 8)
+    adr = m.sensor_adr[m.name2id("torso_subtreelinvel", "sensor")]
+    out = []
+    for e in range(n):
+      o = Oracle(m)
+      o.reset(); o.qpos[:] = qpos[e]; o.qvel[:] = qvel[e]; o.ctrl[:] = ctrl[e]
+      o.forward()
+      v0 = np.array(o.sensordata[adr:adr + 3])
+      for _ in range(steps * dt_div):
+        o.mj_step()
+      o.forward()
+      assert int(o.ncon[0]) == 0
+      out.append(np.abs(np.array(o.sensordata[adr:adr + 3]) - v0).max())
+    return np.array(out)
+
+  e1, e4, r = drift(0, 1), drift(0, 4), drift(1, 1)
+  assert 2.5 < np.median(e1 / e4) < 6.0
+  assert np.median(r) < 0.05 * np.median(e1)
+
+
+def test_efc_J_is_the_derivative_of_efc_pos():
+  """Finite differences: for limit and contact rows, efc_pos(q + eps dq) - efc_pos(q) =
+  eps J dq (dq in dof space, integrated with the engine's own position integration)."""
+  import parity_util as PU
+  m = PU.load_model("cheetah")
+  qpos, qvel, ctrl = PU.random_states(m, 6, 5)
+  om = C and __import__("oracle.oracle_py", fromlist=["OracleModel"]).OracleModel(m)
+  checked = 0
+  for e in range(6):
+    o = Oracle(om)
+    o.reset(); o.qpos[:] = qpos[e]; o.forward()
+    nefc, nv = int(o.nefc[0]), m.nv
+    if nefc == 0:
+      continue
+    J = np.array(o.efc_J[:nefc * nv]).reshape(nefc, nv)
+    pos0, ids0 = np.array(o.efc_pos[:nefc]), np.array(o.efc_id[:nefc])
+    types0 = np.array(o.efc_type[:nefc])
+    rng = np.random.RandomState(e)
+    dq = rng.randn(nv)
+    eps = 1e-7
+    o2 = Oracle(om)
+    o2.reset(); o2.qpos[:] = qpos[e] + eps * dq       # cheetah: slide / hinge joints only
+    o2.forward()
+    if int(o2.nefc[0]) != nefc or not np.array_equal(np.array(o2.efc_id[:nefc]), ids0):
+      continue
+    num = (np.array(o2.efc_pos[:nefc]) - pos0) / eps
+    # pyramidal contact rows share the contact's distance: d pos = Jn dq, and the rows hold
+    # Jn +- mu Jt, so consecutive row PAIRS average to Jn
+    ana = J @ dq
+    for r in range(nefc):
+      if types0[r] == 3:                                # joint limit
+        np.testing.assert_allclose(num[r], ana[r], rtol=1e-5, atol=1e-6); checked += 1
+    con = np.flatnonzero(types0 == 6)
+    for r in con[::2]:
+      np.testing.assert_allclose(num[r], 0.5 * (ana[r] + ana[r + 1]), rtol=1e-4, atol=1e-5)
+      checked += 1
+  assert checked > 5

@@ -120,6 +120,93 @@ def c1_trace(steps=1000):
   print("c1_cartpole_swingup.npz", np.stack(rec["obs"]).shape, "reward sum", np.sum(rec["reward"]))
 
 
+def load_reference_randomizers():
+  """Imports the REFERENCE's suite/utils/randomizers.py by file path.  It is pure numpy but
+  for the `mjbindings` import (enum values of mjtJoint and mju_axisAngle2Quat), which is
+  stubbed here with MuJoCo's documented enum order and the axis-angle formula."""
+  import types
+  mjb = types.ModuleType("dm_control.mujoco.wrapper.mjbindings")
+  mjb.enums = types.SimpleNamespace(mjtJoint=types.SimpleNamespace(
+      mjJNT_FREE=0, mjJNT_BALL=1, mjJNT_SLIDE=2, mjJNT_HINGE=3))
+
+  def mju_axisAngle2Quat(res, axis, angle):
+    res[0] = np.cos(angle / 2)
+    res[1:4] = np.asarray(axis) * np.sin(angle / 2)
+  mjb.mjlib = types.SimpleNamespace(mju_axisAngle2Quat=mju_axisAngle2Quat)
+  saved = {k: sys.modules.get(k) for k in ("dm_control", "dm_control.mujoco",
+                                           "dm_control.mujoco.wrapper",
+                                           "dm_control.mujoco.wrapper.mjbindings")}
+  pk = types.ModuleType("dm_control"); mj = types.ModuleType("dm_control.mujoco")
+  wr = types.ModuleType("dm_control.mujoco.wrapper")
+  wr.mjbindings = mjb; mj.wrapper = wr; pk.mujoco = mj
+  sys.modules.update({"dm_control": pk, "dm_control.mujoco": mj,
+                      "dm_control.mujoco.wrapper": wr,
+                      "dm_control.mujoco.wrapper.mjbindings": mjb})
+  try:
+    spec = importlib.util.spec_from_file_location(
+        "ref_randomizers", "/root/reference/dm_control/suite/utils/randomizers.py")
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+  finally:
+    for k, v in saved.items():
+      if v is None:
+        sys.modules.pop(k, None)
+      else:
+        sys.modules[k] = v
+  return mod
+
+
+class FakePhysics:
+  """The slice of `Physics` that randomizers.py touches: model.njnt / id2name / jnt_type /
+  jnt_limited / jnt_range and named.data.qpos[joint_name] (read: a view, write: assign)."""
+
+  def __init__(self, m):
+    self.qpos = np.array(m.qpos0, dtype=np.float64)
+    width = {0: 7, 1: 4, 2: 1, 3: 1}
+    names = [n if n else "joint%d" % j for j, n in enumerate(m.names["joint"])]
+    outer = self
+
+    class _Qpos:
+      def _slice(self, name):
+        j = names.index(name)
+        a = int(m.jnt_qposadr[j])
+        return slice(a, a + width[int(m.jnt_type[j])])
+
+      def __getitem__(self, name):
+        return outer.qpos[self._slice(name)]
+
+      def __setitem__(self, name, value):
+        outer.qpos[self._slice(name)] = value
+
+    self.named = type("N", (), {"data": type("D", (), {"qpos": _Qpos()})()})()
+    self.model = type("Mdl", (), {
+        "njnt": int(m.njnt), "jnt_type": np.asarray(m.jnt_type),
+        "jnt_limited": np.asarray(m.jnt_limited), "jnt_range": np.asarray(m.jnt_range),
+        "id2name": staticmethod(lambda i, kind: names[i])})()
+
+
+RANDOMIZER_MODELS = ["cartpole", "acrobot", "pendulum", "cheetah", "walker", "hopper",
+                     "humanoid", "humanoid_CMU", "finger", "reacher", "point_mass", "swimmer6",
+                     "fish", "ball_in_cup", "quadruped", "manipulator_ball"]
+
+
+def randomizers_fixture():
+  """qpos after the REFERENCE's randomize_limited_and_rotational_joints for every served
+  model and three seeds -> tests/golden/randomizers.npz (plus a model with a limited ball
+  joint, which no suite model has)."""
+  import parity_util as PU
+  mod = load_reference_randomizers()
+  out = {}
+  for dom in RANDOMIZER_MODELS:
+    m = PU.load_model(dom)
+    for seed in (0, 1, 2):
+      ph = FakePhysics(m)
+      mod.randomize_limited_and_rotational_joints(ph, np.random.RandomState(seed))
+      out["%s/%d" % (dom, seed)] = ph.qpos
+  np.savez(os.path.join(OUT, "randomizers.npz"), **out)
+  print("randomizers.npz", len(out), "cases")
+
+
 def ref_test_humanoid_model():
   """The reference's own test model that asks for RK4 + PGS
   (/root/reference/dm_control/mujoco/testing/assets/humanoid.xml:9), compiled here because
@@ -131,6 +218,7 @@ def ref_test_humanoid_model():
 
 
 if __name__ == "__main__":
+  randomizers_fixture()
   ref_test_humanoid_model()
   os.makedirs(OUT, exist_ok=True)
   rewards_fixture()
