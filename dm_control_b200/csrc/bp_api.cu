@@ -23,6 +23,8 @@ extern "C" int bp_launch_step_g8_lean(const BpParams* P, cudaStream_t stream);
 extern "C" int bp_launch_step_g4_lean(const BpParams* P, cudaStream_t stream);
 extern "C" int bp_launch_step_g16_mid(const BpParams* P, cudaStream_t stream);
 extern "C" int bp_launch_step_g8_mid(const BpParams* P, cudaStream_t stream);
+extern "C" int bp_launch_step_static(const BpParams* P, unsigned long long hash, int plain,
+                                     cudaStream_t stream);
 extern "C" int bp_launch_field_copy(const BpParams* P, long long off, int count, int is_int,
                                     void* dense, long long env0, long long n, int to_image,
                                     cudaStream_t stream);
@@ -59,6 +61,8 @@ struct HostField {
   const void* data() const { return dtype == 0 ? (const void*)f.data() : (const void*)i.data(); }
 };
 
+struct FieldInfo { std::string name; int64_t offset_bytes, count; int dtype; };
+
 struct bp_model {
   int device = 0;
   std::map<std::string, HostField> fields;   // blob fields + derived arrays
@@ -66,6 +70,7 @@ struct bp_model {
   char* dev = nullptr;                        // one device buffer for every array
   size_t dev_bytes = 0;
   BpModel M;                                  // scalars + device pointers
+  unsigned long long struct_hash = 0;         // of everything a static instance bakes in
 };
 
 static const std::vector<int32_t>& I(bp_model* m, const char* n) { return m->fields[n].i; }
@@ -96,6 +101,8 @@ static int refresh_scalars(bp_model* m) {
   if (M.nv == 0) M.any_damping = 0;
   return BP_OK;
 }
+
+static void compute_struct_hash(bp_model* m);
 
 static int derive(bp_model* m) {
   BpModel& M = m->M;
@@ -226,6 +233,7 @@ static int derive(bp_model* m) {
     for (int t = 0; t < M.ntendon; t++)
       if (tl[t] != 0 || tk[t] != 0 || tb[t] != 0) M.mid_static = 0;
   }
+  compute_struct_hash(m);
   return BP_OK;
 }
 
@@ -293,6 +301,51 @@ static int validate(bp_model* m) {
   return BP_OK;
 }
 
+// ---- static (ahead-of-time specialised) instances -------------------------------------
+// A static instance (csrc/static/<name>.cuh, tools/gen_static_model.py) bakes in the model's
+// structure: the structural int scalars, every int array (blob and derived), body_dofmask and
+// the derived counts.  struct_hash identifies that structure; a launch uses a static instance
+// only while the live model still hashes to the instance's value (run-time edits of e.g.
+// dof_frictionloss or jnt_limited change derived arrays and hence the hash).
+static const char* kStaticScalars[] = {
+    "nq", "nv", "nu", "na", "nbody", "njnt", "ngeom", "nsite", "nM", "npair", "nsensor",
+    "nsensordata", "nkey", "ntendon", "neq", "nhfield", "nhfielddata", "nhfpair", "nspatial"};
+
+static void hash_mix(unsigned long long& h, const void* data, size_t n) {
+  const unsigned char* p = (const unsigned char*)data;
+  for (size_t i = 0; i < n; i++) { h ^= p[i]; h *= 1099511628211ull; }
+}
+
+static std::vector<std::string> static_int_arrays() {
+  std::vector<std::string> v;
+#define X(n) v.push_back(#n);
+  BP_MODEL_INT_ARRAYS(X)
+  BP_MODEL_DERIVED_INT_ARRAYS(X)
+#undef X
+  return v;
+}
+
+static void compute_struct_hash(bp_model* m) {
+  unsigned long long h = 1469598103934665603ull;
+  const BpModel& M = m->M;
+  for (const char* n : kStaticScalars) {
+    int v = m->fields[n].dtype == 1 ? m->fields[n].i[0] : (int)m->fields[n].f[0];
+    hash_mix(h, &v, 4);
+  }
+  for (auto& n : static_int_arrays()) {
+    auto& a = m->fields[n].i;
+    int cnt = (int)a.size();
+    hash_mix(h, &cnt, 4);
+    hash_mix(h, a.data(), a.size() * 4);
+  }
+  hash_mix(h, m->dofmask.data(), m->dofmask.size() * 8);
+  int derived[] = {M.nlevel, M.ndoflevel, M.nfric, M.nlim, M.ntri, M.nvp, M.neq_active,
+                   M.any_damping, M.need_subtreevel, M.need_rnepost_stage, M.nhinge, M.nsens_ft,
+                   M.nsens_rf, M.lean_static, M.mid_static};
+  hash_mix(h, derived, sizeof derived);
+  m->struct_hash = h;
+}
+
 static int upload(bp_model* m) {
   size_t off = 0;
   for (auto& kv : m->fields) { kv.second.dev_off = off; off += (kv.second.nbytes() + 15) / 16 * 16; }
@@ -328,6 +381,97 @@ extern "C" int bp_device_count(void) {
   if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
   return n;
 }
+
+static void make_layout(const BpModel& m, int njmax, int nconmax, BpLayout* L,
+                        std::vector<FieldInfo>* fields);
+
+// Host-only: parses a model blob, derives what bp_model_create derives and writes the C++
+// header of a static instance (no CUDA call: runs in the build container).
+extern "C" int bp_static_header(const void* blob, int64_t nbytes, int njmax, int nconmax,
+                                const char* name, const char* path) {
+  if (!blob || nbytes < 16 || memcmp(blob, "BPMODEL1", 8) != 0 || !name || !path)
+    return fail(BP_EINVAL, "bad arguments to bp_static_header");
+  const char* base = (const char*)blob;
+  int nfields = *(const int32_t*)(base + 8);
+  const BlobEntry* ent = (const BlobEntry*)(base + 16);
+  bp_model mm;
+  bp_model* m = &mm;
+  for (int k = 0; k < nfields; k++) {
+    HostField h;
+    h.dtype = ent[k].dtype;
+    if (h.dtype == 0) h.f.assign((const double*)(base + ent[k].offset), (const double*)(base + ent[k].offset) + ent[k].count);
+    else h.i.assign((const int32_t*)(base + ent[k].offset), (const int32_t*)(base + ent[k].offset) + ent[k].count);
+    if (h.dtype == 0 && h.f.empty()) h.f.push_back(0);
+    if (h.dtype == 1 && h.i.empty()) h.i.push_back(0);
+    char nm[41]; memcpy(nm, ent[k].name, 40); nm[40] = 0;
+    m->fields[nm] = h;
+  }
+  if (refresh_scalars(m) != BP_OK || derive(m) != BP_OK) return BP_EINVAL;
+  const BpModel& M = m->M;
+  if (njmax <= 0) njmax = M.njmax;
+  if (nconmax <= 0) nconmax = M.nconmax;
+  BpLayout L;
+  make_layout(M, njmax, nconmax, &L, nullptr);
+  FILE* f = fopen(path, "w");
+  if (!f) return fail(BP_EINVAL, std::string("cannot write ") + path);
+  fprintf(f, "// GENERATED by tools/gen_static_model.py (bp_static_header) -- do not edit.\n");
+  fprintf(f, "// Static instance \"%s\": structure of the compiled model and the data layout for\n", name);
+  fprintf(f, "// njmax = %d, nconmax = %d as compile-time constants (csrc/bp_math.cuh Ctx<.., MT>).\n", njmax, nconmax);
+  fprintf(f, "#ifndef BP_STATIC_%s_CUH_\n#define BP_STATIC_%s_CUH_\n#include \"../bp_types.h\"\n", name, name);
+  fprintf(f, "namespace bp_static_%s {\n", name);
+  auto arrays = static_int_arrays();
+  for (auto& n : arrays) {
+    auto& a = m->fields[n].i;
+    fprintf(f, "__device__ constexpr int %s_[%d] = {", n.c_str(), (int)a.size());
+    for (size_t i = 0; i < a.size(); i++) fprintf(f, "%s%d", i ? ", " : "", a[i]);
+    fprintf(f, "};\n");
+  }
+  fprintf(f, "__device__ constexpr unsigned long long body_dofmask_[%d] = {", (int)(m->dofmask.empty() ? 1 : m->dofmask.size()));
+  for (size_t i = 0; i < m->dofmask.size(); i++) fprintf(f, "%s%lluull", i ? ", " : "", m->dofmask[i]);
+  if (m->dofmask.empty()) fprintf(f, "0ull");
+  fprintf(f, "};\n");
+  fprintf(f, "struct Layout {\n");
+#define X(n, c) fprintf(f, "  static constexpr int %s = %d;\n", #n, L.n);
+  BP_DATA_F64(X)
+  BP_DATA_I32(X)
+  BP_DATA_SCRATCH(X)
+#undef X
+  fprintf(f, "  static constexpr int ints = %d, persist = %d, total = %d, njmax = %d, nconmax = %d;\n};\n",
+          L.ints, L.persist, L.total, L.njmax, L.nconmax);
+  fprintf(f, "struct Model {\n");
+  fprintf(f, "#define X(n) const double* n;\n  BP_MODEL_F64_ARRAYS(X) BP_MODEL_DERIVED_F64_ARRAYS(X)\n#undef X\n");
+  fprintf(f, "#define X(n) double n;\n  BP_MODEL_F64_SCALARS(X)\n#undef X\n");
+  fprintf(f, "  int opt_integrator, opt_cone, opt_solver, opt_iterations, opt_ls_iterations, opt_disableflags, opt_enableflags;\n");
+  fprintf(f, "  int nconmax, njmax;\n");
+  for (const char* n : kStaticScalars) {
+    int v = m->fields[n].dtype == 1 ? m->fields[n].i[0] : (int)m->fields[n].f[0];
+    fprintf(f, "  static constexpr int %s = %d;\n", n, v);
+  }
+  fprintf(f, "  static constexpr int nlevel = %d, ndoflevel = %d, nfric = %d, nlim = %d, ntri = %d, nvp = %d, neq_active = %d;\n",
+          M.nlevel, M.ndoflevel, M.nfric, M.nlim, M.ntri, M.nvp, M.neq_active);
+  fprintf(f, "  static constexpr int any_damping = %d, need_subtreevel = %d, need_rnepost_stage = %d, nhinge = %d, nsens_ft = %d, nsens_rf = %d, lean_static = %d, mid_static = %d;\n",
+          M.any_damping, M.need_subtreevel, M.need_rnepost_stage, M.nhinge, M.nsens_ft, M.nsens_rf, M.lean_static, M.mid_static);
+  for (auto& n : arrays) {
+    fprintf(f, "  struct A_%s { __device__ __forceinline__ int operator[](int i) const { return %s_[i]; } } %s;\n",
+            n.c_str(), n.c_str(), n.c_str());
+  }
+  fprintf(f, "  struct A_body_dofmask { __device__ __forceinline__ unsigned long long operator[](int i) const { return body_dofmask_[i]; } } body_dofmask;\n");
+  fprintf(f, "  __device__ __forceinline__ explicit Model(const BpModel& d)\n      : ");
+  bool first = true;
+#define X(n) fprintf(f, "%s%s(d.%s)", first ? "" : ", ", #n, #n); first = false;
+  BP_MODEL_F64_ARRAYS(X)
+  BP_MODEL_DERIVED_F64_ARRAYS(X)
+  BP_MODEL_F64_SCALARS(X)
+#undef X
+  fprintf(f, ",\n        opt_integrator(d.opt_integrator), opt_cone(d.opt_cone), opt_solver(d.opt_solver), opt_iterations(d.opt_iterations), opt_ls_iterations(d.opt_ls_iterations), opt_disableflags(d.opt_disableflags), opt_enableflags(d.opt_enableflags), nconmax(d.nconmax), njmax(d.njmax) {}\n};\n");
+  fprintf(f, "struct Traits {\n  using Model = bp_static_%s::Model;\n  using Layout = bp_static_%s::Layout;\n", name, name);
+  fprintf(f, "  static constexpr unsigned long long HASH = %lluull;\n  static constexpr int njmax = %d, nconmax = %d;\n};\n", m->struct_hash, njmax, nconmax);
+  fprintf(f, "}  // namespace bp_static_%s\n#endif\n", name);
+  fclose(f);
+  return BP_OK;
+}
+
+extern "C" unsigned long long bp_model_struct_hash(bp_model* m) { return m ? m->struct_hash : 0; }
 
 extern "C" bp_model* bp_model_create(const void* blob, int64_t nbytes, int device,
                                      char* err, int errsz) {
@@ -455,7 +599,6 @@ extern "C" int bp_model_get_field(bp_model* m, const char* name, void* data, int
 }
 
 // ------------------------------------------------------------------ batch
-struct FieldInfo { std::string name; int64_t offset_bytes, count; int dtype; };
 
 struct bp_batch {
   bp_model* model;
@@ -789,7 +932,14 @@ static int launch(bp_batch* b, int mode, int nsub, int disable_actuation,
   const bool plain = M.opt_solver == 2 && M.opt_cone == 0 && M.opt_density == 0 && M.opt_viscosity == 0 &&
                      !P.env_geom_pos && !P.env_site_pos && !P.env_body_pos && !P.env_body_quat &&
                      !getenv("BPHYS_NO_LEAN") && !getenv("BPHYS_SPLIT");
-  if (plain && M.lean_static && (b->lanes == 4 || b->lanes == 8 || b->lanes == 16)) {
+  // a static (ahead-of-time specialised) instance when one serves this model's structure,
+  // this batch's layout and lane width, and the shape the instance was built for still applies
+  // (csrc/bp_step_static.cu); BPHYS_NO_STATIC=1 / BPHYS_SPLIT=1 keep the generic kernels
+  e = -1;
+  if (!getenv("BPHYS_NO_STATIC") && !getenv("BPHYS_SPLIT") && b->lanes != 32)
+    e = bp_launch_step_static(&P, b->model->struct_hash, plain ? 1 : 0, b->stream);
+  if (e != -1) {
+  } else if (plain && M.lean_static && (b->lanes == 4 || b->lanes == 8 || b->lanes == 16)) {
     e = b->lanes == 4 ? bp_launch_step_g4_lean(&P, b->stream)
         : b->lanes == 8 ? bp_launch_step_g8_lean(&P, b->stream)
                         : bp_launch_step_g16_lean(&P, b->stream);

@@ -755,7 +755,7 @@ __device__ __forceinline__ void make_frame(double* f) {
 
 BP_STAGE void bp_write_contact(const C& c, int id, int g1, int g2, double margin, double gap,
                                const RawCon& raw) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   double f[9];
   for (int k = 0; k < 3; k++) { f[k] = raw.n[k]; f[3 + k] = raw.hint[k]; f[6 + k] = 0; }
   make_frame(f);
@@ -792,12 +792,12 @@ BP_STAGE void bp_write_contact(const C& c, int id, int g1, int g2, double margin
 }
 
 BP_STAGE void bp_collision(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   if (c.lane == 0) IF(ncon)[0] = 0;
   SYNC();
   if (m.opt_disableflags & (DSBL_CONTACT | DSBL_CONSTRAINT)) return;
   bool filterparent = !(m.opt_disableflags & DSBL_FILTERPARENT);
-  int nconmax = c.P.L.nconmax, base = 0;
+  int nconmax = bp_lv(c).nconmax, base = 0;
   bool full = false;
   auto gpos = DF(geom_xpos), gmat = DF(geom_xmat);
 #pragma unroll 1

@@ -39,8 +39,8 @@ __device__ __forceinline__ void bp_row_header(const C& c, int r, int type, int i
 }
 
 BP_STAGE void bp_make_constraint(const C& c) {
-  const BpModel& m = c.P.m;
-  const int nv = m.nv, nvp = m.nvp, njmax = c.P.L.njmax;
+  BP_MODEL(m);
+  const int nv = m.nv, nvp = m.nvp, njmax = bp_lv(c).njmax;
   auto J = DF(efc_J);
   if (c.lane == 0) { IF(nefc)[0] = 0; IF(ne)[0] = 0; IF(nf)[0] = 0; }
   SYNC();
@@ -342,7 +342,7 @@ BP_STAGE void bp_make_constraint(const C& c) {
 
 // efc_vel = J qvel, efc_aref = -B vel - K imp (pos - margin)
 BP_STAGE void bp_reference_constraint(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   const int nv = m.nv, nvp = m.nvp, nefc = IF(nefc)[0];
   auto J = DF(efc_J), qvel = DF(qvel);
 #pragma unroll 1

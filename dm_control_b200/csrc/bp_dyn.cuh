@@ -5,20 +5,20 @@
 #include "bp_smooth.cuh"
 
 BP_STAGE void bp_com_vel(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   auto cvel = DF(cvel), cdof = DF(cdof), cdof_dot = DF(cdof_dot), qvel = DF(qvel);
   for (int i = c.lane; i < 6; i += C::G) cvel[i] = 0;
   SYNC();
-#pragma unroll 1
+#pragma unroll (C::UF)
   for (int lev = 1; lev < m.nlevel; lev++) {
-#pragma unroll 1
+#pragma unroll (C::UF)
     for (int idx = m.body_level_adr[lev] + c.lane; idx < m.body_level_adr[lev + 1];
          idx += C::G) {
       int b = m.body_level_list[idx];
       double cv[6];
       for (int i = 0; i < 6; i++) cv[i] = cvel[6 * m.body_parentid[b] + i];
       int jn = m.body_jntnum[b], j0 = m.body_jntadr[b];
-#pragma unroll 1
+#pragma unroll (C::UF)
       for (int k = 0; k < jn; k++) {
         int j = j0 + k, da = m.jnt_dofadr[j], jt = m.jnt_type[j];
         if (jt == JNT_FREE) {
@@ -49,7 +49,7 @@ BP_STAGE void bp_com_vel(const C& c) {
 }
 
 BP_STAGE void bp_passive(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   auto qp = DF(qfrc_passive), qpos = DF(qpos), qvel = DF(qvel);
   bool off = m.opt_disableflags & DSBL_PASSIVE;
   for (int i = c.lane; i < m.nv; i += C::G) {
@@ -81,7 +81,7 @@ BP_STAGE void bp_passive(const C& c) {
   if constexpr (C::FULL) if (!off && (m.opt_density > 0 || m.opt_viscosity > 0)) {
     const double PI = 3.14159265358979323846;
     auto wr = DF(s_cfrc), cvel = DF(cvel), xipos = DF(xipos), ximat = DF(ximat), scom = DF(subtree_com);
-#pragma unroll 1
+#pragma unroll (C::UF)
     for (int b = 1 + c.lane; b < m.nbody; b += C::G) {
       double w[6] = {0, 0, 0, 0, 0, 0};
       const double mass = m.body_mass[b];
@@ -126,7 +126,7 @@ BP_STAGE void bp_passive(const C& c) {
     }
     SYNC();
     auto cdof = DF(cdof);
-#pragma unroll 1
+#pragma unroll (C::UF)
     for (int i = c.lane; i < m.nv; i += C::G) {
       double acc = 0;
       for (int b = 1; b < m.nbody; b++)
@@ -142,7 +142,7 @@ BP_STAGE void bp_passive(const C& c) {
 // Writes cacc / cfrc into the given buffers; result (may be null) = J^T cfrc.
 BP_STAGE void bp_rne(const C& c, bool with_acc, typename C::DP cacc, typename C::DP cfrc,
                      typename C::DP cfrc_ext, typename C::DP result, int stop_level) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   auto cdof = DF(cdof), cdof_dot = DF(cdof_dot), qvel = DF(qvel), qacc = DF(qacc);
   auto cinert = DF(cinert), cvel = DF(cvel);
   bool grav = !(m.opt_disableflags & DSBL_GRAVITY);
@@ -151,16 +151,16 @@ BP_STAGE void bp_rne(const C& c, bool with_acc, typename C::DP cacc, typename C:
     cfrc[i] = 0;
   }
   SYNC();
-#pragma unroll 1
+#pragma unroll (C::UF)
   for (int lev = 1; lev < m.nlevel; lev++) {
-#pragma unroll 1
+#pragma unroll (C::UF)
     for (int idx = m.body_level_adr[lev] + c.lane; idx < m.body_level_adr[lev + 1];
          idx += C::G) {
       int b = m.body_level_list[idx];
       double a[6];
       for (int i = 0; i < 6; i++) a[i] = cacc[6 * m.body_parentid[b] + i];
       int da = m.body_dofadr[b], dn = m.body_dofnum[b];
-#pragma unroll 1
+#pragma unroll (C::UF)
       for (int k = 0; k < dn; k++) {
         double v = qvel[da + k], qa = with_acc ? qacc[da + k] : 0.0;
         for (int i = 0; i < 6; i++) {
@@ -181,7 +181,7 @@ BP_STAGE void bp_rne(const C& c, bool with_acc, typename C::DP cacc, typename C:
     }
     SYNC();
   }
-  bp_tree_gather(c, cfrc, 6, stop_level);
+  bp_tree_gather<6>(c, cfrc, stop_level);
   if (result.valid()) {
     for (int i = c.lane; i < m.nv; i += C::G)
       result[i] = dot6(cdof + 6 * i, cfrc + 6 * m.dof_bodyid[i]);
@@ -192,7 +192,7 @@ BP_STAGE void bp_rne(const C& c, bool with_acc, typename C::DP cacc, typename C:
 // joint transmission with scalar joints (the only kind the compiled subset emits)
 // mj_tendon (fixed tendons: length = sum coef * qpos) + mj_transmission
 BP_STAGE void bp_transmission(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   auto len = DF(actuator_length), qpos = DF(qpos);
   if constexpr (!C::LEAN) if (m.ntendon > 0) {
     auto tl = DF(ten_length);
@@ -207,7 +207,7 @@ BP_STAGE void bp_transmission(const C& c) {
     // Jacobian row  sum_seg (jacp(p1) - jacp(p0))^T dir;  lane 0 keeps the length
     if constexpr (C::FULL) if (m.nspatial > 0) {
       auto sx = DF(site_xpos), cdof = DF(cdof), com = DF(subtree_com), tJ = DF(ten_J);
-#pragma unroll 1
+#pragma unroll (C::UF)
       for (int t = 0; t < m.ntendon; t++) {
         const int ja = m.tendon_Jadr[t];
         if (ja < 0) continue;
@@ -216,7 +216,7 @@ BP_STAGE void bp_transmission(const C& c) {
           const int i = i0 + c.lane;
           double acc = 0;
           length = 0;
-#pragma unroll 1
+#pragma unroll (C::UF)
           for (int w = m.tendon_adr[t]; w + 1 < m.tendon_adr[t] + m.tendon_num[t]; w++) {
             const int s0 = m.wrap_objid[w], s1 = m.wrap_objid[w + 1];
             double p0[3], p1[3], dif[3];
@@ -260,7 +260,7 @@ BP_STAGE void bp_transmission(const C& c) {
 }
 
 BP_STAGE void bp_actuator_velocity(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   auto vel = DF(actuator_velocity), qvel = DF(qvel);
   if constexpr (!C::LEAN) for (int t = c.lane; t < m.ntendon; t += C::G) {
     double s = 0;
@@ -287,7 +287,7 @@ BP_STAGE void bp_actuator_velocity(const C& c) {
 }
 
 BP_STAGE void bp_fwd_actuation(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   int nu = m.nu, nv = m.nv;
   auto ctrl = DF(ctrl), force = DF(actuator_force), qa = DF(qfrc_actuator);
   auto act = DF(act), act_dot = DF(act_dot);
@@ -309,7 +309,7 @@ BP_STAGE void bp_fwd_actuation(const C& c) {
     for (int i = c.lane; i < nu; i += C::G) ctrl[i] = 0;
   }
   SYNC();
-#pragma unroll 1
+#pragma unroll (C::UF)
   for (int i = c.lane; i < nu; i += C::G) {
     double x = ctrl[i];
     if (m.actuator_ctrllimited[i] && !(m.opt_disableflags & DSBL_CLAMPCTRL))
@@ -333,7 +333,7 @@ BP_STAGE void bp_fwd_actuation(const C& c) {
   }
   SYNC();
   // qfrc_actuator = moment^T force: each dof sums its own actuators in id order
-#pragma unroll 1
+#pragma unroll (C::UF)
   for (int d = c.lane; d < nv; d += C::G) {
     double s = 0;
     for (int k = m.dof_actadr[d]; k < m.dof_actadr[d + 1]; k++) {
@@ -346,7 +346,7 @@ BP_STAGE void bp_fwd_actuation(const C& c) {
 }
 
 BP_STAGE void bp_fwd_acceleration(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   auto fs = DF(qfrc_smooth), as = DF(qacc_smooth);
   for (int i = c.lane; i < m.nv; i += C::G) {
     double f = DF(qfrc_passive)[i] - DF(qfrc_bias)[i] + DF(qfrc_actuator)[i] +

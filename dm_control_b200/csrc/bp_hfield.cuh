@@ -21,7 +21,8 @@ struct HField {
   double rx, ry, zs, base, dx, dy;
 };
 
-__device__ __forceinline__ void hf_init(const BpModel& m, const float* env_data, int hid, HField& h) {
+template <class M_>
+__device__ __forceinline__ void hf_init(const M_& m, const float* env_data, int hid, HField& h) {
   h.data = env_data + m.hfield_adr[hid];
   h.nrow = m.hfield_nrow[hid]; h.ncol = m.hfield_ncol[hid];
   h.rx = m.hfield_size[4 * hid]; h.ry = m.hfield_size[4 * hid + 1];

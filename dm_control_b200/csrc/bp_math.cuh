@@ -10,6 +10,7 @@
 #ifndef BP_MATH_CUH_
 #define BP_MATH_CUH_
 #include "bp_types.h"
+#include <type_traits>
 
 template <class T, int S>
 struct SP {
@@ -28,16 +29,41 @@ struct SP {
 // cylinder geoms and actuator dynamics (the quadruped) and drops what only FULL has:
 // elliptic cones, fluid forces, spatial tendons, tendon limits and springs, box geoms, geom
 // priorities, per-env model frames.
-template <int G_, int S_, int SHAPE_ = 0>
+// lane inside the group; for G = 1 it is the compile-time constant 0, also inside the
+// out-of-line stage functions (which see the context by reference)
+template <int G>
+struct LaneT {
+  int v;
+  __device__ __forceinline__ LaneT(int x) : v(x) {}
+  __device__ __forceinline__ operator int() const { return v; }
+};
+template <>
+struct LaneT<1> {
+  __device__ __forceinline__ LaneT(int) {}
+  __device__ __forceinline__ operator int() const { return 0; }
+};
+
+// MT: static model traits (csrc/static/*.cuh, generated ahead of time from a compiled model
+// by tools/gen_static_model.py) or void.  With traits, the model's structure -- sizes, tree,
+// addresses, type tables, pair list, sensor list, the data layout -- is compile-time constant,
+// the structural loops unroll (UF) and every image access has a constant offset; parameters
+// that may be edited at run time (all float arrays, opt_*) are still read from BpModel.
+template <int G_, int S_, int SHAPE_ = 0, class MT_ = void>
 struct Ctx {
   static constexpr int G = G_, S = S_;
   static constexpr bool LEAN = SHAPE_ == 1, FULL = SHAPE_ == 0;
+  using MT = MT_;
+  static constexpr bool STATIC = !std::is_void<MT_>::value;
+#ifndef BP_UF
+#define BP_UF 1
+#endif
+  static constexpr int UF = STATIC ? BP_UF : 1;  // unroll factor of structural loops
   using DP = SP<double, S_>;
   using IP = SP<int, S_>;
   const BpParams& P;
   double* sm;      // element 0 of this env's image
   int* ip;         // element 0 of the int32 region
-  int lane;        // lane inside the group, 0 .. G-1
+  LaneT<G_> lane;  // lane inside the group, 0 .. G-1
   unsigned mask;   // warp lanes of this group
   bool act;        // false: this group has no environment (ragged tail / masked out)
   bool lock;       // true: the block's warps re-align at stage boundaries (BP_LOCK)
@@ -50,8 +76,21 @@ struct Ctx {
   __device__ __forceinline__ DP null() const { return DP{nullptr}; }
 };
 
-#define DF(f) (typename C::DP{c.sm + (long long)c.P.L.f * C::S})
-#define IF(f) (typename C::IP{c.ip + (long long)c.P.L.f * C::S})
+// model / layout as the stage functions see them: BpModel / BpLayout of the launch, or the
+// static traits' views of them
+template <class C>
+__device__ __forceinline__ decltype(auto) bp_mv(const C& c) {
+  if constexpr (C::STATIC) return typename C::MT::Model(c.P.m);
+  else return (c.P.m);
+}
+template <class C>
+__device__ __forceinline__ decltype(auto) bp_lv(const C& c) {
+  if constexpr (C::STATIC) return typename C::MT::Layout();
+  else return (c.P.L);
+}
+#define BP_MODEL(m) const auto& m = bp_mv(c)
+#define DF(f) (typename C::DP{c.sm + (long long)bp_lv(c).f * C::S})
+#define IF(f) (typename C::IP{c.ip + (long long)bp_lv(c).f * C::S})
 // solver arrays that live in the shared-memory arena when there is one (S == 1 only)
 #define HOT(f, off) ((C::S == 1 && c.hot) ? typename C::DP{c.hot + (off)} : DF(f))
 #define SYNC() do { if (C::G > 1) __syncwarp(c.mask); } while (0)

@@ -22,7 +22,7 @@
 // factor M and, for the implicit-damping Euler step, M + dt diag(damping) together
 template <class C>
 __device__ __forceinline__ void bp_factor_stage(const C& c) {
-    const BpModel& m = c.P.m;
+    BP_MODEL(m);
     auto qLD = DF(qLD), qM = DF(qM), MM = DF(s_MM);
     // (not in the shared-memory shape: its scratch does not survive the launch)
     const bool implicit = C::G != 32 && m.any_damping && m.opt_integrator == 0;
@@ -96,9 +96,9 @@ __device__ __forceinline__ void bp_forward(const C& c, bool skipsensor) {
 
 // zero the persistent image, qpos = qpos0 (mj_resetData, engine.py:268-289)
 BP_STAGE void bp_reset_image(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   typename C::DP img{c.sm};
-  for (int w = c.lane; w < c.P.L.persist; w += C::G) img[w] = 0;
+  for (int w = c.lane; w < bp_lv(c).persist; w += C::G) img[w] = 0;
   SYNC();
   for (int i = c.lane; i < m.nq; i += C::G) DF(qpos)[i] = m.qpos0[i];
   SYNC();
@@ -117,7 +117,7 @@ BP_STAGE bool bp_check(const C& c, typename C::DP x, int n, int w) {
 
 BP_STAGE void bp_integrate_pos(const C& c, typename C::DP qpos, typename C::DP qvel,
                                double dt) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
 #pragma unroll 1
   for (int j = c.lane; j < m.njnt; j += C::G) {
     int qa = m.jnt_qposadr[j], da = m.jnt_dofadr[j];
@@ -135,7 +135,7 @@ BP_STAGE void bp_integrate_pos(const C& c, typename C::DP qpos, typename C::DP q
 
 BP_STAGE void bp_advance(const C& c, typename C::DP act_dot, typename C::DP qacc,
                          typename C::DP qvel_for_pos) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   double dt = m.opt_timestep;
   for (int i = c.lane; i < m.na; i += C::G) DF(act)[i] += dt * act_dot[i];
   for (int i = c.lane; i < m.nv; i += C::G) DF(qvel)[i] += dt * qacc[i];
@@ -146,7 +146,7 @@ BP_STAGE void bp_advance(const C& c, typename C::DP act_dot, typename C::DP qacc
 }
 
 BP_STAGE void bp_euler(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   auto qa = DF(s_tmp);
   if (!m.any_damping) {
     for (int i = c.lane; i < m.nv; i += C::G) qa[i] = DF(qacc)[i];
@@ -177,7 +177,7 @@ struct RkView {
   typename C::DP q0, v0, a0, F, dX;
   int nq, nv, na, nf;
   __device__ __forceinline__ RkView(const C& c) {
-    const BpModel& m = c.P.m;
+    BP_MODEL(m);
     nq = m.nq; nv = m.nv; na = m.na; nf = 2 * nv + na;
     q0 = DF(s_rk); v0 = q0 + nq; a0 = v0 + nv; F = a0 + na; dX = F + 4 * nf;
   }
@@ -203,7 +203,7 @@ BP_STAGE void bp_rk4_stage(const C& c, int s) {
   RkView<C> r(c);
   const double A[3][3] = {{0.5, 0, 0}, {0, 0.5, 0}, {0, 0, 1}};
   const double Ct[3] = {0.5, 0.5, 1.0};
-  const double h = c.P.m.opt_timestep, t0 = r.dX[r.nf];
+  const double h = bp_mv(c).opt_timestep, t0 = r.dX[r.nf];
   for (int k = c.lane; k < r.nf; k += C::G) {
     double x = 0;
     for (int j = 0; j < s; j++) x += A[s - 1][j] * r.F[j * r.nf + k];
@@ -259,7 +259,7 @@ __device__ __forceinline__ void bp_rk4(const C& c) {
 // mj_checkAcc: a bad qacc resets the env and recomputes forward.  Data dependent, so
 // the recomputation runs without stage barriers.
 BP_STAGE void bp_check_acc(const C& c) {
-  if (bp_check(c, DF(qacc), c.P.m.nv, W_BADQACC)) {
+  if (bp_check(c, DF(qacc), bp_mv(c).nv, W_BADQACC)) {
     C solo = c;
     solo.lock = false;
     bp_forward(solo, false);
@@ -267,7 +267,7 @@ BP_STAGE void bp_check_acc(const C& c) {
 }
 
 BP_STAGE void bp_check_state(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   bp_check(c, DF(qpos), m.nq, W_BADQPOS);
   bp_check(c, DF(qvel), m.nv, W_BADQVEL);
 }
@@ -280,7 +280,7 @@ __device__ __forceinline__ void bp_mj_step(const C& c, bool skipsensor) {
   RUN(bp_check_state(c));
   bp_forward(c, skipsensor);
   RUN(bp_check_acc(c));
-  if (c.P.m.opt_integrator == 1) bp_rk4(c); else RUN(bp_euler(c));
+  if (bp_mv(c).opt_integrator == 1) bp_rk4(c); else RUN(bp_euler(c));
   BP_LOCK(6);
 }
 
@@ -355,7 +355,7 @@ __device__ __forceinline__ void bp_run_mode(const C& c) {
 #define BP_LOCKSTEP 1    // 1: warps of a block re-align at stage boundaries (BP_LOCK)
 #endif
 #define BP_BOUNDS __launch_bounds__(BP_TPB(G))
-template <int G, int S, int SHAPE>
+template <int G, int S, int SHAPE, class MT = void>
 __global__ void BP_BOUNDS
 bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
   const long long tid = blockIdx.x * (long long)blockDim.x + threadIdx.x;
@@ -386,7 +386,7 @@ bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
   const double* sp = P.env_site_pos ? P.env_site_pos + env * 3LL * P.m.nsite : P.m.site_pos;
   const double* bp = P.env_body_pos ? P.env_body_pos + env * 3LL * P.m.nbody : P.m.body_pos;
   const double* bq = P.env_body_quat ? P.env_body_quat + env * 4LL * P.m.nbody : P.m.body_quat;
-  Ctx<G, S, SHAPE> c{P, base, ib, wl & (G - 1), mask, act, lock, hot, hf, gp, sp, bp, bq};
+  Ctx<G, S, SHAPE, MT> c{P, base, ib, wl & (G - 1), mask, act, lock, hot, hf, gp, sp, bp, bq};
   bp_load_ctrl(c, env);
   bp_run_mode(c);
   if (P.rew_out && act) {           // epilogue: the task's observation and reward

@@ -7,7 +7,7 @@
 #include "bp_hfield.cuh"
 
 BP_STAGE void bp_subtree_vel(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   int nb = m.nbody;
   auto lv = DF(subtree_linvel), cvel = DF(cvel), com = DF(subtree_com), xipos = DF(xipos);
 #pragma unroll 1
@@ -20,7 +20,7 @@ BP_STAGE void bp_subtree_vel(const C& c) {
     for (int k = 0; k < 3; k++) lv[3 * b + k] = m.body_mass[b] * (cv[3 + k] + t[k]);
   }
   SYNC();
-  bp_tree_gather(c, lv, 3, 0);
+  bp_tree_gather<3>(c, lv, 0);
   for (int w = c.lane; w < 3 * nb; w += C::G) {
     double sm = m.body_subtreemass[w / 3];
     lv[w] /= (sm > BP_MINVAL ? sm : BP_MINVAL);
@@ -36,7 +36,7 @@ __device__ __forceinline__ void bp_contact_force(const C& c, int ci, double* f6)
   int dim = IF(contact_dim)[ci];
   auto ef = DF(efc_force);
   if (dim == 1) { f6[0] = ef[a]; return; }
-  if (c.P.m.opt_cone == 0) {
+  if (bp_mv(c).opt_cone == 0) {
     for (int k = 0; k < 2 * (dim - 1); k++) f6[0] += ef[a + k];
     for (int k = 1; k < dim; k++)
       f6[k] = DF(contact_friction)[5 * ci + k - 1] * (ef[a + 2 * k - 2] - ef[a + 2 * k - 1]);
@@ -46,7 +46,7 @@ __device__ __forceinline__ void bp_contact_force(const C& c, int ci, double* f6)
 }
 
 BP_STAGE void bp_rne_post_constraint(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   int nb = m.nbody, ncon = IF(ncon)[0];
   auto ext = DF(cfrc_ext), com = DF(subtree_com);
   // each body gathers its own contacts in contact order (no atomics, fixed order)
@@ -83,7 +83,7 @@ BP_STAGE void bp_rne_post_constraint(const C& c) {
 
 template <class C>
 __device__ __forceinline__ bool bp_inside_site(const C& c, int s, const double* p) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   auto sp = DF(site_xpos) + 3 * s;
   double dif[3] = {p[0] - sp[0], p[1] - sp[1], p[2] - sp[2]}, l[3];
   matT_vec3(l, DF(site_xmat) + 9 * s, dif);
@@ -109,7 +109,7 @@ __device__ __forceinline__ bool bp_inside_site(const C& c, int s, const double* 
 template <class C>
 __device__ __forceinline__ int bp_obj_frame(const C& c, int objtype, int id, double* pos,
                                             double* mat) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   typename C::DP p, R;
   int body;
   if (objtype == OBJ_SITE) { p = DF(site_xpos) + 3 * id; R = DF(site_xmat) + 9 * id; body = m.site_bodyid[id]; }
@@ -124,7 +124,7 @@ __device__ __forceinline__ int bp_obj_frame(const C& c, int objtype, int id, dou
 // mj_ray: nearest geom surface along the unit ray (pnt, vec), geoms of `bodyexclude`
 // skipped; -1 without a hit (the rangefinder's reading, quadruped.py:212-217)
 BP_STAGE double bp_ray(const C& c, const double* pnt, const double* vec, int bodyexclude) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   auto gpos = DF(geom_xpos), gmat = DF(geom_xmat);
   double best = -1;
 #pragma unroll 1
@@ -151,7 +151,7 @@ BP_STAGE double bp_ray(const C& c, const double* pnt, const double* vec, int bod
 }
 
 BP_STAGE void bp_sensors(const C& c, int stage) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   if (m.nsensor == 0) return;
   if (stage == STAGE_VEL && m.need_subtreevel) bp_subtree_vel(c);
   if (stage == m.need_rnepost_stage) bp_rne_post_constraint(c);
@@ -250,7 +250,7 @@ BP_STAGE void bp_sensors(const C& c, int stage) {
 }
 
 BP_STAGE void bp_energy_pos(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   auto en = DF(energy);
   if (!(m.opt_enableflags & ENBL_ENERGY)) {
     for (int i = c.lane; i < 2; i += C::G) en[i] = 0;
@@ -276,7 +276,7 @@ BP_STAGE void bp_energy_pos(const C& c) {
 
 // kinetic energy 0.5 v^T M v from the sparse qM
 BP_STAGE void bp_energy_vel(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   if (!(m.opt_enableflags & ENBL_ENERGY)) return;
   auto qM = DF(qM), v = DF(qvel);
   double e = 0;

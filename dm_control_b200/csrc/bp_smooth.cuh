@@ -11,7 +11,7 @@
 #include "bp_math.cuh"
 
 BP_STAGE void bp_kinematics(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   auto qpos = DF(qpos), xpos = DF(xpos), xquat = DF(xquat), xmat = DF(xmat);
   auto xanchor = DF(xanchor), xaxis = DF(xaxis);
   for (int j = c.lane; j < m.njnt; j += C::G) {
@@ -25,9 +25,9 @@ BP_STAGE void bp_kinematics(const C& c) {
     xmat[i] = (i % 4 == 0) ? 1.0 : 0.0;
   }
   SYNC();
-#pragma unroll 1
+#pragma unroll (C::UF)
   for (int lev = 1; lev < m.nlevel; lev++) {
-#pragma unroll 1
+#pragma unroll (C::UF)
     for (int idx = m.body_level_adr[lev] + c.lane; idx < m.body_level_adr[lev + 1];
          idx += C::G) {
       int b = m.body_level_list[idx], p = m.body_parentid[b];
@@ -36,7 +36,7 @@ BP_STAGE void bp_kinematics(const C& c) {
       for (int k = 0; k < 3; k++) pos[k] = xpos[3 * p + k] + t[k];
       quat_mul(quat, xquat + 4 * p, (C::FULL ? c.bquat : m.body_quat) + 4 * b);
       int jn = m.body_jntnum[b], j0 = m.body_jntadr[b];
-#pragma unroll 1
+#pragma unroll (C::UF)
       for (int k = 0; k < jn; k++) {
         int j = j0 + k, qa = m.jnt_qposadr[j], jt = m.jnt_type[j];
         if (jt == JNT_FREE) {
@@ -75,7 +75,7 @@ BP_STAGE void bp_kinematics(const C& c) {
   }
   // inertial frames, geoms and sites hang off finished body frames: one flat loop
   int nb = m.nbody, ng = m.ngeom, ns = m.nsite;
-#pragma unroll 1
+#pragma unroll (C::UF)
   for (int w = c.lane; w < nb + ng + ns; w += C::G) {
     const double *lp, *lq;
     typename C::DP op, om;
@@ -104,18 +104,19 @@ BP_STAGE void bp_kinematics(const C& c) {
 
 // vals[b*n .. b*n+n) += sum over children, from the deepest level up to `stop_level`
 // (stop_level = 0 also accumulates into the world body, 1 leaves it untouched)
-BP_STAGE void bp_tree_gather(const C& c, typename C::DP vals, int n, int stop_level) {
-  const BpModel& m = c.P.m;
-#pragma unroll 1
+template <int n, class C>
+__device__ __noinline__ void bp_tree_gather(const C& c, typename C::DP vals, int stop_level) {
+  BP_MODEL(m);
+#pragma unroll (C::UF)
   for (int lev = m.nlevel - 2; lev >= stop_level; lev--) {
     int a0 = m.body_level_adr[lev], cnt = m.body_level_adr[lev + 1] - a0;
-#pragma unroll 1
+#pragma unroll (C::UF)
     for (int w = c.lane; w < cnt * n; w += C::G) {
       int b = m.body_level_list[a0 + w / n], k = w % n;
       int c0 = m.body_child_adr[b], c1 = m.body_child_adr[b + 1];
       if (c1 > c0) {
         double s = vals[b * n + k];
-#pragma unroll 1
+#pragma unroll (C::UF)
         for (int ci = c0; ci < c1; ci++) s += vals[m.body_child_list[ci] * n + k];
         vals[b * n + k] = s;
       }
@@ -125,19 +126,19 @@ BP_STAGE void bp_tree_gather(const C& c, typename C::DP vals, int n, int stop_le
 }
 
 BP_STAGE void bp_com_pos(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   int nb = m.nbody;
   auto com = DF(subtree_com), xipos = DF(xipos);
   for (int w = c.lane; w < 3 * nb; w += C::G) com[w] = m.body_mass[w / 3] * xipos[w];
   SYNC();
-  bp_tree_gather(c, com, 3, 0);
+  bp_tree_gather<3>(c, com, 0);
   for (int w = c.lane; w < 3 * nb; w += C::G) {
     double sm = m.body_subtreemass[w / 3];
     com[w] = sm < BP_MINVAL ? xipos[w] : com[w] / sm;
   }
   SYNC();
   auto cinert = DF(cinert), ximat = DF(ximat);
-#pragma unroll 1
+#pragma unroll (C::UF)
   for (int b = 1 + c.lane; b < nb; b += C::G) {
     auto R = ximat + 9 * b;
     const double* I = m.body_inertia + 3 * b;
@@ -161,7 +162,7 @@ BP_STAGE void bp_com_pos(const C& c) {
   }
   for (int i = c.lane; i < 10; i += C::G) cinert[i] = 0;
   auto cdof = DF(cdof), xanchor = DF(xanchor), xaxis = DF(xaxis), xmat = DF(xmat);
-#pragma unroll 1
+#pragma unroll (C::UF)
   for (int j = c.lane; j < m.njnt; j += C::G) {
     int b = m.jnt_bodyid[j], da = m.jnt_dofadr[j], jt = m.jnt_type[j];
     auto cm = com + 3 * m.body_rootid[b];
@@ -196,18 +197,18 @@ BP_STAGE void bp_com_pos(const C& c) {
 }
 
 BP_STAGE void bp_crb(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   auto crb = DF(crb), cinert = DF(cinert), cdof = DF(cdof), qM = DF(qM);
   for (int w = c.lane; w < 10 * m.nbody; w += C::G) crb[w] = cinert[w];
   SYNC();
-  bp_tree_gather(c, crb, 10, 1);
-#pragma unroll 1
+  bp_tree_gather<10>(c, crb, 1);
+#pragma unroll (C::UF)
   for (int i = c.lane; i < m.nv; i += C::G) {
     double buf[6];
     inert_mul(buf, crb + 10 * m.dof_bodyid[i], cdof + 6 * i);
     int adr = m.dof_Madr[i];
     qM[adr++] = m.dof_armature[i] + dot6(cdof + 6 * i, buf);
-#pragma unroll 1
+#pragma unroll (C::UF)
     for (int j = m.dof_parentid[i]; j >= 0; j = m.dof_parentid[j])
       qM[adr++] = dot6(cdof + 6 * j, buf);
   }
@@ -219,26 +220,26 @@ BP_STAGE void bp_crb(const C& c) {
 // along: it shares every index load and barrier of the first.
 BP_STAGE void bp_factor_sparse(const C& c, typename C::DP LD, typename C::DP diaginv,
                                typename C::DP LD2, typename C::DP diaginv2) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   const bool two = LD2.valid();
-#pragma unroll 1
+#pragma unroll (C::UF)
   for (int k = m.nv - 1; k >= 0; k--) {
     int akk = m.dof_Madr[k], na = m.dof_depth[k];
     double dkk = LD[akk], dkk2 = two ? LD2[akk] : 1.0;
-#pragma unroll 1
+#pragma unroll (C::UF)
     for (int a = 1 + c.lane; a <= na; a += C::G) {
       double t = LD[akk + a] / dkk;
       int i = m.M_col[akk + a];
       int aij = m.dof_Madr[i];
       if (two) {
         double t2 = LD2[akk + a] / dkk2;
-#pragma unroll 1
+#pragma unroll (C::UF)
         for (int b = a; b <= na; b++, aij++) {
           LD[aij] -= t * LD[akk + b];
           LD2[aij] -= t2 * LD2[akk + b];
         }
       } else {
-#pragma unroll 1
+#pragma unroll (C::UF)
         for (int b = a; b <= na; b++) LD[aij++] -= t * LD[akk + b];
       }
     }
@@ -258,9 +259,9 @@ BP_STAGE void bp_factor_sparse(const C& c, typename C::DP LD, typename C::DP dia
 // x <- M^-1 x with the factor above
 BP_STAGE void bp_solve_sparse(const C& c, typename C::DP LD, typename C::DP diaginv,
                               typename C::DP x) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   int nv = m.nv;
-#pragma unroll 1
+#pragma unroll (C::UF)
   for (int i = nv - 1; i >= 0; i--) {          // x <- L^-T x
     int a0 = m.dof_Madr[i] + 1, na = m.dof_depth[i];
     double xi = x[i];
@@ -269,9 +270,9 @@ BP_STAGE void bp_solve_sparse(const C& c, typename C::DP LD, typename C::DP diag
   }
   for (int i = c.lane; i < nv; i += C::G) x[i] *= diaginv[i];
   SYNC();
-#pragma unroll 1
+#pragma unroll (C::UF)
   for (int lev = 1; lev < m.ndoflevel; lev++) { // x <- L^-1 x, depth by depth
-#pragma unroll 1
+#pragma unroll (C::UF)
     for (int idx = m.dof_level_adr[lev] + c.lane; idx < m.dof_level_adr[lev + 1];
          idx += C::G) {
       int i = m.dof_level_list[idx], a = m.dof_Madr[i] + 1;

@@ -36,15 +36,15 @@ __device__ __forceinline__ void bp_copy(const C& c, typename C::DP dst, typename
 // y = M x with M a packed lower triangle (row i at i (i + 1) / 2): row i reads its own
 // packed row up to the diagonal, then walks down column i
 BP_STAGE void bp_mul_md(const C& c, typename C::DP Mp, typename C::DP y, typename C::DP x) {
-  const int nv = c.P.m.nv;
-#pragma unroll 1
+  const int nv = bp_mv(c).nv;
+#pragma unroll (C::UF)
   for (int i = c.lane; i < nv; i += C::G) {
     double s = 0;
     const int ri = i * (i + 1) / 2;
-#pragma unroll 4
+#pragma unroll (C::UF > 4 ? C::UF : 4)
     for (int j = 0; j <= i; j++) s += Mp[ri + j] * x[j];
     int a = ri + 2 * i + 1;                       // (i + 1, i)
-#pragma unroll 4
+#pragma unroll (C::UF > 4 ? C::UF : 4)
     for (int j = i + 1; j < nv; j++) { s += Mp[a] * x[j]; a += j + 1; }
     y[i] = s;
   }
@@ -54,12 +54,12 @@ BP_STAGE void bp_mul_md(const C& c, typename C::DP Mp, typename C::DP y, typenam
 // out[r] = J[r,:] x - (sub ? sub[r] : 0)
 BP_STAGE void bp_mul_j(const C& c, typename C::DP out, typename C::DP x, typename C::DP sub,
                        int nefc) {
-  const int nv = c.P.m.nv, nvp = c.P.m.nvp;
+  const int nv = bp_mv(c).nv, nvp = bp_mv(c).nvp;
   auto J = DF(efc_J);
 #pragma unroll 1
   for (int r = c.lane; r < nefc; r += C::G) {
     double s = 0;
-#pragma unroll 4
+#pragma unroll (C::UF > 4 ? C::UF : 4)
     for (int i = 0; i < nv; i++) s += J[r * nvp + i] * x[i];
     out[r] = sub.valid() ? s - sub[r] : s;
   }
@@ -159,7 +159,7 @@ BP_STAGE void bp_cone_ls(const C& c, double alpha, int nefc, double* q, double* 
 // S = diag(mu, fri), u = U_t / T, g = (1, -mu u), P = I - u u^T on the tangential block,
 // kappa = mu^2 - mu N / T.  One contact at a time; its dof-set pairs over the lanes.
 BP_STAGE void bp_cone_hessian(const C& c, typename C::DP H, int nefc) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   const int ncon = IF(ncon)[0], nvp = m.nvp;
   auto J = DF(efc_J), jar = DF(s_jar), D = DF(efc_D);
 #pragma unroll 1
@@ -210,7 +210,7 @@ BP_STAGE void bp_cone_hessian(const C& c, typename C::DP H, int nefc) {
 // the factorisation of H is stale
 BP_STAGE double bp_update_constraint(const C& c, typename C::DP jar, int nefc, bool write,
                                      bool* changed) {
-  const int nv = c.P.m.nv, nvp = c.P.m.nvp;
+  const int nv = bp_mv(c).nv, nvp = bp_mv(c).nvp;
   double cost = 0;
   bool chg = false;
   auto force = DF(efc_force), D = DF(efc_D), R = DF(efc_R);
@@ -239,14 +239,14 @@ BP_STAGE double bp_update_constraint(const C& c, typename C::DP jar, int nefc, b
       DF(s_rw)[r] = w;
     }
   }
-  if constexpr (C::FULL) if (c.P.m.opt_cone == 1) cost += bp_cone_update(c, jar, nefc, write, &chg);
+  if constexpr (C::FULL) if (bp_mv(c).opt_cone == 1) cost += bp_cone_update(c, jar, nefc, write, &chg);
   cost = group_sum(c, cost);
   if (write) {
     *changed = group_any(c, chg);
     SYNC();
     auto J = DF(efc_J);
     auto qc = DF(qfrc_constraint);
-#pragma unroll 1
+#pragma unroll (C::UF)
     for (int i = c.lane; i < nv; i += C::G) {
       double s = 0;
 #pragma unroll 4
@@ -261,7 +261,7 @@ BP_STAGE double bp_update_constraint(const C& c, typename C::DP jar, int nefc, b
 template <class C>
 __device__ __forceinline__ double bp_gauss_cost(const C& c) {
   double g = 0;
-  for (int i = c.lane; i < c.P.m.nv; i += C::G)
+  for (int i = c.lane; i < bp_mv(c).nv; i += C::G)
     g += 0.5 * (DF(s_Ma)[i] - DF(qfrc_smooth)[i]) * (DF(qacc)[i] - DF(qacc_smooth)[i]);
   return group_sum(c, g);
 }
@@ -288,7 +288,7 @@ BP_STAGE LSPoint bp_ls_eval(const C& c, double alpha, double g0, double g1, doub
     else if (x < 0) { c0 += q0; c1 += q1; c2 += q2; }
   }
   double e[3] = {0, 0, 0};
-  if constexpr (C::FULL) if (c.P.m.opt_cone == 1) {
+  if constexpr (C::FULL) if (bp_mv(c).opt_cone == 1) {
     double q[3] = {0, 0, 0};
     bp_cone_ls(c, alpha, nefc, q, e);
     c0 += q[0]; c1 += q[1]; c2 += q[2];
@@ -304,7 +304,7 @@ BP_STAGE LSPoint bp_ls_eval(const C& c, double alpha, double g0, double g1, doub
 
 // exact 1-D minimisation along s_search (safeguarded Newton on the derivative)
 BP_STAGE double bp_linesearch(const C& c, double scale, int nefc) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   double sn = 0, g0 = 0, g1 = 0, g2 = 0;
   for (int i = c.lane; i < m.nv; i += C::G) {
     double s = DF(s_search)[i], r = DF(s_Ma)[i] - DF(qfrc_smooth)[i];
@@ -358,8 +358,8 @@ __device__ __forceinline__ double group_bcast(const C& c, double v, int src) {
 
 // Returns false when a pivot is not positive.
 BP_STAGE bool bp_chol_factor_generic(const C& c, typename C::DP H, typename C::DP dinv) {
-  const int n = c.P.m.nv;
-#pragma unroll 1
+  const int n = bp_mv(c).nv;
+#pragma unroll (C::UF)
   for (int j = 0; j < n; j++) {
     double s = H[PK(j, j)];
     if (s < BP_MINVAL) return false;      // uniform across the group
@@ -369,7 +369,7 @@ BP_STAGE bool bp_chol_factor_generic(const C& c, typename C::DP H, typename C::D
     if (c.lane == 0) { H[PK(j, j)] = s; dinv[j] = inv; }
     for (int i = j + 1 + c.lane; i < n; i += C::G) H[PK(i, j)] /= s;
     SYNC();
-#pragma unroll 1
+#pragma unroll (C::UF)
     for (int i = j + 1 + c.lane; i < n; i += C::G) {
       double lij = H[PK(i, j)];
       for (int k = j + 1; k <= i; k++) H[PK(i, k)] -= lij * H[PK(k, j)];
@@ -452,7 +452,7 @@ __device__ __forceinline__ bool bp_chol_factor_t(const C& c, typename C::DP H,
 }
 
 BP_STAGE bool bp_chol_factor(const C& c, typename C::DP H, typename C::DP dinv) {
-  const int n = c.P.m.nv;
+  const int n = bp_mv(c).nv;
   if (n > BP_RS * C::G) return bp_chol_factor_generic(c, H, dinv);
   const int nrows = bp_chol_fused<C>(n) ? n + 1 : n;
   switch ((nrows + C::G - 1) / C::G) {
@@ -465,8 +465,8 @@ BP_STAGE bool bp_chol_factor(const C& c, typename C::DP H, typename C::DP dinv) 
 
 BP_STAGE void bp_chol_solve_generic(const C& c, typename C::DP L, typename C::DP dinv,
                                     typename C::DP x) {
-  const int n = c.P.m.nv;
-#pragma unroll 1
+  const int n = bp_mv(c).nv;
+#pragma unroll (C::UF)
   for (int k = 0; k < n; k++) {
     double xk = x[k] * dinv[k];
     SYNC();
@@ -474,7 +474,7 @@ BP_STAGE void bp_chol_solve_generic(const C& c, typename C::DP L, typename C::DP
     for (int i = k + 1 + c.lane; i < n; i += C::G) x[i] -= L[PK(i, k)] * xk;
     SYNC();
   }
-#pragma unroll 1
+#pragma unroll (C::UF)
   for (int k = n - 1; k >= 0; k--) {
     double xk = x[k] * dinv[k];
     SYNC();
@@ -529,7 +529,7 @@ __device__ __forceinline__ void bp_chol_solve_t(const C& c, typename C::DP L, ty
 // x <- H^-1 x.  `fwd_done`: y = L^-1 x already sits in row n of L (see bp_chol_fused)
 BP_STAGE void bp_chol_solve(const C& c, typename C::DP L, typename C::DP dinv,
                             typename C::DP x, bool fwd_done) {
-  const int n = c.P.m.nv;
+  const int n = bp_mv(c).nv;
   if (n > BP_RS * C::G) { bp_chol_solve_generic(c, L, dinv, x); return; }
   switch ((n + C::G - 1) / C::G) {
     case 1: bp_chol_solve_t<C, 1>(c, L, dinv, x, fwd_done, n); break;
@@ -544,7 +544,7 @@ template <class C>
 __device__ __forceinline__ double bp_newton_grad(const C& c) {
   auto grad = DF(s_grad);
   double gn = 0;
-  for (int i = c.lane; i < c.P.m.nv; i += C::G) {
+  for (int i = c.lane; i < bp_mv(c).nv; i += C::G) {
     double g = DF(s_Ma)[i] - DF(qfrc_smooth)[i] - DF(qfrc_constraint)[i];
     grad[i] = g;
     gn += g * g;
@@ -563,7 +563,7 @@ __device__ __forceinline__ double bp_newton_grad(const C& c) {
 // k (k + 1) / 2 entries of that dof set, split over the lanes by outer dof.
 BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, int ntenlim,
                                   bool refactor) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   const int nv = m.nv, nvp = m.nvp;
   const int ntri = m.ntri;
   auto H = HOT(s_H, 0), Hdinv = HOT(s_Hdinv, ntri + nv), Mgrad = HOT(s_Mgrad, ntri + 2 * nv);
@@ -579,7 +579,7 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, int ntenlim,
   for (int i = c.lane; i < nv; i += C::G) H[ntri + i] = grad[i];     // bordered rhs row
   SYNC();
   const int ne = IF(ne)[0];
-#pragma unroll 1
+#pragma unroll (C::UF)
   for (int i = c.lane; i < nv; i += C::G) {
     double acc = 0;
     for (int r = ne; r < ne + nsingle; r++)
@@ -665,7 +665,7 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, int ntenlim,
 
 // CG [MJ-doc A.9]: the primal gradient preconditioned by the sparse factor of M
 BP_STAGE void bp_cg_gradient(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   auto Mg = HOT(s_Mgrad, m.ntri + 2 * m.nv), grad = DF(s_grad);
   for (int i = c.lane; i < m.nv; i += C::G) Mg[i] = grad[i];
   SYNC();
@@ -680,7 +680,7 @@ BP_STAGE void bp_cg_gradient(const C& c) {
 // row dot products run on the lanes.  oracle/mjstep_oracle.c pgs_solve is the restatement
 // this is held to.
 BP_STAGE void bp_solver_pgs(const C& c) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   const int nv = m.nv, nvp = m.nvp, nefc = IF(nefc)[0];
   auto qacc = DF(qacc), warm = DF(qacc_warmstart), as = DF(qacc_smooth);
   if (nefc == 0) {
@@ -771,7 +771,7 @@ BP_STAGE void bp_solver_pgs(const C& c) {
     state[i] = st;
   }
   auto qc = DF(qfrc_constraint);
-#pragma unroll 1
+#pragma unroll (C::UF)
   for (int i = c.lane; i < nv; i += C::G) {
     double s = 0;
     for (int r = 0; r < nefc; r++) s += J[r * nvp + i] * f[r];
@@ -800,7 +800,7 @@ struct BpSolve {
 
 // everything up to the first search direction; st.done when there is nothing to iterate
 BP_STAGE void bp_solver_begin(const C& c, BpSolve& st) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   const int nv = m.nv, nvp = m.nvp, nefc = IF(nefc)[0];
   auto qacc = DF(qacc), warm = DF(qacc_warmstart), as = DF(qacc_smooth);
   st.iter = 0; st.improvement = 0; st.gradient = 0; st.nefc = nefc; st.nsingle = 0; st.ntenlim = 0;
@@ -833,7 +833,7 @@ BP_STAGE void bp_solver_begin(const C& c, BpSolve& st) {
   auto Md = DF(s_Md), qM = DF(qM);
   for (int w = c.lane; w < m.ntri; w += C::G) Md[w] = 0;
   SYNC();
-#pragma unroll 1
+#pragma unroll (C::UF)
   for (int i = c.lane; i < nv; i += C::G) {
     int a = m.dof_Madr[i];
     const int ri = i * (i + 1) / 2;
@@ -874,7 +874,7 @@ BP_STAGE void bp_solver_begin(const C& c, BpSolve& st) {
 //   step:      line search along s_search, state update, cost, gradient, convergence test
 //   direction: new search direction -- only for environments that go on
 BP_STAGE void bp_solver_step(const C& c, BpSolve& st) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   const int nv = m.nv, nefc = st.nefc;
   auto qacc = DF(qacc), Ma = DF(s_Ma), jar = DF(s_jar), search = DF(s_search);
   const double scale = 1.0 / (m.stat_meaninertia * (nv > 1 ? nv : 1));
@@ -908,7 +908,7 @@ BP_STAGE void bp_solver_step(const C& c, BpSolve& st) {
 }
 
 BP_STAGE void bp_solver_direction(const C& c, BpSolve& st) {
-  const BpModel& m = c.P.m;
+  BP_MODEL(m);
   if constexpr (C::FULL) if (m.opt_solver == 1) {     // CG: search = -Mgrad + beta search
     bp_cg_gradient(c);
     auto Mg = HOT(s_Mgrad, m.ntri + 2 * m.nv), Mgold = DF(s_tmp), sr = DF(s_search);
@@ -936,7 +936,7 @@ __device__ __forceinline__ void bp_solver_iterate(const C& c, BpSolve& st) {
 
 BP_STAGE void bp_solver_end(const C& c, const BpSolve& st) {
   if (st.nefc == 0) return;
-  const int nv = c.P.m.nv;
+  const int nv = bp_mv(c).nv;
   if (c.lane == 0) {
     IF(solver_iter)[0] = st.iter;
     DF(solver_stat)[0] = st.improvement; DF(solver_stat)[1] = st.gradient;
@@ -950,7 +950,7 @@ BP_STAGE void bp_solver_end(const C& c, const BpSolve& st) {
 // iteration (environments that are done skip the body).
 template <class C>
 __device__ __forceinline__ void bp_fwd_constraint(const C& c) {
-  if constexpr (C::FULL) if (c.P.m.opt_solver == 0) {    // uniform per launch
+  if constexpr (C::FULL) if (bp_mv(c).opt_solver == 0) {    // uniform per launch
     RUN(bp_solver_pgs(c));
     return;
   }

@@ -30,8 +30,9 @@ class PhysicsError(RuntimeError):
 # chosen from the sweep in profiles/)
 def default_lanes(m):
   """Execution shape from the lane sweeps (profiles/r1_tuning.md): 8 lanes per env for the
-  planar models, 16 for humanoid-sized ones (both run the 64-register build)."""
-  return 8 if m.nv <= 12 else 16
+  planar models, 16 for humanoid-sized ones (both run the 72-register build); the finger
+  (nv = 3) runs 4 lanes, which is also what its static instance is built for."""
+  return 4 if m.nv <= 3 else 8 if m.nv <= 12 else 16
 
 
 def default_sizes(m):

@@ -415,6 +415,8 @@ def build_environment(domain_name, task_name, task_kwargs=None, environment_kwar
     m = mjcf_compiler.compile_xml(lqr.make_model(tdef.model[0], tdef.model[1], model_rng))
   else:
     m = _load_model(tdef.model)
+  if njmax is None and nconmax is None and tdef.model in T.STATIC_SIZES:
+    njmax, nconmax = T.STATIC_SIZES[tdef.model]
   physics = BatchedPhysics(m, nenv, device=device, lanes=lanes, njmax=njmax, nconmax=nconmax)
   task = Task(tdef, random=task_kwargs.pop("random", None))
   task_kwargs.pop("model_seed", None)

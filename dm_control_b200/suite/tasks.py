@@ -338,6 +338,13 @@ for _t in _TASKS:
 ALL_TASKS = tuple(sorted(REGISTRY))
 
 
+# Batch sizes (njmax, nconmax) of the models that have a static (ahead-of-time specialised)
+# kernel instance (csrc/static/*.cuh, tools/gen_static_model.py TRAITS): suite.load uses them
+# by default so that its batches are served by those instances.
+STATIC_SIZES = {"cheetah": (64, 16), "walker": (48, 12), "humanoid": (120, 40),
+                "quadruped_escape": (184, 42), "finger": (24, 6)}
+
+
 def n_sub_steps(tdef, m):
   """rl/control.py:164-190 compute_n_steps."""
   if tdef.control_timestep is None:

@@ -387,3 +387,48 @@ def test_reference_test_humanoid_rk4_pgs(lanes):
                              flat_model=m)
   _assert_parity(res)
   assert max(stats["nefc"]) > 5
+
+
+@pytest.mark.parametrize("domain,lanes,sizes", [
+    ("cheetah", 8, dict(njmax=64, nconmax=16)), ("walker", 8, dict(njmax=48, nconmax=12)),
+    ("humanoid", 16, dict(njmax=120, nconmax=40)),
+    ("quadruped_escape", 16, dict(njmax=184, nconmax=42)), ("finger", 4, dict(njmax=24, nconmax=6))])
+def test_static_instances_match_oracle(domain, lanes, sizes, monkeypatch):
+  """The ahead-of-time specialised kernels (csrc/bp_step_static.cu, static/*.cuh: the model's
+  structure and the data layout as compile-time constants) at the lane widths and batch sizes
+  they are generated for: every field against the oracle, and the same results as the generic
+  kernel of that lane width (same arithmetic in the same order; FMA contraction may differ)."""
+  nenv = 160 if domain == "finger" else 48
+  res, stats = PU.run_parity(domain, nenv=nenv, nsteps=10, seed=5, check_steps=[0, 1, 2, 10],
+                             lanes=lanes, **sizes)
+  _assert_parity(res)
+  assert max(stats["nefc"]) > 0.5
+  from dm_control_b200 import binding
+  m = PU.load_model(domain)
+  qpos, qvel, ctrl = PU.random_states(m, 40, 3)
+  hfield = None
+  if int(m.nhfielddata) > 0:
+    hfield = np.stack([PU.escape_terrain(np.random.RandomState(50 + e)) for e in range(40)])
+    PU.terrain_states(m, qpos, hfield, 21)
+  out = []
+  for static in (True, False):
+    if static:
+      monkeypatch.delenv("BPHYS_NO_STATIC", raising=False)
+    else:
+      monkeypatch.setenv("BPHYS_NO_STATIC", "1")
+    model = binding.Model(m)
+    b = binding.Batch(model, 40, sizes["njmax"], sizes["nconmax"], lanes)
+    b.write("qpos", qpos); b.write("qvel", qvel); b.write("ctrl", ctrl)
+    if hfield is not None:
+      b.write_hfield(hfield)
+    b.forward()
+    b.step(5)
+    b.sync()
+    out.append({n: b.read(n) for n in ("qpos", "qvel", "qacc", "sensordata", "efc_force",
+                                       "nefc", "ncon", "solver_iter")})
+    b.free(); model.free()
+  for n in out[0]:
+    if out[0][n].dtype.kind == "f":
+      assert PU.rel_err(out[0][n], out[1][n]) <= 1e-10, n
+    else:
+      np.testing.assert_array_equal(out[0][n], out[1][n], err_msg=n)
