@@ -994,7 +994,7 @@ extern "C" int bp_reset(bp_batch* b, int key) {
 
 extern "C" int bp_set_task(bp_batch* b, int kind, const int32_t* ip, int nip,
                            const double* fp, int nfp) {
-  if (!b || nip < 0 || nip > 16 || nfp < 0 || nfp > 8) return fail(BP_EINVAL, "bad task arguments");
+  if (!b || nip < 0 || nip > 24 || nfp < 0 || nfp > 8) return fail(BP_EINVAL, "bad task arguments");
   BpTask t;
   memset(&t, 0, sizeof t);
   t.kind = kind;

@@ -26,6 +26,7 @@ extern "C" int bp_task_nobs_impl(const BpModel* m, int task) {
     case TASK_SWIMMER: return (m->nq - 3) + 2 + 3 * (m->nbody - 1);
     case TASK_LQR: return m->nq + m->nv;
     case TASK_MANIPULATOR: return 16 + 8 + 5 + 4 + 4 + 3 + 4;
+    case TASK_STACKER: return 16 + 8 + 5 + 4 + 7 * ((m->nq - 8) / 3) + 2;
     case TASK_BALL_IN_CUP: return m->nq + m->nv;
     case TASK_FISH_UPRIGHT: return (m->nq - 7) + 1 + m->nv;
     case TASK_FISH_SWIM: return (m->nq - 7) + 1 + 3 + m->nv;

@@ -19,7 +19,7 @@ enum { TASK_NONE = 0, TASK_CARTPOLE = 1, TASK_ACROBOT = 2, TASK_PENDULUM = 3,
        TASK_LQR = 12, TASK_POINT_MASS = 13, TASK_FINGER_TURN = 14,
        TASK_SWIMMER = 15, TASK_FISH_UPRIGHT = 16,
        TASK_FISH_SWIM = 17, TASK_BALL_IN_CUP = 18,
-       TASK_MANIPULATOR = 19, TASK_QUADRUPED_FETCH = 20 };
+       TASK_MANIPULATOR = 19, TASK_QUADRUPED_FETCH = 20, TASK_STACKER = 21 };
 enum { SIG_GAUSSIAN = 0, SIG_LINEAR = 1, SIG_QUADRATIC = 2, SIG_LONG_TAIL = 3 };
 
 // read-only strided window of one environment's image (see bp_math.cuh for layouts)
@@ -333,12 +333,62 @@ static __device__ __noinline__ void bp_task_eval(const BpParams& P, const BpTask
           if (q == 1) for (int i = 0; i < 3; i++) o[k++] = qvel[T.ip[12] + i];
         }
       }
-      double dd = 0;
-      for (int i = 0; i < 3; i++) {
-        double e = sx[3 * T.ip[13] + i] - sx[3 * T.ip[14] + i];
-        dd += e * e;
+      auto close = [&](int s1, int s2) {        // _is_close(site_distance(s1, s2))
+        double dd = 0;
+        for (int i = 0; i < 3; i++) {
+          double e = sx[3 * s1 + i] - sx[3 * s2 + i];
+          dd += e * e;
+        }
+        return tolerance(sqrt(dd), 0, T.fp[0], 2 * T.fp[0], SIG_GAUSSIAN, .1);
+      };
+      if (T.ip[15]) {
+        // _peg_reward (manipulator.py:276-286).  ip[16..21]: sites peg_grasp, grasp, peg_pinch,
+        // pinch, target_peg_tip, peg_tip
+        const double grasping = (close(T.ip[16], T.ip[17]) + close(T.ip[18], T.ip[19])) / 2;
+        const double bringing = (close(T.ip[13], T.ip[14]) + close(T.ip[20], T.ip[21])) / 2;
+        r = fmax(bringing, grasping / 3);
+      } else {
+        r = close(T.ip[13], T.ip[14]);        // _ball_reward
       }
-      r = tolerance(sqrt(dd), 0, T.fp[0], 2 * T.fp[0], SIG_GAUSSIAN, .1);
+      break;
+    }
+    case TASK_STACKER: {      // suite/stacker.py:187-214
+      // ip[0..7]: arm joint addresses, [8] first touch sensor, [9] hand body, [10] number of
+      // boxes, [11] first box body, [12] first box joint (dof) address, [13] target body,
+      // [14] grasp site, [15] target site, [16] first box site; fp: box size, _CLOSE
+      const ImgView sx = d.at(L.site_xpos), xp = d.at(L.xpos), xq = d.at(L.xquat);
+      const int nb = T.ip[10];
+      if (o) {
+        for (int i = 0; i < 8; i++) { o[k++] = sin(qpos[T.ip[i]]); o[k++] = cos(qpos[T.ip[i]]); }
+        for (int i = 0; i < 8; i++) o[k++] = qvel[T.ip[i]];
+        for (int i = 0; i < 5; i++) o[k++] = log1p(sens[T.ip[8] + i]);
+        { const int b = T.ip[9];
+          o[k++] = xp[3 * b]; o[k++] = xp[3 * b + 2]; o[k++] = xq[4 * b]; o[k++] = xq[4 * b + 2]; }
+        for (int q = 0; q < nb; q++) {
+          const int b = T.ip[11] + q;
+          o[k++] = xp[3 * b]; o[k++] = xp[3 * b + 2]; o[k++] = xq[4 * b]; o[k++] = xq[4 * b + 2];
+        }
+        // stacker.py:133-136 names the box joints x, y, z; the model declares them x, z, y
+        for (int q = 0; q < nb; q++) {
+          const int a = T.ip[12] + 3 * q;
+          o[k++] = qvel[a]; o[k++] = qvel[a + 2]; o[k++] = qvel[a + 1];
+        }
+        o[k++] = xp[3 * T.ip[13]]; o[k++] = xp[3 * T.ip[13] + 2];
+      }
+      auto dist = [&](int s1, int s2) {
+        double dd = 0;
+        for (int i = 0; i < 3; i++) {
+          double e = sx[3 * s1 + i] - sx[3 * s2 + i];
+          dd += e * e;
+        }
+        return sqrt(dd);
+      };
+      double dmin = dist(T.ip[16], T.ip[15]);
+      for (int q = 1; q < nb; q++) dmin = fmin(dmin, dist(T.ip[16] + q, T.ip[15]));
+      const double box_is_close = tolerance(dmin, 0, 0, 2 * T.fp[0], SIG_GAUSSIAN, .1);
+      const double hand_is_far = tolerance(dist(T.ip[14], T.ip[15]), .1, INF, T.fp[1],
+                                           SIG_GAUSSIAN, .1);
+      r = box_is_close * hand_is_far;
       break;
     }
     case TASK_LQR: {        // suite/lqr.py:236-250; fp: control cost coefficient

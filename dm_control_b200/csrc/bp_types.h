@@ -168,7 +168,7 @@ struct BpLayout {   // offsets in doubles from the start of the env's image
 // suite task descriptor: kind + ids / constants resolved by name on the host
 struct BpTask {
   int kind;
-  int ip[16];
+  int ip[24];
   double fp[8];
 };
 

@@ -182,8 +182,12 @@ class Task:
         target_box = .3 if close_target else 2
         gpos[e, tgt, :2] = rng.uniform(-target_box, target_box, size=2)
       physics.set_env_model_field("geom_pos", gpos)
-    elif d == "manipulator":      # suite/manipulator.py:186-247 (bring_ball: no receptacle)
-      _initialize_manipulator(self, physics, qpos, qvel)
+    elif d == "manipulator":      # suite/manipulator.py:186-247
+      _initialize_manipulator(self, physics, qpos, qvel, use_peg="peg" in t,
+                              insert=t.startswith("insert"))
+      return
+    elif d == "stacker":          # suite/stacker.py:139-176
+      _initialize_stacker(self, physics, qpos, int(t[-1]))
       return
     elif d == "ball_in_cup":      # suite/ball_in_cup.py:69-84: a ball position without contacts
       bx = m.jnt_qposadr[m.name2id("ball_x", "joint")]
@@ -248,7 +252,46 @@ class Task:
     physics.data.qvel = qvel
 
 
-def _initialize_manipulator(self, physics, qpos, qvel):
+def _initialize_stacker(self, physics, qpos, n_boxes):
+  """suite/stacker.py:139-176 for every env at once: arm angles, the target's height (a
+  random level of the stack) and x, the boxes' poses, redrawn from the env's own generator
+  until nothing touches."""
+  from dm_control_b200.suite.tasks import MANIPULATOR_ARM_JOINTS
+  m, n = physics.model, physics.nenv
+  arm = [m.name2id(j, "joint") for j in MANIPULATOR_ARM_JOINTS]
+  arm_adr = np.array([m.jnt_qposadr[j] for j in arm])
+  limited = np.asarray(m.jnt_limited)[arm].astype(bool)
+  rng_ = np.asarray(m.jnt_range)[arm]
+  lower = np.where(limited, rng_[:, 0], -np.pi)
+  upper = np.where(limited, rng_[:, 1], np.pi)
+  finger = m.jnt_qposadr[m.name2id("finger", "joint")]
+  thumb = m.jnt_qposadr[m.name2id("thumb", "joint")]
+  target = m.name2id("target", "body")
+  box_size = float(m.geom_size[m.name2id("target", "geom"), 0])
+  box_adr = [[m.jnt_qposadr[m.name2id("box%d_%s" % (b, k), "joint")] for k in "xzy"]
+             for b in range(n_boxes)]
+  bpos = physics.env_model_field("body_pos") if physics._batch.has_env_model("body_pos") else \
+      np.tile(np.asarray(m.body_pos, dtype=np.float64), (n, 1, 1))
+  todo = self._todo(n)
+  while todo.any():
+    for e in np.flatnonzero(todo):
+      rng = self._rngs[e]
+      qpos[e, arm_adr] = rng.uniform(lower, upper)
+      qpos[e, finger] = qpos[e, thumb]
+      target_height = 2 * rng.randint(n_boxes) + 1
+      bpos[e, target, 2] = box_size * target_height
+      bpos[e, target, 0] = rng.uniform(-.37, .37)
+      for adr in box_adr:
+        qpos[e, adr[0]] = rng.uniform(.1, .3)
+        qpos[e, adr[1]] = rng.uniform(0, .7)
+        qpos[e, adr[2]] = rng.uniform(0, 2 * np.pi)
+    physics.set_env_model_field("body_pos", bpos)
+    physics.data.qpos = qpos
+    physics.after_reset()
+    todo &= physics.data.ncon > 0
+
+
+def _initialize_manipulator(self, physics, qpos, qvel, use_peg=False, insert=False):
   """suite/manipulator.py:186-247 for every env at once: each env draws from its own
   generator in the reference's order until its configuration is collision-free; the
   'in_hand' envs read the grasp site after a forward pass with their new arm angles."""
@@ -262,12 +305,17 @@ def _initialize_manipulator(self, physics, qpos, qvel):
   upper = np.where(limited, rng_[:, 1], np.pi)
   finger = m.jnt_qposadr[m.name2id("finger", "joint")]
   thumb = m.jnt_qposadr[m.name2id("thumb", "joint")]
-  target = m.name2id("target_ball", "body")
-  obj = [m.jnt_qposadr[m.name2id("ball_" + k, "joint")] for k in "xzy"]
-  obj_xvel = m.jnt_dofadr[m.name2id("ball_x", "joint")]
+  oname = "peg" if use_peg else "ball"
+  target = m.name2id("target_" + oname, "body")
+  receptacle = m.name2id("slot" if use_peg else "cup", "body") if insert else -1
+  obj = [m.jnt_qposadr[m.name2id(oname + "_" + k, "joint")] for k in "xzy"]
+  obj_xvel = m.jnt_dofadr[m.name2id(oname + "_x", "joint")]
   grasp = m.name2id("grasp", "site")
-  bpos = np.tile(np.asarray(m.body_pos, dtype=np.float64), (n, 1, 1))
-  bquat = np.tile(np.asarray(m.body_quat, dtype=np.float64), (n, 1, 1))
+  if physics._batch.has_env_model("body_pos"):     # partial reset: the others keep theirs
+    bpos, bquat = physics.env_model_field("body_pos"), physics.env_model_field("body_quat")
+  else:
+    bpos = np.tile(np.asarray(m.body_pos, dtype=np.float64), (n, 1, 1))
+    bquat = np.tile(np.asarray(m.body_quat, dtype=np.float64), (n, 1, 1))
   todo = self._todo(n)
   while todo.any():
     idx = np.flatnonzero(todo)
@@ -277,7 +325,12 @@ def _initialize_manipulator(self, physics, qpos, qvel):
       qpos[e, arm_adr] = rng.uniform(lower, upper)
       qpos[e, finger] = qpos[e, thumb]
       tx, tz = rng.uniform(-.4, .4), rng.uniform(.1, .4)
-      ta = rng.uniform(-np.pi, np.pi)
+      if insert:                 # manipulator.py:213-218: the receptacle moves with the target
+        ta = rng.uniform(-np.pi / 3, np.pi / 3)
+        bpos[e, receptacle, 0], bpos[e, receptacle, 2] = tx, tz
+        bquat[e, receptacle, 0], bquat[e, receptacle, 2] = np.cos(ta / 2), np.sin(ta / 2)
+      else:
+        ta = rng.uniform(-np.pi, np.pi)
       bpos[e, target, 0], bpos[e, target, 2] = tx, tz
       bquat[e, target, 0], bquat[e, target, 2] = np.cos(ta / 2), np.sin(ta / 2)
       kind[e] = rng.choice(["in_hand", "in_target", "uniform"], p=[.1, .1, .8])

@@ -22,6 +22,7 @@ FISH_UPRIGHT, FISH_SWIM = 16, 17
 BALL_IN_CUP = 18
 MANIPULATOR = 19
 QUADRUPED_FETCH = 20
+STACKER = 21
 
 TaskDef = collections.namedtuple(
     "TaskDef", "domain task model kind time_limit control_timestep params obs")
@@ -181,18 +182,54 @@ MANIPULATOR_ARM_JOINTS = ["arm_root", "arm_shoulder", "arm_elbow", "arm_wrist",
                           "finger", "fingertip", "thumb", "thumbtip"]   # manipulator.py:36-37
 
 
-def _manipulator(m):
-  # bring_ball (manipulator.py:70-82): object = ball, target = target_ball
-  arm = [int(m.jnt_qposadr[m.name2id(j, "joint")]) for j in MANIPULATOR_ARM_JOINTS]
-  assert arm == [int(m.jnt_dofadr[m.name2id(j, "joint")]) for j in MANIPULATOR_ARM_JOINTS]
-  touch = [_sens_adr(m, s) for s in ("palm_touch", "finger_touch", "thumb_touch",
-                                     "fingertip_touch", "thumbtip_touch")]
-  assert touch == list(range(touch[0], touch[0] + 5))
-  obj = [int(m.jnt_dofadr[m.name2id("ball_" + k, "joint")]) for k in "xzy"]
-  assert obj == list(range(obj[0], obj[0] + 3))
-  return (arm + [touch[0], m.name2id("hand", "body"), m.name2id("ball", "body"),
-                 m.name2id("target_ball", "body"), obj[0], m.name2id("ball", "site"),
-                 m.name2id("target_ball", "site")], [.01])
+def _manipulator(use_peg=False):
+  """manipulator.py:70-130: bring_ball / bring_peg / insert_ball / insert_peg share the
+  observation; object = ball | peg, target = target_ball | target_peg."""
+  def f(m):
+    obj_name = "peg" if use_peg else "ball"
+    arm = [int(m.jnt_qposadr[m.name2id(j, "joint")]) for j in MANIPULATOR_ARM_JOINTS]
+    assert arm == [int(m.jnt_dofadr[m.name2id(j, "joint")]) for j in MANIPULATOR_ARM_JOINTS]
+    touch = [_sens_adr(m, s) for s in ("palm_touch", "finger_touch", "thumb_touch",
+                                       "fingertip_touch", "thumbtip_touch")]
+    assert touch == list(range(touch[0], touch[0] + 5))
+    obj = [int(m.jnt_dofadr[m.name2id(obj_name + "_" + k, "joint")]) for k in "xzy"]
+    assert obj == list(range(obj[0], obj[0] + 3))
+    ip = arm + [touch[0], m.name2id("hand", "body"), m.name2id(obj_name, "body"),
+                m.name2id("target_" + obj_name, "body"), obj[0], m.name2id(obj_name, "site"),
+                m.name2id("target_" + obj_name, "site"), int(use_peg)]
+    if use_peg:          # _peg_reward (manipulator.py:276-286)
+      ip += [m.name2id(k, "site") for k in ("peg_grasp", "grasp", "peg_pinch", "pinch",
+                                            "target_peg_tip", "peg_tip")]
+    return ip, [.01]
+  return f
+
+
+def _stacker(n_boxes):
+  """stacker.py:187-214."""
+  def f(m):
+    arm = [int(m.jnt_qposadr[m.name2id(j, "joint")]) for j in MANIPULATOR_ARM_JOINTS]
+    touch = [_sens_adr(m, s) for s in ("palm_touch", "finger_touch", "thumb_touch",
+                                       "fingertip_touch", "thumbtip_touch")]
+    assert touch == list(range(touch[0], touch[0] + 5))
+    boxes = [m.name2id("box%d" % b, "body") for b in range(n_boxes)]
+    assert boxes == list(range(boxes[0], boxes[0] + n_boxes))
+    joints = [int(m.jnt_dofadr[m.name2id("box%d_%s" % (b, k), "joint")])
+              for b in range(n_boxes) for k in "xzy"]         # stacker.py:133-136 order
+    assert joints == list(range(joints[0], joints[0] + 3 * n_boxes))
+    sites = [m.name2id("box%d" % b, "site") for b in range(n_boxes)]
+    assert sites == list(range(sites[0], sites[0] + n_boxes))
+    return (arm + [touch[0], m.name2id("hand", "body"), n_boxes, boxes[0], joints[0],
+                   m.name2id("target", "body"), m.name2id("grasp", "site"),
+                   m.name2id("target", "site"), sites[0]],
+            [float(m.geom_size[m.name2id("target", "geom"), 0]), .01])
+  return f
+
+
+def _obs_stacker(n_boxes):
+  def f(m):
+    return [("arm_pos", 16), ("arm_vel", 8), ("touch", 5), ("hand_pos", 4),
+            ("box_pos", 4 * n_boxes), ("box_vel", 3 * n_boxes), ("target_pos", 2)]
+  return f
 
 
 def _obs_manipulator(m):
@@ -300,7 +337,18 @@ _TASKS = [
     # manipulator.py:32-33,70-82: 10 s, control timestep .01; fully observable bring_ball
     # (the model keeps the ball and its target: make_model, 47-67)
     TaskDef("manipulator", "bring_ball", "manipulator_ball", MANIPULATOR, 10, .01,
-            _manipulator, _obs_manipulator),
+            _manipulator(False), _obs_manipulator),
+    # manipulator.py:85-130: the peg prop and the receptacles (cup / slot: box geoms against
+    # the ball / peg capsules and the hand)
+    TaskDef("manipulator", "bring_peg", "manipulator_peg", MANIPULATOR, 10, .01,
+            _manipulator(True), _obs_manipulator),
+    TaskDef("manipulator", "insert_ball", "manipulator_insert_ball", MANIPULATOR, 10, .01,
+            _manipulator(False), _obs_manipulator),
+    TaskDef("manipulator", "insert_peg", "manipulator_insert_peg", MANIPULATOR, 10, .01,
+            _manipulator(True), _obs_manipulator),
+    # stacker.py:31-32,52-80: 10 s, control timestep .01; boxes stacked on a target
+    TaskDef("stacker", "stack_2", "stacker_2", STACKER, 10, .01, _stacker(2), _obs_stacker(2)),
+    TaskDef("stacker", "stack_4", "stacker_4", STACKER, 10, .01, _stacker(4), _obs_stacker(4)),
     # fish.py:28-29: 40 s, control timestep .04; gravity and constraints disabled, fluid
     # density 5000, a tendon spring between the fins, position servos
     TaskDef("fish", "upright", "fish", FISH_UPRIGHT, 40, .04, _fish, _obs_fish(False)),

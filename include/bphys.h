@@ -124,7 +124,7 @@ int bp_reset(bp_batch* b, int key);
 
 /* Suite observation / reward kernels (suite/<task>.py get_observation/get_reward).
  * bp_set_task binds a task kind (ids in dm_control_b200/suite/tasks.py) with the
- * object ids (`ip`, <= 16) and constants (`fp`, <= 8) it needs, resolved by name on
+ * object ids (`ip`, <= 24) and constants (`fp`, <= 8) it needs, resolved by name on
  * the host.  obs is [nenv][nobs] float64 and reward [nenv] float64, device memory. */
 int bp_set_task(bp_batch* b, int kind, const int32_t* ip, int nip, const double* fp, int nfp);
 int bp_task_nobs(bp_batch* b);

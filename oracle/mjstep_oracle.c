@@ -1479,7 +1479,7 @@ static int col_sphere_box_raw(const double* c, double r, const double* pb, const
     double depth = h[0] - fabs(d[0]);
     for (int k = 1; k < 3; k++) {
       double dk = h[k] - fabs(d[k]);
-      if (dk < depth) { depth = dk; best = k; }
+      if (dk < depth - 1e-10) { depth = dk; best = k; }
     }
     nl[0] = nl[1] = nl[2] = 0;
     nl[best] = d[best] >= 0 ? -1.0 : 1.0;
@@ -1557,7 +1557,7 @@ static int col_capsule_box_raw(const double* p1, const double* a1, double r, dou
   }
   if (!nh) return 0;
   int first = 0, second = -1;
-  for (int i = 1; i < nh; i++) if (hit[i].dist < hit[first].dist) first = i;
+  for (int i = 1; i < nh; i++) if (hit[i].dist < hit[first].dist - 1e-10) first = i;
   double sep = 1e-6 * (l + r);
   for (int i = 0; i < nh; i++) {
     double si = fabs(th[i] - th[first]);
@@ -1576,8 +1576,11 @@ static int boxbox_clip(const double* xi, const double* yi, const double* zi, int
   for (int i = 0; i < n; i++) {
     int j = (i + 1) % n;
     double ci = sgn * (usey ? yi[i] : xi[i]) - lim, cj = sgn * (usey ? yi[j] : xi[j]) - lim;
-    if (ci <= 0) { xo[m] = xi[i]; yo[m] = yi[i]; zo[m] = zi[i]; m++; }
-    if ((ci <= 0) != (cj <= 0)) {
+    /* a vertex on the boundary (boxes of equal width side by side) counts as inside on both
+     * sides of a rounding error, so that the polygon keeps its vertex order */
+    const int in_i = ci <= 1e-10, in_j = cj <= 1e-10;
+    if (in_i) { xo[m] = xi[i]; yo[m] = yi[i]; zo[m] = zi[i]; m++; }
+    if (in_i != in_j) {
       double w = ci / (ci - cj);
       xo[m] = xi[i] + w * (xi[j] - xi[i]);
       yo[m] = yi[i] + w * (yi[j] - yi[i]);
@@ -1603,13 +1606,13 @@ static int col_box_box_raw(const double* pa, const double* Ra, const double* ha,
   for (int i = 0; i < 3; i++) {
     double s = fabs(t[i]) - (ha[i] + hb[0] * Q[3 * i] + hb[1] * Q[3 * i + 1] + hb[2] * Q[3 * i + 2]);
     if (s > margin) return 0;
-    if (s > best) { best = s; code = i; }
+    if (s > best + 1e-10) { best = s; code = i; }
   }
   for (int j = 0; j < 3; j++) {
     double tb = t[0] * R[j] + t[1] * R[3 + j] + t[2] * R[6 + j];
     double s = fabs(tb) - (hb[j] + ha[0] * Q[j] + ha[1] * Q[3 + j] + ha[2] * Q[6 + j]);
     if (s > margin) return 0;
-    if (s > best) { best = s; code = 3 + j; }
+    if (s > best + 1e-10) { best = s; code = 3 + j; }
   }
   for (int i = 0; i < 3; i++)
     for (int j = 0; j < 3; j++) {
@@ -1638,7 +1641,7 @@ static int col_box_box_raw(const double* pa, const double* Ra, const double* ha,
       double ak[3];
       geom_axis(Ri, k, ak);
       double dk = fabs(dot3(nref, ak));
-      if (dk > bestdot) { bestdot = dk; kf = k; }
+      if (dk > bestdot + 1e-10) { bestdot = dk; kf = k; }
     }
     double af[3], a1[3], a2[3], fc[3];
     const int k1 = (kf + 1) % 3, k2 = (kf + 2) % 3, r1 = (ai + 1) % 3, r2 = (ai + 2) % 3;

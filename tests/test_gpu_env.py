@@ -27,7 +27,9 @@ SERVED = [("cartpole", "swingup"), ("cartpole", "swingup_sparse"), ("cartpole", 
           ("humanoid_CMU", "stand"), ("humanoid_CMU", "run"),
           ("swimmer", "swimmer6"), ("swimmer", "swimmer15"),
           ("fish", "upright"), ("fish", "swim"),
-          ("ball_in_cup", "catch"), ("manipulator", "bring_ball"), ("cartpole", "two_poles"), ("cartpole", "three_poles")]
+          ("ball_in_cup", "catch"), ("manipulator", "bring_ball"), ("cartpole", "two_poles"), ("cartpole", "three_poles"),
+          ("manipulator", "bring_peg"), ("manipulator", "insert_ball"), ("manipulator", "insert_peg"),
+          ("stacker", "stack_2"), ("stacker", "stack_4")]
 FIELDS = ("qpos", "qvel", "act", "ctrl", "xmat", "xpos", "xquat", "xipos", "site_xpos", "geom_xpos",
           "geom_xmat", "sensordata")
 

@@ -24,6 +24,7 @@ SIZES = {"humanoid": HUMANOID_SIZES, "quadruped": dict(njmax=120, nconmax=40),
          "swimmer6": dict(njmax=32, nconmax=1), "swimmer15": dict(njmax=32, nconmax=1),
          "fish": dict(njmax=32, nconmax=1),
          "manipulator_ball": dict(njmax=96, nconmax=24),
+         "manipulator_insert_peg": dict(njmax=128, nconmax=32), "stacker_4": dict(njmax=160, nconmax=40),
          "quadruped_fetch": dict(njmax=160, nconmax=40)}
 
 
@@ -40,7 +41,7 @@ def _assert_parity(res, elem=1.0):
                                     "hopper", "finger", "humanoid", "quadruped",
                                     "quadruped_escape", "reacher", "point_mass", "swimmer6",
                                     "swimmer15", "fish", "cartpole3", "ball_in_cup",
-                                    "manipulator_ball"])
+                                    "manipulator_ball", "manipulator_insert_peg", "stacker_4"])
 @pytest.mark.parametrize("lanes", [32, 8, 4, 1])
 def test_every_field_matches_oracle(domain, lanes):
   kw = SIZES.get(domain, {})
@@ -50,14 +51,17 @@ def test_every_field_matches_oracle(domain, lanes):
   # (BADQACC resets on both sides, at rounding-dependent steps): gentler start states
   vel = 0.3 if domain.startswith("swimmer") else 0.1 if domain == "fish" else 1.0
   # manipulator (timestep 1 ms, solref 5 ms, a 1e-6 kg body): see run_parity's iter_slack
-  slack = domain == "manipulator_ball"
+  slack = domain in ("manipulator_ball", "manipulator_insert_peg", "stacker_4")
   res, stats = PU.run_parity(domain, nenv=nenv, nsteps=10, seed=5, check_steps=[0, 1, 2, 10],
                              lanes=lanes, vel_scale=vel, iter_slack=slack, **kw)
   _assert_parity(res)
   if slack:
     assert stats["loose"] <= nenv // 16, stats
+    # insert_peg thrown together at random has the peg's 1e-6 kg pommel wedged in the slot: one
+    # Newton iteration more or less there moves qacc_smooth-sized terms by 2e-3 of their scale
+    loose_bar = 1e-2 if domain == "manipulator_insert_peg" else 1e-4
     for step, cmp in res.items():
-      assert cmp.loose.worst() <= 1e-4, "step %d\n%s" % (step, cmp.loose.report())
+      assert cmp.loose.worst() <= loose_bar, "step %d\n%s" % (step, cmp.loose.report())
   if domain == "finger":
     assert max(stats["ncon"]) > 0.05
   if domain in ("cheetah", "walker", "hopper", "humanoid", "quadruped", "quadruped_escape"):

@@ -105,10 +105,28 @@ def manipulator_xml(use_peg=False, insert=False):
   return ET.tostring(root, encoding="unicode")
 
 
+def stacker_xml(n_boxes):
+  """suite/stacker.py:38-49 make_model: the unused boxes are removed."""
+  import xml.etree.ElementTree as ET
+  root = ET.fromstring(open(os.path.join(SUITE, "stacker.xml")).read())
+  wb = root.find("worldbody")
+  for b in list(wb.findall("body")):
+    if b.get("name") in ["box%d" % k for k in range(n_boxes, 4)]:
+      wb.remove(b)
+  return ET.tostring(root, encoding="unicode")
+
+
 def manipulators():
-  m = C.compile_xml(manipulator_xml(), _Dir())
-  m.save(os.path.join(OUT, "manipulator_ball.npz"))
-  print("manipulator_ball nq", m.nq, "nbody", m.nbody, "npair", m.npair, "neq", m.neq)
+  for name, kw in (("manipulator_ball", {}), ("manipulator_peg", dict(use_peg=True)),
+                   ("manipulator_insert_ball", dict(insert=True)),
+                   ("manipulator_insert_peg", dict(use_peg=True, insert=True))):
+    m = C.compile_xml(manipulator_xml(**kw), _Dir())
+    m.save(os.path.join(OUT, name + ".npz"))
+    print(name, "nq", m.nq, "nbody", m.nbody, "npair", m.npair, "neq", m.neq)
+  for n in (2, 4):
+    m = C.compile_xml(stacker_xml(n), _Dir())
+    m.save(os.path.join(OUT, "stacker_%d.npz" % n))
+    print("stacker_%d nq" % n, m.nq, "nbody", m.nbody, "npair", m.npair, "njmax", m.njmax)
 
 
 def cartpoles():
