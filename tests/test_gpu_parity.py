@@ -90,6 +90,9 @@ def test_split_pipeline_bit_identical(domain, lanes, seg_g, monkeypatch):
   names = ["qpos", "qvel", "qacc", "qacc_warmstart", "sensordata", "efc_force", "xpos",
            "cfrc_ext", "nefc", "ncon", "solver_iter", "warning"]
   out = []
+  # the fused side is the GENERIC kernel: a static instance is compiled separately and may
+  # contract multiply-adds differently (it is held to 1e-10 of the generic kernel elsewhere)
+  monkeypatch.setenv("BPHYS_NO_STATIC", "1")
   for split in (False, True):
     if split:
       monkeypatch.setenv("BPHYS_SPLIT", "1")
@@ -369,12 +372,16 @@ def test_cg_and_pgs_solvers_match_oracle(domain, solver, lanes):
     m.arrays["opt_solver"][...] = {"PGS": 0, "CG": 1}[solver]
   kw = dict(SIZES.get(domain, dict(njmax=64, nconmax=16)))
   res, stats = PU.run_parity(domain, nenv=32, nsteps=10, seed=6, check_steps=[0, 1, 2, 10],
-                             lanes=lanes, mutate=mutate, **kw)
+                             lanes=lanes, mutate=mutate, iter_slack=solver == "CG", **kw)
   # CG converges linearly and stops on opt.tolerance = 1e-8: rounding differences between the
   # two sides are not contracted as Newton's quadratic convergence contracts them (measured:
   # humanoid cvel 6e-10 of the array's scale after 2 steps), so its element-wise floor is
   # 1e-9 * scale instead of 1e-10 * scale; the array-normalised 1e-8 bar is unchanged
+  # for the same reason an env whose improvement sits on the tolerance can stop one CG iteration
+  # apart on the two sides (a tolerance-sized difference): run_parity's iter_slack takes such envs
+  # out of the strict comparison from that step on; at most 2 of the 32 may do so
   _assert_parity(res, elem=10.0 if solver == "CG" else 1.0)
+  assert stats["loose"] <= 2, stats
   assert max(stats["iter"]) > 0.5, stats
 
 
