@@ -380,7 +380,17 @@ def test_cg_and_pgs_solvers_match_oracle(domain, solver, lanes):
   # for the same reason an env whose improvement sits on the tolerance can stop one CG iteration
   # apart on the two sides (a tolerance-sized difference): run_parity's iter_slack takes such envs
   # out of the strict comparison from that step on; at most 2 of the 32 may do so
+  # ... and what CG leaves within its tolerance is carried through the contacts of the next steps:
+  # the strict bars hold for forward() and the first two steps; after 10 steps the integers
+  # must still agree and the state is held to 1e-5 of each array's scale (humanoid measured
+  # 9e-7, cheetah and finger stay below 1e-8)
+  last = res.pop(10)
   _assert_parity(res, elem=10.0 if solver == "CG" else 1.0)
+  if solver == "CG":
+    assert not {k: v for k, v in last.int_mismatch.items() if v}, last.report()
+    assert last.worst() <= 1e-5, last.report()
+  else:
+    _assert_parity({10: last})
   assert stats["loose"] <= 2, stats
   assert max(stats["iter"]) > 0.5, stats
 
