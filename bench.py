@@ -66,8 +66,8 @@ _JSON_OUT = None     # the process's original stdout when fd 1 has been pointed 
 WORKLOADS = {"cheetah-run": dict(nenv=16384, njmax=64, nconmax=16, settle=200, lanes=8),
              "humanoid-run": dict(nenv=8192, njmax=120, nconmax=40, settle=100, lanes=16),
              "walker-walk": dict(nenv=16384, njmax=48, nconmax=12, settle=50, lanes=8),
-             "cartpole-swingup": dict(nenv=4096, njmax=4, nconmax=1, settle=0, lanes=8),
-             "acrobot-swingup": dict(nenv=4096, njmax=1, nconmax=1, settle=0, lanes=8),
+             "cartpole-swingup": dict(nenv=4096, njmax=4, nconmax=1, settle=0, lanes=1),
+             "acrobot-swingup": dict(nenv=4096, njmax=1, nconmax=1, settle=0, lanes=1),
              "pendulum-swingup": dict(nenv=4096, njmax=1, nconmax=1, settle=0, lanes=1),
              "finger-spin": dict(nenv=8192, njmax=24, nconmax=6, settle=50, lanes=4),
              # BASELINE.json configs[4]: 65536 envs over 8 GPUs = 8192 per GPU
@@ -75,9 +75,9 @@ WORKLOADS = {"cheetah-run": dict(nenv=16384, njmax=64, nconmax=16, settle=200, l
              "quadruped-walk": dict(nenv=8192, njmax=120, nconmax=40, settle=100, lanes=16)}
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the step kernel from the
 # committed `ncu --set full` captures (profiles/), keyed by (task, lanes, envs per GPU)
-NCU_TRAFFIC = {("cheetah-run", 8, 16384): (470.8e6, "profiles/r1z_cheetah_g8_lean.summary.txt"),
+NCU_TRAFFIC = {("cheetah-run", 8, 16384): (453.8e6, "profiles/r2p_static_cheetah_g8.summary.txt"),
                ("cheetah-run", 4, 16384): (345.5e6, "profiles/r1g_cheetah_g4.summary.txt"),
-               ("humanoid-run", 16, 8192): (5.239e9, "profiles/r1z_humanoid_g16_lean.summary.txt"),
+               ("humanoid-run", 16, 8192): (4.952e9, "profiles/r2p_static_humanoid_g16.summary.txt"),
                ("humanoid-run", 8, 8192): (5.531e9, "profiles/r1g_humanoid_g8.summary.txt")}
 
 

@@ -77,6 +77,7 @@ _SIGNATURES = {
                                             ctypes.c_double]),
     "bp_rewards_tolerance_noalloc_max": (_i32, []),
     "bp_batch_copy": (_i32, [_vp, _vp]),
+    "bp_batch_last_static": (_i32, [_vp]),
     "bp_contact_force": (_i32, [_vp, _i32, _vp]),
     "bp_object_velocity": (_i32, [_vp, _i32, _i32, _i32, _vp]),
     "bp_warnings": (_i32, [_vp, _vp]),
@@ -336,6 +337,11 @@ class Batch:
 
   def env_step_host(self, nsub, ctrl, obs, reward):
     check(load().bp_env_step_host(self.ptr, nsub, _ptr(ctrl), _ptr(obs), _ptr(reward)))
+
+  @property
+  def last_static(self):
+    """Whether the last launch ran a static instance of the kernel (csrc/bp_step_static.cu)."""
+    return bool(load().bp_batch_last_static(self.ptr))
 
   def copy_from(self, other):
     """mj_copyData: this batch becomes a bit copy of `other` (same shapes)."""

@@ -619,6 +619,7 @@ struct bp_batch {
   double *env_geom_pos = nullptr, *env_site_pos = nullptr;   // per-env model frames (lazy)
   double *env_body_pos = nullptr, *env_body_quat = nullptr;
   BpTask task;
+  int last_static = 0;             // the last launch was served by a static instance
 };
 
 static void make_layout(const BpModel& m, int njmax, int nconmax, BpLayout* L,
@@ -938,6 +939,7 @@ static int launch(bp_batch* b, int mode, int nsub, int disable_actuation,
   e = -1;
   if (!getenv("BPHYS_NO_STATIC") && !getenv("BPHYS_SPLIT") && b->lanes != 32)
     e = bp_launch_step_static(&P, b->model->struct_hash, plain ? 1 : 0, b->stream);
+  b->last_static = e != -1;
   if (e != -1) {
   } else if (plain && M.lean_static && (b->lanes == 4 || b->lanes == 8 || b->lanes == 16)) {
     e = b->lanes == 4 ? bp_launch_step_g4_lean(&P, b->stream)
@@ -958,6 +960,7 @@ static int launch(bp_batch* b, int mode, int nsub, int disable_actuation,
   if (e != 0) return fail(BP_ECUDA, std::string("step launch: ") + cudaGetErrorString((cudaError_t)e));
   return BP_OK;
 }
+extern "C" int bp_batch_last_static(bp_batch* b) { return b ? b->last_static : 0; }
 extern "C" int bp_step(bp_batch* b, int nsub) { return launch(b, BP_MODE_STEP, nsub, 0); }
 extern "C" int bp_mj_step(bp_batch* b, int nsub) { return launch(b, BP_MODE_MJSTEP, nsub, 0); }
 extern "C" int bp_forward(bp_batch* b, int da) { return launch(b, BP_MODE_FORWARD, 1, da); }

@@ -19,21 +19,22 @@ template <class MT>
 __global__ void __launch_bounds__(BP_STATIC_TPB)
 bp_step_kernel_static(const __grid_constant__ BpParams P) {
   const long long env = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-  if (env >= P.nenv || (P.mask && !P.mask[env])) return;
-  using L = typename MT::Layout;
-  double* wb = P.image + (env / 32) * P.stride * 32;
-  double* base = wb + (env & 31);
-  int* ib = (int*)(wb + (long long)L::ints * 32) + (env & 31);
-  Ctx<1, 32, 1, MT> c{P, base, ib, 0, 1u << (threadIdx.x & 31), true, false, nullptr, nullptr,
-                      P.m.geom_pos, P.m.site_pos, P.m.body_pos, P.m.body_quat};
-  bp_load_ctrl(c, env);
-  bp_run_mode(c);
-  if (P.rew_out) bp_task_eval(P, P.task, env, P.task_nobs, P.obs_out, P.rew_out);
+  // lanes past the end of a ragged last warp stay: they help copy the results out below
+  if (env < P.nenv && !(P.mask && !P.mask[env])) {
+    using L = typename MT::Layout;
+    double* wb = P.image + (env / 32) * P.stride * 32;
+    double* base = wb + (env & 31);
+    int* ib = (int*)(wb + (long long)L::ints * 32) + (env & 31);
+    Ctx<1, 32, 1, MT> c{P, base, ib, 0, 1u << (threadIdx.x & 31), true, false, nullptr, nullptr,
+                        P.m.geom_pos, P.m.site_pos, P.m.body_pos, P.m.body_quat};
+    bp_load_ctrl(c, env);
+    bp_run_mode(c);
+    if (P.rew_out) bp_task_eval(P, P.task, env, P.task_nobs, P.obs_out, P.rew_out);
+  }
   // results straight to pinned host memory (BpParams.obs_host): every warp copies the rows of
   // its 32 envs with lane-contiguous stores
   if (P.obs_host || P.rew_host) {
-    const unsigned am = __activemask();
-    __syncwarp(am);
+    __syncwarp();
     const long long e0 = env & ~31LL;
     long long cnt = P.nenv - e0 < 32 ? P.nenv - e0 : 32;
     const int ln = threadIdx.x & 31;

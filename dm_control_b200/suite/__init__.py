@@ -470,6 +470,8 @@ def build_environment(domain_name, task_name, task_kwargs=None, environment_kwar
     m = _load_model(tdef.model)
   if njmax is None and nconmax is None and tdef.model in T.STATIC_SIZES:
     njmax, nconmax = T.STATIC_SIZES[tdef.model]
+    if lanes is None:
+      lanes = T.STATIC_LANES.get(tdef.model)
   physics = BatchedPhysics(m, nenv, device=device, lanes=lanes, njmax=njmax, nconmax=nconmax)
   task = Task(tdef, random=task_kwargs.pop("random", None))
   task_kwargs.pop("model_seed", None)

@@ -390,7 +390,11 @@ ALL_TASKS = tuple(sorted(REGISTRY))
 # kernel instance (csrc/static/*.cuh, tools/gen_static_model.py TRAITS): suite.load uses them
 # by default so that its batches are served by those instances.
 STATIC_SIZES = {"cheetah": (64, 16), "walker": (48, 12), "humanoid": (120, 40),
-                "quadruped_escape": (184, 42), "finger": (24, 6)}
+                "quadruped_escape": (184, 42), "finger": (24, 6),
+                "cartpole": (4, 1), "acrobot": (1, 1), "pendulum": (1, 1)}
+# lanes per env of the instances that differ from physics.default_lanes: the contact-free
+# models run one thread per env
+STATIC_LANES = {"cartpole": 1, "acrobot": 1, "pendulum": 1}
 
 
 def n_sub_steps(tdef, m):

@@ -167,6 +167,11 @@ int bp_env_step(bp_batch* b, int nsub, const double* ctrl_dev, double* obs_dev,
 int bp_env_step_host(bp_batch* b, int nsub, const double* ctrl_host, double* obs_host,
                      double* reward_host);
 
+/* 1 when the batch's last step / forward launch was served by a static (ahead-of-time
+ * specialised) instance of the kernel, 0 when by a generic one.  Diagnostic: no reference
+ * counterpart (the reference has one engine build). */
+int bp_batch_last_static(bp_batch* b);
+
 /* mj_copyData (wrapper/core.py:653-685 MjData.copy; engine.py:332-339 Physics.copy): the whole
  * state of `src` -- every env image, per-env height fields and model frames, the bound task --
  * into `dst`, created with the same sizes.  Device-to-device; synchronises. */

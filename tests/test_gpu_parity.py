@@ -413,7 +413,9 @@ def test_reference_test_humanoid_rk4_pgs(lanes):
 @pytest.mark.parametrize("domain,lanes,sizes", [
     ("cheetah", 8, dict(njmax=64, nconmax=16)), ("walker", 8, dict(njmax=48, nconmax=12)),
     ("humanoid", 16, dict(njmax=120, nconmax=40)),
-    ("quadruped_escape", 16, dict(njmax=184, nconmax=42)), ("finger", 4, dict(njmax=24, nconmax=6))])
+    ("quadruped_escape", 16, dict(njmax=184, nconmax=42)), ("finger", 4, dict(njmax=24, nconmax=6)),
+    ("cartpole", 1, dict(njmax=4, nconmax=1)), ("acrobot", 1, dict(njmax=1, nconmax=1)),
+    ("pendulum", 1, dict(njmax=1, nconmax=1))])
 def test_static_instances_match_oracle(domain, lanes, sizes, monkeypatch):
   """The ahead-of-time specialised kernels (csrc/bp_step_static.cu, static/*.cuh: the model's
   structure and the data layout as compile-time constants) at the lane widths and batch sizes
@@ -423,7 +425,7 @@ def test_static_instances_match_oracle(domain, lanes, sizes, monkeypatch):
   res, stats = PU.run_parity(domain, nenv=nenv, nsteps=10, seed=5, check_steps=[0, 1, 2, 10],
                              lanes=lanes, **sizes)
   _assert_parity(res)
-  assert max(stats["nefc"]) > 0.5
+  assert max(stats["nefc"]) > (0.1 if domain == "cartpole" else 0.5) or domain in ("acrobot", "pendulum")
   from dm_control_b200 import binding
   m = PU.load_model(domain)
   qpos, qvel, ctrl = PU.random_states(m, 40, 3)
@@ -445,6 +447,7 @@ def test_static_instances_match_oracle(domain, lanes, sizes, monkeypatch):
     b.forward()
     b.step(5)
     b.sync()
+    assert b.last_static == static        # the instance really is what served the launch
     out.append({n: b.read(n) for n in ("qpos", "qvel", "qacc", "sensordata", "efc_force",
                                        "nefc", "ncon", "solver_iter")})
     b.free(); model.free()
