@@ -235,7 +235,8 @@ class Batch:
       check(load().bp_field_write(self.ptr, name.encode(), _ptr(a), env0, a.shape[0]))
 
   def write_env_model(self, name, value, env0=0):
-    """Per-env copy of a model array ("geom_pos", "site_pos", "body_pos", "body_quat"): value [n, count]."""
+    """Per-env copy of a model array ("geom_pos", "site_pos", "body_pos", "body_quat",
+    "wrap_prm"): value [n, count]."""
     cnt = self.model.flat.arrays[name].size
     a = np.ascontiguousarray(value, dtype=np.float64).reshape(-1, cnt)
     check(load().bp_env_model_write(self.ptr, name.encode(), _ptr(a), env0, a.shape[0]))

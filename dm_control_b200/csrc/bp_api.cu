@@ -618,6 +618,7 @@ struct bp_batch {
   float* hfield = nullptr;         // [nenv_alloc][nhfielddata] per-env elevation data
   double *env_geom_pos = nullptr, *env_site_pos = nullptr;   // per-env model frames (lazy)
   double *env_body_pos = nullptr, *env_body_quat = nullptr;
+  double* env_wrap_prm = nullptr;  // per-env tendon coefficients (lazy)
   BpTask task;
   int last_static = 0;             // the last launch was served by a static instance
 };
@@ -721,6 +722,7 @@ extern "C" void bp_batch_free(bp_batch* b) {
   if (b->env_site_pos) cudaFree(b->env_site_pos);
   if (b->env_body_pos) cudaFree(b->env_body_pos);
   if (b->env_body_quat) cudaFree(b->env_body_quat);
+  if (b->env_wrap_prm) cudaFree(b->env_wrap_prm);
   if (b->ctrl_stage) cudaFree(b->ctrl_stage);
   if (b->stage) cudaFree(b->stage);
   if (b->obs_dev) cudaFree(b->obs_dev);
@@ -850,6 +852,8 @@ static BpParams make_params(bp_batch* b, int mode, int nsub, int disable_actuati
   P.hfield = b->hfield;
   P.env_geom_pos = b->env_geom_pos; P.env_site_pos = b->env_site_pos;
   P.env_body_pos = b->env_body_pos; P.env_body_quat = b->env_body_quat;
+  P.env_wrap_prm = b->env_wrap_prm;
+  P.env_wrap_n = (int)b->model->fields["wrap_prm"].f.size();
   return P;
 }
 
@@ -863,8 +867,12 @@ static int env_model_copy(bp_batch* b, const char* name, double* host, int64_t e
   else if (strcmp(name, "site_pos") == 0) { slot = &b->env_site_pos; cnt = 3 * b->model->M.nsite; }
   else if (strcmp(name, "body_pos") == 0) { slot = &b->env_body_pos; cnt = 3 * b->model->M.nbody; }
   else if (strcmp(name, "body_quat") == 0) { slot = &b->env_body_quat; cnt = 4 * b->model->M.nbody; }
+  else if (strcmp(name, "wrap_prm") == 0) {
+    slot = &b->env_wrap_prm; cnt = (int)b->model->fields["wrap_prm"].f.size();
+  }
   else return fail(BP_ENOFIELD, std::string("no per-env model field ") + name +
-                   " (geom_pos, site_pos, body_pos, body_quat; hfield_data has bp_hfield_write)");
+                   " (geom_pos, site_pos, body_pos, body_quat, wrap_prm; hfield_data has "
+                   "bp_hfield_write)");
   if (env0 < 0 || n < 0 || env0 + n > b->nenv) return fail(BP_EINVAL, "env range out of bounds");
   if (cnt == 0 || n == 0) return BP_OK;
   cudaSetDevice(b->model->device);
@@ -932,6 +940,7 @@ static int launch(bp_batch* b, int mode, int nsub, int disable_actuation,
   // BPHYS_NO_LEAN=1 / BPHYS_SPLIT=1 keep the full instantiation
   const bool plain = M.opt_solver == 2 && M.opt_cone == 0 && M.opt_density == 0 && M.opt_viscosity == 0 &&
                      !P.env_geom_pos && !P.env_site_pos && !P.env_body_pos && !P.env_body_quat &&
+                     !P.env_wrap_prm &&
                      !getenv("BPHYS_NO_LEAN") && !getenv("BPHYS_SPLIT");
   // a static (ahead-of-time specialised) instance when one serves this model's structure,
   // this batch's layout and lane width, and the shape the instance was built for still applies
@@ -1135,7 +1144,8 @@ extern "C" int bp_batch_copy(bp_batch* dst, bp_batch* src) {
       {&dst->env_geom_pos, &src->env_geom_pos, 3 * src->model->M.ngeom},
       {&dst->env_site_pos, &src->env_site_pos, 3 * src->model->M.nsite},
       {&dst->env_body_pos, &src->env_body_pos, 3 * src->model->M.nbody},
-      {&dst->env_body_quat, &src->env_body_quat, 4 * src->model->M.nbody}};
+      {&dst->env_body_quat, &src->env_body_quat, 4 * src->model->M.nbody},
+      {&dst->env_wrap_prm, &src->env_wrap_prm, (int)src->model->fields["wrap_prm"].f.size()}};
   for (auto& sl : slots) {
     if (!*sl.s) {
       if (*sl.d) { cudaFree(*sl.d); *sl.d = nullptr; }

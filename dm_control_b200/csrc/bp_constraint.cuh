@@ -180,10 +180,10 @@ BP_STAGE void bp_make_constraint(const C& c) {
     }
     if (tend) {
       for (int w = m.tendon_adr[o1]; w < m.tendon_adr[o1] + m.tendon_num[o1]; w++)
-        J[r * nvp + m.jnt_dofadr[m.wrap_objid[w]]] += m.wrap_prm[w];
+        J[r * nvp + m.jnt_dofadr[m.wrap_objid[w]]] += c.wprm[w];
       if (o2 >= 0)
         for (int w = m.tendon_adr[o2]; w < m.tendon_adr[o2] + m.tendon_num[o2]; w++)
-          J[r * nvp + m.jnt_dofadr[m.wrap_objid[w]]] -= deriv * m.wrap_prm[w];
+          J[r * nvp + m.jnt_dofadr[m.wrap_objid[w]]] -= deriv * c.wprm[w];
     } else {
       J[r * nvp + m.jnt_dofadr[o1]] += 1;
       if (o2 >= 0) J[r * nvp + m.jnt_dofadr[o2]] -= deriv;
@@ -211,7 +211,7 @@ BP_STAGE void bp_make_constraint(const C& c) {
       for (int i = 0; i < nv; i++) J[r * nvp + i] = -side * DF(ten_J)[m.tendon_Jadr[t] * nv + i];
     } else {
       for (int w = m.tendon_adr[t]; w < m.tendon_adr[t] + m.tendon_num[t]; w++)
-        J[r * nvp + m.jnt_dofadr[m.wrap_objid[w]]] += -side * m.wrap_prm[w];
+        J[r * nvp + m.jnt_dofadr[m.wrap_objid[w]]] += -side * c.wprm[w];
     }
   }
   auto cdof = DF(cdof), com = DF(subtree_com);

@@ -68,7 +68,7 @@ BP_STAGE void bp_passive(const C& c) {
         if (kt == 0 && bt == 0) continue;
         double frc = -kt * (DF(ten_length)[t] - m.tendon_length0[t]) - bt * DF(ten_velocity)[t];
         for (int w = m.tendon_adr[t]; w < m.tendon_adr[t] + m.tendon_num[t]; w++)
-          if (m.wrap_objid[w] == j) f += m.wrap_prm[w] * frc;
+          if (m.wrap_objid[w] == j) f += c.wprm[w] * frc;
       }
     }
     qp[i] = f;
@@ -200,7 +200,7 @@ BP_STAGE void bp_transmission(const C& c) {
       if (C::FULL && m.tendon_Jadr[t] >= 0) continue;
       double s = 0;
       for (int w = m.tendon_adr[t]; w < m.tendon_adr[t] + m.tendon_num[t]; w++)
-        s += m.wrap_prm[w] * qpos[m.jnt_qposadr[m.wrap_objid[w]]];
+        s += c.wprm[w] * qpos[m.jnt_qposadr[m.wrap_objid[w]]];
       tl[t] = s;
     }
     // spatial tendons (straight segments between sites): dofs on lanes build the dense
@@ -268,7 +268,7 @@ BP_STAGE void bp_actuator_velocity(const C& c) {
       for (int i = 0; i < m.nv; i++) s += DF(ten_J)[m.tendon_Jadr[t] * m.nv + i] * qvel[i];
     else
       for (int w = m.tendon_adr[t]; w < m.tendon_adr[t] + m.tendon_num[t]; w++)
-        s += m.wrap_prm[w] * qvel[m.jnt_dofadr[m.wrap_objid[w]]];
+        s += c.wprm[w] * qvel[m.jnt_dofadr[m.wrap_objid[w]]];
     DF(ten_velocity)[t] = s;
   }
   for (int i = c.lane; i < m.nu; i += C::G) {
@@ -277,7 +277,7 @@ BP_STAGE void bp_actuator_velocity(const C& c) {
     if (!C::LEAN && m.actuator_trntype[i] == 3) {   // moment row = gear * tendon coefficients
       double s = 0;
       for (int w = m.tendon_adr[id]; w < m.tendon_adr[id] + m.tendon_num[id]; w++)
-        s += g * m.wrap_prm[w] * qvel[m.jnt_dofadr[m.wrap_objid[w]]];
+        s += g * c.wprm[w] * qvel[m.jnt_dofadr[m.wrap_objid[w]]];
       vel[i] = s;
     } else {
       vel[i] = g * qvel[m.jnt_dofadr[id]];
@@ -338,7 +338,18 @@ BP_STAGE void bp_fwd_actuation(const C& c) {
     double s = 0;
     for (int k = m.dof_actadr[d]; k < m.dof_actadr[d + 1]; k++) {
       int u = m.dof_actlist[k];
-      s += m.dof_actcoef[k] * force[u];
+      double cf = m.dof_actcoef[k];
+      if constexpr (C::FULL) {
+        // per-env tendon coefficients (point_mass.py:85-101): the host-derived coefficient
+        // was built from the model's wrap_prm, rebuild it from this env's in the same order
+        if (c.P.env_wrap_prm && m.actuator_trntype[u] == 3) {
+          const int t = m.actuator_trnid[2 * u];
+          cf = 0;
+          for (int w = m.tendon_adr[t]; w < m.tendon_adr[t] + m.tendon_num[t]; w++)
+            if (m.jnt_dofadr[m.wrap_objid[w]] == d) cf += m.actuator_gear[6 * u] * c.wprm[w];
+        }
+      }
+      s += cf * force[u];
     }
     qa[d] = s;
   }

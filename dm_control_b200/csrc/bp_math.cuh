@@ -73,6 +73,7 @@ struct Ctx {
   const double* spos;
   const double* bpos;  // this env's body_pos / body_quat
   const double* bquat;
+  const double* wprm;  // this env's tendon coefficients (wrap_prm)
   __device__ __forceinline__ DP null() const { return DP{nullptr}; }
 };
 

@@ -386,7 +386,8 @@ bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
   const double* sp = P.env_site_pos ? P.env_site_pos + env * 3LL * P.m.nsite : P.m.site_pos;
   const double* bp = P.env_body_pos ? P.env_body_pos + env * 3LL * P.m.nbody : P.m.body_pos;
   const double* bq = P.env_body_quat ? P.env_body_quat + env * 4LL * P.m.nbody : P.m.body_quat;
-  Ctx<G, S, SHAPE, MT> c{P, base, ib, wl & (G - 1), mask, act, lock, hot, hf, gp, sp, bp, bq};
+  const double* wp = P.env_wrap_prm ? P.env_wrap_prm + env * (long long)P.env_wrap_n : P.m.wrap_prm;
+  Ctx<G, S, SHAPE, MT> c{P, base, ib, wl & (G - 1), mask, act, lock, hot, hf, gp, sp, bp, bq, wp};
   bp_load_ctrl(c, env);
   bp_run_mode(c);
   if (P.rew_out && act) {           // epilogue: the task's observation and reward
@@ -445,8 +446,9 @@ bp_seg_kernel(const __grid_constant__ BpParams P, int first, int last) {
   const double* sp = P.env_site_pos ? P.env_site_pos + env * 3LL * P.m.nsite : P.m.site_pos;
   const double* bp = P.env_body_pos ? P.env_body_pos + env * 3LL * P.m.nbody : P.m.body_pos;
   const double* bq = P.env_body_quat ? P.env_body_quat + env * 4LL * P.m.nbody : P.m.body_quat;
+  const double* wp = P.env_wrap_prm ? P.env_wrap_prm + env * (long long)P.env_wrap_n : P.m.wrap_prm;
   using C = Ctx<G, 1>;
-  C c{P, base, ib, wl & (G - 1), mask, act, lock, nullptr, hf, gp, sp, bp, bq};
+  C c{P, base, ib, wl & (G - 1), mask, act, lock, nullptr, hf, gp, sp, bp, bq, wp};
   const bool skip = !last;          // sensors / energy on the last sub-step only
   if (SEG == SEG_ACT) {
     if (first) bp_load_ctrl(c, env);

@@ -17,7 +17,8 @@ bp_step_kernel_smem(const __grid_constant__ BpParams P) {
   const double* bp = P.env_body_pos ? P.env_body_pos + env * 3LL * P.m.nbody : P.m.body_pos;
   const double* bq = P.env_body_quat ? P.env_body_quat + env * 4LL * P.m.nbody : P.m.body_quat;
   Ctx<32, 1> c{P, smem, (int*)(smem + P.L.ints), lane, 0xffffffffu, true, false, nullptr, hf,
-               gp, sp, bp, bq};
+               gp, sp, bp, bq,
+               P.env_wrap_prm ? P.env_wrap_prm + env * (long long)P.env_wrap_n : P.m.wrap_prm};
   bp_load_ctrl(c, env);
   bp_run_mode(c);
   __syncwarp();

@@ -26,7 +26,7 @@ bp_step_kernel_static(const __grid_constant__ BpParams P) {
     double* base = wb + (env & 31);
     int* ib = (int*)(wb + (long long)L::ints * 32) + (env & 31);
     Ctx<1, 32, 1, MT> c{P, base, ib, 0, 1u << (threadIdx.x & 31), true, false, nullptr, nullptr,
-                        P.m.geom_pos, P.m.site_pos, P.m.body_pos, P.m.body_quat};
+                        P.m.geom_pos, P.m.site_pos, P.m.body_pos, P.m.body_quat, P.m.wrap_prm};
     bp_load_ctrl(c, env);
     bp_run_mode(c);
     if (P.rew_out) bp_task_eval(P, P.task, env, P.task_nobs, P.obs_out, P.rew_out);

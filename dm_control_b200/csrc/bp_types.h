@@ -192,6 +192,8 @@ struct BpParams {
   const double* env_site_pos;   // [nenv][3 * nsite]
   const double* env_body_pos;   // [nenv][3 * nbody]   (manipulator.py:218-224 target body)
   const double* env_body_quat;  // [nenv][4 * nbody]
+  const double* env_wrap_prm;   // [nenv][env_wrap_n]   (point_mass.py:85-101 randomize_gains)
+  int env_wrap_n;
   // fused Environment.step (bp_env_step): dense [nenv][nu] controls scattered into the
   // images before the first sub-step, task observation / reward written after the last
   const double* ctrl_in;   // null: images keep their ctrl

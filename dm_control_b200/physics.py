@@ -35,6 +35,10 @@ def default_lanes(m):
   return 4 if m.nv <= 3 else 8 if m.nv <= 12 else 16
 
 
+# model arrays that tasks edit per episode and that a batch therefore holds per env
+ENV_MODEL_FIELDS = ("geom_pos", "site_pos", "body_pos", "body_quat", "wrap_prm")
+
+
 def default_sizes(m):
   """(njmax, nconmax) that fit typical suite episodes; overflow raises the same
   CNSTRFULL / CONTACTFULL warnings the reference surfaces (core_test.py:97-103)."""
@@ -264,7 +268,7 @@ class BatchedPhysics:
     """Everything a bit-exact resume needs: qpos, qvel, act, ctrl, the
     solver's warm start, applied forces and time, plus the per-env model data tasks edit."""
     st = {f: getattr(self.data, f) for f in self.FULL_STATE_FIELDS}
-    for name in ("geom_pos", "site_pos", "body_pos", "body_quat"):
+    for name in ENV_MODEL_FIELDS:
       if self._batch.has_env_model(name):
         st["env_" + name] = self._batch.read_env_model(name)
     if int(self.model.nhfielddata) > 0:
@@ -274,7 +278,7 @@ class BatchedPhysics:
   def set_full_state(self, st):
     """Restores get_full_state() and recomputes what Physics.step() leaves behind (mj_step1 of
     the restored state), so that stepping on continues bit for bit."""
-    for name in ("geom_pos", "site_pos", "body_pos", "body_quat"):
+    for name in ENV_MODEL_FIELDS:
       if "env_" + name in st:
         self._batch.write_env_model(name, st["env_" + name])
     if "hfield" in st:
@@ -312,7 +316,7 @@ class BatchedPhysics:
   def set_env_model_field(self, name, value, env0=0):
     """Per-env run-time model edit (reacher.py:96-101 `geom_pos['target']`): value is
     [n, ...] with the model field's trailing shape; supported: geom_pos, site_pos,
-    body_pos, body_quat (manipulator.py:218-224).  Inside reset_context(mask=...) a
+    body_pos, body_quat (manipulator.py:218-224), wrap_prm (point_mass.py:85-101).  Inside reset_context(mask=...) a
     full-batch value only reaches the envs being reset."""
     if self._reset_mask is not None and env0 == 0 and len(value) == self.nenv:
       cur = self._batch.read_env_model(name)

@@ -157,9 +157,22 @@ class Task:
     elif d == "quadruped":
       self._initialize_quadruped(physics, t)
       return
-    elif d == "point_mass":       # suite/point_mass.py:85-107 (easy: fixed gains)
+    elif d == "point_mass":       # suite/point_mass.py:85-107
+      wprm = np.tile(np.asarray(m.wrap_prm, dtype=np.float64), (n, 1))
       for e, rng in self._each():
         _randomize_limited_and_rotational_joints(m, qpos[e], rng)
+        if t == "hard":           # each control actuates a random combination of the joints
+          dir1 = rng.randn(2)
+          dir1 /= np.linalg.norm(dir1)
+          parallel = True         # a second direction that is not 'too parallel' to the first
+          while parallel:
+            dir2 = rng.randn(2)
+            dir2 /= np.linalg.norm(dir2)
+            parallel = abs(np.dot(dir1, dir2)) > 0.9
+          wprm[e, [0, 1]] = dir1
+          wprm[e, [2, 3]] = dir2
+      if t == "hard":             # per-env model.wrap_prm (bp_env_model_write)
+        physics.set_env_model_field("wrap_prm", wprm)
     elif d == "reacher":          # suite/reacher.py:91-103
       tgt = m.name2id("target", "geom")
       size = np.array(m.geom_size, dtype=np.float64)

@@ -324,9 +324,11 @@ _TASKS = [
             lambda m: [("position", m.nq), ("to_target", 2), ("velocity", m.nv)]),
     TaskDef("reacher", "hard", "reacher", REACHER, 20, None, _reacher(.015),
             lambda m: [("position", m.nq), ("to_target", 2), ("velocity", m.nv)]),
-    # point_mass.py:29-43: 20 s; `hard` rewires the tendon coefficients per episode
-    # (model.wrap_prm) and is not served
+    # point_mass.py:29-43: 20 s; `hard` rewires the tendon coefficients per episode and per
+    # env (model.wrap_prm through bp_env_model_write)
     TaskDef("point_mass", "easy", "point_mass", POINT_MASS, 20, None, _point_mass,
+            lambda m: [("position", m.nq), ("velocity", m.nv)]),
+    TaskDef("point_mass", "hard", "point_mass", POINT_MASS, 20, None, _point_mass,
             lambda m: [("position", m.nq), ("velocity", m.nv)]),
     # swimmer.py:28-30: 30 s, control timestep .03; fluid drag (option density), the target
     # geom moves per episode and per env

@@ -95,10 +95,11 @@ int bp_hfield_read(bp_batch* b, float* host, int64_t env0, int64_t n);
 /* Per-env copies of model arrays that tasks edit per episode
  * (`physics.named.model.geom_pos['target', 'x'] = ...`, suite/reacher.py:96-101;
  * `site_pos['target']`, suite/finger.py:180-181; `body_pos[target]` / `body_quat[target]`,
- * suite/manipulator.py:218-224): name is "geom_pos", "site_pos", "body_pos" or "body_quat",
- * `host` a dense [n][3 * ngeom | 3 * nsite | 3 * nbody | 4 * nbody] float64 array for envs
- * [env0, env0+n).  Every
- * env starts from the model's values; the copy is made on the first write. */
+ * suite/manipulator.py:218-224; `model.wrap_prm[[0, 1]] = dir1`, suite/point_mass.py:85-101):
+ * name is "geom_pos", "site_pos", "body_pos", "body_quat" or "wrap_prm", `host` a dense
+ * [n][3 * ngeom | 3 * nsite | 3 * nbody | 4 * nbody | nwrap] float64 array for envs
+ * [env0, env0+n).  Every env starts from the model's values; the copy is made on the first
+ * write. */
 int bp_env_model_write(bp_batch* b, const char* name, const double* host, int64_t env0,
                        int64_t n);
 int bp_env_model_read(bp_batch* b, const char* name, double* host, int64_t env0, int64_t n);

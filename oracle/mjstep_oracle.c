@@ -220,10 +220,16 @@ struct OData {
   double* hfield;   /* this env's elevation data (Escape writes it per episode) */
   double *geom_pos, *site_pos;   /* this env's copies (per-episode target moves) */
   double *body_pos, *body_quat;
+  double* wrap_prm;   /* this env's tendon coefficients (point_mass.py:85-101 randomize_gains) */
   /* solver scratch */
   double *s_Ma, *s_jar, *s_grad, *s_Mgrad, *s_search, *s_Mv, *s_jv, *s_H,
       *s_Mdense, *s_fluid, *s_AR, *s_Mgold;
 };
+
+static int64_t wrap_count(const OModel* m) {
+  BlobEntry* e = find_entry(m, "wrap_prm");
+  return e ? e->count : 0;
+}
 
 OData* od_create(const OModel* m) {
   OData* d = (OData*)calloc(1, sizeof(OData));
@@ -243,6 +249,8 @@ OData* od_create(const OModel* m) {
   d->body_quat = (double*)calloc(4 * m->nbody + 1, sizeof(double));
   for (int i = 0; i < 3 * m->nbody; i++) d->body_pos[i] = m->body_pos[i];
   for (int i = 0; i < 4 * m->nbody; i++) d->body_quat[i] = m->body_quat[i];
+  d->wrap_prm = (double*)calloc(wrap_count(m) + 1, sizeof(double));
+  for (int64_t i = 0; i < wrap_count(m); i++) d->wrap_prm[i] = m->wrap_prm[i];
   int nv = m->nv > 0 ? m->nv : 1, nj = m->njmax > 0 ? m->njmax : 1;
   d->s_Ma = calloc(nv, 8); d->s_jar = calloc(nj, 8); d->s_grad = calloc(nv, 8);
   d->s_Mgrad = calloc(nv, 8); d->s_search = calloc(nv, 8); d->s_Mv = calloc(nv, 8);
@@ -262,7 +270,7 @@ void od_free(OData* d) {
 #undef X
   free(d->contact);
   free(d->hfield); free(d->geom_pos); free(d->site_pos);
-  free(d->body_pos); free(d->body_quat);
+  free(d->body_pos); free(d->body_quat); free(d->wrap_prm);
   free(d->s_Ma); free(d->s_jar); free(d->s_grad); free(d->s_Mgrad);
   free(d->s_search); free(d->s_Mv); free(d->s_jv); free(d->s_H);
   free(d->s_Mdense); free(d->s_fluid); free(d->s_AR); free(d->s_Mgold);
@@ -281,6 +289,11 @@ void* od_field(OData* d, const char* name, int64_t* count, int* dtype) {
     if (count) *count = (q ? 4 : 3) * d->m->nbody;
     if (dtype) *dtype = 0;
     return q ? d->body_quat : d->body_pos;
+  }
+  if (strcmp(name, "wrap_prm") == 0) {
+    if (count) *count = wrap_count(d->m);
+    if (dtype) *dtype = 0;
+    return d->wrap_prm;
   }
   if (strcmp(name, "hfield_data") == 0) {
     if (count) *count = d->m->nhfielddata;
@@ -671,7 +684,7 @@ static void o_passive(const OModel* m, OData* d) {
     if (k == 0 && b == 0) continue;
     double frc = -k * (d->ten_length[t] - m->tendon_length0[t]) - b * d->ten_velocity[t];
     for (int w = m->tendon_adr[t]; w < m->tendon_adr[t] + m->tendon_num[t]; w++)
-      d->qfrc_passive[m->jnt_dofadr[m->wrap_objid[w]]] += m->wrap_prm[w] * frc;
+      d->qfrc_passive[m->jnt_dofadr[m->wrap_objid[w]]] += d->wrap_prm[w] * frc;
   }
   /* fluid forces [MJ-doc: inertia-box model of mj_passive]: every body is replaced by the
    * box with its mass and inertia; viscous force and torque of the equivalent sphere, plus
@@ -782,7 +795,7 @@ static void o_tendon(const OModel* m, OData* d) {
     int w0 = m->tendon_adr[t], w1 = w0 + m->tendon_num[t], ja = m->tendon_Jadr[t];
     if (ja < 0) {
       for (int w = w0; w < w1; w++)
-        len += m->wrap_prm[w] * d->qpos[m->jnt_qposadr[m->wrap_objid[w]]];
+        len += d->wrap_prm[w] * d->qpos[m->jnt_qposadr[m->wrap_objid[w]]];
     } else {
       double* J = d->ten_J + (size_t)ja * nv;
       double* jp0 = (double*)malloc(sizeof(double) * 6 * (nv + 1));
@@ -816,7 +829,7 @@ static void o_transmission(const OModel* m, OData* d) {
     if (m->actuator_trntype[i] == 3) {          /* tendon transmission */
       d->actuator_length[i] = g * d->ten_length[j];
       for (int w = m->tendon_adr[j]; w < m->tendon_adr[j] + m->tendon_num[j]; w++)
-        d->actuator_moment[i * nv + m->jnt_dofadr[m->wrap_objid[w]]] += g * m->wrap_prm[w];
+        d->actuator_moment[i * nv + m->jnt_dofadr[m->wrap_objid[w]]] += g * d->wrap_prm[w];
       continue;
     }
     /* joint transmission, scalar joints only in this subset */
@@ -2038,10 +2051,10 @@ static void o_make_constraint(const OModel* m, OData* d) {
       double* J = d->efc_J + (size_t)r * nv;
       if (tend) {
         for (int w = m->tendon_adr[o1]; w < m->tendon_adr[o1] + m->tendon_num[o1]; w++)
-          J[m->jnt_dofadr[m->wrap_objid[w]]] += m->wrap_prm[w];
+          J[m->jnt_dofadr[m->wrap_objid[w]]] += d->wrap_prm[w];
         if (o2 >= 0)
           for (int w = m->tendon_adr[o2]; w < m->tendon_adr[o2] + m->tendon_num[o2]; w++)
-            J[m->jnt_dofadr[m->wrap_objid[w]]] -= deriv * m->wrap_prm[w];
+            J[m->jnt_dofadr[m->wrap_objid[w]]] -= deriv * d->wrap_prm[w];
       } else {
         J[m->jnt_dofadr[o1]] += 1;
         if (o2 >= 0) J[m->jnt_dofadr[o2]] -= deriv;
@@ -2088,7 +2101,7 @@ static void o_make_constraint(const OModel* m, OData* d) {
             for (int i = 0; i < nv; i++) row[i] = -side * d->ten_J[(size_t)m->tendon_Jadr[t] * nv + i];
           else
             for (int w = m->tendon_adr[t]; w < m->tendon_adr[t] + m->tendon_num[t]; w++)
-              row[m->jnt_dofadr[m->wrap_objid[w]]] += -side * m->wrap_prm[w];
+              row[m->jnt_dofadr[m->wrap_objid[w]]] += -side * d->wrap_prm[w];
         }
       }
     }
@@ -3149,7 +3162,7 @@ static void fwd_velocity(const OModel* m, OData* d) {
       for (int i = 0; i < nv; i++) v += d->ten_J[(size_t)m->tendon_Jadr[t] * nv + i] * d->qvel[i];
     else
       for (int w = m->tendon_adr[t]; w < m->tendon_adr[t] + m->tendon_num[t]; w++)
-        v += m->wrap_prm[w] * d->qvel[m->jnt_dofadr[m->wrap_objid[w]]];
+        v += d->wrap_prm[w] * d->qvel[m->jnt_dofadr[m->wrap_objid[w]]];
     d->ten_velocity[t] = v;
   }
   o_com_vel(m, d);

@@ -23,7 +23,7 @@ SERVED = [("cartpole", "swingup"), ("cartpole", "swingup_sparse"), ("cartpole", 
           ("humanoid", "stand"), ("humanoid", "walk"), ("humanoid", "run"),
           ("quadruped", "walk"), ("quadruped", "run"), ("quadruped", "escape"), ("quadruped", "fetch"),
           ("lqr", "lqr_2_1"), ("lqr", "lqr_6_2"), ("reacher", "easy"), ("reacher", "hard"),
-          ("point_mass", "easy"), ("finger", "turn_easy"), ("finger", "turn_hard"),
+          ("point_mass", "easy"), ("point_mass", "hard"), ("finger", "turn_easy"), ("finger", "turn_hard"),
           ("humanoid_CMU", "stand"), ("humanoid_CMU", "run"),
           ("swimmer", "swimmer6"), ("swimmer", "swimmer15"),
           ("fish", "upright"), ("fish", "swim"),
@@ -359,3 +359,36 @@ def test_env_step_host_direct_results_equal_copied_results(name, nenv):
     assert np.all(np.isfinite(o1)) and np.abs(o1).max() > 0
     np.testing.assert_array_equal(o1, o2)
     np.testing.assert_array_equal(r1, r2)
+
+
+@pytest.mark.gpu
+def test_point_mass_hard_randomizes_gains_per_env():
+  """suite/point_mass.py:85-101: the hard task draws, per episode, two unit actuation
+  directions that are not 'too parallel' and writes them into model.wrap_prm -- here per env
+  (bp_env_model_write), in the reference's draw order after the joint randomizer."""
+  from dm_control_b200 import suite
+  n = 16
+  env = suite.load("point_mass", "hard", task_kwargs={"random": 3}, nenv=n)
+  env.reset()
+  w = env.physics.env_model_field("wrap_prm").reshape(n, 2, 2)
+  np.testing.assert_allclose(np.linalg.norm(w, axis=2), 1.0, atol=1e-12)
+  assert np.all(np.abs(np.sum(w[:, 0] * w[:, 1], axis=1)) <= 0.9)
+  assert len(np.unique(np.round(w[:, 0, 0], 9))) == n
+  rng = np.random.RandomState(3)          # env 0: two limited slide joints, then the gains
+  rng.uniform(0, 1); rng.uniform(0, 1)
+  d1 = rng.randn(2); d1 /= np.linalg.norm(d1)
+  np.testing.assert_allclose(w[0, 0], d1, atol=1e-12)
+  # control 0 pushes along this env's first direction
+  env.physics.data.qvel = np.zeros((n, 2))
+  env.physics.set_control(np.tile([1.0, 0.0], (n, 1)))
+  env.physics.forward()
+  f = env.physics.data.qfrc_actuator
+  np.testing.assert_allclose(f / np.linalg.norm(f, axis=1, keepdims=True), w[:, 0], atol=1e-10)
+  # a second episode draws new gains; the easy task leaves the model's
+  env.reset()
+  assert not np.allclose(env.physics.env_model_field("wrap_prm").reshape(n, 2, 2), w)
+  env.close()
+  easy = suite.load("point_mass", "easy", task_kwargs={"random": 3}, nenv=4)
+  easy.reset()
+  assert not easy.physics._batch.has_env_model("wrap_prm")
+  easy.close()

@@ -192,6 +192,39 @@ def test_per_env_model_frames(lanes):
   b.free(); model.free()
 
 
+@pytest.mark.parametrize("lanes", [32, 8, 1])
+def test_per_env_tendon_coefficients(lanes):
+  """bp_env_model_write("wrap_prm"): every env with its own fixed-tendon coefficients, i.e.
+  its own mapping from controls to joints (suite/point_mass.py:85-101 randomize_gains) --
+  tendon length / velocity, actuator moment and qfrc_actuator against oracles that each hold
+  their own copy."""
+  m = PU.load_model("point_mass")
+  rng = np.random.RandomState(7)
+  nenv = 40
+  d = rng.randn(nenv, 2, 2)
+  d /= np.linalg.norm(d, axis=2, keepdims=True)
+  res, _ = PU.run_parity("point_mass", nenv=nenv, nsteps=10, seed=4, lanes=lanes,
+                         check_steps=[0, 1, 2, 10], env_model={"wrap_prm": d.reshape(nenv, 4)})
+  _assert_parity(res)
+  res0, _ = PU.run_parity("point_mass", nenv=4, nsteps=1, seed=4, lanes=lanes)
+  # the coefficients do reach the dynamics: the envs above do not move like the model's own
+  assert res[1].f64["qacc"] <= 1e-8 and res0[1].f64["qacc"] <= 1e-8
+  from dm_control_b200 import binding
+  model = binding.Model(m)
+  b = binding.Batch(model, nenv, 0, 0, lanes)
+  qpos, qvel, ctrl = PU.random_states(m, nenv, 4)
+  out = []
+  for per_env in (False, True):
+    if per_env:
+      b.write_env_model("wrap_prm", d.reshape(nenv, 4))
+    b.write("qpos", qpos); b.write("qvel", 0 * qvel); b.write("ctrl", np.tile([1.0, 0.0], (nenv, 1)))
+    b.forward(); b.sync()
+    out.append(b.read("qfrc_actuator"))
+  np.testing.assert_allclose(out[0], np.tile([1.0, 0.0], (nenv, 1)) * m.actuator_gear[0, 0], atol=1e-12)
+  np.testing.assert_allclose(out[1], d[:, 0] * m.actuator_gear[0, 0], atol=1e-12)
+  b.free(); model.free()
+
+
 @pytest.mark.parametrize("lanes", [16, 8, 1])
 def test_cmu_humanoid_matches_oracle(lanes):
   """humanoid_CMU (nv = 62, 1188 candidate pairs, <contact><exclude>): the widest model
