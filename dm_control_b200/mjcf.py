@@ -256,6 +256,12 @@ class Physics(BatchedPhysics):
     assets = mjcf_model.get_assets() if hasattr(mjcf_model, "get_assets") else None
     return cls.from_xml_string(xml, assets=assets, **kw)
 
+  def _reload_from_model(self, flat_model):
+    """mjcf/physics.py:499-518: a reload drops every cached binding."""
+    self._bindings = {(): _EmptyBinding()}
+    self._dirty = False
+    super()._reload_from_model(flat_model)
+
   @property
   def is_dirty(self):
     """Whether derived quantities need to be recalculated (mjcf/physics.py:520-523)."""

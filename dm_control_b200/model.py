@@ -21,6 +21,7 @@ import struct
 import numpy as np
 
 MAGIC = b"BPMODEL1"
+NAMES_MAGIC = b"BPNAMES1"
 _ENTRY = struct.Struct("<40sii4iqq")
 
 # --- enums (values follow MuJoCo 2.0's mjmodel.h; the generated
@@ -152,6 +153,50 @@ class FlatModel:
     for p in payload:
       out.write(p)
     return out.getvalue()
+
+  # ---- model binaries: MjModel.to_bytes / from_byte_string / save_binary /
+  # from_binary_path (wrapper/core.py:460-468, 506-519).  The byte string is the C-ABI blob
+  # above followed by a name trailer (b"BPNAMES1", int64 length, JSON); MuJoCo's own MJB
+  # layout is closed and undocumented in the reference tree, so real .mjb files cannot be
+  # read -- a model saved here loads here, bit for bit.
+  def to_bytes(self):
+    import json
+    meta = json.dumps({"names": self.names, "model_name": self.model_name,
+                       "scalars": sorted(k for k in self.arrays if k in _SCALARS)}).encode()
+    return self.to_blob() + NAMES_MAGIC + struct.pack("<q", len(meta)) + meta
+
+  @classmethod
+  def from_byte_string(cls, byte_string):
+    import json
+    b = bytes(byte_string)
+    if len(b) < 16 or b[:8] != MAGIC:
+      raise ValueError("not a compiled-model byte string (bad magic)")
+    nfields = struct.unpack_from("<i", b, 8)[0]
+    m = cls()
+    end = 16 + _ENTRY.size * nfields
+    for k in range(nfields):
+      name, dt, ndim, d0, d1, d2, d3, off, count = _ENTRY.unpack_from(b, 16 + k * _ENTRY.size)
+      dtype = np.float64 if dt == 0 else np.int32
+      a = np.frombuffer(b, dtype=dtype, count=count, offset=off).copy()
+      m.arrays[name.rstrip(b"\0").decode()] = a.reshape((d0, d1, d2, d3)[:ndim])
+      end = max(end, off + (count * a.itemsize + 7) // 8 * 8)
+    if b[end:end + 8] != NAMES_MAGIC:
+      raise ValueError("compiled-model byte string without its name table")
+    n = struct.unpack_from("<q", b, end + 8)[0]
+    meta = json.loads(b[end + 16:end + 16 + n].decode())
+    m.names = {c: list(v) for c, v in meta["names"].items()}
+    m.model_name = meta["model_name"]
+    _SCALARS.update(meta["scalars"])
+    return m
+
+  def save_binary(self, binary_path):
+    with open(binary_path, "wb") as f:
+      f.write(self.to_bytes())
+
+  @classmethod
+  def from_binary_path(cls, binary_path):
+    with open(binary_path, "rb") as f:
+      return cls.from_byte_string(f.read())
 
   # ---- persistence (the compiled-model cache shipped with the suite) -------
   def save(self, path):

@@ -148,6 +148,35 @@ class BatchedPhysics:
   def from_flat_model(cls, flat_model, **kw):
     return cls(flat_model, **kw)
 
+  from_model = from_flat_model          # engine.py:405-409
+
+  @classmethod
+  def from_byte_string(cls, byte_string, **kw):
+    """engine.py:429-433: from a compiled model's `to_bytes()` (model.FlatModel.to_bytes: this
+    library's own binary layout, not MuJoCo's closed MJB)."""
+    return cls(M.FlatModel.from_byte_string(byte_string), **kw)
+
+  @classmethod
+  def from_binary_path(cls, file_path, **kw):
+    """engine.py:447-458, for files written by `physics.model.save_binary(path)`."""
+    return cls(M.FlatModel.from_binary_path(file_path), **kw)
+
+  def _reload_from_model(self, flat_model):
+    """engine.py:341-359: a new model behind the same Physics object, state as after
+    construction."""
+    device, nenv = self._ctor["device"], self.nenv
+    self.free()
+    # buffer sizes and lane width follow the new model
+    BatchedPhysics.__init__(self, flat_model, nenv, device=device)
+
+  def reload_from_xml_string(self, xml_string, assets=None):
+    """engine.py:460-476."""
+    self._reload_from_model(mjcf_compiler.compile_xml(xml_string, assets))
+
+  def reload_from_xml_path(self, file_path):
+    """engine.py:478-488."""
+    self._reload_from_model(mjcf_compiler.compile_file(file_path))
+
   # ---- simulation (engine.py:141-166, 297-305) ---------------------------------------
   def set_control(self, control):
     """Sets the control signal of every env: [nenv, nu] (or [nu], broadcast)."""

@@ -132,3 +132,27 @@ def test_flatten_observation_orders_keys():
   flat = control.flatten_observation(obs)
   assert list(flat) == ["observations"] and flat["observations"].shape == (3, 3)
   np.testing.assert_array_equal(flat["observations"][0], [1, 1, 0])   # insertion order kept
+
+
+def test_model_binary_roundtrip(tmp_path):
+  """MjModel.to_bytes / from_byte_string / save_binary / from_binary_path
+  (wrapper/core.py:460-468,506-519; core_test.py:82-95 testSerialize... pattern): a model
+  that went through its byte string has the same arrays, names and scalars."""
+  for domain in ("cheetah", "quadruped_escape", "point_mass"):
+    m = PU.load_model(domain)
+    b = m.to_bytes()
+    assert b[:8] == b"BPMODEL1" and b.startswith(m.to_blob())
+    for m2 in (M.FlatModel.from_byte_string(b),):
+      assert sorted(m2.arrays) == sorted(m.arrays)
+      for k, a in m.arrays.items():
+        assert m2.arrays[k].dtype == a.dtype and m2.arrays[k].shape == a.shape, k
+        np.testing.assert_array_equal(m2.arrays[k], a, err_msg=k)
+      assert m2.names == m.names and m2.model_name == m.model_name
+      assert m2.nq == m.nq and isinstance(m2.nq, int) and m2.to_bytes() == b
+    path = str(tmp_path / (domain + ".bpb"))
+    m.save_binary(path)
+    assert M.FlatModel.from_binary_path(path).to_bytes() == b
+  with pytest.raises(ValueError):
+    M.FlatModel.from_byte_string(b"MJB\0" + b"\0" * 64)
+  with pytest.raises(ValueError):
+    M.FlatModel.from_byte_string(m.to_blob())          # blob without its name table

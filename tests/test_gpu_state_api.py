@@ -111,3 +111,31 @@ def test_contact_force_and_object_velocity_match_oracle():
   np.testing.assert_array_equal(p.data.object_velocity("left_hand", "body"),
                                 p.data.object_velocity(hand, 1))
   p.free()
+
+
+def test_from_byte_string_and_reload(tmp_path):
+  """engine.py:429-433,447-488: a Physics built from a model's byte string / binary file steps
+  bit for bit like the one it came from; reload_from_xml_string swaps the model behind the
+  same object and leaves it in the state of a fresh one."""
+  p, ctrl = _physics("walker")
+  blob = p.model.to_bytes()
+  path = str(tmp_path / "walker.bpb")
+  p.model.save_binary(path)
+  for q in (BatchedPhysics.from_byte_string(blob, nenv=p.nenv),
+            BatchedPhysics.from_binary_path(path, nenv=p.nenv)):
+    q.set_full_state(p.get_full_state())
+    p2 = p.copy()
+    q.step(7); p2.step(7)
+    for f in ("qpos", "qvel", "qacc", "sensordata", "time"):
+      np.testing.assert_array_equal(getattr(q.data, f), getattr(p2.data, f), err_msg=f)
+    assert q.named.data.xpos["torso"].shape == (p.nenv, 3)
+    q.free(); p2.free()
+  xml = """<mujoco><worldbody><body name="b"><joint name="j" type="hinge" axis="0 1 0"/>
+  <geom name="g" type="capsule" fromto="0 0 0 0 0 -1" size=".05"/></body></worldbody></mujoco>"""
+  p.reload_from_xml_string(xml)
+  assert p.model.nq == 1 and p.data.qpos.shape == (p.nenv, 1) and np.all(p.data.time == 0)
+  fresh = BatchedPhysics.from_xml_string(xml, nenv=p.nenv)
+  p.step(5); fresh.step(5)
+  np.testing.assert_array_equal(p.data.qpos, fresh.data.qpos)
+  assert p.named.data.xpos["b"].shape == (p.nenv, 3)
+  p.free(); fresh.free()
