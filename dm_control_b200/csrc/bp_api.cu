@@ -625,23 +625,41 @@ struct bp_batch {
 
 static void make_layout(const BpModel& m, int njmax, int nconmax, BpLayout* L,
                         std::vector<FieldInfo>* fields) {
+  // alignment inside an env's image: an array of at least one 128-byte line (16 doubles / 32
+  // ints) starts on a line, smaller arrays stay packed, and the image is a whole number of
+  // lines -- so the big arrays (J, H, the contact / body tables) touch as few lines as their
+  // size allows.  Measured with the static instances, same box (profiles/r2_tuning.md):
+  // cheetah +2.9 %, humanoid +2.7 %, walker +2.6 %, quadruped-escape +1.7 %, finger -0.9 %;
+  // aligning the small arrays as well costs the small models more lines than it saves.
+  // BPHYS_ALIGN=1 packs everything, 16 puts every array on its own line (static instances
+  // are generated for the default).
+  int al = 0;
+  if (const char* e = getenv("BPHYS_ALIGN")) { int v = atoi(e); if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) al = v; }
+  auto up = [&](int x, int cnt, int cap) {
+    int a = 1;
+    if (al > 0) a = cnt > 1 ? al * (cap / 16) : 1;
+    else if (cnt >= cap) a = cap;
+    return (x + a - 1) / a * a;
+  };
   int off = 0;
-#define X(n, cnt) { L->n = off; int c_ = (cnt); \
+#define X(n, cnt) { int c_ = (cnt); off = up(off, c_, 16); L->n = off; \
     if (fields) fields->push_back({#n, (int64_t)off * 8, c_, 0}); off += c_; }
   BP_DATA_F64(X)
 #undef X
+  off = (off + 15) / 16 * 16;
   L->ints = off;
   int ioff = 0;
-#define X(n, cnt) { L->n = ioff; int c_ = (cnt); \
+#define X(n, cnt) { int c_ = (cnt); ioff = up(ioff, c_, 32); L->n = ioff; \
     if (fields) fields->push_back({#n, (int64_t)L->ints * 8 + (int64_t)ioff * 4, c_, 1}); ioff += c_; }
   BP_DATA_I32(X)
 #undef X
   off += (ioff + 1) / 2;
-  off = (off + 1) / 2 * 2;      // keep 16-byte alignment of each env image
+  off = (off + 15) / 16 * 16;
   L->persist = off;
-#define X(n, cnt) { L->n = off; off += (cnt); }
+#define X(n, cnt) { int c_ = (cnt); off = up(off, c_, 16); L->n = off; off += c_; }
   BP_DATA_SCRATCH(X)
 #undef X
+  off = (off + 15) / 16 * 16;
   L->total = off;
   L->njmax = njmax; L->nconmax = nconmax;
 }
