@@ -439,7 +439,7 @@ extern "C" int bp_static_header(const void* blob, int64_t nbytes, int njmax, int
   fprintf(f, "  static constexpr int ints = %d, persist = %d, total = %d, njmax = %d, nconmax = %d;\n};\n",
           L.ints, L.persist, L.total, L.njmax, L.nconmax);
   fprintf(f, "struct Model {\n");
-  fprintf(f, "#define X(n) const double* n;\n  BP_MODEL_F64_ARRAYS(X) BP_MODEL_DERIVED_F64_ARRAYS(X)\n#undef X\n");
+  fprintf(f, "#define X(n) BpRO<double> n;\n  BP_MODEL_F64_ARRAYS(X) BP_MODEL_DERIVED_F64_ARRAYS(X)\n#undef X\n");
   fprintf(f, "#define X(n) double n;\n  BP_MODEL_F64_SCALARS(X)\n#undef X\n");
   fprintf(f, "  int opt_integrator, opt_cone, opt_solver, opt_iterations, opt_ls_iterations, opt_disableflags, opt_enableflags;\n");
   fprintf(f, "  int nconmax, njmax;\n");

@@ -382,11 +382,11 @@ bp_step_kernel_gmem(const __grid_constant__ BpParams P) {
   double* hot = (S == 1 && P.hot_doubles > 0)
       ? bp_arena + (long long)(threadIdx.x / G) * P.hot_doubles : nullptr;
   const float* hf = P.hfield ? P.hfield + env * (long long)P.m.nhfielddata : nullptr;
-  const double* gp = P.env_geom_pos ? P.env_geom_pos + env * 3LL * P.m.ngeom : P.m.geom_pos;
-  const double* sp = P.env_site_pos ? P.env_site_pos + env * 3LL * P.m.nsite : P.m.site_pos;
-  const double* bp = P.env_body_pos ? P.env_body_pos + env * 3LL * P.m.nbody : P.m.body_pos;
-  const double* bq = P.env_body_quat ? P.env_body_quat + env * 4LL * P.m.nbody : P.m.body_quat;
-  const double* wp = P.env_wrap_prm ? P.env_wrap_prm + env * (long long)P.env_wrap_n : P.m.wrap_prm;
+  const double* gp = P.env_geom_pos ? P.env_geom_pos + env * 3LL * P.m.ngeom : (const double*)P.m.geom_pos;
+  const double* sp = P.env_site_pos ? P.env_site_pos + env * 3LL * P.m.nsite : (const double*)P.m.site_pos;
+  const double* bp = P.env_body_pos ? P.env_body_pos + env * 3LL * P.m.nbody : (const double*)P.m.body_pos;
+  const double* bq = P.env_body_quat ? P.env_body_quat + env * 4LL * P.m.nbody : (const double*)P.m.body_quat;
+  const double* wp = P.env_wrap_prm ? P.env_wrap_prm + env * (long long)P.env_wrap_n : (const double*)P.m.wrap_prm;
   Ctx<G, S, SHAPE, MT> c{P, base, ib, wl & (G - 1), mask, act, lock, hot, hf, gp, sp, bp, bq, wp};
   bp_load_ctrl(c, env);
   bp_run_mode(c);
@@ -442,11 +442,11 @@ bp_seg_kernel(const __grid_constant__ BpParams P, int first, int last) {
   int* ib = (int*)(base + P.L.ints);
   unsigned mask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (wl & ~(G - 1)));
   const float* hf = P.hfield ? P.hfield + env * (long long)P.m.nhfielddata : nullptr;
-  const double* gp = P.env_geom_pos ? P.env_geom_pos + env * 3LL * P.m.ngeom : P.m.geom_pos;
-  const double* sp = P.env_site_pos ? P.env_site_pos + env * 3LL * P.m.nsite : P.m.site_pos;
-  const double* bp = P.env_body_pos ? P.env_body_pos + env * 3LL * P.m.nbody : P.m.body_pos;
-  const double* bq = P.env_body_quat ? P.env_body_quat + env * 4LL * P.m.nbody : P.m.body_quat;
-  const double* wp = P.env_wrap_prm ? P.env_wrap_prm + env * (long long)P.env_wrap_n : P.m.wrap_prm;
+  const double* gp = P.env_geom_pos ? P.env_geom_pos + env * 3LL * P.m.ngeom : (const double*)P.m.geom_pos;
+  const double* sp = P.env_site_pos ? P.env_site_pos + env * 3LL * P.m.nsite : (const double*)P.m.site_pos;
+  const double* bp = P.env_body_pos ? P.env_body_pos + env * 3LL * P.m.nbody : (const double*)P.m.body_pos;
+  const double* bq = P.env_body_quat ? P.env_body_quat + env * 4LL * P.m.nbody : (const double*)P.m.body_quat;
+  const double* wp = P.env_wrap_prm ? P.env_wrap_prm + env * (long long)P.env_wrap_n : (const double*)P.m.wrap_prm;
   using C = Ctx<G, 1>;
   C c{P, base, ib, wl & (G - 1), mask, act, lock, nullptr, hf, gp, sp, bp, bq, wp};
   const bool skip = !last;          // sensors / energy on the last sub-step only

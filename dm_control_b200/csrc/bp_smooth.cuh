@@ -32,9 +32,9 @@ BP_STAGE void bp_kinematics(const C& c) {
          idx += C::G) {
       int b = m.body_level_list[idx], p = m.body_parentid[b];
       double pos[3], quat[4], R[9], t[3];
-      mat_vec3(t, xmat + 9 * p, (C::FULL ? c.bpos : m.body_pos) + 3 * b);
+      mat_vec3(t, xmat + 9 * p, (C::FULL ? c.bpos : (const double*)m.body_pos) + 3 * b);
       for (int k = 0; k < 3; k++) pos[k] = xpos[3 * p + k] + t[k];
-      quat_mul(quat, xquat + 4 * p, (C::FULL ? c.bquat : m.body_quat) + 4 * b);
+      quat_mul(quat, xquat + 4 * p, (C::FULL ? c.bquat : (const double*)m.body_quat) + 4 * b);
       int jn = m.body_jntnum[b], j0 = m.body_jntadr[b];
 #pragma unroll (C::UF)
       for (int k = 0; k < jn; k++) {
@@ -85,11 +85,11 @@ BP_STAGE void bp_kinematics(const C& c) {
       op = DF(xipos) + 3 * w; om = DF(ximat) + 9 * w;
     } else if (w < nb + ng) {
       int g = w - nb;
-      b = m.geom_bodyid[g]; lp = (C::FULL ? c.gpos : m.geom_pos) + 3 * g; lq = m.geom_quat + 4 * g;
+      b = m.geom_bodyid[g]; lp = (C::FULL ? c.gpos : (const double*)m.geom_pos) + 3 * g; lq = m.geom_quat + 4 * g;
       op = DF(geom_xpos) + 3 * g; om = DF(geom_xmat) + 9 * g;
     } else {
       int s = w - nb - ng;
-      b = m.site_bodyid[s]; lp = (C::FULL ? c.spos : m.site_pos) + 3 * s; lq = m.site_quat + 4 * s;
+      b = m.site_bodyid[s]; lp = (C::FULL ? c.spos : (const double*)m.site_pos) + 3 * s; lq = m.site_quat + 4 * s;
       op = DF(site_xpos) + 3 * s; om = DF(site_xmat) + 9 * s;
     }
     double t[3], q[4], R[9];

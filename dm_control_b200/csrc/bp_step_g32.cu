@@ -12,13 +12,13 @@ bp_step_kernel_smem(const __grid_constant__ BpParams P) {
   for (int w = lane; w < P.L.persist; w += 32) smem[w] = g[w];
   __syncwarp();
   const float* hf = P.hfield ? P.hfield + env * (long long)P.m.nhfielddata : nullptr;
-  const double* gp = P.env_geom_pos ? P.env_geom_pos + env * 3LL * P.m.ngeom : P.m.geom_pos;
-  const double* sp = P.env_site_pos ? P.env_site_pos + env * 3LL * P.m.nsite : P.m.site_pos;
-  const double* bp = P.env_body_pos ? P.env_body_pos + env * 3LL * P.m.nbody : P.m.body_pos;
-  const double* bq = P.env_body_quat ? P.env_body_quat + env * 4LL * P.m.nbody : P.m.body_quat;
+  const double* gp = P.env_geom_pos ? P.env_geom_pos + env * 3LL * P.m.ngeom : (const double*)P.m.geom_pos;
+  const double* sp = P.env_site_pos ? P.env_site_pos + env * 3LL * P.m.nsite : (const double*)P.m.site_pos;
+  const double* bp = P.env_body_pos ? P.env_body_pos + env * 3LL * P.m.nbody : (const double*)P.m.body_pos;
+  const double* bq = P.env_body_quat ? P.env_body_quat + env * 4LL * P.m.nbody : (const double*)P.m.body_quat;
   Ctx<32, 1> c{P, smem, (int*)(smem + P.L.ints), lane, 0xffffffffu, true, false, nullptr, hf,
                gp, sp, bp, bq,
-               P.env_wrap_prm ? P.env_wrap_prm + env * (long long)P.env_wrap_n : P.m.wrap_prm};
+               P.env_wrap_prm ? P.env_wrap_prm + env * (long long)P.env_wrap_n : (const double*)P.m.wrap_prm};
   bp_load_ctrl(c, env);
   bp_run_mode(c);
   __syncwarp();

@@ -91,6 +91,25 @@ enum { BP_MODE_STEP = 0, BP_MODE_FORWARD = 1, BP_MODE_STEP1 = 2,
 //                coefficient for tendon transmissions)
 #define BP_MODEL_DERIVED_F64_ARRAYS(X) X(dof_actcoef)
 
+// Read-only model array: element reads go through the non-coherent path (ld.global.nc), which
+// also tells the compiler that stores to an env's image cannot alias them.
+template <class T>
+struct BpRO {
+  const T* p;
+  BpRO() = default;
+  __host__ __device__ BpRO(const T* q) : p(q) {}
+#ifdef __CUDA_ARCH__
+  __device__ __forceinline__ T operator[](int i) const { return __ldg(p + i); }
+  __device__ __forceinline__ T operator[](long long i) const { return __ldg(p + i); }
+#else
+  T operator[](int i) const { return p[i]; }
+  T operator[](long long i) const { return p[i]; }
+#endif
+  __host__ __device__ operator const T*() const { return p; }
+  __host__ __device__ BpRO operator+(long long i) const { return BpRO(p + i); }
+  __host__ __device__ BpRO operator+(int i) const { return BpRO(p + i); }
+};
+
 struct BpModel {
 #define X(n) int n;
   BP_MODEL_INT_SCALARS(X)
@@ -98,11 +117,11 @@ struct BpModel {
 #define X(n) double n;
   BP_MODEL_F64_SCALARS(X)
 #undef X
-#define X(n) const int* n;
+#define X(n) BpRO<int> n;
   BP_MODEL_INT_ARRAYS(X)
   BP_MODEL_DERIVED_INT_ARRAYS(X)
 #undef X
-#define X(n) const double* n;
+#define X(n) BpRO<double> n;
   BP_MODEL_F64_ARRAYS(X)
   BP_MODEL_DERIVED_F64_ARRAYS(X)
 #undef X
