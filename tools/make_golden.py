@@ -217,7 +217,89 @@ def ref_test_humanoid_model():
   print("model_ref_test_humanoid.npz solver", int(m.opt_solver), "integrator", int(m.opt_integrator))
 
 
+def suite_tasks_fixture():
+  """suite_tasks.json -- what the reference's own suite modules declare for every task, read
+  from their source with `ast` (the modules cannot be imported: they load the MuJoCo
+  binary): time limit and control timestep of each `@SUITE.add` function, and the
+  observation keys every Task class assigns in `get_observation`, in source order."""
+  import ast
+  import json
+  suite_dir = "/root/reference/dm_control/suite"
+
+  def resolve(node, consts):
+    if node is None:
+      return None
+    if isinstance(node, ast.Name):
+      return consts.get(node.id, node.id)
+    try:
+      return ast.literal_eval(node)
+    except Exception:
+      return ast.unparse(node)
+
+  def obs_keys(fn):
+    keys = []
+    for sub in ast.walk(fn):
+      if (isinstance(sub, ast.Subscript) and isinstance(sub.value, ast.Name) and
+          sub.value.id == "obs" and isinstance(sub.ctx, ast.Store)):
+        try:
+          keys.append((sub.lineno, ast.literal_eval(sub.slice)))
+        except Exception:
+          pass
+    return [k for _, k in sorted(keys)]
+
+  res = {}
+  for f in sorted(os.listdir(suite_dir)):
+    if not f.endswith(".py") or f.startswith("_") or f.endswith("_test.py"):
+      continue
+    tree = ast.parse(open(os.path.join(suite_dir, f)).read())
+    consts = {}
+    for n in tree.body:
+      if isinstance(n, ast.Assign) and len(n.targets) == 1 and isinstance(n.targets[0], ast.Name):
+        try:
+          consts[n.targets[0].id] = ast.literal_eval(n.value)
+        except Exception:
+          if ast.unparse(n.value) == "float('inf')":
+            consts[n.targets[0].id] = "inf"
+    tasks, obs = {}, {}
+    helpers = {n.name: obs_keys(n) for n in tree.body
+               if isinstance(n, ast.FunctionDef) and obs_keys(n)}
+    for n in tree.body:
+      if isinstance(n, ast.FunctionDef) and any(
+          isinstance(d, ast.Call) and getattr(d.func, "attr", "") == "add"
+          for d in n.decorator_list):
+        tl = ct = None
+        for a, d in zip(n.args.args[::-1], n.args.defaults[::-1]):
+          if a.arg == "time_limit":
+            tl = resolve(d, consts)
+        envs = [c for c in ast.walk(n)
+                if isinstance(c, ast.Call) and getattr(c.func, "attr", "") == "Environment"]
+        if not envs:      # built by a module-level helper (swimmer._make_swimmer)
+          envs = [c for c in ast.walk(tree)
+                  if isinstance(c, ast.Call) and getattr(c.func, "attr", "") == "Environment"]
+        for c in envs:
+          for k in c.keywords:
+            if k.arg == "control_timestep":
+              ct = resolve(k.value, consts)
+        tasks[n.name] = {"time_limit": tl, "control_timestep": ct}
+      if isinstance(n, ast.ClassDef):
+        for m in n.body:
+          if isinstance(m, ast.FunctionDef) and m.name == "get_observation":
+            keys = obs_keys(m)
+            # observations started by a module-level helper (quadruped._common_observations)
+            for sub in ast.walk(m):
+              if isinstance(sub, ast.Call) and isinstance(sub.func, ast.Name) and \
+                  sub.func.id in helpers:
+                keys = helpers[sub.func.id] + keys
+            obs[n.name] = keys
+    if tasks:
+      res[f[:-3]] = {"tasks": tasks, "observations": obs}
+  with open(os.path.join(OUT, "suite_tasks.json"), "w") as fh:
+    json.dump(res, fh, indent=1, sort_keys=True)
+  print("suite_tasks.json", sum(len(v["tasks"]) for v in res.values()), "tasks of", len(res), "modules")
+
+
 if __name__ == "__main__":
+  suite_tasks_fixture()
   randomizers_fixture()
   ref_test_humanoid_model()
   os.makedirs(OUT, exist_ok=True)
