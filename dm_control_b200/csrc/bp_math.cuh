@@ -113,8 +113,15 @@ static __device__ long long bp_timeline_prev;
     if (blockIdx.x == 0 && threadIdx.x == 0) { long long t = clock64(); \
       bp_timeline[id] += (unsigned long long)(t - bp_timeline_prev); bp_timeline[16 + (id)]++; \
       bp_timeline_prev = t; } } } while (0)
+// finer stamps inside the solver: cycles of block 0's first group between consecutive BP_TL
+static __device__ unsigned long long bp_tl2[64];
+static __device__ long long bp_tl2_prev;
+#define BP_TL(slot) do { if (blockIdx.x == 0 && threadIdx.x == 0) { long long t_ = clock64(); \
+    if ((slot) >= 0) { bp_tl2[slot] += (unsigned long long)(t_ - bp_tl2_prev); bp_tl2[32 + (slot)]++; } \
+    bp_tl2_prev = t_; } } while (0)
 #else
 #define BP_LOCK(id) do { if (((BP_LOCKMASK) >> (id) & 1) && c.lock) __syncthreads(); } while (0)
+#define BP_TL(slot) do { } while (0)
 #endif
 #define RUN(call) do { if (c.act) { call; } } while (0)
 

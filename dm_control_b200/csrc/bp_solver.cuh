@@ -572,9 +572,12 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, int ntenlim,
   for (int i = c.lane; i < nv; i += C::G) Mgrad[i] = grad[i];
   if (!refactor) {            // same active set as last time: H and its factor stand
     SYNC();
+    BP_TL(-1);
     bp_chol_solve(c, H, Hdinv, Mgrad, false);
+    BP_TL(8);
     return;
   }
+  BP_TL(-1);
   bp_copy(c, H, Md, ntri);
   for (int i = c.lane; i < nv; i += C::G) H[ntri + i] = grad[i];     // bordered rhs row
   SYNC();
@@ -601,6 +604,7 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, int ntenlim,
     }
   }
   SYNC();
+  BP_TL(4);
   const int ncon = IF(ncon)[0];
 #pragma unroll 1
   for (int ci = 0; ci < ncon; ci++) {
@@ -653,6 +657,7 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, int ntenlim,
     }
   }
   if constexpr (C::FULL) if (m.opt_cone == 1) bp_cone_hessian(c, H, nefc);
+  BP_TL(5);
   if (!bp_chol_factor(c, H, Hdinv)) {
     SYNC();
     bp_copy(c, H, Md, ntri);
@@ -660,7 +665,9 @@ BP_STAGE void bp_newton_gradient(const C& c, int nefc, int nsingle, int ntenlim,
     SYNC();
     bp_chol_factor(c, H, Hdinv);
   }
+  BP_TL(6);
   bp_chol_solve(c, H, Hdinv, Mgrad, bp_chol_fused<C>(nv));
+  BP_TL(7);
 }
 
 // CG [MJ-doc A.9]: the primal gradient preconditioned by the sparse factor of M
@@ -878,9 +885,12 @@ BP_STAGE void bp_solver_step(const C& c, BpSolve& st) {
   const int nv = m.nv, nefc = st.nefc;
   auto qacc = DF(qacc), Ma = DF(s_Ma), jar = DF(s_jar), search = DF(s_search);
   const double scale = 1.0 / (m.stat_meaninertia * (nv > 1 ? nv : 1));
+  BP_TL(-1);
   bp_mul_md(c, DF(s_Md), DF(s_Mv), search);
   bp_mul_j(c, DF(s_jv), search, c.null(), nefc);
+  BP_TL(0);
   double alpha = bp_linesearch(c, scale, nefc);
+  BP_TL(1);
   if (alpha == 0) { st.done = true; return; }
   for (int i = c.lane; i < nv; i += C::G) {
     qacc[i] += alpha * search[i];
@@ -898,7 +908,9 @@ BP_STAGE void bp_solver_step(const C& c, BpSolve& st) {
     SYNC();
   }
   st.cost = bp_update_constraint(c, jar, nefc, true, &changed) + bp_gauss_cost(c);
+  BP_TL(2);
   double gn = bp_newton_grad(c);
+  BP_TL(3);
   st.improvement = scale * (old - st.cost); st.gradient = scale * sqrt(gn);
   st.iter++;
   st.stale |= changed;

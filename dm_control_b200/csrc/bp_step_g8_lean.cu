@@ -5,3 +5,12 @@
 extern "C" int bp_launch_step_g8_lean(const BpParams* P, cudaStream_t stream) {
   return bp_launch_gmem<8, 1, 1>(P, stream);
 }
+
+#ifdef BP_TIMELINE
+extern "C" int bp_debug_tl2_g8_lean(unsigned long long* out, int reset) {
+  cudaDeviceSynchronize();
+  cudaMemcpyFromSymbol(out, bp_tl2, sizeof(unsigned long long) * 64);
+  if (reset) { unsigned long long z[64] = {0}; cudaMemcpyToSymbol(bp_tl2, z, sizeof(z)); }
+  return 0;
+}
+#endif
