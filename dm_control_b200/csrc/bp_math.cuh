@@ -95,7 +95,13 @@ __device__ __forceinline__ decltype(auto) bp_lv(const C& c) {
 // solver arrays that live in the shared-memory arena when there is one (S == 1 only)
 #define HOT(f, off) ((C::S == 1 && c.hot) ? typename C::DP{c.hot + (off)} : DF(f))
 #define SYNC() do { if (C::G > 1) __syncwarp(c.mask); } while (0)
+#if defined(BP_STAGE_FORCE_INLINE)
+#define BP_STAGE template <class C> __device__ __forceinline__
+#elif defined(BP_STAGE_AUTO_INLINE)  // static instances: inlining of the stage functions left to the compiler
+#define BP_STAGE template <class C> __device__
+#else
 #define BP_STAGE template <class C> __device__ __noinline__
+#endif
 // Stage boundary of the lock-step shapes: every thread of the block (active or not)
 // arrives, so the block's warps execute the same stage -- and share its instruction
 // cache lines -- at the same time.  Only in code whose trip count is uniform per launch.
