@@ -12,10 +12,17 @@
 #include "bp_types.h"
 #include <type_traits>
 
-template <class T, int S>
+// GL: the pointer is known to address global memory (the images of a static instance: no
+// shared-memory arena, no shared-memory image), which lets the compiler emit LDG / STG instead
+// of generic LD / ST.
+template <class T, int S, bool GL = false>
 struct SP {
   T* p;
-  __device__ __forceinline__ T& operator[](int i) const { return p[(long long)i * S]; }
+  __device__ __forceinline__ T& operator[](int i) const {
+    T* q = p + (long long)i * S;
+    if constexpr (GL) __builtin_assume(__isGlobal(q));
+    return *q;
+  }
   __device__ __forceinline__ SP operator+(int n) const { return SP{p + (long long)n * S}; }
   __device__ __forceinline__ bool valid() const { return p != nullptr; }
 };
@@ -58,8 +65,8 @@ struct Ctx {
 #define BP_UF 1
 #endif
   static constexpr int UF = STATIC ? BP_UF : 1;  // unroll factor of structural loops
-  using DP = SP<double, S_>;
-  using IP = SP<int, S_>;
+  using DP = SP<double, S_, STATIC>;
+  using IP = SP<int, S_, STATIC>;
   const BpParams& P;
   double* sm;      // element 0 of this env's image
   int* ip;         // element 0 of the int32 region
@@ -97,10 +104,13 @@ __device__ __forceinline__ decltype(auto) bp_lv(const C& c) {
 #define SYNC() do { if (C::G > 1) __syncwarp(c.mask); } while (0)
 #if defined(BP_STAGE_FORCE_INLINE)
 #define BP_STAGE template <class C> __device__ __forceinline__
+#define BP_STAGE_NOINLINE
 #elif defined(BP_STAGE_AUTO_INLINE)  // static instances: inlining of the stage functions left to the compiler
 #define BP_STAGE template <class C> __device__
+#define BP_STAGE_NOINLINE
 #else
 #define BP_STAGE template <class C> __device__ __noinline__
+#define BP_STAGE_NOINLINE __noinline__
 #endif
 // Stage boundary of the lock-step shapes: every thread of the block (active or not)
 // arrives, so the block's warps execute the same stage -- and share its instruction

@@ -105,7 +105,7 @@ BP_STAGE void bp_kinematics(const C& c) {
 // vals[b*n .. b*n+n) += sum over children, from the deepest level up to `stop_level`
 // (stop_level = 0 also accumulates into the world body, 1 leaves it untouched)
 template <int n, class C>
-__device__ __noinline__ void bp_tree_gather(const C& c, typename C::DP vals, int stop_level) {
+__device__ BP_STAGE_NOINLINE void bp_tree_gather(const C& c, typename C::DP vals, int stop_level) {
   BP_MODEL(m);
 #pragma unroll (C::UF)
   for (int lev = m.nlevel - 2; lev >= stop_level; lev--) {
