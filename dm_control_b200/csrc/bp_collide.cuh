@@ -584,7 +584,7 @@ static __device__ __noinline__ int col_box_box(const double* pa, const double* R
 // registers (p = centre, z = local z axis, R2 = full frame of geom 2 for boxes).
 // Returns the number of raw contacts written to out[0..3].
 template <int SHAPE>
-static __device__ __noinline__ int bp_collide_prims(int t1, int t2, const double* p1,
+static __device__ BP_STAGE_NOINLINE int bp_collide_prims(int t1, int t2, const double* p1,
                                                     const double* z1, const double* s1,
                                                     const double* p2, const double* z2,
                                                     const double* R2, const double* s2,

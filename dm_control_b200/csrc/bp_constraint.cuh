@@ -9,7 +9,7 @@
 // one shared copy of pow(): the inlined expansion is ~200 instructions per call site
 static __device__ __noinline__ double bp_pow(double x, double p) { return pow(x, p); }
 
-static __device__ __noinline__ void bp_impedance(const double* si, double pos, double margin,
+static __device__ BP_STAGE_NOINLINE void bp_impedance(const double* si, double pos, double margin,
                                                  double* imp, double* impP) {
   if (si[0] == si[1] || si[2] <= BP_MINVAL) { *imp = 0.5 * (si[0] + si[1]); *impP = 0; return; }
   double x = (pos - margin) / si[2], sgn = 1;
