@@ -75,9 +75,9 @@ WORKLOADS = {"cheetah-run": dict(nenv=16384, njmax=64, nconmax=16, settle=200, l
              "quadruped-walk": dict(nenv=8192, njmax=120, nconmax=40, settle=100, lanes=16)}
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the step kernel from the
 # committed `ncu --set full` captures (profiles/), keyed by (task, lanes, envs per GPU)
-NCU_TRAFFIC = {("cheetah-run", 8, 16384): (433.2e6, "profiles/r2z_static_cheetah_g8.summary.txt"),
+NCU_TRAFFIC = {("cheetah-run", 8, 16384): (375.1e6, "profiles/r2z_static_cheetah_g8.summary.txt"),
                ("cheetah-run", 4, 16384): (345.5e6, "profiles/r1g_cheetah_g4.summary.txt"),
-               ("humanoid-run", 16, 8192): (4.498e9, "profiles/r2z_static_humanoid_g16.summary.txt"),
+               ("humanoid-run", 16, 8192): (4.317e9, "profiles/r2z_static_humanoid_g16.summary.txt"),
                ("humanoid-run", 8, 8192): (5.531e9, "profiles/r1g_humanoid_g8.summary.txt")}
 
 
