@@ -22,29 +22,66 @@ ALL_TASKS = T.ALL_TASKS
 BENCHMARKING = T.ALL_TASKS
 
 
-def _randomize_limited_and_rotational_joints(m, qpos, rng):
-  """suite/utils/randomizers.py:35-86 for one env (qpos: [nq], edited in place)."""
+_RANDOMIZER_PLANS = {}
+
+
+def _randomizer_plan(m):
+  """The draws of randomizers.py:35-86 for one model, in joint order, with runs of consecutive
+  scalar uniform draws (limited hinge / slide joints, unlimited hinges) merged into one
+  vectorised `uniform(lo, hi)` call: RandomState.uniform with array bounds computes
+  lo + (hi - lo) * random_sample() element by element from the same stream, so the values
+  equal those of the reference's one-call-per-joint loop bit for bit (pinned by
+  tests/test_golden_cpu.py against the reference's own randomizers.py)."""
+  # cached per model; `set_model_field` replaces the edited array object, which invalidates it
+  a = m.arrays
+  key = (a["jnt_range"], a["jnt_limited"], a["jnt_type"])
+  plan = _RANDOMIZER_PLANS.get(id(m))
+  if plan is not None and plan[0] is m and all(x is y for x, y in zip(plan[1], key)):
+    return plan[2]
+  ops, run = [], []
+
+  def flush():
+    if run:
+      ops.append(("u", np.array([r[0] for r in run]), np.array([r[1] for r in run]),
+                  np.array([r[2] for r in run])))
+      del run[:]
   for j in range(m.njnt):
-    jt, qa = m.jnt_type[j], m.jnt_qposadr[j]
-    lo, hi = m.jnt_range[j]
+    jt, qa = int(m.jnt_type[j]), int(m.jnt_qposadr[j])
+    lo, hi = (float(x) for x in m.jnt_range[j])
     if m.jnt_limited[j]:
       if jt in (M.JNT_HINGE, M.JNT_SLIDE):
-        qpos[qa] = rng.uniform(lo, hi)
-      elif jt == M.JNT_BALL:     # randomizers.py:23-33 random_limited_quaternion
-        axis = rng.randn(3)
-        axis /= np.linalg.norm(axis)
-        angle = rng.rand() * hi
-        qpos[qa] = np.cos(angle / 2)             # mju_axisAngle2Quat
-        qpos[qa + 1:qa + 4] = axis * np.sin(angle / 2)
-    else:
-      if jt == M.JNT_HINGE:
-        qpos[qa] = rng.uniform(-np.pi, np.pi)
+        run.append((qa, lo, hi))
       elif jt == M.JNT_BALL:
-        q = rng.randn(4)
-        qpos[qa:qa + 4] = q / np.linalg.norm(q)
-      elif jt == M.JNT_FREE:
-        q = rng.rand(4)
-        qpos[qa + 3:qa + 7] = q / np.linalg.norm(q)
+        flush(); ops.append(("ball_limited", qa, hi))
+    elif jt == M.JNT_HINGE:
+      run.append((qa, -np.pi, np.pi))
+    elif jt == M.JNT_BALL:
+      flush(); ops.append(("ball", qa))
+    elif jt == M.JNT_FREE:
+      flush(); ops.append(("free", qa))
+  flush()
+  _RANDOMIZER_PLANS[id(m)] = (m, key, ops)
+  return ops
+
+
+def _randomize_limited_and_rotational_joints(m, qpos, rng):
+  """suite/utils/randomizers.py:35-86 for one env (qpos: [nq], edited in place)."""
+  for op in _randomizer_plan(m):
+    kind, qa = op[0], op[1]
+    if kind == "u":
+      qpos[qa] = rng.uniform(op[2], op[3])
+    elif kind == "ball_limited":     # randomizers.py:23-33 random_limited_quaternion
+      axis = rng.randn(3)
+      axis /= np.linalg.norm(axis)
+      angle = rng.rand() * op[2]
+      qpos[qa] = np.cos(angle / 2)             # mju_axisAngle2Quat
+      qpos[qa + 1:qa + 4] = axis * np.sin(angle / 2)
+    elif kind == "ball":
+      q = rng.randn(4)
+      qpos[qa:qa + 4] = q / np.linalg.norm(q)
+    else:                            # free joint: a random orientation, position untouched
+      q = rng.rand(4)
+      qpos[qa + 3:qa + 7] = q / np.linalg.norm(q)
 
 
 class Task:

@@ -90,9 +90,12 @@ def test_split_pipeline_bit_identical(domain, lanes, seg_g, monkeypatch):
   names = ["qpos", "qvel", "qacc", "qacc_warmstart", "sensordata", "efc_force", "xpos",
            "cfrc_ext", "nefc", "ncon", "solver_iter", "warning"]
   out = []
-  # the fused side is the GENERIC kernel: a static instance is compiled separately and may
-  # contract multiply-adds differently (it is held to 1e-10 of the generic kernel elsewhere)
+  # the fused side is the generic FULL kernel, i.e. the same compiled stage functions the split
+  # launches run (same translation unit): static instances and the LEAN / MID kernels are
+  # compiled with their stages inlined and may contract multiply-adds differently (they are
+  # held to the oracle and to 1e-10 of each other elsewhere)
   monkeypatch.setenv("BPHYS_NO_STATIC", "1")
+  monkeypatch.setenv("BPHYS_NO_LEAN", "1")
   for split in (False, True):
     if split:
       monkeypatch.setenv("BPHYS_SPLIT", "1")
