@@ -227,6 +227,14 @@ def run_gpu(name, nenv, steps, warmup, rank, world, device, action_scale=1.0):
       torch.distributed.barrier()
     torch.cuda.synchronize(device)
 
+  # host buffers of the end-to-end section, allocated (pinned) before anything is timed
+  rng = np.random.RandomState(7 + rank)
+  ew = max(2, warmup)
+  h_ctrl = torch.from_numpy(action_scale * rng.uniform(-1, 1, (steps + ew, nenv, nu))).pin_memory()
+  h_obs = torch.empty((nenv, nobs), dtype=torch.float64).pin_memory()
+  h_rew = torch.empty((nenv,), dtype=torch.float64).pin_memory()
+  hc, ho, hr = h_ctrl.numpy(), h_obs.numpy(), h_rew.numpy()
+
   # ---- device-resident timing (value) ---------------------------------------------
   ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
   kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
@@ -249,19 +257,20 @@ def run_gpu(name, nenv, steps, warmup, rank, world, device, action_scale=1.0):
   # every step's actions wait in pinned host memory (one [nenv][nu] buffer per step); the
   # timed region is the public host call: H2D of that buffer, the fused step, D2H of
   # observations and rewards into pinned host buffers, stream synchronisation
-  rng = np.random.RandomState(7 + rank)
-  h_ctrl = torch.from_numpy(action_scale * rng.uniform(-1, 1, (steps + 2, nenv, nu))).pin_memory()
-  h_obs = torch.empty((nenv, nobs), dtype=torch.float64).pin_memory()
-  h_rew = torch.empty((nenv,), dtype=torch.float64).pin_memory()
-  hc, ho, hr = h_ctrl.numpy(), h_obs.numpy(), h_rew.numpy()
-  for k in range(2):
+  for k in range(ew):
     batch.env_step_host(nsub, hc[k], ho, hr)
   barrier()
   t0 = time.perf_counter()
+  _ts = []
   for k in range(steps):
-    batch.env_step_host(nsub, hc[2 + k], ho, hr)
+    _t = time.perf_counter()
+    batch.env_step_host(nsub, hc[ew + k], ho, hr)
+    _ts.append((time.perf_counter() - _t) * 1e6)
   torch.cuda.synchronize(device)
   e2e_s = time.perf_counter() - t0
+  if os.environ.get("BENCH_E2E_TRACE"):
+    print("e2e per-step us:", " ".join("%.0f" % t for t in _ts), "total %.0f" % (e2e_s * 1e6), file=sys.stderr)
+    print("device-resident kernel us:", " ".join("%.0f" % (a.elapsed_time(b) * 1e3) for a, b in kev), file=sys.stderr)
   barrier()
   warn = batch.warnings().sum(axis=0)
   finite = bool(np.all(np.isfinite(ho)) and np.all(np.isfinite(hr)))
