@@ -156,3 +156,34 @@ def test_model_binary_roundtrip(tmp_path):
     M.FlatModel.from_byte_string(b"MJB\0" + b"\0" * 64)
   with pytest.raises(ValueError):
     M.FlatModel.from_byte_string(m.to_blob())          # blob without its name table
+
+
+def test_committed_static_headers_match_the_library(tmp_path):
+  """csrc/static/<model>.cuh are GENERATED by the library's own bp_static_header (host-only)
+  through tools/gen_static_model.py; a layout or derivation change without regenerating them
+  would leave instances that no longer match any live model (their hash / layout check would
+  send every launch to the generic kernels).  Regenerate into a scratch directory and compare,
+  and check that suite.load's default sizes are the ones the instances were generated for."""
+  import ctypes
+  import importlib.util
+  root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+  spec = importlib.util.spec_from_file_location("gen_static", os.path.join(root, "tools",
+                                                                           "gen_static_model.py"))
+  gen = importlib.util.module_from_spec(spec)
+  spec.loader.exec_module(gen)
+  lib = ctypes.CDLL(binding.lib_path())
+  lib.bp_static_header.argtypes = [ctypes.c_char_p, ctypes.c_int64, ctypes.c_int, ctypes.c_int,
+                                   ctypes.c_char_p, ctypes.c_char_p]
+  for name, (model, njmax, nconmax) in gen.TRAITS.items():
+    blob = PU.load_model(model).to_blob()
+    out = str(tmp_path / (name + ".cuh"))
+    assert lib.bp_static_header(blob, len(blob), njmax, nconmax, name.encode(), out.encode()) == 0
+    committed = os.path.join(root, "dm_control_b200", "csrc", "static", name + ".cuh")
+    assert open(out).read() == open(committed).read(), \
+        "%s is stale: run tools/gen_static_model.py and rebuild" % committed
+    assert T.STATIC_SIZES[model] == (njmax, nconmax)
+  for name, lanes, _ in gen.INSTANCES:
+    assert os.path.exists(os.path.join(root, "dm_control_b200", "csrc",
+                                       "bp_static_%s_g%d.cu" % (name, lanes)))
+    if lanes == 1:
+      assert T.STATIC_LANES[gen.TRAITS[name][0]] == 1
