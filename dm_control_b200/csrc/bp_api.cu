@@ -1094,8 +1094,7 @@ extern "C" int bp_env_step_host(bp_batch* b, int nsub, const double* ctrl_host,
   int eb = ensure_task_buffers(b, nobs);
   if (eb != BP_OK) return eb;
   // A pinned (mapped) host control buffer is read by the kernel itself over PCIe instead
-  // of being staged by a copy (BPHYS_NO_ZEROCOPY=1 turns that off).  (Writing observations straight to host
-  // memory was measured too: 8-byte PCIe writes, 18.2 M vs 22.2 M cheetah env-steps/s.)
+  // of being staged by a copy (BPHYS_NO_ZEROCOPY=1 turns that off).
   static const bool zerocopy = getenv("BPHYS_NO_ZEROCOPY") == nullptr;
   const double* ctrl_src = b->ctrl_stage;
   if (zerocopy && nu > 0) {
